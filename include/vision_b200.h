@@ -1,0 +1,113 @@
+/* vision_b200.h — C ABI of libvision_b200.so (sm_100a CUDA behind it).
+ *
+ * This boundary replaces the reference's compute/RHI layer for the megakernel path-tracing hot
+ * path: the (absent, un-vendored) ocarina DSL codegen + OptiX dispatch that Vision reaches through
+ *   Device::create_mesh / RHIMesh::build_bvh / Accel::add_instance / Accel::build_bvh
+ *                                   reference src/base/mgr/geometry.cpp:36-53
+ *   Accel::trace_closest / trace_occlusion      reference src/base/mgr/geometry.cpp:168-174
+ *   Shader dispatch of "rt_geom", "path_tracing", "RGBFilm-accumulation", "RGBFilm-tone_mapping"
+ *                                   reference src/base/sensor/frame_buffer.cpp:156-219,117-144
+ *                                   reference src/base/integral/integrator.cpp:82-107
+ *   Managed<T>::upload_immediately / download_immediately
+ *                                   reference src/base/mgr/geometry.cpp:64-71, frame_buffer.cpp:424-427
+ *
+ * Conventions: every function returns int status (VB_OK = 0). vb_last_error(ctx) returns a
+ * NUL-terminated message owned by the context (valid until the next call on that context).
+ * One context per GPU. Calls on one context are not re-entrant; different contexts may be driven
+ * from different host threads. Pointers are caller-owned; each pointer argument that may be either
+ * host or device memory travels with a vb_mem tag. No C++ or torch types cross this boundary.
+ */
+#ifndef VISION_B200_H
+#define VISION_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VB_API __attribute__((visibility("default")))
+
+typedef struct vb_ctx vb_ctx;
+
+enum { VB_OK = 0, VB_ERR_INVALID = 1, VB_ERR_CUDA = 2, VB_ERR_STATE = 3, VB_ERR_UNSUPPORTED = 4 };
+typedef enum { VB_MEM_HOST = 0, VB_MEM_DEVICE = 1 } vb_mem;
+
+#define VB_INVALID_ID 0xffffffffu
+
+/* ---- lifecycle ------------------------------------------------------------------------- */
+VB_API int vb_ctx_create(int device, vb_ctx **out);
+VB_API int vb_ctx_destroy(vb_ctx *ctx);
+VB_API const char *vb_last_error(vb_ctx *ctx);           /* ctx may be NULL: last create error */
+/* run all work of this context on an existing cudaStream_t (e.g. torch's current stream), so
+ * the caller's CUDA events bracket it; NULL restores the context's own stream */
+VB_API int vb_ctx_set_stream(vb_ctx *ctx, void *cuda_stream);
+VB_API int vb_ctx_synchronize(vb_ctx *ctx);
+/* device time (ms, CUDA events on the launching stream) and launch count of the kernels this
+ * library launched since the last vb_profile_reset; name = "trace_closest" | "trace_any" |
+ * "path_trace" | "bvh_build" | "film" | "all" */
+VB_API int vb_profile_reset(vb_ctx *ctx);
+VB_API int vb_profile_get(vb_ctx *ctx, const char *name, double *ms, uint64_t *launches);
+
+/* ---- geometry: replaces Geometry::upload + Geometry::build_accel -------------------------- */
+/* Mesh = the reference's vision::Mesh (src/base/shape.h:78-112): vertices (pos, normal, uv) and
+ * Triangle{i,j,k}. Triangle order defines prim_id. nrm3 / uv2 may be NULL (zeros). */
+VB_API int vb_mesh_upload(vb_ctx *ctx, const float *pos3, const float *nrm3, const float *uv2, uint32_t nv,
+                          const uint32_t *tri3, uint32_t nt, uint32_t *mesh_id);
+/* non-indexed triangle soup already resident on host or device: triangle i = vertices 3i..3i+2 */
+VB_API int vb_mesh_upload_soup(vb_ctx *ctx, const float *pos9, vb_mem mem, uint64_t nt, uint32_t *mesh_id);
+
+/* InstanceData of the reference (src/base/shape.h:21-33): encoded ids + object-to-world.
+ * o2w is column-major 4x4 (m[3] = translation), as the reference's float4x4. Array index = inst_id. */
+typedef struct vb_instance {
+    uint32_t mesh_id;
+    uint32_t material_id;      /* index into vb_materials_set table, VB_INVALID_ID = none */
+    uint32_t light_id;         /* index into vb_lights_set table,    VB_INVALID_ID = none */
+    uint32_t inside_medium;    /* VB_INVALID_ID = none */
+    uint32_t outside_medium;
+    uint32_t lightmap_id;      /* carried, unused by the PT path */
+    float o2w[16];
+} vb_instance;
+VB_API int vb_instances_set(vb_ctx *ctx, const vb_instance *inst, uint32_t n);
+
+typedef struct vb_build_opts {
+    uint32_t flags;            /* reserved, 0 */
+} vb_build_opts;
+typedef struct vb_build_stats {
+    uint64_t n_triangles;      /* flattened world-space triangles */
+    uint64_t n_nodes;          /* 80-byte wide nodes */
+    uint64_t node_bytes, tri_bytes;
+    double build_ms;           /* device time of the whole build */
+    float scene_lo[3], scene_hi[3];
+} vb_build_stats;
+/* flattens instances to world space, builds the compressed 8-wide BVH on the GPU */
+VB_API int vb_accel_build(vb_ctx *ctx, const vb_build_opts *opts, vb_build_stats *out);
+/* copies the built structure to host (test/diagnostic surface): nodes = n_nodes*80 bytes,
+ * tris = n_triangles*48 bytes (float4 v0|prim, e1|inst, e2|0). Either pointer may be NULL. */
+VB_API int vb_accel_download(vb_ctx *ctx, void *nodes, void *tris);
+
+/* ---- batch trace: replaces Accel::trace_closest / trace_occlusion -------------------------- */
+/* SoA rays (reference Ray = {org_min, dir_max}: origin + t_min, direction + t_max) */
+typedef struct vb_rays_soa {
+    const float *ox, *oy, *oz, *tmin, *dx, *dy, *dz, *tmax;
+    vb_mem mem;
+} vb_rays_soa;
+/* SoA hits (reference TriangleHit{inst_id, prim_id, bary} + distance). Miss: inst = prim =
+ * VB_INVALID_ID, u = v = t = 0. bary: hit point = (1-u-v)*p0 + u*p1 + v*p2 */
+typedef struct vb_hits_soa {
+    uint32_t *inst, *prim;
+    float *u, *v, *t;
+    vb_mem mem;
+} vb_hits_soa;
+VB_API int vb_trace_closest(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out);
+VB_API int vb_trace_any(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, uint8_t *occluded, vb_mem out_mem);
+/* instrumented variants (never timed): per-call totals of wide nodes popped and triangles tested */
+VB_API int vb_trace_closest_counted(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out,
+                                    uint64_t *nodes_popped, uint64_t *tris_tested);
+VB_API int vb_trace_any_counted(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, uint8_t *occluded, vb_mem out_mem,
+                                uint64_t *nodes_popped, uint64_t *tris_tested);
+
+#include "vision_b200_pt.h"
+
+#ifdef __cplusplus
+}
+#endif
+#endif

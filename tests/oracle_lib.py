@@ -1,0 +1,118 @@
+"""ctypes binding of oracle/liboracle.so - the CPU checker. Test infrastructure only."""
+from __future__ import annotations
+
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+LIB = ROOT / "oracle" / "liboracle.so"
+
+RAY_FIELDS = ("ox", "oy", "oz", "tmin", "dx", "dy", "dz", "tmax")
+_lib = None
+
+
+def build():
+    subprocess.run(["make", "-C", str(ROOT / "oracle")], check=True, capture_output=True)
+
+
+def load() -> "Oracle":
+    global _lib
+    if _lib is None:
+        if not LIB.exists():
+            build()
+        _lib = Oracle(C.CDLL(str(LIB)))
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Oracle:
+    def __init__(self, lib):
+        self.lib = lib
+        vp = C.c_void_p
+        lib.vo_hw_threads.restype = C.c_int
+        lib.vo_synth_mesh.argtypes = [C.c_uint64, C.c_uint64, vp, C.c_int]
+        lib.vo_synth_mesh.restype = None
+        lib.vo_synth_rays.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64] + [vp] * 9 + [C.c_int]
+        lib.vo_synth_rays.restype = None
+        lib.vo_accel_create.restype = vp
+        lib.vo_accel_destroy.argtypes = [vp]
+        lib.vo_accel_add_instance.argtypes = [vp, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32]
+        lib.vo_accel_add_instance.restype = None
+        lib.vo_accel_add_soup.argtypes = [vp, vp, C.c_uint64, C.c_uint32]
+        lib.vo_accel_add_soup.restype = None
+        lib.vo_accel_build.argtypes = [vp, C.c_int]
+        lib.vo_accel_build.restype = C.c_double
+        lib.vo_accel_num_nodes.argtypes = [vp]
+        lib.vo_accel_num_nodes.restype = C.c_uint64
+        lib.vo_trace_closest.argtypes = [vp, C.c_uint64] + [vp] * 8 + [vp] * 5 + [C.c_int, C.c_int, vp]
+        lib.vo_trace_closest.restype = C.c_double
+        lib.vo_trace_any.argtypes = [vp, C.c_uint64] + [vp] * 8 + [vp, C.c_int, C.c_int, vp]
+        lib.vo_trace_any.restype = C.c_double
+
+    def hw_threads(self) -> int:
+        return self.lib.vo_hw_threads()
+
+    def synth_mesh(self, n: int, seed: int = 1, threads: int = 8) -> np.ndarray:
+        out = np.empty((n, 9), np.float32)
+        self.lib.vo_synth_mesh(seed, n, _p(out), threads)
+        return out
+
+    def synth_rays(self, n: int, seed: int = 2, seed_any: int = 3, threads: int = 8) -> dict:
+        r = {f: np.empty(n, np.float32) for f in RAY_FIELDS + ("tmax_any",)}
+        self.lib.vo_synth_rays(seed, seed_any, n, *[_p(r[f]) for f in RAY_FIELDS], _p(r["tmax_any"]), threads)
+        return r
+
+    def accel(self) -> "OracleAccel":
+        return OracleAccel(self)
+
+
+class OracleAccel:
+    def __init__(self, o: Oracle):
+        self.o = o
+        self.h = C.c_void_p(o.lib.vo_accel_create())
+        self.build_s = 0.0
+
+    def __del__(self):
+        if self.h:
+            self.o.lib.vo_accel_destroy(self.h)
+            self.h = None
+
+    def add_instance(self, pos, tri, o2w=None, inst_id=0):
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+        tri = np.ascontiguousarray(tri, np.uint32).reshape(-1, 3)
+        m = None if o2w is None else np.ascontiguousarray(o2w, np.float32).reshape(16)
+        self.o.lib.vo_accel_add_instance(self.h, _p(pos), len(pos), _p(tri), len(tri), _p(m), inst_id)
+
+    def add_soup(self, pos9, inst_id=0):
+        pos9 = np.ascontiguousarray(pos9, np.float32)
+        self.o.lib.vo_accel_add_soup(self.h, _p(pos9), pos9.shape[0], inst_id)
+
+    def build(self, threads=8):
+        self.build_s = self.o.lib.vo_accel_build(self.h, threads)
+        return self.build_s
+
+    def trace_closest(self, rays, threads=8, brute=False, stats=False):
+        n = rays["ox"].shape[0]
+        out = {"inst": np.empty(n, np.uint32), "prim": np.empty(n, np.uint32), "u": np.empty(n, np.float32),
+               "v": np.empty(n, np.float32), "t": np.empty(n, np.float32)}
+        st = np.zeros(2, np.uint64) if stats else None
+        dt = self.o.lib.vo_trace_closest(self.h, n, *[_p(np.ascontiguousarray(rays[f])) for f in RAY_FIELDS],
+                                         *[_p(out[f]) for f in ("inst", "prim", "u", "v", "t")],
+                                         threads, 1 if brute else 0, _p(st))
+        out["seconds"] = dt
+        if stats:
+            out["stats"] = st
+        return out
+
+    def trace_any(self, rays, threads=8, brute=False):
+        n = rays["ox"].shape[0]
+        occ = np.empty(n, np.uint8)
+        dt = self.o.lib.vo_trace_any(self.h, n, *[_p(np.ascontiguousarray(rays[f])) for f in RAY_FIELDS], _p(occ),
+                                     threads, 1 if brute else 0, None)
+        return occ, dt

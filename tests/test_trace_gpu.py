@@ -1,0 +1,141 @@
+"""GPU parity: libvision_b200.so (through the C ABI) vs the oracle on the same seeded inputs.
+Bar (BASELINE.json north_star): inst_id / prim_id bit-exact; t and barycentrics <= 1e-5 relative -
+both sides implement one normative fp32 operation order, so we assert bit equality of t,u,v too."""
+import numpy as np
+import pytest
+
+from vision_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+MISS = 0xFFFFFFFF
+
+
+def _build_soup(vbctx, mesh):
+    mid = vbctx.mesh_upload_soup(mesh)
+    vbctx.instances_set([{"mesh_id": mid}])
+    return vbctx.accel_build()
+
+
+def _compare_closest(g, o):
+    assert np.array_equal(g["inst"], o["inst"]), f"inst mismatches: {(g['inst'] != o['inst']).sum()}"
+    assert np.array_equal(g["prim"], o["prim"]), f"prim mismatches: {(g['prim'] != o['prim']).sum()}"
+    hit = o["inst"] != MISS
+    for f in ("t", "u", "v"):
+        np.testing.assert_allclose(g[f][hit], o[f][hit], rtol=1e-5, atol=0)
+        assert g[f].tobytes() == o[f].tobytes(), f"{f} not bit-exact"
+
+
+@pytest.mark.parametrize("ntri", [1, 2, 3, 4, 9, 100, 20000])
+def test_closest_and_any_vs_bruteforce_oracle(vbctx, oracle, ntri):
+    mesh = oracle.synth_mesh(ntri, seed=21)
+    rays = oracle.synth_rays(20000, seed=22, seed_any=23)
+    st = _build_soup(vbctx, mesh)
+    assert st["n_triangles"] == ntri
+    acc = oracle.accel()
+    acc.add_soup(mesh)
+    acc.build(4)
+    brute = ntri <= 100
+    o = acc.trace_closest(rays, threads=8, brute=brute)
+    g = vbctx.trace_closest(rays)
+    _compare_closest(g, o)
+    any_rays = dict(rays, tmax=rays["tmax_any"])
+    oa, _ = acc.trace_any(any_rays, brute=brute)
+    ga = vbctx.trace_any(any_rays)
+    assert np.array_equal(ga, oa)
+
+
+def test_million_triangle_soup_vs_oracle_bvh(vbctx, oracle):
+    mesh = synth.synth_mesh(1_000_000, seed=1)
+    rays = synth.synth_rays(1 << 18, seed=2, seed_any=3)
+    st = _build_soup(vbctx, mesh)
+    assert st["n_triangles"] == 1_000_000
+    acc = oracle.accel()
+    acc.add_soup(mesh)
+    acc.build(oracle.hw_threads())
+    o = acc.trace_closest(rays, threads=oracle.hw_threads())
+    g, nodes, tris = vbctx.trace_closest(rays, counted=True)
+    _compare_closest(g, o)
+    assert nodes > 0 and tris > 0
+    assert (o["inst"] != MISS).mean() > 0.5
+    any_rays = dict(rays, tmax=rays["tmax_any"])
+    oa, _ = acc.trace_any(any_rays, threads=oracle.hw_threads())
+    ga = vbctx.trace_any(any_rays)
+    assert np.array_equal(ga, oa)
+    assert 0.05 < oa.mean() < 0.95
+
+
+def test_instanced_indexed_meshes_and_ties(vbctx, oracle):
+    """two instances of one indexed quad, the second translated onto the first: equal-t ties
+    resolve to the smallest (inst, prim); a third instance is rotated+scaled"""
+    pos = np.array([[-1, -1, 0], [1, -1, 0], [-1, 1, 0], [1, 1, 0]], np.float32)
+    tri = np.array([[0, 1, 2], [2, 1, 3]], np.uint32)      # reference quad order (quad.cpp:44)
+    ident = np.eye(4, dtype=np.float32).T.reshape(-1)
+    m3 = np.eye(4, dtype=np.float32)
+    c, s = np.cos(0.7), np.sin(0.7)
+    m3[:3, :3] = np.array([[c, 0, s], [0, 1, 0], [-s, 0, c]], np.float32) * 0.5
+    m3[:3, 3] = [0.1, 0.2, -0.8]
+    o2w3 = np.ascontiguousarray(m3.T).reshape(-1)           # column-major
+    mid = vbctx.mesh_upload(pos, tri)
+    vbctx.instances_set([{"mesh_id": mid, "o2w": ident}, {"mesh_id": mid, "o2w": ident}, {"mesh_id": mid, "o2w": o2w3}])
+    st = vbctx.accel_build()
+    assert st["n_triangles"] == 6
+    acc = oracle.accel()
+    for i, m in enumerate((ident, ident, o2w3)):
+        acc.add_instance(pos, tri, m, inst_id=i)
+    acc.build(1)
+    rays = oracle.synth_rays(50000, seed=31, seed_any=32)
+    o = acc.trace_closest(rays, brute=True)
+    g = vbctx.trace_closest(rays)
+    _compare_closest(g, o)
+    hit0 = o["inst"] == 0
+    assert hit0.sum() > 1000 and (o["inst"] == 1).sum() == 0     # inst 1 always loses the tie
+    assert (o["inst"] == 2).sum() > 100
+
+
+def test_ragged_and_degenerate_rays(vbctx, oracle):
+    mesh = oracle.synth_mesh(3000, seed=41)
+    _build_soup(vbctx, mesh)
+    acc = oracle.accel()
+    acc.add_soup(mesh)
+    acc.build(2)
+    rays = oracle.synth_rays(1000, seed=42, seed_any=43)
+    rays["dx"][0:10] = 0.0; rays["dy"][0:10] = 0.0; rays["dz"][0:10] = 1.0      # axis-aligned
+    rays["dx"][10:20] = 0.0; rays["dy"][10:20] = 0.0; rays["dz"][10:20] = 0.0   # zero direction
+    rays["tmax"][20:30] = 0.0                                                    # empty interval
+    rays["tmin"][30:40] = 0.3                                                    # t_min honoured
+    rays["dx"][40:50] *= 7.5; rays["dy"][40:50] *= 7.5; rays["dz"][40:50] *= 7.5  # un-normalised dirs
+    rays["ox"][50:55] = np.nan                                                   # NaN rays miss
+    for n in (0, 1, 31, 33, 1000):
+        sub = {k: np.ascontiguousarray(v[:n]) for k, v in rays.items()}
+        if n == 0:
+            g = vbctx.trace_closest(sub)
+            assert g["inst"].shape == (0,)
+            continue
+        o = acc.trace_closest(sub, brute=True)
+        g = vbctx.trace_closest(sub)
+        _compare_closest(g, o)
+        oa, _ = acc.trace_any(sub, brute=True)
+        assert np.array_equal(vbctx.trace_any(sub), oa)
+
+
+def test_device_resident_rays(vbctx, oracle):
+    import torch
+    mesh = oracle.synth_mesh(5000, seed=51)
+    _build_soup(vbctx, mesh)
+    rays = oracle.synth_rays(10000, seed=52, seed_any=53)
+    host = vbctx.trace_closest(rays)
+    drays = {k: torch.from_numpy(v).cuda() for k, v in rays.items()}
+    dev = vbctx.trace_closest(drays)
+    vbctx.synchronize()
+    torch.cuda.synchronize()
+    assert np.array_equal(dev["prim"].cpu().numpy().view(np.uint32), host["prim"])
+    assert dev["t"].cpu().numpy().tobytes() == host["t"].tobytes()
+
+
+def test_errors_are_reported(vbctx):
+    from vision_b200 import VbError
+    with pytest.raises(VbError):
+        vbctx.instances_set([{"mesh_id": 10_000}])
+    with pytest.raises(VbError):
+        vbctx.mesh_upload(np.zeros((3, 3), np.float32), np.array([[0, 1, 7]], np.uint32))

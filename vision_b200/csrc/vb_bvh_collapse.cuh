@@ -1,0 +1,251 @@
+// Collapse of the binary radix tree into the compressed 8-wide BVH + host driver of the build.
+// Included by vb_bvh_build.cu only.
+#pragma once
+
+namespace {
+
+struct WorkItem { uint32_t bvh2, wide; };
+struct Counters { uint32_t next_items, n_nodes, n_tris, pad; };
+
+__device__ __forceinline__ float half_area(float4 lo, float4 hi) {
+    float x = hi.x - lo.x, y = hi.y - lo.y, z = hi.z - lo.z;
+    return x * y + y * z + z * x;
+}
+
+// smallest exponent byte e (float exponent bits) with extent <= 255 * 2^(e-127)
+__device__ __forceinline__ uint32_t quant_exp(float extent) {
+    float s = extent / 255.0f;
+    uint32_t bits = __float_as_uint(s);
+    uint32_t e = (bits >> 23) & 0xffu;
+    if (bits & 0x7fffffu) e++;
+    e = max(e, 1u);
+    while (e < 254u && ceilf(extent / __uint_as_float(e << 23)) > 255.0f) e++;
+    return min(e, 254u);
+}
+
+__global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n_in, WorkItem *out, Counters *cnt,
+                                                  uint32_t T, BuildBufs b, vb_wide_node *nodes, float4 *tris_out) {
+    uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= n_in) return;
+    WorkItem it = in[w];
+    auto tri_count = [&](uint32_t x) -> uint32_t { return x >= T - 1 ? 1u : b.last[x] - b.first[x] + 1u; };
+    auto leaf_like = [&](uint32_t x) -> bool { return tri_count(x) <= 3u; };
+
+    uint32_t c[8]; int n;
+    if (leaf_like(it.bvh2)) { c[0] = it.bvh2; n = 1; }
+    else {
+        c[0] = b.left[it.bvh2]; c[1] = b.right[it.bvh2]; n = 2;
+        while (n < 8) {
+            int best = -1; float best_a = -1.f;
+            for (int j = 0; j < n; ++j) {
+                if (leaf_like(c[j])) continue;
+                float a = half_area(b.nlo[c[j]], b.nhi[c[j]]);
+                if (a > best_a) { best_a = a; best = j; }
+            }
+            if (best < 0) break;
+            uint32_t x = c[best];
+            c[best] = b.left[x]; c[n++] = b.right[x];
+        }
+    }
+    float4 nlo = b.nlo[it.bvh2], nhi = b.nhi[it.bvh2];
+    float ncx = 0.5f * (nlo.x + nhi.x), ncy = 0.5f * (nlo.y + nhi.y), ncz = 0.5f * (nlo.z + nhi.z);
+
+    // greedy child -> slot assignment: slot bit2/1/0 = child on the +x/+y/+z side
+    float ccx[8], ccy[8], ccz[8];
+    for (int j = 0; j < n; ++j) {
+        float4 lo = b.nlo[c[j]], hi = b.nhi[c[j]];
+        ccx[j] = 0.5f * (lo.x + hi.x) - ncx; ccy[j] = 0.5f * (lo.y + hi.y) - ncy; ccz[j] = 0.5f * (lo.z + hi.z) - ncz;
+    }
+    int slot_of[8]; uint32_t child_done = 0, slot_used = 0;
+    for (int iter = 0; iter < n; ++iter) {
+        int bj = -1, bs = -1; float bc = -FLT_MAX;
+        for (int j = 0; j < n; ++j) {
+            if (child_done >> j & 1) continue;
+            for (int s = 0; s < 8; ++s) {
+                if (slot_used >> s & 1) continue;
+                float cost = ((s & 4) ? ccx[j] : -ccx[j]) + ((s & 2) ? ccy[j] : -ccy[j]) + ((s & 1) ? ccz[j] : -ccz[j]);
+                if (cost > bc) { bc = cost; bj = j; bs = s; }
+            }
+        }
+        slot_of[bj] = bs; child_done |= 1u << bj; slot_used |= 1u << bs;
+    }
+    int child_in_slot[8];
+    for (int s = 0; s < 8; ++s) child_in_slot[s] = -1;
+    for (int j = 0; j < n; ++j) child_in_slot[slot_of[j]] = j;
+
+    uint32_t imask = 0, k_inner = 0, n_tri = 0;
+    for (int s = 0; s < 8; ++s) {
+        int j = child_in_slot[s];
+        if (j < 0) continue;
+        if (leaf_like(c[j])) n_tri += tri_count(c[j]); else { imask |= 1u << s; k_inner++; }
+    }
+    uint32_t child_base = k_inner ? atomicAdd(&cnt->n_nodes, k_inner) : 0u;
+    uint32_t tri_base = n_tri ? atomicAdd(&cnt->n_tris, n_tri) : 0u;
+    uint32_t out_base = k_inner ? atomicAdd(&cnt->next_items, k_inner) : 0u;
+
+    vb_wide_node N;
+    N.px = nlo.x; N.py = nlo.y; N.pz = nlo.z;
+    uint32_t ex = quant_exp(nhi.x - nlo.x), ey = quant_exp(nhi.y - nlo.y), ez = quant_exp(nhi.z - nlo.z);
+    N.ex = (uint8_t)ex; N.ey = (uint8_t)ey; N.ez = (uint8_t)ez; N.imask = (uint8_t)imask;
+    N.child_base = child_base; N.tri_base = tri_base;
+    float isx = 1.0f / __uint_as_float(ex << 23), isy = 1.0f / __uint_as_float(ey << 23), isz = 1.0f / __uint_as_float(ez << 23);
+    uint32_t tri_off = 0, inner_rel = 0;
+    for (int s = 0; s < 8; ++s) {
+        int j = child_in_slot[s];
+        if (j < 0) {
+            N.meta[s] = 0;
+            N.qlox[s] = N.qloy[s] = N.qloz[s] = 255; N.qhix[s] = N.qhiy[s] = N.qhiz[s] = 0;   // empty: inverted box
+            continue;
+        }
+        float4 lo = b.nlo[c[j]], hi = b.nhi[c[j]];
+        N.qlox[s] = (uint8_t)fminf(fmaxf(floorf((lo.x - nlo.x) * isx), 0.f), 255.f);
+        N.qloy[s] = (uint8_t)fminf(fmaxf(floorf((lo.y - nlo.y) * isy), 0.f), 255.f);
+        N.qloz[s] = (uint8_t)fminf(fmaxf(floorf((lo.z - nlo.z) * isz), 0.f), 255.f);
+        N.qhix[s] = (uint8_t)fminf(fmaxf(ceilf((hi.x - nlo.x) * isx), 0.f), 255.f);
+        N.qhiy[s] = (uint8_t)fminf(fmaxf(ceilf((hi.y - nlo.y) * isy), 0.f), 255.f);
+        N.qhiz[s] = (uint8_t)fminf(fmaxf(ceilf((hi.z - nlo.z) * isz), 0.f), 255.f);
+        if (imask >> s & 1) {
+            N.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
+            out[out_base + inner_rel] = WorkItem{c[j], child_base + inner_rel};
+            inner_rel++;
+        } else {
+            uint32_t cntj = tri_count(c[j]);
+            uint32_t first = c[j] >= T - 1 ? c[j] - (T - 1) : b.first[c[j]];
+            N.meta[s] = (uint8_t)((((1u << cntj) - 1u) << 5) | tri_off);
+            for (uint32_t t = 0; t < cntj; ++t) {
+                size_t src = 3 * (size_t)b.vals[first + t], dst = 3 * (size_t)(tri_base + tri_off + t);
+                tris_out[dst] = b.tri_in[src]; tris_out[dst + 1] = b.tri_in[src + 1]; tris_out[dst + 2] = b.tri_in[src + 2];
+            }
+            tri_off += cntj;
+        }
+    }
+    const uint4 *src = reinterpret_cast<const uint4 *>(&N);
+    uint4 *dst = reinterpret_cast<uint4 *>(nodes + it.wide);
+#pragma unroll
+    for (int q = 0; q < 5; ++q) dst[q] = src[q];
+}
+
+template <class T> struct DevBuf {
+    T *p = nullptr;
+    cudaError_t alloc(size_t n) { return cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)); }
+    ~DevBuf() { if (p) cudaFree(p); }
+};
+
+}  // namespace
+
+int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
+    cudaStream_t st = ctx->stream;
+    uint32_t n_inst = (uint32_t)ctx->instances.size();
+    if (n_inst == 0) return ctx->fail(VB_ERR_STATE, "vb_accel_build: no instances set");
+    std::vector<InstGeom> hg(n_inst);
+    std::vector<uint32_t> off(n_inst + 1, 0);
+    uint64_t total = 0;
+    for (uint32_t i = 0; i < n_inst; ++i) {
+        const vb_device_mesh &m = ctx->meshes[ctx->instances[i].mesh_id];
+        hg[i].pos = m.pos; hg[i].tri = m.tri; hg[i].soup = m.soup ? 1u : 0u; hg[i].pad = 0;
+        memcpy(hg[i].o2w, ctx->instances[i].o2w, 64);
+        off[i] = (uint32_t)total;
+        total += m.nt;
+    }
+    if (total == 0) return ctx->fail(VB_ERR_STATE, "vb_accel_build: scene has no triangles");
+    if (total > 0x7fffffffull / 3) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_accel_build: more than 715M triangles");
+    off[n_inst] = (uint32_t)total;
+    uint32_t T = (uint32_t)total;
+
+    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
+    ctx->accel = vb_accel();
+
+    DevBuf<InstGeom> d_geom; DevBuf<uint32_t> d_off;
+    DevBuf<float4> tri_in, blo, bhi, nlo, nhi;
+    DevBuf<uint32_t> scene, vals, vals2, left, right, first, last, parent, flags;
+    DevBuf<uint64_t> keys, keys2;
+    DevBuf<WorkItem> q0, q1; DevBuf<Counters> cnt;
+    VB_CUDA(d_geom.alloc(n_inst)); VB_CUDA(d_off.alloc(n_inst + 1));
+    VB_CUDA(tri_in.alloc(3 * (size_t)T)); VB_CUDA(blo.alloc(T)); VB_CUDA(bhi.alloc(T));
+    VB_CUDA(nlo.alloc(2 * (size_t)T)); VB_CUDA(nhi.alloc(2 * (size_t)T));
+    VB_CUDA(scene.alloc(8)); VB_CUDA(vals.alloc(T)); VB_CUDA(vals2.alloc(T));
+    VB_CUDA(left.alloc(T)); VB_CUDA(right.alloc(T)); VB_CUDA(first.alloc(T)); VB_CUDA(last.alloc(T));
+    VB_CUDA(parent.alloc(2 * (size_t)T)); VB_CUDA(flags.alloc(T));
+    VB_CUDA(keys.alloc(T)); VB_CUDA(keys2.alloc(T));
+    VB_CUDA(q0.alloc(T)); VB_CUDA(q1.alloc(T)); VB_CUDA(cnt.alloc(1));
+    // worst case one wide node per 2 triangles is never reached; T+1 nodes is a safe bound
+    vb_wide_node *d_nodes = nullptr; float4 *d_tris = nullptr;
+    VB_CUDA(cudaMalloc(&d_nodes, ((size_t)T + 1) * sizeof(vb_wide_node)));
+    VB_CUDA(cudaMalloc(&d_tris, 3 * (size_t)T * sizeof(float4)));
+
+    BuildBufs b{tri_in.p, blo.p, bhi.p, scene.p, keys.p, keys2.p, vals.p, vals2.p, nlo.p, nhi.p,
+                left.p, right.p, first.p, last.p, parent.p, flags.p};
+
+    cudaEvent_t e0 = ctx->get_event(), e1 = ctx->get_event();
+    VB_CUDA(cudaMemcpyAsync(d_geom.p, hg.data(), sizeof(InstGeom) * n_inst, cudaMemcpyHostToDevice, st));
+    VB_CUDA(cudaMemcpyAsync(d_off.p, off.data(), sizeof(uint32_t) * (n_inst + 1), cudaMemcpyHostToDevice, st));
+    uint32_t scene_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    VB_CUDA(cudaMemcpyAsync(scene.p, scene_init, sizeof(scene_init), cudaMemcpyHostToDevice, st));
+    VB_CUDA(cudaEventRecord(e0, st));
+    uint64_t launches = 0;
+    uint32_t grid = (T + 255) / 256;
+    k_flatten<<<grid, 256, 0, st>>>(d_geom.p, d_off.p, n_inst, T, b); launches++;
+    VB_CHECK_LAUNCH();
+    k_morton<<<grid, 256, 0, st>>>(T, b); launches++;
+    VB_CHECK_LAUNCH();
+    {
+        size_t tmp_bytes = 0;
+        cub::DoubleBuffer<uint64_t> dk(keys.p, keys2.p);
+        cub::DoubleBuffer<uint32_t> dv(vals.p, vals2.p);
+        VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)T, 0, 63, st));
+        int rc = ctx->ensure_stage(tmp_bytes);
+        if (rc) return rc;
+        VB_CUDA(cub::DeviceRadixSort::SortPairs(ctx->stage, tmp_bytes, dk, dv, (int)T, 0, 63, st));
+        launches += 8;
+        b.keys = dk.Current(); b.vals = dv.Current();
+    }
+    VB_CUDA(cudaMemsetAsync(flags.p, 0, sizeof(uint32_t) * T, st));
+    if (T > 1) { k_karras<<<(T - 1 + 255) / 256, 256, 0, st>>>((int)T, b.keys, b); launches++; VB_CHECK_LAUNCH(); }
+    k_refit<<<grid, 256, 0, st>>>(T, b); launches++;
+    VB_CHECK_LAUNCH();
+
+    // level-synchronous collapse; root work item: BVH2 root = node 0 (or the single leaf when T==1)
+    Counters hc{0, 1, 0, 0};
+    WorkItem root{T == 1 ? 0u : 0u, 0u};
+    VB_CUDA(cudaMemcpyAsync(q0.p, &root, sizeof(root), cudaMemcpyHostToDevice, st));
+    VB_CUDA(cudaMemcpyAsync(cnt.p, &hc, sizeof(hc), cudaMemcpyHostToDevice, st));
+    WorkItem *qin = q0.p, *qout = q1.p;
+    uint32_t n_items = 1;
+    int levels = 0;
+    while (n_items) {
+        k_collapse<<<(n_items + 127) / 128, 128, 0, st>>>(qin, n_items, qout, cnt.p, T, b, d_nodes, d_tris); launches++;
+        VB_CHECK_LAUNCH();
+        VB_CUDA(cudaMemcpyAsync(&hc, cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+        VB_CUDA(cudaStreamSynchronize(st));
+        n_items = hc.next_items;
+        uint32_t zero = 0;
+        VB_CUDA(cudaMemcpyAsync(&cnt.p->next_items, &zero, 4, cudaMemcpyHostToDevice, st));
+        std::swap(qin, qout);
+        if (++levels > 256) return ctx->fail(VB_ERR_STATE, "vb_accel_build: collapse did not terminate");
+    }
+    VB_CUDA(cudaEventRecord(e1, st));
+    VB_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    ctx->ev_pool.push_back(e0); ctx->ev_pool.push_back(e1);
+    if (hc.n_tris != T) return ctx->fail(VB_ERR_STATE, "vb_accel_build: triangle count mismatch after collapse");
+
+    uint32_t hs[6];
+    VB_CUDA(cudaMemcpy(hs, scene.p, sizeof(hs), cudaMemcpyDeviceToHost));
+    // shrink node array to its final size
+    uint4 *final_nodes = nullptr;
+    VB_CUDA(cudaMalloc(&final_nodes, (size_t)hc.n_nodes * sizeof(vb_wide_node)));
+    VB_CUDA(cudaMemcpy(final_nodes, d_nodes, (size_t)hc.n_nodes * sizeof(vb_wide_node), cudaMemcpyDeviceToDevice));
+    cudaFree(d_nodes);
+    ctx->accel.nodes = final_nodes; ctx->accel.tris = d_tris;
+    ctx->accel.n_nodes = hc.n_nodes; ctx->accel.n_tris = T; ctx->accel.built = true;
+
+    vb_build_stats &s = ctx->build_stats;
+    s.n_triangles = T; s.n_nodes = hc.n_nodes; s.node_bytes = (uint64_t)hc.n_nodes * 80; s.tri_bytes = (uint64_t)T * 48;
+    s.build_ms = ms;
+    for (int a = 0; a < 3; ++a) { s.scene_lo[a] = ord2f(hs[a]); s.scene_hi[a] = ord2f(hs[3 + a]); }
+    ctx->prof["bvh_build"].ms += ms; ctx->prof["bvh_build"].launches += launches;
+    ctx->prof["all"].ms += ms; ctx->prof["all"].launches += launches;
+    if (out) *out = s;
+    return VB_OK;
+}

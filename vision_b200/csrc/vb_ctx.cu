@@ -1,0 +1,207 @@
+// Context lifecycle, mesh/instance tables, profiling slots of libvision_b200.so.
+#include "vb_internal.h"
+#include <cstring>
+
+static std::string g_create_err;
+
+int vb_ctx::ensure_stage(size_t bytes) {
+    if (bytes <= stage_bytes) return VB_OK;
+    vb_ctx *ctx = this;
+    if (stage) cudaFree(stage);
+    stage = nullptr; stage_bytes = 0;
+    VB_CUDA(cudaMalloc(&stage, bytes));
+    stage_bytes = bytes;
+    return VB_OK;
+}
+
+cudaEvent_t vb_ctx::get_event() {
+    if (!ev_pool.empty()) { cudaEvent_t e = ev_pool.back(); ev_pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+void vb_ctx::prof_begin(const char *name, uint64_t launches) {
+    cur_name = name; cur_launches = launches;
+    cur_start = get_event();
+    cudaEventRecord(cur_start, stream);
+}
+void vb_ctx::prof_end() {
+    cudaEvent_t e = get_event();
+    cudaEventRecord(e, stream);
+    pending.push_back({std::string(cur_name), {cur_start, e}});
+    prof[cur_name].launches += cur_launches;
+    prof["all"].launches += cur_launches;
+    cur_start = nullptr;
+    if (pending.size() > 4096) { cudaStreamSynchronize(stream); prof_resolve(); }
+}
+void vb_ctx::prof_resolve() {
+    for (auto &p : pending) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, p.second.first, p.second.second) == cudaSuccess) {
+            prof[p.first].ms += ms;
+            prof["all"].ms += ms;
+        }
+        ev_pool.push_back(p.second.first); ev_pool.push_back(p.second.second);
+    }
+    pending.clear();
+}
+
+extern "C" {
+
+int vb_ctx_create(int device, vb_ctx **out) {
+    if (!out) return VB_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        g_create_err = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (libvision_b200 has no CPU fallback)";
+        return VB_ERR_CUDA;
+    }
+    if (device < 0 || device >= n) { g_create_err = "device index out of range"; return VB_ERR_INVALID; }
+    if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_err = cudaGetErrorString(e); return VB_ERR_CUDA; }
+    cudaDeviceProp prop{};
+    cudaGetDeviceProperties(&prop, device);
+    if (prop.major != 10) {
+        g_create_err = "libvision_b200 is built for sm_100a only; device is sm_" + std::to_string(prop.major) + std::to_string(prop.minor);
+        return VB_ERR_UNSUPPORTED;
+    }
+    vb_ctx *c = new vb_ctx();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    if ((e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        g_create_err = cudaGetErrorString(e); delete c; return VB_ERR_CUDA;
+    }
+    c->stream = c->own_stream;
+    *out = c;
+    return VB_OK;
+}
+
+int vb_ctx_destroy(vb_ctx *ctx) {
+    if (!ctx) return VB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->prof_resolve();
+    for (auto e : ctx->ev_pool) cudaEventDestroy(e);
+    for (auto &m : ctx->meshes) {
+        if (m.owns_pos) cudaFree(m.pos);
+        cudaFree(m.nrm); cudaFree(m.uv); cudaFree(m.tri);
+    }
+    cudaFree(ctx->d_instances);
+    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
+    cudaFree(ctx->stage);
+    vb_pt_destroy(ctx);
+    cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+    return VB_OK;
+}
+
+const char *vb_last_error(vb_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int vb_ctx_set_stream(vb_ctx *ctx, void *s) {
+    if (!ctx) return VB_ERR_INVALID;
+    ctx->stream = s ? (cudaStream_t)s : ctx->own_stream;
+    return VB_OK;
+}
+int vb_ctx_synchronize(vb_ctx *ctx) {
+    if (!ctx) return VB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VB_OK;
+}
+int vb_profile_reset(vb_ctx *ctx) {
+    if (!ctx) return VB_ERR_INVALID;
+    cudaStreamSynchronize(ctx->stream);
+    ctx->prof_resolve();
+    ctx->prof.clear();
+    return VB_OK;
+}
+int vb_profile_get(vb_ctx *ctx, const char *name, double *ms, uint64_t *launches) {
+    if (!ctx || !name) return VB_ERR_INVALID;
+    cudaStreamSynchronize(ctx->stream);
+    ctx->prof_resolve();
+    auto it = ctx->prof.find(name);
+    if (ms) *ms = it == ctx->prof.end() ? 0.0 : it->second.ms;
+    if (launches) *launches = it == ctx->prof.end() ? 0 : it->second.launches;
+    return VB_OK;
+}
+
+int vb_mesh_upload(vb_ctx *ctx, const float *pos3, const float *nrm3, const float *uv2, uint32_t nv,
+                   const uint32_t *tri3, uint32_t nt, uint32_t *mesh_id) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (!pos3 || !tri3 || !mesh_id) return ctx->fail(VB_ERR_INVALID, "vb_mesh_upload: null argument");
+    for (uint64_t i = 0; i < 3ull * nt; ++i)
+        if (tri3[i] >= nv) return ctx->fail(VB_ERR_INVALID, "vb_mesh_upload: triangle index out of range");
+    cudaSetDevice(ctx->device);
+    vb_device_mesh m;
+    m.nv = nv; m.nt = nt;
+    if (nv) {
+        VB_CUDA(cudaMalloc(&m.pos, sizeof(float) * 3 * nv));
+        VB_CUDA(cudaMemcpyAsync(m.pos, pos3, sizeof(float) * 3 * nv, cudaMemcpyHostToDevice, ctx->stream));
+        VB_CUDA(cudaMalloc(&m.nrm, sizeof(float) * 3 * nv));
+        if (nrm3) VB_CUDA(cudaMemcpyAsync(m.nrm, nrm3, sizeof(float) * 3 * nv, cudaMemcpyHostToDevice, ctx->stream));
+        else VB_CUDA(cudaMemsetAsync(m.nrm, 0, sizeof(float) * 3 * nv, ctx->stream));
+        VB_CUDA(cudaMalloc(&m.uv, sizeof(float) * 2 * nv));
+        if (uv2) VB_CUDA(cudaMemcpyAsync(m.uv, uv2, sizeof(float) * 2 * nv, cudaMemcpyHostToDevice, ctx->stream));
+        else VB_CUDA(cudaMemsetAsync(m.uv, 0, sizeof(float) * 2 * nv, ctx->stream));
+    }
+    if (nt) {
+        VB_CUDA(cudaMalloc(&m.tri, sizeof(uint32_t) * 3 * nt));
+        VB_CUDA(cudaMemcpyAsync(m.tri, tri3, sizeof(uint32_t) * 3 * nt, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    *mesh_id = (uint32_t)ctx->meshes.size();
+    ctx->meshes.push_back(m);
+    ctx->accel.built = false;
+    return VB_OK;
+}
+
+int vb_mesh_upload_soup(vb_ctx *ctx, const float *pos9, vb_mem mem, uint64_t nt, uint32_t *mesh_id) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (!pos9 || !mesh_id) return ctx->fail(VB_ERR_INVALID, "vb_mesh_upload_soup: null argument");
+    if (nt > 0x55555555ull) return ctx->fail(VB_ERR_INVALID, "vb_mesh_upload_soup: too many triangles");
+    cudaSetDevice(ctx->device);
+    vb_device_mesh m;
+    m.soup = true; m.nt = nt; m.nv = (uint32_t)(3 * nt);
+    if (nt) {
+        VB_CUDA(cudaMalloc(&m.pos, sizeof(float) * 9 * nt));
+        VB_CUDA(cudaMemcpyAsync(m.pos, pos9, sizeof(float) * 9 * nt,
+                                mem == VB_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, ctx->stream));
+        VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    *mesh_id = (uint32_t)ctx->meshes.size();
+    ctx->meshes.push_back(m);
+    ctx->accel.built = false;
+    return VB_OK;
+}
+
+int vb_instances_set(vb_ctx *ctx, const vb_instance *inst, uint32_t n) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (n && !inst) return ctx->fail(VB_ERR_INVALID, "vb_instances_set: null argument");
+    for (uint32_t i = 0; i < n; ++i)
+        if (inst[i].mesh_id >= ctx->meshes.size()) return ctx->fail(VB_ERR_INVALID, "vb_instances_set: unknown mesh_id");
+    cudaSetDevice(ctx->device);
+    ctx->instances.assign(inst, inst + n);
+    cudaFree(ctx->d_instances); ctx->d_instances = nullptr;
+    if (n) {
+        VB_CUDA(cudaMalloc(&ctx->d_instances, sizeof(vb_instance) * n));
+        VB_CUDA(cudaMemcpy(ctx->d_instances, inst, sizeof(vb_instance) * n, cudaMemcpyHostToDevice));
+    }
+    ctx->accel.built = false;
+    return VB_OK;
+}
+
+int vb_accel_build(vb_ctx *ctx, const vb_build_opts *, vb_build_stats *out) {
+    if (!ctx) return VB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    return vb_accel_build_impl(ctx, out);
+}
+
+int vb_accel_download(vb_ctx *ctx, void *nodes, void *tris) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (!ctx->accel.built) return ctx->fail(VB_ERR_STATE, "vb_accel_download: accel not built");
+    cudaSetDevice(ctx->device);
+    VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (nodes && ctx->accel.n_nodes) VB_CUDA(cudaMemcpy(nodes, ctx->accel.nodes, ctx->accel.n_nodes * 80, cudaMemcpyDeviceToHost));
+    if (tris && ctx->accel.n_tris) VB_CUDA(cudaMemcpy(tris, ctx->accel.tris, ctx->accel.n_tris * 48, cudaMemcpyDeviceToHost));
+    return VB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,83 @@
+// Internal declarations of libvision_b200.so (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include <map>
+#include "../../include/vision_b200.h"
+
+#define VB_CUDA(call)                                                                         \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            return ctx->fail(VB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+        }                                                                                     \
+    } while (0)
+
+#define VB_CHECK_LAUNCH() VB_CUDA(cudaGetLastError())
+
+struct vb_device_mesh {
+    float *pos = nullptr;      // 3*nv
+    float *nrm = nullptr;      // 3*nv (may be null)
+    float *uv = nullptr;       // 2*nv (may be null)
+    uint32_t *tri = nullptr;   // 3*nt (null for soups)
+    uint32_t nv = 0;
+    uint64_t nt = 0;
+    bool soup = false;
+    bool owns_pos = true;
+};
+
+// 80-byte compressed 8-wide node (5 x uint4). See DESIGN.md "Wide node".
+struct __align__(16) vb_wide_node {
+    float px, py, pz;          // quantisation origin
+    uint8_t ex, ey, ez, imask; // per-axis scale exponent (float exponent bits), internal-child mask
+    uint32_t child_base;       // index of first internal child (wide node index)
+    uint32_t tri_base;         // index of first triangle of this node's leaf children
+    uint8_t meta[8];
+    uint8_t qlox[8], qloy[8], qloz[8];
+    uint8_t qhix[8], qhiy[8], qhiz[8];
+};
+static_assert(sizeof(vb_wide_node) == 80, "wide node must be 80 bytes");
+
+struct vb_prof_slot { double ms = 0; uint64_t launches = 0; };
+
+struct vb_accel {
+    uint4 *nodes = nullptr;    // n_nodes * 5 uint4
+    float4 *tris = nullptr;    // n_tris * 3 float4: (v0,prim) (e1,inst) (e2,0)
+    uint64_t n_nodes = 0, n_tris = 0;
+    bool built = false;
+};
+
+struct vb_pt_state;   // vb_pt.cu
+
+struct vb_ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    std::string err;
+    std::vector<vb_device_mesh> meshes;
+    std::vector<vb_instance> instances;
+    vb_instance *d_instances = nullptr;
+    vb_accel accel;
+    vb_build_stats build_stats{};
+    std::map<std::string, vb_prof_slot> prof;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::vector<std::pair<std::string, std::pair<cudaEvent_t, cudaEvent_t>>> pending;  // un-resolved timings
+    std::vector<cudaEvent_t> ev_pool;
+    // staging for host-pointer calls
+    void *stage = nullptr; size_t stage_bytes = 0;
+    int sm_count = 148;
+    vb_pt_state *pt = nullptr;
+
+    int fail(int code, const std::string &msg) { err = msg; return code; }
+    int ensure_stage(size_t bytes);
+    // profiling helpers: bracket kernels with events on the launching stream
+    cudaEvent_t get_event();
+    void prof_begin(const char *name, uint64_t launches);
+    void prof_end();
+    void prof_resolve();
+    const char *cur_name = nullptr; cudaEvent_t cur_start = nullptr; uint64_t cur_launches = 0;
+};
+
+int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out);
+void vb_pt_destroy(vb_ctx *ctx);

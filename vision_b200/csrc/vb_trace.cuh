@@ -1,0 +1,156 @@
+// Device traversal core for the compressed 8-wide BVH (sm_100a). Shared by the batch trace
+// kernels (vb_trace.cu) and the path-tracing megakernel (vb_pt.cu).
+//
+// Stands in for ocarina::Accel::trace_closest / trace_occlusion (OptiX) called from
+// reference src/base/mgr/geometry.cpp:168-174.
+//
+// Node = 5 x 128-bit read-only loads (ld.global.nc.v4); triangle = 3 x 128-bit loads.
+// Traversal stack: VB_SM_STACK entries per thread in shared memory laid out [entry][thread]
+// (conflict-free), spilling to a small local array only on very deep paths.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define VB_SM_STACK 10
+#define VB_LOCAL_STACK 54
+
+struct VbRay { float ox, oy, oz, tmin, dx, dy, dz, tmax; };
+struct VbHit { uint32_t inst, prim; float u, v, t; };
+
+struct VbAccelView {
+    const uint4 *__restrict__ nodes;
+    const float4 *__restrict__ tris;
+};
+
+// Normative triangle test (DESIGN.md "Intersection contract"); mirrors oracle
+// vo::intersect_triangle operation for operation. __f*_rn intrinsics are never contracted.
+__device__ __forceinline__ float vb_dot(float ax, float ay, float az, float bx, float by, float bz) {
+    return __fmaf_rn(az, bz, __fmaf_rn(ay, by, __fmul_rn(ax, bx)));
+}
+__device__ __forceinline__ void vb_cross(float ax, float ay, float az, float bx, float by, float bz,
+                                         float &cx, float &cy, float &cz) {
+    cx = __fmaf_rn(ay, bz, -__fmul_rn(az, by));
+    cy = __fmaf_rn(az, bx, -__fmul_rn(ax, bz));
+    cz = __fmaf_rn(ax, by, -__fmul_rn(ay, bx));
+}
+__device__ __forceinline__ bool vb_intersect_triangle(const VbRay &r, float4 a, float4 b, float4 c, float tmax,
+                                                      float &t, float &u, float &v) {
+    float px, py, pz;
+    vb_cross(r.dx, r.dy, r.dz, c.x, c.y, c.z, px, py, pz);
+    float det = vb_dot(b.x, b.y, b.z, px, py, pz);
+    if (!(det != 0.0f)) return false;
+    float inv = __frcp_rn(det);
+    float sx = __fsub_rn(r.ox, a.x), sy = __fsub_rn(r.oy, a.y), sz = __fsub_rn(r.oz, a.z);
+    u = __fmul_rn(vb_dot(sx, sy, sz, px, py, pz), inv);
+    if (!(u >= 0.0f && u <= 1.0f)) return false;
+    float qx, qy, qz;
+    vb_cross(sx, sy, sz, b.x, b.y, b.z, qx, qy, qz);
+    v = __fmul_rn(vb_dot(r.dx, r.dy, r.dz, qx, qy, qz), inv);
+    if (!(v >= 0.0f && __fadd_rn(u, v) <= 1.0f)) return false;
+    t = __fmul_rn(vb_dot(c.x, c.y, c.z, qx, qy, qz), inv);
+    return t > r.tmin && t < tmax;
+}
+
+__device__ __forceinline__ float vb_safe_rcp(float d) {
+    return 1.0f / (fabsf(d) > 1e-20f ? d : copysignf(1e-20f, d));
+}
+
+__device__ __forceinline__ uint32_t vb_byte(uint32_t w, int i) { return (w >> (8 * i)) & 0xffu; }
+
+// Tests the 8 quantised child boxes of one node; returns the 32-bit hit mask
+// (bits 31..24: internal children in octant order, bits 23..0: triangles).
+__device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
+                                                 const uint4 n4, const VbRay &r, float idx, float idy, float idz,
+                                                 uint32_t oct_inv4, float tmax) {
+    float adjx = __uint_as_float((n0.w & 0xffu) << 23) * idx;
+    float adjy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idy;
+    float adjz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idz;
+    float orx = (__uint_as_float(n0.x) - r.ox) * idx;
+    float ory = (__uint_as_float(n0.y) - r.oy) * idy;
+    float orz = (__uint_as_float(n0.z) - r.oz) * idz;
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        uint32_t meta4 = h ? n1.w : n1.z;
+        uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+        uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
+        uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+        uint32_t qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
+        uint32_t qhx = h ? n3.w : n3.z, qhy = h ? n4.y : n4.x, qhz = h ? n4.w : n4.z;
+        uint32_t nx = idx < 0.f ? qhx : qlx, fx = idx < 0.f ? qlx : qhx;
+        uint32_t ny = idy < 0.f ? qhy : qly, fy = idy < 0.f ? qly : qhy;
+        uint32_t nz = idz < 0.f ? qhz : qlz, fz = idz < 0.f ? qlz : qhz;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float tnx = fmaf((float)vb_byte(nx, j), adjx, orx), tfx = fmaf((float)vb_byte(fx, j), adjx, orx);
+            float tny = fmaf((float)vb_byte(ny, j), adjy, ory), tfy = fmaf((float)vb_byte(fy, j), adjy, ory);
+            float tnz = fmaf((float)vb_byte(nz, j), adjz, orz), tfz = fmaf((float)vb_byte(fz, j), adjz, orz);
+            float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tmin));
+            float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
+            if (cmin <= cmax) hitmask |= vb_byte(child_bits4, j) << vb_byte(bit_index4, j);
+        }
+    }
+    return hitmask;
+}
+
+// s_stack points at this thread's column of the shared stack: entry e lives at s_stack[e * stride]
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool vb_traverse(const VbAccelView &A, VbRay r, VbHit &hit, uint2 *s_stack, int stride,
+                                            uint32_t &n_nodes, uint32_t &n_tris) {
+    uint2 l_stack[VB_LOCAL_STACK];
+    int sp = 0;
+    float idx = vb_safe_rcp(r.dx), idy = vb_safe_rcp(r.dy), idz = vb_safe_rcp(r.dz);
+    uint32_t oct = (r.dx < 0.f ? 4u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 1u : 0u);
+    uint32_t oct_inv4 = (7u - oct) * 0x01010101u;
+    float tmax = r.tmax;
+    hit.inst = 0xffffffffu; hit.prim = 0xffffffffu; hit.u = 0.f; hit.v = 0.f; hit.t = 0.f;
+    if (!(r.tmin < r.tmax)) return false;
+
+    uint2 G = make_uint2(0u, 0x80000000u);     // root group: node 0, "slot 7" hit, imask 0
+    uint2 Tg = make_uint2(0u, 0u);
+    for (;;) {
+        // invariant: G holds at least one un-visited internal child here (only such groups are pushed)
+        {
+            uint32_t hits_imask = G.y;
+            uint32_t bit = 31u - __clz(hits_imask);
+            G.y &= ~(1u << bit);
+            if (G.y & 0xff000000u) {           // siblings remain: push the rest of the group
+                if (sp < VB_SM_STACK) s_stack[sp * stride] = G;
+                else if (sp < VB_SM_STACK + VB_LOCAL_STACK) l_stack[sp - VB_SM_STACK] = G;
+                sp++;
+            }
+            uint32_t slot = (bit - 24u) ^ (oct_inv4 & 0xffu);
+            uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot) & 0xffu);
+            const uint4 *np = A.nodes + (size_t)(G.x + rel) * 5;
+            uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+            if (COUNT) n_nodes++;
+            uint32_t hm = vb_node_hits(n0, n1, n2, n3, n4, r, idx, idy, idz, oct_inv4, tmax);
+            G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
+            Tg = make_uint2(n1.y, hm & 0x00ffffffu);
+        }
+        while (Tg.y) {
+            uint32_t ti = 31u - __clz(Tg.y);
+            Tg.y &= ~(1u << ti);
+            const float4 *tp = A.tris + (size_t)(Tg.x + ti) * 3;
+            float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+            if (COUNT) n_tris++;
+            float t, u, v;
+            if (vb_intersect_triangle(r, a, b, c, r.tmax, t, u, v)) {
+                if (ANY) return true;
+                uint32_t inst = __float_as_uint(b.w), prim = __float_as_uint(a.w);
+                bool better = hit.inst == 0xffffffffu || t < hit.t ||
+                              (t == hit.t && (inst < hit.inst || (inst == hit.inst && prim < hit.prim)));
+                if (better) { hit.inst = inst; hit.prim = prim; hit.u = u; hit.v = v; hit.t = t; tmax = t; }
+            }
+        }
+        if (!(G.y & 0xff000000u)) {
+            if (sp == 0) break;
+            sp--;
+            if (sp < VB_SM_STACK) G = s_stack[sp * stride];
+            else if (sp < VB_SM_STACK + VB_LOCAL_STACK) G = l_stack[sp - VB_SM_STACK];
+            else G = make_uint2(0u, 0u);
+        }
+    }
+    return hit.inst != 0xffffffffu;
+}
