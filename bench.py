@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""bench.py - headline benchmark of the hot path (BASELINE.json configs[1]):
+16 Mi incoherent rays, closest-hit + any-hit, against the 10M-triangle random mesh M(10M).
+
+  python bench.py --gpus N --steps K --warmup W            # this framework (CUDA, sm_100a)
+  python bench.py --impl reference --gpus N --steps K ...  # the reference-side CPU arm (oracle port)
+
+One "step" = one closest-hit pass + one any-hit pass over the ray batch. `value` is whole-job
+Mrays/s with rays resident in HBM; `e2e` is the same through the C ABI with pinned HOST buffers
+(H2D of the rays and D2H of the hits inside the timed region). Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "Mrays/s (closest-hit + any-hit, incoherent rays, software BVH traversal)"
+RAY_FIELDS = ("ox", "oy", "oz", "tmin", "dx", "dy", "dz", "tmax")
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=10)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--tris", type=int, default=10_000_000)
+    p.add_argument("--rays", type=int, default=1 << 24)
+    p.add_argument("--cpu-sample-rays", type=int, default=1 << 18)
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    return p.parse_args()
+
+
+def workload_name(a):
+    return f"synthetic ray-cast microbench: {a.rays} incoherent rays x (closest-hit + any-hit) vs M({a.tris}) random triangle mesh, seeds mesh=1 rays=2 any=3"
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks and throttle reasons DURING the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_arm(a, mesh, rays, threads: int, steps: int, warmup: int):
+    """times the oracle port (scalar C++ restatement) on a bounded sample"""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle_lib
+    o = oracle_lib.load()
+    threads = threads or o.hw_threads()
+    acc = o.accel()
+    acc.add_soup(mesh)
+    build_s = acc.build(threads)
+    ns = min(a.cpu_sample_rays, a.rays)
+    sub = {k: np.ascontiguousarray(v[:ns]) for k, v in rays.items()}
+    sub_any = dict(sub, tmax=sub["tmax_any"])
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        acc.trace_closest(sub, threads=threads)
+        acc.trace_any(sub_any, threads=threads)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    total = sum(times)
+    val = 2 * ns * len(times) / total / 1e6
+    return {"value": val, "unit": "Mrays/s", "cores": threads, "kind": "port",
+            "sample": f"first {ns} rays of the workload (closest + any) vs the full M({a.tris}) mesh, "
+                      f"oracle binned-SAH BVH2 (build {build_s:.1f} s, untimed)",
+            "ms_per_step": 1e3 * total / len(times)}
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    from vision_b200 import synth
+
+    if a.impl == "reference":
+        if rank != 0:
+            return 0
+        mesh = synth.synth_mesh(a.tris, seed=1)
+        ns = min(a.cpu_sample_rays, a.rays)
+        rays = synth.synth_rays(ns, seed=2, seed_any=3)
+        cb = cpu_arm(a, mesh, rays, 0, max(1, min(a.steps, 5)), min(a.warmup, 1))
+        line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "Mrays/s", "n_gpus": a.gpus,
+                "steps": a.steps, "warmup": a.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": workload_name(a)},
+                "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": cb["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "note": "reference has no CPU backend and its compute layer (ocarina+OptiX) is absent: this arm is the "
+                        "scalar C++ oracle port on all host threads (BASELINE.json fallback)"}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from vision_b200 import Context
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - vision_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    ctx = Context(local_rank)
+    stream = torch.cuda.Stream(device=local_rank)      # a real (non-default) stream shared with the library
+    torch.cuda.set_stream(stream)
+    ctx.set_stream(stream.cuda_stream)
+
+    # ---- inputs (untimed): replicated mesh, per-rank ray shard (weak scaling: a.rays per GPU) --------
+    mesh = synth.synth_mesh(a.tris, seed=1)
+    rays = synth.synth_rays(a.rays, seed=2 + 100 * rank, seed_any=3 + 100 * rank)
+    mid = ctx.mesh_upload_soup(mesh)
+    ctx.instances_set([{"mesh_id": mid}])
+    bst = ctx.accel_build()
+    dev = torch.device("cuda", local_rank)
+    d_rays = {k: torch.from_numpy(v).to(dev) for k, v in rays.items()}
+    d_any = dict(d_rays, tmax=d_rays["tmax_any"])
+    n = a.rays
+    d_hits = {"inst": torch.empty(n, dtype=torch.int32, device=dev), "prim": torch.empty(n, dtype=torch.int32, device=dev),
+              "u": torch.empty(n, dtype=torch.float32, device=dev), "v": torch.empty(n, dtype=torch.float32, device=dev),
+              "t": torch.empty(n, dtype=torch.float32, device=dev)}
+    d_occ = torch.empty(n, dtype=torch.uint8, device=dev)
+
+    # per-ray work counters from the instrumented kernels (never timed)
+    _, nodes_c, tris_c = ctx.trace_closest(d_rays, d_hits, counted=True)
+    _, nodes_a, tris_a = ctx.trace_any(d_any, d_occ, counted=True)
+    torch.cuda.synchronize()
+    hit_frac = float((d_hits["inst"] != -1).float().mean().item())
+    occ_frac = float(d_occ.float().mean().item())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        ctx.trace_closest(d_rays, d_hits)
+        ctx.trace_any(d_any, d_occ)
+
+    for _ in range(a.warmup):
+        step()
+    barrier()
+    ctx.profile_reset()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(a.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = e0.elapsed_time(e1)
+    k_closest_ms, k_closest_n = ctx.profile_get("trace_closest")
+    k_any_ms, k_any_n = ctx.profile_get("trace_any")
+    launches = k_closest_n + k_any_n
+
+    # ---- e2e: pinned host buffers through the C ABI, H2D + D2H inside the timed region -------------
+    h_rays = {k: torch.from_numpy(v).pin_memory() for k, v in rays.items()}
+    hr = {k: v.numpy() for k, v in h_rays.items()}
+    hr_any = dict(hr, tmax=hr["tmax_any"])
+    h_hits_t = {"inst": torch.empty(n, dtype=torch.int32).pin_memory(), "prim": torch.empty(n, dtype=torch.int32).pin_memory(),
+                "u": torch.empty(n, dtype=torch.float32).pin_memory(), "v": torch.empty(n, dtype=torch.float32).pin_memory(),
+                "t": torch.empty(n, dtype=torch.float32).pin_memory()}
+    h_hits = {k: v.numpy() for k, v in h_hits_t.items()}
+    h_hits["inst"] = h_hits["inst"].view(np.uint32); h_hits["prim"] = h_hits["prim"].view(np.uint32)
+    h_occ_t = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h_occ = h_occ_t.numpy()
+    e2e_steps = max(1, min(a.steps, 5))
+
+    def e2e_step():
+        ctx.trace_closest(hr, h_hits)
+        ctx.trace_any(hr_any, h_occ)
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record(stream)
+    for _ in range(e2e_steps):
+        e2e_step()
+    f1.record(stream)
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    e2e_ms = max(f0.elapsed_time(f1), wall_ms)   # device bracket vs host wall clock: the slower one
+    assert np.array_equal(h_hits["prim"], d_hits["prim"].cpu().numpy().view(np.uint32)), "e2e result differs"
+    h2d = 2 * 8 * n * 4
+    d2h = 5 * n * 4 + n
+
+    # ---- reduce over ranks -------------------------------------------------------------------------
+    t = torch.tensor([ms_total, e2e_ms, k_closest_ms, k_any_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms, k_closest_ms_max, k_any_ms_max = [float(x) for x in t.tolist()]
+    total_rays_step = 2 * n * world
+    value = total_rays_step * a.steps / (ms_total * 1e-3) / 1e6
+    e2e_value = total_rays_step * e2e_steps / (e2e_ms * 1e-3) / 1e6
+
+    if rank == 0:
+        peaks = {}
+        pk = ROOT / "MEASURED_PEAKS.json"
+        peak_src = "fallback 6650 GB/s (B200_PROFILING.md)"
+        peak = 6650.0
+        if pk.exists():
+            peaks = json.loads(pk.read_text())
+            peak = float(peaks.get("hbm_gbs", peak)); peak_src = "MEASURED_PEAKS.json hbm_gbs (burst copy)"
+        npr, tpr = nodes_c / n, tris_c / n
+        bytes_per_ray = 32 + 20 + 80 * npr + 48 * tpr
+        dur_ms = k_closest_ms / max(1, k_closest_n)
+        achieved = bytes_per_ray * n / (dur_ms * 1e-3) / 1e9
+        prof_traffic = None
+        tf = ROOT / "profiles" / "traffic.json"
+        if tf.exists():
+            try:
+                prof_traffic = json.loads(tf.read_text()).get("trace_closest_bytes_per_launch")
+            except Exception:
+                prof_traffic = None
+        bpa = 32 + 1 + 80 * nodes_a / n + 48 * tris_a / n
+        line = {
+            "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "rays_per_gpu": n, "triangles": a.tris,
+                       "l2_policy": "inputs larger than L2 (BVH %.0f MB + rays %.0f MB per pass >> 126 MB)" % (
+                           (bst["node_bytes"] + bst["tri_bytes"]) / 1e6, 32 * n / 1e6),
+                       "partition": "rays sharded per rank, BVH replicated, no data-path collective"},
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": prof_traffic, "peak_source": peak_src,
+                         "bytes_per_ray": bytes_per_ray, "nodes_per_ray": npr, "tris_per_ray": tpr,
+                         "kernel_ms": dur_ms, "rays_per_launch": n},
+            "kernels": {"trace_closest": {"ms": dur_ms, "mrays_s": n / dur_ms / 1e3, "hit_frac": hit_frac},
+                        "trace_any": {"ms": k_any_ms / max(1, k_any_n), "mrays_s": n / (k_any_ms / max(1, k_any_n)) / 1e3,
+                                      "occluded_frac": occ_frac, "bytes_per_ray": bpa,
+                                      "achieved_gbs": bpa * n / (k_any_ms / max(1, k_any_n) * 1e-3) / 1e9}},
+            "bvh": {"build_ms": bst["build_ms"], "nodes": bst["n_nodes"], "node_bytes": bst["node_bytes"],
+                    "tri_bytes": bst["tri_bytes"]},
+        }
+        if world == 1 and not a.no_cpu_baseline:
+            cb = cpu_arm(a, mesh, rays, 0, 2, 1)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    ctx.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -84,6 +84,12 @@ __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n
     uint32_t out_base = k_inner ? atomicAdd(&cnt->next_items, k_inner) : 0u;
 
     vb_wide_node N;
+    // quantisation frame = node box grown by 1/64 of its extent per side, so that the 2^-6 grid-unit
+    // inflation of the child boxes below never clamps at 0/255 (see vb_qf in vb_trace.cuh)
+    {
+        float mx = (nhi.x - nlo.x) * 0.015625f, my = (nhi.y - nlo.y) * 0.015625f, mz = (nhi.z - nlo.z) * 0.015625f;
+        nlo.x -= mx; nlo.y -= my; nlo.z -= mz; nhi.x += mx; nhi.y += my; nhi.z += mz;
+    }
     N.px = nlo.x; N.py = nlo.y; N.pz = nlo.z;
     uint32_t ex = quant_exp(nhi.x - nlo.x), ey = quant_exp(nhi.y - nlo.y), ez = quant_exp(nhi.z - nlo.z);
     N.ex = (uint8_t)ex; N.ey = (uint8_t)ey; N.ez = (uint8_t)ez; N.imask = (uint8_t)imask;
@@ -98,12 +104,12 @@ __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n
             continue;
         }
         float4 lo = b.nlo[c[j]], hi = b.nhi[c[j]];
-        N.qlox[s] = (uint8_t)fminf(fmaxf(floorf((lo.x - nlo.x) * isx), 0.f), 255.f);
-        N.qloy[s] = (uint8_t)fminf(fmaxf(floorf((lo.y - nlo.y) * isy), 0.f), 255.f);
-        N.qloz[s] = (uint8_t)fminf(fmaxf(floorf((lo.z - nlo.z) * isz), 0.f), 255.f);
-        N.qhix[s] = (uint8_t)fminf(fmaxf(ceilf((hi.x - nlo.x) * isx), 0.f), 255.f);
-        N.qhiy[s] = (uint8_t)fminf(fmaxf(ceilf((hi.y - nlo.y) * isy), 0.f), 255.f);
-        N.qhiz[s] = (uint8_t)fminf(fmaxf(ceilf((hi.z - nlo.z) * isz), 0.f), 255.f);
+        N.qlox[s] = (uint8_t)fminf(fmaxf(floorf((lo.x - nlo.x) * isx - 0.015625f), 0.f), 255.f);
+        N.qloy[s] = (uint8_t)fminf(fmaxf(floorf((lo.y - nlo.y) * isy - 0.015625f), 0.f), 255.f);
+        N.qloz[s] = (uint8_t)fminf(fmaxf(floorf((lo.z - nlo.z) * isz - 0.015625f), 0.f), 255.f);
+        N.qhix[s] = (uint8_t)fminf(fmaxf(ceilf((hi.x - nlo.x) * isx + 0.015625f), 0.f), 255.f);
+        N.qhiy[s] = (uint8_t)fminf(fmaxf(ceilf((hi.y - nlo.y) * isy + 0.015625f), 0.f), 255.f);
+        N.qhiz[s] = (uint8_t)fminf(fmaxf(ceilf((hi.z - nlo.z) * isz + 0.015625f), 0.f), 255.f);
         if (imask >> s & 1) {
             N.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
             out[out_base + inner_rel] = WorkItem{c[j], child_base + inner_rel};

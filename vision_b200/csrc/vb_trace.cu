@@ -3,32 +3,150 @@
 // as a bulk SoA-in / SoA-out API (the microbench and parity surface of SURVEY.md §8b).
 #include "vb_internal.h"
 #include "vb_trace.cuh"
+#include <algorithm>
 
 namespace {
 
 constexpr int TRACE_BLOCK = 128;
+constexpr int TRACE_BLOCKS_PER_SM = 6;
 
 struct RaysDev { const float *ox, *oy, *oz, *tmin, *dx, *dy, *dz, *tmax; };
 struct HitsDev { uint32_t *inst, *prim; float *u, *v, *t; };
 
+// Persistent-warp traversal with per-lane dynamic ray fetch and triangle postponing.
+//  * each lane owns one ray at a time; when fewer than REFILL_THR lanes of a warp are busy the
+//    idle lanes grab consecutive ray indices with one warp-aggregated atomicAdd
+//  * every loop iteration is two warp-converged phases: (N) lanes with internal-child work pop one
+//    child and test its 8 boxes; (T) triangle rounds, run only when >= TRI_THR lanes have pending
+//    triangles or some lane cannot continue without testing its triangles (both pending slots
+//    full, or no node work left) - warp votes decide, so no lane spins alone in a triangle loop
+//  * results are independent of order by the tie rule, so postponing never changes the answer
+constexpr int REFILL_THR = 22;
+constexpr int TRI_THR = 10;
+
 template <bool ANY, bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(VbAccelView A, RaysDev R, uint64_t n, HitsDev H, uint8_t *occ,
-                                                       unsigned long long *counters) {
-    __shared__ uint2 s_stack[VB_SM_STACK * TRACE_BLOCK];
-    uint64_t i = (uint64_t)blockIdx.x * TRACE_BLOCK + threadIdx.x;
+                                                       unsigned long long *counters, unsigned long long *next_ray) {
+    __shared__ uint2 s_stack_all[VB_SM_STACK * TRACE_BLOCK];
+    uint2 *s_stack = s_stack_all + threadIdx.x;
+    uint2 l_stack[VB_LOCAL_STACK];
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
     uint32_t nn = 0, nt = 0;
-    if (i < n) {
-        VbRay r;
-        r.ox = __ldg(R.ox + i); r.oy = __ldg(R.oy + i); r.oz = __ldg(R.oz + i); r.tmin = __ldg(R.tmin + i);
-        r.dx = __ldg(R.dx + i); r.dy = __ldg(R.dy + i); r.dz = __ldg(R.dz + i); r.tmax = __ldg(R.tmax + i);
-        VbHit h;
-        bool got = vb_traverse<ANY, COUNT>(A, r, h, s_stack + threadIdx.x, TRACE_BLOCK, nn, nt);
-        if (ANY) occ[i] = got ? 1 : 0;
-        else { H.inst[i] = h.inst; H.prim[i] = h.prim; H.u[i] = h.u; H.v[i] = h.v; H.t[i] = h.t; }
+
+    bool active = false, exhausted = false;
+    uint64_t idx = 0;
+    VbRay r{};
+    float idx_ = 0.f, idy_ = 0.f, idz_ = 0.f, tmax = 0.f;
+    uint32_t oct_inv4 = 0;
+    VbHit hit{};
+    uint2 G = make_uint2(0u, 0u), Tg = make_uint2(0u, 0u), Td = make_uint2(0u, 0u);
+    int sp = 0;
+    bool occluded = false;
+
+    for (;;) {
+        // ---------------- refill idle lanes ----------------
+        unsigned idle = __ballot_sync(~0u, !active);
+        if (idle && !exhausted) {
+            unsigned long long base = 0;
+            int leader = __ffs(idle) - 1;
+            if ((int)lane == leader) base = atomicAdd(next_ray, (unsigned long long)__popc(idle));
+            base = __shfl_sync(~0u, base, leader);
+            if (base + __popc(idle) >= n) exhausted = true;
+            if (!active) {
+                idx = base + __popc(idle & lt_mask);
+                if (idx < n) {
+                    r.ox = __ldg(R.ox + idx); r.oy = __ldg(R.oy + idx); r.oz = __ldg(R.oz + idx); r.tmin = __ldg(R.tmin + idx);
+                    r.dx = __ldg(R.dx + idx); r.dy = __ldg(R.dy + idx); r.dz = __ldg(R.dz + idx); r.tmax = __ldg(R.tmax + idx);
+                    idx_ = vb_safe_rcp(r.dx); idy_ = vb_safe_rcp(r.dy); idz_ = vb_safe_rcp(r.dz);
+                    uint32_t oct = (r.dx < 0.f ? 4u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 1u : 0u);
+                    oct_inv4 = (7u - oct) * 0x01010101u;
+                    tmax = r.tmax;
+                    hit.inst = 0xffffffffu; hit.prim = 0xffffffffu; hit.u = 0.f; hit.v = 0.f; hit.t = 0.f;
+                    occluded = false;
+                    sp = 0; Tg = make_uint2(0u, 0u); Td = make_uint2(0u, 0u);
+                    // root group; an empty interval (or NaN bounds) never enters the tree
+                    G = make_uint2(0u, (r.tmin < r.tmax) ? 0x80000000u : 0u);
+                    active = true;
+                }
+            }
+        }
+        if (__ballot_sync(~0u, active) == 0u) break;
+
+        // ---------------- traverse ----------------
+        unsigned act;
+        do {
+            bool has_node = false;
+            if (active) {
+                if (!(G.y & 0xff000000u) && sp > 0 && !(Tg.y && Td.y)) {       // fetch the next node group
+                    sp--;
+                    if (sp < VB_SM_STACK) G = s_stack[sp * TRACE_BLOCK];
+                    else if (sp < VB_SM_STACK + VB_LOCAL_STACK) G = l_stack[sp - VB_SM_STACK];
+                    else G = make_uint2(0u, 0u);
+                }
+                has_node = (G.y & 0xff000000u) && !(Tg.y && Td.y);
+            }
+            // ---- phase N: one child box-test per lane ----
+            if (has_node) {
+                uint32_t hits_imask = G.y;
+                uint32_t bit = 31u - __clz(hits_imask);
+                G.y &= ~(1u << bit);
+                if (G.y & 0xff000000u) {
+                    if (sp < VB_SM_STACK) s_stack[sp * TRACE_BLOCK] = G;
+                    else if (sp < VB_SM_STACK + VB_LOCAL_STACK) l_stack[sp - VB_SM_STACK] = G;
+                    sp++;
+                }
+                uint32_t slot = (bit - 24u) ^ (oct_inv4 & 0xffu);
+                uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot) & 0xffu);
+                const uint4 *np = A.nodes + (size_t)(G.x + rel) * 5;
+                uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+                if (COUNT) nn++;
+                uint32_t hm = vb_node_hits(n0, n1, n2, n3, n4, r, idx_, idy_, idz_, oct_inv4, tmax);
+                G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
+                if (hm & 0x00ffffffu) {
+                    if (Tg.y) Td = Tg;                     // at most one of them was occupied (has_node)
+                    Tg = make_uint2(n1.y, hm & 0x00ffffffu);
+                }
+            }
+            // ---- phase T: warp-voted triangle rounds ----
+            {
+                bool tri = active && Tg.y;
+                bool node_left = (G.y & 0xff000000u) || sp > 0;
+                bool must = tri && ((Tg.y && Td.y) || !node_left);
+                unsigned tm = __ballot_sync(~0u, tri);
+                unsigned mm = __ballot_sync(~0u, must);
+                while (tm && (mm || __popc(tm) >= TRI_THR)) {
+                    if (tri) {
+                        uint32_t ti = 31u - __clz(Tg.y);
+                        Tg.y &= ~(1u << ti);
+                        const float4 *tp = A.tris + (size_t)(Tg.x + ti) * 3;
+                        float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                        if (COUNT) nt++;
+                        float t, u, v;
+                        if (vb_intersect_triangle(r, a, b, c, r.tmax, t, u, v)) {
+                            if (ANY) { occluded = true; Tg.y = 0; Td.y = 0; G.y = 0; sp = 0; }
+                            else vb_commit_hit(hit, tmax, a, b, t, u, v);
+                        }
+                        if (!Tg.y) { Tg = Td; Td = make_uint2(0u, 0u); }
+                        tri = Tg.y != 0;
+                        must = tri && ((Tg.y && Td.y) || !node_left);
+                    }
+                    tm = __ballot_sync(~0u, tri);
+                    mm = __ballot_sync(~0u, must);
+                }
+            }
+            // ---- retire finished rays ----
+            if (active && !(G.y & 0xff000000u) && sp == 0 && !Tg.y) {
+                if (ANY) occ[idx] = occluded ? 1 : 0;
+                else { H.inst[idx] = hit.inst; H.prim[idx] = hit.prim; H.u[idx] = hit.u; H.v[idx] = hit.v; H.t[idx] = hit.t; }
+                active = false;
+            }
+            act = __ballot_sync(~0u, active);
+        } while (act && (exhausted || __popc(act) >= REFILL_THR));
     }
     if (COUNT) {
         for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(~0u, nn, o); nt += __shfl_xor_sync(~0u, nt, o); }
-        if ((threadIdx.x & 31) == 0) { atomicAdd(&counters[0], nn); atomicAdd(&counters[1], nt); }
+        if (lane == 0) { atomicAdd(&counters[0], nn); atomicAdd(&counters[1], nt); }
     }
 }
 
@@ -49,7 +167,7 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
     // staging layout: [8 ray arrays][hit arrays or occlusion bytes][2 counters]
     size_t ray_bytes = rays_host ? 8 * n * sizeof(float) : 0;
     size_t out_bytes = out_host ? (any ? ((n + 15) & ~15ull) : 5 * n * 4) : 0;
-    size_t need = ray_bytes + out_bytes + 64;
+    size_t need = ray_bytes + out_bytes + 128;
     int rc = ctx->ensure_stage(need);
     if (rc) return rc;
     char *base = (char *)ctx->stage;
@@ -73,17 +191,19 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
     }
     unsigned long long *d_cnt = (unsigned long long *)(base + ray_bytes + out_bytes);
     d_cnt = (unsigned long long *)(((uintptr_t)d_cnt + 15) & ~(uintptr_t)15);
-    if (count) VB_CUDA(cudaMemsetAsync(d_cnt, 0, 16, st));
+    VB_CUDA(cudaMemsetAsync(d_cnt, 0, 32, st));       // [nodes, tris, next_ray, pad]
+    unsigned long long *d_next = d_cnt + 2;
 
     VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
-    unsigned grid = (unsigned)((n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+    // persistent grid: a multiple of the SM count, never more threads than rays
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * TRACE_BLOCKS_PER_SM, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
     ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
     if (any) {
-        if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt);
-        else k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt);
+        if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next);
+        else k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next);
     } else {
-        if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt);
-        else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt);
+        if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next);
+        else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next);
     }
     ctx->prof_end();
     VB_CHECK_LAUNCH();

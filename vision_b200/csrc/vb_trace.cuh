@@ -11,8 +11,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#define VB_SM_STACK 10
-#define VB_LOCAL_STACK 54
+#define VB_SM_STACK 12
+#define VB_LOCAL_STACK 52
 
 struct VbRay { float ox, oy, oz, tmin, dx, dy, dz, tmax; };
 struct VbHit { uint32_t inst, prim; float u, v, t; };
@@ -57,6 +57,14 @@ __device__ __forceinline__ float vb_safe_rcp(float d) {
 
 __device__ __forceinline__ uint32_t vb_byte(uint32_t w, int i) { return (w >> (8 * i)) & 0xffu; }
 
+// byte j of w -> float (32768 + byte) with ONE PRMT (no I2F): bits = 0x47000000 | byte << 8.
+// The 32768 bias is folded into the FMA addend per node; its rounding error (<= 2^-9 grid
+// units) is covered by the builder inflating every quantised child box by 2^-6 grid units.
+template <int J>
+__device__ __forceinline__ float vb_qf(uint32_t w) {
+    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404u | (J << 4)));
+}
+
 // Tests the 8 quantised child boxes of one node; returns the 32-bit hit mask
 // (bits 31..24: internal children in octant order, bits 23..0: triangles).
 __device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
@@ -65,9 +73,9 @@ __device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1,
     float adjx = __uint_as_float((n0.w & 0xffu) << 23) * idx;
     float adjy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idy;
     float adjz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idz;
-    float orx = (__uint_as_float(n0.x) - r.ox) * idx;
-    float ory = (__uint_as_float(n0.y) - r.oy) * idy;
-    float orz = (__uint_as_float(n0.z) - r.oz) * idz;
+    float orx = fmaf(-32768.f, adjx, (__uint_as_float(n0.x) - r.ox) * idx);
+    float ory = fmaf(-32768.f, adjy, (__uint_as_float(n0.y) - r.oy) * idy);
+    float orz = fmaf(-32768.f, adjz, (__uint_as_float(n0.z) - r.oz) * idz);
     uint32_t hitmask = 0;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -81,17 +89,27 @@ __device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1,
         uint32_t nx = idx < 0.f ? qhx : qlx, fx = idx < 0.f ? qlx : qhx;
         uint32_t ny = idy < 0.f ? qhy : qly, fy = idy < 0.f ? qly : qhy;
         uint32_t nz = idz < 0.f ? qhz : qlz, fz = idz < 0.f ? qlz : qhz;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            float tnx = fmaf((float)vb_byte(nx, j), adjx, orx), tfx = fmaf((float)vb_byte(fx, j), adjx, orx);
-            float tny = fmaf((float)vb_byte(ny, j), adjy, ory), tfy = fmaf((float)vb_byte(fy, j), adjy, ory);
-            float tnz = fmaf((float)vb_byte(nz, j), adjz, orz), tfz = fmaf((float)vb_byte(fz, j), adjz, orz);
-            float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tmin));
-            float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
-            if (cmin <= cmax) hitmask |= vb_byte(child_bits4, j) << vb_byte(bit_index4, j);
+#define VB_CHILD(J)                                                                                      \
+        {                                                                                                \
+            float tnx = fmaf(vb_qf<J>(nx), adjx, orx), tfx = fmaf(vb_qf<J>(fx), adjx, orx);              \
+            float tny = fmaf(vb_qf<J>(ny), adjy, ory), tfy = fmaf(vb_qf<J>(fy), adjy, ory);              \
+            float tnz = fmaf(vb_qf<J>(nz), adjz, orz), tfz = fmaf(vb_qf<J>(fz), adjz, orz);              \
+            float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tmin));                                     \
+            float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));                                       \
+            if (cmin <= cmax) hitmask |= vb_byte(child_bits4, J) << vb_byte(bit_index4, J);              \
         }
+        VB_CHILD(0) VB_CHILD(1) VB_CHILD(2) VB_CHILD(3)
+#undef VB_CHILD
     }
     return hitmask;
+}
+
+// closest-hit bookkeeping with the normative tie rule (smallest t, then smallest (inst, prim))
+__device__ __forceinline__ void vb_commit_hit(VbHit &hit, float &tmax, float4 a, float4 b, float t, float u, float v) {
+    uint32_t inst = __float_as_uint(b.w), prim = __float_as_uint(a.w);
+    bool better = hit.inst == 0xffffffffu || t < hit.t ||
+                  (t == hit.t && (inst < hit.inst || (inst == hit.inst && prim < hit.prim)));
+    if (better) { hit.inst = inst; hit.prim = prim; hit.u = u; hit.v = v; hit.t = t; tmax = t; }
 }
 
 // s_stack points at this thread's column of the shared stack: entry e lives at s_stack[e * stride]
@@ -138,10 +156,7 @@ __device__ __forceinline__ bool vb_traverse(const VbAccelView &A, VbRay r, VbHit
             float t, u, v;
             if (vb_intersect_triangle(r, a, b, c, r.tmax, t, u, v)) {
                 if (ANY) return true;
-                uint32_t inst = __float_as_uint(b.w), prim = __float_as_uint(a.w);
-                bool better = hit.inst == 0xffffffffu || t < hit.t ||
-                              (t == hit.t && (inst < hit.inst || (inst == hit.inst && prim < hit.prim)));
-                if (better) { hit.inst = inst; hit.prim = prim; hit.u = u; hit.v = v; hit.t = t; tmax = t; }
+                vb_commit_hit(hit, tmax, a, b, t, u, v);
             }
         }
         if (!(G.y & 0xff000000u)) {
