@@ -41,6 +41,8 @@ VB_API const char *vb_last_error(vb_ctx *ctx);           /* ctx may be NULL: las
  * the caller's CUDA events bracket it; NULL restores the context's own stream */
 VB_API int vb_ctx_set_stream(vb_ctx *ctx, void *cuda_stream);
 VB_API int vb_ctx_synchronize(vb_ctx *ctx);
+/* tuning knobs (defaults are the tuned values): "trace.refill_thr", "trace.tri_thr", "trace.blocks_per_sm" */
+VB_API int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value);
 /* device time (ms, CUDA events on the launching stream) and launch count of the kernels this
  * library launched since the last vb_profile_reset; name = "trace_closest" | "trace_any" |
  * "path_trace" | "bvh_build" | "film" | "all" */

@@ -68,6 +68,7 @@ def load_library() -> C.CDLL:
         "vb_ctx_destroy": [vp],
         "vb_ctx_set_stream": [vp, vp],
         "vb_ctx_synchronize": [vp],
+        "vb_ctx_set_option": [vp, C.c_char_p, C.c_double],
         "vb_profile_reset": [vp],
         "vb_profile_get": [vp, C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_uint64)],
         "vb_mesh_upload": [vp, vp, vp, vp, C.c_uint32, vp, C.c_uint32, _u32p],
@@ -143,6 +144,9 @@ class Context:
 
     def synchronize(self):
         self._check(self.lib.vb_ctx_synchronize(self.h), "vb_ctx_synchronize")
+
+    def set_option(self, key: str, value: float):
+        self._check(self.lib.vb_ctx_set_option(self.h, key.encode(), float(value)), "vb_ctx_set_option")
 
     def profile_reset(self):
         self._check(self.lib.vb_profile_reset(self.h), "vb_profile_reset")

@@ -1,6 +1,7 @@
 // Context lifecycle, mesh/instance tables, profiling slots of libvision_b200.so.
 #include "vb_internal.h"
 #include <cstring>
+#include <algorithm>
 
 static std::string g_create_err;
 
@@ -86,7 +87,7 @@ int vb_ctx_destroy(vb_ctx *ctx) {
     }
     cudaFree(ctx->d_instances);
     cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
-    cudaFree(ctx->stage);
+    cudaFree(ctx->stage); cudaFree(ctx->sort_buf);
     vb_pt_destroy(ctx);
     cudaStreamDestroy(ctx->own_stream);
     delete ctx;
@@ -104,6 +105,17 @@ int vb_ctx_synchronize(vb_ctx *ctx) {
     if (!ctx) return VB_ERR_INVALID;
     cudaSetDevice(ctx->device);
     VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VB_OK;
+}
+int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
+    if (!ctx || !key) return VB_ERR_INVALID;
+    std::string k(key);
+    if (k == "trace.refill_thr") ctx->opt_refill_thr = (int)value;
+    else if (k == "trace.tri_thr") ctx->opt_tri_thr = (int)value;
+    else if (k == "trace.sort_rays") ctx->opt_sort_rays = (int)value;
+    else if (k == "trace.sort_min_rays") ctx->opt_sort_min_rays = std::max(1, (int)value);
+    else if (k == "trace.blocks_per_sm") ctx->opt_blocks_per_sm = std::max(1, (int)value);
+    else return ctx->fail(VB_ERR_INVALID, "vb_ctx_set_option: unknown key " + k);
     return VB_OK;
 }
 int vb_profile_reset(vb_ctx *ctx) {

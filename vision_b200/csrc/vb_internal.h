@@ -67,6 +67,10 @@ struct vb_ctx {
     // staging for host-pointer calls
     void *stage = nullptr; size_t stage_bytes = 0;
     int sm_count = 148;
+    // tunables (vb_ctx_set_option)
+    int opt_refill_thr = 28, opt_tri_thr = 12, opt_blocks_per_sm = 8;
+    int opt_sort_rays = 1, opt_sort_min_rays = 1 << 16;
+    void *sort_buf = nullptr; size_t sort_bytes = 0;
     vb_pt_state *pt = nullptr;
 
     int fail(int code, const std::string &msg) { err = msg; return code; }

@@ -4,11 +4,12 @@
 #include "vb_internal.h"
 #include "vb_trace.cuh"
 #include <algorithm>
+#include <cub/device/device_radix_sort.cuh>
 
 namespace {
 
 constexpr int TRACE_BLOCK = 128;
-constexpr int TRACE_BLOCKS_PER_SM = 6;
+constexpr int TRACE_MIN_BLOCKS = 8;
 
 struct RaysDev { const float *ox, *oy, *oz, *tmin, *dx, *dy, *dz, *tmax; };
 struct HitsDev { uint32_t *inst, *prim; float *u, *v, *t; };
@@ -21,12 +22,12 @@ struct HitsDev { uint32_t *inst, *prim; float *u, *v, *t; };
 //    triangles or some lane cannot continue without testing its triangles (both pending slots
 //    full, or no node work left) - warp votes decide, so no lane spins alone in a triangle loop
 //  * results are independent of order by the tie rule, so postponing never changes the answer
-constexpr int REFILL_THR = 22;
-constexpr int TRI_THR = 10;
 
 template <bool ANY, bool COUNT>
-__global__ void __launch_bounds__(TRACE_BLOCK) k_trace(VbAccelView A, RaysDev R, uint64_t n, HitsDev H, uint8_t *occ,
-                                                       unsigned long long *counters, unsigned long long *next_ray) {
+__global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccelView A, RaysDev R, uint64_t n, HitsDev H, uint8_t *occ,
+                                                       unsigned long long *counters, unsigned long long *next_ray,
+                                                       int REFILL_THR, int TRI_THR,
+                                                       const float4 *__restrict__ RS, const uint32_t *__restrict__ perm) {
     __shared__ uint2 s_stack_all[VB_SM_STACK * TRACE_BLOCK];
     uint2 *s_stack = s_stack_all + threadIdx.x;
     uint2 l_stack[VB_LOCAL_STACK];
@@ -56,8 +57,14 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(VbAccelView A, RaysDev R,
             if (!active) {
                 idx = base + __popc(idle & lt_mask);
                 if (idx < n) {
-                    r.ox = __ldg(R.ox + idx); r.oy = __ldg(R.oy + idx); r.oz = __ldg(R.oz + idx); r.tmin = __ldg(R.tmin + idx);
-                    r.dx = __ldg(R.dx + idx); r.dy = __ldg(R.dy + idx); r.dz = __ldg(R.dz + idx); r.tmax = __ldg(R.tmax + idx);
+                    if (RS) {       // rays pre-sorted into AoS by k_reorder; results go back to slot perm[idx]
+                        float4 a = __ldg(RS + 2 * idx), b = __ldg(RS + 2 * idx + 1);
+                        r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
+                        idx = __ldg(perm + idx);
+                    } else {
+                        r.ox = __ldg(R.ox + idx); r.oy = __ldg(R.oy + idx); r.oz = __ldg(R.oz + idx); r.tmin = __ldg(R.tmin + idx);
+                        r.dx = __ldg(R.dx + idx); r.dy = __ldg(R.dy + idx); r.dz = __ldg(R.dz + idx); r.tmax = __ldg(R.tmax + idx);
+                    }
                     idx_ = vb_safe_rcp(r.dx); idy_ = vb_safe_rcp(r.dy); idz_ = vb_safe_rcp(r.dz);
                     uint32_t oct = (r.dx < 0.f ? 4u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 1u : 0u);
                     oct_inv4 = (7u - oct) * 0x01010101u;
@@ -110,12 +117,13 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(VbAccelView A, RaysDev R,
             }
             // ---- phase T: warp-voted triangle rounds ----
             {
+                // A round runs when enough lanes hold pending triangles, or when no lane of the warp
+                // could do node work this iteration (everyone is blocked on its triangles). A lane that
+                // is blocked alone just idles through phase N: cheaper than a 1-lane triangle round.
                 bool tri = active && Tg.y;
-                bool node_left = (G.y & 0xff000000u) || sp > 0;
-                bool must = tri && ((Tg.y && Td.y) || !node_left);
                 unsigned tm = __ballot_sync(~0u, tri);
-                unsigned mm = __ballot_sync(~0u, must);
-                while (tm && (mm || __popc(tm) >= TRI_THR)) {
+                bool force = __ballot_sync(~0u, has_node) == 0u;
+                while (tm && (force || __popc(tm) >= TRI_THR)) {
                     if (tri) {
                         uint32_t ti = 31u - __clz(Tg.y);
                         Tg.y &= ~(1u << ti);
@@ -129,10 +137,8 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(VbAccelView A, RaysDev R,
                         }
                         if (!Tg.y) { Tg = Td; Td = make_uint2(0u, 0u); }
                         tri = Tg.y != 0;
-                        must = tri && ((Tg.y && Td.y) || !node_left);
                     }
                     tm = __ballot_sync(~0u, tri);
-                    mm = __ballot_sync(~0u, must);
                 }
             }
             // ---- retire finished rays ----
@@ -148,6 +154,44 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(VbAccelView A, RaysDev R,
         for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(~0u, nn, o); nt += __shfl_xor_sync(~0u, nt, o); }
         if (lane == 0) { atomicAdd(&counters[0], nn); atomicAdd(&counters[1], nt); }
     }
+}
+
+
+// ---- ray sorting: 24-bit Morton code of the origin (scene-normalised) + 3-bit direction octant ----
+// Incoherent rays become spatially coherent batches: consecutive rays walk the same subtrees, so
+// node/triangle fetches hit in L1/L2 instead of going to HBM as random 80/48-byte gathers.
+__device__ __forceinline__ uint32_t expand8(uint32_t v) {      // 8 bits -> every 3rd bit
+    v &= 0xffu;
+    v = (v | (v << 8)) & 0x00f00fu;
+    v = (v | (v << 4)) & 0x0c30c3u;
+    v = (v | (v << 2)) & 0x249249u;
+    return v;
+}
+__global__ void __launch_bounds__(256) k_ray_keys(RaysDev R, uint32_t n, float3 lo, float3 inv_ext, uint32_t *keys, uint32_t *vals,
+                                                  float4 *aos) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float ox = __ldg(R.ox + i), oy = __ldg(R.oy + i), oz = __ldg(R.oz + i);
+    float dx = __ldg(R.dx + i), dy = __ldg(R.dy + i), dz = __ldg(R.dz + i);
+    // fminf/fmaxf drop NaN operands, so NaN origins land in cell 0
+    uint32_t ix = (uint32_t)fminf(fmaxf((ox - lo.x) * inv_ext.x * 256.f, 0.f), 255.f);
+    uint32_t iy = (uint32_t)fminf(fmaxf((oy - lo.y) * inv_ext.y * 256.f, 0.f), 255.f);
+    uint32_t iz = (uint32_t)fminf(fmaxf((oz - lo.z) * inv_ext.z * 256.f, 0.f), 255.f);
+    uint32_t oct = (dx < 0.f ? 4u : 0u) | (dy < 0.f ? 2u : 0u) | (dz < 0.f ? 1u : 0u);
+    keys[i] = (((expand8(ix) << 2) | (expand8(iy) << 1) | expand8(iz)) << 3) | oct;
+    vals[i] = i;
+    // SoA -> AoS copy (streaming) so that the post-sort gather touches ONE 32-byte sector per ray
+    aos[2 * (size_t)i] = make_float4(ox, oy, oz, __ldg(R.tmin + i));
+    aos[2 * (size_t)i + 1] = make_float4(dx, dy, dz, __ldg(R.tmax + i));
+}
+__global__ void __launch_bounds__(256) k_ray_reorder(const float4 *__restrict__ aos, uint32_t n, const uint32_t *__restrict__ perm,
+                                                     float4 *RS) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t j = __ldg(perm + i);
+    float4 a = __ldg(aos + 2 * (size_t)j), b = __ldg(aos + 2 * (size_t)j + 1);
+    RS[2 * (size_t)i] = a;
+    RS[2 * (size_t)i + 1] = b;
 }
 
 int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out, uint8_t *occ, vb_mem occ_mem,
@@ -196,15 +240,52 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
 
     VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
     // persistent grid: a multiple of the SM count, never more threads than rays
-    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * TRACE_BLOCKS_PER_SM, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
-    ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
-    if (any) {
-        if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next);
-        else k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next);
-    } else {
-        if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next);
-        else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next);
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctx->opt_blocks_per_sm, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+    const float4 *RS = nullptr; const uint32_t *perm = nullptr;
+    bool do_sort = ctx->opt_sort_rays && n >= (uint64_t)ctx->opt_sort_min_rays && n < (1ull << 32);
+    uint64_t launches = 1;
+    size_t cub_bytes = 0;
+    uint32_t *k0 = nullptr, *k1 = nullptr, *v0 = nullptr, *v1 = nullptr; float4 *d_rs = nullptr, *d_aos = nullptr; void *cub_tmp = nullptr;
+    if (do_sort) {
+        cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
+        VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk, dv, (int)n, 0, 27, st));
+        size_t nb = ((n * 4 + 255) & ~255ull);
+        size_t total = 4 * nb + 64 * n + cub_bytes + 256;
+        if (total > ctx->sort_bytes) {
+            if (ctx->sort_buf) cudaFree(ctx->sort_buf);
+            ctx->sort_buf = nullptr; ctx->sort_bytes = 0;
+            VB_CUDA(cudaMalloc(&ctx->sort_buf, total));
+            ctx->sort_bytes = total;
+        }
+        char *sb = (char *)ctx->sort_buf;
+        k0 = (uint32_t *)sb; k1 = (uint32_t *)(sb + nb); v0 = (uint32_t *)(sb + 2 * nb); v1 = (uint32_t *)(sb + 3 * nb);
+        d_rs = (float4 *)(sb + 4 * nb); d_aos = (float4 *)(sb + 4 * nb + 32 * n); cub_tmp = sb + 4 * nb + 64 * n;
+        cub_tmp = (void *)(((uintptr_t)cub_tmp + 255) & ~(uintptr_t)255);
     }
+    ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
+    if (do_sort) {
+        const vb_build_stats &bs = ctx->build_stats;
+        float3 lo = make_float3(bs.scene_lo[0], bs.scene_lo[1], bs.scene_lo[2]);
+        float3 ie = make_float3(1.f / fmaxf(bs.scene_hi[0] - bs.scene_lo[0], 1e-30f), 1.f / fmaxf(bs.scene_hi[1] - bs.scene_lo[1], 1e-30f),
+                                1.f / fmaxf(bs.scene_hi[2] - bs.scene_lo[2], 1e-30f));
+        unsigned g2 = (unsigned)((n + 255) / 256);
+        k_ray_keys<<<g2, 256, 0, st>>>(R, (uint32_t)n, lo, ie, k0, v0, d_aos);
+        cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
+        cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)n, 0, 27, st);
+        if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }
+        perm = dv.Current();
+        k_ray_reorder<<<g2, 256, 0, st>>>(d_aos, (uint32_t)n, perm, d_rs);
+        RS = d_rs;
+        launches += 6;
+    }
+    if (any) {
+        if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm);
+        else k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm);
+    } else {
+        if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm);
+        else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm);
+    }
+    ctx->cur_launches = launches;
     ctx->prof_end();
     VB_CHECK_LAUNCH();
 

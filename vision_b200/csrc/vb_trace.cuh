@@ -60,9 +60,18 @@ __device__ __forceinline__ uint32_t vb_byte(uint32_t w, int i) { return (w >> (8
 // byte j of w -> float (32768 + byte) with ONE PRMT (no I2F): bits = 0x47000000 | byte << 8.
 // The 32768 bias is folded into the FMA addend per node; its rounding error (<= 2^-9 grid
 // units) is covered by the builder inflating every quantised child box by 2^-6 grid units.
+// The 0x47000000 operand is kept in a register (opaque to the compiler) so that the SELECTOR is
+// the PRMT immediate; otherwise ptxas materialises one selector register per PRMT.
+__device__ __forceinline__ uint32_t vb_qf_magic() {
+    uint32_t m;
+    asm("mov.b32 %0, 0x47000000;" : "=r"(m));
+    return m;
+}
 template <int J>
-__device__ __forceinline__ float vb_qf(uint32_t w) {
-    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404u | (J << 4)));
+__device__ __forceinline__ float vb_qf(uint32_t w, uint32_t magic) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(magic), "n"(0x7404 | (J << 4)));
+    return __uint_as_float(d);
 }
 
 // Tests the 8 quantised child boxes of one node; returns the 32-bit hit mask
@@ -77,6 +86,7 @@ __device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1,
     float ory = fmaf(-32768.f, adjy, (__uint_as_float(n0.y) - r.oy) * idy);
     float orz = fmaf(-32768.f, adjz, (__uint_as_float(n0.z) - r.oz) * idz);
     uint32_t hitmask = 0;
+    const uint32_t mg = vb_qf_magic();
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         uint32_t meta4 = h ? n1.w : n1.z;
@@ -91,9 +101,9 @@ __device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1,
         uint32_t nz = idz < 0.f ? qhz : qlz, fz = idz < 0.f ? qlz : qhz;
 #define VB_CHILD(J)                                                                                      \
         {                                                                                                \
-            float tnx = fmaf(vb_qf<J>(nx), adjx, orx), tfx = fmaf(vb_qf<J>(fx), adjx, orx);              \
-            float tny = fmaf(vb_qf<J>(ny), adjy, ory), tfy = fmaf(vb_qf<J>(fy), adjy, ory);              \
-            float tnz = fmaf(vb_qf<J>(nz), adjz, orz), tfz = fmaf(vb_qf<J>(fz), adjz, orz);              \
+            float tnx = fmaf(vb_qf<J>(nx, mg), adjx, orx), tfx = fmaf(vb_qf<J>(fx, mg), adjx, orx);              \
+            float tny = fmaf(vb_qf<J>(ny, mg), adjy, ory), tfy = fmaf(vb_qf<J>(fy, mg), adjy, ory);              \
+            float tnz = fmaf(vb_qf<J>(nz, mg), adjz, orz), tfz = fmaf(vb_qf<J>(fz, mg), adjz, orz);              \
             float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tmin));                                     \
             float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));                                       \
             if (cmin <= cmax) hitmask |= vb_byte(child_bits4, J) << vb_byte(bit_index4, J);              \
