@@ -1,5 +1,116 @@
-/* vision_b200_pt.h — path-tracing part of the C ABI (included by vision_b200.h). */
+/* vision_b200_pt.h — path-tracing part of the C ABI (included by vision_b200.h).
+ *
+ * The reference's plugins (Material, Light, Sensor, Filter, Sampler, Integrator, Spectrum, ToneMapper)
+ * serialise their parameters into device memory through ocarina's Encodable/EncodedObject and are
+ * dispatched by Polymorphic<T> inside the JIT-compiled "path_tracing" kernel
+ * (reference src/base/encoded_object.cpp:22-43, src/base/mgr/scene.cpp:165-187,
+ *  src/base/integral/integrator.cpp:82-107,262-268). Here each plugin fills one POD record with a
+ * type tag; the megakernel switches on the tag. Array index = the id stored in vb_instance.
+ */
 #ifndef VISION_B200_PT_H
 #define VISION_B200_PT_H
-/* filled in below as the megakernel lands */
+
+/* ---- shader-graph slot (reference src/base/shader_graph/shader_node.cpp:242-273) -------------- */
+/* constant vector (NumberArray, number.cpp:106-109) or image texture sample at it.uv (image.cpp:87-97) */
+typedef struct vb_slot {
+    float value[4];            /* constant; when tex_id is valid the texel is multiplied by value */
+    uint32_t tex_id;           /* VB_INVALID_ID = constant */
+    uint32_t pad[3];
+} vb_slot;
+
+/* ---- textures: ImagePool (reference src/base/mgr/image_pool.cpp:13-35) ------------------------ */
+/* float4 texels, row-major, already converted to linear when the file's colour space was sRGB.
+ * Sampling: normalised uv, bilinear, wrap addressing. */
+typedef struct vb_texture {
+    const float *texels;       /* host pointer, w*h*4 floats */
+    uint32_t width, height;
+} vb_texture;
+VB_API int vb_textures_set(vb_ctx *ctx, const vb_texture *tex, uint32_t n);
+
+/* ---- materials (reference src/render_core/material/<name>.cpp) ------------------------------------- */
+enum { VB_MAT_DIFFUSE = 0, VB_MAT_MIRROR = 1, VB_MAT_GLASS = 2, VB_MAT_METAL = 3, VB_MAT_SUBSTRATE = 4,
+       VB_MAT_PRINCIPLED = 5, VB_MAT_BLACK_BODY = 6 };
+typedef struct vb_material_rec {
+    uint32_t type;
+    uint32_t flags;            /* bit0: has sigma (Oren-Nayar), bit1: remapping_roughness */
+    uint32_t pad[2];
+    vb_slot color;             /* diffuse.cpp:23, glass/mirror color, substrate diff */
+    vb_slot roughness;         /* xy */
+    vb_slot spec;              /* substrate spec / principled */
+    vb_slot ior;               /* x; glass */
+    vb_slot sigma;             /* diffuse Oren-Nayar */
+    float eta[4], k[4];        /* metal: complex ior at the 3 sRGB peak wavelengths */
+    float params[16];          /* principled: metallic, spec_tint, anisotropic, sheen, ... */
+} vb_material_rec;
+VB_API int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n);
+
+/* ---- lights (reference src/render_core/light/<name>.cpp) + alias tables (warper/alias.h:86-122) ---- */
+enum { VB_LIGHT_AREA = 0, VB_LIGHT_POINT = 1, VB_LIGHT_SPOT = 2, VB_LIGHT_ENV = 3 };
+typedef struct vb_alias_entry { float prob; uint32_t alias; } vb_alias_entry;
+typedef struct vb_light_rec {
+    uint32_t type;
+    uint32_t inst_id;          /* area: instance that carries the emission */
+    uint32_t two_sided;
+    uint32_t alias_offset;     /* area: first entry of this light's table in the shared arrays */
+    uint32_t alias_size;       /* area: number of triangles */
+    float alias_integral;      /* sum(weights)/n, alias.h:119 */
+    float scale;               /* Light::scale_ after colour normalisation (light.cpp:19-24) */
+    float pad0;
+    vb_slot color;
+    float position[4];         /* point/spot */
+    float direction[4];        /* spot */
+    float params[8];           /* spot: cos_falloff_start, cos_total_width; env: ... */
+} vb_light_rec;
+VB_API int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n,
+                         const vb_alias_entry *alias_table, const float *alias_func, uint32_t n_alias);
+
+/* ---- sensor + filter (reference src/base/sensor/sensor.cpp:44-78,153-162, thin_lens.cpp:34-42,
+ *      filter/box.cpp:16-20, filter/triangle.cpp:16-18) ------------------------------------------- */
+enum { VB_FILTER_BOX = 0, VB_FILTER_TRIANGLE = 1 };
+typedef struct vb_camera {
+    float c2w[16];             /* camera_to_world(), column-major */
+    float tan_fov_y_over_2;
+    float lens_radius, focal_distance;
+    uint32_t medium_id;
+    float screen_lo[2], screen_hi[2];   /* FrameBuffer::screen_window (frame_buffer.cpp:93-102) */
+    uint32_t filter_type;
+    float filter_radius[2];
+    uint32_t pad;
+} vb_camera;
+VB_API int vb_camera_set(vb_ctx *ctx, const vb_camera *cam);
+
+/* ---- integrator (reference src/base/integral/integrator.cpp:59-66) ---------------------------- */
+typedef struct vb_pt_params {
+    uint32_t max_depth, min_depth;
+    float rr_threshold;
+    uint32_t mis_mode;         /* 0 both, 1 light, 2 bsdf (integrator.h:116-120) */
+    uint32_t spectrum;         /* 0 = srgb */
+    uint32_t sampler;          /* 0 = independent (TEA + LCG) */
+    uint32_t process_mediums;
+    float ray_offset_factor;   /* Interaction::s_ray_offset_factor, node_desc.cpp:375 */
+} vb_pt_params;
+VB_API int vb_integrator_set(vb_ctx *ctx, const vb_pt_params *p);
+
+/* ---- film (reference src/base/sensor/frame_buffer.cpp:117-144) -------------------------------- */
+enum { VB_ACCUM_LERP = 0, VB_ACCUM_SUM = 1 };
+enum { VB_FILM_RT = 0, VB_FILM_ACCUM = 1, VB_FILM_OUTPUT = 2 };
+enum { VB_TONEMAP_LINEAR = 0, VB_TONEMAP_ACES = 1, VB_TONEMAP_REINHARD = 2 };
+VB_API int vb_film_create(vb_ctx *ctx, uint32_t width, uint32_t height);
+VB_API int vb_film_clear(vb_ctx *ctx);
+/* renders frames first, first+stride, ... (n_frames of them): camera ray (rt_geom) + Li (path_tracing)
+ * + accumulation. LERP = the reference's running mean acc = lerp(1/(k+1), acc, rt) with k the count of
+ * frames accumulated so far on this context; SUM = acc += (L, 1) for multi-GPU reduction. */
+VB_API int vb_render_frames(vb_ctx *ctx, uint32_t first_frame, uint32_t n_frames, uint32_t frame_stride, int accumulate_mode);
+/* ACCUM -> OUTPUT: (SUM mode: divide by acc.w first) 1-exp(-x*exposure) -> tone map -> w = 1 */
+VB_API int vb_film_resolve(vb_ctx *ctx, int accumulate_mode, float exposure, int tonemap);
+VB_API int vb_film_download(vb_ctx *ctx, float *rgba, int which);
+/* device address of a film plane (w*h float4), for the NCCL all-reduce of the SUM film across GPUs */
+VB_API int vb_film_device_ptr(vb_ctx *ctx, int which, void **ptr);
+
+/* ---- debug / parity surface ------------------------------------------------------------------- */
+/* primary hit of every pixel for one frame index (== reference rt_compute_pixel, frame_buffer.cpp:277-291) */
+VB_API int vb_dump_primary_hits(vb_ctx *ctx, uint32_t frame_index, const vb_hits_soa *out);
+/* counters of the last vb_render_frames call: [0] closest-hit rays, [1] any-hit rays, [2] shaded vertices */
+VB_API int vb_render_stats(vb_ctx *ctx, uint64_t stats[4]);
+
 #endif

@@ -1,0 +1,134 @@
+// ORACLE — test infrastructure only (see vo_math.h header). PARITY UNPINNED.
+// extern "C" surface of the oracle path tracer for ctypes.
+#include "vo_pt.h"
+#include <thread>
+#include <atomic>
+#include <chrono>
+
+using namespace vo;
+
+extern "C" {
+
+void *vo_scene_create() { return new Scene(); }
+void vo_scene_destroy(void *h) { delete (Scene *)h; }
+
+uint32_t vo_scene_add_mesh(void *h, const float *pos3, const float *nrm3, const float *uv2, uint32_t nv,
+                           const uint32_t *tri3, uint32_t nt) {
+    Scene &s = *(Scene *)h;
+    MeshData m;
+    m.pos.resize(nv); m.nrm.assign(nv, float3{0, 0, 0}); m.uv.assign(nv, float2{0, 0});
+    for (uint32_t i = 0; i < nv; ++i) {
+        m.pos[i] = {pos3[3 * i], pos3[3 * i + 1], pos3[3 * i + 2]};
+        if (nrm3) m.nrm[i] = {nrm3[3 * i], nrm3[3 * i + 1], nrm3[3 * i + 2]};
+        if (uv2) m.uv[i] = {uv2[2 * i], uv2[2 * i + 1]};
+    }
+    m.tri.assign(tri3, tri3 + 3 * (size_t)nt);
+    s.meshes.push_back(std::move(m));
+    return (uint32_t)s.meshes.size() - 1;
+}
+void vo_scene_set_instances(void *h, const vb_instance *inst, uint32_t n) { ((Scene *)h)->set_instances(inst, n); }
+void vo_scene_set_materials(void *h, const vb_material_rec *m, uint32_t n) { ((Scene *)h)->materials.assign(m, m + n); }
+void vo_scene_set_lights(void *h, const vb_light_rec *l, uint32_t n, const vb_alias_entry *t, const float *f, uint32_t na) {
+    Scene &s = *(Scene *)h;
+    s.lights.assign(l, l + n);
+    s.alias_table.assign(t, t + na);
+    s.alias_func.assign(f, f + na);
+}
+void vo_scene_set_textures(void *h, const vb_texture *t, uint32_t n) {
+    Scene &s = *(Scene *)h;
+    s.textures.resize(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        s.textures[i].w = t[i].width; s.textures[i].h = t[i].height;
+        const float4 *p = (const float4 *)t[i].texels;
+        s.textures[i].texels.assign(p, p + (size_t)t[i].width * t[i].height);
+    }
+}
+void vo_scene_set_camera(void *h, const vb_camera *c) { ((Scene *)h)->camera = *c; }
+void vo_scene_set_integrator(void *h, const vb_pt_params *p) { ((Scene *)h)->params = *p; }
+void vo_scene_build(void *h, int threads, int brute) {
+    Scene &s = *(Scene *)h;
+    s.brute = brute != 0;
+    s.build(threads);
+}
+
+// Renders frames first, first+stride, ... into accum (w*h float4).
+// mode 0 (LERP): acc = lerp(1/(k+1), acc, (L,1)), k = frames_done + i  (reference frame_buffer.cpp:117-126)
+// mode 1 (SUM):  acc += (L,1)
+// stats5 (nullable): closest rays, any rays, shaded vertices, nodes, tris. Returns seconds.
+double vo_render(void *h, uint32_t w, uint32_t hgt, uint32_t first, uint32_t n_frames, uint32_t stride, int mode,
+                 uint32_t frames_done, float *accum, int threads, uint64_t *stats5) {
+    const Scene &s = *(Scene *)h;
+    threads = std::max(1, threads);
+    std::vector<PathStats> st(threads);
+    auto t0 = std::chrono::steady_clock::now();
+    std::atomic<uint32_t> next_row{0};
+    auto work = [&](int tid) {
+        for (;;) {
+            uint32_t y = next_row.fetch_add(1);
+            if (y >= hgt) break;
+            for (uint32_t x = 0; x < w; ++x) {
+                float *a = accum + 4 * ((size_t)y * w + x);
+                for (uint32_t i = 0; i < n_frames; ++i) {
+                    uint32_t frame = first + i * stride;
+                    float3 L = s.render_sample(x, y, w, hgt, frame, nullptr, stats5 ? &st[tid] : nullptr);
+                    float v[4] = {L.x, L.y, L.z, 1.0f};
+                    if (mode == 0) {
+                        float t = 1.0f / (float)(frames_done + i + 1);
+                        for (int c = 0; c < 4; ++c) a[c] = a[c] + t * (v[c] - a[c]);
+                    } else {
+                        for (int c = 0; c < 4; ++c) a[c] += v[c];
+                    }
+                }
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < threads; ++t) th.emplace_back(work, t);
+    work(0);
+    for (auto &x : th) x.join();
+    double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (stats5) {
+        for (int i = 0; i < 5; ++i) stats5[i] = 0;
+        for (auto &p : st) { stats5[0] += p.closest; stats5[1] += p.any; stats5[2] += p.vertices; stats5[3] += p.nodes; stats5[4] += p.tris; }
+    }
+    return dt;
+}
+
+// primary hits for one frame index (== reference rt_compute_pixel / the trace inside rt_geom)
+void vo_primary_hits(void *h, uint32_t w, uint32_t hgt, uint32_t frame, uint32_t *inst, uint32_t *prim, float *u, float *v,
+                     float *t, int threads) {
+    const Scene &s = *(Scene *)h;
+    // only the camera ray + first trace are needed: run with max_depth 0 on a copy of the params
+    Scene *ms = (Scene *)h;
+    uint32_t saved = ms->params.max_depth;
+    ms->params.max_depth = 0;
+    std::atomic<uint32_t> next_row{0};
+    auto work = [&]() {
+        for (;;) {
+            uint32_t y = next_row.fetch_add(1);
+            if (y >= hgt) break;
+            for (uint32_t x = 0; x < w; ++x) {
+                Hit ph;
+                s.render_sample(x, y, w, hgt, frame, &ph, nullptr);
+                size_t i = (size_t)y * w + x;
+                inst[i] = ph.inst; prim[i] = ph.prim; u[i] = ph.u; v[i] = ph.v; t[i] = ph.t;
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (int k = 1; k < std::max(1, threads); ++k) th.emplace_back(work);
+    work();
+    for (auto &x : th) x.join();
+    ms->params.max_depth = saved;
+}
+
+// known-answer helpers
+uint32_t vo_tea4(uint32_t a, uint32_t b) { return tea4(a, b); }
+float vo_lcg(uint32_t *state) { return lcg(*state); }
+void vo_sincos_2pi(float u, float *s, float *c) { sincos_2pi(u, *s, *c); }
+void vo_offset_ray_origin(const float *p, const float *n, float *out) {
+    float3 r = offset_ray_origin({p[0], p[1], p[2]}, {n[0], n[1], n[2]});
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+
+}  // extern "C"

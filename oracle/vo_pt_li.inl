@@ -1,0 +1,317 @@
+// ORACLE — test infrastructure only. Included by vo_pt.cpp (same translation unit).
+// Interaction, lights, materials, Li and the per-pixel-sample driver.
+namespace vo {
+namespace {
+
+inline float3 apply_normal(const InstanceX &I, float3 n) {
+    const float *m = I.nmat;
+    return {std::fmaf(m[2], n.z, std::fmaf(m[1], n.y, m[0] * n.x)),
+            std::fmaf(m[5], n.z, std::fmaf(m[4], n.y, m[3] * n.x)),
+            std::fmaf(m[8], n.z, std::fmaf(m[7], n.y, m[6] * n.x))};
+}
+
+// reference src/base/mgr/geometry.cpp:79-166
+Interaction compute_surface_interaction(const Scene &sc, uint32_t inst_id, uint32_t prim_id, float bu, float bv, bool is_complete) {
+    Interaction it;
+    it.prim_id = prim_id;
+    const InstanceX &I = sc.instances[inst_id];
+    const MeshData &m = sc.meshes[I.rec.mesh_id];
+    uint32_t i0 = m.tri[3 * prim_id], i1 = m.tri[3 * prim_id + 1], i2 = m.tri[3 * prim_id + 2];
+    it.light_id = I.rec.light_id; it.mat_id = I.rec.material_id;
+    it.inside = I.rec.inside_medium; it.outside = I.rec.outside_medium;
+    float3 p0 = transform_point(I.o2w, m.pos[i0]), p1 = transform_point(I.o2w, m.pos[i1]), p2 = transform_point(I.o2w, m.pos[i2]);
+    it.pos = lerp3(bu, bv, p0, p1, p2);
+    float3 dp02 = p0 - p2, dp12 = p1 - p2;
+    float3 ng_un = cross(dp02, dp12);
+    it.prim_area = 0.5f * length(ng_un);
+    float2 t0 = m.uv[i0], t1 = m.uv[i1], t2 = m.uv[i2];
+    float2 duv02{t0.x - t2.x, t0.y - t2.y}, duv12{t1.x - t2.x, t1.y - t2.y};
+    float det = duv02.x * duv12.y - duv02.y * duv12.x;
+    bool degenerate_uv = std::fabs(det) < 1e-8f;
+    Frame frame;
+    if (is_complete) {
+        float3 dp_du, dp_dv;
+        if (!degenerate_uv) {
+            float inv_det = 1.0f / det;
+            dp_du = normalize((dp02 * duv12.y - dp12 * duv02.y) * inv_det);
+            dp_dv = normalize((dp02 * (-duv12.x) + dp12 * duv02.x) * inv_det);
+        } else {
+            dp_du = normalize(p1 - p0);
+            dp_dv = normalize(p2 - p0);
+        }
+        frame.x = dp_du; frame.y = dp_dv; frame.z = normalize(ng_un);
+    } else {
+        frame.x = dp02; frame.y = dp12; frame.z = normalize(ng_un);
+    }
+    it.shading = frame;
+    if (is_complete) {
+        float3 normal = lerp3(bu, bv, m.nrm[i0], m.nrm[i1], m.nrm[i2]);
+        if (!is_zero(normal)) {
+            float3 ns = normalize(apply_normal(I, normal));
+            it.shading.update(ns);
+        }
+    }
+    it.uv = lerp2(bu, bv, t0, t1, t2);
+    it.ng = frame.z;
+    return it;
+}
+
+inline float3 flip_to(float3 n, float3 dir) { return dot(n, dir) > 0.f ? n : -n; }
+
+// reference interaction.h:279-299 / interaction.cpp:115-135
+inline Ray spawn_ray(const Interaction &it, float3 dir) {
+    float3 n = flip_to(it.ng, dir);
+    float3 org = offset_ray_origin(it.pos, n);
+    return Ray{org, 0.f, dir, RayTMax};
+}
+inline Ray spawn_ray_to(const Interaction &it, float3 target) {
+    float3 dir = target - it.pos;
+    float3 n = flip_to(it.ng, dir);
+    float3 org = offset_ray_origin(it.pos, n);
+    return Ray{org, 0.f, dir, 1.0f - ShadowEpsilon};
+}
+
+struct LightEvalCtx { float3 pos, ng; float2 uv; float pdf_pos; };
+struct LightEval { float3 L{0, 0, 0}; float pdf = 0.f; };
+struct LightSample { LightEval eval; float3 p_light{0, 0, 0}; };
+
+// ---- alias table, reference warper/alias.h:45-53,135-167 ----
+inline float alias_pmf(const Scene &sc, const vb_light_rec &l, uint32_t i) {
+    return l.alias_integral > 0.f ? sc.alias_func[l.alias_offset + i] / (l.alias_integral * (float)l.alias_size) : 0.f;
+}
+inline uint32_t alias_sample(const Scene &sc, const vb_light_rec &l, float u, float &pmf, float &u_remapped) {
+    uint32_t size = l.alias_size;
+    u = u * (float)size;
+    uint32_t idx = std::min((uint32_t)u, size - 1);
+    u = std::min(u - (float)idx, OneMinusEpsilon);
+    vb_alias_entry e = sc.alias_table[l.alias_offset + idx];
+    bool keep = u < e.prob;
+    uint32_t out = keep ? idx : e.alias;
+    u_remapped = keep ? std::min(u / e.prob, OneMinusEpsilon) : std::min((1.0f - u) / (1.0f - e.prob), OneMinusEpsilon);
+    pmf = alias_pmf(sc, l, out);
+    return out;
+}
+
+// ---- area light, reference render_core/light/area.cpp:92-149, light.h:126-130, warp.h:88-94 ----
+inline LightEval area_evaluate_wi(const Scene &sc, const vb_light_rec &l, float3 ref_pos, const LightEvalCtx &pl) {
+    LightEval ev;
+    float3 w = ref_pos - pl.pos;
+    float3 color = eval_slot3(sc, l.color, pl.uv);
+    float s = (dot(w, pl.ng) > 0.f || l.two_sided) ? 1.f : 0.f;
+    ev.L = color * l.scale * s;
+    float cos_theta = std::fabs(dot(pl.ng, normalize(w)));
+    float pdf = pl.pdf_pos * length_squared(w) / cos_theta;
+    ev.pdf = (std::isinf(pdf) || std::isnan(pdf)) ? 0.f : pdf;
+    return ev;
+}
+
+inline LightSample area_sample_wi(const Scene &sc, const vb_light_rec &l, const Interaction &ref, float2 u) {
+    float pmf, ux;
+    uint32_t prim = alias_sample(sc, l, u.x, pmf, ux);
+    float su0 = std::sqrt(ux);
+    float b0 = 1.0f - su0, b1 = u.y * su0;                       // square_to_triangle, warp.h:64-68
+    Interaction li = compute_surface_interaction(sc, l.inst_id, prim, b0, b1, false);
+    LightEvalCtx pl{li.pos, li.ng, li.uv, 1.0f / li.prim_area};
+    pl.pdf_pos *= pmf;
+    LightSample ls;
+    ls.eval = area_evaluate_wi(sc, l, ref.pos, pl);
+    float3 dir = ref.pos - pl.pos;
+    float factor = dot(pl.ng, dir) > 0.f ? 1.f : -1.f;           // SpacePoint::robust_pos
+    ls.p_light = offset_ray_origin(pl.pos, pl.ng * factor * sc.params.ray_offset_factor);
+    return ls;
+}
+
+// reference lightsampler.cpp:210-216 + uniform.cpp:24-33
+inline LightSample sample_light(const Scene &sc, const Interaction &it, Sampler &sampler) {
+    float u_light = sampler.next_1d();
+    float2 u_surface = sampler.next_2d();
+    LightSample ls;
+    uint32_t n = (uint32_t)sc.lights.size();
+    if (n == 0) return ls;
+    uint32_t index = (uint32_t)std::min(u_light * (float)n, (float)n - 1.0f);
+    float pmf = 1.0f / (float)n;
+    const vb_light_rec &l = sc.lights[index];
+    if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(sc, l, it, u_surface);
+    ls.eval.pdf *= pmf;
+    return ls;
+}
+
+// reference lightsampler.cpp:252-267
+inline LightEval evaluate_hit_wi(const Scene &sc, float3 ref_pos, const Interaction &it) {
+    LightEval ev;
+    const vb_light_rec &l = sc.lights[it.light_id];
+    if (l.type != VB_LIGHT_AREA) return ev;
+    LightEvalCtx pl{it.pos, it.ng, it.uv, 1.0f / it.prim_area};
+    pl.pdf_pos *= alias_pmf(sc, l, it.prim_id);
+    ev = area_evaluate_wi(sc, l, ref_pos, pl);
+    ev.pdf *= 1.0f / (float)sc.lights.size();
+    return ev;
+}
+
+struct ScatterEval { float3 f{0, 0, 0}; float pdf = 0.f; uint32_t flags = 1; };
+struct BSDFSample { ScatterEval eval; float3 wi{0, 0, 0}; float eta = 1.f; };
+constexpr uint32_t FlagReflection = 1u << 1, FlagTransmission = 1u << 2, FlagDiffuse = 1u << 3;
+
+struct DiffuseLobe { float3 kr; Frame frame; };
+
+// reference lobe.cpp:53-63 (evaluate_impl), bxdf.cpp:34-46 (safe_evaluate), bxdf.h:82-96 (Lambert)
+inline ScatterEval diffuse_evaluate(const DiffuseLobe &lb, float3 world_wo, float3 world_wi) {
+    float3 wo = lb.frame.to_local(world_wo), wi = lb.frame.to_local(world_wi);
+    ScatterEval se;
+    bool s = wo.z * wi.z > 0.f;                                   // same_hemisphere
+    se.f = s ? lb.kr * InvPi : float3{0, 0, 0};
+    se.pdf = s ? std::fabs(wi.z) * InvPi : 0.f;                   // cosine_hemisphere_PDF(abs_cos_theta)
+    se.flags = FlagDiffuse | FlagReflection;
+    se.f = se.f * std::fabs(wi.z);
+    return se;
+}
+// reference bxdf.cpp:48-52 + warp.h:23-40
+inline float3 diffuse_sample_wi(const DiffuseLobe &lb, float3 world_wo, float2 u) {
+    float3 wo = lb.frame.to_local(world_wo);
+    float r = std::sqrt(u.x), s, c;
+    sincos_2pi(u.y, s, c);
+    float dx = r * c, dy = r * s;
+    float z = std::sqrt(std::max(0.0f, 1.0f - dx * dx - dy * dy));
+    if (wo.z < 0.f) z = -z;
+    return lb.frame.to_world(float3{dx, dy, z});
+}
+
+// MaterialEvaluator (individual_ns branch), reference material.cpp:132-142,163-175
+struct Evaluator {
+    uint32_t type = VB_MAT_DIFFUSE;
+    DiffuseLobe diffuse;
+    float3 ng;
+    ScatterEval evaluate(float3 wo, float3 wi) const {
+        ScatterEval se = diffuse_evaluate(diffuse, wo, wi);
+        bool same = dot(wo, ng) * dot(wi, ng) > 0.f;
+        bool is_trans = (se.flags & FlagTransmission) != 0;
+        if (same == is_trans) se.pdf = 0.f;
+        return se;
+    }
+    BSDFSample sample(float3 wo, Sampler &sampler) const {
+        BSDFSample bs;
+        float2 u = sampler.next_2d();
+        bs.wi = diffuse_sample_wi(diffuse, wo, u);
+        bs.eval = evaluate(wo, bs.wi);
+        bs.eta = 1.f;
+        return bs;
+    }
+};
+
+inline Evaluator create_evaluator(const Scene &sc, const Interaction &it) {
+    Evaluator ev;
+    const vb_material_rec &m = sc.materials[it.mat_id];
+    ev.type = m.type;
+    ev.ng = it.ng;
+    ev.diffuse.frame = it.shading;
+    ev.diffuse.kr = (m.type == VB_MAT_DIFFUSE) ? eval_slot3(sc, m.color, it.uv) : float3{0, 0, 0};
+    return ev;
+}
+
+inline float mis_weight(float f, float g) { return (1.0f * f) / (1.0f * f + 1.0f * g); }   // warp.h:148-153,187-199
+
+}  // namespace
+
+float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st) const {
+    Sampler sampler;
+    // ---- rt_geom: camera ray, reference frame_buffer.cpp:172-182, sampler.h:65-73 ----
+    sampler.start(px, py, frame, 0u);
+    float2 uf = sampler.next_2d();
+    float2 fp;
+    if (camera.filter_type == VB_FILTER_TRIANGLE) {
+        auto sample_linear10 = [](float u) {           // sample_linear(u, a=1, b=0), warp.h:123-130
+            float a = 1.f, b = 0.f;
+            float x = u * (a + b) / (a + std::sqrt((a * a) + u * ((b * b) - (a * a))));
+            return std::min(x, OneMinusEpsilon);
+        };
+        auto tent = [&](float u, float r) {
+            return u < 0.5f ? -r * sample_linear10((0.5f - u) * 2.f) : r * sample_linear10((u - 0.5f) * 2.f);
+        };
+        fp = {tent(uf.x, camera.filter_radius[0]), tent(uf.y, camera.filter_radius[1])};
+    } else {
+        float rx = camera.filter_radius[0], ry = camera.filter_radius[1];
+        fp = {-rx + uf.x * (rx - (-rx)), -ry + uf.y * (ry - (-ry))};
+    }
+    float2 p_film{(float)px + 0.5f + fp.x, (float)py + 0.5f + fp.y};
+    float2 u_lens = sampler.next_2d();
+    (void)sampler.next_1d();   // time
+    // Sensor::generate_ray, sensor.cpp:44-56 (raster -> screen window -> camera space at z = 1)
+    float sx = camera.screen_lo[0] + p_film.x / (float)w * (camera.screen_hi[0] - camera.screen_lo[0]);
+    float sy = camera.screen_hi[1] - p_film.y / (float)h * (camera.screen_hi[1] - camera.screen_lo[1]);
+    float3 dir = normalize(float3{sx * camera.tan_fov_y_over_2, sy * camera.tan_fov_y_over_2, 1.0f});
+    float3 org{0, 0, 0};
+    {   // thin_lens.cpp:34-42 (lens_radius 0 still draws the lens sample)
+        float rr = std::sqrt(u_lens.x), s, c;
+        sincos_2pi(u_lens.y, s, c);
+        float2 pl{rr * c * camera.lens_radius, rr * s * camera.lens_radius};
+        float ft = camera.focal_distance / dir.z;
+        float3 p_focus = dir * ft;
+        org = {pl.x, pl.y, 0.f};
+        dir = normalize(p_focus - org);
+    }
+    float4x4 c2w; std::memcpy(&c2w, camera.c2w, 64);
+    Ray ray{transform_point(c2w, org), 0.f, transform_vector(c2w, dir), RayTMax};
+    Hit ph = trace_closest(ray, st);          // rt_geom's own primary trace (frame_buffer.cpp:179)
+    if (primary) *primary = ph;
+
+    // ---- path_tracing kernel: reference integrator.cpp:85-99 ----
+    sampler.start(px, py, frame, 1u);
+    float scatter_pdf = 1e16f;
+    float3 throughput{1, 1, 1}, ret{0, 0, 0};
+    float3 prev_surface_ng = ray.d;
+    float eta_scale = 1.f;
+    const uint32_t max_depth = params.max_depth;
+    for (uint32_t bounces = 0; bounces < max_depth; ++bounces) {
+        Hit hit = trace_closest(ray, st);
+        if (hit.is_miss()) break;                                   // no environment light in this build
+        Interaction it = compute_surface_interaction(*this, hit.inst, hit.prim, hit.u, hit.v, true);
+        it.wo = normalize(-ray.d);
+        if (st) st->vertices++;
+        if (it.mat_id == VB_INVALID_ID) {                          // integrator.cpp:208-214
+            ray = spawn_ray(it, ray.d);
+            bounces -= 1;                                           // wraps like the reference's Uint
+            continue;
+        }
+        if (it.light_id != VB_INVALID_ID) {                        // integrator.cpp:221-231
+            LightEval ev = evaluate_hit_wi(*this, ray.o, it);
+            float weight = mis_weight(scatter_pdf, ev.pdf);
+            if (params.mis_mode == 2) weight = 1.f;
+            else if (params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
+            ret += ev.L * throughput * weight;
+        }
+        prev_surface_ng = it.ng;
+        // light sampling + shadow ray, integrator.cpp:241-244
+        LightSample ls = sample_light(*this, it, sampler);
+        Ray shadow = spawn_ray_to(it, ls.p_light);
+        bool occluded = trace_any(shadow, st);
+        // material, integrator.cpp:262-268 + direct_lighting :20-37
+        Evaluator evaluator = create_evaluator(*this, it);
+        float3 wi = normalize(ls.p_light - it.pos);
+        ScatterEval se = evaluator.evaluate(it.wo, wi);
+        BSDFSample bs = evaluator.sample(it.wo, sampler);
+        bool is_delta = ls.eval.pdf < 0.f;
+        float weight = is_delta ? 1.f : mis_weight(ls.eval.pdf, se.pdf);
+        if (params.mis_mode == 1) weight = 1.f;
+        float lpdf = is_delta ? -ls.eval.pdf : ls.eval.pdf;
+        float3 Ld{0, 0, 0};
+        if (!occluded && se.pdf > 0.f && lpdf > 0.f) Ld = ls.eval.L * se.f * weight / lpdf;
+        if (params.mis_mode == 2) Ld = Ld * 0.f;
+        ret += throughput * Ld;
+        eta_scale *= bs.eta * bs.eta;
+        float lum = max_comp(throughput);
+        if (!(bs.eval.pdf > 0.f) || lum == 0.f) break;
+        throughput *= bs.eval.f / bs.eval.pdf;
+        if (eta_scale * lum < params.rr_threshold && bounces >= params.min_depth) {
+            float q = std::min(0.95f, lum);
+            float rr = sampler.next_1d();
+            if (q < rr) break;
+            throughput = throughput / q;
+        }
+        scatter_pdf = bs.eval.pdf;
+        ray = spawn_ray(it, bs.wi);
+    }
+    (void)prev_surface_ng;
+    return ret;
+}
+
+}  // namespace vo

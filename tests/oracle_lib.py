@@ -116,3 +116,86 @@ class OracleAccel:
         dt = self.o.lib.vo_trace_any(self.h, n, *[_p(np.ascontiguousarray(rays[f])) for f in RAY_FIELDS], _p(occ),
                                      threads, 1 if brute else 0, None)
         return occ, dt
+
+
+# ---------------------------------------------------------------------------------------------
+# oracle path tracer
+# ---------------------------------------------------------------------------------------------
+class OracleScene:
+    """uploads a vision_b200.capi.SceneRecords into the oracle and renders it on the CPU"""
+
+    def __init__(self, o: Oracle, sc, brute=False, threads=8):
+        from vision_b200 import capi
+        self.o, self.sc = o, sc
+        lib = o.lib
+        vp = C.c_void_p
+        lib.vo_scene_create.restype = vp
+        lib.vo_scene_destroy.argtypes = [vp]
+        lib.vo_scene_add_mesh.argtypes = [vp, vp, vp, vp, C.c_uint32, vp, C.c_uint32]
+        lib.vo_scene_add_mesh.restype = C.c_uint32
+        lib.vo_scene_set_instances.argtypes = [vp, vp, C.c_uint32]
+        lib.vo_scene_set_materials.argtypes = [vp, vp, C.c_uint32]
+        lib.vo_scene_set_lights.argtypes = [vp, vp, C.c_uint32, vp, vp, C.c_uint32]
+        lib.vo_scene_set_textures.argtypes = [vp, vp, C.c_uint32]
+        lib.vo_scene_set_camera.argtypes = [vp, vp]
+        lib.vo_scene_set_integrator.argtypes = [vp, vp]
+        lib.vo_scene_build.argtypes = [vp, C.c_int, C.c_int]
+        lib.vo_render.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_uint32, vp, C.c_int, vp]
+        lib.vo_render.restype = C.c_double
+        lib.vo_primary_hits.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp, C.c_int]
+        for f in ("vo_scene_destroy", "vo_scene_set_instances", "vo_scene_set_materials", "vo_scene_set_lights",
+                  "vo_scene_set_textures", "vo_scene_set_camera", "vo_scene_set_integrator", "vo_scene_build", "vo_primary_hits"):
+            getattr(lib, f).restype = None
+        self.h = C.c_void_p(lib.vo_scene_create())
+        for m in sc.meshes:
+            pos = np.ascontiguousarray(m["pos"], np.float32).reshape(-1, 3)
+            tri = np.ascontiguousarray(m["tri"], np.uint32).reshape(-1, 3)
+            nrm = None if m.get("nrm") is None else np.ascontiguousarray(m["nrm"], np.float32)
+            uv = None if m.get("uv") is None else np.ascontiguousarray(m["uv"], np.float32)
+            lib.vo_scene_add_mesh(self.h, _p(pos), _p(nrm), _p(uv), len(pos), _p(tri), len(tri))
+        inst = (capi.vb_instance * len(sc.instances))()
+        for i, d in enumerate(sc.instances):
+            inst[i].mesh_id = d["mesh_id"]
+            for k in ("material_id", "light_id", "inside_medium", "outside_medium", "lightmap_id"):
+                setattr(inst[i], k, d.get(k, 0xFFFFFFFF))
+            inst[i].o2w[:] = [float(x) for x in np.asarray(d["o2w"], np.float32).reshape(-1)]
+        lib.vo_scene_set_instances(self.h, C.cast(inst, vp), len(sc.instances))
+        mats = (capi.vb_material_rec * max(1, len(sc.materials)))(*sc.materials)
+        lib.vo_scene_set_materials(self.h, C.cast(mats, vp), len(sc.materials))
+        lights = (capi.vb_light_rec * max(1, len(sc.lights)))(*sc.lights)
+        na = len(sc.alias_table)
+        tab = (capi.vb_alias_entry * max(1, na))(*[capi.vb_alias_entry(p, a) for p, a in sc.alias_table])
+        func = np.ascontiguousarray(sc.alias_func if na else [0.0], np.float32)
+        lib.vo_scene_set_lights(self.h, C.cast(lights, vp), len(sc.lights), C.cast(tab, vp), _p(func), na)
+        texs = (capi.vb_texture * max(1, len(sc.textures)))()
+        keep = []
+        for i, t in enumerate(sc.textures):
+            a = np.ascontiguousarray(t, np.float32); keep.append(a)
+            texs[i].texels = a.ctypes.data; texs[i].height, texs[i].width = a.shape[0], a.shape[1]
+        lib.vo_scene_set_textures(self.h, C.cast(texs, vp), len(sc.textures))
+        lib.vo_scene_set_camera(self.h, C.addressof(sc.camera))
+        lib.vo_scene_set_integrator(self.h, C.addressof(sc.params))
+        lib.vo_scene_build(self.h, threads, 1 if brute else 0)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.o.lib.vo_scene_destroy(self.h)
+            self.h = None
+
+    def render(self, first, n, stride=1, mode=0, frames_done=0, accum=None, threads=8, stats=False):
+        w, h = self.sc.resolution
+        if accum is None:
+            accum = np.zeros((h, w, 4), np.float32)
+        st = np.zeros(5, np.uint64) if stats else None
+        dt = self.o.lib.vo_render(self.h, w, h, first, n, stride, mode, frames_done, _p(accum), threads, _p(st))
+        if stats:
+            return accum, dt, {"closest": int(st[0]), "any": int(st[1]), "vertices": int(st[2]), "nodes": int(st[3]), "tris": int(st[4])}
+        return accum, dt
+
+    def primary_hits(self, frame, threads=8):
+        w, h = self.sc.resolution
+        n = w * h
+        out = {"inst": np.empty(n, np.uint32), "prim": np.empty(n, np.uint32), "u": np.empty(n, np.float32),
+               "v": np.empty(n, np.float32), "t": np.empty(n, np.float32)}
+        self.o.lib.vo_primary_hits(self.h, w, h, frame, *[_p(out[f]) for f in ("inst", "prim", "u", "v", "t")], threads)
+        return out

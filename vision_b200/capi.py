@@ -262,3 +262,174 @@ class Context:
             return out, a.value, b.value
         self._check(self.lib.vb_trace_any(self.h, C.byref(r), n, _ptr(out), mem), "vb_trace_any")
         return out
+
+
+# ---------------------------------------------------------------------------------------------
+# path-tracing records (include/vision_b200_pt.h)
+# ---------------------------------------------------------------------------------------------
+class vb_slot(C.Structure):
+    _fields_ = [("value", C.c_float * 4), ("tex_id", C.c_uint32), ("pad", C.c_uint32 * 3)]
+
+
+class vb_texture(C.Structure):
+    _fields_ = [("texels", C.c_void_p), ("width", C.c_uint32), ("height", C.c_uint32)]
+
+
+class vb_material_rec(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("flags", C.c_uint32), ("pad", C.c_uint32 * 2),
+                ("color", vb_slot), ("roughness", vb_slot), ("spec", vb_slot), ("ior", vb_slot), ("sigma", vb_slot),
+                ("eta", C.c_float * 4), ("k", C.c_float * 4), ("params", C.c_float * 16)]
+
+
+class vb_alias_entry(C.Structure):
+    _fields_ = [("prob", C.c_float), ("alias", C.c_uint32)]
+
+
+class vb_light_rec(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("inst_id", C.c_uint32), ("two_sided", C.c_uint32), ("alias_offset", C.c_uint32),
+                ("alias_size", C.c_uint32), ("alias_integral", C.c_float), ("scale", C.c_float), ("pad0", C.c_float),
+                ("color", vb_slot), ("position", C.c_float * 4), ("direction", C.c_float * 4), ("params", C.c_float * 8)]
+
+
+class vb_camera(C.Structure):
+    _fields_ = [("c2w", C.c_float * 16), ("tan_fov_y_over_2", C.c_float), ("lens_radius", C.c_float),
+                ("focal_distance", C.c_float), ("medium_id", C.c_uint32), ("screen_lo", C.c_float * 2),
+                ("screen_hi", C.c_float * 2), ("filter_type", C.c_uint32), ("filter_radius", C.c_float * 2),
+                ("pad", C.c_uint32)]
+
+
+class vb_pt_params(C.Structure):
+    _fields_ = [("max_depth", C.c_uint32), ("min_depth", C.c_uint32), ("rr_threshold", C.c_float),
+                ("mis_mode", C.c_uint32), ("spectrum", C.c_uint32), ("sampler", C.c_uint32),
+                ("process_mediums", C.c_uint32), ("ray_offset_factor", C.c_float)]
+
+
+VB_MAT_DIFFUSE, VB_MAT_MIRROR, VB_MAT_GLASS, VB_MAT_METAL, VB_MAT_SUBSTRATE, VB_MAT_PRINCIPLED, VB_MAT_BLACK_BODY = range(7)
+VB_LIGHT_AREA, VB_LIGHT_POINT, VB_LIGHT_SPOT, VB_LIGHT_ENV = range(4)
+VB_FILTER_BOX, VB_FILTER_TRIANGLE = 0, 1
+VB_ACCUM_LERP, VB_ACCUM_SUM = 0, 1
+VB_FILM_RT, VB_FILM_ACCUM, VB_FILM_OUTPUT = 0, 1, 2
+VB_TONEMAP_LINEAR, VB_TONEMAP_ACES, VB_TONEMAP_REINHARD = 0, 1, 2
+
+
+def make_slot(value, tex_id=VB_INVALID_ID) -> vb_slot:
+    s = vb_slot()
+    v = list(value) + [0.0] * (4 - len(value))
+    s.value[:] = [float(x) for x in v[:4]]
+    s.tex_id = tex_id
+    return s
+
+
+def _bind_pt(lib):
+    vp = C.c_void_p
+    sigs = {
+        "vb_textures_set": [vp, C.POINTER(vb_texture), C.c_uint32],
+        "vb_materials_set": [vp, C.POINTER(vb_material_rec), C.c_uint32],
+        "vb_lights_set": [vp, C.POINTER(vb_light_rec), C.c_uint32, C.POINTER(vb_alias_entry), vp, C.c_uint32],
+        "vb_camera_set": [vp, C.POINTER(vb_camera)],
+        "vb_integrator_set": [vp, C.POINTER(vb_pt_params)],
+        "vb_film_create": [vp, C.c_uint32, C.c_uint32],
+        "vb_film_clear": [vp],
+        "vb_render_frames": [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int],
+        "vb_film_resolve": [vp, C.c_int, C.c_float, C.c_int],
+        "vb_film_download": [vp, vp, C.c_int],
+        "vb_film_device_ptr": [vp, C.c_int, C.POINTER(vp)],
+        "vb_dump_primary_hits": [vp, C.c_uint32, C.POINTER(vb_hits_soa)],
+        "vb_render_stats": [vp, C.POINTER(C.c_uint64)],
+    }
+    for name, args in sigs.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = C.c_int
+
+
+class SceneRecords:
+    """Plain container of the POD records of one scene, uploadable to a Context (GPU) or to the oracle."""
+
+    def __init__(self):
+        self.meshes = []        # dicts: pos (nv,3), nrm (nv,3), uv (nv,2), tri (nt,3)
+        self.instances = []     # dicts as Context.instances_set
+        self.materials = []     # vb_material_rec
+        self.lights = []        # vb_light_rec
+        self.alias_table = []   # (prob, alias)
+        self.alias_func = []    # float
+        self.textures = []      # (h, w, 4) float32 arrays
+        self.camera = vb_camera()
+        self.params = vb_pt_params()
+        self.resolution = (256, 256)
+        self.exposure = 1.0
+        self.tonemap = VB_TONEMAP_LINEAR
+        self.spp = 1
+
+
+def _pt_methods():
+    def upload_scene(self, sc: SceneRecords):
+        """meshes + instances + BVH + tables + camera + film"""
+        _bind_pt(self.lib)
+        ids = [self.mesh_upload(m["pos"], m["tri"], m.get("nrm"), m.get("uv")) for m in sc.meshes]
+        inst = [dict(d, mesh_id=ids[d["mesh_id"]]) for d in sc.instances]
+        self.instances_set(inst)
+        st = self.accel_build()
+        texs = (vb_texture * max(1, len(sc.textures)))()
+        keep = []
+        for i, t in enumerate(sc.textures):
+            a = np.ascontiguousarray(t, np.float32)
+            keep.append(a)
+            texs[i].texels = a.ctypes.data; texs[i].height, texs[i].width = a.shape[0], a.shape[1]
+        self._check(self.lib.vb_textures_set(self.h, texs, len(sc.textures)), "vb_textures_set")
+        mats = (vb_material_rec * max(1, len(sc.materials)))(*sc.materials)
+        self._check(self.lib.vb_materials_set(self.h, mats, len(sc.materials)), "vb_materials_set")
+        lights = (vb_light_rec * max(1, len(sc.lights)))(*sc.lights)
+        na = len(sc.alias_table)
+        tab = (vb_alias_entry * max(1, na))(*[vb_alias_entry(p, a) for p, a in sc.alias_table])
+        func = np.ascontiguousarray(sc.alias_func if na else [0.0], np.float32)
+        self._check(self.lib.vb_lights_set(self.h, lights, len(sc.lights), tab, func.ctypes.data, na), "vb_lights_set")
+        self._check(self.lib.vb_camera_set(self.h, C.byref(sc.camera)), "vb_camera_set")
+        self._check(self.lib.vb_integrator_set(self.h, C.byref(sc.params)), "vb_integrator_set")
+        self._check(self.lib.vb_film_create(self.h, sc.resolution[0], sc.resolution[1]), "vb_film_create")
+        self._res = sc.resolution
+        return st
+
+    def render_frames(self, first, n, stride=1, mode=VB_ACCUM_LERP):
+        self._check(self.lib.vb_render_frames(self.h, first, n, stride, mode), "vb_render_frames")
+
+    def film_clear(self):
+        self._check(self.lib.vb_film_clear(self.h), "vb_film_clear")
+
+    def film_resolve(self, mode=VB_ACCUM_LERP, exposure=1.0, tonemap=VB_TONEMAP_LINEAR):
+        self._check(self.lib.vb_film_resolve(self.h, mode, exposure, tonemap), "vb_film_resolve")
+
+    def film_download(self, which=VB_FILM_ACCUM):
+        w, h = self._res
+        out = np.empty((h, w, 4), np.float32)
+        self._check(self.lib.vb_film_download(self.h, out.ctypes.data, which), "vb_film_download")
+        return out
+
+    def film_device_ptr(self, which=VB_FILM_ACCUM) -> int:
+        p = C.c_void_p()
+        self._check(self.lib.vb_film_device_ptr(self.h, which, C.byref(p)), "vb_film_device_ptr")
+        return p.value
+
+    def dump_primary_hits(self, frame):
+        w, h = self._res
+        n = w * h
+        out = {"inst": np.empty(n, np.uint32), "prim": np.empty(n, np.uint32), "u": np.empty(n, np.float32),
+               "v": np.empty(n, np.float32), "t": np.empty(n, np.float32)}
+        hs = vb_hits_soa()
+        for f in HIT_FIELDS:
+            setattr(hs, f, _ptr(out[f]))
+        hs.mem = VB_MEM_HOST
+        self._check(self.lib.vb_dump_primary_hits(self.h, frame, C.byref(hs)), "vb_dump_primary_hits")
+        return out
+
+    def render_stats(self):
+        st = (C.c_uint64 * 4)()
+        self._check(self.lib.vb_render_stats(self.h, st), "vb_render_stats")
+        return {"closest": st[0], "any": st[1], "vertices": st[2]}
+
+    for f in (upload_scene, render_frames, film_clear, film_resolve, film_download, film_device_ptr,
+              dump_primary_hits, render_stats):
+        setattr(Context, f.__name__, f)
+
+
+_pt_methods()

@@ -1,0 +1,99 @@
+// Device fp32 math for the path-tracing megakernel. Operation order mirrors oracle/vo_math.h
+// (the normative statement); vb_pt.cu is compiled with -fmad=false so only the FMAs written here
+// as __fmaf_rn fuse, exactly like the oracle under -ffp-contract=off.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace vbm {
+
+struct f3 { float x, y, z; };
+struct f2 { float x, y; };
+
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { return f3{x, y, z}; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ f3 operator*(f3 a, f3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
+__device__ __forceinline__ f3 operator*(f3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ f3 operator/(f3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+__device__ __forceinline__ f3 operator-(f3 a) { return {-a.x, -a.y, -a.z}; }
+
+__device__ __forceinline__ float dot(f3 a, f3 b) { return __fmaf_rn(a.z, b.z, __fmaf_rn(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ f3 cross(f3 a, f3 b) {
+    return {__fmaf_rn(a.y, b.z, -(a.z * b.y)), __fmaf_rn(a.z, b.x, -(a.x * b.z)), __fmaf_rn(a.x, b.y, -(a.y * b.x))};
+}
+__device__ __forceinline__ float length_squared(f3 a) { return dot(a, a); }
+__device__ __forceinline__ float length(f3 a) { return __fsqrt_rn(dot(a, a)); }
+__device__ __forceinline__ f3 normalize(f3 a) {
+    float inv = __fdiv_rn(1.0f, __fsqrt_rn(dot(a, a)));
+    return a * inv;
+}
+__device__ __forceinline__ float fmin_(float a, float b) { return b < a ? b : a; }   // == std::min
+__device__ __forceinline__ float fmax_(float a, float b) { return a < b ? b : a; }   // == std::max
+__device__ __forceinline__ float max_comp(f3 a) { return fmax_(a.x, fmax_(a.y, a.z)); }
+
+// column-major 4x4 in a flat array m[4*c + r]
+__device__ __forceinline__ f3 transform_point(const float *m, f3 p) {
+    return {__fmaf_rn(m[8], p.z, __fmaf_rn(m[4], p.y, __fmaf_rn(m[0], p.x, m[12]))),
+            __fmaf_rn(m[9], p.z, __fmaf_rn(m[5], p.y, __fmaf_rn(m[1], p.x, m[13]))),
+            __fmaf_rn(m[10], p.z, __fmaf_rn(m[6], p.y, __fmaf_rn(m[2], p.x, m[14])))};
+}
+__device__ __forceinline__ f3 transform_vector(const float *m, f3 v) {
+    return {__fmaf_rn(m[8], v.z, __fmaf_rn(m[4], v.y, m[0] * v.x)),
+            __fmaf_rn(m[9], v.z, __fmaf_rn(m[5], v.y, m[1] * v.x)),
+            __fmaf_rn(m[10], v.z, __fmaf_rn(m[6], v.y, m[2] * v.x))};
+}
+// row-major 3x3 normal matrix
+__device__ __forceinline__ f3 apply_normal(const float *m, f3 n) {
+    return {__fmaf_rn(m[2], n.z, __fmaf_rn(m[1], n.y, m[0] * n.x)),
+            __fmaf_rn(m[5], n.z, __fmaf_rn(m[4], n.y, m[3] * n.x)),
+            __fmaf_rn(m[8], n.z, __fmaf_rn(m[7], n.y, m[6] * n.x))};
+}
+
+constexpr float Pi = 3.14159265358979323846f;
+constexpr float InvPi = 0.31830988618379067154f;
+constexpr float OneMinusEpsilon = 0x1.fffffep-1f;
+constexpr float ShadowEpsilon = 1e-4f;
+constexpr float RayTMax = 1e30f;
+
+// mirrors vo::sincos_2pi
+__device__ __forceinline__ void sincos_2pi(float u, float &s, float &c) {
+    float q = floorf(u * 4.0f + 0.5f);
+    float r = u - q * 0.25f;
+    float x = r * 6.28318530717958647692f;
+    float z = x * x;
+    float sp = ((-1.9515295891e-4f * z + 8.3321608736e-3f) * z - 1.6666654611e-1f) * z * x + x;
+    float cp = ((2.443315711809948e-5f * z - 1.388731625493765e-3f) * z + 4.166664568298827e-2f) * z * z - 0.5f * z + 1.0f;
+    int iq = (int)q & 3;
+    if (iq == 0) { s = sp; c = cp; }
+    else if (iq == 1) { s = cp; c = -sp; }
+    else if (iq == 2) { s = -sp; c = -cp; }
+    else { s = -cp; c = sp; }
+}
+
+// mirrors vo::offset_ray_origin (Waechter & Binder)
+__device__ __forceinline__ float offset1(float pc, float nc) {
+    int32_t of_i = (int32_t)(256.0f * nc);
+    int32_t pi = __float_as_int(pc);
+    float p_i = __int_as_float(pi + (pc < 0.f ? -of_i : of_i));
+    return fabsf(pc) < (1.0f / 32.0f) ? pc + (1.0f / 65536.0f) * nc : p_i;
+}
+__device__ __forceinline__ f3 offset_ray_origin(f3 p, f3 n) { return {offset1(p.x, n.x), offset1(p.y, n.y), offset1(p.z, n.z)}; }
+
+// reference src/math/util.h:13-34
+__device__ __forceinline__ uint32_t tea4(uint32_t v0, uint32_t v1) {
+    uint32_t s0 = 0;
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        s0 += 0x9e3779b9u;
+        v0 += ((v1 << 4) + 0xa341316cu) ^ (v1 + s0) ^ ((v1 >> 5) + 0xc8013ea4u);
+        v1 += ((v0 << 4) + 0xad90777du) ^ (v0 + s0) ^ ((v0 >> 5) + 0x7e95761eu);
+    }
+    return v0;
+}
+__device__ __forceinline__ float lcg(uint32_t &state) {
+    state = 1664525u * state + 1013904223u;
+    return (float)(state & 0x00ffffffu) * (1.0f / 16777216.0f);
+}
+
+}  // namespace vbm

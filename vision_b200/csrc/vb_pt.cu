@@ -1,2 +1,276 @@
+// Path-tracing megakernel (sm_100a) + film kernels + their C ABI.
+// One launch = camera ray (reference "rt_geom", src/base/sensor/frame_buffer.cpp:156-183) + Li
+// (reference "path_tracing", src/base/integral/integrator.cpp:82-107,160-311) + film accumulation
+// (reference "RGBFilm-accumulation", frame_buffer.cpp:117-126) for a batch of frame indices.
+// Mirrors oracle/vo_pt_li.inl operation for operation; compiled with -fmad=false (see vb_math.cuh).
 #include "vb_internal.h"
-void vb_pt_destroy(vb_ctx *) {}
+#include "vb_trace.cuh"
+#include "vb_math.cuh"
+#include <vector>
+#include <cstring>
+
+using namespace vbm;
+
+namespace {
+
+struct DevMesh { const float *pos, *nrm, *uv; const uint32_t *tri; };
+struct DevInst {
+    uint32_t mesh_id, mat_id, light_id, inside, outside, pad[3];
+    float o2w[16];
+    float nmat[12];            // 9 used: sign(det) * cofactor(o2w 3x3), row-major
+};
+struct DevTex { const float4 *texels; uint32_t w, h; };
+
+struct PtScene {
+    VbAccelView accel;
+    const DevMesh *meshes;
+    const DevInst *instances;
+    const vb_material_rec *materials;
+    const vb_light_rec *lights;
+    uint32_t n_lights;
+    const vb_alias_entry *alias_table;
+    const float *alias_func;
+    const DevTex *textures;
+    vb_camera cam;
+    vb_pt_params params;
+    uint32_t width, height;
+};
+
+constexpr int PT_BLOCK = 128;
+
+struct Frame3 {
+    f3 x, y, z;
+    __device__ f3 to_local(f3 v) const { return {dot(v, x), dot(v, y), dot(v, z)}; }
+    __device__ f3 to_world(f3 v) const { return x * v.x + y * v.y + z * v.z; }
+    __device__ void update(f3 n) {
+        z = n;
+        x = normalize(cross(n, y)) * length(x);
+        y = normalize(cross(n, x)) * length(y);
+    }
+};
+
+struct Interaction {
+    f3 pos, wo, ng;
+    f2 uv;
+    Frame3 shading;
+    float prim_area;
+    uint32_t prim_id, mat_id, light_id;
+};
+
+__device__ __forceinline__ f3 ld3(const float *p, uint32_t i) { return {__ldg(p + 3 * i), __ldg(p + 3 * i + 1), __ldg(p + 3 * i + 2)}; }
+__device__ __forceinline__ f2 ld2(const float *p, uint32_t i) { return {__ldg(p + 2 * i), __ldg(p + 2 * i + 1)}; }
+__device__ __forceinline__ f3 lerp3(float u, float v, f3 a, f3 b, f3 c) {
+    float w = 1.0f - u - v;
+    return a * w + b * u + c * v;
+}
+__device__ __forceinline__ bool is_zero(f3 v) { return v.x == 0.f && v.y == 0.f && v.z == 0.f; }
+
+// reference src/base/mgr/geometry.cpp:79-166
+__device__ Interaction compute_surface_interaction(const PtScene &S, uint32_t inst_id, uint32_t prim_id, float bu, float bv,
+                                                   bool is_complete) {
+    Interaction it;
+    it.prim_id = prim_id;
+    const DevInst &I = S.instances[inst_id];
+    const DevMesh M = S.meshes[I.mesh_id];
+    uint32_t i0 = __ldg(M.tri + 3 * prim_id), i1 = __ldg(M.tri + 3 * prim_id + 1), i2 = __ldg(M.tri + 3 * prim_id + 2);
+    it.light_id = I.light_id; it.mat_id = I.mat_id;
+    f3 p0 = transform_point(I.o2w, ld3(M.pos, i0)), p1 = transform_point(I.o2w, ld3(M.pos, i1)), p2 = transform_point(I.o2w, ld3(M.pos, i2));
+    it.pos = lerp3(bu, bv, p0, p1, p2);
+    f3 dp02 = p0 - p2, dp12 = p1 - p2;
+    f3 ng_un = cross(dp02, dp12);
+    it.prim_area = 0.5f * length(ng_un);
+    f2 t0 = ld2(M.uv, i0), t1 = ld2(M.uv, i1), t2 = ld2(M.uv, i2);
+    f2 duv02{t0.x - t2.x, t0.y - t2.y}, duv12{t1.x - t2.x, t1.y - t2.y};
+    float det = duv02.x * duv12.y - duv02.y * duv12.x;
+    bool degenerate_uv = fabsf(det) < 1e-8f;
+    Frame3 frame;
+    if (is_complete) {
+        f3 dp_du, dp_dv;
+        if (!degenerate_uv) {
+            float inv_det = 1.0f / det;
+            dp_du = normalize((dp02 * duv12.y - dp12 * duv02.y) * inv_det);
+            dp_dv = normalize((dp02 * (-duv12.x) + dp12 * duv02.x) * inv_det);
+        } else {
+            dp_du = normalize(p1 - p0);
+            dp_dv = normalize(p2 - p0);
+        }
+        frame.x = dp_du; frame.y = dp_dv; frame.z = normalize(ng_un);
+    } else {
+        frame.x = dp02; frame.y = dp12; frame.z = normalize(ng_un);
+    }
+    it.shading = frame;
+    if (is_complete) {
+        f3 normal = lerp3(bu, bv, ld3(M.nrm, i0), ld3(M.nrm, i1), ld3(M.nrm, i2));
+        if (!is_zero(normal)) {
+            f3 ns = normalize(apply_normal(I.nmat, normal));
+            it.shading.update(ns);
+        }
+    }
+    float w = 1.0f - bu - bv;
+    it.uv = {t0.x * w + t1.x * bu + t2.x * bv, t0.y * w + t1.y * bu + t2.y * bv};
+    it.ng = frame.z;
+    return it;
+}
+
+__device__ __forceinline__ f3 flip_to(f3 n, f3 dir) { return dot(n, dir) > 0.f ? n : -n; }
+
+__device__ __forceinline__ VbRay make_ray(f3 o, f3 d, float tmax) { return VbRay{o.x, o.y, o.z, 0.f, d.x, d.y, d.z, tmax}; }
+__device__ __forceinline__ VbRay spawn_ray(const Interaction &it, f3 dir) {
+    return make_ray(offset_ray_origin(it.pos, flip_to(it.ng, dir)), dir, RayTMax);
+}
+__device__ __forceinline__ VbRay spawn_ray_to(const Interaction &it, f3 target) {
+    f3 dir = target - it.pos;
+    return make_ray(offset_ray_origin(it.pos, flip_to(it.ng, dir)), dir, 1.0f - ShadowEpsilon);
+}
+
+// bilinear, wrap, normalised uv - mirrors vo sample_texture
+__device__ float4 sample_texture(const DevTex &t, f2 uv) {
+    float x = uv.x * (float)t.w - 0.5f, y = uv.y * (float)t.h - 0.5f;
+    float fx0 = floorf(x), fy0 = floorf(y);
+    float fx = x - fx0, fy = y - fy0;
+    int W = (int)t.w, H = (int)t.h;
+    int x0 = (int)fx0 % W; if (x0 < 0) x0 += W;
+    int x1 = ((int)fx0 + 1) % W; if (x1 < 0) x1 += W;
+    int y0 = (int)fy0 % H; if (y0 < 0) y0 += H;
+    int y1 = ((int)fy0 + 1) % H; if (y1 < 0) y1 += H;
+    float4 a = __ldg(t.texels + (size_t)y0 * W + x0), b = __ldg(t.texels + (size_t)y0 * W + x1);
+    float4 c = __ldg(t.texels + (size_t)y1 * W + x0), d = __ldg(t.texels + (size_t)y1 * W + x1);
+    float4 ab{a.x + fx * (b.x - a.x), a.y + fx * (b.y - a.y), a.z + fx * (b.z - a.z), a.w + fx * (b.w - a.w)};
+    float4 cd{c.x + fx * (d.x - c.x), c.y + fx * (d.y - c.y), c.z + fx * (d.z - c.z), c.w + fx * (d.w - c.w)};
+    return float4{ab.x + fy * (cd.x - ab.x), ab.y + fy * (cd.y - ab.y), ab.z + fy * (cd.z - ab.z), ab.w + fy * (cd.w - ab.w)};
+}
+__device__ f3 eval_slot3(const PtScene &S, const vb_slot &s, f2 uv) {
+    f3 v{s.value[0], s.value[1], s.value[2]};
+    if (s.tex_id != VB_INVALID_ID) {
+        float4 t = sample_texture(S.textures[s.tex_id], uv);
+        v = {v.x * t.x, v.y * t.y, v.z * t.z};
+    }
+    return v;
+}
+
+struct LightEvalCtx { f3 pos, ng; f2 uv; float pdf_pos; };
+struct LightEval { f3 L; float pdf; };
+struct LightSample { LightEval eval; f3 p_light; };
+
+__device__ __forceinline__ float alias_pmf(const PtScene &S, const vb_light_rec &l, uint32_t i) {
+    return l.alias_integral > 0.f ? __ldg(S.alias_func + l.alias_offset + i) / (l.alias_integral * (float)l.alias_size) : 0.f;
+}
+__device__ uint32_t alias_sample(const PtScene &S, const vb_light_rec &l, float u, float &pmf, float &u_remapped) {
+    uint32_t size = l.alias_size;
+    u = u * (float)size;
+    uint32_t idx = min((uint32_t)u, size - 1);
+    u = fmin_(u - (float)idx, OneMinusEpsilon);
+    vb_alias_entry e = S.alias_table[l.alias_offset + idx];
+    bool keep = u < e.prob;
+    uint32_t out = keep ? idx : e.alias;
+    u_remapped = keep ? fmin_(u / e.prob, OneMinusEpsilon) : fmin_((1.0f - u) / (1.0f - e.prob), OneMinusEpsilon);
+    pmf = alias_pmf(S, l, out);
+    return out;
+}
+
+__device__ LightEval area_evaluate_wi(const PtScene &S, const vb_light_rec &l, f3 ref_pos, const LightEvalCtx &pl) {
+    LightEval ev;
+    f3 w = ref_pos - pl.pos;
+    f3 color = eval_slot3(S, l.color, pl.uv);
+    float s = (dot(w, pl.ng) > 0.f || l.two_sided) ? 1.f : 0.f;
+    ev.L = color * l.scale * s;
+    float cos_theta = fabsf(dot(pl.ng, normalize(w)));
+    float pdf = pl.pdf_pos * length_squared(w) / cos_theta;
+    ev.pdf = (isinf(pdf) || isnan(pdf)) ? 0.f : pdf;
+    return ev;
+}
+
+__device__ LightSample area_sample_wi(const PtScene &S, const vb_light_rec &l, const Interaction &ref, f2 u) {
+    float pmf, ux;
+    uint32_t prim = alias_sample(S, l, u.x, pmf, ux);
+    float su0 = __fsqrt_rn(ux);
+    float b0 = 1.0f - su0, b1 = u.y * su0;
+    Interaction li = compute_surface_interaction(S, l.inst_id, prim, b0, b1, false);
+    LightEvalCtx pl{li.pos, li.ng, li.uv, 1.0f / li.prim_area};
+    pl.pdf_pos *= pmf;
+    LightSample ls;
+    ls.eval = area_evaluate_wi(S, l, ref.pos, pl);
+    f3 dir = ref.pos - pl.pos;
+    float factor = dot(pl.ng, dir) > 0.f ? 1.f : -1.f;
+    ls.p_light = offset_ray_origin(pl.pos, pl.ng * factor * S.params.ray_offset_factor);
+    return ls;
+}
+
+struct ScatterEval { f3 f; float pdf; uint32_t flags; };
+constexpr uint32_t FlagReflection = 1u << 1, FlagTransmission = 1u << 2, FlagDiffuse = 1u << 3;
+
+struct Evaluator {
+    uint32_t type;
+    f3 kr, ng;
+    Frame3 frame;
+    __device__ ScatterEval evaluate(f3 world_wo, f3 world_wi) const {
+        f3 wo = frame.to_local(world_wo), wi = frame.to_local(world_wi);
+        ScatterEval se;
+        bool s = wo.z * wi.z > 0.f;
+        se.f = s ? kr * InvPi : f3{0, 0, 0};
+        se.pdf = s ? fabsf(wi.z) * InvPi : 0.f;
+        se.flags = FlagDiffuse | FlagReflection;
+        se.f = se.f * fabsf(wi.z);
+        bool same = dot(world_wo, ng) * dot(world_wi, ng) > 0.f;
+        bool is_trans = (se.flags & FlagTransmission) != 0;
+        if (same == is_trans) se.pdf = 0.f;
+        return se;
+    }
+    __device__ f3 sample_wi(f3 world_wo, f2 u) const {
+        f3 wo = frame.to_local(world_wo);
+        float r = __fsqrt_rn(u.x), s, c;
+        sincos_2pi(u.y, s, c);
+        float dx = r * c, dy = r * s;
+        float z = __fsqrt_rn(fmax_(0.0f, 1.0f - dx * dx - dy * dy));
+        if (wo.z < 0.f) z = -z;
+        return frame.to_world(f3{dx, dy, z});
+    }
+};
+
+__device__ __forceinline__ float mis_weight(float f, float g) { return (1.0f * f) / (1.0f * f + 1.0f * g); }
+
+struct Sampler {
+    uint32_t state;
+    __device__ void start(uint32_t px, uint32_t py, uint32_t si, uint32_t dim) { state = tea4(tea4(px, py), tea4(si, dim)); }
+    __device__ float next_1d() { return lcg(state); }
+    __device__ f2 next_2d() { float x = next_1d(); float y = next_1d(); return {x, y}; }
+};
+
+__device__ __forceinline__ float sample_linear10(float u) {
+    float a = 1.f, b = 0.f;
+    float x = u * (a + b) / (a + __fsqrt_rn((a * a) + u * ((b * b) - (a * a))));
+    return fmin_(x, OneMinusEpsilon);
+}
+__device__ __forceinline__ float sample_tent(float u, float r) {
+    return u < 0.5f ? -r * sample_linear10((0.5f - u) * 2.f) : r * sample_linear10((u - 0.5f) * 2.f);
+}
+
+// camera ray: reference sampler.h:65-73, sensor.cpp:44-56, thin_lens.cpp:34-42
+__device__ VbRay generate_camera_ray(const PtScene &S, Sampler &sampler, uint32_t px, uint32_t py) {
+    const vb_camera &cam = S.cam;
+    f2 uf = sampler.next_2d();
+    f2 fp;
+    if (cam.filter_type == VB_FILTER_TRIANGLE) fp = {sample_tent(uf.x, cam.filter_radius[0]), sample_tent(uf.y, cam.filter_radius[1])};
+    else {
+        float rx = cam.filter_radius[0], ry = cam.filter_radius[1];
+        fp = {-rx + uf.x * (rx - (-rx)), -ry + uf.y * (ry - (-ry))};
+    }
+    f2 p_film{(float)px + 0.5f + fp.x, (float)py + 0.5f + fp.y};
+    f2 u_lens = sampler.next_2d();
+    (void)sampler.next_1d();
+    float sx = cam.screen_lo[0] + p_film.x / (float)S.width * (cam.screen_hi[0] - cam.screen_lo[0]);
+    float sy = cam.screen_hi[1] - p_film.y / (float)S.height * (cam.screen_hi[1] - cam.screen_lo[1]);
+    f3 dir = normalize(f3{sx * cam.tan_fov_y_over_2, sy * cam.tan_fov_y_over_2, 1.0f});
+    float rr = __fsqrt_rn(u_lens.x), s, c;
+    sincos_2pi(u_lens.y, s, c);
+    f2 pl{rr * c * cam.lens_radius, rr * s * cam.lens_radius};
+    float ft = cam.focal_distance / dir.z;
+    f3 p_focus = dir * ft;
+    f3 org{pl.x, pl.y, 0.f};
+    dir = normalize(p_focus - org);
+    return make_ray(transform_point(cam.c2w, org), transform_vector(cam.c2w, dir), RayTMax);
+}
+
+}  // namespace
+
+#include "vb_pt_kernel.cuh"

@@ -1,0 +1,448 @@
+// Megakernel, film kernels and the PT part of the C ABI. Included by vb_pt.cu only.
+#pragma once
+
+namespace {
+
+struct PtCounters { unsigned long long closest, any, vertices, pad; };
+
+// One thread = one pixel; it runs all frames of the batch for that pixel back to back (a finished
+// path is immediately replaced by the next frame's path, so lanes stay busy), keeps the running
+// film value in registers and writes the film once per launch.
+template <bool DUMP_PRIMARY>
+__global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t first_frame, uint32_t n_frames, uint32_t stride, int mode,
+                                                         uint32_t frames_done, float4 *rt, float4 *accum, PtCounters *counters,
+                                                         uint32_t *h_inst, uint32_t *h_prim, float *h_u, float *h_v, float *h_t) {
+    __shared__ uint2 s_stack_all[VB_SM_STACK * PT_BLOCK];
+    uint2 *s_stack = s_stack_all + threadIdx.x;
+    uint32_t pix = blockIdx.x * PT_BLOCK + threadIdx.x;
+    uint32_t n_pix = S.width * S.height;
+    uint32_t c_closest = 0, c_any = 0, c_vert = 0, dummy0 = 0, dummy1 = 0;
+    if (pix < n_pix) {
+        uint32_t px = pix % S.width, py = pix / S.width;
+        float4 acc = accum[pix];
+        float4 last = make_float4(0.f, 0.f, 0.f, 1.f);
+        for (uint32_t fi = 0; fi < n_frames; ++fi) {
+            uint32_t frame = first_frame + fi * stride;
+            Sampler sampler;
+            sampler.start(px, py, frame, 0u);
+            VbRay ray = generate_camera_ray(S, sampler, px, py);
+            VbHit hit;
+            // the reference traces the primary ray in rt_geom and again as bounce 0 of Li with the
+            // same ray; the second result is identical, so it is reused (counted once)
+            vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1);
+            c_closest++;
+            if (DUMP_PRIMARY) {
+                h_inst[pix] = hit.inst; h_prim[pix] = hit.prim; h_u[pix] = hit.u; h_v[pix] = hit.v; h_t[pix] = hit.t;
+                continue;
+            }
+            sampler.start(px, py, frame, 1u);
+            float scatter_pdf = 1e16f;
+            f3 throughput{1, 1, 1}, ret{0, 0, 0};
+            float eta_scale = 1.f;
+            const uint32_t max_depth = S.params.max_depth;
+            bool have_hit = true;
+            for (uint32_t bounces = 0; bounces < max_depth; ++bounces) {
+                if (!have_hit) { vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1); c_closest++; }
+                have_hit = false;
+                if (hit.inst == VB_INVALID_ID) break;
+                Interaction it = compute_surface_interaction(S, hit.inst, hit.prim, hit.u, hit.v, true);
+                f3 rd{ray.dx, ray.dy, ray.dz}, ro{ray.ox, ray.oy, ray.oz};
+                it.wo = normalize(-rd);
+                c_vert++;
+                if (it.mat_id == VB_INVALID_ID) {
+                    ray = spawn_ray(it, rd);
+                    bounces -= 1;
+                    continue;
+                }
+                if (it.light_id != VB_INVALID_ID) {
+                    const vb_light_rec &l = S.lights[it.light_id];
+                    LightEval ev{f3{0, 0, 0}, 0.f};
+                    if (l.type == VB_LIGHT_AREA) {
+                        LightEvalCtx pl{it.pos, it.ng, it.uv, 1.0f / it.prim_area};
+                        pl.pdf_pos *= alias_pmf(S, l, it.prim_id);
+                        ev = area_evaluate_wi(S, l, ro, pl);
+                        ev.pdf *= 1.0f / (float)S.n_lights;
+                    }
+                    float weight = mis_weight(scatter_pdf, ev.pdf);
+                    if (S.params.mis_mode == 2) weight = 1.f;
+                    else if (S.params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
+                    f3 d = ev.L * throughput * weight;
+                    ret = ret + d;
+                }
+                // light sampling
+                float u_light = sampler.next_1d();
+                f2 u_surface = sampler.next_2d();
+                LightSample ls{{f3{0, 0, 0}, 0.f}, f3{0, 0, 0}};
+                if (S.n_lights) {
+                    uint32_t n = S.n_lights;
+                    uint32_t index = (uint32_t)fmin_(u_light * (float)n, (float)n - 1.0f);
+                    const vb_light_rec &l = S.lights[index];
+                    if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(S, l, it, u_surface);
+                    ls.eval.pdf *= 1.0f / (float)n;
+                }
+                VbRay shadow = spawn_ray_to(it, ls.p_light);
+                VbHit sh;
+                bool occluded = vb_traverse<true, false>(S.accel, shadow, sh, s_stack, PT_BLOCK, dummy0, dummy1);
+                c_any++;
+                // material
+                const vb_material_rec &m = S.materials[it.mat_id];
+                Evaluator evr;
+                evr.type = m.type; evr.ng = it.ng; evr.frame = it.shading;
+                evr.kr = (m.type == VB_MAT_DIFFUSE) ? eval_slot3(S, m.color, it.uv) : f3{0, 0, 0};
+                f3 wi = normalize(ls.p_light - it.pos);
+                ScatterEval se = evr.evaluate(it.wo, wi);
+                f2 ub = sampler.next_2d();
+                f3 bwi = evr.sample_wi(it.wo, ub);
+                ScatterEval be = evr.evaluate(it.wo, bwi);
+                float beta = 1.f;
+                bool is_delta = ls.eval.pdf < 0.f;
+                float weight = is_delta ? 1.f : mis_weight(ls.eval.pdf, se.pdf);
+                if (S.params.mis_mode == 1) weight = 1.f;
+                float lpdf = is_delta ? -ls.eval.pdf : ls.eval.pdf;
+                f3 Ld{0, 0, 0};
+                if (!occluded && se.pdf > 0.f && lpdf > 0.f) Ld = ls.eval.L * se.f * weight / lpdf;
+                if (S.params.mis_mode == 2) Ld = Ld * 0.f;
+                ret = ret + throughput * Ld;
+                eta_scale *= beta * beta;
+                float lum = max_comp(throughput);
+                if (!(be.pdf > 0.f) || lum == 0.f) break;
+                throughput = throughput * (be.f / be.pdf);
+                if (eta_scale * lum < S.params.rr_threshold && bounces >= S.params.min_depth) {
+                    float q = fmin_(0.95f, lum);
+                    float rr = sampler.next_1d();
+                    if (q < rr) break;
+                    throughput = throughput / q;
+                }
+                scatter_pdf = be.pdf;
+                ray = spawn_ray(it, bwi);
+            }
+            last = make_float4(ret.x, ret.y, ret.z, 1.f);
+            if (mode == VB_ACCUM_LERP) {
+                float t = 1.0f / (float)(frames_done + fi + 1);
+                acc.x = acc.x + t * (last.x - acc.x); acc.y = acc.y + t * (last.y - acc.y);
+                acc.z = acc.z + t * (last.z - acc.z); acc.w = acc.w + t * (last.w - acc.w);
+            } else {
+                acc.x += last.x; acc.y += last.y; acc.z += last.z; acc.w += last.w;
+            }
+        }
+        if (!DUMP_PRIMARY) { accum[pix] = acc; rt[pix] = last; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        c_closest += __shfl_xor_sync(~0u, c_closest, o); c_any += __shfl_xor_sync(~0u, c_any, o); c_vert += __shfl_xor_sync(~0u, c_vert, o);
+    }
+    if ((threadIdx.x & 31) == 0 && counters) {
+        atomicAdd(&counters->closest, (unsigned long long)c_closest); atomicAdd(&counters->any, (unsigned long long)c_any);
+        atomicAdd(&counters->vertices, (unsigned long long)c_vert);
+    }
+}
+
+// reference frame_buffer.cpp:72-74,135-144 + tonemapper/impl.cpp:21-46
+__global__ void __launch_bounds__(256) k_film_resolve(const float4 *accum, float4 *out, uint32_t n, int mode, float exposure, int tonemap) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 v = accum[i];
+    if (mode == VB_ACCUM_SUM) {
+        float inv = v.w > 0.f ? 1.0f / v.w : 0.f;
+        v.x *= inv; v.y *= inv; v.z *= inv;
+    }
+    float c[3] = {v.x, v.y, v.z};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float x = 1.0f - expf(-c[k] * exposure);
+        if (tonemap == VB_TONEMAP_ACES) {
+            float y = (x * (2.51f * x + 0.03f)) / (x * (2.43f * x + 0.59f) + 0.14f);
+            x = fmin_(1.0f, fmax_(0.0f, y));
+        } else if (tonemap == VB_TONEMAP_REINHARD) {
+            x = x / (x + 1.0f);
+        }
+        c[k] = x;
+    }
+    out[i] = make_float4(c[0], c[1], c[2], 1.0f);
+}
+
+}  // namespace
+
+struct vb_pt_state {
+    std::vector<DevMesh> h_meshes;
+    DevMesh *d_meshes = nullptr;
+    DevInst *d_inst = nullptr;
+    vb_material_rec *d_mat = nullptr; uint32_t n_mat = 0;
+    vb_light_rec *d_lights = nullptr; uint32_t n_lights = 0;
+    vb_alias_entry *d_alias = nullptr; float *d_func = nullptr;
+    DevTex *d_tex = nullptr; std::vector<float4 *> tex_mem;
+    vb_camera cam{}; bool have_cam = false;
+    vb_pt_params params{}; bool have_params = false;
+    uint32_t w = 0, h = 0;
+    float4 *rt = nullptr, *accum = nullptr, *output = nullptr;
+    uint32_t frames_done = 0;
+    PtCounters *d_counters = nullptr;
+    PtCounters last{};
+    uint64_t geom_version = ~0ull;
+};
+
+static vb_pt_state *pt_state(vb_ctx *ctx) {
+    if (!ctx->pt) ctx->pt = new vb_pt_state();
+    return ctx->pt;
+}
+
+void vb_pt_destroy(vb_ctx *ctx) {
+    vb_pt_state *p = ctx->pt;
+    if (!p) return;
+    cudaFree(p->d_meshes); cudaFree(p->d_inst); cudaFree(p->d_mat); cudaFree(p->d_lights); cudaFree(p->d_alias); cudaFree(p->d_func);
+    cudaFree(p->d_tex);
+    for (auto t : p->tex_mem) cudaFree(t);
+    cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output); cudaFree(p->d_counters);
+    delete p;
+    ctx->pt = nullptr;
+}
+
+// device tables for meshes/instances (the analogue of Geometry::upload, geometry.cpp:64-71)
+static int pt_sync_geometry(vb_ctx *ctx) {
+    vb_pt_state *p = pt_state(ctx);
+    cudaFree(p->d_meshes); cudaFree(p->d_inst); p->d_meshes = nullptr; p->d_inst = nullptr;
+    std::vector<DevMesh> hm(ctx->meshes.size());
+    for (size_t i = 0; i < hm.size(); ++i) hm[i] = DevMesh{ctx->meshes[i].pos, ctx->meshes[i].nrm, ctx->meshes[i].uv, ctx->meshes[i].tri};
+    std::vector<DevInst> hi(ctx->instances.size());
+    for (size_t i = 0; i < hi.size(); ++i) {
+        const vb_instance &s = ctx->instances[i];
+        if (ctx->meshes[s.mesh_id].soup) return ctx->fail(VB_ERR_UNSUPPORTED, "path tracing needs indexed meshes (vb_mesh_upload)");
+        DevInst &d = hi[i];
+        memset(&d, 0, sizeof(d));
+        d.mesh_id = s.mesh_id; d.mat_id = s.material_id; d.light_id = s.light_id; d.inside = s.inside_medium; d.outside = s.outside_medium;
+        memcpy(d.o2w, s.o2w, 64);
+        double m[3][3], cf[3][3];
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) m[r][c] = s.o2w[4 * c + r];
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) {
+                int r1 = (r + 1) % 3, r2 = (r + 2) % 3, c1 = (c + 1) % 3, c2 = (c + 2) % 3;
+                cf[r][c] = m[r1][c1] * m[r2][c2] - m[r1][c2] * m[r2][c1];
+            }
+        double det = m[0][0] * cf[0][0] + m[0][1] * cf[0][1] + m[0][2] * cf[0][2];
+        double sg = det < 0 ? -1.0 : 1.0;
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) d.nmat[3 * r + c] = (float)(sg * cf[r][c]);
+    }
+    if (!hm.empty()) {
+        VB_CUDA(cudaMalloc(&p->d_meshes, sizeof(DevMesh) * hm.size()));
+        VB_CUDA(cudaMemcpy(p->d_meshes, hm.data(), sizeof(DevMesh) * hm.size(), cudaMemcpyHostToDevice));
+    }
+    if (!hi.empty()) {
+        VB_CUDA(cudaMalloc(&p->d_inst, sizeof(DevInst) * hi.size()));
+        VB_CUDA(cudaMemcpy(p->d_inst, hi.data(), sizeof(DevInst) * hi.size(), cudaMemcpyHostToDevice));
+    }
+    return VB_OK;
+}
+
+extern "C" {
+
+int vb_textures_set(vb_ctx *ctx, const vb_texture *tex, uint32_t n) {
+    if (!ctx) return VB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    vb_pt_state *p = pt_state(ctx);
+    for (auto t : p->tex_mem) cudaFree(t);
+    p->tex_mem.clear();
+    cudaFree(p->d_tex); p->d_tex = nullptr;
+    std::vector<DevTex> ht(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        if (!tex[i].texels || !tex[i].width || !tex[i].height) return ctx->fail(VB_ERR_INVALID, "vb_textures_set: empty texture");
+        float4 *d = nullptr;
+        size_t bytes = sizeof(float4) * (size_t)tex[i].width * tex[i].height;
+        VB_CUDA(cudaMalloc(&d, bytes));
+        VB_CUDA(cudaMemcpy(d, tex[i].texels, bytes, cudaMemcpyHostToDevice));
+        p->tex_mem.push_back(d);
+        ht[i] = DevTex{d, tex[i].width, tex[i].height};
+    }
+    if (n) {
+        VB_CUDA(cudaMalloc(&p->d_tex, sizeof(DevTex) * n));
+        VB_CUDA(cudaMemcpy(p->d_tex, ht.data(), sizeof(DevTex) * n, cudaMemcpyHostToDevice));
+    }
+    return VB_OK;
+}
+
+int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (n && !mat) return ctx->fail(VB_ERR_INVALID, "vb_materials_set: null argument");
+    cudaSetDevice(ctx->device);
+    vb_pt_state *p = pt_state(ctx);
+    for (uint32_t i = 0; i < n; ++i)
+        if (mat[i].type != VB_MAT_DIFFUSE && mat[i].type != VB_MAT_BLACK_BODY)
+            return ctx->fail(VB_ERR_UNSUPPORTED, "vb_materials_set: material type " + std::to_string(mat[i].type) + " not implemented yet");
+    cudaFree(p->d_mat); p->d_mat = nullptr; p->n_mat = n;
+    if (n) {
+        VB_CUDA(cudaMalloc(&p->d_mat, sizeof(vb_material_rec) * n));
+        VB_CUDA(cudaMemcpy(p->d_mat, mat, sizeof(vb_material_rec) * n, cudaMemcpyHostToDevice));
+    }
+    return VB_OK;
+}
+
+int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n, const vb_alias_entry *alias_table, const float *alias_func,
+                  uint32_t n_alias) {
+    if (!ctx) return VB_ERR_INVALID;
+    if ((n && !lights) || (n_alias && (!alias_table || !alias_func))) return ctx->fail(VB_ERR_INVALID, "vb_lights_set: null argument");
+    cudaSetDevice(ctx->device);
+    vb_pt_state *p = pt_state(ctx);
+    for (uint32_t i = 0; i < n; ++i) {
+        if (lights[i].type != VB_LIGHT_AREA) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_lights_set: light type not implemented yet");
+        if (lights[i].alias_offset + lights[i].alias_size > n_alias) return ctx->fail(VB_ERR_INVALID, "vb_lights_set: alias range out of bounds");
+    }
+    cudaFree(p->d_lights); cudaFree(p->d_alias); cudaFree(p->d_func);
+    p->d_lights = nullptr; p->d_alias = nullptr; p->d_func = nullptr; p->n_lights = n;
+    if (n) {
+        VB_CUDA(cudaMalloc(&p->d_lights, sizeof(vb_light_rec) * n));
+        VB_CUDA(cudaMemcpy(p->d_lights, lights, sizeof(vb_light_rec) * n, cudaMemcpyHostToDevice));
+    }
+    if (n_alias) {
+        VB_CUDA(cudaMalloc(&p->d_alias, sizeof(vb_alias_entry) * n_alias));
+        VB_CUDA(cudaMemcpy(p->d_alias, alias_table, sizeof(vb_alias_entry) * n_alias, cudaMemcpyHostToDevice));
+        VB_CUDA(cudaMalloc(&p->d_func, sizeof(float) * n_alias));
+        VB_CUDA(cudaMemcpy(p->d_func, alias_func, sizeof(float) * n_alias, cudaMemcpyHostToDevice));
+    }
+    return VB_OK;
+}
+
+int vb_camera_set(vb_ctx *ctx, const vb_camera *cam) {
+    if (!ctx || !cam) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    p->cam = *cam; p->have_cam = true;
+    return VB_OK;
+}
+int vb_integrator_set(vb_ctx *ctx, const vb_pt_params *prm) {
+    if (!ctx || !prm) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (prm->spectrum != 0 || prm->sampler != 0) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_integrator_set: only srgb spectrum + independent sampler");
+    if (prm->process_mediums) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_integrator_set: mediums not implemented yet");
+    p->params = *prm; p->have_params = true;
+    return VB_OK;
+}
+
+int vb_film_create(vb_ctx *ctx, uint32_t width, uint32_t height) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (!width || !height) return ctx->fail(VB_ERR_INVALID, "vb_film_create: empty film");
+    cudaSetDevice(ctx->device);
+    vb_pt_state *p = pt_state(ctx);
+    cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output);
+    p->rt = p->accum = p->output = nullptr;
+    size_t bytes = sizeof(float4) * (size_t)width * height;
+    VB_CUDA(cudaMalloc(&p->rt, bytes)); VB_CUDA(cudaMalloc(&p->accum, bytes)); VB_CUDA(cudaMalloc(&p->output, bytes));
+    p->w = width; p->h = height;
+    if (!p->d_counters) VB_CUDA(cudaMalloc(&p->d_counters, sizeof(PtCounters)));
+    return vb_film_clear(ctx);
+}
+int vb_film_clear(vb_ctx *ctx) {
+    if (!ctx) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_film_clear: no film");
+    size_t bytes = sizeof(float4) * (size_t)p->w * p->h;
+    VB_CUDA(cudaMemsetAsync(p->rt, 0, bytes, ctx->stream));
+    VB_CUDA(cudaMemsetAsync(p->accum, 0, bytes, ctx->stream));
+    VB_CUDA(cudaMemsetAsync(p->output, 0, bytes, ctx->stream));
+    p->frames_done = 0;
+    return VB_OK;
+}
+
+static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_frames, uint32_t stride, int mode, bool dump,
+                     uint32_t *hi, uint32_t *hp, float *hu, float *hv, float *ht) {
+    vb_pt_state *p = pt_state(ctx);
+    if (!ctx->accel.built) return ctx->fail(VB_ERR_STATE, std::string(fn) + ": accel not built");
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, std::string(fn) + ": no film (vb_film_create)");
+    if (!p->have_cam || !p->have_params) return ctx->fail(VB_ERR_STATE, std::string(fn) + ": camera/integrator not set");
+    for (auto &in : ctx->instances) {
+        if (in.material_id != VB_INVALID_ID && in.material_id >= p->n_mat) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": instance material_id out of range");
+        if (in.light_id != VB_INVALID_ID && in.light_id >= p->n_lights) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": instance light_id out of range");
+    }
+    int rc = pt_sync_geometry(ctx);
+    if (rc) return rc;
+    PtScene S{};
+    S.accel = VbAccelView{ctx->accel.nodes, ctx->accel.tris};
+    S.meshes = p->d_meshes; S.instances = p->d_inst; S.materials = p->d_mat; S.lights = p->d_lights; S.n_lights = p->n_lights;
+    S.alias_table = p->d_alias; S.alias_func = p->d_func; S.textures = p->d_tex;
+    S.cam = p->cam; S.params = p->params; S.width = p->w; S.height = p->h;
+    if (S.params.ray_offset_factor == 0.f) S.params.ray_offset_factor = 1.f;
+    uint32_t n_pix = p->w * p->h;
+    unsigned grid = (n_pix + PT_BLOCK - 1) / PT_BLOCK;
+    VB_CUDA(cudaMemsetAsync(p->d_counters, 0, sizeof(PtCounters), ctx->stream));
+    ctx->prof_begin("path_trace", 1);
+    if (dump) k_path_trace<true><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, 1, 1, mode, 0, p->rt, p->accum, p->d_counters, hi, hp, hu, hv, ht);
+    else k_path_trace<false><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum, p->d_counters,
+                                                                nullptr, nullptr, nullptr, nullptr, nullptr);
+    ctx->prof_end();
+    VB_CHECK_LAUNCH();
+    VB_CUDA(cudaMemcpyAsync(&p->last, p->d_counters, sizeof(PtCounters), cudaMemcpyDeviceToHost, ctx->stream));
+    if (!dump) p->frames_done += n_frames;
+    return VB_OK;
+}
+
+int vb_render_frames(vb_ctx *ctx, uint32_t first_frame, uint32_t n_frames, uint32_t frame_stride, int accumulate_mode) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (n_frames == 0) return VB_OK;
+    if (accumulate_mode != VB_ACCUM_LERP && accumulate_mode != VB_ACCUM_SUM) return ctx->fail(VB_ERR_INVALID, "vb_render_frames: bad mode");
+    cudaSetDevice(ctx->device);
+    return pt_launch(ctx, "vb_render_frames", first_frame, n_frames, frame_stride ? frame_stride : 1, accumulate_mode, false,
+                     nullptr, nullptr, nullptr, nullptr, nullptr);
+}
+
+int vb_film_resolve(vb_ctx *ctx, int accumulate_mode, float exposure, int tonemap) {
+    if (!ctx) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_film_resolve: no film");
+    cudaSetDevice(ctx->device);
+    uint32_t n = p->w * p->h;
+    ctx->prof_begin("film", 1);
+    k_film_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(p->accum, p->output, n, accumulate_mode, exposure, tonemap);
+    ctx->prof_end();
+    VB_CHECK_LAUNCH();
+    return VB_OK;
+}
+
+int vb_film_download(vb_ctx *ctx, float *rgba, int which) {
+    if (!ctx || !rgba) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_film_download: no film");
+    cudaSetDevice(ctx->device);
+    const float4 *src = which == VB_FILM_RT ? p->rt : (which == VB_FILM_OUTPUT ? p->output : p->accum);
+    VB_CUDA(cudaMemcpyAsync(rgba, src, sizeof(float4) * (size_t)p->w * p->h, cudaMemcpyDeviceToHost, ctx->stream));
+    VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VB_OK;
+}
+
+int vb_film_device_ptr(vb_ctx *ctx, int which, void **ptr) {
+    if (!ctx || !ptr) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_film_device_ptr: no film");
+    *ptr = which == VB_FILM_RT ? (void *)p->rt : (which == VB_FILM_OUTPUT ? (void *)p->output : (void *)p->accum);
+    return VB_OK;
+}
+
+int vb_dump_primary_hits(vb_ctx *ctx, uint32_t frame_index, const vb_hits_soa *out) {
+    if (!ctx || !out) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_dump_primary_hits: no film");
+    cudaSetDevice(ctx->device);
+    size_t n = (size_t)p->w * p->h;
+    bool host = out->mem == VB_MEM_HOST;
+    uint32_t *hi = out->inst, *hp = out->prim; float *hu = out->u, *hv = out->v, *ht = out->t;
+    if (host) {
+        int rc = ctx->ensure_stage(5 * n * 4);
+        if (rc) return rc;
+        uint32_t *d = (uint32_t *)ctx->stage;
+        hi = d; hp = d + n; hu = (float *)(d + 2 * n); hv = (float *)(d + 3 * n); ht = (float *)(d + 4 * n);
+    }
+    int rc = pt_launch(ctx, "vb_dump_primary_hits", frame_index, 1, 1, VB_ACCUM_SUM, true, hi, hp, hu, hv, ht);
+    if (rc) return rc;
+    if (host) {
+        void *dst[5] = {out->inst, out->prim, out->u, out->v, out->t};
+        const void *src[5] = {hi, hp, hu, hv, ht};
+        for (int k = 0; k < 5; ++k) VB_CUDA(cudaMemcpyAsync(dst[k], src[k], n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return VB_OK;
+}
+
+int vb_render_stats(vb_ctx *ctx, uint64_t stats[4]) {
+    if (!ctx || !stats) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    stats[0] = p->last.closest; stats[1] = p->last.any; stats[2] = p->last.vertices; stats[3] = 0;
+    return VB_OK;
+}
+
+}  // extern "C"
