@@ -314,7 +314,7 @@ VB_TONEMAP_LINEAR, VB_TONEMAP_ACES, VB_TONEMAP_REINHARD = 0, 1, 2
 
 def make_slot(value, tex_id=VB_INVALID_ID) -> vb_slot:
     s = vb_slot()
-    v = list(value) + [0.0] * (4 - len(value))
+    v = list(value) + [1.0] * (4 - len(value))
     s.value[:] = [float(x) for x in v[:4]]
     s.tex_id = tex_id
     return s

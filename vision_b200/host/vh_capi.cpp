@@ -1,0 +1,91 @@
+// extern "C" surface of the host layer (libvision_host.so) for the Python harness and the CLI.
+#include "vh_scene.h"
+#include <cstring>
+
+using namespace vh;
+
+static thread_local std::string g_err;
+struct vh_pipeline { std::shared_ptr<Pipeline> p; };
+
+#define VH_TRY(body) try { body; return 0; } catch (const std::exception &e) { g_err = e.what(); return 1; }
+
+extern "C" {
+
+VB_API const char *vh_last_error() { return g_err.c_str(); }
+
+VB_API vh_pipeline *vh_import_scene(const char *path) {
+    try { auto h = new vh_pipeline{import_scene(path)}; return h; }
+    catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+VB_API void vh_destroy(vh_pipeline *h) { delete h; }
+
+/* optional overrides before prepare (the CLI/bench knobs): key = "resolution" (a,b), "max_depth", "min_depth", "spp" */
+VB_API int vh_override(vh_pipeline *h, const char *key, double a, double b) {
+    VH_TRY({
+        Scene &s = h->p->scene; std::string k(key);
+        if (k == "resolution") { s.frame_buffer->width = (uint32_t)a; s.frame_buffer->height = (uint32_t)b; }
+        else if (k == "max_depth") s.integrator->max_depth = (uint32_t)a;
+        else if (k == "min_depth") s.integrator->min_depth = (uint32_t)a;
+        else if (k == "spp") s.desc.output_desc.spp = (uint32_t)a;
+        else throw std::runtime_error("unknown override " + k);
+    })
+}
+/* scene preparation only (records, no GPU) */
+VB_API int vh_prepare_records(vh_pipeline *h) { VH_TRY(h->p->scene.prepare(h->p->records)) }
+/* full prepare: records + upload through the C ABI + BVH build */
+VB_API int vh_prepare(vh_pipeline *h, int device) { VH_TRY(h->p->prepare(device)) }
+VB_API int vh_render(vh_pipeline *h, uint32_t n_frames) { VH_TRY(h->p->render(n_frames)) }
+VB_API int vh_final_picture(vh_pipeline *h, float *rgba) {
+    VH_TRY({ std::vector<float> v; h->p->final_picture(v); std::memcpy(rgba, v.data(), v.size() * 4); })
+}
+VB_API int vh_download_accum(vh_pipeline *h, float *rgba) { VH_TRY(h->p->check(vb_film_download(h->p->ctx, rgba, VB_FILM_ACCUM), "vb_film_download")) }
+VB_API void *vh_ctx(vh_pipeline *h) { return h->p->ctx; }
+
+/* info[0..9] = width, height, spp, n_meshes, n_instances, n_materials, n_lights, n_alias, n_textures, tonemap */
+VB_API void vh_info(vh_pipeline *h, uint32_t *info, float *exposure) {
+    const SceneRecords &r = h->p->records;
+    uint32_t v[10] = {r.width, r.height, r.spp, (uint32_t)r.meshes.size(), (uint32_t)r.instances.size(), (uint32_t)r.materials.size(),
+                      (uint32_t)r.lights.size(), (uint32_t)r.alias_table.size(), (uint32_t)r.textures.size(), (uint32_t)r.tonemap};
+    std::memcpy(info, v, sizeof(v));
+    if (exposure) *exposure = r.exposure;
+}
+/* which: 0 instances, 1 materials, 2 lights, 3 alias_table, 4 alias_func, 5 camera, 6 params; returns bytes copied */
+VB_API uint64_t vh_records_blob(vh_pipeline *h, int which, void *dst, uint64_t cap) {
+    const SceneRecords &r = h->p->records;
+    const void *src = nullptr; uint64_t n = 0;
+    switch (which) {
+        case 0: src = r.instances.data(); n = r.instances.size() * sizeof(vb_instance); break;
+        case 1: src = r.materials.data(); n = r.materials.size() * sizeof(vb_material_rec); break;
+        case 2: src = r.lights.data(); n = r.lights.size() * sizeof(vb_light_rec); break;
+        case 3: src = r.alias_table.data(); n = r.alias_table.size() * sizeof(vb_alias_entry); break;
+        case 4: src = r.alias_func.data(); n = r.alias_func.size() * sizeof(float); break;
+        case 5: src = &r.camera; n = sizeof(vb_camera); break;
+        case 6: src = &r.params; n = sizeof(vb_pt_params); break;
+        default: return 0;
+    }
+    if (dst && cap >= n && n) std::memcpy(dst, src, n);
+    return n;
+}
+VB_API void vh_mesh_info(vh_pipeline *h, uint32_t i, uint32_t *nv, uint32_t *nt) { *nv = h->p->records.meshes[i]->nv(); *nt = h->p->records.meshes[i]->nt(); }
+VB_API void vh_mesh_copy(vh_pipeline *h, uint32_t i, float *pos, float *nrm, float *uv, uint32_t *tri) {
+    const MeshData &m = *h->p->records.meshes[i];
+    std::memcpy(pos, m.pos.data(), m.pos.size() * 4); std::memcpy(nrm, m.nrm.data(), m.nrm.size() * 4);
+    std::memcpy(uv, m.uv.data(), m.uv.size() * 4); std::memcpy(tri, m.tri.data(), m.tri.size() * 4);
+}
+VB_API void vh_texture_info(vh_pipeline *h, uint32_t i, uint32_t *w, uint32_t *hh) { *w = h->p->records.textures[i].w; *hh = h->p->records.textures[i].h; }
+VB_API void vh_texture_copy(vh_pipeline *h, uint32_t i, float *rgba) { const Image &t = h->p->records.textures[i]; std::memcpy(rgba, t.rgba.data(), t.rgba.size() * 4); }
+/* registered plugins, '\n' separated "vision-<category>-<name>#<constructor>" */
+VB_API uint64_t vh_plugin_names(char *dst, uint64_t cap) {
+    std::string s;
+    for (auto &n : PluginRegistry::instance().names()) s += n + "\n";
+    if (dst && cap > s.size()) std::memcpy(dst, s.c_str(), s.size() + 1);
+    return s.size() + 1;
+}
+VB_API uint64_t vh_scene_log(vh_pipeline *h, char *dst, uint64_t cap) {
+    std::string s;
+    for (auto &n : h->p->scene.log) s += n + "\n";
+    if (dst && cap > s.size()) std::memcpy(dst, s.c_str(), s.size() + 1);
+    return s.size() + 1;
+}
+
+}  // extern "C"

@@ -1,0 +1,235 @@
+// Plugin implementations of the host layer (one shared library instead of one MODULE per plugin).
+// Each class cites the reference plugin it restates; host-side behaviour (desc keys, defaults,
+// vertex/triangle order, table construction) is kept, device code is a POD record.
+#include "vh_scene.h"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+namespace vh {
+
+PluginRegistry &PluginRegistry::instance() { static PluginRegistry r; return r; }
+void PluginRegistry::add(const std::string &p, const std::string &c, INodeConstructor *k) { entries_.push_back({p + "#" + c, k}); }
+INodeConstructor *PluginRegistry::find(const std::string &p, const std::string &c) const {
+    for (auto &e : entries_) if (e.first == p + "#" + c) return e.second;
+    return nullptr;
+}
+std::vector<std::string> PluginRegistry::names() const { std::vector<std::string> v; for (auto &e : entries_) v.push_back(e.first); return v; }
+
+// ---- meshes ----------------------------------------------------------------------------------
+std::vector<float> MeshData::surface_areas() const {
+    std::vector<float> out;
+    for (uint32_t t = 0; t < nt(); ++t) {
+        const float *a = &pos[3 * tri[3 * t]], *b = &pos[3 * tri[3 * t + 1]], *c = &pos[3 * tri[3 * t + 2]];
+        float e1[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, e2[3] = {c[0] - a[0], c[1] - a[1], c[2] - a[2]};
+        float cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
+        out.push_back(0.5f * std::sqrt(cx * cx + cy * cy + cz * cz));
+    }
+    return out;
+}
+uint64_t MeshData::hash() const {
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&](const void *p, size_t n) { const unsigned char *b = (const unsigned char *)p; for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; } };
+    mix(pos.data(), pos.size() * 4); mix(nrm.data(), nrm.size() * 4); mix(uv.data(), uv.size() * 4); mix(tri.data(), tri.size() * 4);
+    return h;
+}
+void ShapeGroup::add_instance(MeshData mesh) {
+    auto inst = std::make_shared<ShapeInstance>();
+    inst->mesh = std::make_shared<MeshData>(std::move(mesh));
+    instances.push_back(inst);
+}
+void ShapeGroup::post_init(const ShapeDesc &desc) {
+    std::string mat = desc["material"].as_string();
+    for (size_t i = 0; i < instances.size(); ++i) {
+        instances[i]->material_name = mat;
+        instances[i]->o2w = desc.o2w.mat;
+        instances[i]->name = name_ + "_" + std::to_string(i);
+    }
+}
+
+// reference src/render_core/shape/quad.cpp:21-50
+class Quad : public ShapeGroup {
+public:
+    explicit Quad(const ShapeDesc &desc) : ShapeGroup(desc) {
+        name_ = desc.name;
+        float w = desc["width"].as_float(1.f) / 2, h = desc["height"].as_float(1.f) / 2;
+        MeshData m;
+        float P[4][3] = {{w, 0, h}, {w, 0, -h}, {-w, 0, h}, {-w, 0, -h}};
+        float UV[4][2] = {{1, 1}, {1, 0}, {0, 1}, {0, 0}};
+        float d02[3] = {P[0][0] - P[2][0], P[0][1] - P[2][1], P[0][2] - P[2][2]}, d12[3] = {P[1][0] - P[2][0], P[1][1] - P[2][1], P[1][2] - P[2][2]};
+        float ng[3] = {d02[1] * d12[2] - d02[2] * d12[1], d02[2] * d12[0] - d02[0] * d12[2], d02[0] * d12[1] - d02[1] * d12[0]};
+        for (int i = 0; i < 4; ++i) {
+            m.pos.insert(m.pos.end(), P[i], P[i] + 3); m.nrm.insert(m.nrm.end(), ng, ng + 3); m.uv.insert(m.uv.end(), UV[i], UV[i] + 2);
+        }
+        m.tri = {0, 1, 2, 2, 1, 3};
+        add_instance(std::move(m));
+        post_init(desc);
+    }
+    std::string impl_type() const override { return "quad"; }
+};
+VH_MAKE_CLASS_CREATOR(Quad, shape, quad, constructor)
+
+// reference src/render_core/shape/cube.cpp:20-71
+class Cube : public ShapeGroup {
+public:
+    explicit Cube(const ShapeDesc &desc) : ShapeGroup(desc) {
+        name_ = desc.name;
+        float x = desc["x"].as_float(1.f), y = desc["y"].as_float(1.f), z = desc["z"].as_float(1.f);
+        y = y == 0 ? x : y; z = z == 0 ? y : z;
+        x /= 2.f; y /= 2.f; z /= 2.f;
+        const float P[24][3] = {{-x, -y, z}, {x, -y, z}, {-x, y, z}, {x, y, z}, {-x, y, -z}, {x, y, -z}, {-x, -y, -z}, {x, -y, -z},
+                                {-x, y, z}, {x, y, z}, {-x, y, -z}, {x, y, -z}, {-x, -y, z}, {x, -y, z}, {-x, -y, -z}, {x, -y, -z},
+                                {x, -y, z}, {x, y, z}, {x, y, -z}, {x, -y, -z}, {-x, -y, z}, {-x, y, z}, {-x, y, -z}, {-x, -y, -z}};
+        const float N[6][3] = {{0, 0, 1}, {0, 0, -1}, {0, 1, 0}, {0, -1, 0}, {1, 0, 0}, {-1, 0, 0}};
+        const float UV[24][2] = {{0, 0}, {1, 0}, {0, 1}, {1, 1}, {0, 1}, {1, 1}, {0, 0}, {1, 0}, {0, 1}, {1, 1}, {0, 0}, {1, 0},
+                                 {0, 1}, {1, 1}, {0, 0}, {1, 0}, {0, 1}, {1, 1}, {1, 0}, {0, 0}, {0, 1}, {1, 1}, {1, 0}, {0, 0}};
+        MeshData m;
+        for (int i = 0; i < 24; ++i) {
+            m.pos.insert(m.pos.end(), P[i], P[i] + 3); m.nrm.insert(m.nrm.end(), N[i / 4], N[i / 4] + 3); m.uv.insert(m.uv.end(), UV[i], UV[i] + 2);
+        }
+        m.tri = {0, 1, 3, 0, 3, 2, 6, 5, 7, 4, 5, 6, 10, 9, 11, 8, 9, 10, 13, 14, 15, 13, 12, 14, 18, 17, 19, 17, 16, 19, 21, 22, 23, 20, 21, 23};
+        add_instance(std::move(m));
+        post_init(desc);
+    }
+    std::string impl_type() const override { return "cube"; }
+};
+VH_MAKE_CLASS_CREATOR(Cube, shape, cube, constructor)
+
+// ---- slots -------------------------------------------------------------------------------------
+// SlotDesc / ShaderNodeDesc::init (node_desc.cpp:128-152,318-348): a colour attribute is
+//   [r,g,b] | number | {"channels","node":X} | {"type":"number","param":{"value"}} | {"fn","color_space"} | {"type":"image","param":{..}}
+static vb_slot make_slot(const ParameterSet &ps, float3 def, const SlotContext &ctx) {
+    vb_slot s{};
+    s.tex_id = VB_INVALID_ID;
+    s.value[0] = def.x; s.value[1] = def.y; s.value[2] = def.z; s.value[3] = 1.f;
+    const Json &j = ps.data();
+    if (j.is_null()) return s;
+    if (j.is_object() && j.contains("node")) return make_slot(ps["node"], def, ctx);
+    if (j.is_number()) { s.value[0] = s.value[1] = s.value[2] = (float)j.num; return s; }
+    if (j.is_array()) {
+        for (size_t i = 0; i < j.arr.size() && i < 4; ++i) s.value[i] = (float)j.arr[i].num;
+        if (j.arr.size() == 1) s.value[1] = s.value[2] = s.value[0];
+        return s;
+    }
+    if (j.is_object()) {
+        std::string type = ps["type"].as_string(j.contains("fn") ? "image" : "number");
+        ParameterSet prm = j.contains("param") ? ps["param"] : ps;
+        if (type == "number") return make_slot(prm["value"], def, ctx);
+        if (type == "image") {
+            s.value[0] = s.value[1] = s.value[2] = s.value[3] = 1.f;
+            s.tex_id = ctx.images->obtain(ctx.scene_path + "/" + prm["fn"].as_string(), prm["color_space"].as_string("srgb"));
+            return s;
+        }
+        throw std::runtime_error("shader node type not supported on this path: " + type);
+    }
+    return s;
+}
+
+// ---- materials ---------------------------------------------------------------------------------
+// reference src/render_core/material/diffuse.cpp:12-52
+class DiffuseMaterial : public Material {
+    MaterialDesc desc_;
+public:
+    explicit DiffuseMaterial(const MaterialDesc &d) : Material(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "diffuse"; }
+    void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
+        std::memset(&r, 0, sizeof(r));
+        r.type = VB_MAT_DIFFUSE;
+        r.color = make_slot(desc_["color"], {0.5f, 0.5f, 0.5f}, ctx);
+        if (desc_.has_attr("sigma")) { r.flags |= 1u; r.sigma = make_slot(desc_["sigma"], {0.5f, 0.5f, 0.5f}, ctx); }
+    }
+};
+VH_MAKE_CLASS_CREATOR(DiffuseMaterial, material, diffuse, constructor)
+
+// reference src/render_core/material/black_body.cpp (material of light-created geometry, area.cpp:55-68)
+class BlackBodyMaterial : public Material {
+public:
+    explicit BlackBodyMaterial(const MaterialDesc &d) : Material(d) { name_ = d.name; }
+    std::string impl_type() const override { return "black_body"; }
+    void fill_record(vb_material_rec &r, const SlotContext &) const override { std::memset(&r, 0, sizeof(r)); r.type = VB_MAT_BLACK_BODY; r.color.tex_id = VB_INVALID_ID; }
+};
+VH_MAKE_CLASS_CREATOR(BlackBodyMaterial, material, black_body, constructor)
+
+// ---- warper ------------------------------------------------------------------------------------
+// reference src/render_core/warper/alias.h:86-122 (sum in double, probabilities in float, LIFO stacks)
+class AliasTable : public Warper {
+public:
+    explicit AliasTable(const WarperDesc &d) : Warper(d) {}
+    std::string impl_type() const override { return "alias"; }
+    void build(const std::vector<float> &weights, std::vector<vb_alias_entry> &table, std::vector<float> &func, float &integral) const override {
+        double sum = std::accumulate(weights.begin(), weights.end(), 0.0);
+        double ratio = (double)weights.size() / sum;
+        std::vector<uint32_t> over, under;
+        std::vector<vb_alias_entry> t(weights.size());
+        for (uint32_t i = 0; i < weights.size(); ++i) {
+            float p = (float)(weights[i] * ratio);
+            t[i] = {p, i};
+            (p > 1.0f ? over : under).push_back(i);
+        }
+        while (!over.empty() && !under.empty()) {
+            uint32_t o = over.back(), u = under.back();
+            over.pop_back(); under.pop_back();
+            t[o].prob -= 1.0f - t[u].prob;
+            t[u].alias = o;
+            if (t[o].prob > 1.0f) over.push_back(o);
+            else if (t[o].prob < 1.0f) under.push_back(o);
+        }
+        for (auto i : over) t[i] = {1.0f, i};
+        for (auto i : under) t[i] = {1.0f, i};
+        integral = (float)(sum / weights.size());
+        table.insert(table.end(), t.begin(), t.end());
+        func.insert(func.end(), weights.begin(), weights.end());
+    }
+};
+VH_MAKE_CLASS_CREATOR(AliasTable, warper, alias, constructor)
+
+// ---- lights ------------------------------------------------------------------------------------
+// reference src/render_core/light/area.cpp:33-177 + Light::initialize_slots (light.cpp:19-24)
+class AreaLight : public Light {
+    LightDesc desc_;
+public:
+    explicit AreaLight(const LightDesc &d) : Light(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "area"; }
+    int type_order() const override { return VB_LIGHT_AREA; }
+    void fill_record(vb_light_rec &r, const Scene &scene, const SlotContext &ctx, std::vector<vb_alias_entry> &table,
+                     std::vector<float> &func) const override {
+        std::memset(&r, 0, sizeof(r));
+        r.type = VB_LIGHT_AREA;
+        r.inst_id = inst_idx;
+        r.two_sided = desc_["two_sided"].as_bool(false) ? 1u : 0u;
+        r.color = make_slot(desc_["color"], {0.5f, 0.5f, 0.5f}, ctx);
+        float scale = make_slot(desc_["scale"], {1.f, 1.f, 1.f}, ctx).value[0];
+        if (!desc_.has_attr("scale")) scale = 1.f;
+        if (r.color.tex_id == VB_INVALID_ID) {                 // NumberArray::normalize (number.cpp:40-49)
+            float mx = std::max(r.color.value[0], std::max(r.color.value[1], r.color.value[2]));
+            if (!(mx < 1.f)) { for (int i = 0; i < 3; ++i) r.color.value[i] /= mx; scale *= mx; }
+        }
+        r.scale = scale;
+        std::vector<float> w = scene.instances[inst_idx]->mesh->surface_areas();
+        r.alias_offset = (uint32_t)table.size(); r.alias_size = (uint32_t)w.size();
+        scene.warper->build(w, table, func, r.alias_integral);
+    }
+};
+VH_MAKE_CLASS_CREATOR(AreaLight, light, area, constructor)
+
+void LightSampler::tidy_up() {
+    // Polymorphic topology order = order in which light TYPES were first added
+    std::vector<int> first;
+    for (auto &l : lights) if (std::find(first.begin(), first.end(), l->type_order()) == first.end()) first.push_back(l->type_order());
+    std::stable_sort(lights.begin(), lights.end(), [&](const std::shared_ptr<Light> &a, const std::shared_ptr<Light> &b) {
+        return std::find(first.begin(), first.end(), a->type_order()) < std::find(first.begin(), first.end(), b->type_order());
+    });
+    for (uint32_t i = 0; i < lights.size(); ++i) lights[i]->index = i;
+}
+// reference src/render_core/lightsampler/uniform.cpp:12-34 (device part: index = min(u*N, N-1), PMF 1/N)
+class UniformLightSampler : public LightSampler {
+public:
+    explicit UniformLightSampler(const LightSamplerDesc &d) : LightSampler(d) {}
+    std::string impl_type() const override { return "uniform"; }
+};
+VH_MAKE_CLASS_CREATOR(UniformLightSampler, lightsampler, uniform, constructor)
+
+}  // namespace vh
+
+#include "vh_plugins2.inl"

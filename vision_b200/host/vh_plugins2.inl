@@ -1,0 +1,122 @@
+// Included by vh_plugins.cpp: sampler, filters, spectrum, tone mappers, sensor, integrator, frame buffer.
+namespace vh {
+
+// reference src/render_core/sampler/independent.cpp:13-43
+class IndependentSampler : public Sampler {
+public:
+    explicit IndependentSampler(const SamplerDesc &d) : Sampler(d) {}
+    std::string impl_type() const override { return "independent"; }
+    uint32_t device_tag() const override { return 0; }
+};
+VH_MAKE_CLASS_CREATOR(IndependentSampler, sampler, independent, constructor)
+
+// reference src/render_core/filter/box.cpp:16-20, triangle.cpp:16-18
+class BoxFilter : public Filter {
+public:
+    explicit BoxFilter(const FilterDesc &d) : Filter(d) {}
+    std::string impl_type() const override { return "box"; }
+    uint32_t device_tag() const override { return VB_FILTER_BOX; }
+};
+VH_MAKE_CLASS_CREATOR(BoxFilter, filter, box, constructor)
+class TriangleFilter : public Filter {
+public:
+    explicit TriangleFilter(const FilterDesc &d) : Filter(d) {}
+    std::string impl_type() const override { return "triangle"; }
+    uint32_t device_tag() const override { return VB_FILTER_TRIANGLE; }
+};
+VH_MAKE_CLASS_CREATOR(TriangleFilter, filter, triangle, constructor)
+
+// reference src/render_core/spectrum/srgb.cpp:16-57
+class SRGBSpectrum : public Spectrum {
+public:
+    explicit SRGBSpectrum(const SpectrumDesc &d) : Spectrum(d) {}
+    std::string impl_type() const override { return "srgb"; }
+    uint32_t device_tag() const override { return 0; }
+};
+VH_MAKE_CLASS_CREATOR(SRGBSpectrum, spectrum, srgb, constructor)
+
+// reference src/render_core/tonemapper/impl.cpp:9-52: one module "vision-tonemapper-impl", three constructors
+class LinearToneMapper : public ToneMapper { public: explicit LinearToneMapper(const ToneMapperDesc &d) : ToneMapper(d) {} std::string impl_type() const override { return "linear"; } int device_tag() const override { return VB_TONEMAP_LINEAR; } };
+class ACESToneMapper : public ToneMapper { public: explicit ACESToneMapper(const ToneMapperDesc &d) : ToneMapper(d) {} std::string impl_type() const override { return "aces"; } int device_tag() const override { return VB_TONEMAP_ACES; } };
+class ReinhardToneMapper : public ToneMapper { public: explicit ReinhardToneMapper(const ToneMapperDesc &d) : ToneMapper(d) {} std::string impl_type() const override { return "reinhard"; } int device_tag() const override { return VB_TONEMAP_REINHARD; } };
+VH_MAKE_CLASS_CREATOR(LinearToneMapper, tonemapper, impl, linear)
+VH_MAKE_CLASS_CREATOR(ACESToneMapper, tonemapper, impl, aces)
+VH_MAKE_CLASS_CREATOR(ReinhardToneMapper, tonemapper, impl, reinhard)
+
+// ---- sensor: reference src/base/sensor/sensor.cpp:13-25,58-78,153-162; thin_lens.cpp:15-42 ----
+Sensor::Sensor(const SensorDesc &desc) {
+    name_ = desc.name;
+    fov_y = std::min(120.f, std::max(15.f, desc["fov_y"].as_float(20.f)));
+    focal_distance = desc["focal_distance"].as_float(5.f);
+    lens_radius = desc["lens_radius"].as_float(0.f);
+    update_mat(desc.transform_desc.mat);
+    filter = create_shared<Filter>(desc.filter_desc);
+}
+void Sensor::update_mat(const Mat4 &m) {
+    const double R2D = 180.0 / 3.14159265358979323846;
+    pitch = (float)(std::atan2((double)m[4 * 1 + 2], (double)m[4 * 1 + 1]) * R2D);   // m[1][2], m[1][1]
+    yaw = (float)(std::atan2((double)m[4 * 2 + 0], (double)m[4 * 0 + 0]) * R2D);     // m[2][0], m[0][0]
+    position = {m[12], m[13], m[14]};
+}
+Mat4 Sensor::camera_to_world() const {
+    Mat4 rot = mat4_mul(mat4_mul(scaling({1, 1, -1}), rotation_y(yaw)), rotation_x(-pitch));
+    return mat4_mul(translation(position), rot);
+}
+void Sensor::fill_record(vb_camera &cam, uint32_t w, uint32_t h) const {
+    std::memset(&cam, 0, sizeof(cam));
+    Mat4 c2w = camera_to_world();
+    std::memcpy(cam.c2w, c2w.data(), 64);
+    cam.tan_fov_y_over_2 = (float)std::tan((double)fov_y * 3.14159265358979323846 / 180.0 * 0.5);
+    cam.lens_radius = lens_radius; cam.focal_distance = focal_distance; cam.medium_id = VB_INVALID_ID;
+    float ratio = (float)w * 1.f / (float)h;                        // frame_buffer.cpp:93-102
+    cam.screen_lo[0] = cam.screen_lo[1] = -1.f; cam.screen_hi[0] = cam.screen_hi[1] = 1.f;
+    if (ratio > 1.f) { cam.screen_lo[0] = -ratio; cam.screen_hi[0] = ratio; }
+    else { cam.screen_lo[1] = -1.f / ratio; cam.screen_hi[1] = 1.f / ratio; }
+    cam.filter_type = filter->device_tag();
+    cam.filter_radius[0] = filter->radius[0]; cam.filter_radius[1] = filter->radius[1];
+}
+class ThinLensCamera : public Sensor {
+public:
+    explicit ThinLensCamera(const SensorDesc &d) : Sensor(d) {}
+    std::string impl_type() const override { return "thin_lens"; }
+};
+VH_MAKE_CLASS_CREATOR(ThinLensCamera, sensor, thin_lens, constructor)
+class PinholeCamera : public Sensor {
+public:
+    explicit PinholeCamera(const SensorDesc &d) : Sensor(d) { lens_radius = 0.f; }
+    std::string impl_type() const override { return "pinhole"; }
+};
+VH_MAKE_CLASS_CREATOR(PinholeCamera, sensor, pinhole, constructor)
+
+// ---- frame buffer: reference src/base/sensor/frame_buffer.cpp:16-26 ----
+FrameBuffer::FrameBuffer(const FrameBufferDesc &d) {
+    std::vector<float> res = d["resolution"].as_floats();
+    width = res.size() >= 2 ? (uint32_t)res[0] : 1280u;
+    height = res.size() >= 2 ? (uint32_t)res[1] : 720u;
+    exposure = d["exposure"].as_float(1.f);
+    tone_mapper = create_shared<ToneMapper>(d.tone_mapper);
+}
+class NormalFrameBuffer : public FrameBuffer {
+public:
+    explicit NormalFrameBuffer(const FrameBufferDesc &d) : FrameBuffer(d) {}
+    std::string impl_type() const override { return "normal"; }
+};
+VH_MAKE_CLASS_CREATOR(NormalFrameBuffer, framebuffer, normal, constructor)
+
+// ---- integrator: reference src/render_core/integrator/pt.cpp:27-37,96-116 ----
+class PathTracingIntegrator : public Integrator {
+public:
+    explicit PathTracingIntegrator(const IntegratorDesc &d) : Integrator(d) {}
+    std::string impl_type() const override { return "pt"; }
+    void render(Pipeline &p, uint32_t n_frames) override {
+        // reference: per frame GBuffer -> path_tracing -> accumulate -> tone map, frame_index_++ ;
+        // here one launch renders the whole batch of frame indices (film kept in registers)
+        p.check(vb_render_frames(p.ctx, frame_index, n_frames, 1, VB_ACCUM_LERP), "vb_render_frames");
+        frame_index += n_frames;
+    }
+};
+VH_MAKE_CLASS_CREATOR(PathTracingIntegrator, integrator, pt, constructor)
+
+VH_MAKE_CLASS_CREATOR(Pipeline, pipeline, fixed, constructor)
+
+}  // namespace vh

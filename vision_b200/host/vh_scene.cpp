@@ -1,0 +1,203 @@
+#include "vh_scene.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <map>
+
+namespace vh {
+
+// ---- images ------------------------------------------------------------------------------------
+static float srgb_to_linear(float c) { return c <= 0.04045f ? c / 12.92f : std::pow((c + 0.055f) / 1.055f, 2.4f); }
+static float linear_to_srgb(float c) { c = std::min(1.f, std::max(0.f, c)); return c <= 0.0031308f ? 12.92f * c : 1.055f * std::pow(c, 1.f / 2.4f) - 0.055f; }
+
+static bool read_pnm_token(std::istream &f, std::string &tok) {
+    tok.clear();
+    int c;
+    while ((c = f.get()) != EOF) {
+        if (c == '#') { while ((c = f.get()) != EOF && c != '\n') {} continue; }
+        if (!isspace(c)) { tok.push_back((char)c); break; }
+    }
+    while ((c = f.get()) != EOF && !isspace(c)) tok.push_back((char)c);
+    return !tok.empty();
+}
+
+Image load_image(const std::string &path, bool to_linear) {
+    std::string p = path;
+    auto ends = [&](const char *e) { size_t n = strlen(e); return p.size() >= n && strcasecmp(p.c_str() + p.size() - n, e) == 0; };
+    if (!ends(".pfm") && !ends(".ppm")) p = path + ".pfm";          // decoded side-car (tools/convert_textures.py)
+    std::ifstream f(p, std::ios::binary);
+    if (!f) throw std::runtime_error("cannot open image " + path + " (run tools/convert_textures.py to write " + p + ")");
+    std::string magic, tw, th, ts;
+    read_pnm_token(f, magic); read_pnm_token(f, tw); read_pnm_token(f, th); read_pnm_token(f, ts);
+    Image im; im.w = (uint32_t)std::stoul(tw); im.h = (uint32_t)std::stoul(th);
+    im.rgba.resize((size_t)im.w * im.h * 4);
+    if (magic == "PF" || magic == "Pf") {
+        int ch = magic == "PF" ? 3 : 1;
+        std::vector<float> raw((size_t)im.w * im.h * ch);
+        f.read((char *)raw.data(), raw.size() * 4);
+        for (uint32_t y = 0; y < im.h; ++y)                         // PFM rows are bottom-up
+            for (uint32_t x = 0; x < im.w; ++x) {
+                const float *s = &raw[((size_t)(im.h - 1 - y) * im.w + x) * ch];
+                float *d = &im.rgba[((size_t)y * im.w + x) * 4];
+                d[0] = s[0]; d[1] = s[ch == 3 ? 1 : 0]; d[2] = s[ch == 3 ? 2 : 0]; d[3] = 1.f;
+            }
+    } else if (magic == "P6") {
+        std::vector<unsigned char> raw((size_t)im.w * im.h * 3);
+        f.read((char *)raw.data(), raw.size());
+        for (size_t i = 0; i < (size_t)im.w * im.h; ++i) { for (int c = 0; c < 3; ++c) im.rgba[4 * i + c] = raw[3 * i + c] / 255.f; im.rgba[4 * i + 3] = 1.f; }
+    } else throw std::runtime_error("unsupported image format " + p);
+    if (to_linear) for (size_t i = 0; i < (size_t)im.w * im.h; ++i) for (int c = 0; c < 3; ++c) im.rgba[4 * i + c] = srgb_to_linear(im.rgba[4 * i + c]);
+    return im;
+}
+void save_pfm(const std::string &path, const float *rgba, uint32_t w, uint32_t h) {
+    std::ofstream f(path, std::ios::binary);
+    f << "PF\n" << w << " " << h << "\n-1.0\n";
+    for (uint32_t y = 0; y < h; ++y) for (uint32_t x = 0; x < w; ++x) f.write((const char *)&rgba[((size_t)(h - 1 - y) * w + x) * 4], 12);
+}
+void save_ppm(const std::string &path, const float *rgba01, uint32_t w, uint32_t h) {
+    std::ofstream f(path, std::ios::binary);
+    f << "P6\n" << w << " " << h << "\n255\n";
+    for (size_t i = 0; i < (size_t)w * h; ++i) for (int c = 0; c < 3; ++c) { unsigned char b = (unsigned char)(linear_to_srgb(rgba01[4 * i + c]) * 255.f + 0.5f); f.put((char)b); }
+}
+// reference image_pool.cpp:13-35: .exr/.hdr are linear, everything else follows color_space (default srgb)
+uint32_t ImagePool::obtain(const std::string &path, const std::string &color_space) {
+    std::string key = path + "|" + color_space;
+    for (uint32_t i = 0; i < keys.size(); ++i) if (keys[i] == key) return i;
+    auto ends = [&](const char *e) { size_t n = strlen(e); return path.size() >= n && strcasecmp(path.c_str() + path.size() - n, e) == 0; };
+    // side-car .pfm files written by tools/convert_textures.py hold the decoded 8-bit values / 255 of LDR sources
+    bool to_linear = color_space == "srgb" && !ends(".exr") && !ends(".hdr");
+    images.push_back(load_image(path, to_linear));
+    keys.push_back(key);
+    return (uint32_t)images.size() - 1;
+}
+
+// ---- scene -------------------------------------------------------------------------------------
+std::shared_ptr<Material> Scene::obtain_black_body() {
+    if (!black_body) { MaterialDesc d; d.sub_type = "black_body"; d.name = "__black_body"; black_body = create_shared<Material>(d); materials.push_back(black_body); }
+    return black_body;
+}
+
+// reference scene.cpp:16-34: light_sampler, spectrum, materials, mediums, sensor, shapes, integrator, sampler
+void Scene::init(const SceneDesc &d) {
+    desc = d;
+    warper = create_shared<Warper>(d.warper_desc);
+    light_sampler = create_shared<LightSampler>(d.light_sampler_desc);
+    for (const LightDesc &ld : d.light_sampler_desc.light_descs) light_sampler->add_light(create_shared<Light>(ld));
+    spectrum = create_shared<Spectrum>(d.spectrum_desc);
+    for (const MaterialDesc &md : d.material_descs) materials.push_back(create_shared<Material>(md));
+    if (d.process_mediums) throw std::runtime_error("mediums.process = true: not implemented on this path yet");
+    frame_buffer = create_shared<FrameBuffer>(d.pipeline_desc.frame_buffer_desc);
+    sensor = create_shared<Sensor>(d.sensor_desc);
+    for (const ShapeDesc &sd : d.shape_descs) add_shape(create_shared<ShapeGroup>(sd), sd);
+    integrator = create_shared<Integrator>(d.integrator_desc);
+    sampler = create_shared<Sampler>(d.sampler_desc);
+    for (auto &k : d.ignored_keys) log.push_back("scene key ignored on this path: " + k);
+}
+
+// reference scene.cpp:118-151
+void Scene::add_shape(const std::shared_ptr<ShapeGroup> &group, const ShapeDesc &sd) {
+    groups.push_back(group);
+    for (auto &inst : group->instances) {
+        auto it = std::find_if(materials.begin(), materials.end(), [&](const std::shared_ptr<Material> &m) { return m->name() == inst->material_name; });
+        if (it != materials.end() && !inst->material) inst->material = *it;
+        if (sd.has_emission && sd.emission.valid()) {
+            LightDesc ld = sd.emission;
+            ld.parameter.set_value("inst_id", Json::number((double)instances.size()));
+            auto light = create_shared<Light>(ld);
+            light_sampler->add_light(light);
+            inst->emission = light;
+        }
+        instances.push_back(inst);
+    }
+}
+
+// reference scene.cpp:79-91 (remove unused materials -> tidy_up -> fill_instances -> prepare) and
+// geometry.cpp:20-34 (mesh handles / instance table); MeshRegistry dedupes meshes by content hash
+void Scene::prepare(SceneRecords &out) {
+    out = SceneRecords();
+    // remove_unused_materials + index assignment
+    std::vector<std::shared_ptr<Material>> used;
+    for (auto &m : materials) {
+        bool u = false;
+        for (auto &i : instances) u |= i->material == m;
+        if (u) { m->index = (uint32_t)used.size(); used.push_back(m); }
+    }
+    materials = used;
+    light_sampler->tidy_up();
+    SlotContext sctx{&image_pool, desc.scene_path};
+    out.materials.resize(materials.size());
+    for (auto &m : materials) m->fill_record(out.materials[m->index], sctx);
+    std::map<uint64_t, uint32_t> mesh_ids;
+    for (auto &i : instances) {
+        if (!i->material) throw std::runtime_error("instance " + i->name + ": material '" + i->material_name + "' not found");
+        uint64_t h = i->mesh->hash();
+        auto f = mesh_ids.find(h);
+        if (f == mesh_ids.end()) { f = mesh_ids.emplace(h, (uint32_t)out.meshes.size()).first; out.meshes.push_back(i->mesh); }
+        vb_instance r{};
+        r.mesh_id = f->second; r.material_id = i->material->index; r.light_id = i->emission ? i->emission->index : VB_INVALID_ID;
+        r.inside_medium = r.outside_medium = r.lightmap_id = VB_INVALID_ID;
+        std::memcpy(r.o2w, i->o2w.data(), 64);
+        out.instances.push_back(r);
+    }
+    out.lights.resize(light_sampler->lights.size());
+    for (auto &l : light_sampler->lights) l->fill_record(out.lights[l->index], *this, sctx, out.alias_table, out.alias_func);
+    out.textures = image_pool.images;
+    out.width = frame_buffer->width; out.height = frame_buffer->height;
+    sensor->fill_record(out.camera, out.width, out.height);
+    out.params = vb_pt_params{};
+    out.params.max_depth = integrator->max_depth; out.params.min_depth = integrator->min_depth;
+    out.params.rr_threshold = integrator->rr_threshold; out.params.mis_mode = integrator->mis_mode;
+    out.params.spectrum = spectrum->device_tag(); out.params.sampler = sampler->device_tag();
+    out.params.process_mediums = 0; out.params.ray_offset_factor = desc.render_setting.ray_offset_factor;
+    out.spp = desc.output_desc.spp ? desc.output_desc.spp : sampler->spp;
+    out.exposure = frame_buffer->exposure; out.tonemap = frame_buffer->tone_mapper->device_tag();
+}
+
+// ---- pipeline ----------------------------------------------------------------------------------
+void Pipeline::check(int rc, const char *what) const {
+    if (rc != VB_OK) throw std::runtime_error(std::string(what) + " failed: " + vb_last_error(ctx));
+}
+Pipeline::~Pipeline() { if (ctx) vb_ctx_destroy(ctx); }
+void Pipeline::init_scene(const SceneDesc &d) { scene.init(d); }
+
+// FixedRenderPipeline::prepare (fixed/pipeline.cpp:14-23) + Pipeline::prepare_geometry (pipeline.cpp:272-277)
+void Pipeline::prepare(int device) {
+    scene.prepare(records);
+    if (vb_ctx_create(device, &ctx) != VB_OK) throw std::runtime_error(std::string("vb_ctx_create failed: ") + vb_last_error(nullptr));
+    std::vector<uint32_t> ids;
+    for (auto &m : records.meshes) {
+        uint32_t id;
+        check(vb_mesh_upload(ctx, m->pos.data(), m->nrm.data(), m->uv.data(), m->nv(), m->tri.data(), m->nt(), &id), "vb_mesh_upload");
+        ids.push_back(id);
+    }
+    std::vector<vb_instance> inst = records.instances;
+    for (auto &i : inst) i.mesh_id = ids[i.mesh_id];
+    check(vb_instances_set(ctx, inst.data(), (uint32_t)inst.size()), "vb_instances_set");
+    check(vb_accel_build(ctx, nullptr, &build_stats), "vb_accel_build");
+    std::vector<vb_texture> tex;
+    for (auto &t : records.textures) tex.push_back(vb_texture{t.rgba.data(), t.w, t.h});
+    check(vb_textures_set(ctx, tex.data(), (uint32_t)tex.size()), "vb_textures_set");
+    check(vb_materials_set(ctx, records.materials.data(), (uint32_t)records.materials.size()), "vb_materials_set");
+    check(vb_lights_set(ctx, records.lights.data(), (uint32_t)records.lights.size(), records.alias_table.data(), records.alias_func.data(),
+                        (uint32_t)records.alias_table.size()), "vb_lights_set");
+    check(vb_camera_set(ctx, &records.camera), "vb_camera_set");
+    check(vb_integrator_set(ctx, &records.params), "vb_integrator_set");
+    check(vb_film_create(ctx, records.width, records.height), "vb_film_create");
+}
+void Pipeline::render(uint32_t n_frames) { scene.integrator->render(*this, n_frames); }
+void Pipeline::final_picture(std::vector<float> &rgba) {
+    check(vb_film_resolve(ctx, VB_ACCUM_LERP, records.exposure, records.tonemap), "vb_film_resolve");
+    rgba.resize((size_t)records.width * records.height * 4);
+    check(vb_film_download(ctx, rgba.data(), VB_FILM_OUTPUT), "vb_film_download");
+}
+
+std::shared_ptr<Pipeline> import_scene(const std::string &path) {
+    SceneDesc sd = SceneDesc::from_json(path);
+    auto p = create_shared<Pipeline>(sd.pipeline_desc);
+    p->init_scene(sd);
+    return p;
+}
+
+}  // namespace vh

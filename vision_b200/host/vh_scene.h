@@ -1,0 +1,82 @@
+// Scene / Pipeline / ImagePool of the host layer.
+//   Scene::init order, add_shape, fill_instances   reference src/base/mgr/scene.cpp:16-34,118-187
+//   Pipeline::prepare (FixedRenderPipeline)        reference src/pipelines/fixed/pipeline.cpp:14-42
+//   Geometry::update_instances/upload/build_accel  reference src/base/mgr/geometry.cpp:20-71
+//   ImagePool::load_texture                        reference src/base/mgr/image_pool.cpp:13-35
+#pragma once
+#include "vh_node.h"
+
+namespace vh {
+
+struct Image { uint32_t w = 0, h = 0; std::vector<float> rgba; };
+// .pfm / .ppm natively; other formats through a decoded side-car "<file>.pfm" written by
+// tools/convert_textures.py (image decoding is a §8f "next" row; no image library in this image)
+Image load_image(const std::string &path, bool srgb_to_linear);
+void save_pfm(const std::string &path, const float *rgba, uint32_t w, uint32_t h);
+void save_ppm(const std::string &path, const float *rgba01, uint32_t w, uint32_t h);   // applies linear_to_srgb
+
+class ImagePool {
+public:
+    std::vector<Image> images;
+    std::vector<std::string> keys;
+    uint32_t obtain(const std::string &path, const std::string &color_space);   // dedupes by (path, colour space)
+};
+
+// POD view of a prepared scene: exactly what is pushed through the C ABI (and what tests feed the oracle)
+struct SceneRecords {
+    std::vector<std::shared_ptr<MeshData>> meshes;
+    std::vector<vb_instance> instances;
+    std::vector<vb_material_rec> materials;
+    std::vector<vb_light_rec> lights;
+    std::vector<vb_alias_entry> alias_table;
+    std::vector<float> alias_func;
+    std::vector<Image> textures;
+    vb_camera camera{};
+    vb_pt_params params{};
+    uint32_t width = 0, height = 0, spp = 1;
+    float exposure = 1.f; int tonemap = 0;
+};
+
+class Scene {
+public:
+    SceneDesc desc;
+    std::shared_ptr<LightSampler> light_sampler;
+    std::shared_ptr<Spectrum> spectrum;
+    std::vector<std::shared_ptr<Material>> materials;
+    std::shared_ptr<Sensor> sensor;
+    std::vector<std::shared_ptr<ShapeGroup>> groups;
+    std::vector<std::shared_ptr<ShapeInstance>> instances;
+    std::shared_ptr<Integrator> integrator;
+    std::shared_ptr<Sampler> sampler;
+    std::shared_ptr<Warper> warper;
+    std::shared_ptr<FrameBuffer> frame_buffer;
+    ImagePool image_pool;
+    std::shared_ptr<Material> black_body;
+    std::vector<std::string> log;
+
+    void init(const SceneDesc &d);                    // scene.cpp:16-34
+    void add_shape(const std::shared_ptr<ShapeGroup> &group, const ShapeDesc &sd);
+    void prepare(SceneRecords &out);                  // scene.cpp:79-91 + geometry.cpp:20-34
+    std::shared_ptr<Material> obtain_black_body();
+};
+
+class Pipeline : public Node {     // "vision-pipeline-fixed"
+public:
+    using Desc = PipelineDesc;
+    Scene scene;
+    SceneRecords records;
+    vb_ctx *ctx = nullptr;
+    vb_build_stats build_stats{};
+    explicit Pipeline(const PipelineDesc &) {}
+    std::string impl_type() const override { return "fixed"; }
+    void init_scene(const SceneDesc &d);
+    void prepare(int device);                         // uploads through the C ABI, builds the BVH
+    void render(uint32_t n_frames);                   // integrator->render
+    void final_picture(std::vector<float> &rgba);     // resolve + download (pipeline.cpp:337-354)
+    ~Pipeline() override;
+    void check(int rc, const char *what) const;
+};
+
+std::shared_ptr<Pipeline> import_scene(const std::string &path);   // Importer::import_scene (importer.cpp:23-26)
+
+}  // namespace vh

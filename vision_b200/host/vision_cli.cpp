@@ -1,0 +1,52 @@
+// vision-cli: headless stand-in for the reference's GUI-only driver (src/apps/vision-gui/main.cpp:10-14,
+// application.cpp:37-49,174-199; CLI flags of src/base/cli_parser.cpp:18-43 that this path uses).
+//   vision-cli -s <scene.json> [-o out.ppm] [--spp N] [-d cuda] [--device-index I] [--pfm out.pfm]
+#include "vh_scene.h"
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+
+int main(int argc, char **argv) {
+    std::string scene, out = "output.ppm", pfm, device = "cuda";
+    uint32_t spp = 0; int dev_index = 0;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        auto next = [&]() { if (i + 1 >= argc) { fprintf(stderr, "missing value for %s\n", a.c_str()); exit(2); } return std::string(argv[++i]); };
+        if (a == "-s" || a == "--scene") scene = next();
+        else if (a == "-o" || a == "--output") out = next();
+        else if (a == "--pfm") pfm = next();
+        else if (a == "--spp") spp = (uint32_t)std::stoul(next());
+        else if (a == "-d" || a == "--device") device = next();
+        else if (a == "--device-index") dev_index = std::stoi(next());
+        else if (a == "-h" || a == "--help") { printf("vision-cli -s scene.json [-o out.ppm] [--pfm out.pfm] [--spp N] [-d cuda]\n"); return 0; }
+        else fprintf(stderr, "ignored argument %s\n", a.c_str());
+    }
+    if (scene.empty()) { fprintf(stderr, "vision-cli: -s <scene file> is required\n"); return 2; }
+    if (device != "cuda") { fprintf(stderr, "vision-cli: only -d cuda exists (no CPU backend)\n"); return 2; }
+    try {
+        auto t0 = std::chrono::steady_clock::now();
+        auto p = vh::import_scene(scene);
+        p->prepare(dev_index);
+        for (auto &l : p->scene.log) fprintf(stderr, "[vision] %s\n", l.c_str());
+        uint32_t n = spp ? spp : p->records.spp;
+        auto t1 = std::chrono::steady_clock::now();
+        p->render(n);
+        std::vector<float> img;
+        p->final_picture(img);
+        auto t2 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[vision] %ux%u, %u spp, %llu triangles, %llu wide nodes, BVH build %.2f ms, init %.1f ms, render %.1f ms\n",
+                p->records.width, p->records.height, n, (unsigned long long)p->build_stats.n_triangles,
+                (unsigned long long)p->build_stats.n_nodes, p->build_stats.build_ms,
+                std::chrono::duration<double, std::milli>(t1 - t0).count(), std::chrono::duration<double, std::milli>(t2 - t1).count());
+        vh::save_ppm(out, img.data(), p->records.width, p->records.height);
+        if (!pfm.empty()) {
+            std::vector<float> acc((size_t)p->records.width * p->records.height * 4);
+            p->check(vb_film_download(p->ctx, acc.data(), VB_FILM_ACCUM), "vb_film_download");
+            vh::save_pfm(pfm, acc.data(), p->records.width, p->records.height);
+        }
+    } catch (const std::exception &e) {
+        fprintf(stderr, "vision-cli: %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}

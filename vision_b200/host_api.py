@@ -1,0 +1,150 @@
+"""ctypes binding of libvision_host.so - the C++ host layer (scene JSON -> desc -> plugins -> C ABI)."""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+from . import capi
+
+LIB_PATH = Path(__file__).resolve().parent / "libvision_host.so"
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise capi.VbError(f"{LIB_PATH} missing: run __graft_entry__.build()")
+        capi.load_library()
+        lib = C.CDLL(str(LIB_PATH))
+        vp = C.c_void_p
+        lib.vh_last_error.restype = C.c_char_p
+        lib.vh_import_scene.argtypes = [C.c_char_p]; lib.vh_import_scene.restype = vp
+        lib.vh_destroy.argtypes = [vp]; lib.vh_destroy.restype = None
+        lib.vh_override.argtypes = [vp, C.c_char_p, C.c_double, C.c_double]
+        lib.vh_prepare_records.argtypes = [vp]
+        lib.vh_prepare.argtypes = [vp, C.c_int]
+        lib.vh_render.argtypes = [vp, C.c_uint32]
+        lib.vh_final_picture.argtypes = [vp, vp]
+        lib.vh_download_accum.argtypes = [vp, vp]
+        lib.vh_info.argtypes = [vp, vp, vp]; lib.vh_info.restype = None
+        lib.vh_records_blob.argtypes = [vp, C.c_int, vp, C.c_uint64]; lib.vh_records_blob.restype = C.c_uint64
+        lib.vh_mesh_info.argtypes = [vp, C.c_uint32, vp, vp]; lib.vh_mesh_info.restype = None
+        lib.vh_mesh_copy.argtypes = [vp, C.c_uint32, vp, vp, vp, vp]; lib.vh_mesh_copy.restype = None
+        lib.vh_texture_info.argtypes = [vp, C.c_uint32, vp, vp]; lib.vh_texture_info.restype = None
+        lib.vh_texture_copy.argtypes = [vp, C.c_uint32, vp]; lib.vh_texture_copy.restype = None
+        lib.vh_plugin_names.argtypes = [vp, C.c_uint64]; lib.vh_plugin_names.restype = C.c_uint64
+        lib.vh_scene_log.argtypes = [vp, vp, C.c_uint64]; lib.vh_scene_log.restype = C.c_uint64
+        _lib = lib
+    return _lib
+
+
+def plugin_names():
+    lib = load()
+    n = lib.vh_plugin_names(None, 0)
+    buf = C.create_string_buffer(n + 1)
+    lib.vh_plugin_names(buf, n + 1)
+    return [s for s in buf.value.decode().split("\n") if s]
+
+
+class HostPipeline:
+    """Importer::import_scene + Pipeline::prepare/render/final_picture of the reference, through libvision_host"""
+
+    def __init__(self, scene_path, overrides=None):
+        self.lib = load()
+        self.h = C.c_void_p(self.lib.vh_import_scene(str(scene_path).encode()))
+        if not self.h:
+            raise capi.VbError("vh_import_scene: " + self.lib.vh_last_error().decode())
+        for k, v in (overrides or {}).items():
+            a, b = (v if isinstance(v, (list, tuple)) else (v, 0))
+            self._check(self.lib.vh_override(self.h, k.encode(), float(a), float(b)), "vh_override")
+
+    def _check(self, rc, what):
+        if rc:
+            raise capi.VbError(f"{what}: {self.lib.vh_last_error().decode()}")
+
+    def close(self):
+        if self.h:
+            self.lib.vh_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def prepare_records(self):
+        self._check(self.lib.vh_prepare_records(self.h), "vh_prepare_records")
+
+    def prepare(self, device=0):
+        self._check(self.lib.vh_prepare(self.h, device), "vh_prepare")
+
+    def info(self):
+        v = (C.c_uint32 * 10)()
+        e = C.c_float()
+        self.lib.vh_info(self.h, v, C.byref(e))
+        keys = ("width", "height", "spp", "n_meshes", "n_instances", "n_materials", "n_lights", "n_alias", "n_textures", "tonemap")
+        d = dict(zip(keys, list(v)))
+        d["exposure"] = e.value
+        return d
+
+    def render(self, n_frames):
+        self._check(self.lib.vh_render(self.h, n_frames), "vh_render")
+
+    def accum(self):
+        i = self.info()
+        out = np.empty((i["height"], i["width"], 4), np.float32)
+        self._check(self.lib.vh_download_accum(self.h, out.ctypes.data), "vh_download_accum")
+        return out
+
+    def final_picture(self):
+        i = self.info()
+        out = np.empty((i["height"], i["width"], 4), np.float32)
+        self._check(self.lib.vh_final_picture(self.h, out.ctypes.data), "vh_final_picture")
+        return out
+
+    def log(self):
+        n = self.lib.vh_scene_log(self.h, None, 0)
+        buf = C.create_string_buffer(n + 1)
+        self.lib.vh_scene_log(self.h, buf, n + 1)
+        return [s for s in buf.value.decode().split("\n") if s]
+
+    def _blob(self, which, ctype):
+        n = self.lib.vh_records_blob(self.h, which, None, 0)
+        cnt = n // C.sizeof(ctype)
+        arr = (ctype * max(1, cnt))()
+        self.lib.vh_records_blob(self.h, which, arr, n)
+        return list(arr)[:cnt]
+
+    def records(self) -> capi.SceneRecords:
+        """the POD records the C++ host layer produced, as a capi.SceneRecords (feedable to the oracle)"""
+        i = self.info()
+        sc = capi.SceneRecords()
+        for m in range(i["n_meshes"]):
+            nv, nt = C.c_uint32(), C.c_uint32()
+            self.lib.vh_mesh_info(self.h, m, C.byref(nv), C.byref(nt))
+            pos = np.empty((nv.value, 3), np.float32); nrm = np.empty((nv.value, 3), np.float32)
+            uv = np.empty((nv.value, 2), np.float32); tri = np.empty((nt.value, 3), np.uint32)
+            self.lib.vh_mesh_copy(self.h, m, pos.ctypes.data, nrm.ctypes.data, uv.ctypes.data, tri.ctypes.data)
+            sc.meshes.append({"pos": pos, "nrm": nrm, "uv": uv, "tri": tri})
+        for r in self._blob(0, capi.vb_instance):
+            sc.instances.append({"mesh_id": r.mesh_id, "material_id": r.material_id, "light_id": r.light_id,
+                                 "inside_medium": r.inside_medium, "outside_medium": r.outside_medium,
+                                 "lightmap_id": r.lightmap_id, "o2w": np.array(list(r.o2w), np.float32)})
+        sc.materials = self._blob(1, capi.vb_material_rec)
+        sc.lights = self._blob(2, capi.vb_light_rec)
+        sc.alias_table = [(e.prob, e.alias) for e in self._blob(3, capi.vb_alias_entry)]
+        sc.alias_func = [float(x) for x in self._blob(4, C.c_float)]
+        sc.camera = self._blob(5, capi.vb_camera)[0]
+        sc.params = self._blob(6, capi.vb_pt_params)[0]
+        for t in range(i["n_textures"]):
+            w, h = C.c_uint32(), C.c_uint32()
+            self.lib.vh_texture_info(self.h, t, C.byref(w), C.byref(h))
+            a = np.empty((h.value, w.value, 4), np.float32)
+            self.lib.vh_texture_copy(self.h, t, a.ctypes.data)
+            sc.textures.append(a)
+        sc.resolution = (i["width"], i["height"]); sc.spp = i["spp"]; sc.exposure = i["exposure"]; sc.tonemap = i["tonemap"]
+        return sc
