@@ -39,6 +39,9 @@ def parse():
     p.add_argument("--rays", type=int, default=1 << 24)
     p.add_argument("--cpu-sample-rays", type=int, default=1 << 18)
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--pt-res", type=int, default=1024)
+    p.add_argument("--pt-spp", type=int, default=64)
+    p.add_argument("--no-pt", action="store_true")
     return p.parse_args()
 
 
@@ -116,6 +119,65 @@ def cpu_arm(a, mesh, rays, threads: int, steps: int, warmup: int):
             "sample": f"first {ns} rays of the workload (closest + any) vs the full M({a.tris}) mesh, "
                       f"oracle binned-SAH BVH2 (build {build_s:.1f} s, untimed)",
             "ms_per_step": 1e3 * total / len(times)}
+
+
+
+class _DevPtr:
+    """wraps a raw device pointer as a CUDA-array-interface object so torch can all-reduce it in place"""
+
+    def __init__(self, ptr, n_floats):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
+def pt_section(a, rank, world, local_rank, stream):
+    """secondary measurement: the path tracer on the cbox-matte scene (BASELINE.json configs[0] geometry at
+    1024x1024), sample-partitioned across ranks (rank g renders frames g, g+G, ...) with ONE NCCL all-reduce of
+    the SUM film followed by the fused resolve. Returns samples/s and Mrays/s (whole job)."""
+    import torch
+    import torch.distributed as dist
+    from vision_b200 import Context, scene_py, capi
+    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", dict(scene_py.CBOX_MATTE_OVERRIDES, resolution=[a.pt_res, a.pt_res]))
+    ctx = Context(local_rank)
+    ctx.set_stream(stream.cuda_stream)
+    ctx.upload_scene(sc)
+    w, h = sc.resolution
+    spp_rank = a.pt_spp
+    film = torch.as_tensor(_DevPtr(ctx.film_device_ptr(capi.VB_FILM_ACCUM), w * h * 4), device=torch.device("cuda", local_rank))
+
+    def run():
+        ctx.film_clear()
+        ctx.render_frames(rank, spp_rank, world, capi.VB_ACCUM_SUM)
+        if world > 1:
+            dist.all_reduce(film)
+        ctx.film_resolve(capi.VB_ACCUM_SUM, sc.exposure, sc.tonemap)
+
+    run()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 3
+    e0.record(stream)
+    for _ in range(reps):
+        run()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    st = ctx.render_stats()
+    t = torch.tensor([ms, float(st["closest"] + st["any"])], dtype=torch.float64, device=torch.device("cuda", local_rank))
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms, rays = float(tmax[0]), float(tsum[1])
+    else:
+        rays = float(t[1])
+    out_mean = float(torch.as_tensor(_DevPtr(ctx.film_device_ptr(capi.VB_FILM_OUTPUT), w * h * 4), device=torch.device("cuda", local_rank)).mean())
+    ctx.close()
+    samples = w * h * spp_rank * world
+    return {"scene": f"cbox matte {w}x{h}, {spp_rank} spp per GPU x {world} GPU(s), max depth 5", "ms": ms,
+            "samples_per_s": samples / (ms * 1e-3), "mrays_per_s": rays / (ms * 1e-3) / 1e6, "rays_per_sample": rays / samples,
+            "film_allreduce": "torch.distributed NCCL sum over the float4 film" if world > 1 else "none (1 GPU)",
+            "output_mean": out_mean}
 
 
 def main():
@@ -250,6 +312,11 @@ def main():
     value = total_rays_step * a.steps / (ms_total * 1e-3) / 1e6
     e2e_value = total_rays_step * e2e_steps / (e2e_ms * 1e-3) / 1e6
 
+    # free the microbench buffers, then the secondary path-tracing measurement (all ranks)
+    del d_rays, d_any, d_hits, d_occ, h_rays, h_hits_t, h_occ_t
+    torch.cuda.empty_cache()
+    pt = None if a.no_pt else pt_section(a, rank, world, local_rank, stream)
+
     if rank == 0:
         peaks = {}
         pk = ROOT / "MEASURED_PEAKS.json"
@@ -260,7 +327,7 @@ def main():
             peak = float(peaks.get("hbm_gbs", peak)); peak_src = "MEASURED_PEAKS.json hbm_gbs (burst copy)"
         npr, tpr = nodes_c / n, tris_c / n
         bytes_per_ray = 32 + 20 + 80 * npr + 48 * tpr
-        dur_ms = k_closest_ms / max(1, k_closest_n)
+        dur_ms = k_closest_ms / a.steps          # one trace_closest call (sort + traverse) per step
         achieved = bytes_per_ray * n / (dur_ms * 1e-3) / 1e9
         prof_traffic = None
         tf = ROOT / "profiles" / "traffic.json"
@@ -282,17 +349,19 @@ def main():
                     "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "vb_trace_closest = k_ray_keys + radix sort + k_ray_reorder + k_trace<closest> (timed together)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": prof_traffic, "peak_source": peak_src,
                          "bytes_per_ray": bytes_per_ray, "nodes_per_ray": npr, "tris_per_ray": tpr,
                          "kernel_ms": dur_ms, "rays_per_launch": n},
             "kernels": {"trace_closest": {"ms": dur_ms, "mrays_s": n / dur_ms / 1e3, "hit_frac": hit_frac},
-                        "trace_any": {"ms": k_any_ms / max(1, k_any_n), "mrays_s": n / (k_any_ms / max(1, k_any_n)) / 1e3,
+                        "trace_any": {"ms": k_any_ms / a.steps, "mrays_s": n / (k_any_ms / a.steps) / 1e3,
                                       "occluded_frac": occ_frac, "bytes_per_ray": bpa,
-                                      "achieved_gbs": bpa * n / (k_any_ms / max(1, k_any_n) * 1e-3) / 1e9}},
+                                      "achieved_gbs": bpa * n / (k_any_ms / a.steps * 1e-3) / 1e9}},
             "bvh": {"build_ms": bst["build_ms"], "nodes": bst["n_nodes"], "node_bytes": bst["node_bytes"],
                     "tri_bytes": bst["tri_bytes"]},
         }
+        if pt is not None:
+            line["path_tracer"] = pt
         if world == 1 and not a.no_cpu_baseline:
             cb = cpu_arm(a, mesh, rays, 0, 2, 1)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
