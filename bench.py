@@ -136,6 +136,7 @@ def pt_section(a, rank, world, local_rank, stream):
     import torch
     import torch.distributed as dist
     from vision_b200 import Context, scene_py, capi
+    from vision_b200.dist import frames_for_rank
     sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", dict(scene_py.CBOX_MATTE_OVERRIDES, resolution=[a.pt_res, a.pt_res]))
     ctx = Context(local_rank)
     ctx.set_stream(stream.cuda_stream)
@@ -146,7 +147,8 @@ def pt_section(a, rank, world, local_rank, stream):
 
     def run():
         ctx.film_clear()
-        ctx.render_frames(rank, spp_rank, world, capi.VB_ACCUM_SUM)
+        first, n_fr, stride = frames_for_rank(rank, world, spp_rank * world)      # rank g: frames g, g+G, ...
+        ctx.render_frames(first, n_fr, stride, capi.VB_ACCUM_SUM)
         if world > 1:
             dist.all_reduce(film)
         ctx.film_resolve(capi.VB_ACCUM_SUM, sc.exposure, sc.tonemap)
