@@ -10,7 +10,7 @@ n = int(sys.argv[2]) if len(sys.argv) > 2 else 1 << 24
 ctx = Context(0)
 mesh = synth.synth_mesh(tris, seed=1)
 rays = synth.synth_rays(n)
-mid = ctx.mesh_upload_soup(mesh); ctx.instances_set([{"mesh_id": mid}]); print(ctx.accel_build())
+mid = ctx.mesh_upload_soup(mesh); ctx.instances_set([{"mesh_id": mid}])
 d = {k: torch.from_numpy(v).cuda() for k, v in rays.items()}
 da = dict(d, tmax=d["tmax_any"])
 hits = None; occ = None
@@ -22,7 +22,11 @@ def run(tag):
     for _ in range(3):
         hits = ctx.trace_closest(d, hits); occ = ctx.trace_any(da, occ)
     c, _ = ctx.profile_get("trace_closest"); a, _ = ctx.profile_get("trace_any")
-    print(f"{tag}: closest {c/3:.2f} ms ({n/(c/3)/1e3:.0f} Mrays/s)  any {a/3:.2f} ms ({n/(a/3)/1e3:.0f} Mrays/s)", flush=True)
-for refill, tri in ((28, 10), (28, 12), (28, 14)):
-    ctx.set_option("trace.refill_thr", refill); ctx.set_option("trace.tri_thr", tri)
-    run(f"refill={refill} tri={tri}")
+    _, nn, nt = ctx.trace_closest(d, hits, counted=True)
+    print(f"{tag}: closest {c/3:.2f} ms ({n/(c/3)/1e3:.0f} Mrays/s)  any {a/3:.2f} ms ({n/(a/3)/1e3:.0f} Mrays/s) nodes/ray {nn/n:.1f} tris/ray {nt/n:.1f}", flush=True)
+for ml in (1,):
+    ctx.set_option("build.max_leaf", ml)
+    st = ctx.accel_build()
+    for bps in (8, 10):
+        ctx.set_option("trace.blocks_per_sm", bps)
+        run(f"max_leaf={ml} bps={bps}")

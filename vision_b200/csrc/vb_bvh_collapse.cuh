@@ -24,12 +24,12 @@ __device__ __forceinline__ uint32_t quant_exp(float extent) {
 }
 
 __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n_in, WorkItem *out, Counters *cnt,
-                                                  uint32_t T, BuildBufs b, vb_wide_node *nodes, float4 *tris_out) {
+                                                  uint32_t T, BuildBufs b, vb_wide_node *nodes, float4 *tris_out, uint32_t max_leaf) {
     uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= n_in) return;
     WorkItem it = in[w];
     auto tri_count = [&](uint32_t x) -> uint32_t { return x >= T - 1 ? 1u : b.last[x] - b.first[x] + 1u; };
-    auto leaf_like = [&](uint32_t x) -> bool { return tri_count(x) <= 3u; };
+    auto leaf_like = [&](uint32_t x) -> bool { return tri_count(x) <= max_leaf; };
 
     uint32_t c[8]; int n;
     if (leaf_like(it.bvh2)) { c[0] = it.bvh2; n = 1; }
@@ -219,7 +219,7 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     uint32_t n_items = 1;
     int levels = 0;
     while (n_items) {
-        k_collapse<<<(n_items + 127) / 128, 128, 0, st>>>(qin, n_items, qout, cnt.p, T, b, d_nodes, d_tris); launches++;
+        k_collapse<<<(n_items + 127) / 128, 128, 0, st>>>(qin, n_items, qout, cnt.p, T, b, d_nodes, d_tris, (uint32_t)std::min(3, std::max(1, ctx->opt_max_leaf))); launches++;
         VB_CHECK_LAUNCH();
         VB_CUDA(cudaMemcpyAsync(&hc, cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
         VB_CUDA(cudaStreamSynchronize(st));

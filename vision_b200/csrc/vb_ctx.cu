@@ -112,6 +112,7 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     std::string k(key);
     if (k == "trace.refill_thr") ctx->opt_refill_thr = (int)value;
     else if (k == "trace.tri_thr") ctx->opt_tri_thr = (int)value;
+    else if (k == "build.max_leaf") ctx->opt_max_leaf = (int)value;
     else if (k == "trace.sort_rays") ctx->opt_sort_rays = (int)value;
     else if (k == "trace.sort_min_rays") ctx->opt_sort_min_rays = std::max(1, (int)value);
     else if (k == "trace.blocks_per_sm") ctx->opt_blocks_per_sm = std::max(1, (int)value);

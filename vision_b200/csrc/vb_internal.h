@@ -69,6 +69,7 @@ struct vb_ctx {
     int sm_count = 148;
     // tunables (vb_ctx_set_option)
     int opt_refill_thr = 28, opt_tri_thr = 12, opt_blocks_per_sm = 8;
+    int opt_max_leaf = 1;
     int opt_sort_rays = 1, opt_sort_min_rays = 1 << 16;
     void *sort_buf = nullptr; size_t sort_bytes = 0;
     vb_pt_state *pt = nullptr;
