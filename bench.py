@@ -351,7 +351,7 @@ def main():
                     "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "vb_trace_closest = k_ray_keys + radix sort + k_ray_reorder + k_trace<closest> (timed together)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "vb_trace_closest = k_ray_keys + 3-pass radix sort + k_trace<closest> (timed together; k_trace is 95 % of it)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": prof_traffic, "peak_source": peak_src,
                          "bytes_per_ray": bytes_per_ray, "nodes_per_ray": npr, "tris_per_ray": tpr,
                          "kernel_ms": dur_ms, "rays_per_launch": n},

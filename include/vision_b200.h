@@ -75,14 +75,14 @@ typedef struct vb_build_opts {
 } vb_build_opts;
 typedef struct vb_build_stats {
     uint64_t n_triangles;      /* flattened world-space triangles */
-    uint64_t n_nodes;          /* 80-byte wide nodes */
+    uint64_t n_nodes;          /* wide nodes: 80-byte payload in 96-byte, 32-byte-aligned slots */
     uint64_t node_bytes, tri_bytes;
     double build_ms;           /* device time of the whole build */
     float scene_lo[3], scene_hi[3];
 } vb_build_stats;
 /* flattens instances to world space, builds the compressed 8-wide BVH on the GPU */
 VB_API int vb_accel_build(vb_ctx *ctx, const vb_build_opts *opts, vb_build_stats *out);
-/* copies the built structure to host (test/diagnostic surface): nodes = n_nodes*80 bytes,
+/* copies the built structure to host (test/diagnostic surface): nodes = n_nodes*96 bytes,
  * tris = n_triangles*48 bytes (float4 v0|prim, e1|inst, e2|0). Either pointer may be NULL. */
 VB_API int vb_accel_download(vb_ctx *ctx, void *nodes, void *tris);
 

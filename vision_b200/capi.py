@@ -202,7 +202,7 @@ class Context:
                 "scene_lo": list(st.scene_lo), "scene_hi": list(st.scene_hi)}
 
     def accel_download(self, n_nodes: int, n_tris: int):
-        nodes = np.empty((n_nodes, 80), np.uint8)
+        nodes = np.empty((n_nodes, 96), np.uint8)
         tris = np.empty((n_tris, 12), np.float32)
         self._check(self.lib.vb_accel_download(self.h, _ptr(nodes), _ptr(tris)), "vb_accel_download")
         return nodes, tris

@@ -84,6 +84,7 @@ __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n
     uint32_t out_base = k_inner ? atomicAdd(&cnt->next_items, k_inner) : 0u;
 
     vb_wide_node N;
+    N.pad[0] = N.pad[1] = N.pad[2] = N.pad[3] = 0u;
     // quantisation frame = node box grown by 1/64 of its extent per side, so that the 2^-6 grid-unit
     // inflation of the child boxes below never clamps at 0/255 (see vb_qf in vb_trace.cuh)
     {
@@ -128,7 +129,7 @@ __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n
     const uint4 *src = reinterpret_cast<const uint4 *>(&N);
     uint4 *dst = reinterpret_cast<uint4 *>(nodes + it.wide);
 #pragma unroll
-    for (int q = 0; q < 5; ++q) dst[q] = src[q];
+    for (int q = 0; q < VB_NODE_U4; ++q) dst[q] = src[q];
 }
 
 template <class T> struct DevBuf {
@@ -247,7 +248,7 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     ctx->accel.n_nodes = hc.n_nodes; ctx->accel.n_tris = T; ctx->accel.built = true;
 
     vb_build_stats &s = ctx->build_stats;
-    s.n_triangles = T; s.n_nodes = hc.n_nodes; s.node_bytes = (uint64_t)hc.n_nodes * 80; s.tri_bytes = (uint64_t)T * 48;
+    s.n_triangles = T; s.n_nodes = hc.n_nodes; s.node_bytes = (uint64_t)hc.n_nodes * sizeof(vb_wide_node); s.tri_bytes = (uint64_t)T * 48;
     s.build_ms = ms;
     for (int a = 0; a < 3; ++a) { s.scene_lo[a] = ord2f(hs[a]); s.scene_hi[a] = ord2f(hs[3 + a]); }
     ctx->prof["bvh_build"].ms += ms; ctx->prof["bvh_build"].launches += launches;

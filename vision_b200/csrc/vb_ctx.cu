@@ -212,7 +212,7 @@ int vb_accel_download(vb_ctx *ctx, void *nodes, void *tris) {
     if (!ctx->accel.built) return ctx->fail(VB_ERR_STATE, "vb_accel_download: accel not built");
     cudaSetDevice(ctx->device);
     VB_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (nodes && ctx->accel.n_nodes) VB_CUDA(cudaMemcpy(nodes, ctx->accel.nodes, ctx->accel.n_nodes * 80, cudaMemcpyDeviceToHost));
+    if (nodes && ctx->accel.n_nodes) VB_CUDA(cudaMemcpy(nodes, ctx->accel.nodes, ctx->accel.n_nodes * sizeof(vb_wide_node), cudaMemcpyDeviceToHost));
     if (tris && ctx->accel.n_tris) VB_CUDA(cudaMemcpy(tris, ctx->accel.tris, ctx->accel.n_tris * 48, cudaMemcpyDeviceToHost));
     return VB_OK;
 }

@@ -14,6 +14,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                                                          uint32_t *h_inst, uint32_t *h_prim, float *h_u, float *h_v, float *h_t) {
     __shared__ uint2 s_stack_all[VB_SM_STACK * PT_BLOCK];
     uint2 *s_stack = s_stack_all + threadIdx.x;
+    const uint32_t mg = vb_qf_magic_init();
     uint32_t pix = blockIdx.x * PT_BLOCK + threadIdx.x;
     uint32_t n_pix = S.width * S.height;
     uint32_t c_closest = 0, c_any = 0, c_vert = 0, dummy0 = 0, dummy1 = 0;
@@ -29,7 +30,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
             VbHit hit;
             // the reference traces the primary ray in rt_geom and again as bounce 0 of Li with the
             // same ray; the second result is identical, so it is reused (counted once)
-            vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1);
+            vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1, mg);
             c_closest++;
             if (DUMP_PRIMARY) {
                 h_inst[pix] = hit.inst; h_prim[pix] = hit.prim; h_u[pix] = hit.u; h_v[pix] = hit.v; h_t[pix] = hit.t;
@@ -42,7 +43,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
             const uint32_t max_depth = S.params.max_depth;
             bool have_hit = true;
             for (uint32_t bounces = 0; bounces < max_depth; ++bounces) {
-                if (!have_hit) { vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1); c_closest++; }
+                if (!have_hit) { vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1, mg); c_closest++; }
                 have_hit = false;
                 if (hit.inst == VB_INVALID_ID) break;
                 Interaction it = compute_surface_interaction(S, hit.inst, hit.prim, hit.u, hit.v, true);
@@ -82,7 +83,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                 }
                 VbRay shadow = spawn_ray_to(it, ls.p_light);
                 VbHit sh;
-                bool occluded = vb_traverse<true, false>(S.accel, shadow, sh, s_stack, PT_BLOCK, dummy0, dummy1);
+                bool occluded = vb_traverse<true, false>(S.accel, shadow, sh, s_stack, PT_BLOCK, dummy0, dummy1, mg);
                 c_any++;
                 // material
                 const vb_material_rec &m = S.materials[it.mat_id];

@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
     __shared__ uint2 s_stack_all[VB_SM_STACK * TRACE_BLOCK];
     uint2 *s_stack = s_stack_all + threadIdx.x;
     uint2 l_stack[VB_LOCAL_STACK];
+    const uint32_t mg = vb_qf_magic_init();
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     uint32_t nn = 0, nt = 0;
@@ -57,10 +58,10 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
             if (!active) {
                 idx = base + __popc(idle & lt_mask);
                 if (idx < n) {
-                    if (RS) {       // rays pre-sorted into AoS by k_reorder; results go back to slot perm[idx]
+                    if (RS) {       // sorted order: gather ray perm[idx] from the AoS copy (one 32-byte sector); results go back to that slot
+                        idx = __ldg(perm + idx);
                         float4 a = __ldg(RS + 2 * idx), b = __ldg(RS + 2 * idx + 1);
                         r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
-                        idx = __ldg(perm + idx);
                     } else {
                         r.ox = __ldg(R.ox + idx); r.oy = __ldg(R.oy + idx); r.oz = __ldg(R.oz + idx); r.tmin = __ldg(R.tmin + idx);
                         r.dx = __ldg(R.dx + idx); r.dy = __ldg(R.dy + idx); r.dz = __ldg(R.dz + idx); r.tmax = __ldg(R.tmax + idx);
@@ -105,10 +106,10 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                 }
                 uint32_t slot = (bit - 24u) ^ (oct_inv4 & 0xffu);
                 uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot) & 0xffu);
-                const uint4 *np = A.nodes + (size_t)(G.x + rel) * 5;
-                uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+                uint4 n0, n1, n2, n3, n4;
+                vb_load_node(A.nodes, G.x + rel, n0, n1, n2, n3, n4);
                 if (COUNT) nn++;
-                uint32_t hm = vb_node_hits(n0, n1, n2, n3, n4, r, idx_, idy_, idz_, oct_inv4, tmax);
+                uint32_t hm = vb_node_hits(n0, n1, n2, n3, n4, r, idx_, idy_, idz_, oct_inv4, tmax, mg);
                 G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
                 if (hm & 0x00ffffffu) {
                     if (Tg.y) Td = Tg;                     // at most one of them was occupied (has_node)
@@ -174,26 +175,18 @@ __global__ void __launch_bounds__(256) k_ray_keys(RaysDev R, uint32_t n, float3 
     float ox = __ldg(R.ox + i), oy = __ldg(R.oy + i), oz = __ldg(R.oz + i);
     float dx = __ldg(R.dx + i), dy = __ldg(R.dy + i), dz = __ldg(R.dz + i);
     // fminf/fmaxf drop NaN operands, so NaN origins land in cell 0
-    uint32_t ix = (uint32_t)fminf(fmaxf((ox - lo.x) * inv_ext.x * 256.f, 0.f), 255.f);
-    uint32_t iy = (uint32_t)fminf(fmaxf((oy - lo.y) * inv_ext.y * 256.f, 0.f), 255.f);
-    uint32_t iz = (uint32_t)fminf(fmaxf((oz - lo.z) * inv_ext.z * 256.f, 0.f), 255.f);
+    uint32_t ix = (uint32_t)fminf(fmaxf((ox - lo.x) * inv_ext.x * 128.f, 0.f), 127.f);
+    uint32_t iy = (uint32_t)fminf(fmaxf((oy - lo.y) * inv_ext.y * 128.f, 0.f), 127.f);
+    uint32_t iz = (uint32_t)fminf(fmaxf((oz - lo.z) * inv_ext.z * 128.f, 0.f), 127.f);
     uint32_t oct = (dx < 0.f ? 4u : 0u) | (dy < 0.f ? 2u : 0u) | (dz < 0.f ? 1u : 0u);
+    // 24-bit key = 3 onesweep passes: 21-bit Morton code (128^3 cells; with 16 Mi rays that is still ~1 ray
+    // per key) + octant
     keys[i] = (((expand8(ix) << 2) | (expand8(iy) << 1) | expand8(iz)) << 3) | oct;
     vals[i] = i;
     // SoA -> AoS copy (streaming) so that the post-sort gather touches ONE 32-byte sector per ray
     aos[2 * (size_t)i] = make_float4(ox, oy, oz, __ldg(R.tmin + i));
     aos[2 * (size_t)i + 1] = make_float4(dx, dy, dz, __ldg(R.tmax + i));
 }
-__global__ void __launch_bounds__(256) k_ray_reorder(const float4 *__restrict__ aos, uint32_t n, const uint32_t *__restrict__ perm,
-                                                     float4 *RS) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    uint32_t j = __ldg(perm + i);
-    float4 a = __ldg(aos + 2 * (size_t)j), b = __ldg(aos + 2 * (size_t)j + 1);
-    RS[2 * (size_t)i] = a;
-    RS[2 * (size_t)i + 1] = b;
-}
-
 int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out, uint8_t *occ, vb_mem occ_mem,
               bool any, uint64_t *cnt_nodes, uint64_t *cnt_tris) {
     if (!ctx) return VB_ERR_INVALID;
@@ -245,12 +238,12 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
     bool do_sort = ctx->opt_sort_rays && n >= (uint64_t)ctx->opt_sort_min_rays && n < (1ull << 32);
     uint64_t launches = 1;
     size_t cub_bytes = 0;
-    uint32_t *k0 = nullptr, *k1 = nullptr, *v0 = nullptr, *v1 = nullptr; float4 *d_rs = nullptr, *d_aos = nullptr; void *cub_tmp = nullptr;
+    uint32_t *k0 = nullptr, *k1 = nullptr, *v0 = nullptr, *v1 = nullptr; float4 *d_aos = nullptr; void *cub_tmp = nullptr;
     if (do_sort) {
         cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
-        VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk, dv, (int)n, 0, 27, st));
+        VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk, dv, (int)n, 0, 24, st));
         size_t nb = ((n * 4 + 255) & ~255ull);
-        size_t total = 4 * nb + 64 * n + cub_bytes + 256;
+        size_t total = 4 * nb + 32 * n + cub_bytes + 256;
         if (total > ctx->sort_bytes) {
             if (ctx->sort_buf) cudaFree(ctx->sort_buf);
             ctx->sort_buf = nullptr; ctx->sort_bytes = 0;
@@ -259,7 +252,7 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
         }
         char *sb = (char *)ctx->sort_buf;
         k0 = (uint32_t *)sb; k1 = (uint32_t *)(sb + nb); v0 = (uint32_t *)(sb + 2 * nb); v1 = (uint32_t *)(sb + 3 * nb);
-        d_rs = (float4 *)(sb + 4 * nb); d_aos = (float4 *)(sb + 4 * nb + 32 * n); cub_tmp = sb + 4 * nb + 64 * n;
+        d_aos = (float4 *)(sb + 4 * nb); cub_tmp = sb + 4 * nb + 32 * n;
         cub_tmp = (void *)(((uintptr_t)cub_tmp + 255) & ~(uintptr_t)255);
     }
     ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
@@ -271,12 +264,11 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
         unsigned g2 = (unsigned)((n + 255) / 256);
         k_ray_keys<<<g2, 256, 0, st>>>(R, (uint32_t)n, lo, ie, k0, v0, d_aos);
         cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
-        cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)n, 0, 27, st);
+        cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)n, 0, 24, st);
         if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }
         perm = dv.Current();
-        k_ray_reorder<<<g2, 256, 0, st>>>(d_aos, (uint32_t)n, perm, d_rs);
-        RS = d_rs;
-        launches += 6;
+        RS = d_aos;                 // k_trace gathers ray perm[i] itself: no separate reorder pass
+        launches += 5;
     }
     if (any) {
         if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm);

@@ -51,42 +51,71 @@ __device__ __forceinline__ bool vb_intersect_triangle(const VbRay &r, float4 a, 
     return t > r.tmin && t < tmax;
 }
 
+// node fetch: 96-byte slot, 32-byte aligned -> 2 x ld.global.nc.v8 (256-bit, sm_100+) + 1 x v4
+#ifndef VB_NODE_U4
+#define VB_NODE_U4 6
+#endif
+__device__ __forceinline__ void vb_ld256(const uint4 *p, uint4 &a, uint4 &b) {
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(p));
+}
+__device__ __forceinline__ void vb_load_node(const uint4 *nodes, uint32_t index, uint4 &n0, uint4 &n1, uint4 &n2, uint4 &n3, uint4 &n4) {
+    const uint4 *np = nodes + (size_t)index * VB_NODE_U4;
+    vb_ld256(np, n0, n1);
+    vb_ld256(np + 2, n2, n3);
+    n4 = __ldg(np + 4);
+}
+
 __device__ __forceinline__ float vb_safe_rcp(float d) {
     return 1.0f / (fabsf(d) > 1e-20f ? d : copysignf(1e-20f, d));
 }
 
 __device__ __forceinline__ uint32_t vb_byte(uint32_t w, int i) { return (w >> (8 * i)) & 0xffu; }
 
-// byte j of w -> float (32768 + byte) with ONE PRMT (no I2F): bits = 0x47000000 | byte << 8.
-// The 32768 bias is folded into the FMA addend per node; its rounding error (<= 2^-9 grid
-// units) is covered by the builder inflating every quantised child box by 2^-6 grid units.
-// The 0x47000000 operand is kept in a register (opaque to the compiler) so that the SELECTOR is
-// the PRMT immediate; otherwise ptxas materialises one selector register per PRMT.
-__device__ __forceinline__ uint32_t vb_qf_magic() {
-    uint32_t m;
-    asm("mov.b32 %0, 0x47000000;" : "=r"(m));
-    return m;
+// Quantised byte -> float, balanced over the two math pipes of an SMSP (each issues one warp
+// instruction every 2 cycles; the box test was ALU-pipe bound - profiles/r1_trace_v4_leaf1_ncu_full.txt):
+//   ONE PRMT (alu pipe) builds a half2 from two bytes: 0x6400 | byte = fp16(1024 + byte), exact;
+//   HADD2.F32 (fma pipe) widens each half to fp32. The 1024 bias is folded into the FMA addend per
+//   node; its rounding error is covered by the builder inflating every child box by 2^-6 grid units.
+// The 0x64646464 operand must live in a REGISTER so that the SELECTOR is the PRMT immediate (SASS
+// PRMT has one non-register operand slot). ptxas constant-folds any "mov r, imm" and then
+// re-materialises one selector register per PRMT, so the value is read back from shared memory
+// once per kernel, which ptxas cannot fold. Every kernel that traverses calls vb_qf_magic_init() first.
+#define VB_Q_BIAS 1024.f
+__device__ __forceinline__ uint32_t vb_qf_magic_init() {
+    __shared__ uint32_t s_vb_magic;
+    if (threadIdx.x == 0) s_vb_magic = 0x64646464u;
+    __syncthreads();
+    return *(volatile uint32_t *)&s_vb_magic;
+}
+// a << (b & 31): SHF.L.W, so a packed byte field can be used as the shift amount without masking
+__device__ __forceinline__ uint32_t vb_shl_wrap(uint32_t a, uint32_t b) {
+    uint32_t d;
+    asm("shf.l.wrap.b32 %0, 0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));   // high word of (a:0) << n
+    return d;
 }
 template <int J>
 __device__ __forceinline__ float vb_qf(uint32_t w, uint32_t magic) {
-    uint32_t d;
-    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(magic), "n"(0x7404 | (J << 4)));
-    return __uint_as_float(d);
+    uint32_t d;      // bytes (J&~1, J|1) of w as two fp16 values 1024+byte; identical PRMTs are CSE'd per pair
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(magic), "n"(J < 2 ? 0x4140 : 0x4342));
+    float f;
+    if (J & 1) asm("{ .reg .b16 lo, hi; mov.b32 {lo, hi}, %1; cvt.f32.f16 %0, hi; }" : "=f"(f) : "r"(d));
+    else asm("{ .reg .b16 lo, hi; mov.b32 {lo, hi}, %1; cvt.f32.f16 %0, lo; }" : "=f"(f) : "r"(d));
+    return f;
 }
 
 // Tests the 8 quantised child boxes of one node; returns the 32-bit hit mask
 // (bits 31..24: internal children in octant order, bits 23..0: triangles).
 __device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
                                                  const uint4 n4, const VbRay &r, float idx, float idy, float idz,
-                                                 uint32_t oct_inv4, float tmax) {
+                                                 uint32_t oct_inv4, float tmax, const uint32_t mg) {
     float adjx = __uint_as_float((n0.w & 0xffu) << 23) * idx;
     float adjy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idy;
     float adjz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idz;
-    float orx = fmaf(-32768.f, adjx, (__uint_as_float(n0.x) - r.ox) * idx);
-    float ory = fmaf(-32768.f, adjy, (__uint_as_float(n0.y) - r.oy) * idy);
-    float orz = fmaf(-32768.f, adjz, (__uint_as_float(n0.z) - r.oz) * idz);
+    float orx = fmaf(-VB_Q_BIAS, adjx, (__uint_as_float(n0.x) - r.ox) * idx);
+    float ory = fmaf(-VB_Q_BIAS, adjy, (__uint_as_float(n0.y) - r.oy) * idy);
+    float orz = fmaf(-VB_Q_BIAS, adjz, (__uint_as_float(n0.z) - r.oz) * idz);
     uint32_t hitmask = 0;
-    const uint32_t mg = vb_qf_magic();
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         uint32_t meta4 = h ? n1.w : n1.z;
@@ -106,7 +135,8 @@ __device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1,
             float tnz = fmaf(vb_qf<J>(nz, mg), adjz, orz), tfz = fmaf(vb_qf<J>(fz, mg), adjz, orz);              \
             float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tmin));                                     \
             float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));                                       \
-            if (cmin <= cmax) hitmask |= vb_byte(child_bits4, J) << vb_byte(bit_index4, J);              \
+            /* byte J of child_bits4 with one PRMT; the shift amount needs no masking: shl wraps (bit_index < 32) */ \
+            if (cmin <= cmax) hitmask |= vb_shl_wrap(__byte_perm(child_bits4, 0u, 0x4440 | J), bit_index4 >> (8 * J)); \
         }
         VB_CHILD(0) VB_CHILD(1) VB_CHILD(2) VB_CHILD(3)
 #undef VB_CHILD
@@ -125,7 +155,7 @@ __device__ __forceinline__ void vb_commit_hit(VbHit &hit, float &tmax, float4 a,
 // s_stack points at this thread's column of the shared stack: entry e lives at s_stack[e * stride]
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool vb_traverse(const VbAccelView &A, VbRay r, VbHit &hit, uint2 *s_stack, int stride,
-                                            uint32_t &n_nodes, uint32_t &n_tris) {
+                                            uint32_t &n_nodes, uint32_t &n_tris, const uint32_t mg) {
     uint2 l_stack[VB_LOCAL_STACK];
     int sp = 0;
     float idx = vb_safe_rcp(r.dx), idy = vb_safe_rcp(r.dy), idz = vb_safe_rcp(r.dz);
@@ -150,10 +180,10 @@ __device__ __forceinline__ bool vb_traverse(const VbAccelView &A, VbRay r, VbHit
             }
             uint32_t slot = (bit - 24u) ^ (oct_inv4 & 0xffu);
             uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot) & 0xffu);
-            const uint4 *np = A.nodes + (size_t)(G.x + rel) * 5;
-            uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+            uint4 n0, n1, n2, n3, n4;
+            vb_load_node(A.nodes, G.x + rel, n0, n1, n2, n3, n4);
             if (COUNT) n_nodes++;
-            uint32_t hm = vb_node_hits(n0, n1, n2, n3, n4, r, idx, idy, idz, oct_inv4, tmax);
+            uint32_t hm = vb_node_hits(n0, n1, n2, n3, n4, r, idx, idy, idz, oct_inv4, tmax, mg);
             G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
             Tg = make_uint2(n1.y, hm & 0x00ffffffu);
         }
