@@ -32,7 +32,7 @@ enum { VB_MAT_DIFFUSE = 0, VB_MAT_MIRROR = 1, VB_MAT_GLASS = 2, VB_MAT_METAL = 3
        VB_MAT_PRINCIPLED = 5, VB_MAT_BLACK_BODY = 6 };
 typedef struct vb_material_rec {
     uint32_t type;
-    uint32_t flags;            /* bit0: has sigma (Oren-Nayar), bit1: remapping_roughness */
+    uint32_t flags;            /* bit0: has sigma (Oren-Nayar, diffuse.cpp:26-29), bit1: remapping_roughness */
     uint32_t pad[2];
     vb_slot color;             /* diffuse.cpp:23, glass/mirror color, substrate diff */
     vb_slot roughness;         /* xy */
@@ -40,9 +40,30 @@ typedef struct vb_material_rec {
     vb_slot ior;               /* x; glass */
     vb_slot sigma;             /* diffuse Oren-Nayar */
     float eta[4], k[4];        /* metal: complex ior at the 3 sRGB peak wavelengths */
-    float params[16];          /* principled: metallic, spec_tint, anisotropic, sheen, ... */
+    float params[16];          /* [0] anisotropic (mirror/glass/metal/substrate); principled: metallic, spec_tint, ... */
 } vb_material_rec;
 VB_API int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n);
+
+/* ---- energy-compensation LUTs: MaterialLut (reference src/base/scattering/material.cpp:14-27) ------ */
+/* The reference uploads the tables of src/base/scattering/precomputed_table.h as float textures and
+ * samples them with normalised coordinates; here they are plain float arrays, x fastest, sampled in
+ * software (linear, clamp). PURE_REFLECTION: 32x32x1, 1 channel (lobe.cpp:716-735);
+ * DIELECTRIC / DIELECTRIC_INV: 32x32x32, 2 channels (lobe.cpp:253-306). A missing table = no compensation. */
+enum { VB_LUT_PURE_REFLECTION = 0, VB_LUT_DIELECTRIC = 1, VB_LUT_DIELECTRIC_INV = 2, VB_LUT_COUNT = 3 };
+VB_API int vb_luts_set(vb_ctx *ctx, int which, const float *data, uint32_t nx, uint32_t ny, uint32_t nz, uint32_t channels);
+
+/* ---- mediums (reference src/render_core/medium/homogeneous.cpp:11-70) ------------------------------ */
+/* index = the id stored in vb_instance.inside_medium / outside_medium and vb_camera.medium_id; only
+ * consulted when vb_pt_params.process_mediums != 0 */
+enum { VB_MEDIUM_HOMOGENEOUS = 0 };
+typedef struct vb_medium_rec {
+    uint32_t type;
+    float g;                   /* Henyey-Greenstein g, clamped to +-0.99 by the host */
+    float scale;
+    float pad;
+    float sigma_a[4], sigma_s[4];
+} vb_medium_rec;
+VB_API int vb_mediums_set(vb_ctx *ctx, const vb_medium_rec *med, uint32_t n);
 
 /* ---- lights (reference src/render_core/light/<name>.cpp) + alias tables (warper/alias.h:86-122) ---- */
 enum { VB_LIGHT_AREA = 0, VB_LIGHT_POINT = 1, VB_LIGHT_SPOT = 2, VB_LIGHT_ENV = 3 };

@@ -43,6 +43,12 @@ void vo_scene_set_textures(void *h, const vb_texture *t, uint32_t n) {
         s.textures[i].texels.assign(p, p + (size_t)t[i].width * t[i].height);
     }
 }
+void vo_scene_set_lut(void *h, int which, const float *data, uint32_t nx, uint32_t ny, uint32_t nz, uint32_t ch) {
+    Lut &l = ((Scene *)h)->luts[which];
+    l.nx = nx; l.ny = ny; l.nz = nz; l.channels = ch;
+    l.data.assign(data, data + (size_t)nx * ny * nz * ch);
+}
+void vo_scene_set_mediums(void *h, const vb_medium_rec *m, uint32_t n) { ((Scene *)h)->mediums.assign(m, m + n); }
 void vo_scene_set_camera(void *h, const vb_camera *c) { ((Scene *)h)->camera = *c; }
 void vo_scene_set_integrator(void *h, const vb_pt_params *p) { ((Scene *)h)->params = *p; }
 void vo_scene_build(void *h, int threads, int brute) {
@@ -126,6 +132,8 @@ void vo_primary_hits(void *h, uint32_t w, uint32_t hgt, uint32_t frame, uint32_t
 uint32_t vo_tea4(uint32_t a, uint32_t b) { return tea4(a, b); }
 float vo_lcg(uint32_t *state) { return lcg(*state); }
 void vo_sincos_2pi(float u, float *s, float *c) { sincos_2pi(u, *s, *c); }
+float vo_vexp(float x) { return vexp(x); }
+float vo_vlog(float x) { return vlog(x); }
 void vo_offset_ray_origin(const float *p, const float *n, float *out) {
     float3 r = offset_ray_origin({p[0], p[1], p[2]}, {n[0], n[1], n[2]});
     out[0] = r.x; out[1] = r.y; out[2] = r.z;

@@ -3,6 +3,7 @@
 // for the CUDA megakernel (vision_b200/csrc/vb_pt.cu), which mirrors it under -fmad=false.
 #include "vo_pt.h"
 #include <cassert>
+#include <limits>
 
 namespace vo {
 
@@ -31,6 +32,36 @@ void sincos_2pi(float u, float &s, float &c) {
     else if (iq == 1) { s = cp; c = -sp; }
     else if (iq == 2) { s = -sp; c = -cp; }
     else { s = -cp; c = sp; }
+}
+
+// exp / log with a fixed operation sequence (cephes expf/logf polynomials, plain mul/add + the
+// fmaf written below) so that medium transmittance and free-flight sampling take bit-identical
+// values on host and device; libm and CUDA's expf/logf differ in the last ulp.
+float vexp(float x) {
+    if (!(x > -87.0f)) return x != x ? x : 0.0f;
+    if (x > 88.0f) return std::numeric_limits<float>::infinity();
+    float n = std::floor(x * 1.44269504088896341f + 0.5f);
+    float r = std::fmaf(n, -0.693359375f, x);
+    r = std::fmaf(n, 2.12194440e-4f, r);
+    float z = r * r;
+    float p = ((((1.9875691500e-4f * r + 1.3981999507e-3f) * r + 8.3334519073e-3f) * r + 4.1665795894e-2f) * r + 1.6666665459e-1f) * r + 5.0000001201e-1f;
+    float y = p * z + r + 1.0f;
+    return u2f(f2u(y) + ((uint32_t)(int32_t)n << 23));       // y in [0.7, 1.42): scale by 2^n (|n| <= 127)
+}
+float vlog(float x) {
+    if (!(x > 0.0f)) return x == 0.0f ? -std::numeric_limits<float>::infinity() : std::numeric_limits<float>::quiet_NaN();
+    uint32_t b = f2u(x);
+    int32_t e = (int32_t)((b >> 23) & 0xffu) - 126;
+    float m = u2f((b & 0x007fffffu) | 0x3f000000u);            // [0.5, 1)
+    if (m < 0.70710678118654752440f) { e -= 1; m = m + m - 1.0f; } else { m = m - 1.0f; }
+    float z = m * m;
+    float y = ((((((((7.0376836292e-2f * m - 1.1514610310e-1f) * m + 1.1676998740e-1f) * m - 1.2420140846e-1f) * m + 1.4249322787e-1f) * m
+                 - 1.6668057665e-1f) * m + 2.0000714765e-1f) * m - 2.4999993993e-1f) * m + 3.3333331174e-1f) * m * z;
+    float fe = (float)e;
+    y = y + -2.12194440e-4f * fe;
+    y = y + -0.5f * z;
+    float r = m + y;
+    return r + 0.693359375f * fe;
 }
 
 // Waechter & Binder (Ray Tracing Gems ch.6) integer-ULP offset; ocarina absent.
@@ -84,6 +115,8 @@ struct Interaction {
     float prim_area = 0.f;
     uint32_t prim_id = VB_INVALID_ID, mat_id = VB_INVALID_ID, light_id = VB_INVALID_ID;
     uint32_t inside = VB_INVALID_ID, outside = VB_INVALID_ID;
+    bool has_phase = false;        // medium interaction (Interaction::init_phase, interaction.cpp:58-63)
+    float g = 0.f;
 };
 
 // bilinear, wrap addressing, normalised uv (SURVEY A1 texture row)

@@ -25,6 +25,7 @@ struct MeshData {
 };
 
 struct Texture { std::vector<float4> texels; uint32_t w = 0, h = 0; };
+struct Lut { std::vector<float> data; uint32_t nx = 0, ny = 0, nz = 0, channels = 0; };
 
 struct InstanceX {                 // instance + derived normal matrix
     vb_instance rec;
@@ -42,6 +43,8 @@ struct Scene {
     std::vector<vb_alias_entry> alias_table;
     std::vector<float> alias_func;
     std::vector<Texture> textures;
+    Lut luts[VB_LUT_COUNT];
+    std::vector<vb_medium_rec> mediums;
     vb_camera camera{};
     vb_pt_params params{};
     Accel accel;
@@ -63,6 +66,8 @@ inline float lcg(uint32_t &state) {
     return (float)(state & 0x00ffffffu) * (1.0f / 16777216.0f);
 }
 void sincos_2pi(float u, float &s, float &c);
+float vexp(float x);
+float vlog(float x);
 float3 offset_ray_origin(float3 p, float3 n);
 
 }  // namespace vo

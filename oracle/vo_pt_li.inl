@@ -148,67 +148,55 @@ inline LightEval evaluate_hit_wi(const Scene &sc, float3 ref_pos, const Interact
     return ev;
 }
 
-struct ScatterEval { float3 f{0, 0, 0}; float pdf = 0.f; uint32_t flags = 1; };
-struct BSDFSample { ScatterEval eval; float3 wi{0, 0, 0}; float eta = 1.f; };
-constexpr uint32_t FlagReflection = 1u << 1, FlagTransmission = 1u << 2, FlagDiffuse = 1u << 3;
-
-struct DiffuseLobe { float3 kr; Frame frame; };
-
-// reference lobe.cpp:53-63 (evaluate_impl), bxdf.cpp:34-46 (safe_evaluate), bxdf.h:82-96 (Lambert)
-inline ScatterEval diffuse_evaluate(const DiffuseLobe &lb, float3 world_wo, float3 world_wi) {
-    float3 wo = lb.frame.to_local(world_wo), wi = lb.frame.to_local(world_wi);
-    ScatterEval se;
-    bool s = wo.z * wi.z > 0.f;                                   // same_hemisphere
-    se.f = s ? lb.kr * InvPi : float3{0, 0, 0};
-    se.pdf = s ? std::fabs(wi.z) * InvPi : 0.f;                   // cosine_hemisphere_PDF(abs_cos_theta)
-    se.flags = FlagDiffuse | FlagReflection;
-    se.f = se.f * std::fabs(wi.z);
-    return se;
-}
-// reference bxdf.cpp:48-52 + warp.h:23-40
-inline float3 diffuse_sample_wi(const DiffuseLobe &lb, float3 world_wo, float2 u) {
-    float3 wo = lb.frame.to_local(world_wo);
-    float r = std::sqrt(u.x), s, c;
-    sincos_2pi(u.y, s, c);
-    float dx = r * c, dy = r * s;
-    float z = std::sqrt(std::max(0.0f, 1.0f - dx * dx - dy * dy));
-    if (wo.z < 0.f) z = -z;
-    return lb.frame.to_world(float3{dx, dy, z});
-}
-
-// MaterialEvaluator (individual_ns branch), reference material.cpp:132-142,163-175
-struct Evaluator {
-    uint32_t type = VB_MAT_DIFFUSE;
-    DiffuseLobe diffuse;
-    float3 ng;
-    ScatterEval evaluate(float3 wo, float3 wi) const {
-        ScatterEval se = diffuse_evaluate(diffuse, wo, wi);
-        bool same = dot(wo, ng) * dot(wi, ng) > 0.f;
-        bool is_trans = (se.flags & FlagTransmission) != 0;
-        if (same == is_trans) se.pdf = 0.f;
-        return se;
-    }
-    BSDFSample sample(float3 wo, Sampler &sampler) const {
-        BSDFSample bs;
-        float2 u = sampler.next_2d();
-        bs.wi = diffuse_sample_wi(diffuse, wo, u);
-        bs.eval = evaluate(wo, bs.wi);
-        bs.eta = 1.f;
-        return bs;
-    }
-};
-
-inline Evaluator create_evaluator(const Scene &sc, const Interaction &it) {
-    Evaluator ev;
-    const vb_material_rec &m = sc.materials[it.mat_id];
-    ev.type = m.type;
-    ev.ng = it.ng;
-    ev.diffuse.frame = it.shading;
-    ev.diffuse.kr = (m.type == VB_MAT_DIFFUSE) ? eval_slot3(sc, m.color, it.uv) : float3{0, 0, 0};
-    return ev;
-}
+}  // namespace
+}  // namespace vo
+#include "vo_bsdf.inl"
+namespace vo {
+namespace {
 
 inline float mis_weight(float f, float g) { return (1.0f * f) / (1.0f * f + 1.0f * g); }   // warp.h:148-153,187-199
+
+// ---- homogeneous medium, reference render_core/medium/homogeneous.cpp:30-70 ----
+inline float3 medium_sigma_t(const vb_medium_rec &m) {
+    return float3{m.sigma_a[0] + m.sigma_s[0], m.sigma_a[1] + m.sigma_s[1], m.sigma_a[2] + m.sigma_s[2]} * m.scale;
+}
+inline float3 medium_Tr(const vb_medium_rec &m, float t) {
+    float3 st = medium_sigma_t(m);
+    float tt = std::min(RayTMax, t);
+    return {vexp(-st.x * tt), vexp(-st.y * tt), vexp(-st.z * tt)};
+}
+// Geometry::Tr (geometry.cpp:187-199) for a ray inside medium `id`
+inline float3 ray_Tr(const Scene &sc, uint32_t medium, const Ray &ray) {
+    if (!sc.params.process_mediums || medium == VB_INVALID_ID) return float3{1, 1, 1};
+    return medium_Tr(sc.mediums[medium], length(ray.d) * ray.tmax);
+}
+// coordinate_system (pbrt v3 form)
+inline void coordinate_system(float3 n, float3 &a, float3 &b) {
+    if (std::fabs(n.x) > std::fabs(n.y)) a = float3{-n.z, 0.f, n.x} / std::sqrt(n.x * n.x + n.z * n.z);
+    else a = float3{0.f, n.z, -n.y} / std::sqrt(n.y * n.y + n.z * n.z);
+    b = cross(n, a);
+}
+inline float phase_HG(float cos_theta, float g) {                       // interaction.h:135-139
+    float denom = 1.0f + sqr(g) + 2.0f * g * cos_theta;
+    return Inv4Pi * (1.0f - sqr(g)) / (denom * std::sqrt(denom));
+}
+// HenyeyGreenstein::sample, interaction.cpp:16-32
+inline BSDFSample phase_sample(float g, float3 wo, Sampler &sampler) {
+    float2 u = sampler.next_2d();
+    float sqr_term = (1.0f - sqr(g)) / (1.0f + g - 2.0f * g * u.x);
+    float cos_theta = -(1.0f + sqr(g) - sqr(sqr_term)) / (2.0f * g);
+    if (std::fabs(g) < 1e-3f) cos_theta = 1.0f - 2.0f * u.x;
+    float sin_theta = safe_sqrt(1.0f - sqr(cos_theta));
+    float s, c;
+    sincos_2pi(u.y, s, c);
+    float3 v1, v2;
+    coordinate_system(wo, v1, v2);
+    BSDFSample bs;
+    bs.wi = v1 * (sin_theta * c) + v2 * (sin_theta * s) + wo * cos_theta;
+    float f = phase_HG(cos_theta, g);
+    bs.eval.f = float3{f, f, f}; bs.eval.pdf = f; bs.eval.flags = 0;
+    return bs;
+}
 
 }  // namespace
 
@@ -256,6 +244,8 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
 
     // ---- path_tracing kernel: reference integrator.cpp:85-99 ----
     sampler.start(px, py, frame, 1u);
+    const bool mediums = params.process_mediums != 0;
+    uint32_t ray_medium = mediums ? camera.medium_id : VB_INVALID_ID;          // RayData::dir_medium.w
     float scatter_pdf = 1e16f;
     float3 throughput{1, 1, 1}, ret{0, 0, 0};
     float3 prev_surface_ng = ray.d;
@@ -266,29 +256,68 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
         if (hit.is_miss()) break;                                   // no environment light in this build
         Interaction it = compute_surface_interaction(*this, hit.inst, hit.prim, hit.u, hit.v, true);
         it.wo = normalize(-ray.d);
+        ray.tmax = length(it.pos - ray.o) / length(ray.d);         // geometry.h:64-69
         if (st) st->vertices++;
-        if (it.mat_id == VB_INVALID_ID) {                          // integrator.cpp:208-214
+        if (mediums && ray_medium != VB_INVALID_ID) {              // integrator.cpp:199-206, homogeneous.cpp:50-70
+            const vb_medium_rec &md = this->mediums[ray_medium];
+            float3 sigma_t = medium_sigma_t(md);
+            float3 sigma_s{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale};
+            uint32_t channel = std::min((uint32_t)(sampler.next_1d() * 3.0f), 2u);
+            float sc_t = channel == 0 ? sigma_t.x : (channel == 1 ? sigma_t.y : sigma_t.z);
+            float dist = -vlog(1.0f - sampler.next_1d()) / sc_t;
+            float t = std::min(dist / length(ray.d), ray.tmax);
+            bool sampled_medium = t < ray.tmax;
+            if (sampled_medium) {
+                Interaction mi;
+                mi.pos = ray.o + ray.d * t;
+                mi.wo = -ray.d;
+                mi.ng = float3{0, 0, 0};
+                mi.uv = float2{0, 0};
+                mi.shading = Frame{float3{0, 0, 0}, float3{0, 0, 0}, float3{0, 0, 0}};
+                mi.has_phase = true; mi.g = md.g;
+                mi.inside = ray_medium; mi.outside = ray_medium;
+                it = mi;
+            }
+            float3 tr = medium_Tr(md, t);
+            float3 density = sampled_medium ? sigma_t * tr : tr;
+            float pdf = average3(density);
+            float3 mt = sampled_medium ? tr * sigma_s / pdf : tr / pdf;
+            throughput *= mt;
+        }
+        if (it.mat_id == VB_INVALID_ID && !it.has_phase) {         // integrator.cpp:208-214
             ray = spawn_ray(it, ray.d);
+            if (mediums) ray_medium = dot(it.ng, ray.d) > 0.f ? it.outside : it.inside;
             bounces -= 1;                                           // wraps like the reference's Uint
             continue;
         }
         if (it.light_id != VB_INVALID_ID) {                        // integrator.cpp:221-231
             LightEval ev = evaluate_hit_wi(*this, ray.o, it);
+            float3 tr = ray_Tr(*this, ray_medium, ray);
             float weight = mis_weight(scatter_pdf, ev.pdf);
             if (params.mis_mode == 2) weight = 1.f;
             else if (params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
-            ret += ev.L * throughput * weight;
+            ret += ev.L * throughput * weight * tr;
         }
         prev_surface_ng = it.ng;
         // light sampling + shadow ray, integrator.cpp:241-244
         LightSample ls = sample_light(*this, it, sampler);
         Ray shadow = spawn_ray_to(it, ls.p_light);
+        uint32_t shadow_medium = mediums ? (dot(it.ng, shadow.d) > 0.f ? it.outside : it.inside) : VB_INVALID_ID;
         bool occluded = trace_any(shadow, st);
-        // material, integrator.cpp:262-268 + direct_lighting :20-37
-        Evaluator evaluator = create_evaluator(*this, it);
+        float3 tr = ray_Tr(*this, shadow_medium, shadow);
+        // material / phase function, integrator.cpp:246-283 + direct_lighting :20-37
         float3 wi = normalize(ls.p_light - it.pos);
-        ScatterEval se = evaluator.evaluate(it.wo, wi);
-        BSDFSample bs = evaluator.sample(it.wo, sampler);
+        ScatterEval se;
+        BSDFSample bs;
+        if (mediums && it.has_phase) {
+            float f = phase_HG(dot(it.wo, wi), it.g);
+            se.f = float3{f, f, f}; se.pdf = f; se.flags = 0;
+            bs = phase_sample(it.g, it.wo, sampler);
+        } else {
+            Evaluator evaluator{create_lobe(*this, it), it.ng};
+            se = evaluator.evaluate(*this, it.wo, wi);
+            bs = evaluator.sample(*this, it.wo, sampler);
+        }
         bool is_delta = ls.eval.pdf < 0.f;
         float weight = is_delta ? 1.f : mis_weight(ls.eval.pdf, se.pdf);
         if (params.mis_mode == 1) weight = 1.f;
@@ -296,8 +325,8 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
         float3 Ld{0, 0, 0};
         if (!occluded && se.pdf > 0.f && lpdf > 0.f) Ld = ls.eval.L * se.f * weight / lpdf;
         if (params.mis_mode == 2) Ld = Ld * 0.f;
-        ret += throughput * Ld;
-        eta_scale *= bs.eta * bs.eta;
+        ret += throughput * Ld * tr;
+        eta_scale *= sqr(bs.eta);
         float lum = max_comp(throughput);
         if (!(bs.eval.pdf > 0.f) || lum == 0.f) break;
         throughput *= bs.eval.f / bs.eval.pdf;
@@ -309,6 +338,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
         }
         scatter_pdf = bs.eval.pdf;
         ray = spawn_ray(it, bs.wi);
+        if (mediums) ray_medium = dot(it.ng, bs.wi) > 0.f ? it.outside : it.inside;
     }
     (void)prev_surface_ng;
     return ret;

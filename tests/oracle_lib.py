@@ -138,6 +138,10 @@ class OracleScene:
         lib.vo_scene_set_lights.argtypes = [vp, vp, C.c_uint32, vp, vp, C.c_uint32]
         lib.vo_scene_set_textures.argtypes = [vp, vp, C.c_uint32]
         lib.vo_scene_set_camera.argtypes = [vp, vp]
+        lib.vo_scene_set_lut.argtypes = [vp, C.c_int, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+        lib.vo_scene_set_lut.restype = None
+        lib.vo_scene_set_mediums.argtypes = [vp, vp, C.c_uint32]
+        lib.vo_scene_set_mediums.restype = None
         lib.vo_scene_set_integrator.argtypes = [vp, vp]
         lib.vo_scene_build.argtypes = [vp, C.c_int, C.c_int]
         lib.vo_render.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_uint32, vp, C.c_int, vp]
@@ -173,6 +177,13 @@ class OracleScene:
             a = np.ascontiguousarray(t, np.float32); keep.append(a)
             texs[i].texels = a.ctypes.data; texs[i].height, texs[i].width = a.shape[0], a.shape[1]
         lib.vo_scene_set_textures(self.h, C.cast(texs, vp), len(sc.textures))
+        for which, (a, (nx, ny, nz, ch)) in getattr(sc, "luts", {}).items():
+            a = np.ascontiguousarray(a, np.float32)
+            lib.vo_scene_set_lut(self.h, which, _p(a), nx, ny, nz, ch)
+        meds = getattr(sc, "mediums", [])
+        if meds:
+            arr = (capi.vb_medium_rec * len(meds))(*meds)
+            lib.vo_scene_set_mediums(self.h, C.cast(arr, vp), len(meds))
         lib.vo_scene_set_camera(self.h, C.addressof(sc.camera))
         lib.vo_scene_set_integrator(self.h, C.addressof(sc.params))
         lib.vo_scene_build(self.h, threads, 1 if brute else 0)

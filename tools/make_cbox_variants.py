@@ -1,0 +1,49 @@
+"""Writes the derived cbox test scenes from scenes/cbox/cbox_matte.json (itself the matte variant of the
+reference's res/render_scene/cbox/vision_scene.json). Material parameter blocks are the ones the
+reference scene files use (cbox/vision_scene.json materials Glass2, Mirror, Metal, substrate;
+cbox-dragon.json medium "fog").
+  cbox_materials.json : short box = glass (BK7), tall box = mirror (roughness 0.3), floor = substrate,
+                        right wall = metal (Cu)
+  cbox_fog.json       : short box = glass boundary filled with the Skin1 medium (scale 20), global thin fog,
+                        mediums.process = true
+"""
+import copy
+import json
+from pathlib import Path
+import sys
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from vision_b200.scene_py import load_json_with_comments
+
+root = Path(__file__).resolve().parent.parent / "scenes" / "cbox"
+base = load_json_with_comments(root / "cbox_matte.json")
+
+extra = [
+    {"type": "glass", "name": "Glass2", "param": {"material_name": "BK7", "color": {"channels": "xyz", "node": [1, 1, 1]}, "ior": 1.5, "roughness": [0.001, 0.001]}},
+    {"type": "mirror", "name": "Mirror", "param": {"color": {"channels": "xyz", "node": [1, 1, 1]}, "roughness": 0.3}},
+    {"type": "metal", "name": "Metal", "param": {"material_name": "Cu", "roughness": [0.001, 0.001]}},
+    {"type": "substrate", "name": "substrate", "param": {"roughness": 0.001, "spec": [0.04, 0.04, 0.04], "color": [0.725, 0.71, 0.68]}},
+]
+
+def assign(d, mapping):
+    for s in d["shapes"]:
+        if s["name"] in mapping:
+            s["param"]["material"] = mapping[s["name"]]
+
+a = copy.deepcopy(base)
+a["materials"] += extra
+assign(a, {"shape_5": "Glass2", "shape_6": "Mirror", "shape_0": "substrate", "shape_4": "Metal"})
+a["integrator"]["param"]["max_depth"] = 8
+(root / "cbox_materials.json").write_text(json.dumps(a, indent=1))
+
+b = copy.deepcopy(base)
+b["materials"] += extra[:1]
+assign(b, {"shape_5": "Glass2"})
+b["mediums"] = {"process": True, "global": "air", "list": [
+    {"type": "homogeneous", "name": "fog", "param": {"g": 0, "medium_name": "Skin1", "scale": 20}},
+    {"type": "homogeneous", "name": "air", "param": {"g": 0.3, "scale": 0.25, "sigma_s": [1, 1, 1], "sigma_a": [0, 0, 0]}}]}
+for s in b["shapes"]:
+    if s["name"] == "shape_5":
+        s["param"]["medium"] = {"inside": "fog", "outside": "air"}
+b["integrator"]["param"]["max_depth"] = 8
+(root / "cbox_fog.json").write_text(json.dumps(b, indent=1))
+print("wrote", root / "cbox_materials.json", root / "cbox_fog.json")

@@ -281,6 +281,24 @@ class vb_material_rec(C.Structure):
                 ("eta", C.c_float * 4), ("k", C.c_float * 4), ("params", C.c_float * 16)]
 
 
+class vb_medium_rec(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("g", C.c_float), ("scale", C.c_float), ("pad", C.c_float),
+                ("sigma_a", C.c_float * 4), ("sigma_s", C.c_float * 4)]
+
+
+VB_LUT_PURE_REFLECTION, VB_LUT_DIELECTRIC, VB_LUT_DIELECTRIC_INV = 0, 1, 2
+LUT_FILES = {VB_LUT_PURE_REFLECTION: ("lut_pure_reflection_32x32x1x1.f32", (32, 32, 1, 1)),
+             VB_LUT_DIELECTRIC: ("lut_dielectric_32x32x32x2.f32", (32, 32, 32, 2)),
+             VB_LUT_DIELECTRIC_INV: ("lut_dielectric_inv_32x32x32x2.f32", (32, 32, 32, 2))}
+
+
+def load_luts() -> dict:
+    """the energy-compensation tables shipped under vision_b200/data (tools/extract_luts.py)"""
+    from pathlib import Path
+    d = Path(__file__).resolve().parent / "data"
+    return {k: (np.fromfile(d / fn, np.float32), dims) for k, (fn, dims) in LUT_FILES.items()}
+
+
 class vb_alias_entry(C.Structure):
     _fields_ = [("prob", C.c_float), ("alias", C.c_uint32)]
 
@@ -325,6 +343,8 @@ def _bind_pt(lib):
     sigs = {
         "vb_textures_set": [vp, C.POINTER(vb_texture), C.c_uint32],
         "vb_materials_set": [vp, C.POINTER(vb_material_rec), C.c_uint32],
+        "vb_luts_set": [vp, C.c_int, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32],
+        "vb_mediums_set": [vp, C.POINTER(vb_medium_rec), C.c_uint32],
         "vb_lights_set": [vp, C.POINTER(vb_light_rec), C.c_uint32, C.POINTER(vb_alias_entry), vp, C.c_uint32],
         "vb_camera_set": [vp, C.POINTER(vb_camera)],
         "vb_integrator_set": [vp, C.POINTER(vb_pt_params)],
@@ -354,6 +374,8 @@ class SceneRecords:
         self.alias_table = []   # (prob, alias)
         self.alias_func = []    # float
         self.textures = []      # (h, w, 4) float32 arrays
+        self.mediums = []       # vb_medium_rec
+        self.luts = {}          # which -> (float32 array, (nx, ny, nz, channels)); filled when a material needs them
         self.camera = vb_camera()
         self.params = vb_pt_params()
         self.resolution = (256, 256)
@@ -379,6 +401,15 @@ def _pt_methods():
         self._check(self.lib.vb_textures_set(self.h, texs, len(sc.textures)), "vb_textures_set")
         mats = (vb_material_rec * max(1, len(sc.materials)))(*sc.materials)
         self._check(self.lib.vb_materials_set(self.h, mats, len(sc.materials)), "vb_materials_set")
+        for which in range(3):
+            if which in sc.luts:
+                a, (nx, ny, nz, ch) = sc.luts[which]
+                a = np.ascontiguousarray(a, np.float32)
+                self._check(self.lib.vb_luts_set(self.h, which, a.ctypes.data, nx, ny, nz, ch), "vb_luts_set")
+            else:
+                self._check(self.lib.vb_luts_set(self.h, which, None, 0, 0, 0, 0), "vb_luts_set")
+        meds = (vb_medium_rec * max(1, len(sc.mediums)))(*sc.mediums)
+        self._check(self.lib.vb_mediums_set(self.h, meds, len(sc.mediums)), "vb_mediums_set")
         lights = (vb_light_rec * max(1, len(sc.lights)))(*sc.lights)
         na = len(sc.alias_table)
         tab = (vb_alias_entry * max(1, na))(*[vb_alias_entry(p, a) for p, a in sc.alias_table])

@@ -1,0 +1,260 @@
+// Lobe evaluation / sampling / construction (device). Second half of vb_bsdf.cuh; mirrors the
+// corresponding part of oracle/vo_bsdf.inl statement by statement.
+#pragma once
+
+namespace {
+
+// the lobe of one surface hit (the reference builds exactly one Lobe per material on this path)
+struct Lobe {
+    uint32_t type;
+    Frame3 frame;              // Material::compute_shading_frame without a normal map
+    f3 kr;                     // diffuse Kr | mirror kr | glass kt | substrate Rd
+    f3 rs;                     // substrate Rs | metal eta
+    f3 kk;                     // metal k
+    GGX mf;
+    float eta;                 // glass: corrected relative ior (Interaction::correct_eta)
+    bool oren_nayar; float on_A, on_B;
+};
+
+__device__ f3 lobe_fresnel(const Lobe &lb, float cos_theta) {
+    switch (lb.type) {
+        case VB_MAT_METAL: return {fresnel_complex(cos_theta, lb.rs.x, lb.kk.x), fresnel_complex(cos_theta, lb.rs.y, lb.kk.y),
+                                   fresnel_complex(cos_theta, lb.rs.z, lb.kk.z)};
+        case VB_MAT_GLASS: return splat(fresnel_dielectric(cos_theta, lb.eta));
+        case VB_MAT_SUBSTRATE: return splat(fresnel_dielectric(cos_theta, 1.5f));
+        default: return splat(1.f);
+    }
+}
+
+// -- DielectricLobe, lobe.cpp:253-449 --
+__device__ float dielectric_compensate(const PtScene &S, const Lobe &lb, f3 wo) {
+    const DevLut &L = lb.eta > 1.0f ? S.luts[VB_LUT_DIELECTRIC] : S.luts[VB_LUT_DIELECTRIC_INV];
+    if (!L.data) return 1.0f;
+    float x = __fsqrt_rn(__fsqrt_rn(lb.mf.ax * lb.mf.ay));
+    float y = fabsf(wo.z);
+    const float lo = 1.003f, hi = 5.0f;
+    float z = lb.eta > 1.0f ? (lb.eta - lo) / (hi - lo) : (1.0f / lb.eta - lo) / (hi - lo);
+    return 1.0f / lut_sample3d_ch0(L, x, y, z);
+}
+__device__ __forceinline__ float dielectric_refl_prob(const Lobe &lb, float F) {
+    float T = 1.0f - F;
+    f3 total = lb.kr * T + splat(F);
+    return F / average3(total);
+}
+__device__ ScatterEval dielectric_evaluate_local(const PtScene &S, const Lobe &lb, f3 wo, f3 wi, bool flip_wh, float *eta_out) {
+    bool reflect_ = same_hemisphere(wo, wi);
+    float eta_p = reflect_ ? 1.0f : lb.eta;
+    if (eta_out) *eta_out = eta_p;
+    f3 wh = normalize(wo + wi * eta_p);
+    if (flip_wh) wh = face_forward(wh, wo);
+    float F = fresnel_dielectric(abs_dot(wh, wo), lb.eta);
+    ScatterEval se;
+    if (reflect_) {
+        se.f = splat(ggx_brdf_div_fr(lb.mf, wo, wh, wi) * F);
+        se.pdf = ggx_pdf_wi_reflection(lb.mf, wo, wh) * dielectric_refl_prob(lb, F);
+        se.flags = FlagGlossy | FlagReflection;
+        se.f = se.f * dielectric_compensate(S, lb, wo);
+    } else {
+        f3 new_wh = face_forward(wh, wo);
+        f3 wh2 = normalize(wo + wi * lb.eta);
+        float tr = ggx_btdf_div_ft(lb.mf, wo, wh2, wi, lb.eta) * (1.0f - F);
+        se.f = lb.kr * tr;
+        se.pdf = ggx_pdf_wi_transmission(lb.mf, wo, new_wh, wi, lb.eta) * (1.0f - dielectric_refl_prob(lb, F));
+        se.flags = FlagGlossy | FlagTransmission;
+        se.f = se.f * dielectric_compensate(S, lb, wo);
+    }
+    return se;
+}
+
+// -- MicrofacetReflection (mirror, metal), bxdf.cpp:65-85 + PureReflectionLobe lobe.cpp:716-730 --
+__device__ ScatterEval microfacet_refl_evaluate_local(const PtScene &S, const Lobe &lb, f3 wo, f3 wi) {
+    ScatterEval se;
+    bool s = same_hemisphere(wo, wi);
+    f3 wh = normalize(wo + wi);
+    f3 whf = face_forward(wh, f3{0, 0, 1});
+    f3 F = lobe_fresnel(lb, abs_dot(wo, whf));
+    f3 fr = F * ggx_brdf_div_fr(lb.mf, wo, whf, wi);
+    f3 f = fr * lb.kr;
+    float pdf = ggx_pdf_wi_reflection(lb.mf, wo, wh);
+    se.f = s ? f : f3{0, 0, 0};
+    se.pdf = s ? pdf : 0.f;
+    se.flags = FlagGlossy | FlagReflection;
+    const DevLut &L = S.luts[VB_LUT_PURE_REFLECTION];
+    if (L.data) {
+        float alpha = __fsqrt_rn(lb.mf.ax * lb.mf.ay);
+        se.f = se.f * (1.0f / lut_sample2d(L, alpha, wo.z));
+    }
+    return se;
+}
+
+// -- FresnelBlend (substrate), substrate.cpp:12-70 --
+__device__ ScatterEval fresnel_blend_evaluate_local(const Lobe &lb, f3 wo, f3 wi) {
+    ScatterEval se;
+    bool s = same_hemisphere(wo, wi);
+    float aci = fabsf(wi.z), aco = fabsf(wo.z);
+    f3 diffuse = lb.kr * (28.f / (23.f * Pi)) * (splat(1.f) - lb.rs) * (1.0f - pow5(1.0f - .5f * aci)) * (1.0f - pow5(1.0f - .5f * aco));
+    f3 wh = normalize(wi + wo);
+    float sw = pow5(fmin_(fmax_(1.0f - dot(wi, wh), 0.f), 1.f));
+    f3 schlick{lerp(sw, lb.rs.x, 1.f), lerp(sw, lb.rs.y, 1.f), lerp(sw, lb.rs.z, 1.f)};
+    f3 specular = schlick * (ggx_D(lb.mf, wh) / (4.0f * abs_dot(wi, wh) * fmax_(aci, aco)));
+    if (is_zero(wh)) specular = specular * 0.f;
+    f3 f = specular + diffuse;
+    float fr = fresnel_dielectric(aco, 1.5f);
+    float pdf = lerp(fr, aci * InvPi, ggx_pdf_wi_reflection(lb.mf, wo, normalize(wo + wi)));
+    se.f = s ? f : f3{0, 0, 0};
+    se.pdf = s ? pdf : 0.f;
+    se.flags = FlagReflection;
+    return se;
+}
+
+// -- Lambert / Oren-Nayar, bxdf.cpp:13-46,94-121 --
+__device__ ScatterEval diffuse_evaluate_local(const Lobe &lb, f3 wo, f3 wi) {
+    ScatterEval se;
+    bool s = same_hemisphere(wo, wi);
+    f3 f = lb.kr * InvPi;
+    if (lb.oren_nayar) {
+        float sti = __fsqrt_rn(fmax_(0.f, 1.0f - wi.z * wi.z)), sto = __fsqrt_rn(fmax_(0.f, 1.0f - wo.z * wo.z));
+        float cpi = sti == 0.f ? 1.f : fmin_(fmax_(wi.x / sti, -1.f), 1.f), spi = sti == 0.f ? 0.f : fmin_(fmax_(wi.y / sti, -1.f), 1.f);
+        float cpo = sto == 0.f ? 1.f : fmin_(fmax_(wo.x / sto, -1.f), 1.f), spo = sto == 0.f ? 0.f : fmin_(fmax_(wo.y / sto, -1.f), 1.f);
+        float d_cos = cpi * cpo + spi * spo;
+        float max_cos = fmax_(0.f, d_cos);
+        bool cond = fabsf(wi.z) > fabsf(wo.z);
+        float sin_alpha = cond ? sto : sti;
+        float tan_beta = cond ? sti / fabsf(wi.z) : sto / fabsf(wo.z);
+        f = lb.kr * InvPi * (lb.on_A + lb.on_B * max_cos * sin_alpha * tan_beta);
+    }
+    se.f = s ? f : f3{0, 0, 0};
+    se.pdf = s ? fabsf(wi.z) * InvPi : 0.f;
+    se.flags = FlagDiffuse | FlagReflection;
+    return se;
+}
+
+// Lobe::evaluate_impl (lobe.cpp:53-77): world -> local, f *= |cos(wi)|
+__device__ ScatterEval lobe_evaluate(const PtScene &S, const Lobe &lb, f3 world_wo, f3 world_wi, bool with_eta, float *eta_out) {
+    f3 wo = lb.frame.to_local(world_wo), wi = lb.frame.to_local(world_wi);
+    ScatterEval se;
+    switch (lb.type) {
+        case VB_MAT_GLASS: se = dielectric_evaluate_local(S, lb, wo, wi, with_eta, eta_out); break;
+        case VB_MAT_MIRROR: case VB_MAT_METAL: se = microfacet_refl_evaluate_local(S, lb, wo, wi); break;
+        case VB_MAT_SUBSTRATE: se = fresnel_blend_evaluate_local(lb, wo, wi); break;
+        default: se = diffuse_evaluate_local(lb, wo, wi); break;
+    }
+    se.f = se.f * fabsf(wi.z);
+    return se;
+}
+
+__device__ __forceinline__ f3 cosine_hemisphere(f2 u, float woz) {
+    float r = __fsqrt_rn(u.x), s, c;
+    sincos_2pi(u.y, s, c);
+    float dx = r * c, dy = r * s;
+    float z = __fsqrt_rn(fmax_(0.0f, 1.0f - dx * dx - dy * dy));
+    if (woz < 0.f) z = -z;
+    return {dx, dy, z};
+}
+
+// Lobe::sample (lobe.cpp:111-119) with each lobe's sample_wi_local_impl; draws in the reference's order
+__device__ BSDFSample lobe_sample(const PtScene &S, const Lobe &lb, f3 world_wo, Sampler &sampler) {
+    f3 wo = lb.frame.to_local(world_wo);
+    f3 wi;
+    bool valid = true;
+    switch (lb.type) {
+        case VB_MAT_GLASS: {
+            f3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
+            float d = dot(wo, wh);
+            float F = fresnel_dielectric(fabsf(d), lb.eta);
+            float uc = sampler.next_1d();
+            if (uc < dielectric_refl_prob(lb, F)) {
+                wi = reflect(wo, wh);
+                valid = same_hemisphere(wo, wi);
+            } else {
+                bool ok = refract(wo, wh, lb.eta, wi);
+                valid = ok && !same_hemisphere(wo, wi);
+            }
+        } break;
+        case VB_MAT_MIRROR: case VB_MAT_METAL: {
+            f3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
+            wi = reflect(wo, wh);
+            valid = same_hemisphere(wo, wi);
+        } break;
+        case VB_MAT_SUBSTRATE: {
+            f2 u = sampler.next_2d();
+            float fr = fresnel_dielectric(fabsf(wo.z), 1.5f);
+            if (u.x < fr) {
+                u.x = (u.x - 0.f) / (fr - 0.f);
+                f3 wh = ggx_sample_wh(lb.mf, wo, u);
+                wi = reflect(wo, wh);
+            } else {
+                u.x = (u.x - fr) / (1.f - fr);
+                wi = cosine_hemisphere(u, wo.z);
+            }
+        } break;
+        default: wi = cosine_hemisphere(sampler.next_2d(), wo.z); break;
+    }
+    BSDFSample bs;
+    bs.eta = 1.f;
+    bs.wi = lb.frame.to_world(wi);
+    bs.eval = lobe_evaluate(S, lb, world_wo, bs.wi, true, &bs.eta);
+    if (!valid) bs.eval.pdf *= 0.f;
+    return bs;
+}
+
+__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fmin_(fmax_(v, lo), hi); }
+
+// Material::create_evaluator -> create_lobe_set of the plugin
+__device__ Lobe create_lobe(const PtScene &S, const Interaction &it) {
+    const vb_material_rec &m = S.materials[it.mat_id];
+    Lobe lb;
+    lb.type = m.type;
+    lb.frame = it.shading;
+    lb.kr = f3{0, 0, 0}; lb.rs = f3{0, 0, 0}; lb.kk = f3{0, 0, 0};
+    lb.mf = GGX{1.f, 1.f}; lb.eta = 1.f; lb.oren_nayar = false; lb.on_A = 1.f; lb.on_B = 0.f;
+    bool remap = (m.flags & 2u) != 0;
+    float anis = clampf(m.params[0], -0.9f, 0.9f);
+    switch (m.type) {
+        case VB_MAT_DIFFUSE:
+            lb.kr = eval_slot3(S, m.color, it.uv);
+            if (m.flags & 1u) {
+                float sigma = eval_slot3(S, m.sigma, it.uv).x * PiOver2;
+                float sigma2 = sqr(sigma * sigma);
+                lb.oren_nayar = true;
+                lb.on_A = 1.f - (sigma2 / (2.f * (sigma2 + 0.33f)));
+                lb.on_B = 0.45f * sigma2 / (sigma2 + 0.09f);
+            }
+            break;
+        case VB_MAT_MIRROR: case VB_MAT_METAL: {
+            lb.kr = m.type == VB_MAT_MIRROR ? eval_slot3(S, m.color, it.uv) : splat(1.f);
+            float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
+            r = remap ? sqr(r) : r;
+            calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
+            lb.rs = f3{m.eta[0], m.eta[1], m.eta[2]}; lb.kk = f3{m.k[0], m.k[1], m.k[2]};
+        } break;
+        case VB_MAT_GLASS: {
+            lb.kr = eval_slot3(S, m.color, it.uv);
+            float ior = eval_slot3(S, m.ior, it.uv).x;
+            lb.eta = dot(it.wo, it.ng) > 0.f ? ior : 1.0f / ior;
+            float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.01f, 1.f);
+            r = remap ? sqr(r) : r;
+            calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
+        } break;
+        case VB_MAT_SUBSTRATE: {
+            lb.kr = eval_slot3(S, m.color, it.uv);
+            lb.rs = eval_slot3(S, m.spec, it.uv);
+            float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
+            r = remap ? sqr(r) : r;
+            calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
+            if (remap) { lb.mf.ax = sqr(lb.mf.ax); lb.mf.ay = sqr(lb.mf.ay); }
+            lb.mf.ax = clampf(lb.mf.ax, 0.0001f, 1.f); lb.mf.ay = clampf(lb.mf.ay, 0.0001f, 1.f);
+        } break;
+        default: break;
+    }
+    return lb;
+}
+
+// MaterialEvaluator (individual_ns branch), material.cpp:132-142,163-175
+__device__ __forceinline__ void hemisphere_discard(ScatterEval &se, f3 wo, f3 wi, f3 ng) {
+    bool same = dot(wo, ng) * dot(wi, ng) > 0.f;
+    bool is_trans = (se.flags & FlagTransmission) != 0;
+    if (same == is_trans) se.pdf = 0.f;
+}
+
+}  // namespace

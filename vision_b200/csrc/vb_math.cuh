@@ -31,6 +31,10 @@ __device__ __forceinline__ f3 normalize(f3 a) {
 __device__ __forceinline__ float fmin_(float a, float b) { return b < a ? b : a; }   // == std::min
 __device__ __forceinline__ float fmax_(float a, float b) { return a < b ? b : a; }   // == std::max
 __device__ __forceinline__ float max_comp(f3 a) { return fmax_(a.x, fmax_(a.y, a.z)); }
+__device__ __forceinline__ float lerp(float t, float a, float b) { return a + t * (b - a); }
+__device__ __forceinline__ float sqr(float x) { return x * x; }
+__device__ __forceinline__ float safe_sqrt(float x) { return __fsqrt_rn(fmax_(0.0f, x)); }
+__device__ __forceinline__ f3 splat(float v) { return {v, v, v}; }
 
 // column-major 4x4 in a flat array m[4*c + r]
 __device__ __forceinline__ f3 transform_point(const float *m, f3 p) {
@@ -52,6 +56,8 @@ __device__ __forceinline__ f3 apply_normal(const float *m, f3 n) {
 
 constexpr float Pi = 3.14159265358979323846f;
 constexpr float InvPi = 0.31830988618379067154f;
+constexpr float Inv4Pi = 0.07957747154594766788f;
+constexpr float PiOver2 = 1.57079632679489661923f;
 constexpr float OneMinusEpsilon = 0x1.fffffep-1f;
 constexpr float ShadowEpsilon = 1e-4f;
 constexpr float RayTMax = 1e30f;
@@ -69,6 +75,34 @@ __device__ __forceinline__ void sincos_2pi(float u, float &s, float &c) {
     else if (iq == 1) { s = cp; c = -sp; }
     else if (iq == 2) { s = -sp; c = -cp; }
     else { s = -cp; c = sp; }
+}
+
+// mirror vo::vexp / vo::vlog (oracle/vo_pt.cpp): fixed operation sequence, bit-identical to the host
+__device__ __forceinline__ float vexp(float x) {
+    if (!(x > -87.0f)) return x != x ? x : 0.0f;
+    if (x > 88.0f) return __int_as_float(0x7f800000);
+    float n = floorf(x * 1.44269504088896341f + 0.5f);
+    float r = __fmaf_rn(n, -0.693359375f, x);
+    r = __fmaf_rn(n, 2.12194440e-4f, r);
+    float z = r * r;
+    float p = ((((1.9875691500e-4f * r + 1.3981999507e-3f) * r + 8.3334519073e-3f) * r + 4.1665795894e-2f) * r + 1.6666665459e-1f) * r + 5.0000001201e-1f;
+    float y = p * z + r + 1.0f;
+    return __uint_as_float(__float_as_uint(y) + ((uint32_t)(int32_t)n << 23));
+}
+__device__ __forceinline__ float vlog(float x) {
+    if (!(x > 0.0f)) return x == 0.0f ? __int_as_float(0xff800000) : __int_as_float(0x7fc00000);
+    uint32_t b = __float_as_uint(x);
+    int32_t e = (int32_t)((b >> 23) & 0xffu) - 126;
+    float m = __uint_as_float((b & 0x007fffffu) | 0x3f000000u);
+    if (m < 0.70710678118654752440f) { e -= 1; m = m + m - 1.0f; } else { m = m - 1.0f; }
+    float z = m * m;
+    float y = ((((((((7.0376836292e-2f * m - 1.1514610310e-1f) * m + 1.1676998740e-1f) * m - 1.2420140846e-1f) * m + 1.4249322787e-1f) * m
+                 - 1.6668057665e-1f) * m + 2.0000714765e-1f) * m - 2.4999993993e-1f) * m + 3.3333331174e-1f) * m * z;
+    float fe = (float)e;
+    y = y + -2.12194440e-4f * fe;
+    y = y + -0.5f * z;
+    float r = m + y;
+    return r + 0.693359375f * fe;
 }
 
 // mirrors vo::offset_ray_origin (Waechter & Binder)

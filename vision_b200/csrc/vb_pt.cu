@@ -20,6 +20,7 @@ struct DevInst {
     float nmat[12];            // 9 used: sign(det) * cofactor(o2w 3x3), row-major
 };
 struct DevTex { const float4 *texels; uint32_t w, h; };
+struct DevLut { const float *data; uint32_t nx, ny, nz, channels; };
 
 struct PtScene {
     VbAccelView accel;
@@ -31,6 +32,8 @@ struct PtScene {
     const vb_alias_entry *alias_table;
     const float *alias_func;
     const DevTex *textures;
+    DevLut luts[VB_LUT_COUNT];
+    const vb_medium_rec *mediums;
     vb_camera cam;
     vb_pt_params params;
     uint32_t width, height;
@@ -55,6 +58,9 @@ struct Interaction {
     Frame3 shading;
     float prim_area;
     uint32_t prim_id, mat_id, light_id;
+    uint32_t inside, outside;      // medium interface (Interaction::set_medium)
+    bool has_phase;                // medium interaction (Interaction::init_phase, interaction.cpp:58-63)
+    float g;
 };
 
 __device__ __forceinline__ f3 ld3(const float *p, uint32_t i) { return {__ldg(p + 3 * i), __ldg(p + 3 * i + 1), __ldg(p + 3 * i + 2)}; }
@@ -74,6 +80,7 @@ __device__ Interaction compute_surface_interaction(const PtScene &S, uint32_t in
     const DevMesh M = S.meshes[I.mesh_id];
     uint32_t i0 = __ldg(M.tri + 3 * prim_id), i1 = __ldg(M.tri + 3 * prim_id + 1), i2 = __ldg(M.tri + 3 * prim_id + 2);
     it.light_id = I.light_id; it.mat_id = I.mat_id;
+    it.inside = I.inside; it.outside = I.outside; it.has_phase = false; it.g = 0.f;
     f3 p0 = transform_point(I.o2w, ld3(M.pos, i0)), p1 = transform_point(I.o2w, ld3(M.pos, i1)), p2 = transform_point(I.o2w, ld3(M.pos, i2));
     it.pos = lerp3(bu, bv, p0, p1, p2);
     f3 dp02 = p0 - p2, dp12 = p1 - p2;
@@ -196,45 +203,61 @@ __device__ LightSample area_sample_wi(const PtScene &S, const vb_light_rec &l, c
     return ls;
 }
 
-struct ScatterEval { f3 f; float pdf; uint32_t flags; };
-constexpr uint32_t FlagReflection = 1u << 1, FlagTransmission = 1u << 2, FlagDiffuse = 1u << 3;
-
-struct Evaluator {
-    uint32_t type;
-    f3 kr, ng;
-    Frame3 frame;
-    __device__ ScatterEval evaluate(f3 world_wo, f3 world_wi) const {
-        f3 wo = frame.to_local(world_wo), wi = frame.to_local(world_wi);
-        ScatterEval se;
-        bool s = wo.z * wi.z > 0.f;
-        se.f = s ? kr * InvPi : f3{0, 0, 0};
-        se.pdf = s ? fabsf(wi.z) * InvPi : 0.f;
-        se.flags = FlagDiffuse | FlagReflection;
-        se.f = se.f * fabsf(wi.z);
-        bool same = dot(world_wo, ng) * dot(world_wi, ng) > 0.f;
-        bool is_trans = (se.flags & FlagTransmission) != 0;
-        if (same == is_trans) se.pdf = 0.f;
-        return se;
-    }
-    __device__ f3 sample_wi(f3 world_wo, f2 u) const {
-        f3 wo = frame.to_local(world_wo);
-        float r = __fsqrt_rn(u.x), s, c;
-        sincos_2pi(u.y, s, c);
-        float dx = r * c, dy = r * s;
-        float z = __fsqrt_rn(fmax_(0.0f, 1.0f - dx * dx - dy * dy));
-        if (wo.z < 0.f) z = -z;
-        return frame.to_world(f3{dx, dy, z});
-    }
-};
-
-__device__ __forceinline__ float mis_weight(float f, float g) { return (1.0f * f) / (1.0f * f + 1.0f * g); }
-
 struct Sampler {
     uint32_t state;
     __device__ void start(uint32_t px, uint32_t py, uint32_t si, uint32_t dim) { state = tea4(tea4(px, py), tea4(si, dim)); }
     __device__ float next_1d() { return lcg(state); }
     __device__ f2 next_2d() { float x = next_1d(); float y = next_1d(); return {x, y}; }
 };
+
+}  // namespace
+#include "vb_bsdf.cuh"
+namespace {
+
+// ---- homogeneous medium, reference render_core/medium/homogeneous.cpp:30-70 ----
+__device__ __forceinline__ f3 medium_sigma_t(const vb_medium_rec &m) {
+    return f3{m.sigma_a[0] + m.sigma_s[0], m.sigma_a[1] + m.sigma_s[1], m.sigma_a[2] + m.sigma_s[2]} * m.scale;
+}
+__device__ __forceinline__ f3 medium_Tr(const vb_medium_rec &m, float t) {
+    f3 st = medium_sigma_t(m);
+    float tt = fmin_(RayTMax, t);
+    return {vexp(-st.x * tt), vexp(-st.y * tt), vexp(-st.z * tt)};
+}
+// Geometry::Tr (geometry.cpp:187-199)
+__device__ __forceinline__ f3 ray_Tr(const PtScene &S, uint32_t medium, const VbRay &ray) {
+    if (!S.params.process_mediums || medium == VB_INVALID_ID) return f3{1, 1, 1};
+    return medium_Tr(S.mediums[medium], length(f3{ray.dx, ray.dy, ray.dz}) * ray.tmax);
+}
+__device__ __forceinline__ void coordinate_system(f3 n, f3 &a, f3 &b) {
+    if (fabsf(n.x) > fabsf(n.y)) a = f3{-n.z, 0.f, n.x} / __fsqrt_rn(n.x * n.x + n.z * n.z);
+    else a = f3{0.f, n.z, -n.y} / __fsqrt_rn(n.y * n.y + n.z * n.z);
+    b = cross(n, a);
+}
+__device__ __forceinline__ float phase_HG(float cos_theta, float g) {
+    float denom = 1.0f + sqr(g) + 2.0f * g * cos_theta;
+    return Inv4Pi * (1.0f - sqr(g)) / (denom * __fsqrt_rn(denom));
+}
+// HenyeyGreenstein::sample, interaction.cpp:16-32
+__device__ BSDFSample phase_sample(float g, f3 wo, Sampler &sampler) {
+    f2 u = sampler.next_2d();
+    float sqr_term = (1.0f - sqr(g)) / (1.0f + g - 2.0f * g * u.x);
+    float cos_theta = -(1.0f + sqr(g) - sqr(sqr_term)) / (2.0f * g);
+    if (fabsf(g) < 1e-3f) cos_theta = 1.0f - 2.0f * u.x;
+    float sin_theta = safe_sqrt(1.0f - sqr(cos_theta));
+    float s, c;
+    sincos_2pi(u.y, s, c);
+    f3 v1, v2;
+    coordinate_system(wo, v1, v2);
+    BSDFSample bs;
+    bs.eta = 1.f;
+    bs.wi = v1 * (sin_theta * c) + v2 * (sin_theta * s) + wo * cos_theta;
+    float f = phase_HG(cos_theta, g);
+    bs.eval.f = f3{f, f, f}; bs.eval.pdf = f; bs.eval.flags = 0;
+    return bs;
+}
+
+__device__ __forceinline__ float mis_weight(float f, float g) { return (1.0f * f) / (1.0f * f + 1.0f * g); }
+
 
 __device__ __forceinline__ float sample_linear10(float u) {
     float a = 1.f, b = 0.f;

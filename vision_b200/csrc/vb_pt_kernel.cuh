@@ -37,6 +37,8 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                 continue;
             }
             sampler.start(px, py, frame, 1u);
+            const bool mediums = S.params.process_mediums != 0;
+            uint32_t ray_medium = mediums ? S.cam.medium_id : VB_INVALID_ID;
             float scatter_pdf = 1e16f;
             f3 throughput{1, 1, 1}, ret{0, 0, 0};
             float eta_scale = 1.f;
@@ -49,13 +51,41 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                 Interaction it = compute_surface_interaction(S, hit.inst, hit.prim, hit.u, hit.v, true);
                 f3 rd{ray.dx, ray.dy, ray.dz}, ro{ray.ox, ray.oy, ray.oz};
                 it.wo = normalize(-rd);
+                ray.tmax = length(it.pos - ro) / length(rd);             // geometry.h:64-69
                 c_vert++;
-                if (it.mat_id == VB_INVALID_ID) {
+                if (mediums && ray_medium != VB_INVALID_ID) {            // integrator.cpp:199-206, homogeneous.cpp:50-70
+                    const vb_medium_rec &md = S.mediums[ray_medium];
+                    f3 sigma_t = medium_sigma_t(md);
+                    f3 sigma_s{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale};
+                    uint32_t channel = min((uint32_t)(sampler.next_1d() * 3.0f), 2u);
+                    float sc_t = channel == 0 ? sigma_t.x : (channel == 1 ? sigma_t.y : sigma_t.z);
+                    float dist = -vlog(1.0f - sampler.next_1d()) / sc_t;
+                    float t = fmin_(dist / length(rd), ray.tmax);
+                    bool sampled_medium = t < ray.tmax;
+                    if (sampled_medium) {
+                        it.pos = ro + rd * t;
+                        it.wo = -rd;
+                        it.ng = f3{0, 0, 0};
+                        it.uv = f2{0, 0};
+                        it.shading.x = f3{0, 0, 0}; it.shading.y = f3{0, 0, 0}; it.shading.z = f3{0, 0, 0};
+                        it.prim_area = 0.f;
+                        it.prim_id = VB_INVALID_ID; it.mat_id = VB_INVALID_ID; it.light_id = VB_INVALID_ID;
+                        it.has_phase = true; it.g = md.g;
+                        it.inside = ray_medium; it.outside = ray_medium;
+                    }
+                    f3 tr = medium_Tr(md, t);
+                    f3 density = sampled_medium ? sigma_t * tr : tr;
+                    float pdf = average3(density);
+                    f3 mt = sampled_medium ? tr * sigma_s / pdf : tr / pdf;
+                    throughput = throughput * mt;
+                }
+                if (it.mat_id == VB_INVALID_ID && !it.has_phase) {       // integrator.cpp:208-214
                     ray = spawn_ray(it, rd);
+                    if (mediums) ray_medium = dot(it.ng, rd) > 0.f ? it.outside : it.inside;
                     bounces -= 1;
                     continue;
                 }
-                if (it.light_id != VB_INVALID_ID) {
+                if (it.light_id != VB_INVALID_ID) {                      // integrator.cpp:221-231
                     const vb_light_rec &l = S.lights[it.light_id];
                     LightEval ev{f3{0, 0, 0}, 0.f};
                     if (l.type == VB_LIGHT_AREA) {
@@ -64,10 +94,11 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                         ev = area_evaluate_wi(S, l, ro, pl);
                         ev.pdf *= 1.0f / (float)S.n_lights;
                     }
+                    f3 tr = ray_Tr(S, ray_medium, ray);
                     float weight = mis_weight(scatter_pdf, ev.pdf);
                     if (S.params.mis_mode == 2) weight = 1.f;
                     else if (S.params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
-                    f3 d = ev.L * throughput * weight;
+                    f3 d = ev.L * throughput * weight * tr;
                     ret = ret + d;
                 }
                 // light sampling
@@ -82,20 +113,26 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                     ls.eval.pdf *= 1.0f / (float)n;
                 }
                 VbRay shadow = spawn_ray_to(it, ls.p_light);
+                uint32_t shadow_medium = mediums ? (dot(it.ng, f3{shadow.dx, shadow.dy, shadow.dz}) > 0.f ? it.outside : it.inside) : VB_INVALID_ID;
                 VbHit sh;
                 bool occluded = vb_traverse<true, false>(S.accel, shadow, sh, s_stack, PT_BLOCK, dummy0, dummy1, mg);
                 c_any++;
-                // material
-                const vb_material_rec &m = S.materials[it.mat_id];
-                Evaluator evr;
-                evr.type = m.type; evr.ng = it.ng; evr.frame = it.shading;
-                evr.kr = (m.type == VB_MAT_DIFFUSE) ? eval_slot3(S, m.color, it.uv) : f3{0, 0, 0};
+                f3 tr = ray_Tr(S, shadow_medium, shadow);
+                // material / phase function, integrator.cpp:246-283 + direct_lighting :20-37
                 f3 wi = normalize(ls.p_light - it.pos);
-                ScatterEval se = evr.evaluate(it.wo, wi);
-                f2 ub = sampler.next_2d();
-                f3 bwi = evr.sample_wi(it.wo, ub);
-                ScatterEval be = evr.evaluate(it.wo, bwi);
-                float beta = 1.f;
+                ScatterEval se;
+                BSDFSample bs;
+                if (mediums && it.has_phase) {
+                    float f = phase_HG(dot(it.wo, wi), it.g);
+                    se.f = f3{f, f, f}; se.pdf = f; se.flags = 0;
+                    bs = phase_sample(it.g, it.wo, sampler);
+                } else {
+                    Lobe lobe = create_lobe(S, it);
+                    se = lobe_evaluate(S, lobe, it.wo, wi, false, nullptr);
+                    hemisphere_discard(se, it.wo, wi, it.ng);
+                    bs = lobe_sample(S, lobe, it.wo, sampler);
+                    hemisphere_discard(bs.eval, it.wo, bs.wi, it.ng);
+                }
                 bool is_delta = ls.eval.pdf < 0.f;
                 float weight = is_delta ? 1.f : mis_weight(ls.eval.pdf, se.pdf);
                 if (S.params.mis_mode == 1) weight = 1.f;
@@ -103,19 +140,20 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                 f3 Ld{0, 0, 0};
                 if (!occluded && se.pdf > 0.f && lpdf > 0.f) Ld = ls.eval.L * se.f * weight / lpdf;
                 if (S.params.mis_mode == 2) Ld = Ld * 0.f;
-                ret = ret + throughput * Ld;
-                eta_scale *= beta * beta;
+                ret = ret + throughput * Ld * tr;
+                eta_scale *= sqr(bs.eta);
                 float lum = max_comp(throughput);
-                if (!(be.pdf > 0.f) || lum == 0.f) break;
-                throughput = throughput * (be.f / be.pdf);
+                if (!(bs.eval.pdf > 0.f) || lum == 0.f) break;
+                throughput = throughput * (bs.eval.f / bs.eval.pdf);
                 if (eta_scale * lum < S.params.rr_threshold && bounces >= S.params.min_depth) {
                     float q = fmin_(0.95f, lum);
                     float rr = sampler.next_1d();
                     if (q < rr) break;
                     throughput = throughput / q;
                 }
-                scatter_pdf = be.pdf;
-                ray = spawn_ray(it, bwi);
+                scatter_pdf = bs.eval.pdf;
+                ray = spawn_ray(it, bs.wi);
+                if (mediums) ray_medium = dot(it.ng, bs.wi) > 0.f ? it.outside : it.inside;
             }
             last = make_float4(ret.x, ret.y, ret.z, 1.f);
             if (mode == VB_ACCUM_LERP) {
@@ -171,6 +209,8 @@ struct vb_pt_state {
     vb_light_rec *d_lights = nullptr; uint32_t n_lights = 0;
     vb_alias_entry *d_alias = nullptr; float *d_func = nullptr;
     DevTex *d_tex = nullptr; std::vector<float4 *> tex_mem;
+    DevLut luts[VB_LUT_COUNT] = {};
+    vb_medium_rec *d_mediums = nullptr; uint32_t n_mediums = 0;
     vb_camera cam{}; bool have_cam = false;
     vb_pt_params params{}; bool have_params = false;
     uint32_t w = 0, h = 0;
@@ -192,6 +232,8 @@ void vb_pt_destroy(vb_ctx *ctx) {
     cudaFree(p->d_meshes); cudaFree(p->d_inst); cudaFree(p->d_mat); cudaFree(p->d_lights); cudaFree(p->d_alias); cudaFree(p->d_func);
     cudaFree(p->d_tex);
     for (auto t : p->tex_mem) cudaFree(t);
+    for (auto &l : p->luts) cudaFree((void *)l.data);
+    cudaFree(p->d_mediums);
     cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output); cudaFree(p->d_counters);
     delete p;
     ctx->pt = nullptr;
@@ -265,12 +307,44 @@ int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n) {
     cudaSetDevice(ctx->device);
     vb_pt_state *p = pt_state(ctx);
     for (uint32_t i = 0; i < n; ++i)
-        if (mat[i].type != VB_MAT_DIFFUSE && mat[i].type != VB_MAT_BLACK_BODY)
+        if (mat[i].type == VB_MAT_PRINCIPLED || mat[i].type > VB_MAT_BLACK_BODY)
             return ctx->fail(VB_ERR_UNSUPPORTED, "vb_materials_set: material type " + std::to_string(mat[i].type) + " not implemented yet");
     cudaFree(p->d_mat); p->d_mat = nullptr; p->n_mat = n;
     if (n) {
         VB_CUDA(cudaMalloc(&p->d_mat, sizeof(vb_material_rec) * n));
         VB_CUDA(cudaMemcpy(p->d_mat, mat, sizeof(vb_material_rec) * n, cudaMemcpyHostToDevice));
+    }
+    return VB_OK;
+}
+
+int vb_luts_set(vb_ctx *ctx, int which, const float *data, uint32_t nx, uint32_t ny, uint32_t nz, uint32_t channels) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (which < 0 || which >= VB_LUT_COUNT) return ctx->fail(VB_ERR_INVALID, "vb_luts_set: unknown table");
+    cudaSetDevice(ctx->device);
+    vb_pt_state *p = pt_state(ctx);
+    cudaFree((void *)p->luts[which].data);
+    p->luts[which] = DevLut{};
+    if (!data) return VB_OK;                       // clears the table: no compensation
+    size_t n = (size_t)nx * ny * nz * channels;
+    if (n == 0) return ctx->fail(VB_ERR_INVALID, "vb_luts_set: empty table");
+    float *d = nullptr;
+    VB_CUDA(cudaMalloc(&d, n * sizeof(float)));
+    VB_CUDA(cudaMemcpy(d, data, n * sizeof(float), cudaMemcpyHostToDevice));
+    p->luts[which] = DevLut{d, nx, ny, nz, channels};
+    return VB_OK;
+}
+
+int vb_mediums_set(vb_ctx *ctx, const vb_medium_rec *med, uint32_t n) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (n && !med) return ctx->fail(VB_ERR_INVALID, "vb_mediums_set: null argument");
+    cudaSetDevice(ctx->device);
+    vb_pt_state *p = pt_state(ctx);
+    for (uint32_t i = 0; i < n; ++i)
+        if (med[i].type != VB_MEDIUM_HOMOGENEOUS) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_mediums_set: medium type not implemented");
+    cudaFree(p->d_mediums); p->d_mediums = nullptr; p->n_mediums = n;
+    if (n) {
+        VB_CUDA(cudaMalloc(&p->d_mediums, sizeof(vb_medium_rec) * n));
+        VB_CUDA(cudaMemcpy(p->d_mediums, med, sizeof(vb_medium_rec) * n, cudaMemcpyHostToDevice));
     }
     return VB_OK;
 }
@@ -310,7 +384,6 @@ int vb_integrator_set(vb_ctx *ctx, const vb_pt_params *prm) {
     if (!ctx || !prm) return VB_ERR_INVALID;
     vb_pt_state *p = pt_state(ctx);
     if (prm->spectrum != 0 || prm->sampler != 0) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_integrator_set: only srgb spectrum + independent sampler");
-    if (prm->process_mediums) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_integrator_set: mediums not implemented yet");
     p->params = *prm; p->have_params = true;
     return VB_OK;
 }
@@ -356,6 +429,14 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     S.accel = VbAccelView{ctx->accel.nodes, ctx->accel.tris};
     S.meshes = p->d_meshes; S.instances = p->d_inst; S.materials = p->d_mat; S.lights = p->d_lights; S.n_lights = p->n_lights;
     S.alias_table = p->d_alias; S.alias_func = p->d_func; S.textures = p->d_tex;
+    for (int k = 0; k < VB_LUT_COUNT; ++k) S.luts[k] = p->luts[k];
+    S.mediums = p->d_mediums;
+    if (p->params.process_mediums) {
+        auto bad = [&](uint32_t id) { return id != VB_INVALID_ID && id >= p->n_mediums; };
+        if (bad(p->cam.medium_id)) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": camera medium_id out of range");
+        for (auto &in : ctx->instances)
+            if (bad(in.inside_medium) || bad(in.outside_medium)) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": instance medium id out of range");
+    }
     S.cam = p->cam; S.params = p->params; S.width = p->w; S.height = p->h;
     if (S.params.ray_offset_factor == 0.f) S.params.ray_offset_factor = 1.f;
     uint32_t n_pix = p->w * p->h;

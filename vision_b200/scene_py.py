@@ -157,6 +157,109 @@ def load_image(path, color_space):
     return np.ascontiguousarray(im, f32)
 
 
+def _number(v, default):
+    """a Number attribute read with as_scalar(): x | [x, y] | {"node": ...} | {"type":"number","param":{"value":..}}"""
+    if v is None:
+        return float(default)
+    if isinstance(v, dict):
+        if "node" in v:
+            return _number(v["node"], default)
+        if "param" in v:
+            return _number(v["param"].get("value"), default)
+        return float(default)
+    if isinstance(v, (list, tuple)):
+        return float(v[0])
+    return float(v)
+
+
+_DATA = Path(__file__).resolve().parent / "data"
+
+
+def glass_ior(name, lam=602.785):
+    """IORCurve::eta for BK7 / LASF9 (glass.cpp:104-134) at rgb_spectrum_peak_wavelengths.x (non-spectral spectrum)"""
+    coef = {"BK7": ((1.03961212, 0.00600069867), (0.231792344, 0.0200179144), (1.01046945, 103.560653)),
+            "LASF9": ((2.00029547, 0.0121426017), (0.298926886, 0.0538736236), (1.80691843, 156.530829))}
+    c = coef.get(name, coef["BK7"])
+    l = f32(lam) / f32(1000.0)
+    l2 = f32(l * l)
+    f = f32(0)
+    acc = None
+    for b, cc in c:
+        term = f32(f32(f32(b) * l2) / f32(l2 - f32(cc)))
+        acc = term if acc is None else f32(acc + term)
+    return float(f32(np.sqrt(f32(acc + f32(1)))))
+
+
+def _material_record(m, textures, base, spectrum_complete=False):
+    """plugin -> POD record: diffuse.cpp:36-42, mirror.cpp:35-41, glass.cpp:183-238, metal.cpp:59-133, substrate.cpp:113-124"""
+    prm = m.get("param", {})
+    rec = capi.vb_material_rec()
+    t = m["type"]
+    remap = bool(prm.get("remapping_roughness", True))
+    rec.flags = 2 if remap else 0
+    rec.params[0] = _number(prm.get("anisotropic"), 0.0)
+    if t == "diffuse":
+        rec.type = capi.VB_MAT_DIFFUSE
+        rec.flags = 0
+        rec.color = _color_slot(prm.get("color", [0.5, 0.5, 0.5]), textures, base)
+        if "sigma" in prm:
+            rec.flags |= 1
+            rec.sigma = make_slot([_number(prm["sigma"], 0.5)] * 3)
+    elif t == "mirror":
+        rec.type = capi.VB_MAT_MIRROR
+        rec.color = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
+        rec.roughness = make_slot([_number(prm.get("roughness"), 0.001)] * 3)
+    elif t == "glass":
+        rec.type = capi.VB_MAT_GLASS
+        rec.color = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
+        rec.roughness = make_slot([_number(prm.get("roughness"), 0.5)] * 3)
+        name = prm.get("material_name", "")
+        ior = _number(prm.get("ior"), 1.5) if not name else glass_ior(name)
+        rec.ior = make_slot([ior] * 3)
+    elif t == "metal":
+        rec.type = capi.VB_MAT_METAL
+        rec.roughness = make_slot([_number(prm.get("roughness"), 0.01)] * 3)
+        table = json.loads((_DATA / "metal_ior_srgb.json").read_text())
+        name = prm.get("material_name", "")
+        names = sorted(table)                                  # std::map order; unknown name -> first key (metal.cpp:106-108)
+        e = table[name if name in table else names[0]]
+        rec.eta[:3] = e["eta"]; rec.k[:3] = e["k"]
+    elif t == "substrate":
+        rec.type = capi.VB_MAT_SUBSTRATE
+        rec.color = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
+        rec.spec = _color_slot(prm.get("spec", [0.05, 0.05, 0.05]), textures, base)
+        rec.roughness = make_slot([_number(prm.get("roughness"), 0.5)] * 3)
+    else:
+        return None
+    return rec
+
+
+def _medium_records(d):
+    """MediumsDesc (scene_desc.cpp:24-34) + MediumDesc::init (node_desc.cpp:182-197) + HomogeneousMedium ctor"""
+    md = d.get("mediums")
+    if not md:
+        return [], {}, False, ""
+    lst, process, glob = (md, False, "") if isinstance(md, list) else (md.get("list", []), bool(md.get("process", False)), md.get("global", ""))
+    table = json.loads((_DATA / "medium_scatter.json").read_text())
+    recs, index = [], {}
+    for m in lst:
+        prm = m.get("param", {})
+        r = capi.vb_medium_rec()
+        r.type = 0
+        name = prm.get("medium_name", "")
+        if name:
+            e = table.get(name) or next(iter(table.values()))
+            ss, sa = e["sigma_s"], e["sigma_a"]
+        else:
+            ss, sa = prm.get("sigma_s", [0, 0, 0]), prm.get("sigma_a", [0, 0, 0])
+        r.sigma_s[:3] = [float(f32(x)) for x in ss]; r.sigma_a[:3] = [float(f32(x)) for x in sa]
+        r.scale = float(f32(_number(prm.get("scale"), 0.0)))
+        r.g = float(f32(min(max(_number(prm.get("g"), 0.0), -0.99), 0.99)))
+        index[m.get("name", "")] = len(recs)
+        recs.append(r)
+    return recs, index, process, glob
+
+
 def build_scene(path, overrides=None) -> SceneRecords:
     """overrides: dict with optional keys resolution, max_depth, min_depth, spp, shape_material {name: mat}, drop_lights"""
     ov = overrides or {}
@@ -166,14 +269,18 @@ def build_scene(path, overrides=None) -> SceneRecords:
     # materials (Scene::load_materials)
     mat_index = {}
     for m in d.get("materials", []):
-        rec = capi.vb_material_rec()
-        if m["type"] != "diffuse":
-            mat_index[m["name"]] = None          # present but unsupported by this python twin
+        rec = _material_record(m, sc.textures, base)
+        if rec is None:
+            mat_index[m["name"]] = None          # present but unsupported (principled_bsdf, mix, ...)
             continue
-        rec.type = capi.VB_MAT_DIFFUSE
-        rec.color = _color_slot(m["param"].get("color", [0.5, 0.5, 0.5]), sc.textures, base)
         mat_index.setdefault(m["name"], len(sc.materials))
         sc.materials.append(rec)
+    if any(r.type in (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL) for r in sc.materials) and ov.get("luts", True):
+        sc.luts = capi.load_luts()
+    sc.mediums, med_index, process_mediums, global_medium = _medium_records(d)
+    if "process_mediums" in ov:
+        process_mediums = ov["process_mediums"]
+    gm = med_index.get(global_medium, VB_INVALID_ID)
     # shapes -> meshes, instances, area lights (Scene::load_shapes / add_shape)
     for sh in d["shapes"]:
         prm = sh["param"]
@@ -184,11 +291,16 @@ def build_scene(path, overrides=None) -> SceneRecords:
         else:
             raise NotImplementedError(sh["type"])
         mat_name = ov.get("shape_material", {}).get(sh["name"], prm.get("material"))
-        mid = mat_index.get(mat_name)
-        if mid is None:
+        if mat_name in mat_index and mat_index[mat_name] is None:
             raise NotImplementedError(f"material {mat_name} of {sh['name']}")
+        mid = mat_index.get(mat_name, VB_INVALID_ID)                # unknown / empty name: no material (medium boundary)
         o2w = np.asarray(prm["transform"]["param"]["matrix4x4"], f32).reshape(-1)   # JSON rows are columns
         inst = {"mesh_id": len(sc.meshes), "material_id": mid, "light_id": VB_INVALID_ID, "o2w": o2w}
+        if "medium" in prm:                                       # ShapeGroup::post_init, shape.cpp:245-270
+            inst["inside_medium"] = med_index.get(prm["medium"].get("inside", ""), VB_INVALID_ID)
+            inst["outside_medium"] = med_index.get(prm["medium"].get("outside", ""), VB_INVALID_ID)
+        else:
+            inst["inside_medium"] = inst["outside_medium"] = gm
         sc.meshes.append(mesh)
         em = prm.get("emission")
         if em:
@@ -228,7 +340,9 @@ def build_scene(path, overrides=None) -> SceneRecords:
     sc.camera.tan_fov_y_over_2 = float(f32(math.tan(math.radians(float(f32(cam.get("fov_y", 20.0)))) * 0.5)))
     sc.camera.lens_radius = float(cam.get("lens_radius", 0.0))
     sc.camera.focal_distance = float(cam.get("focal_distance", 5.0))
-    sc.camera.medium_id = VB_INVALID_ID
+    # Photosensory ctor (photosensory.cpp:15-33): only when mediums are processed; named medium or the global one
+    sc.camera.medium_id = (med_index.get(cam["medium"], VB_INVALID_ID) if "medium" in cam else gm) if process_mediums else VB_INVALID_ID
+    sc.params.process_mediums = 1 if process_mediums else 0
     ratio = f32(sc.resolution[0]) * f32(1.0) / f32(sc.resolution[1])
     lo, hi = [-1.0, -1.0], [1.0, 1.0]
     if ratio > 1.0:
