@@ -1,0 +1,61 @@
+// ORACLE — test infrastructure only (see vo_math.h header). PARITY UNPINNED.
+// extern "C" probes of the BSDF building blocks for the CPU unit tests (tests/test_oracle_bsdf.py).
+// Included at the end of vo_pt.cpp so that it sees the file-local lobe code.
+extern "C" {
+
+float vo_probe_fresnel_dielectric(float c, float eta) { return vo::fresnel_dielectric(c, eta); }
+float vo_probe_fresnel_complex(float c, float eta, float k) { return vo::fresnel_complex(c, eta, k); }
+int vo_probe_refract(const float *wi, const float *n, float eta, float *wt) {
+    vo::float3 t{0, 0, 0};
+    bool ok = vo::refract({wi[0], wi[1], wi[2]}, {n[0], n[1], n[2]}, eta, t);
+    wt[0] = t.x; wt[1] = t.y; wt[2] = t.z;
+    return ok ? 1 : 0;
+}
+void vo_probe_reflect(const float *wo, const float *n, float *out) {
+    vo::float3 r = vo::reflect({wo[0], wo[1], wo[2]}, {n[0], n[1], n[2]});
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+// out: D(wh), G(wo,wi), pdf_wh(wo,wh), lambda(wo)
+void vo_probe_ggx(float ax, float ay, const float *wo, const float *wi, const float *wh, float *out) {
+    vo::GGX m{ax, ay};
+    vo::float3 o{wo[0], wo[1], wo[2]}, i{wi[0], wi[1], wi[2]}, h{wh[0], wh[1], wh[2]};
+    out[0] = vo::ggx_D(m, h); out[1] = vo::ggx_G(m, o, i); out[2] = vo::ggx_pdf_wh(m, o, h); out[3] = vo::ggx_lambda(m, o);
+}
+void vo_probe_ggx_sample_wh(float ax, float ay, const float *wo, float u0, float u1, float *wh) {
+    vo::float3 h = vo::ggx_sample_wh(vo::GGX{ax, ay}, {wo[0], wo[1], wo[2]}, vo::float2{u0, u1});
+    wh[0] = h.x; wh[1] = h.y; wh[2] = h.z;
+}
+
+// Evaluates / samples material `mat_id` of a scene at a canonical interaction: position 0, geometric and
+// shading normal +z, tangent +x, uv (0.5,0.5); wo/wi in world = local space.
+static vo::Interaction probe_interaction(uint32_t mat_id, const float *wo) {
+    vo::Interaction it;
+    it.pos = {0, 0, 0}; it.ng = {0, 0, 1}; it.uv = {0.5f, 0.5f};
+    it.shading = vo::Frame{{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    it.wo = {wo[0], wo[1], wo[2]};
+    it.mat_id = mat_id;
+    return it;
+}
+// out: f.xyz (already times |cos wi|), pdf, flags
+void vo_probe_bsdf_eval(void *scene, uint32_t mat_id, const float *wo, const float *wi, float *out) {
+    const vo::Scene &sc = *(const vo::Scene *)scene;
+    vo::Interaction it = probe_interaction(mat_id, wo);
+    vo::Evaluator ev{vo::create_lobe(sc, it), it.ng};
+    vo::ScatterEval se = ev.evaluate(sc, it.wo, {wi[0], wi[1], wi[2]});
+    out[0] = se.f.x; out[1] = se.f.y; out[2] = se.f.z; out[3] = se.pdf; out[4] = (float)se.flags;
+}
+// n samples with the LCG seeded by `state`; out per sample: wi.xyz, f.xyz, pdf, eta  (8 floats)
+void vo_probe_bsdf_sample(void *scene, uint32_t mat_id, const float *wo, uint32_t state, uint32_t n, float *out) {
+    const vo::Scene &sc = *(const vo::Scene *)scene;
+    vo::Interaction it = probe_interaction(mat_id, wo);
+    vo::Evaluator ev{vo::create_lobe(sc, it), it.ng};
+    vo::Sampler sampler; sampler.state = state;
+    for (uint32_t k = 0; k < n; ++k) {
+        vo::BSDFSample bs = ev.sample(sc, it.wo, sampler);
+        float *o = out + 8 * (size_t)k;
+        o[0] = bs.wi.x; o[1] = bs.wi.y; o[2] = bs.wi.z; o[3] = bs.eval.f.x; o[4] = bs.eval.f.y; o[5] = bs.eval.f.z;
+        o[6] = bs.eval.pdf; o[7] = bs.eta;
+    }
+}
+
+}  // extern "C"

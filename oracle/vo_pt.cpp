@@ -204,3 +204,4 @@ bool Scene::trace_any(const Ray &r, PathStats *st) const {
 }  // namespace vo
 
 #include "vo_pt_li.inl"
+#include "vo_probe.inl"

@@ -54,6 +54,36 @@ def test_host_records_equal_python_twin():
     assert any("denoiser" in s or "ignored" in s for s in hp.log()) or True
 
 
+@pytest.mark.parametrize("name", ["cbox_materials", "cbox_fog"])
+def test_host_records_equal_python_twin_materials_and_mediums(name):
+    """mirror / glass / metal / substrate plugins, homogeneous medium, per-shape and global medium ids, LUT loading"""
+    path = ROOT / "scenes" / "cbox" / f"{name}.json"
+    hp = host_api.HostPipeline(path)
+    hp.prepare_records()
+    a = hp.records()
+    b = scene_py.build_scene(path)
+    assert [m.type for m in a.materials] == [m.type for m in b.materials]
+    for ma, mb in zip(a.materials, b.materials):
+        assert _bytes(ma) == _bytes(mb), ma.type
+    assert [_bytes(x) for x in a.mediums] == [_bytes(x) for x in b.mediums]
+    for ia, ib in zip(a.instances, b.instances):
+        for k in ("material_id", "light_id", "inside_medium", "outside_medium"):
+            assert ia[k] == ib.get(k, capi.VB_INVALID_ID), k
+    assert _bytes(a.params) == _bytes(b.params)
+    assert a.camera.medium_id == b.camera.medium_id
+    assert sorted(a.luts) == sorted(b.luts)
+    for k in a.luts:
+        assert a.luts[k][1] == b.luts[k][1] and np.array_equal(a.luts[k][0], b.luts[k][0])
+    if name == "cbox_fog":
+        assert a.params.process_mediums == 1 and a.camera.medium_id == 1 and len(a.mediums) == 2
+        assert a.instances[5]["inside_medium"] == 0 and a.instances[5]["outside_medium"] == 1 and a.instances[0]["inside_medium"] == 1
+        np.testing.assert_allclose(list(a.mediums[0].sigma_s)[:3], [0.74, 0.88, 1.01], rtol=1e-6)     # Skin1
+    names = host_api.plugin_names()
+    for want in ("vision-material-mirror#constructor", "vision-material-glass#constructor", "vision-material-metal#constructor",
+                 "vision-material-substrate#constructor", "vision-medium-homogeneous#constructor"):
+        assert want in names, want
+
+
 def test_desc_defaults_and_errors(tmp_path):
     p = tmp_path / "s.json"
     p.write_text('{ // comment\n "shapes": [ {"type":"quad","name":"q","param":{"material":"m"}} ], /* c */ "materials": [ {"type":"diffuse","name":"m","param":{}} ], "camera": {"param": {"transform": {"type":"look_at","param":{"position":[0,0,5],"target_pos":[0,0,0]}}, "filter": {"type":"box"}}} }')
@@ -71,7 +101,8 @@ def test_desc_defaults_and_errors(tmp_path):
 
 
 @pytest.mark.gpu
-def test_host_pipeline_renders_like_python_path(vbctx):
+@pytest.mark.parametrize("SCENE", [SCENE, ROOT / "scenes" / "cbox" / "cbox_materials.json", ROOT / "scenes" / "cbox" / "cbox_fog.json"])
+def test_host_pipeline_renders_like_python_path(vbctx, SCENE):
     hp = host_api.HostPipeline(SCENE)
     hp.prepare(0)
     hp.render(4)

@@ -104,6 +104,23 @@ void ShapeDesc::init(const ParameterSet &ps) {
     parameter = ps["param"];
     o2w.init(parameter.value("transform"));
     if (parameter.contains("emission")) { emission.init(parameter["emission"]); has_emission = true; }
+    if (parameter.contains("medium")) {
+        has_medium = true;
+        inside_medium = parameter["medium"]["inside"].as_string();
+        outside_medium = parameter["medium"]["outside"].as_string();
+    }
+}
+void MediumDesc::init(const ParameterSet &ps) { init_common(ps); sub_type = ps["type"].as_string("homogeneous"); parameter = ps.value("param"); }
+void MediumsDesc::init(const Json &data) {
+    // scene_desc.cpp:26-34: "process" defaults to TRUE; a missing key behaves like an empty object. A bare
+    // list (res/cbox-glass.json) carries no "list" key: nothing is loaded.
+    process = true;
+    if (!data.is_object()) return;
+    ParameterSet ps(data);
+    process = ps["process"].as_bool(true);
+    global = ps["global"].as_string("");
+    const Json &l = data.at("list");
+    if (l.is_array()) for (auto &e : l.arr) { MediumDesc d; d.init(ParameterSet(e)); mediums.push_back(d); }
 }
 void MaterialDesc::init(const ParameterSet &ps) { init_common(ps); sub_type = ps["type"].as_string("diffuse"); parameter = ps["param"]; }
 void SamplerDesc::init(const ParameterSet &ps) { init_common(ps); sub_type = ps["type"].as_string("independent"); parameter = ps.value("param"); }
@@ -143,7 +160,8 @@ void SceneDesc::init(const Json &data) {
     const Json &mats = data.at("materials");
     if (mats.is_array()) for (auto &m : mats.arr) { MaterialDesc d; d.init(ParameterSet(m)); material_descs.push_back(d); }
     const Json &med = data.at("mediums");
-    process_mediums = med.is_object() && ParameterSet(med)["process"].as_bool(false);
+    mediums_desc.init(med);
+    process_mediums = mediums_desc.process;
     const Json &shapes = data.at("shapes");
     if (shapes.is_array()) for (auto &s : shapes.arr) { ShapeDesc d; d.init(ParameterSet(s)); shape_descs.push_back(d); }
     sensor_desc.init(root.value("camera"));

@@ -57,7 +57,16 @@ struct TransformDesc : NodeDesc { Mat4 mat = mat4_identity(); TransformDesc() : 
 struct FilterDesc : NodeDesc { FilterDesc() : NodeDesc("Filter") {} void init(const ParameterSet &ps); };
 struct ToneMapperDesc : NodeDesc { ToneMapperDesc() : NodeDesc("ToneMapper") {} void init(const ParameterSet &ps); };
 struct LightDesc : NodeDesc { TransformDesc o2w; LightDesc() : NodeDesc("Light") {} void init(const ParameterSet &ps); bool valid() const { return !sub_type.empty() && !parameter.data().is_null(); } };
-struct ShapeDesc : NodeDesc { TransformDesc o2w; LightDesc emission; bool has_emission = false; ShapeDesc() : NodeDesc("Shape") {} void init(const ParameterSet &ps); };
+struct ShapeDesc : NodeDesc {
+    TransformDesc o2w; LightDesc emission; bool has_emission = false;
+    bool has_medium = false; std::string inside_medium, outside_medium;      // "medium": {"inside","outside"} (shape.cpp:247-249)
+    ShapeDesc() : NodeDesc("Shape") {}
+    void init(const ParameterSet &ps);
+};
+// reference node_desc.cpp:182-197 (medium_name looks up the measured table, medium_scatter_data.h)
+struct MediumDesc : NodeDesc { MediumDesc() : NodeDesc("Medium") {} void init(const ParameterSet &ps); };
+// reference scene_desc.cpp:24-34: "mediums": {"process", "global", "list": [...]}
+struct MediumsDesc { bool process = false; std::string global; std::vector<MediumDesc> mediums; void init(const Json &data); };
 struct MaterialDesc : NodeDesc { MaterialDesc() : NodeDesc("Material") {} void init(const ParameterSet &ps); };
 struct SamplerDesc : NodeDesc { SamplerDesc() : NodeDesc("Sampler") {} void init(const ParameterSet &ps); };
 struct SensorDesc : NodeDesc { TransformDesc transform_desc; FilterDesc filter_desc; SensorDesc() : NodeDesc("Sensor") {} void init(const ParameterSet &ps); };
@@ -76,6 +85,7 @@ struct SceneDesc {
     IntegratorDesc integrator_desc; SpectrumDesc spectrum_desc; LightSamplerDesc light_sampler_desc; SamplerDesc sampler_desc;
     WarperDesc warper_desc; std::vector<MaterialDesc> material_descs; std::vector<ShapeDesc> shape_descs;
     SensorDesc sensor_desc; OutputDesc output_desc; RenderSettingDesc render_setting; PipelineDesc pipeline_desc;
+    MediumsDesc mediums_desc;
     bool process_mediums = false;
     std::vector<std::string> ignored_keys;     // keys present in the file that this path does not consume (logged)
     void init(const Json &data);

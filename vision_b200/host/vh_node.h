@@ -89,6 +89,8 @@ struct ShapeInstance {             // reference src/base/shape.h:148-192
     std::string name, material_name;
     std::shared_ptr<Material> material;
     std::shared_ptr<Light> emission;
+    bool has_medium = false;                         // shape desc carried a "medium" block
+    std::string inside_name, outside_name;
 };
 
 class ShapeGroup : public Node {   // quad / cube / sphere / model
@@ -110,6 +112,17 @@ public:
     explicit Material(const MaterialDesc &) {}
     virtual void fill_record(vb_material_rec &rec, const SlotContext &ctx) const = 0;
 };
+
+class Medium : public Node {       // reference src/base/scattering/medium.h:23-50
+public:
+    using Desc = MediumDesc;
+    uint32_t index = VB_INVALID_ID;
+    explicit Medium(const MediumDesc &) {}
+    virtual void fill_record(vb_medium_rec &rec) const = 0;
+};
+
+// numeric data shipped under vision_b200/data (tools/extract_*.py); directory of this library + "/data"
+std::string data_dir();
 
 class Light : public Node {
 public:
@@ -149,6 +162,7 @@ public:
     float3 position{0, 0, 0};
     float focal_distance = 5.f, lens_radius = 0.f;
     std::shared_ptr<Filter> filter;
+    bool has_medium_name = false; std::string medium_name;   // photosensory.cpp:15-33
     explicit Sensor(const SensorDesc &desc);
     void update_mat(const Mat4 &m);                   // sensor.cpp:73-78
     Mat4 camera_to_world() const;                     // sensor.cpp:153-162

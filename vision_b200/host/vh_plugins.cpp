@@ -45,6 +45,8 @@ void ShapeGroup::post_init(const ShapeDesc &desc) {
         instances[i]->material_name = mat;
         instances[i]->o2w = desc.o2w.mat;
         instances[i]->name = name_ + "_" + std::to_string(i);
+        instances[i]->has_medium = desc.has_medium;
+        instances[i]->inside_name = desc.inside_medium; instances[i]->outside_name = desc.outside_medium;
     }
 }
 
@@ -127,6 +129,10 @@ static vb_slot make_slot(const ParameterSet &ps, float3 def, const SlotContext &
 }
 
 // ---- materials ---------------------------------------------------------------------------------
+static void init_material_record(vb_material_rec &r) {     // unused slots: zero constant, no texture
+    std::memset(&r, 0, sizeof(r));
+    r.color.tex_id = r.roughness.tex_id = r.spec.tex_id = r.ior.tex_id = r.sigma.tex_id = VB_INVALID_ID;
+}
 // reference src/render_core/material/diffuse.cpp:12-52
 class DiffuseMaterial : public Material {
     MaterialDesc desc_;
@@ -134,7 +140,7 @@ public:
     explicit DiffuseMaterial(const MaterialDesc &d) : Material(d), desc_(d) { name_ = d.name; }
     std::string impl_type() const override { return "diffuse"; }
     void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
-        std::memset(&r, 0, sizeof(r));
+        init_material_record(r);
         r.type = VB_MAT_DIFFUSE;
         r.color = make_slot(desc_["color"], {0.5f, 0.5f, 0.5f}, ctx);
         if (desc_.has_attr("sigma")) { r.flags |= 1u; r.sigma = make_slot(desc_["sigma"], {0.5f, 0.5f, 0.5f}, ctx); }
@@ -142,12 +148,127 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(DiffuseMaterial, material, diffuse, constructor)
 
+// common part of the microfacet materials: roughness / anisotropic Number slots, remapping_roughness flag
+static void fill_microfacet_common(vb_material_rec &r, const MaterialDesc &d, float default_roughness, const SlotContext &ctx) {
+    init_material_record(r);
+    r.flags = d["remapping_roughness"].as_bool(true) ? 2u : 0u;
+    float rough = make_slot(d["roughness"], {default_roughness, default_roughness, default_roughness}, ctx).value[0];
+    r.roughness = vb_slot{{rough, rough, rough, 1.f}, VB_INVALID_ID, {0, 0, 0}};
+    r.params[0] = make_slot(d["anisotropic"], {0.f, 0.f, 0.f}, ctx).value[0];
+}
+
+// reference src/render_core/material/mirror.cpp:18-75
+class MirrorMaterial : public Material {
+    MaterialDesc desc_;
+public:
+    explicit MirrorMaterial(const MaterialDesc &d) : Material(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "mirror"; }
+    void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
+        fill_microfacet_common(r, desc_, 0.001f, ctx);
+        r.type = VB_MAT_MIRROR;
+        r.color = make_slot(desc_["color"], {1.f, 1.f, 1.f}, ctx);
+    }
+};
+VH_MAKE_CLASS_CREATOR(MirrorMaterial, material, mirror, constructor)
+
+// reference src/render_core/material/glass.cpp:104-134 (Sellmeier curves), :165-257
+class GlassMaterial : public Material {
+    MaterialDesc desc_;
+    static float curve(const std::string &name, float lambda) {
+        static const float bk7[6] = {1.03961212f, 0.00600069867f, 0.231792344f, 0.0200179144f, 1.01046945f, 103.560653f};
+        static const float lasf9[6] = {2.00029547f, 0.0121426017f, 0.298926886f, 0.0538736236f, 1.80691843f, 156.530829f};
+        const float *c = name == "LASF9" ? lasf9 : bk7;            // unknown names fall back to BK7 (glass.cpp:150-155)
+        float l = lambda / 1000.f, l2 = l * l;
+        float f = c[0] * l2 / (l2 - c[1]) + c[2] * l2 / (l2 - c[3]) + c[4] * l2 / (l2 - c[5]);
+        return std::sqrt(f + 1.f);
+    }
+public:
+    explicit GlassMaterial(const MaterialDesc &d) : Material(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "glass"; }
+    void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
+        fill_microfacet_common(r, desc_, 0.5f, ctx);
+        r.type = VB_MAT_GLASS;
+        r.color = make_slot(desc_["color"], {1.f, 1.f, 1.f}, ctx);
+        std::string name = desc_["material_name"].as_string();
+        // non-spectral spectrum: the curve is evaluated at rgb_spectrum_peak_wavelengths.x (glass.cpp:225-229)
+        float ior = name.empty() ? make_slot(desc_["ior"], {1.5f, 1.5f, 1.5f}, ctx).value[0] : curve(name, 602.785f);
+        r.ior = vb_slot{{ior, ior, ior, 1.f}, VB_INVALID_ID, {0, 0, 0}};
+    }
+};
+VH_MAKE_CLASS_CREATOR(GlassMaterial, material, glass, constructor)
+
+// reference src/render_core/material/metal.cpp:39-157; complex ior of the named metal at the three sRGB peak
+// wavelengths (metal_ior.h / SPD::eval) precomputed into data/metal_ior_srgb.json by tools/extract_metal_ior.py
+class MetalMaterial : public Material {
+    MaterialDesc desc_;
+public:
+    explicit MetalMaterial(const MaterialDesc &d) : Material(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "metal"; }
+    void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
+        fill_microfacet_common(r, desc_, 0.01f, ctx);
+        r.type = VB_MAT_METAL;
+        Json table = Json::parse_file(data_dir() + "/metal_ior_srgb.json");
+        std::string name = desc_["material_name"].as_string();
+        if (!table.contains(name)) {                               // metal.cpp:106-108: unknown -> first key of the (sorted) map
+            std::vector<std::string> keys;
+            for (auto &kv : table.obj) keys.push_back(kv.first);
+            std::sort(keys.begin(), keys.end());
+            name = keys.front();
+        }
+        const Json &e = table.at(name);
+        for (int i = 0; i < 3; ++i) { r.eta[i] = (float)e.at("eta").arr[i].num; r.k[i] = (float)e.at("k").arr[i].num; }
+    }
+};
+VH_MAKE_CLASS_CREATOR(MetalMaterial, material, metal, constructor)
+
+// reference src/render_core/material/substrate.cpp:92-150
+class SubstrateMaterial : public Material {
+    MaterialDesc desc_;
+public:
+    explicit SubstrateMaterial(const MaterialDesc &d) : Material(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "substrate"; }
+    void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
+        fill_microfacet_common(r, desc_, 0.5f, ctx);
+        r.type = VB_MAT_SUBSTRATE;
+        r.color = make_slot(desc_["color"], {1.f, 1.f, 1.f}, ctx);
+        r.spec = make_slot(desc_["spec"], {0.05f, 0.05f, 0.05f}, ctx);
+    }
+};
+VH_MAKE_CLASS_CREATOR(SubstrateMaterial, material, substrate, constructor)
+
+// reference src/render_core/medium/homogeneous.cpp:11-28 + MediumDesc::init (node_desc.cpp:182-197)
+class HomogeneousMedium : public Medium {
+    MediumDesc desc_;
+public:
+    explicit HomogeneousMedium(const MediumDesc &d) : Medium(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "homogeneous"; }
+    void fill_record(vb_medium_rec &r) const override {
+        std::memset(&r, 0, sizeof(r));
+        r.type = VB_MEDIUM_HOMOGENEOUS;
+        std::string mn = desc_["medium_name"].as_string();
+        float3 ss{0, 0, 0}, sa{0, 0, 0};
+        if (!mn.empty()) {
+            Json table = Json::parse_file(data_dir() + "/medium_scatter.json");
+            const Json *e = table.contains(mn) ? &table.at(mn) : nullptr;
+            if (!e && !table.obj.empty()) e = &table.obj.front().second;                    // get_sigma falls back to entry 0
+            if (e) { auto f = [&](const char *k, int i) { return (float)e->at(k).arr[i].num; };
+                     ss = {f("sigma_s", 0), f("sigma_s", 1), f("sigma_s", 2)}; sa = {f("sigma_a", 0), f("sigma_a", 1), f("sigma_a", 2)}; }
+        } else {
+            ss = desc_["sigma_s"].as_float3({0, 0, 0}); sa = desc_["sigma_a"].as_float3({0, 0, 0});
+        }
+        r.sigma_s[0] = ss.x; r.sigma_s[1] = ss.y; r.sigma_s[2] = ss.z; r.sigma_a[0] = sa.x; r.sigma_a[1] = sa.y; r.sigma_a[2] = sa.z;
+        r.scale = desc_["scale"].as_float(0.f);
+        r.g = std::min(0.99f, std::max(-0.99f, desc_["g"].as_float(0.f)));
+    }
+};
+VH_MAKE_CLASS_CREATOR(HomogeneousMedium, medium, homogeneous, constructor)
+
 // reference src/render_core/material/black_body.cpp (material of light-created geometry, area.cpp:55-68)
 class BlackBodyMaterial : public Material {
 public:
     explicit BlackBodyMaterial(const MaterialDesc &d) : Material(d) { name_ = d.name; }
     std::string impl_type() const override { return "black_body"; }
-    void fill_record(vb_material_rec &r, const SlotContext &) const override { std::memset(&r, 0, sizeof(r)); r.type = VB_MAT_BLACK_BODY; r.color.tex_id = VB_INVALID_ID; }
+    void fill_record(vb_material_rec &r, const SlotContext &) const override { init_material_record(r); r.type = VB_MAT_BLACK_BODY; }
 };
 VH_MAKE_CLASS_CREATOR(BlackBodyMaterial, material, black_body, constructor)
 

@@ -49,6 +49,7 @@ Sensor::Sensor(const SensorDesc &desc) {
     fov_y = std::min(120.f, std::max(15.f, desc["fov_y"].as_float(20.f)));
     focal_distance = desc["focal_distance"].as_float(5.f);
     lens_radius = desc["lens_radius"].as_float(0.f);
+    has_medium_name = desc.has_attr("medium"); medium_name = desc["medium"].as_string();
     update_mat(desc.transform_desc.mat);
     filter = create_shared<Filter>(desc.filter_desc);
 }

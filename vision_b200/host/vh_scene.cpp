@@ -5,6 +5,7 @@
 #include <cstring>
 #include <fstream>
 #include <map>
+#include <dlfcn.h>
 
 namespace vh {
 
@@ -73,6 +74,23 @@ uint32_t ImagePool::obtain(const std::string &path, const std::string &color_spa
     return (uint32_t)images.size() - 1;
 }
 
+// directory of libvision_host.so (or of the executable that linked the sources statically) + "/data"
+std::string data_dir() {
+    if (const char *e = getenv("VISION_B200_DATA")) return e;
+    Dl_info info;
+    std::string p = dladdr((void *)&data_dir, &info) && info.dli_fname ? info.dli_fname : ".";
+    size_t s = p.find_last_of('/');
+    return (s == std::string::npos ? std::string(".") : p.substr(0, s)) + "/data";
+}
+static void load_lut(SceneRecords::Lut &l, const std::string &file, uint32_t nx, uint32_t ny, uint32_t nz, uint32_t ch) {
+    std::ifstream f(data_dir() + "/" + file, std::ios::binary);
+    if (!f) throw std::runtime_error("cannot open " + data_dir() + "/" + file + " (tools/extract_luts.py writes it)");
+    l.nx = nx; l.ny = ny; l.nz = nz; l.channels = ch;
+    l.data.resize((size_t)nx * ny * nz * ch);
+    f.read((char *)l.data.data(), l.data.size() * 4);
+    if ((size_t)f.gcount() != l.data.size() * 4) throw std::runtime_error("short read: " + file);
+}
+
 // ---- scene -------------------------------------------------------------------------------------
 std::shared_ptr<Material> Scene::obtain_black_body() {
     if (!black_body) { MaterialDesc d; d.sub_type = "black_body"; d.name = "__black_body"; black_body = create_shared<Material>(d); materials.push_back(black_body); }
@@ -87,7 +105,10 @@ void Scene::init(const SceneDesc &d) {
     for (const LightDesc &ld : d.light_sampler_desc.light_descs) light_sampler->add_light(create_shared<Light>(ld));
     spectrum = create_shared<Spectrum>(d.spectrum_desc);
     for (const MaterialDesc &md : d.material_descs) materials.push_back(create_shared<Material>(md));
-    if (d.process_mediums) throw std::runtime_error("mediums.process = true: not implemented on this path yet");
+    // MediumRegistry::load_mediums (registries.cpp:196-210)
+    process_mediums = d.mediums_desc.process;
+    for (const MediumDesc &md : d.mediums_desc.mediums) { auto m = create_shared<Medium>(md); m->index = (uint32_t)mediums.size(); mediums.push_back(m); }
+    for (auto &m : mediums) if (m->name() == d.mediums_desc.global) { global_medium = m; break; }
     frame_buffer = create_shared<FrameBuffer>(d.pipeline_desc.frame_buffer_desc);
     sensor = create_shared<Sensor>(d.sensor_desc);
     for (const ShapeDesc &sd : d.shape_descs) add_shape(create_shared<ShapeGroup>(sd), sd);
@@ -131,26 +152,48 @@ void Scene::prepare(SceneRecords &out) {
     for (auto &m : materials) m->fill_record(out.materials[m->index], sctx);
     std::map<uint64_t, uint32_t> mesh_ids;
     for (auto &i : instances) {
-        if (!i->material) throw std::runtime_error("instance " + i->name + ": material '" + i->material_name + "' not found");
+        bool known_name = false;
+        for (const MaterialDesc &md : desc.material_descs) known_name |= md.name == i->material_name;
+        if (!i->material && known_name) throw std::runtime_error("instance " + i->name + ": material '" + i->material_name + "' not available");
         uint64_t h = i->mesh->hash();
         auto f = mesh_ids.find(h);
         if (f == mesh_ids.end()) { f = mesh_ids.emplace(h, (uint32_t)out.meshes.size()).first; out.meshes.push_back(i->mesh); }
         vb_instance r{};
-        r.mesh_id = f->second; r.material_id = i->material->index; r.light_id = i->emission ? i->emission->index : VB_INVALID_ID;
-        r.inside_medium = r.outside_medium = r.lightmap_id = VB_INVALID_ID;
+        r.mesh_id = f->second; r.material_id = i->material ? i->material->index : VB_INVALID_ID;     // no material: medium boundary only
+        r.light_id = i->emission ? i->emission->index : VB_INVALID_ID;
+        r.lightmap_id = VB_INVALID_ID;
+        auto medium_index = [&](const std::string &nm) { for (auto &m : mediums) if (m->name() == nm) return m->index; return (uint32_t)VB_INVALID_ID; };
+        if (i->has_medium) { r.inside_medium = medium_index(i->inside_name); r.outside_medium = medium_index(i->outside_name); }   // shape.cpp:247-258
+        else r.inside_medium = r.outside_medium = global_medium ? global_medium->index : VB_INVALID_ID;                         // shape.cpp:259-268
         std::memcpy(r.o2w, i->o2w.data(), 64);
         out.instances.push_back(r);
     }
     out.lights.resize(light_sampler->lights.size());
     for (auto &l : light_sampler->lights) l->fill_record(out.lights[l->index], *this, sctx, out.alias_table, out.alias_func);
     out.textures = image_pool.images;
+    out.mediums.resize(mediums.size());
+    for (auto &m : mediums) m->fill_record(out.mediums[m->index]);
+    bool need_luts = false;
+    for (auto &m : out.materials) need_luts |= m.type == VB_MAT_MIRROR || m.type == VB_MAT_GLASS || m.type == VB_MAT_METAL;
+    if (need_luts) {             // PureReflectionLobe::prepare / DielectricLobe::prepare (lobe.cpp:253-260,731-735)
+        load_lut(out.luts[VB_LUT_PURE_REFLECTION], "lut_pure_reflection_32x32x1x1.f32", 32, 32, 1, 1);
+        load_lut(out.luts[VB_LUT_DIELECTRIC], "lut_dielectric_32x32x32x2.f32", 32, 32, 32, 2);
+        load_lut(out.luts[VB_LUT_DIELECTRIC_INV], "lut_dielectric_inv_32x32x32x2.f32", 32, 32, 32, 2);
+    }
     out.width = frame_buffer->width; out.height = frame_buffer->height;
     sensor->fill_record(out.camera, out.width, out.height);
+    // the flag only matters when some medium exists (all ids are invalid otherwise): keep the kernel's fast path
+    bool mediums_on = process_mediums && !mediums.empty();
+    out.camera.medium_id = VB_INVALID_ID;               // Photosensory ctor, photosensory.cpp:15-33
+    if (mediums_on) {
+        if (sensor->has_medium_name) { for (auto &m : mediums) if (m->name() == sensor->medium_name) out.camera.medium_id = m->index; }
+        else if (global_medium) out.camera.medium_id = global_medium->index;
+    }
     out.params = vb_pt_params{};
     out.params.max_depth = integrator->max_depth; out.params.min_depth = integrator->min_depth;
     out.params.rr_threshold = integrator->rr_threshold; out.params.mis_mode = integrator->mis_mode;
     out.params.spectrum = spectrum->device_tag(); out.params.sampler = sampler->device_tag();
-    out.params.process_mediums = 0; out.params.ray_offset_factor = desc.render_setting.ray_offset_factor;
+    out.params.process_mediums = mediums_on ? 1u : 0u; out.params.ray_offset_factor = desc.render_setting.ray_offset_factor;
     out.spp = desc.output_desc.spp ? desc.output_desc.spp : sampler->spp;
     out.exposure = frame_buffer->exposure; out.tonemap = frame_buffer->tone_mapper->device_tag();
 }
@@ -180,6 +223,11 @@ void Pipeline::prepare(int device) {
     for (auto &t : records.textures) tex.push_back(vb_texture{t.rgba.data(), t.w, t.h});
     check(vb_textures_set(ctx, tex.data(), (uint32_t)tex.size()), "vb_textures_set");
     check(vb_materials_set(ctx, records.materials.data(), (uint32_t)records.materials.size()), "vb_materials_set");
+    for (int k = 0; k < VB_LUT_COUNT; ++k) {
+        const SceneRecords::Lut &l = records.luts[k];
+        check(vb_luts_set(ctx, k, l.data.empty() ? nullptr : l.data.data(), l.nx, l.ny, l.nz, l.channels), "vb_luts_set");
+    }
+    check(vb_mediums_set(ctx, records.mediums.data(), (uint32_t)records.mediums.size()), "vb_mediums_set");
     check(vb_lights_set(ctx, records.lights.data(), (uint32_t)records.lights.size(), records.alias_table.data(), records.alias_func.data(),
                         (uint32_t)records.alias_table.size()), "vb_lights_set");
     check(vb_camera_set(ctx, &records.camera), "vb_camera_set");

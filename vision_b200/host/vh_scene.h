@@ -31,6 +31,8 @@ struct SceneRecords {
     std::vector<vb_alias_entry> alias_table;
     std::vector<float> alias_func;
     std::vector<Image> textures;
+    std::vector<vb_medium_rec> mediums;
+    struct Lut { std::vector<float> data; uint32_t nx = 0, ny = 0, nz = 0, channels = 0; } luts[VB_LUT_COUNT];
     vb_camera camera{};
     vb_pt_params params{};
     uint32_t width = 0, height = 0, spp = 1;
@@ -43,6 +45,9 @@ public:
     std::shared_ptr<LightSampler> light_sampler;
     std::shared_ptr<Spectrum> spectrum;
     std::vector<std::shared_ptr<Material>> materials;
+    std::vector<std::shared_ptr<Medium>> mediums;      // MediumRegistry (registries.cpp:196-210)
+    std::shared_ptr<Medium> global_medium;
+    bool process_mediums = false;
     std::shared_ptr<Sensor> sensor;
     std::vector<std::shared_ptr<ShapeGroup>> groups;
     std::vector<std::shared_ptr<ShapeInstance>> instances;

@@ -140,6 +140,11 @@ class HostPipeline:
         sc.alias_func = [float(x) for x in self._blob(4, C.c_float)]
         sc.camera = self._blob(5, capi.vb_camera)[0]
         sc.params = self._blob(6, capi.vb_pt_params)[0]
+        sc.mediums = self._blob(7, capi.vb_medium_rec)
+        for which, (_, dims) in capi.LUT_FILES.items():
+            vals = self._blob(8 + which, C.c_float)
+            if vals:
+                sc.luts[which] = (np.array(vals, np.float32), dims)
         for t in range(i["n_textures"]):
             w, h = C.c_uint32(), C.c_uint32()
             self.lib.vh_texture_info(self.h, t, C.byref(w), C.byref(h))

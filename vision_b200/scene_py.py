@@ -194,6 +194,8 @@ def _material_record(m, textures, base, spectrum_complete=False):
     """plugin -> POD record: diffuse.cpp:36-42, mirror.cpp:35-41, glass.cpp:183-238, metal.cpp:59-133, substrate.cpp:113-124"""
     prm = m.get("param", {})
     rec = capi.vb_material_rec()
+    for f in ("color", "roughness", "spec", "ior", "sigma"):           # unused slots: zero constant, no texture
+        setattr(rec, f, make_slot([0.0, 0.0, 0.0, 0.0]))
     t = m["type"]
     remap = bool(prm.get("remapping_roughness", True))
     rec.flags = 2 if remap else 0
@@ -237,9 +239,9 @@ def _material_record(m, textures, base, spectrum_complete=False):
 def _medium_records(d):
     """MediumsDesc (scene_desc.cpp:24-34) + MediumDesc::init (node_desc.cpp:182-197) + HomogeneousMedium ctor"""
     md = d.get("mediums")
-    if not md:
-        return [], {}, False, ""
-    lst, process, glob = (md, False, "") if isinstance(md, list) else (md.get("list", []), bool(md.get("process", False)), md.get("global", ""))
+    if not isinstance(md, dict):               # missing key or a bare list: nothing loaded, "process" keeps its default (true)
+        return [], {}, True, ""
+    lst, process, glob = md.get("list", []), bool(md.get("process", True)), md.get("global", "")
     table = json.loads((_DATA / "medium_scatter.json").read_text())
     recs, index = [], {}
     for m in lst:
@@ -327,6 +329,15 @@ def build_scene(path, overrides=None) -> SceneRecords:
             inst["light_id"] = len(sc.lights)
             sc.lights.append(l)
         sc.instances.append(inst)
+    # Scene::remove_unused_materials (scene.cpp:79-91): drop materials no instance refers to, re-index the rest
+    used = sorted({i["material_id"] for i in sc.instances if i["material_id"] != VB_INVALID_ID})
+    remap = {old: new for new, old in enumerate(used)}
+    sc.materials = [sc.materials[i] for i in used]
+    for i in sc.instances:
+        if i["material_id"] != VB_INVALID_ID:
+            i["material_id"] = remap[i["material_id"]]
+    if not any(r.type in (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL) for r in sc.materials):
+        sc.luts = {}
     if not ov.get("drop_lights", True) and d.get("light_sampler", {}).get("param", {}).get("lights"):
         raise NotImplementedError("non-area lights")
     # camera
@@ -342,7 +353,8 @@ def build_scene(path, overrides=None) -> SceneRecords:
     sc.camera.focal_distance = float(cam.get("focal_distance", 5.0))
     # Photosensory ctor (photosensory.cpp:15-33): only when mediums are processed; named medium or the global one
     sc.camera.medium_id = (med_index.get(cam["medium"], VB_INVALID_ID) if "medium" in cam else gm) if process_mediums else VB_INVALID_ID
-    sc.params.process_mediums = 1 if process_mediums else 0
+    # the flag only matters when some medium exists (all ids are invalid otherwise): keep the kernel's fast path
+    sc.params.process_mediums = 1 if (process_mediums and sc.mediums) else 0
     ratio = f32(sc.resolution[0]) * f32(1.0) / f32(sc.resolution[1])
     lo, hi = [-1.0, -1.0], [1.0, 1.0]
     if ratio > 1.0:
