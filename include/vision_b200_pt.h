@@ -80,7 +80,15 @@ typedef struct vb_light_rec {
     vb_slot color;
     float position[4];         /* point/spot */
     float direction[4];        /* spot */
-    float params[8];           /* spot: cos_falloff_start, cos_total_width; env: ... */
+    float params[8];           /* spot: cos_falloff_start, cos_total_width; env: [0] Scene::world_diameter() (scene.h:108-109) */
+    /* env ("spherical", environments/spherical.cpp:26-211): lat-long map = color slot texture, importance
+     * sampled through AliasTable2D (alias2d.cpp:31-129): marginal table over rows at alias_offset /
+     * alias_size (= env_res[1]) / alias_integral, conditional row tables (env_res[0] entries per row)
+     * from cond_offset in the same shared arrays */
+    uint32_t env_res[2];
+    uint32_t cond_offset;
+    uint32_t pad1;
+    float w2o[16], o2w[16];    /* column-major; o2w = desc.o2w * rotation_x(-90) * scale(1, flip_u ? 1 : -1, 1) */
 } vb_light_rec;
 VB_API int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n,
                          const vb_alias_entry *alias_table, const float *alias_func, uint32_t n_alias);

@@ -134,6 +134,7 @@ float vo_lcg(uint32_t *state) { return lcg(*state); }
 void vo_sincos_2pi(float u, float *s, float *c) { sincos_2pi(u, *s, *c); }
 float vo_vexp(float x) { return vexp(x); }
 float vo_vlog(float x) { return vlog(x); }
+float vo_vatan2(float y, float x) { return vatan2(y, x); }
 void vo_offset_ray_origin(const float *p, const float *n, float *out) {
     float3 r = offset_ray_origin({p[0], p[1], p[2]}, {n[0], n[1], n[2]});
     out[0] = r.x; out[1] = r.y; out[2] = r.z;

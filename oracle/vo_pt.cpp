@@ -64,6 +64,26 @@ float vlog(float x) {
     return r + 0.693359375f * fe;
 }
 
+// atan2 with a fixed operation sequence (cephes atanf reduction + polynomial); acos(x) is taken as
+// vatan2(sqrt(1 - x*x), x). Used for the lat-long environment map lookup (spherical_theta / spherical_phi).
+float vatan2(float y, float x) {
+    float ax = std::fabs(x), ay = std::fabs(y);
+    float r;
+    if (ax == 0.f && ay == 0.f) r = 0.f;
+    else {
+        bool swap = ay > ax;
+        float t = swap ? ax / ay : ay / ax;                     // in [0, 1]
+        float off = 0.f;
+        if (t > 0.4142135623730950f) { off = 0.78539816339744830961f; t = (t - 1.0f) / (t + 1.0f); }
+        float z = t * t;
+        float p = (((8.05374449538e-2f * z - 1.38776856032e-1f) * z + 1.99777106478e-1f) * z - 3.33329491539e-1f) * z * t + t;
+        r = off + p;
+        if (swap) r = 1.57079632679489661923f - r;
+    }
+    if (x < 0.f) r = 3.14159265358979323846f - r;
+    return y < 0.f ? -r : r;
+}
+
 // Waechter & Binder (Ray Tracing Gems ch.6) integer-ULP offset; ocarina absent.
 float3 offset_ray_origin(float3 p, float3 n) {
     const float origin = 1.0f / 32.0f, float_scale = 1.0f / 65536.0f, int_scale = 256.0f;

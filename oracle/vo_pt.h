@@ -68,6 +68,7 @@ inline float lcg(uint32_t &state) {
 void sincos_2pi(float u, float &s, float &c);
 float vexp(float x);
 float vlog(float x);
+float vatan2(float y, float x);
 float3 offset_ray_origin(float3 p, float3 n);
 
 }  // namespace vo

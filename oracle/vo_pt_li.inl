@@ -121,6 +121,99 @@ inline LightSample area_sample_wi(const Scene &sc, const vb_light_rec &l, const 
     return ls;
 }
 
+// ---- point / spot lights, reference render_core/light/point.cpp:36-42, spot.cpp:47-70, light.cpp:49-58 ----
+inline LightSample point_sample_wi(const Scene &sc, const vb_light_rec &l, const Interaction &ref) {
+    LightSample ls;
+    float3 pos{l.position[0], l.position[1], l.position[2]};
+    float3 value = eval_slot3(sc, l.color, float2{0, 0}) * l.scale;
+    float3 w_un = ref.pos - pos;
+    if (l.type == VB_LIGHT_POINT) ls.eval.L = value / length_squared(w_un);
+    else {
+        float3 w = normalize(w_un);
+        float3 dir{l.direction[0], l.direction[1], l.direction[2]};
+        float cos_angle = l.params[0], cos_falloff_start = l.params[1];
+        float cos_theta = std::min(std::max(dot(dir, w), cos_angle), cos_falloff_start);
+        float factor = (cos_theta - cos_angle) / (cos_falloff_start - cos_angle);
+        float f2 = factor * factor;
+        ls.eval.L = value / length_squared(w_un) * (f2 * f2);
+    }
+    ls.eval.pdf = -1.f;                                            // delta light marker (light.h:227-231)
+    ls.p_light = pos;
+    return ls;
+}
+
+// ---- AliasTable2D over the env map, reference render_core/warper/alias2d.cpp:92-129 ----
+inline float env_map_pdf(const Scene &sc, const vb_light_rec &l, float2 p) {
+    uint32_t rx = l.env_res[0], ry = l.env_res[1];
+    uint32_t iu = std::min((uint32_t)(p.x * (float)rx), rx - 1), iv = std::min((uint32_t)(p.y * (float)ry), ry - 1);
+    return l.alias_integral > 0.f ? sc.alias_func[l.cond_offset + iv * rx + iu] / l.alias_integral : 0.f;
+}
+inline uint32_t alias_offset_remap(const Scene &sc, uint32_t base, uint32_t size, float u, float &u_remapped) {   // alias.h:125-140
+    u = u * (float)size;
+    uint32_t idx = std::min((uint32_t)u, size - 1);
+    u = std::min(u - (float)idx, OneMinusEpsilon);
+    vb_alias_entry e = sc.alias_table[base + idx];
+    bool keep = u < e.prob;
+    u_remapped = keep ? std::min(u / e.prob, OneMinusEpsilon) : std::min((1.0f - u) / (1.0f - e.prob), OneMinusEpsilon);
+    return keep ? idx : e.alias;
+}
+inline float2 env_sample_continuous(const Scene &sc, const vb_light_rec &l, float2 u, float &pdf) {
+    uint32_t rx = l.env_res[0], ry = l.env_res[1];
+    float ur;
+    uint32_t iv = alias_offset_remap(sc, l.alias_offset, ry, u.y, ur);
+    float fv = ((float)iv + ur) / (float)ry;
+    float pdf_v = l.alias_integral > 0.f ? sc.alias_func[l.alias_offset + iv] / l.alias_integral : 0.f;
+    uint32_t off = rx * iv;
+    uint32_t iu = alias_offset_remap(sc, l.cond_offset + off, rx, u.x, ur);
+    float fu = ((float)iu + ur) / (float)rx;
+    float integral_u = sc.alias_func[l.alias_offset + iv];
+    float func_u = sc.alias_func[l.cond_offset + off + iu];
+    float pdf_u = integral_u > 0.f ? func_u / integral_u : 0.f;
+    pdf = pdf_u * pdf_v;
+    return {fu, fv};
+}
+
+// ---- spherical environment map, reference render_core/light/environments/spherical.cpp:58-160 ----
+inline float2 env_calculate_uv(float3 local_dir) {                  // spherical_phi / spherical_theta (pbrt forms)
+    float phi = vatan2(local_dir.y, local_dir.x);
+    if (phi < 0.f) phi = phi + 2.0f * Pi;
+    float cz = std::min(std::max(local_dir.z, -1.f), 1.f);
+    float theta = vatan2(safe_sqrt(1.0f - cz * cz), cz);
+    return {phi * Inv2Pi, theta * InvPi};
+}
+inline float3 env_L(const Scene &sc, const vb_light_rec &l, float3 local_dir) {
+    return eval_slot3(sc, l.color, env_calculate_uv(local_dir)) * l.scale;
+}
+inline LightEval env_evaluate_wi(const Scene &sc, const vb_light_rec &l, float3 ref_pos, float3 light_pos) {
+    LightEval ev;
+    float4x4 w2o; std::memcpy(&w2o, l.w2o, 64);
+    float3 world_dir = normalize(light_pos - ref_pos);
+    float3 local_dir = transform_vector(w2o, world_dir);
+    float2 uv = env_calculate_uv(local_dir);
+    float s, c;
+    sincos_2pi(uv.y * 0.5f, s, c);                                  // sin(theta), theta = uv.y * pi
+    ev.L = env_L(sc, l, local_dir);
+    float pdf = env_map_pdf(sc, l, uv) / (2.0f * Pi * Pi * s);
+    ev.pdf = s == 0.f ? 0.f : pdf;
+    return ev;
+}
+inline LightSample env_sample_wi(const Scene &sc, const vb_light_rec &l, const Interaction &ref, float2 u) {
+    LightSample ls;
+    float pdf_map;
+    float2 uv = env_sample_continuous(sc, l, u, pdf_map);
+    float st, ct, sp, cp;
+    sincos_2pi(uv.y * 0.5f, st, ct);
+    sincos_2pi(uv.x, sp, cp);
+    float3 local_dir{st * cp, st * sp, ct};
+    float4x4 o2w; std::memcpy(&o2w, l.o2w, 64);
+    float3 world_dir = normalize(transform_vector(o2w, local_dir));
+    float pdf_dir = pdf_map / (2.0f * Pi * Pi * st);
+    ls.eval.pdf = std::isinf(pdf_dir) ? 0.f : pdf_dir;
+    ls.eval.L = env_L(sc, l, local_dir);
+    ls.p_light = ref.pos + world_dir * l.params[0];
+    return ls;
+}
+
 // reference lightsampler.cpp:210-216 + uniform.cpp:24-33
 inline LightSample sample_light(const Scene &sc, const Interaction &it, Sampler &sampler) {
     float u_light = sampler.next_1d();
@@ -132,6 +225,8 @@ inline LightSample sample_light(const Scene &sc, const Interaction &it, Sampler 
     float pmf = 1.0f / (float)n;
     const vb_light_rec &l = sc.lights[index];
     if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(sc, l, it, u_surface);
+    else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(sc, l, it, u_surface);
+    else ls = point_sample_wi(sc, l, it);
     ls.eval.pdf *= pmf;
     return ls;
 }
@@ -251,9 +346,24 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
     float3 prev_surface_ng = ray.d;
     float eta_scale = 1.f;
     const uint32_t max_depth = params.max_depth;
+    uint32_t env_light = VB_INVALID_ID;                             // LightSampler::env_light_ (lightsampler.cpp:18-25): the last one wins
+    for (uint32_t i = 0; i < lights.size(); ++i) if (lights[i].type == VB_LIGHT_ENV) env_light = i;
     for (uint32_t bounces = 0; bounces < max_depth; ++bounces) {
         Hit hit = trace_closest(ray, st);
-        if (hit.is_miss()) break;                                   // no environment light in this build
+        if (hit.is_miss()) {                                        // evaluate_miss, integrator.cpp:137-158 + lightsampler.cpp:289-300
+            if (env_light != VB_INVALID_ID) {
+                const vb_light_rec &l = lights[env_light];
+                float3 tr{1, 1, 1};
+                if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(*this, ray_medium, ray); }
+                LightEval ev = env_evaluate_wi(*this, l, ray.o, ray.o + ray.d);
+                ev.pdf *= 1.0f / (float)lights.size();
+                float weight = mis_weight(scatter_pdf, ev.pdf);
+                if (params.mis_mode == 2) weight = 1.f;
+                else if (params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
+                ret += ev.L * tr * weight * throughput;
+            }
+            break;
+        }
         Interaction it = compute_surface_interaction(*this, hit.inst, hit.prim, hit.u, hit.v, true);
         it.wo = normalize(-ray.d);
         ray.tmax = length(it.pos - ray.o) / length(ray.d);         // geometry.h:64-69

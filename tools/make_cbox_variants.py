@@ -6,6 +6,10 @@ cbox-dragon.json medium "fog").
                         right wall = metal (Cu)
   cbox_fog.json       : short box = glass boundary filled with the Skin1 medium (scale 20), global thin fog,
                         mediums.process = true
+  cbox_lights.json    : the ceiling quad keeps its emission; adds a point light, a spot light (the reference's
+                        commented examples in point.cpp:11-20 / spot.cpp:10-18) and a spherical environment
+                        map (spherical.cpp:12-25) over scenes/cbox/env_small.pfm (64x32 analytic gradient with a
+                        bright patch, written here); the back wall is removed so that camera rays can miss
 """
 import copy
 import json
@@ -46,4 +50,22 @@ for s in b["shapes"]:
         s["param"]["medium"] = {"inside": "fog", "outside": "air"}
 b["integrator"]["param"]["max_depth"] = 8
 (root / "cbox_fog.json").write_text(json.dumps(b, indent=1))
-print("wrote", root / "cbox_materials.json", root / "cbox_fog.json")
+
+import numpy as np
+c = copy.deepcopy(base)
+c["shapes"] = [s for s in c["shapes"] if s["name"] != "shape_2"]
+c["light_sampler"]["param"]["lights"] = [
+    {"type": "point", "param": {"color": {"channels": "xyz", "node": [1, 0.8, 0.6]}, "position": [-0.5, 1.8, 0], "scale": 0.2}},
+    {"type": "spot", "param": {"angle": 20, "falloff": 2, "direction": [0.2, -1, 0], "color": [0.4, 0.6, 2], "position": [-0.5, 1.9, 0], "scale": 1}},
+    {"type": "spherical", "param": {"flip_u": True, "color": {"fn": "env_small.pfm", "color_space": "linear"},
+                                     "o2w": {"type": "Euler", "param": {"yaw": -30}}, "scale": 0.5}},
+]
+w, h = 64, 32
+v, u = np.meshgrid((np.arange(h) + 0.5) / h, (np.arange(w) + 0.5) / w, indexing="ij")
+img = np.stack([0.3 + 0.5 * u, 0.4 + 0.4 * (1 - v), 0.8 - 0.5 * u * v], axis=-1).astype(np.float32)
+img[6:10, 20:26] = [30.0, 25.0, 18.0]
+with open(root / "env_small.pfm", "wb") as f:
+    f.write(b"PF\n%d %d\n-1.0\n" % (w, h))
+    f.write(img[::-1].astype("<f4").tobytes())
+(root / "cbox_lights.json").write_text(json.dumps(c, indent=1))
+print("wrote", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json")

@@ -306,7 +306,9 @@ class vb_alias_entry(C.Structure):
 class vb_light_rec(C.Structure):
     _fields_ = [("type", C.c_uint32), ("inst_id", C.c_uint32), ("two_sided", C.c_uint32), ("alias_offset", C.c_uint32),
                 ("alias_size", C.c_uint32), ("alias_integral", C.c_float), ("scale", C.c_float), ("pad0", C.c_float),
-                ("color", vb_slot), ("position", C.c_float * 4), ("direction", C.c_float * 4), ("params", C.c_float * 8)]
+                ("color", vb_slot), ("position", C.c_float * 4), ("direction", C.c_float * 4), ("params", C.c_float * 8),
+                ("env_res", C.c_uint32 * 2), ("cond_offset", C.c_uint32), ("pad1", C.c_uint32),
+                ("w2o", C.c_float * 16), ("o2w", C.c_float * 16)]
 
 
 class vb_camera(C.Structure):

@@ -56,6 +56,7 @@ __device__ __forceinline__ f3 apply_normal(const float *m, f3 n) {
 
 constexpr float Pi = 3.14159265358979323846f;
 constexpr float InvPi = 0.31830988618379067154f;
+constexpr float Inv2Pi = 0.15915494309189533577f;
 constexpr float Inv4Pi = 0.07957747154594766788f;
 constexpr float PiOver2 = 1.57079632679489661923f;
 constexpr float OneMinusEpsilon = 0x1.fffffep-1f;
@@ -103,6 +104,25 @@ __device__ __forceinline__ float vlog(float x) {
     y = y + -0.5f * z;
     float r = m + y;
     return r + 0.693359375f * fe;
+}
+
+// mirrors vo::vatan2
+__device__ __forceinline__ float vatan2(float y, float x) {
+    float ax = fabsf(x), ay = fabsf(y);
+    float r;
+    if (ax == 0.f && ay == 0.f) r = 0.f;
+    else {
+        bool swap = ay > ax;
+        float t = swap ? ax / ay : ay / ax;
+        float off = 0.f;
+        if (t > 0.4142135623730950f) { off = 0.78539816339744830961f; t = (t - 1.0f) / (t + 1.0f); }
+        float z = t * t;
+        float p = (((8.05374449538e-2f * z - 1.38776856032e-1f) * z + 1.99777106478e-1f) * z - 3.33329491539e-1f) * z * t + t;
+        r = off + p;
+        if (swap) r = 1.57079632679489661923f - r;
+    }
+    if (x < 0.f) r = 3.14159265358979323846f - r;
+    return y < 0.f ? -r : r;
 }
 
 // mirrors vo::offset_ray_origin (Waechter & Binder)

@@ -29,6 +29,7 @@ struct PtScene {
     const vb_material_rec *materials;
     const vb_light_rec *lights;
     uint32_t n_lights;
+    uint32_t env_light;            // LightSampler::env_light_ (index of the last Infinite light) or VB_INVALID_ID
     const vb_alias_entry *alias_table;
     const float *alias_func;
     const DevTex *textures;
@@ -200,6 +201,97 @@ __device__ LightSample area_sample_wi(const PtScene &S, const vb_light_rec &l, c
     f3 dir = ref.pos - pl.pos;
     float factor = dot(pl.ng, dir) > 0.f ? 1.f : -1.f;
     ls.p_light = offset_ray_origin(pl.pos, pl.ng * factor * S.params.ray_offset_factor);
+    return ls;
+}
+
+// ---- point / spot lights: render_core/light/point.cpp:36-42, spot.cpp:47-70, light.cpp:49-58 ----
+__device__ LightSample point_sample_wi(const PtScene &S, const vb_light_rec &l, const Interaction &ref) {
+    LightSample ls;
+    f3 pos{l.position[0], l.position[1], l.position[2]};
+    f3 value = eval_slot3(S, l.color, f2{0, 0}) * l.scale;
+    f3 w_un = ref.pos - pos;
+    if (l.type == VB_LIGHT_POINT) ls.eval.L = value / length_squared(w_un);
+    else {
+        f3 w = normalize(w_un);
+        f3 dir{l.direction[0], l.direction[1], l.direction[2]};
+        float cos_angle = l.params[0], cos_falloff_start = l.params[1];
+        float cos_theta = fmin_(fmax_(dot(dir, w), cos_angle), cos_falloff_start);
+        float factor = (cos_theta - cos_angle) / (cos_falloff_start - cos_angle);
+        float f2_ = factor * factor;
+        ls.eval.L = value / length_squared(w_un) * (f2_ * f2_);
+    }
+    ls.eval.pdf = -1.f;
+    ls.p_light = pos;
+    return ls;
+}
+
+// ---- AliasTable2D over the env map: render_core/warper/alias2d.cpp:92-129 ----
+__device__ __forceinline__ float env_map_pdf(const PtScene &S, const vb_light_rec &l, f2 p) {
+    uint32_t rx = l.env_res[0], ry = l.env_res[1];
+    uint32_t iu = min((uint32_t)(p.x * (float)rx), rx - 1), iv = min((uint32_t)(p.y * (float)ry), ry - 1);
+    return l.alias_integral > 0.f ? __ldg(S.alias_func + l.cond_offset + iv * rx + iu) / l.alias_integral : 0.f;
+}
+__device__ __forceinline__ uint32_t alias_offset_remap(const PtScene &S, uint32_t base, uint32_t size, float u, float &u_remapped) {
+    u = u * (float)size;
+    uint32_t idx = min((uint32_t)u, size - 1);
+    u = fmin_(u - (float)idx, OneMinusEpsilon);
+    vb_alias_entry e = S.alias_table[base + idx];
+    bool keep = u < e.prob;
+    u_remapped = keep ? fmin_(u / e.prob, OneMinusEpsilon) : fmin_((1.0f - u) / (1.0f - e.prob), OneMinusEpsilon);
+    return keep ? idx : e.alias;
+}
+__device__ f2 env_sample_continuous(const PtScene &S, const vb_light_rec &l, f2 u, float &pdf) {
+    uint32_t rx = l.env_res[0], ry = l.env_res[1];
+    float ur;
+    uint32_t iv = alias_offset_remap(S, l.alias_offset, ry, u.y, ur);
+    float fv = ((float)iv + ur) / (float)ry;
+    float pdf_v = l.alias_integral > 0.f ? __ldg(S.alias_func + l.alias_offset + iv) / l.alias_integral : 0.f;
+    uint32_t off = rx * iv;
+    uint32_t iu = alias_offset_remap(S, l.cond_offset + off, rx, u.x, ur);
+    float fu = ((float)iu + ur) / (float)rx;
+    float integral_u = __ldg(S.alias_func + l.alias_offset + iv);
+    float func_u = __ldg(S.alias_func + l.cond_offset + off + iu);
+    float pdf_u = integral_u > 0.f ? func_u / integral_u : 0.f;
+    pdf = pdf_u * pdf_v;
+    return {fu, fv};
+}
+
+// ---- spherical environment map: render_core/light/environments/spherical.cpp:58-160 ----
+__device__ __forceinline__ f2 env_calculate_uv(f3 local_dir) {
+    float phi = vatan2(local_dir.y, local_dir.x);
+    if (phi < 0.f) phi = phi + 2.0f * Pi;
+    float cz = fmin_(fmax_(local_dir.z, -1.f), 1.f);
+    float theta = vatan2(safe_sqrt(1.0f - cz * cz), cz);
+    return {phi * Inv2Pi, theta * InvPi};
+}
+__device__ __forceinline__ f3 env_L(const PtScene &S, const vb_light_rec &l, f3 local_dir) {
+    return eval_slot3(S, l.color, env_calculate_uv(local_dir)) * l.scale;
+}
+__device__ LightEval env_evaluate_wi(const PtScene &S, const vb_light_rec &l, f3 ref_pos, f3 light_pos) {
+    LightEval ev;
+    f3 world_dir = normalize(light_pos - ref_pos);
+    f3 local_dir = transform_vector(l.w2o, world_dir);
+    f2 uv = env_calculate_uv(local_dir);
+    float s, c;
+    sincos_2pi(uv.y * 0.5f, s, c);
+    ev.L = env_L(S, l, local_dir);
+    float pdf = env_map_pdf(S, l, uv) / (2.0f * Pi * Pi * s);
+    ev.pdf = s == 0.f ? 0.f : pdf;
+    return ev;
+}
+__device__ LightSample env_sample_wi(const PtScene &S, const vb_light_rec &l, const Interaction &ref, f2 u) {
+    LightSample ls;
+    float pdf_map;
+    f2 uv = env_sample_continuous(S, l, u, pdf_map);
+    float st, ct, sp, cp;
+    sincos_2pi(uv.y * 0.5f, st, ct);
+    sincos_2pi(uv.x, sp, cp);
+    f3 local_dir{st * cp, st * sp, ct};
+    f3 world_dir = normalize(transform_vector(l.o2w, local_dir));
+    float pdf_dir = pdf_map / (2.0f * Pi * Pi * st);
+    ls.eval.pdf = isinf(pdf_dir) ? 0.f : pdf_dir;
+    ls.eval.L = env_L(S, l, local_dir);
+    ls.p_light = ref.pos + world_dir * l.params[0];
     return ls;
 }
 

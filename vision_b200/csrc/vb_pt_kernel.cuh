@@ -47,7 +47,21 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
             for (uint32_t bounces = 0; bounces < max_depth; ++bounces) {
                 if (!have_hit) { vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1, mg); c_closest++; }
                 have_hit = false;
-                if (hit.inst == VB_INVALID_ID) break;
+                if (hit.inst == VB_INVALID_ID) {                          // evaluate_miss, integrator.cpp:137-158 + lightsampler.cpp:289-300
+                    if (S.env_light != VB_INVALID_ID) {
+                        const vb_light_rec &l = S.lights[S.env_light];
+                        f3 tr{1, 1, 1};
+                        if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(S, ray_medium, ray); }
+                        f3 ro{ray.ox, ray.oy, ray.oz}, rd{ray.dx, ray.dy, ray.dz};
+                        LightEval ev = env_evaluate_wi(S, l, ro, ro + rd);
+                        ev.pdf *= 1.0f / (float)S.n_lights;
+                        float weight = mis_weight(scatter_pdf, ev.pdf);
+                        if (S.params.mis_mode == 2) weight = 1.f;
+                        else if (S.params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
+                        ret = ret + ev.L * tr * weight * throughput;
+                    }
+                    break;
+                }
                 Interaction it = compute_surface_interaction(S, hit.inst, hit.prim, hit.u, hit.v, true);
                 f3 rd{ray.dx, ray.dy, ray.dz}, ro{ray.ox, ray.oy, ray.oz};
                 it.wo = normalize(-rd);
@@ -110,6 +124,8 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                     uint32_t index = (uint32_t)fmin_(u_light * (float)n, (float)n - 1.0f);
                     const vb_light_rec &l = S.lights[index];
                     if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(S, l, it, u_surface);
+                    else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(S, l, it, u_surface);
+                    else ls = point_sample_wi(S, l, it);
                     ls.eval.pdf *= 1.0f / (float)n;
                 }
                 VbRay shadow = spawn_ray_to(it, ls.p_light);
@@ -206,7 +222,7 @@ struct vb_pt_state {
     DevMesh *d_meshes = nullptr;
     DevInst *d_inst = nullptr;
     vb_material_rec *d_mat = nullptr; uint32_t n_mat = 0;
-    vb_light_rec *d_lights = nullptr; uint32_t n_lights = 0;
+    vb_light_rec *d_lights = nullptr; uint32_t n_lights = 0; uint32_t env_light = VB_INVALID_ID;
     vb_alias_entry *d_alias = nullptr; float *d_func = nullptr;
     DevTex *d_tex = nullptr; std::vector<float4 *> tex_mem;
     DevLut luts[VB_LUT_COUNT] = {};
@@ -356,11 +372,19 @@ int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n, const vb_
     cudaSetDevice(ctx->device);
     vb_pt_state *p = pt_state(ctx);
     for (uint32_t i = 0; i < n; ++i) {
-        if (lights[i].type != VB_LIGHT_AREA) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_lights_set: light type not implemented yet");
-        if (lights[i].alias_offset + lights[i].alias_size > n_alias) return ctx->fail(VB_ERR_INVALID, "vb_lights_set: alias range out of bounds");
+        if (lights[i].type > VB_LIGHT_ENV) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_lights_set: light type not implemented yet");
+        bool tabled = lights[i].type == VB_LIGHT_AREA || lights[i].type == VB_LIGHT_ENV;
+        if (tabled && lights[i].alias_offset + lights[i].alias_size > n_alias) return ctx->fail(VB_ERR_INVALID, "vb_lights_set: alias range out of bounds");
+        if (lights[i].type == VB_LIGHT_ENV) {
+            uint64_t cells = (uint64_t)lights[i].env_res[0] * lights[i].env_res[1];
+            if (!cells || lights[i].alias_size != lights[i].env_res[1] || lights[i].cond_offset + cells > n_alias)
+                return ctx->fail(VB_ERR_INVALID, "vb_lights_set: env map tables out of bounds");
+        }
     }
     cudaFree(p->d_lights); cudaFree(p->d_alias); cudaFree(p->d_func);
     p->d_lights = nullptr; p->d_alias = nullptr; p->d_func = nullptr; p->n_lights = n;
+    p->env_light = VB_INVALID_ID;
+    for (uint32_t i = 0; i < n; ++i) if (lights[i].type == VB_LIGHT_ENV) p->env_light = i;
     if (n) {
         VB_CUDA(cudaMalloc(&p->d_lights, sizeof(vb_light_rec) * n));
         VB_CUDA(cudaMemcpy(p->d_lights, lights, sizeof(vb_light_rec) * n, cudaMemcpyHostToDevice));
@@ -427,7 +451,7 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     if (rc) return rc;
     PtScene S{};
     S.accel = VbAccelView{ctx->accel.nodes, ctx->accel.tris};
-    S.meshes = p->d_meshes; S.instances = p->d_inst; S.materials = p->d_mat; S.lights = p->d_lights; S.n_lights = p->n_lights;
+    S.meshes = p->d_meshes; S.instances = p->d_inst; S.materials = p->d_mat; S.lights = p->d_lights; S.n_lights = p->n_lights; S.env_light = p->env_light;
     S.alias_table = p->d_alias; S.alias_func = p->d_func; S.textures = p->d_tex;
     for (int k = 0; k < VB_LUT_COUNT; ++k) S.luts[k] = p->luts[k];
     S.mediums = p->d_mediums;

@@ -147,7 +147,127 @@ def _color_slot(v, textures, base_dir):
     return make_slot([float(x) for x in v])
 
 
+def read_pfm(path):
+    with open(path, "rb") as f:
+        magic = f.readline().strip()
+        w, h = (int(x) for x in f.readline().split())
+        scale = float(f.readline())
+        ch = 3 if magic == b"PF" else 1
+        a = np.frombuffer(f.read(), "<f4" if scale < 0 else ">f4").reshape(h, w, ch)[::-1]
+    if ch == 1:
+        a = np.repeat(a, 3, axis=-1)
+    return np.ascontiguousarray(np.concatenate([a, np.ones((h, w, 1), np.float32)], axis=-1), np.float32)
+
+
+def obj_mesh(path, smooth=False, flip_uv=True):
+    """Model shape (model.cpp:27-36). The reference imports through assimp with JoinIdenticalVertices |
+    GenNormals | ImproveCacheLocality | FindDegenerates | OptimizeMeshes | Triangulate | FlipUVs
+    (assimp_parser.cpp:309-341), whose cache-locality pass re-orders triangles; this loader keeps FILE order
+    (prim_id = order of the f statements): one mesh per file, vertices de-duplicated by
+    their (v, vt, vn) index triple in first-use order, polygons fan-triangulated, v -> 1 - v when flip_uv,
+    faces with a repeated position index dropped, missing normals = face normals (or their sum per
+    position when smooth)."""
+    V, VT, VN, faces = [], [], [], []
+    with open(path) as f:
+        for line in f:
+            t = line.split()
+            if not t:
+                continue
+            if t[0] == "v":
+                V.append([float(x) for x in t[1:4]])
+            elif t[0] == "vt":
+                VT.append([float(t[1]), float(t[2]) if len(t) > 2 else 0.0])
+            elif t[0] == "vn":
+                VN.append([float(x) for x in t[1:4]])
+            elif t[0] == "f":
+                idx = []
+                for c in t[1:]:
+                    q = (c.split("/") + ["", ""])[:3]
+                    a = [int(x) if x else 0 for x in q]
+                    a = [(x - 1 if x > 0 else (len(L) + x if x < 0 else -1)) for x, L in zip(a, (V, VT, VN))]
+                    idx.append(tuple(a))
+                for k in range(1, len(idx) - 1):
+                    tri = (idx[0], idx[k], idx[k + 1])
+                    if len({tri[0][0], tri[1][0], tri[2][0]}) == 3:
+                        faces.append(tri)
+    V = np.asarray(V, f32).reshape(-1, 3); VT = np.asarray(VT, f32).reshape(-1, 2); VN = np.asarray(VN, f32).reshape(-1, 3)
+    key_to_index, pos, nrm, uv, tris = {}, [], [], [], []
+    acc = None
+    if smooth and not len(VN):
+        acc = np.zeros((len(V), 3), np.float64)
+        for tri in faces:
+            p = V[[c[0] for c in tri]].astype(np.float64)
+            acc[[c[0] for c in tri]] += np.cross(p[1] - p[0], p[2] - p[0])
+    for tri in faces:
+        fn = None
+        if not len(VN) and acc is None:
+            p = V[[c[0] for c in tri]]
+            n = np.cross((p[1] - p[0]).astype(f32), (p[2] - p[0]).astype(f32)).astype(f32)
+            l = f32(np.sqrt(f32(np.dot(n, n))))
+            fn = tuple((n / l).astype(f32)) if l > 0 else (0.0, 0.0, 0.0)
+        out = []
+        for (iv, it, inn) in tri:
+            key = (iv, it, inn, fn)
+            j = key_to_index.get(key)
+            if j is None:
+                j = len(pos)
+                key_to_index[key] = j
+                pos.append(V[iv])
+                if inn >= 0:
+                    nrm.append(VN[inn])
+                elif acc is not None:
+                    a = acc[iv]; l = np.linalg.norm(a)
+                    nrm.append((a / l if l > 0 else a).astype(f32))
+                else:
+                    nrm.append(np.asarray(fn, f32))
+                t = VT[it] if it >= 0 else np.zeros(2, f32)
+                uv.append(np.array([t[0], f32(1.0) - t[1] if flip_uv else t[1]], f32))
+            out.append(j)
+        tris.append(out)
+    return {"pos": np.asarray(pos, f32).reshape(-1, 3), "nrm": np.asarray(nrm, f32).reshape(-1, 3),
+            "uv": np.asarray(uv, f32).reshape(-1, 2), "tri": np.asarray(tris, np.uint32).reshape(-1, 3)}
+
+
+def euler_matrix(prm):
+    """TransformDesc 'Euler' (node_desc.cpp:43-48): translation * pitch(x) * roll(z) * yaw(y), degrees"""
+    def rot(axis, deg):
+        a = math.radians(deg); c, s_ = math.cos(a), math.sin(a)
+        m = np.eye(4)
+        i, j = {"x": (1, 2), "y": (2, 0), "z": (0, 1)}[axis]
+        m[i, i] = c; m[j, j] = c; m[i, j] = -s_; m[j, i] = s_
+        return m
+    t = np.eye(4); t[:3, 3] = prm.get("position", [0, 0, 0])
+    return t @ rot("x", prm.get("pitch", 0.0)) @ rot("z", prm.get("roll", 0.0)) @ rot("y", prm.get("yaw", 0.0))
+
+
+def transform_matrix(tr):
+    """row-major numpy 4x4 from a transform block (matrix4x4 rows are columns; look_at; Euler)"""
+    if not tr:
+        return np.eye(4)
+    t, prm = tr.get("type", "matrix4x4"), tr.get("param", {})
+    if t == "matrix4x4":
+        return np.asarray(prm["matrix4x4"], np.float64).T
+    if t == "look_at":
+        return look_at(prm["position"], prm["target_pos"], prm.get("up", [0, 1, 0]))
+    if t == "Euler":
+        return euler_matrix(prm)
+    raise NotImplementedError(t)
+
+
+def alias2d_build(weights, rx, ry):
+    """AliasTable2D::build (alias2d.cpp:47-82): one table per row, marginal over the row integrals"""
+    cond_table, cond_func, marg = [], [], []
+    for v in range(ry):
+        t, fn, integral = alias_build(weights[v * rx:(v + 1) * rx]) if any(weights[v * rx:(v + 1) * rx]) else \
+            ([(1.0, i) for i in range(rx)], [0.0] * rx, 0.0)
+        cond_table += t; cond_func += fn; marg.append(integral)
+    mt, mf, mi = alias_build(marg)
+    return mt, mf, mi, cond_table, cond_func
+
+
 def load_image(path, color_space):
+    if Path(path).suffix.lower() == ".pfm":
+        return read_pfm(path)
     from PIL import Image
     im = np.asarray(Image.open(path).convert("RGBA"), np.float32) / f32(255.0)
     if color_space == "srgb" and Path(path).suffix.lower() not in (".exr", ".hdr"):
@@ -236,6 +356,107 @@ def _material_record(m, textures, base, spectrum_complete=False):
     return rec
 
 
+_libm = None
+
+
+def _cfun(name, x):
+    """glibc sinf / cosf: the C++ host calls std::sin / std::cos on floats; numpy's float32 kernels may differ by an ulp"""
+    global _libm
+    if _libm is None:
+        import ctypes
+        _libm = ctypes.CDLL("libm.so.6")
+        for n in ("sinf", "cosf"):
+            getattr(_libm, n).restype = ctypes.c_float
+            getattr(_libm, n).argtypes = [ctypes.c_float]
+    return f32(getattr(_libm, name)(float(f32(x))))
+
+
+def _light_common(l, prm, textures, base):
+    """Light ctor + initialize_slots (light.cpp:10-24): colour slot, scale, colour normalised into the scale"""
+    slot = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
+    scale = f32(_number(prm.get("scale", 1.0), 1.0))
+    if slot.tex_id == VB_INVALID_ID:
+        col = [f32(c) for c in slot.value[:3]]
+        mx = max(col)
+        if mx >= 1.0:
+            slot = make_slot([float(f32(c / mx)) for c in col])
+            scale = f32(scale * mx)
+    l.color = slot
+    l.scale = float(scale)
+
+
+def env_weights(tex):
+    """SphericalMap::calculate_weights (spherical.cpp:170-196) incl. its index quirk: v = idx / res.y + 0.5,
+    theta = v / res.x (integer division by the HEIGHT, normalised by the WIDTH); luminance = Rec.709"""
+    h, w = tex.shape[:2]
+    px = tex.reshape(-1, 4).astype(f32)
+    lum = (f32(0.212671) * px[:, 0] + f32(0.715160) * px[:, 1]) + f32(0.072169) * px[:, 2]
+    idx = np.arange(w * h, dtype=np.int64)
+    theta = ((idx // h).astype(f32) + f32(0.5)) / f32(w)
+    ang = (f32(math.pi) * theta).astype(f32)
+    uniq = np.unique(ang)
+    table = {float(a): _cfun("sinf", a) for a in uniq}
+    sin_t = np.array([table[float(a)] for a in ang], f32)
+    return (lum * sin_t).astype(f32)
+
+
+def _free_light_record(ld, sc, base, world_diameter):
+    """lights listed under light_sampler.param.lights: point.cpp:24-27, spot.cpp:29-35, spherical.cpp:36-45,199-211"""
+    t, prm = ld["type"], ld.get("param", {})
+    l = capi.vb_light_rec()
+    l.inst_id = VB_INVALID_ID
+    _light_common(l, prm, sc.textures, base)
+    if t in ("point", "spot"):
+        l.type = capi.VB_LIGHT_POINT if t == "point" else capi.VB_LIGHT_SPOT
+        l.position[:3] = [float(f32(x)) for x in prm.get("position", [0, 0, 0])]
+        if t == "spot":
+            angle = f32(math.radians(float(np.clip(f32(prm.get("angle", 45.0)), f32(1.0), f32(89.0)))))
+            falloff = f32(math.radians(float(np.clip(f32(prm.get("falloff", 10.0)), f32(0.0), angle))))
+            dv = np.asarray(prm.get("direction", [0, 0, 1]), f32)
+            inv = f32(1.0) / f32(np.sqrt(f32(f32(f32(dv[0] * dv[0]) + f32(dv[1] * dv[1])) + f32(dv[2] * dv[2]))))
+            l.direction[:3] = [float(f32(x * inv)) for x in dv]
+            l.params[0] = float(_cfun("cosf", angle))
+            l.params[1] = float(_cfun("cosf", max(f32(0.0), f32(angle - falloff))))
+    elif t == "spherical":
+        l.type = capi.VB_LIGHT_ENV
+        o2w = transform_matrix(prm.get("o2w")) @ euler_matrix({"pitch": -90.0}) @ np.diag([1.0, 1.0 if prm.get("flip_u", False) else -1.0, 1.0, 1.0])
+        o2w = o2w.astype(f32).astype(np.float64)
+        l.o2w[:] = [float(x) for x in o2w.T.reshape(-1)]
+        l.w2o[:] = [float(f32(x)) for x in np.linalg.inv(o2w).T.reshape(-1)]
+        if l.color.tex_id != VB_INVALID_ID:
+            tex = sc.textures[l.color.tex_id]
+            ry, rx = tex.shape[:2]
+            weights = env_weights(tex)
+        else:
+            rx = ry = 1
+            weights = np.ones(1, f32)
+        mt, mf, mi, ct, cf = alias2d_build([float(x) for x in weights], rx, ry)
+        l.alias_offset, l.alias_size, l.alias_integral = len(sc.alias_table), ry, mi
+        sc.alias_table += mt; sc.alias_func += mf
+        l.cond_offset = len(sc.alias_table)
+        sc.alias_table += ct; sc.alias_func += cf
+        l.env_res[:] = [rx, ry]
+        l.params[0] = world_diameter
+    else:
+        raise NotImplementedError(f"light {t}")
+    return l
+
+
+def world_diameter(sc, min_world_radius):
+    """Scene::world_diameter (scene.h:108-109) over the instance boxes (shape.cpp:73-85), accumulated in double"""
+    lo, hi = np.full(3, np.inf), np.full(3, -np.inf)
+    for inst in sc.instances:
+        m = np.asarray(inst["o2w"], np.float64).reshape(4, 4).T          # row-major
+        mesh = sc.meshes[inst["mesh_id"]]
+        p = mesh["pos"][np.unique(mesh["tri"])].astype(np.float64)
+        q = np.stack([p[:, 0] * m[r, 0] + p[:, 1] * m[r, 1] + p[:, 2] * m[r, 2] + m[r, 3] for r in range(3)], axis=1)
+        if len(q):
+            lo, hi = np.minimum(lo, q.min(0)), np.maximum(hi, q.max(0))
+    d = hi - lo
+    radius = 0.5 * math.sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]) if len(sc.instances) and np.all(np.isfinite(d)) else 0.0
+    return float(f32(2.0 * max(radius, float(min_world_radius))))
+
+
 def _medium_records(d):
     """MediumsDesc (scene_desc.cpp:24-34) + MediumDesc::init (node_desc.cpp:182-197) + HomogeneousMedium ctor"""
     md = d.get("mediums")
@@ -290,13 +511,15 @@ def build_scene(path, overrides=None) -> SceneRecords:
             mesh = quad_mesh(prm.get("width", 1.0), prm.get("height", 1.0))
         elif sh["type"] == "cube":
             mesh = cube_mesh(prm.get("x", 1.0), prm.get("y", 1.0), prm.get("z", 1.0))
+        elif sh["type"] == "model":
+            mesh = obj_mesh(base / prm["fn"], smooth=bool(prm.get("smooth", False)), flip_uv=bool(prm.get("flip_uv", True)))
         else:
             raise NotImplementedError(sh["type"])
         mat_name = ov.get("shape_material", {}).get(sh["name"], prm.get("material"))
         if mat_name in mat_index and mat_index[mat_name] is None:
             raise NotImplementedError(f"material {mat_name} of {sh['name']}")
         mid = mat_index.get(mat_name, VB_INVALID_ID)                # unknown / empty name: no material (medium boundary)
-        o2w = np.asarray(prm["transform"]["param"]["matrix4x4"], f32).reshape(-1)   # JSON rows are columns
+        o2w = transform_matrix(prm.get("transform")).astype(f32).T.reshape(-1)       # column-major
         inst = {"mesh_id": len(sc.meshes), "material_id": mid, "light_id": VB_INVALID_ID, "o2w": o2w}
         if "medium" in prm:                                       # ShapeGroup::post_init, shape.cpp:245-270
             inst["inside_medium"] = med_index.get(prm["medium"].get("inside", ""), VB_INVALID_ID)
@@ -338,8 +561,20 @@ def build_scene(path, overrides=None) -> SceneRecords:
             i["material_id"] = remap[i["material_id"]]
     if not any(r.type in (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL) for r in sc.materials):
         sc.luts = {}
-    if not ov.get("drop_lights", True) and d.get("light_sampler", {}).get("param", {}).get("lights"):
-        raise NotImplementedError("non-area lights")
+    # LightSampler ctor (lightsampler.cpp:11-27): listed lights come first, the shapes' emissions follow; tidy_up
+    # (lightsampler.cpp:67-77) then groups them by type in first-seen order
+    free = [] if ov.get("drop_lights", False) else d.get("light_sampler", {}).get("param", {}).get("lights", [])
+    if free:
+        wd = world_diameter(sc, d.get("render_setting", {}).get("min_world_radius", 10.0))
+        lights = [_free_light_record(ld, sc, base, wd) for ld in free] + sc.lights
+        first = {}
+        for l in lights:
+            first.setdefault(l.type, len(first))
+        order = sorted(range(len(lights)), key=lambda i: first[lights[i].type])
+        sc.lights = [lights[i] for i in order]
+        for new, l in enumerate(sc.lights):
+            if l.type == capi.VB_LIGHT_AREA:
+                sc.instances[l.inst_id]["light_id"] = new
     # camera
     cam = d["camera"]["param"]
     res = ov.get("resolution") or d.get("pipeline", {}).get("param", {}).get("frame_buffer", {}).get("param", {}).get("resolution", [1280, 720])
