@@ -42,6 +42,8 @@ def parse():
     p.add_argument("--pt-res", type=int, default=1024)
     p.add_argument("--pt-spp", type=int, default=64)
     p.add_argument("--no-pt", action="store_true")
+    p.add_argument("--classroom-spp", type=int, default=16)
+    p.add_argument("--no-classroom", action="store_true")
     return p.parse_args()
 
 
@@ -129,20 +131,25 @@ class _DevPtr:
         self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 2}
 
 
-def pt_section(a, rank, world, local_rank, stream):
-    """secondary measurement: the path tracer on the cbox-matte scene (BASELINE.json configs[0] geometry at
-    1024x1024), sample-partitioned across ranks (rank g renders frames g, g+G, ...) with ONE NCCL all-reduce of
-    the SUM film followed by the fused resolve. Returns samples/s and Mrays/s (whole job)."""
+def pt_section(a, rank, world, local_rank, stream, which="cbox"):
+    """secondary measurement: the path tracer, sample-partitioned across ranks (rank g renders frames g, g+G, ...)
+    with ONE NCCL all-reduce of the SUM film followed by the fused resolve. Returns samples/s and Mrays/s (whole
+    job). which = "cbox": cbox-matte (BASELINE.json configs[0] geometry at 1024x1024, depth 5);
+    "classroom": BASELINE.json configs[4] (1920x1080, depth 16, env map + fog + glass/metal/substrate)."""
     import torch
     import torch.distributed as dist
     from vision_b200 import Context, scene_py, capi
     from vision_b200.dist import frames_for_rank
-    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", dict(scene_py.CBOX_MATTE_OVERRIDES, resolution=[a.pt_res, a.pt_res]))
+    if which == "cbox":
+        sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", dict(scene_py.CBOX_MATTE_OVERRIDES, resolution=[a.pt_res, a.pt_res]))
+        spp_rank, label = a.pt_spp, "cbox matte"
+    else:
+        sc = scene_py.build_scene(ROOT / "scenes" / "classroom" / "vision_scene.json", {})
+        spp_rank, label = a.classroom_spp, "classroom (sky stand-in env map)"
     ctx = Context(local_rank)
     ctx.set_stream(stream.cuda_stream)
     ctx.upload_scene(sc)
     w, h = sc.resolution
-    spp_rank = a.pt_spp
     film = torch.as_tensor(_DevPtr(ctx.film_device_ptr(capi.VB_FILM_ACCUM), w * h * 4), device=torch.device("cuda", local_rank))
 
     def run():
@@ -176,7 +183,7 @@ def pt_section(a, rank, world, local_rank, stream):
     out_mean = float(torch.as_tensor(_DevPtr(ctx.film_device_ptr(capi.VB_FILM_OUTPUT), w * h * 4), device=torch.device("cuda", local_rank)).mean())
     ctx.close()
     samples = w * h * spp_rank * world
-    return {"scene": f"cbox matte {w}x{h}, {spp_rank} spp per GPU x {world} GPU(s), max depth 5", "ms": ms,
+    return {"scene": f"{label} {w}x{h}, {spp_rank} spp per GPU x {world} GPU(s), max depth {sc.params.max_depth}", "ms": ms,
             "samples_per_s": samples / (ms * 1e-3), "mrays_per_s": rays / (ms * 1e-3) / 1e6, "rays_per_sample": rays / samples,
             "film_allreduce": "torch.distributed NCCL sum over the float4 film" if world > 1 else "none (1 GPU)",
             "output_mean": out_mean}
@@ -318,6 +325,7 @@ def main():
     del d_rays, d_any, d_hits, d_occ, h_rays, h_hits_t, h_occ_t
     torch.cuda.empty_cache()
     pt = None if a.no_pt else pt_section(a, rank, world, local_rank, stream)
+    pt_room = None if (a.no_pt or a.no_classroom) else pt_section(a, rank, world, local_rank, stream, "classroom")
 
     if rank == 0:
         peaks = {}
@@ -364,6 +372,8 @@ def main():
         }
         if pt is not None:
             line["path_tracer"] = pt
+        if pt_room is not None:
+            line["path_tracer_classroom"] = pt_room
         if world == 1 and not a.no_cpu_baseline:
             cb = cpu_arm(a, mesh, rays, 0, 2, 1)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}

@@ -139,7 +139,9 @@ VB_API int vb_film_device_ptr(vb_ctx *ctx, int which, void **ptr);
 /* ---- debug / parity surface ------------------------------------------------------------------- */
 /* primary hit of every pixel for one frame index (== reference rt_compute_pixel, frame_buffer.cpp:277-291) */
 VB_API int vb_dump_primary_hits(vb_ctx *ctx, uint32_t frame_index, const vb_hits_soa *out);
-/* counters of the last vb_render_frames call: [0] closest-hit rays, [1] any-hit rays, [2] shaded vertices */
+/* counters of the last vb_render_frames call: [0] closest-hit rays, [1] any-hit rays, [2] shaded vertices,
+ * [3] shadow rays culled before tracing because their contribution is exactly zero (the reference traces them:
+ * [1] + [3] is its any-hit count) */
 VB_API int vb_render_stats(vb_ctx *ctx, uint64_t stats[4]);
 
 #endif

@@ -41,4 +41,4 @@ def test_image_matches_oracle(vbctx, oracle, name, min_mean):
     assert err <= REL_MSE_TOL
     assert frac <= MAX_DIFF_PIXELS
     gst = vbctx.render_stats()
-    assert abs(int(gst["any"]) - ost["any"]) <= 1e-3 * ost["any"]
+    assert abs(int(gst["any"] + gst["culled"]) - ost["any"]) <= 1e-3 * ost["any"]

@@ -1,0 +1,28 @@
+"""One path-tracing launch on a scene, for ncu / quick timing (run under gpurun).
+usage: prof_pt.py <scene.json> <width> <height> <spp> [reps] [process_mediums 0/1]"""
+import sys
+import time
+from pathlib import Path
+import torch
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from vision_b200 import Context, scene_py, capi
+
+path = sys.argv[1]
+w, h, spp = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
+reps = int(sys.argv[5]) if len(sys.argv) > 5 else 1
+ov = {"resolution": [w, h], "spp": spp}
+if len(sys.argv) > 6:
+    ov["process_mediums"] = bool(int(sys.argv[6]))
+sc = scene_py.build_scene(path, ov)
+ctx = Context(0)
+ctx.upload_scene(sc)
+for r in range(reps):
+    ctx.film_clear()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    ctx.render_frames(0, spp, 1, capi.VB_ACCUM_SUM)
+    ctx.synchronize()
+    dt = time.perf_counter() - t0
+    st = ctx.render_stats()
+    rays = st["closest"] + st["any"]
+    print(f"rep {r}: {dt * 1e3:.2f} ms, {w * h * spp / dt / 1e6:.2f} Msamples/s, {rays / dt / 1e6:.1f} Mrays/s, {rays / (w * h * spp):.2f} rays/sample")

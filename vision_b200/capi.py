@@ -458,7 +458,7 @@ def _pt_methods():
     def render_stats(self):
         st = (C.c_uint64 * 4)()
         self._check(self.lib.vb_render_stats(self.h, st), "vb_render_stats")
-        return {"closest": st[0], "any": st[1], "vertices": st[2]}
+        return {"closest": st[0], "any": st[1], "vertices": st[2], "culled": st[3]}
 
     for f in (upload_scene, render_frames, film_clear, film_resolve, film_download, film_device_ptr,
               dump_primary_hits, render_stats):

@@ -3,11 +3,14 @@
 
 namespace {
 
-struct PtCounters { unsigned long long closest, any, vertices, pad; };
+struct PtCounters { unsigned long long closest, any, vertices, culled; };
 
-// One thread = one pixel; it runs all frames of the batch for that pixel back to back (a finished
-// path is immediately replaced by the next frame's path, so lanes stay busy), keeps the running
-// film value in registers and writes the film once per launch.
+// Megakernel schedule. One thread = one pixel; it runs all frames of the batch for that pixel back to
+// back as a state machine: every loop iteration is [regenerate a finished path] -> closest-hit
+// traversal -> pt_bounce -> any-hit traversal, so the lanes of a warp meet at ONE closest and ONE
+// any-hit call site whatever bounce or frame each of them is at, and a lane whose path ended starts
+// its next frame in the same iteration instead of waiting for the longest path of the warp. The
+// running film value stays in registers and is written once per launch.
 template <bool DUMP_PRIMARY>
 __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t first_frame, uint32_t n_frames, uint32_t stride, int mode,
                                                          uint32_t frames_done, float4 *rt, float4 *accum, PtCounters *counters,
@@ -17,161 +20,59 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
     const uint32_t mg = vb_qf_magic_init();
     uint32_t pix = blockIdx.x * PT_BLOCK + threadIdx.x;
     uint32_t n_pix = S.width * S.height;
-    uint32_t c_closest = 0, c_any = 0, c_vert = 0, dummy0 = 0, dummy1 = 0;
-    if (pix < n_pix) {
-        uint32_t px = pix % S.width, py = pix / S.width;
-        float4 acc = accum[pix];
-        float4 last = make_float4(0.f, 0.f, 0.f, 1.f);
-        for (uint32_t fi = 0; fi < n_frames; ++fi) {
-            uint32_t frame = first_frame + fi * stride;
+    uint32_t c_closest = 0, c_any = 0, c_vert = 0, c_culled = 0, dummy0 = 0, dummy1 = 0;
+    const uint32_t px = pix % S.width, py = pix / S.width;
+    if (DUMP_PRIMARY) {
+        if (pix < n_pix) {
             Sampler sampler;
-            sampler.start(px, py, frame, 0u);
+            sampler.start(px, py, first_frame, 0u);
             VbRay ray = generate_camera_ray(S, sampler, px, py);
             VbHit hit;
-            // the reference traces the primary ray in rt_geom and again as bounce 0 of Li with the
-            // same ray; the second result is identical, so it is reused (counted once)
             vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1, mg);
-            c_closest++;
-            if (DUMP_PRIMARY) {
-                h_inst[pix] = hit.inst; h_prim[pix] = hit.prim; h_u[pix] = hit.u; h_v[pix] = hit.v; h_t[pix] = hit.t;
-                continue;
+            h_inst[pix] = hit.inst; h_prim[pix] = hit.prim; h_u[pix] = hit.u; h_v[pix] = hit.v; h_t[pix] = hit.t;
+        }
+        return;
+    }
+    bool done = pix >= n_pix, need_new = true;
+    float4 acc = done ? make_float4(0.f, 0.f, 0.f, 0.f) : accum[pix];
+    float4 last = make_float4(0.f, 0.f, 0.f, 1.f);
+    uint32_t fi = 0;
+    PathState ps;
+    VbRay ray;
+    const uint32_t max_depth = S.params.max_depth;
+    for (;;) {
+        if (!done && need_new) {
+            if (fi == n_frames) done = true;
+            else {
+                // the reference traces the primary ray in rt_geom and again as bounce 0 of Li with the
+                // same ray; the second result is identical, so it is traced (and counted) once
+                uint32_t frame = first_frame + fi * stride;
+                Sampler sampler;
+                sampler.start(px, py, frame, 0u);
+                ray = generate_camera_ray(S, sampler, px, py);
+                path_begin(S, ps, px, py, frame);
+                need_new = max_depth == 0;
+                if (need_new) { fi++; last = make_float4(0.f, 0.f, 0.f, 1.f); }      // no bounce: black sample
             }
-            sampler.start(px, py, frame, 1u);
-            const bool mediums = S.params.process_mediums != 0;
-            uint32_t ray_medium = mediums ? S.cam.medium_id : VB_INVALID_ID;
-            float scatter_pdf = 1e16f;
-            f3 throughput{1, 1, 1}, ret{0, 0, 0};
-            float eta_scale = 1.f;
-            const uint32_t max_depth = S.params.max_depth;
-            bool have_hit = true;
-            for (uint32_t bounces = 0; bounces < max_depth; ++bounces) {
-                if (!have_hit) { vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1, mg); c_closest++; }
-                have_hit = false;
-                if (hit.inst == VB_INVALID_ID) {                          // evaluate_miss, integrator.cpp:137-158 + lightsampler.cpp:289-300
-                    if (S.env_light != VB_INVALID_ID) {
-                        const vb_light_rec &l = S.lights[S.env_light];
-                        f3 tr{1, 1, 1};
-                        if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(S, ray_medium, ray); }
-                        f3 ro{ray.ox, ray.oy, ray.oz}, rd{ray.dx, ray.dy, ray.dz};
-                        LightEval ev = env_evaluate_wi(S, l, ro, ro + rd);
-                        ev.pdf *= 1.0f / (float)S.n_lights;
-                        float weight = mis_weight(scatter_pdf, ev.pdf);
-                        if (S.params.mis_mode == 2) weight = 1.f;
-                        else if (S.params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
-                        ret = ret + ev.L * tr * weight * throughput;
-                    }
-                    break;
-                }
-                Interaction it = compute_surface_interaction(S, hit.inst, hit.prim, hit.u, hit.v, true);
-                f3 rd{ray.dx, ray.dy, ray.dz}, ro{ray.ox, ray.oy, ray.oz};
-                it.wo = normalize(-rd);
-                ray.tmax = length(it.pos - ro) / length(rd);             // geometry.h:64-69
-                c_vert++;
-                if (mediums && ray_medium != VB_INVALID_ID) {            // integrator.cpp:199-206, homogeneous.cpp:50-70
-                    const vb_medium_rec &md = S.mediums[ray_medium];
-                    f3 sigma_t = medium_sigma_t(md);
-                    f3 sigma_s{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale};
-                    uint32_t channel = min((uint32_t)(sampler.next_1d() * 3.0f), 2u);
-                    float sc_t = channel == 0 ? sigma_t.x : (channel == 1 ? sigma_t.y : sigma_t.z);
-                    float dist = -vlog(1.0f - sampler.next_1d()) / sc_t;
-                    float t = fmin_(dist / length(rd), ray.tmax);
-                    bool sampled_medium = t < ray.tmax;
-                    if (sampled_medium) {
-                        it.pos = ro + rd * t;
-                        it.wo = -rd;
-                        it.ng = f3{0, 0, 0};
-                        it.uv = f2{0, 0};
-                        it.shading.x = f3{0, 0, 0}; it.shading.y = f3{0, 0, 0}; it.shading.z = f3{0, 0, 0};
-                        it.prim_area = 0.f;
-                        it.prim_id = VB_INVALID_ID; it.mat_id = VB_INVALID_ID; it.light_id = VB_INVALID_ID;
-                        it.has_phase = true; it.g = md.g;
-                        it.inside = ray_medium; it.outside = ray_medium;
-                    }
-                    f3 tr = medium_Tr(md, t);
-                    f3 density = sampled_medium ? sigma_t * tr : tr;
-                    float pdf = average3(density);
-                    f3 mt = sampled_medium ? tr * sigma_s / pdf : tr / pdf;
-                    throughput = throughput * mt;
-                }
-                if (it.mat_id == VB_INVALID_ID && !it.has_phase) {       // integrator.cpp:208-214
-                    ray = spawn_ray(it, rd);
-                    if (mediums) ray_medium = dot(it.ng, rd) > 0.f ? it.outside : it.inside;
-                    bounces -= 1;
-                    continue;
-                }
-                if (it.light_id != VB_INVALID_ID) {                      // integrator.cpp:221-231
-                    const vb_light_rec &l = S.lights[it.light_id];
-                    LightEval ev{f3{0, 0, 0}, 0.f};
-                    if (l.type == VB_LIGHT_AREA) {
-                        LightEvalCtx pl{it.pos, it.ng, it.uv, 1.0f / it.prim_area};
-                        pl.pdf_pos *= alias_pmf(S, l, it.prim_id);
-                        ev = area_evaluate_wi(S, l, ro, pl);
-                        ev.pdf *= 1.0f / (float)S.n_lights;
-                    }
-                    f3 tr = ray_Tr(S, ray_medium, ray);
-                    float weight = mis_weight(scatter_pdf, ev.pdf);
-                    if (S.params.mis_mode == 2) weight = 1.f;
-                    else if (S.params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
-                    f3 d = ev.L * throughput * weight * tr;
-                    ret = ret + d;
-                }
-                // light sampling
-                float u_light = sampler.next_1d();
-                f2 u_surface = sampler.next_2d();
-                LightSample ls{{f3{0, 0, 0}, 0.f}, f3{0, 0, 0}};
-                if (S.n_lights) {
-                    uint32_t n = S.n_lights;
-                    uint32_t index = (uint32_t)fmin_(u_light * (float)n, (float)n - 1.0f);
-                    const vb_light_rec &l = S.lights[index];
-                    if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(S, l, it, u_surface);
-                    else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(S, l, it, u_surface);
-                    else ls = point_sample_wi(S, l, it);
-                    ls.eval.pdf *= 1.0f / (float)n;
-                }
-                VbRay shadow = spawn_ray_to(it, ls.p_light);
-                uint32_t shadow_medium = mediums ? (dot(it.ng, f3{shadow.dx, shadow.dy, shadow.dz}) > 0.f ? it.outside : it.inside) : VB_INVALID_ID;
-                VbHit sh;
-                bool occluded = vb_traverse<true, false>(S.accel, shadow, sh, s_stack, PT_BLOCK, dummy0, dummy1, mg);
-                c_any++;
-                f3 tr = ray_Tr(S, shadow_medium, shadow);
-                // material / phase function, integrator.cpp:246-283 + direct_lighting :20-37
-                f3 wi = normalize(ls.p_light - it.pos);
-                ScatterEval se;
-                BSDFSample bs;
-                if (mediums && it.has_phase) {
-                    float f = phase_HG(dot(it.wo, wi), it.g);
-                    se.f = f3{f, f, f}; se.pdf = f; se.flags = 0;
-                    bs = phase_sample(it.g, it.wo, sampler);
-                } else {
-                    Lobe lobe = create_lobe(S, it);
-                    se = lobe_evaluate(S, lobe, it.wo, wi, false, nullptr);
-                    hemisphere_discard(se, it.wo, wi, it.ng);
-                    bs = lobe_sample(S, lobe, it.wo, sampler);
-                    hemisphere_discard(bs.eval, it.wo, bs.wi, it.ng);
-                }
-                bool is_delta = ls.eval.pdf < 0.f;
-                float weight = is_delta ? 1.f : mis_weight(ls.eval.pdf, se.pdf);
-                if (S.params.mis_mode == 1) weight = 1.f;
-                float lpdf = is_delta ? -ls.eval.pdf : ls.eval.pdf;
-                f3 Ld{0, 0, 0};
-                if (!occluded && se.pdf > 0.f && lpdf > 0.f) Ld = ls.eval.L * se.f * weight / lpdf;
-                if (S.params.mis_mode == 2) Ld = Ld * 0.f;
-                ret = ret + throughput * Ld * tr;
-                eta_scale *= sqr(bs.eta);
-                float lum = max_comp(throughput);
-                if (!(bs.eval.pdf > 0.f) || lum == 0.f) break;
-                throughput = throughput * (bs.eval.f / bs.eval.pdf);
-                if (eta_scale * lum < S.params.rr_threshold && bounces >= S.params.min_depth) {
-                    float q = fmin_(0.95f, lum);
-                    float rr = sampler.next_1d();
-                    if (q < rr) break;
-                    throughput = throughput / q;
-                }
-                scatter_pdf = bs.eval.pdf;
-                ray = spawn_ray(it, bs.wi);
-                if (mediums) ray_medium = dot(it.ng, bs.wi) > 0.f ? it.outside : it.inside;
-            }
-            last = make_float4(ret.x, ret.y, ret.z, 1.f);
+        }
+        if (__all_sync(~0u, done)) break;
+        bool run = !done && !need_new;
+        VbHit hit;
+        if (run) { vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, dummy0, dummy1, mg); c_closest++; }
+        int flags = 0;
+        VbRay shadow;
+        f3 pending{0, 0, 0};
+        if (run) flags = pt_bounce(S, ps, ray, hit, shadow, pending);
+        if (flags & PT_VERTEX) c_vert++;
+        if ((flags & PT_LIGHT) && !(flags & PT_SHADOW)) c_culled++;
+        if (flags & PT_SHADOW) {
+            VbHit sh;
+            bool occluded = vb_traverse<true, false>(S.accel, shadow, sh, s_stack, PT_BLOCK, dummy0, dummy1, mg);
+            c_any++;
+            if (!occluded) ps.ret = ps.ret + pending;
+        }
+        if (run && (!(flags & PT_CONTINUE) || ps.bounces >= max_depth)) {
+            last = make_float4(ps.ret.x, ps.ret.y, ps.ret.z, 1.f);
             if (mode == VB_ACCUM_LERP) {
                 float t = 1.0f / (float)(frames_done + fi + 1);
                 acc.x = acc.x + t * (last.x - acc.x); acc.y = acc.y + t * (last.y - acc.y);
@@ -179,15 +80,18 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
             } else {
                 acc.x += last.x; acc.y += last.y; acc.z += last.z; acc.w += last.w;
             }
+            fi++;
+            need_new = true;
         }
-        if (!DUMP_PRIMARY) { accum[pix] = acc; rt[pix] = last; }
     }
+    if (pix < n_pix) { accum[pix] = acc; rt[pix] = last; }
     for (int o = 16; o > 0; o >>= 1) {
         c_closest += __shfl_xor_sync(~0u, c_closest, o); c_any += __shfl_xor_sync(~0u, c_any, o); c_vert += __shfl_xor_sync(~0u, c_vert, o);
+        c_culled += __shfl_xor_sync(~0u, c_culled, o);
     }
     if ((threadIdx.x & 31) == 0 && counters) {
         atomicAdd(&counters->closest, (unsigned long long)c_closest); atomicAdd(&counters->any, (unsigned long long)c_any);
-        atomicAdd(&counters->vertices, (unsigned long long)c_vert);
+        atomicAdd(&counters->vertices, (unsigned long long)c_vert); atomicAdd(&counters->culled, (unsigned long long)c_culled);
     }
 }
 
@@ -547,7 +451,7 @@ int vb_render_stats(vb_ctx *ctx, uint64_t stats[4]) {
     if (!ctx || !stats) return VB_ERR_INVALID;
     vb_pt_state *p = pt_state(ctx);
     VB_CUDA(cudaStreamSynchronize(ctx->stream));
-    stats[0] = p->last.closest; stats[1] = p->last.any; stats[2] = p->last.vertices; stats[3] = 0;
+    stats[0] = p->last.closest; stats[1] = p->last.any; stats[2] = p->last.vertices; stats[3] = p->last.culled;
     return VB_OK;
 }
 
