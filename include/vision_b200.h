@@ -41,11 +41,14 @@ VB_API const char *vb_last_error(vb_ctx *ctx);           /* ctx may be NULL: las
  * the caller's CUDA events bracket it; NULL restores the context's own stream */
 VB_API int vb_ctx_set_stream(vb_ctx *ctx, void *cuda_stream);
 VB_API int vb_ctx_synchronize(vb_ctx *ctx);
-/* tuning knobs (defaults are the tuned values): "trace.refill_thr", "trace.tri_thr", "trace.blocks_per_sm" */
+/* tuning knobs (defaults are the tuned values): "trace.refill_thr", "trace.tri_thr", "trace.blocks_per_sm",
+ * "trace.sort_rays", "trace.sort_min_rays", "build.max_leaf"; path tracer: "pt.schedule" (0 = wavefront pipeline,
+ * default; 1 = single megakernel - same results), "pt.max_paths" (wavefront paths in flight) */
 VB_API int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value);
 /* device time (ms, CUDA events on the launching stream) and launch count of the kernels this
  * library launched since the last vb_profile_reset; name = "trace_closest" | "trace_any" |
- * "path_trace" | "bvh_build" | "film" | "all" */
+ * "path_trace" (megakernel) | "pt_generate" | "pt_shade" | "pt_shadow_resolve" | "pt_film" (wavefront) |
+ * "bvh_build" | "film" | "all" */
 VB_API int vb_profile_reset(vb_ctx *ctx);
 VB_API int vb_profile_get(vb_ctx *ctx, const char *name, double *ms, uint64_t *launches);
 

@@ -42,3 +42,21 @@ def test_image_matches_oracle(vbctx, oracle, name, min_mean):
     assert frac <= MAX_DIFF_PIXELS
     gst = vbctx.render_stats()
     assert abs(int(gst["any"] + gst["culled"]) - ost["any"]) <= 1e-3 * ost["any"]
+    # the megakernel schedule runs the same per-path code: identical film and counters
+    vbctx.set_option("pt.schedule", 1)
+    try:
+        vbctx.film_clear()
+        vbctx.render_frames(0, sc.spp, 1, capi.VB_ACCUM_LERP)
+        g2 = vbctx.film_download(capi.VB_FILM_ACCUM)
+        assert vbctx.render_stats() == gst
+    finally:
+        vbctx.set_option("pt.schedule", 0)
+    assert np.array_equal(g, g2)
+    # small batches (several per call) give the same film as one large batch
+    vbctx.set_option("pt.max_paths", 3 * sc.resolution[0] * sc.resolution[1])
+    try:
+        vbctx.film_clear()
+        vbctx.render_frames(0, sc.spp, 1, capi.VB_ACCUM_LERP)
+        assert np.array_equal(g, vbctx.film_download(capi.VB_FILM_ACCUM))
+    finally:
+        vbctx.set_option("pt.max_paths", 1 << 22)

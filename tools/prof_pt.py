@@ -16,6 +16,10 @@ if len(sys.argv) > 6:
 sc = scene_py.build_scene(path, ov)
 ctx = Context(0)
 ctx.upload_scene(sc)
+import os
+ctx.set_option("pt.schedule", int(os.environ.get("VB_SCHED", "0")))
+if "VB_MAX_PATHS" in os.environ:
+    ctx.set_option("pt.max_paths", int(os.environ["VB_MAX_PATHS"]))
 for r in range(reps):
     ctx.film_clear()
     torch.cuda.synchronize()
@@ -25,4 +29,7 @@ for r in range(reps):
     dt = time.perf_counter() - t0
     st = ctx.render_stats()
     rays = st["closest"] + st["any"]
+    prof = {k: ctx.profile_get(k) for k in ("trace_closest", "trace_any", "pt_generate", "pt_shade", "pt_shadow_resolve", "pt_film", "path_trace")}
+    ctx.profile_reset()
+    print("   ", {k: round(v[0], 2) for k, v in prof.items() if v[1]})
     print(f"rep {r}: {dt * 1e3:.2f} ms, {w * h * spp / dt / 1e6:.2f} Msamples/s, {rays / dt / 1e6:.1f} Mrays/s, {rays / (w * h * spp):.2f} rays/sample")

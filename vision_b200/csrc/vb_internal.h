@@ -75,6 +75,9 @@ struct vb_ctx {
     int opt_refill_thr = 28, opt_tri_thr = 12, opt_blocks_per_sm = 8;
     int opt_max_leaf = 1;
     int opt_sort_rays = 1, opt_sort_min_rays = 1 << 16;
+    int opt_pt_schedule = 0;                 // 0 = wavefront (default), 1 = megakernel
+    int opt_pt_sort_material = 1;            // wavefront: order shading entries by material
+    int64_t opt_pt_max_paths = 1 << 22;      // wavefront: paths in flight per batch
     void *sort_buf = nullptr; size_t sort_bytes = 0;
     vb_pt_state *pt = nullptr;
 
@@ -89,4 +92,5 @@ struct vb_ctx {
 };
 
 int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out);
+int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *keyidx_alt, uint32_t n, uint4 *hits4, uint8_t *occ);
 void vb_pt_destroy(vb_ctx *ctx);

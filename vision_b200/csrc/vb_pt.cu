@@ -389,4 +389,5 @@ __device__ VbRay generate_camera_ray(const PtScene &S, Sampler &sampler, uint32_
 }  // namespace
 
 #include "vb_pt_bounce.cuh"
+#include "vb_pt_wavefront.cuh"
 #include "vb_pt_kernel.cuh"

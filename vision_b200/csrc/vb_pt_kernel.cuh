@@ -121,7 +121,9 @@ __global__ void __launch_bounds__(256) k_film_resolve(const float4 *accum, float
 
 }  // namespace
 
+struct vb_wf_buffers;
 struct vb_pt_state {
+    vb_wf_buffers *wf = nullptr;       // queues of the wavefront schedule (allocated on first use)
     std::vector<DevMesh> h_meshes;
     DevMesh *d_meshes = nullptr;
     DevInst *d_inst = nullptr;
@@ -141,6 +143,8 @@ struct vb_pt_state {
     uint64_t geom_version = ~0ull;
 };
 
+#include "vb_pt_wavefront_host.cuh"
+
 static vb_pt_state *pt_state(vb_ctx *ctx) {
     if (!ctx->pt) ctx->pt = new vb_pt_state();
     return ctx->pt;
@@ -155,6 +159,7 @@ void vb_pt_destroy(vb_ctx *ctx) {
     for (auto &l : p->luts) cudaFree((void *)l.data);
     cudaFree(p->d_mediums);
     cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output); cudaFree(p->d_counters);
+    if (p->wf) { wf_free(*p->wf); delete p->wf; }
     delete p;
     ctx->pt = nullptr;
 }
@@ -368,6 +373,23 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     S.cam = p->cam; S.params = p->params; S.width = p->w; S.height = p->h;
     if (S.params.ray_offset_factor == 0.f) S.params.ray_offset_factor = 1.f;
     uint32_t n_pix = p->w * p->h;
+    if (!dump && ctx->opt_pt_schedule == 0) {
+        // wavefront schedule: batches of whole frames, at most opt_pt_max_paths paths in flight
+        if (!p->wf) p->wf = new vb_wf_buffers();
+        uint32_t per_batch = (uint32_t)std::max<uint64_t>(1, (uint64_t)ctx->opt_pt_max_paths / n_pix);
+        per_batch = std::min(per_batch, n_frames);
+        if ((uint64_t)per_batch * n_pix >= (1ull << 32)) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": film too large");
+        rc = wf_ensure(ctx, *p->wf, (size_t)per_batch * n_pix);
+        if (rc) return rc;
+        PtCounters total{};
+        for (uint32_t fi0 = 0; fi0 < n_frames; fi0 += per_batch) {
+            rc = wf_render_batch(ctx, p, *p->wf, S, first, stride, fi0, std::min(per_batch, n_frames - fi0), mode, total);
+            if (rc) return rc;
+        }
+        p->last = total;
+        p->frames_done += n_frames;
+        return VB_OK;
+    }
     unsigned grid = (n_pix + PT_BLOCK - 1) / PT_BLOCK;
     VB_CUDA(cudaMemsetAsync(p->d_counters, 0, sizeof(PtCounters), ctx->stream));
     ctx->prof_begin("path_trace", 1);

@@ -27,7 +27,8 @@ template <bool ANY, bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccelView A, RaysDev R, uint64_t n, HitsDev H, uint8_t *occ,
                                                        unsigned long long *counters, unsigned long long *next_ray,
                                                        int REFILL_THR, int TRI_THR,
-                                                       const float4 *__restrict__ RS, const uint32_t *__restrict__ perm) {
+                                                       const float4 *__restrict__ RS, const uint32_t *__restrict__ perm, int perm_stride,
+                                                       uint4 *H4) {
     __shared__ uint2 s_stack_all[VB_SM_STACK * TRACE_BLOCK];
     uint2 *s_stack = s_stack_all + threadIdx.x;
     uint2 l_stack[VB_LOCAL_STACK];
@@ -59,7 +60,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                 idx = base + __popc(idle & lt_mask);
                 if (idx < n) {
                     if (RS) {       // sorted order: gather ray perm[idx] from the AoS copy (one 32-byte sector); results go back to that slot
-                        idx = __ldg(perm + idx);
+                        if (perm) idx = __ldg(perm + idx * perm_stride);      // stride 2: low word of a 64-bit (key << 32 | index) record
                         float4 a = __ldg(RS + 2 * idx), b = __ldg(RS + 2 * idx + 1);
                         r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
                     } else {
@@ -145,6 +146,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
             // ---- retire finished rays ----
             if (active && !(G.y & 0xff000000u) && sp == 0 && !Tg.y) {
                 if (ANY) occ[idx] = occluded ? 1 : 0;
+                else if (H4) H4[idx] = make_uint4(hit.inst, hit.prim, __float_as_uint(hit.u), __float_as_uint(hit.v));   // queue form: one 16-byte record
                 else { H.inst[idx] = hit.inst; H.prim[idx] = hit.prim; H.u[idx] = hit.u; H.v[idx] = hit.v; H.t[idx] = hit.t; }
                 active = false;
             }
@@ -161,13 +163,6 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
 // ---- ray sorting: 24-bit Morton code of the origin (scene-normalised) + 3-bit direction octant ----
 // Incoherent rays become spatially coherent batches: consecutive rays walk the same subtrees, so
 // node/triangle fetches hit in L1/L2 instead of going to HBM as random 80/48-byte gathers.
-__device__ __forceinline__ uint32_t expand8(uint32_t v) {      // 8 bits -> every 3rd bit
-    v &= 0xffu;
-    v = (v | (v << 8)) & 0x00f00fu;
-    v = (v | (v << 4)) & 0x0c30c3u;
-    v = (v | (v << 2)) & 0x249249u;
-    return v;
-}
 __global__ void __launch_bounds__(256) k_ray_keys(RaysDev R, uint32_t n, float3 lo, float3 inv_ext, uint32_t *keys, uint32_t *vals,
                                                   float4 *aos) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -175,13 +170,7 @@ __global__ void __launch_bounds__(256) k_ray_keys(RaysDev R, uint32_t n, float3 
     float ox = __ldg(R.ox + i), oy = __ldg(R.oy + i), oz = __ldg(R.oz + i);
     float dx = __ldg(R.dx + i), dy = __ldg(R.dy + i), dz = __ldg(R.dz + i);
     // fminf/fmaxf drop NaN operands, so NaN origins land in cell 0
-    uint32_t ix = (uint32_t)fminf(fmaxf((ox - lo.x) * inv_ext.x * 128.f, 0.f), 127.f);
-    uint32_t iy = (uint32_t)fminf(fmaxf((oy - lo.y) * inv_ext.y * 128.f, 0.f), 127.f);
-    uint32_t iz = (uint32_t)fminf(fmaxf((oz - lo.z) * inv_ext.z * 128.f, 0.f), 127.f);
-    uint32_t oct = (dx < 0.f ? 4u : 0u) | (dy < 0.f ? 2u : 0u) | (dz < 0.f ? 1u : 0u);
-    // 24-bit key = 3 onesweep passes: 21-bit Morton code (128^3 cells; with 16 Mi rays that is still ~1 ray
-    // per key) + octant
-    keys[i] = (((expand8(ix) << 2) | (expand8(iy) << 1) | expand8(iz)) << 3) | oct;
+    keys[i] = vb_ray_sort_key(ox, oy, oz, dx, dy, dz, lo, inv_ext);
     vals[i] = i;
     // SoA -> AoS copy (streaming) so that the post-sort gather touches ONE 32-byte sector per ray
     aos[2 * (size_t)i] = make_float4(ox, oy, oz, __ldg(R.tmin + i));
@@ -271,11 +260,11 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
         launches += 5;
     }
     if (any) {
-        if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm);
-        else k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm);
+        if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+        else k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
     } else {
-        if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm);
-        else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm);
+        if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+        else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
     }
     ctx->cur_launches = launches;
     ctx->prof_end();
@@ -302,6 +291,48 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
 }
 
 }  // namespace
+
+// ---- queue form used by the wavefront path tracer (vb_pt_wavefront_host.cuh) -----------------------
+// rays: AoS records (o.xyz, tmin)(d.xyz, tmax); keyidx: (vb_ray_sort_key << 32 | queue index) per ray, written
+// by the producer kernel, sorted here on its 24 key bits (keyidx_alt = same-size scratch); results go to
+// hits4[index] = (inst, prim, u, v) or occ[index]. No staging, no host synchronisation.
+int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *keyidx_alt, uint32_t n, uint4 *hits4, uint8_t *occ) {
+    if (n == 0) return VB_OK;
+    const bool any = occ != nullptr;
+    cudaStream_t st = ctx->stream;
+    int rc = ctx->ensure_stage(128);
+    if (rc) return rc;
+    unsigned long long *d_cnt = (unsigned long long *)ctx->stage;
+    VB_CUDA(cudaMemsetAsync(d_cnt, 0, 32, st));
+    const uint32_t *perm = nullptr;
+    uint64_t launches = 1;
+    ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
+    if (ctx->opt_sort_rays && n >= (uint32_t)ctx->opt_sort_min_rays) {
+        size_t cub_bytes = 0;
+        cub::DoubleBuffer<uint64_t> dk(keyidx, keyidx_alt);
+        VB_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, cub_bytes, dk, (int)n, 32, 56, st));
+        if (cub_bytes > ctx->sort_bytes) {
+            if (ctx->sort_buf) cudaFree(ctx->sort_buf);
+            ctx->sort_buf = nullptr; ctx->sort_bytes = 0;
+            VB_CUDA(cudaMalloc(&ctx->sort_buf, cub_bytes + 256));
+            ctx->sort_bytes = cub_bytes + 256;
+        }
+        cudaError_t ce = cub::DeviceRadixSort::SortKeys(ctx->sort_buf, cub_bytes, dk, (int)n, 32, 56, st);
+        if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }
+        perm = (const uint32_t *)dk.Current();
+        launches += 4;
+    }
+    VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctx->opt_blocks_per_sm, ((uint64_t)n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+    RaysDev R{};
+    HitsDev H{};
+    if (any) k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, occ, d_cnt, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, nullptr);
+    else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, nullptr, d_cnt, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, hits4);
+    ctx->cur_launches = launches;
+    ctx->prof_end();
+    VB_CHECK_LAUNCH();
+    return VB_OK;
+}
 
 extern "C" {
 

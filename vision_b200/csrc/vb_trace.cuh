@@ -209,3 +209,20 @@ __device__ __forceinline__ bool vb_traverse(const VbAccelView &A, VbRay r, VbHit
     }
     return hit.inst != 0xffffffffu;
 }
+
+// ---- ray sort key: 21-bit Morton code of the origin (128^3 cells of the scene box) + 3-bit direction
+// octant = 24 bits = 3 onesweep radix passes. fminf/fmaxf drop NaN operands, so NaN origins land in cell 0.
+__device__ __forceinline__ uint32_t vb_expand8(uint32_t v) {      // 8 bits -> every 3rd bit
+    v &= 0xffu;
+    v = (v | (v << 8)) & 0x00f00fu;
+    v = (v | (v << 4)) & 0x0c30c3u;
+    v = (v | (v << 2)) & 0x249249u;
+    return v;
+}
+__device__ __forceinline__ uint32_t vb_ray_sort_key(float ox, float oy, float oz, float dx, float dy, float dz, float3 lo, float3 inv_ext) {
+    uint32_t ix = (uint32_t)fminf(fmaxf((ox - lo.x) * inv_ext.x * 128.f, 0.f), 127.f);
+    uint32_t iy = (uint32_t)fminf(fmaxf((oy - lo.y) * inv_ext.y * 128.f, 0.f), 127.f);
+    uint32_t iz = (uint32_t)fminf(fmaxf((oz - lo.z) * inv_ext.z * 128.f, 0.f), 127.f);
+    uint32_t oct = (dx < 0.f ? 4u : 0u) | (dy < 0.f ? 2u : 0u) | (dz < 0.f ? 1u : 0u);
+    return (((vb_expand8(ix) << 2) | (vb_expand8(iy) << 1) | vb_expand8(iz)) << 3) | oct;
+}
