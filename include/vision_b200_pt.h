@@ -143,5 +143,8 @@ VB_API int vb_dump_primary_hits(vb_ctx *ctx, uint32_t frame_index, const vb_hits
  * [3] shadow rays culled before tracing because their contribution is exactly zero (the reference traces them:
  * [1] + [3] is its any-hit count) */
 VB_API int vb_render_stats(vb_ctx *ctx, uint64_t stats[4]);
+/* traversal work of the last vb_render_frames call made with option "pt.count_work" = 1 (instrumented kernels,
+ * never timed): [0] wide nodes popped and [1] triangles tested by closest-hit rays, [2], [3] the same for any-hit rays */
+VB_API int vb_render_work(vb_ctx *ctx, uint64_t work[4]);
 
 #endif

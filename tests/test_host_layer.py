@@ -84,6 +84,44 @@ def test_host_records_equal_python_twin_materials_and_mediums(name):
         assert want in names, want
 
 
+@pytest.mark.parametrize("rel", ["scenes/cbox/cbox_lights.json", "scenes/classroom/vision_scene.json"])
+def test_host_records_equal_python_twin_lights_and_models(rel):
+    """model shape (OBJ), point / spot / spherical lights, AliasTable2D, world diameter, Euler transforms, light order"""
+    path = ROOT / rel
+    hp = host_api.HostPipeline(path)
+    hp.prepare_records()
+    a = hp.records()
+    b = scene_py.build_scene(path)
+    assert len(a.instances) == len(b.instances) and len(a.materials) == len(b.materials) and len(a.lights) == len(b.lights)
+    for ia, ib in zip(a.instances, b.instances):
+        assert np.array_equal(ia["o2w"], np.asarray(ib["o2w"], np.float32))
+        for k in ("material_id", "light_id", "inside_medium", "outside_medium"):
+            assert ia[k] == ib.get(k, capi.VB_INVALID_ID), k
+        ma, mb = a.meshes[ia["mesh_id"]], b.meshes[ib["mesh_id"]]
+        for k in ("pos", "nrm", "uv", "tri"):
+            assert np.array_equal(ma[k], np.asarray(mb[k]).reshape(ma[k].shape)), k
+    assert [_bytes(x) for x in a.materials] == [_bytes(x) for x in b.materials]
+    assert [_bytes(x) for x in a.lights] == [_bytes(x) for x in b.lights]
+    assert a.alias_table == [(float(np.float32(p)), i) for p, i in b.alias_table] and a.alias_func == b.alias_func
+    assert _bytes(a.params) == _bytes(b.params) and a.camera.medium_id == b.camera.medium_id
+    assert len(a.textures) == len(b.textures)
+    for x, y in zip(a.textures, b.textures):
+        assert x.shape == y.shape
+        np.testing.assert_allclose(x, y, atol=2e-6)
+    if "classroom" in rel:
+        assert len(a.meshes) == 79 and sum(len(m["tri"]) for m in a.meshes) == 103832
+        env = a.lights[0]
+        assert env.type == capi.VB_LIGHT_ENV and list(env.env_res) == [512, 256] and env.alias_size == 256 and env.cond_offset == 256
+        assert env.params[0] > 300.0            # the scaled ground plane sets the world diameter
+    else:
+        assert [l.type for l in a.lights] == [capi.VB_LIGHT_POINT, capi.VB_LIGHT_SPOT, capi.VB_LIGHT_ENV, capi.VB_LIGHT_AREA]
+        assert a.instances[-1]["light_id"] == 3
+    names = host_api.plugin_names()
+    for want in ("vision-shape-model#constructor", "vision-light-point#constructor", "vision-light-spot#constructor",
+                 "vision-light-spherical#constructor"):
+        assert want in names, want
+
+
 def test_desc_defaults_and_errors(tmp_path):
     p = tmp_path / "s.json"
     p.write_text('{ // comment\n "shapes": [ {"type":"quad","name":"q","param":{"material":"m"}} ], /* c */ "materials": [ {"type":"diffuse","name":"m","param":{}} ], "camera": {"param": {"transform": {"type":"look_at","param":{"position":[0,0,5],"target_pos":[0,0,0]}}, "filter": {"type":"box"}}} }')
@@ -101,7 +139,8 @@ def test_desc_defaults_and_errors(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("SCENE", [SCENE, ROOT / "scenes" / "cbox" / "cbox_materials.json", ROOT / "scenes" / "cbox" / "cbox_fog.json"])
+@pytest.mark.parametrize("SCENE", [SCENE, ROOT / "scenes" / "cbox" / "cbox_materials.json", ROOT / "scenes" / "cbox" / "cbox_fog.json",
+                                   ROOT / "scenes" / "cbox" / "cbox_lights.json"])
 def test_host_pipeline_renders_like_python_path(vbctx, SCENE):
     hp = host_api.HostPipeline(SCENE)
     hp.prepare(0)

@@ -20,6 +20,13 @@ import os
 ctx.set_option("pt.schedule", int(os.environ.get("VB_SCHED", "0")))
 if "VB_MAX_PATHS" in os.environ:
     ctx.set_option("pt.max_paths", int(os.environ["VB_MAX_PATHS"]))
+if os.environ.get("VB_COUNT"):
+    ctx.set_option("pt.count_work", 1)
+    ctx.film_clear(); ctx.render_frames(0, 1, 1, capi.VB_ACCUM_SUM); ctx.synchronize()
+    st, wk = ctx.render_stats(), ctx.render_work()
+    print(f"work: closest {wk['closest_nodes'] / st['closest']:.1f} nodes {wk['closest_tris'] / st['closest']:.2f} tris per ray; "
+          f"any {wk['any_nodes'] / max(st['any'], 1):.1f} nodes {wk['any_tris'] / max(st['any'], 1):.2f} tris per ray; build", ctx.build_stats if hasattr(ctx, "build_stats") else "")
+    ctx.set_option("pt.count_work", 0)
 for r in range(reps):
     ctx.film_clear()
     torch.cuda.synchronize()

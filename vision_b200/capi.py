@@ -358,6 +358,7 @@ def _bind_pt(lib):
         "vb_film_device_ptr": [vp, C.c_int, C.POINTER(vp)],
         "vb_dump_primary_hits": [vp, C.c_uint32, C.POINTER(vb_hits_soa)],
         "vb_render_stats": [vp, C.POINTER(C.c_uint64)],
+        "vb_render_work": [vp, C.POINTER(C.c_uint64)],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
@@ -460,7 +461,12 @@ def _pt_methods():
         self._check(self.lib.vb_render_stats(self.h, st), "vb_render_stats")
         return {"closest": st[0], "any": st[1], "vertices": st[2], "culled": st[3]}
 
-    for f in (upload_scene, render_frames, film_clear, film_resolve, film_download, film_device_ptr,
+    def render_work(self):
+        w = (C.c_uint64 * 4)()
+        self._check(self.lib.vb_render_work(self.h, w), "vb_render_work")
+        return {"closest_nodes": w[0], "closest_tris": w[1], "any_nodes": w[2], "any_tris": w[3]}
+
+    for f in (render_work, upload_scene, render_frames, film_clear, film_resolve, film_download, film_device_ptr,
               dump_primary_hits, render_stats):
         setattr(Context, f.__name__, f)
 

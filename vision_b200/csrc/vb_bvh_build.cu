@@ -35,6 +35,7 @@ struct BuildBufs {
     uint32_t *left, *right, *first, *last;   // T-1
     uint32_t *parent;      // 2T-1
     uint32_t *flags;       // T-1
+    double *moments;       // 6    sum and sum of squares of the normalised triangle centroids (ray-sort box)
 };
 
 // normative world transform: FMA chain identical to oracle vo::transform_point
@@ -106,6 +107,21 @@ __device__ __forceinline__ uint64_t expand21(uint32_t v) {   // spread 21 bits t
 
 __global__ void __launch_bounds__(256) k_morton(uint32_t T, BuildBufs b) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    double m[6] = {0, 0, 0, 0, 0, 0};
+    if (g < T) {
+        float3 slo = make_float3(ord2f(b.scene[0]), ord2f(b.scene[1]), ord2f(b.scene[2]));
+        float3 shi = make_float3(ord2f(b.scene[3]), ord2f(b.scene[4]), ord2f(b.scene[5]));
+        float4 lo = b.blo[g], hi = b.bhi[g];
+        m[0] = (0.5f * (lo.x + hi.x) - slo.x) / fmaxf(shi.x - slo.x, 1e-30f);
+        m[1] = (0.5f * (lo.y + hi.y) - slo.y) / fmaxf(shi.y - slo.y, 1e-30f);
+        m[2] = (0.5f * (lo.z + hi.z) - slo.z) / fmaxf(shi.z - slo.z, 1e-30f);
+        m[3] = m[0] * m[0]; m[4] = m[1] * m[1]; m[5] = m[2] * m[2];
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        for (int o = 16; o > 0; o >>= 1) m[k] += __shfl_xor_sync(~0u, m[k], o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(b.moments + k, m[k]);
+    }
     if (g >= T) return;
     float3 slo = make_float3(ord2f(b.scene[0]), ord2f(b.scene[1]), ord2f(b.scene[2]));
     float3 shi = make_float3(ord2f(b.scene[3]), ord2f(b.scene[4]), ord2f(b.scene[5]));

@@ -166,6 +166,7 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     DevBuf<float4> tri_in, blo, bhi, nlo, nhi;
     DevBuf<uint32_t> scene, vals, vals2, left, right, first, last, parent, flags;
     DevBuf<uint64_t> keys, keys2;
+    DevBuf<double> moments;
     DevBuf<WorkItem> q0, q1; DevBuf<Counters> cnt;
     VB_CUDA(d_geom.alloc(n_inst)); VB_CUDA(d_off.alloc(n_inst + 1));
     VB_CUDA(tri_in.alloc(3 * (size_t)T)); VB_CUDA(blo.alloc(T)); VB_CUDA(bhi.alloc(T));
@@ -174,6 +175,7 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     VB_CUDA(left.alloc(T)); VB_CUDA(right.alloc(T)); VB_CUDA(first.alloc(T)); VB_CUDA(last.alloc(T));
     VB_CUDA(parent.alloc(2 * (size_t)T)); VB_CUDA(flags.alloc(T));
     VB_CUDA(keys.alloc(T)); VB_CUDA(keys2.alloc(T));
+    VB_CUDA(moments.alloc(6));
     VB_CUDA(q0.alloc(T)); VB_CUDA(q1.alloc(T)); VB_CUDA(cnt.alloc(1));
     // worst case one wide node per 2 triangles is never reached; T+1 nodes is a safe bound
     vb_wide_node *d_nodes = nullptr; float4 *d_tris = nullptr;
@@ -181,13 +183,14 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     VB_CUDA(cudaMalloc(&d_tris, 3 * (size_t)T * sizeof(float4)));
 
     BuildBufs b{tri_in.p, blo.p, bhi.p, scene.p, keys.p, keys2.p, vals.p, vals2.p, nlo.p, nhi.p,
-                left.p, right.p, first.p, last.p, parent.p, flags.p};
+                left.p, right.p, first.p, last.p, parent.p, flags.p, moments.p};
 
     cudaEvent_t e0 = ctx->get_event(), e1 = ctx->get_event();
     VB_CUDA(cudaMemcpyAsync(d_geom.p, hg.data(), sizeof(InstGeom) * n_inst, cudaMemcpyHostToDevice, st));
     VB_CUDA(cudaMemcpyAsync(d_off.p, off.data(), sizeof(uint32_t) * (n_inst + 1), cudaMemcpyHostToDevice, st));
     uint32_t scene_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
     VB_CUDA(cudaMemcpyAsync(scene.p, scene_init, sizeof(scene_init), cudaMemcpyHostToDevice, st));
+    VB_CUDA(cudaMemsetAsync(moments.p, 0, 6 * sizeof(double), st));
     VB_CUDA(cudaEventRecord(e0, st));
     uint64_t launches = 0;
     uint32_t grid = (T + 255) / 256;
@@ -251,6 +254,18 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     s.n_triangles = T; s.n_nodes = hc.n_nodes; s.node_bytes = (uint64_t)hc.n_nodes * sizeof(vb_wide_node); s.tri_bytes = (uint64_t)T * 48;
     s.build_ms = ms;
     for (int a = 0; a < 3; ++a) { s.scene_lo[a] = ord2f(hs[a]); s.scene_hi[a] = ord2f(hs[3 + a]); }
+    // ray-sort box: mean +- 2.5 sigma of the triangle centroids, clipped to the scene box. Rays start on
+    // surfaces, so the Morton cells of the sort key go where the geometry is even when a few huge
+    // triangles (ground planes, sky domes) inflate the scene box.
+    double hm[6];
+    VB_CUDA(cudaMemcpy(hm, moments.p, sizeof(hm), cudaMemcpyDeviceToHost));
+    for (int a = 0; a < 3; ++a) {
+        double mean = hm[a] / T, var = std::max(0.0, hm[3 + a] / T - mean * mean), sd = std::sqrt(var);
+        double lo = std::max(0.0, mean - 2.5 * sd), hi = std::min(1.0, mean + 2.5 * sd);
+        if (!(hi > lo)) { lo = 0.0; hi = 1.0; }
+        double ext = (double)s.scene_hi[a] - (double)s.scene_lo[a];
+        ctx->sort_lo[a] = (float)(s.scene_lo[a] + lo * ext); ctx->sort_hi[a] = (float)(s.scene_lo[a] + hi * ext);
+    }
     ctx->prof["bvh_build"].ms += ms; ctx->prof["bvh_build"].launches += launches;
     ctx->prof["all"].ms += ms; ctx->prof["all"].launches += launches;
     if (out) *out = s;

@@ -64,6 +64,7 @@ struct vb_ctx {
     vb_instance *d_instances = nullptr;
     vb_accel accel;
     vb_build_stats build_stats{};
+    float sort_lo[3] = {0, 0, 0}, sort_hi[3] = {1, 1, 1};   // box of the ray-sort Morton key (vb_bvh_collapse.cuh)
     std::map<std::string, vb_prof_slot> prof;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::vector<std::pair<std::string, std::pair<cudaEvent_t, cudaEvent_t>>> pending;  // un-resolved timings
@@ -77,6 +78,7 @@ struct vb_ctx {
     int opt_sort_rays = 1, opt_sort_min_rays = 1 << 16;
     int opt_pt_schedule = 0;                 // 0 = wavefront (default), 1 = megakernel
     int opt_pt_sort_material = 1;            // wavefront: order shading entries by material
+    int opt_pt_count_work = 0;               // wavefront: instrumented traversal (nodes / triangles per ray), never timed
     int64_t opt_pt_max_paths = 1 << 22;      // wavefront: paths in flight per batch
     void *sort_buf = nullptr; size_t sort_bytes = 0;
     vb_pt_state *pt = nullptr;
@@ -92,5 +94,6 @@ struct vb_ctx {
 };
 
 int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out);
-int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *keyidx_alt, uint32_t n, uint4 *hits4, uint8_t *occ);
+int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *keyidx_alt, uint32_t n, uint4 *hits4, uint8_t *occ,
+                   unsigned long long *work = nullptr);
 void vb_pt_destroy(vb_ctx *ctx);

@@ -124,6 +124,8 @@ __global__ void __launch_bounds__(256) k_film_resolve(const float4 *accum, float
 struct vb_wf_buffers;
 struct vb_pt_state {
     vb_wf_buffers *wf = nullptr;       // queues of the wavefront schedule (allocated on first use)
+    uint32_t n_mat_types = 0;          // distinct material models in use (one: ordering the shading queue is pointless)
+    uint64_t work[4] = {0, 0, 0, 0};
     std::vector<DevMesh> h_meshes;
     DevMesh *d_meshes = nullptr;
     DevInst *d_inst = nullptr;
@@ -235,6 +237,9 @@ int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n) {
         if (mat[i].type == VB_MAT_PRINCIPLED || mat[i].type > VB_MAT_BLACK_BODY)
             return ctx->fail(VB_ERR_UNSUPPORTED, "vb_materials_set: material type " + std::to_string(mat[i].type) + " not implemented yet");
     cudaFree(p->d_mat); p->d_mat = nullptr; p->n_mat = n;
+    uint32_t types = 0;
+    for (uint32_t i = 0; i < n; ++i) types |= 1u << mat[i].type;
+    p->n_mat_types = (uint32_t)__builtin_popcount(types);
     if (n) {
         VB_CUDA(cudaMalloc(&p->d_mat, sizeof(vb_material_rec) * n));
         VB_CUDA(cudaMemcpy(p->d_mat, mat, sizeof(vb_material_rec) * n, cudaMemcpyHostToDevice));
@@ -382,11 +387,16 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
         rc = wf_ensure(ctx, *p->wf, (size_t)per_batch * n_pix);
         if (rc) return rc;
         PtCounters total{};
+        if (ctx->opt_pt_count_work) VB_CUDA(cudaMemsetAsync(p->wf->d_work, 0, 32, ctx->stream));
         for (uint32_t fi0 = 0; fi0 < n_frames; fi0 += per_batch) {
             rc = wf_render_batch(ctx, p, *p->wf, S, first, stride, fi0, std::min(per_batch, n_frames - fi0), mode, total);
             if (rc) return rc;
         }
         p->last = total;
+        if (ctx->opt_pt_count_work) {
+            VB_CUDA(cudaMemcpyAsync(p->work, p->wf->d_work, 32, cudaMemcpyDeviceToHost, ctx->stream));
+            VB_CUDA(cudaStreamSynchronize(ctx->stream));
+        }
         p->frames_done += n_frames;
         return VB_OK;
     }
@@ -474,6 +484,14 @@ int vb_render_stats(vb_ctx *ctx, uint64_t stats[4]) {
     vb_pt_state *p = pt_state(ctx);
     VB_CUDA(cudaStreamSynchronize(ctx->stream));
     stats[0] = p->last.closest; stats[1] = p->last.any; stats[2] = p->last.vertices; stats[3] = p->last.culled;
+    return VB_OK;
+}
+
+int vb_render_work(vb_ctx *ctx, uint64_t work[4]) {
+    if (!ctx || !work) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < 4; ++k) work[k] = p->work[k];
     return VB_OK;
 }
 

@@ -15,11 +15,13 @@ struct vb_wf_buffers {
     uint8_t *occ = nullptr;
     WfCounters *d_cnt = nullptr, *h_cnt = nullptr;
     void *cub_tmp = nullptr; size_t cub_bytes = 0;
+    unsigned long long *d_work = nullptr;    // [closest nodes, closest tris, any nodes, any tris] of an instrumented call
 };
 
 static void wf_free(vb_wf_buffers &w) {
     cudaFree(w.mem); w.mem = nullptr; w.capacity = 0;
     cudaFree(w.d_cnt); w.d_cnt = nullptr;
+    cudaFree(w.d_work); w.d_work = nullptr;
     cudaFree(w.cub_tmp); w.cub_tmp = nullptr; w.cub_bytes = 0;
     if (w.h_cnt) cudaFreeHost(w.h_cnt);
     w.h_cnt = nullptr;
@@ -29,6 +31,7 @@ static int wf_ensure(vb_ctx *ctx, vb_wf_buffers &w, size_t P) {
     if (!w.d_cnt) {
         VB_CUDA(cudaMalloc(&w.d_cnt, sizeof(WfCounters)));
         VB_CUDA(cudaMallocHost(&w.h_cnt, sizeof(WfCounters)));
+        VB_CUDA(cudaMalloc(&w.d_work, 4 * sizeof(unsigned long long)));
     }
     if (P <= w.capacity) return VB_OK;
     cudaFree(w.mem); w.mem = nullptr; w.capacity = 0;
@@ -70,11 +73,10 @@ static int wf_render_batch(vb_ctx *ctx, vb_pt_state *p, vb_wf_buffers &w, const 
     cudaStream_t st = ctx->stream;
     const uint32_t n_pix = p->w * p->h;
     const uint32_t P = n_pix * nf;
-    const vb_build_stats &bs = ctx->build_stats;
     WfSortBox B;
-    B.lo = make_float3(bs.scene_lo[0], bs.scene_lo[1], bs.scene_lo[2]);
-    B.inv_ext = make_float3(1.f / fmaxf(bs.scene_hi[0] - bs.scene_lo[0], 1e-30f), 1.f / fmaxf(bs.scene_hi[1] - bs.scene_lo[1], 1e-30f),
-                            1.f / fmaxf(bs.scene_hi[2] - bs.scene_lo[2], 1e-30f));
+    B.lo = make_float3(ctx->sort_lo[0], ctx->sort_lo[1], ctx->sort_lo[2]);
+    B.inv_ext = make_float3(1.f / fmaxf(ctx->sort_hi[0] - ctx->sort_lo[0], 1e-30f), 1.f / fmaxf(ctx->sort_hi[1] - ctx->sort_lo[1], 1e-30f),
+                            1.f / fmaxf(ctx->sort_hi[2] - ctx->sort_lo[2], 1e-30f));
     ctx->prof_begin("pt_generate", 1);
     k_wf_generate<<<(P + 255) / 256, 256, 0, st>>>(S, first, stride, fi0, P, WfQueue{w.rays[0], w.keys[0], w.slot_q[0]}, B, w.st);
     ctx->prof_end();
@@ -87,13 +89,14 @@ static int wf_render_batch(vb_ctx *ctx, vb_pt_state *p, vb_wf_buffers &w, const 
         WfQueue Qin{w.rays[cur], k0, w.slot_q[cur]};
         WfQueue Qout{w.rays[cur ^ 1], w.keys[2 * (cur ^ 1)], w.slot_q[cur ^ 1]};
         WfQueue Qsh{w.rays[2], w.keys[4], nullptr};
-        int rc = vb_trace_queue(ctx, Qin.rays, k0, k1, n, w.hits4, nullptr);
+        unsigned long long *work = ctx->opt_pt_count_work ? w.d_work : nullptr;
+        int rc = vb_trace_queue(ctx, Qin.rays, k0, k1, n, w.hits4, nullptr, work);
         if (rc) return rc;
         total.closest += n;
         VB_CUDA(cudaMemsetAsync(w.d_cnt, 0, sizeof(WfCounters), st));
         const uint64_t *order = nullptr;
         ctx->prof_begin("pt_shade", 1);
-        if (ctx->opt_pt_sort_material && n >= 4096) {
+        if (ctx->opt_pt_sort_material && p->n_mat_types > 1 && n >= 4096) {
             k_wf_material_keys<<<(n + 255) / 256, 256, 0, st>>>(S, n, w.hits4, k0);
             rc = wf_sort_by_material(ctx, w, k0, k1, n, &order);
             if (rc) { ctx->prof_end(); return rc; }
@@ -106,7 +109,7 @@ static int wf_render_batch(vb_ctx *ctx, vb_pt_state *p, vb_wf_buffers &w, const 
         const WfCounters c = *w.h_cnt;
         total.vertices += c.vertices; total.culled += c.culled;
         if (c.n_shadow) {
-            rc = vb_trace_queue(ctx, Qsh.rays, w.keys[4], k0, c.n_shadow, nullptr, w.occ);     // k0/k1 are free again
+            rc = vb_trace_queue(ctx, Qsh.rays, w.keys[4], k0, c.n_shadow, nullptr, w.occ, work ? work + 2 : nullptr);     // k0/k1 are free again
             if (rc) return rc;
             total.any += c.n_shadow;
             ctx->prof_begin("pt_shadow_resolve", 1);

@@ -246,10 +246,9 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
     }
     ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
     if (do_sort) {
-        const vb_build_stats &bs = ctx->build_stats;
-        float3 lo = make_float3(bs.scene_lo[0], bs.scene_lo[1], bs.scene_lo[2]);
-        float3 ie = make_float3(1.f / fmaxf(bs.scene_hi[0] - bs.scene_lo[0], 1e-30f), 1.f / fmaxf(bs.scene_hi[1] - bs.scene_lo[1], 1e-30f),
-                                1.f / fmaxf(bs.scene_hi[2] - bs.scene_lo[2], 1e-30f));
+        float3 lo = make_float3(ctx->sort_lo[0], ctx->sort_lo[1], ctx->sort_lo[2]);
+        float3 ie = make_float3(1.f / fmaxf(ctx->sort_hi[0] - ctx->sort_lo[0], 1e-30f), 1.f / fmaxf(ctx->sort_hi[1] - ctx->sort_lo[1], 1e-30f),
+                                1.f / fmaxf(ctx->sort_hi[2] - ctx->sort_lo[2], 1e-30f));
         unsigned g2 = (unsigned)((n + 255) / 256);
         k_ray_keys<<<g2, 256, 0, st>>>(R, (uint32_t)n, lo, ie, k0, v0, d_aos);
         cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
@@ -296,7 +295,8 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
 // rays: AoS records (o.xyz, tmin)(d.xyz, tmax); keyidx: (vb_ray_sort_key << 32 | queue index) per ray, written
 // by the producer kernel, sorted here on its 24 key bits (keyidx_alt = same-size scratch); results go to
 // hits4[index] = (inst, prim, u, v) or occ[index]. No staging, no host synchronisation.
-int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *keyidx_alt, uint32_t n, uint4 *hits4, uint8_t *occ) {
+int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *keyidx_alt, uint32_t n, uint4 *hits4, uint8_t *occ,
+                   unsigned long long *work) {
     if (n == 0) return VB_OK;
     const bool any = occ != nullptr;
     cudaStream_t st = ctx->stream;
@@ -326,7 +326,10 @@ int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctx->opt_blocks_per_sm, ((uint64_t)n + TRACE_BLOCK - 1) / TRACE_BLOCK);
     RaysDev R{};
     HitsDev H{};
-    if (any) k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, occ, d_cnt, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, nullptr);
+    // work != null: instrumented run, [nodes popped, triangles tested] are ADDED to work[0..1] (never timed)
+    if (work && any) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, occ, work, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, nullptr);
+    else if (work) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, nullptr, work, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, hits4);
+    else if (any) k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, occ, d_cnt, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, nullptr);
     else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, nullptr, d_cnt, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, hits4);
     ctx->cur_launches = launches;
     ctx->prof_end();

@@ -136,7 +136,8 @@ void LightSamplerDesc::init(const ParameterSet &ps) {
     init_common(ps);
     sub_type = ps["type"].as_string("uniform");
     parameter = ps.value("param");
-    const Json &l = parameter["lights"].data();
+    const ParameterSet lights = parameter["lights"];        // keep the temporary alive: data() returns a reference into it
+    const Json &l = lights.data();
     if (l.is_array()) for (auto &e : l.arr) { LightDesc d; d.init(ParameterSet(e)); light_descs.push_back(d); }
 }
 void SpectrumDesc::init(const ParameterSet &ps) { init_common(ps); sub_type = ps["type"].as_string("srgb"); parameter = ps.value("param"); }
@@ -163,7 +164,7 @@ void SceneDesc::init(const Json &data) {
     mediums_desc.init(med);
     process_mediums = mediums_desc.process;
     const Json &shapes = data.at("shapes");
-    if (shapes.is_array()) for (auto &s : shapes.arr) { ShapeDesc d; d.init(ParameterSet(s)); shape_descs.push_back(d); }
+    if (shapes.is_array()) for (auto &s : shapes.arr) { ShapeDesc d; d.init(ParameterSet(s)); d.parameter.set_value("scene_path", Json::string(scene_path)); shape_descs.push_back(d); }
     sensor_desc.init(root.value("camera"));
     output_desc.init(root.value("output"));
     render_setting.init(root.value("render_setting"));

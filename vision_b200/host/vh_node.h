@@ -65,7 +65,7 @@ template <class T, class D> std::shared_ptr<T> create_shared(const D &desc) {
         static vh::NodeConstructor<Class> ret;                                                                 \
         return &ret;                                                                                           \
     }                                                                                                          \
-    static const bool VH_CONCAT(vh_reg_, __LINE__) = [] {                                                      \
+    static const bool VH_CONCAT(vh_reg_, __COUNTER__) = [] {                                                      \
         vh::PluginRegistry::instance().add("vision-" #category "-" #plugname, #ctor,                           \
                                            VH_CONCAT(VH_CONCAT(vision_##category##_##plugname, __), ctor)());  \
         return true;                                                                                           \

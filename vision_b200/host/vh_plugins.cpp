@@ -354,3 +354,4 @@ VH_MAKE_CLASS_CREATOR(UniformLightSampler, lightsampler, uniform, constructor)
 }  // namespace vh
 
 #include "vh_plugins2.inl"
+#include "vh_plugins3.inl"

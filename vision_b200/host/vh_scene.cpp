@@ -27,7 +27,10 @@ static bool read_pnm_token(std::istream &f, std::string &tok) {
 Image load_image(const std::string &path, bool to_linear) {
     std::string p = path;
     auto ends = [&](const char *e) { size_t n = strlen(e); return p.size() >= n && strcasecmp(p.c_str() + p.size() - n, e) == 0; };
-    if (!ends(".pfm") && !ends(".ppm")) p = path + ".pfm";          // decoded side-car (tools/convert_textures.py)
+    if (!ends(".pfm") && !ends(".ppm")) {                          // decoded side-car (tools/convert_textures.py): 8-bit .ppm, else float .pfm
+        p = path + ".ppm";
+        if (!std::ifstream(p, std::ios::binary)) p = path + ".pfm";
+    }
     std::ifstream f(p, std::ios::binary);
     if (!f) throw std::runtime_error("cannot open image " + path + " (run tools/convert_textures.py to write " + p + ")");
     std::string magic, tw, th, ts;
@@ -95,6 +98,30 @@ static void load_lut(SceneRecords::Lut &l, const std::string &file, uint32_t nx,
 std::shared_ptr<Material> Scene::obtain_black_body() {
     if (!black_body) { MaterialDesc d; d.sub_type = "black_body"; d.name = "__black_body"; black_body = create_shared<Material>(d); materials.push_back(black_body); }
     return black_body;
+}
+
+// 2 * max(radius of the world box, render_setting.min_world_radius); the box is accumulated in double over the
+// vertices the triangles use (vision_b200/scene_py.py world_diameter is the twin)
+float Scene::world_diameter() const {
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    bool any = false;
+    for (auto &i : instances) {
+        const MeshData &m = *i->mesh;
+        std::vector<char> used(m.nv(), 0);
+        for (uint32_t v : m.tri) used[v] = 1;
+        for (uint32_t v = 0; v < m.nv(); ++v) {
+            if (!used[v]) continue;
+            double p[3] = {m.pos[3 * v], m.pos[3 * v + 1], m.pos[3 * v + 2]};
+            for (int r = 0; r < 3; ++r) {
+                double q = p[0] * (double)i->o2w[r] + p[1] * (double)i->o2w[4 + r] + p[2] * (double)i->o2w[8 + r] + (double)i->o2w[12 + r];
+                lo[r] = std::min(lo[r], q); hi[r] = std::max(hi[r], q);
+            }
+            any = true;
+        }
+    }
+    double radius = 0.0;
+    if (any) { double d[3] = {hi[0] - lo[0], hi[1] - lo[1], hi[2] - lo[2]}; radius = 0.5 * std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]); }
+    return (float)(2.0 * std::max(radius, (double)desc.render_setting.min_world_radius));
 }
 
 // reference scene.cpp:16-34: light_sampler, spectrum, materials, mediums, sensor, shapes, integrator, sampler

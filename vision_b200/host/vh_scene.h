@@ -63,6 +63,7 @@ public:
     void add_shape(const std::shared_ptr<ShapeGroup> &group, const ShapeDesc &sd);
     void prepare(SceneRecords &out);                  // scene.cpp:79-91 + geometry.cpp:20-34
     std::shared_ptr<Material> obtain_black_body();
+    float world_diameter() const;                     // scene.h:108-109 over the instance boxes (shape.cpp:73-85)
 };
 
 class Pipeline : public Node {     // "vision-pipeline-fixed"

@@ -192,19 +192,21 @@ def obj_mesh(path, smooth=False, flip_uv=True):
                         faces.append(tri)
     V = np.asarray(V, f32).reshape(-1, 3); VT = np.asarray(VT, f32).reshape(-1, 2); VN = np.asarray(VN, f32).reshape(-1, 3)
     key_to_index, pos, nrm, uv, tris = {}, [], [], [], []
+    def cross3(a, b, t):
+        return np.array([t(t(a[1] * b[2]) - t(a[2] * b[1])), t(t(a[2] * b[0]) - t(a[0] * b[2])), t(t(a[0] * b[1]) - t(a[1] * b[0]))], t)
     acc = None
     if smooth and not len(VN):
         acc = np.zeros((len(V), 3), np.float64)
         for tri in faces:
             p = V[[c[0] for c in tri]].astype(np.float64)
-            acc[[c[0] for c in tri]] += np.cross(p[1] - p[0], p[2] - p[0])
+            acc[[c[0] for c in tri]] += cross3(p[1] - p[0], p[2] - p[0], np.float64)
     for tri in faces:
         fn = None
         if not len(VN) and acc is None:
             p = V[[c[0] for c in tri]]
-            n = np.cross((p[1] - p[0]).astype(f32), (p[2] - p[0]).astype(f32)).astype(f32)
-            l = f32(np.sqrt(f32(np.dot(n, n))))
-            fn = tuple((n / l).astype(f32)) if l > 0 else (0.0, 0.0, 0.0)
+            n = cross3((p[1] - p[0]).astype(f32), (p[2] - p[0]).astype(f32), f32)
+            l = f32(np.sqrt(f32(f32(f32(n[0] * n[0]) + f32(n[1] * n[1])) + f32(n[2] * n[2]))))
+            fn = tuple(float(x) for x in (n / l).astype(f32)) if l > 0 else (0.0, 0.0, 0.0)
         out = []
         for (iv, it, inn) in tri:
             key = (iv, it, inn, fn)
@@ -216,7 +218,7 @@ def obj_mesh(path, smooth=False, flip_uv=True):
                 if inn >= 0:
                     nrm.append(VN[inn])
                 elif acc is not None:
-                    a = acc[iv]; l = np.linalg.norm(a)
+                    a = acc[iv]; l = math.sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2])
                     nrm.append((a / l if l > 0 else a).astype(f32))
                 else:
                     nrm.append(np.asarray(fn, f32))
@@ -228,16 +230,38 @@ def obj_mesh(path, smooth=False, flip_uv=True):
             "uv": np.asarray(uv, f32).reshape(-1, 2), "tri": np.asarray(tris, np.uint32).reshape(-1, 3)}
 
 
+K_DEG = 3.14159265358979323846 / 180.0
+
+
+def mat4_mul_f32(a, b):
+    """vh::mat4_mul: float operands, products summed in double in k order, one rounding to float"""
+    a = np.asarray(a, f32).astype(np.float64); b = np.asarray(b, f32).astype(np.float64)
+    r = np.zeros((4, 4), f32)
+    for i in range(4):
+        for j in range(4):
+            acc = 0.0
+            for k in range(4):
+                acc += float(a[i, k]) * float(b[k, j])
+            r[i, j] = f32(acc)
+    return r
+
+
+def rotation_f32(axis, deg):
+    """vh::rotation_x/y/z: float degrees, double trigonometry, float entries (row-major here)"""
+    ang = float(f32(deg)) * K_DEG
+    c, s_ = math.cos(ang), math.sin(ang)
+    m = np.eye(4, dtype=f32)
+    i, j = {"x": (1, 2), "y": (2, 0), "z": (0, 1)}[axis]
+    m[i, i] = f32(c); m[j, j] = f32(c); m[i, j] = f32(-s_); m[j, i] = f32(s_)
+    return m
+
+
 def euler_matrix(prm):
     """TransformDesc 'Euler' (node_desc.cpp:43-48): translation * pitch(x) * roll(z) * yaw(y), degrees"""
-    def rot(axis, deg):
-        a = math.radians(deg); c, s_ = math.cos(a), math.sin(a)
-        m = np.eye(4)
-        i, j = {"x": (1, 2), "y": (2, 0), "z": (0, 1)}[axis]
-        m[i, i] = c; m[j, j] = c; m[i, j] = -s_; m[j, i] = s_
-        return m
-    t = np.eye(4); t[:3, 3] = prm.get("position", [0, 0, 0])
-    return t @ rot("x", prm.get("pitch", 0.0)) @ rot("z", prm.get("roll", 0.0)) @ rot("y", prm.get("yaw", 0.0))
+    t = np.eye(4, dtype=f32); t[:3, 3] = np.asarray(prm.get("position", [0, 0, 0]), f32)
+    m = mat4_mul_f32(t, rotation_f32("x", prm.get("pitch", 0.0)))
+    m = mat4_mul_f32(m, rotation_f32("z", prm.get("roll", 0.0)))
+    return mat4_mul_f32(m, rotation_f32("y", prm.get("yaw", 0.0)))
 
 
 def transform_matrix(tr):
@@ -250,8 +274,52 @@ def transform_matrix(tr):
     if t == "look_at":
         return look_at(prm["position"], prm["target_pos"], prm.get("up", [0, 1, 0]))
     if t == "Euler":
-        return euler_matrix(prm)
+        return euler_matrix(prm).astype(np.float64)
     raise NotImplementedError(t)
+
+
+def invert4(m):
+    """Gauss-Jordan with partial pivoting in double (vh invert4); m row-major"""
+    a = [[float(m[r][c]) for c in range(4)] + [1.0 if r == c else 0.0 for c in range(4)] for r in range(4)]
+    for i in range(4):
+        p = i
+        for r in range(i + 1, 4):
+            if abs(a[r][i]) > abs(a[p][i]):
+                p = r
+        if a[p][i] == 0.0:
+            raise ValueError("singular matrix")
+        if p != i:
+            a[i], a[p] = a[p], a[i]
+        d = a[i][i]
+        a[i] = [x / d for x in a[i]]
+        for r in range(4):
+            if r != i:
+                f = a[r][i]
+                if f != 0.0:
+                    a[r] = [x - f * y for x, y in zip(a[r], a[i])]
+    return np.array([row[4:] for row in a], np.float64)
+
+
+def env_o2w(prm):
+    """SphericalMap ctor (spherical.cpp:36-45): desc.o2w * rotation_x(-90) * scale(1, flip_u ? 1 : -1, 1); the two
+    products in double from the float o2w, one rounding to float; w2o = inverse of the rounded matrix"""
+    A = transform_matrix(prm.get("o2w")).astype(f32).astype(np.float64)
+    ang = -90.0 * 3.14159265358979323846 / 180.0
+    c, s_ = math.cos(ang), math.sin(ang)
+    RX = np.array([[1, 0, 0, 0], [0, c, -s_, 0], [0, s_, c, 0], [0, 0, 0, 1]], np.float64)
+    SC = np.diag([1.0, 1.0 if prm.get("flip_u", False) else -1.0, 1.0, 1.0])
+    def mul(x, y):
+        o = np.zeros((4, 4))
+        for i in range(4):
+            for j in range(4):
+                v = 0.0
+                for k in range(4):
+                    v += float(x[i, k]) * float(y[k, j])
+                o[i, j] = v
+        return o
+    o2w = mul(mul(A, RX), SC).astype(f32)
+    w2o = invert4(o2w.astype(np.float64)).astype(f32)
+    return o2w, w2o
 
 
 def alias2d_build(weights, rx, ry):
@@ -371,9 +439,9 @@ def _cfun(name, x):
     return f32(getattr(_libm, name)(float(f32(x))))
 
 
-def _light_common(l, prm, textures, base):
+def _light_common(l, prm, textures, base, default_color=(1, 1, 1)):
     """Light ctor + initialize_slots (light.cpp:10-24): colour slot, scale, colour normalised into the scale"""
-    slot = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
+    slot = _color_slot(prm.get("color", list(default_color)), textures, base)
     scale = f32(_number(prm.get("scale", 1.0), 1.0))
     if slot.tex_id == VB_INVALID_ID:
         col = [f32(c) for c in slot.value[:3]]
@@ -419,10 +487,9 @@ def _free_light_record(ld, sc, base, world_diameter):
             l.params[1] = float(_cfun("cosf", max(f32(0.0), f32(angle - falloff))))
     elif t == "spherical":
         l.type = capi.VB_LIGHT_ENV
-        o2w = transform_matrix(prm.get("o2w")) @ euler_matrix({"pitch": -90.0}) @ np.diag([1.0, 1.0 if prm.get("flip_u", False) else -1.0, 1.0, 1.0])
-        o2w = o2w.astype(f32).astype(np.float64)
+        o2w, w2o = env_o2w(prm)
         l.o2w[:] = [float(x) for x in o2w.T.reshape(-1)]
-        l.w2o[:] = [float(f32(x)) for x in np.linalg.inv(o2w).T.reshape(-1)]
+        l.w2o[:] = [float(x) for x in w2o.T.reshape(-1)]
         if l.color.tex_id != VB_INVALID_ID:
             tex = sc.textures[l.color.tex_id]
             ry, rx = tex.shape[:2]
@@ -489,22 +556,17 @@ def build_scene(path, overrides=None) -> SceneRecords:
     d = load_json_with_comments(path)
     base = Path(path).parent
     sc = SceneRecords()
-    # materials (Scene::load_materials)
-    mat_index = {}
+    # materials (Scene::load_materials): records are made further down, for the materials in use only
+    mat_descs, mat_index = [], {}
     for m in d.get("materials", []):
-        rec = _material_record(m, sc.textures, base)
-        if rec is None:
-            mat_index[m["name"]] = None          # present but unsupported (principled_bsdf, mix, ...)
-            continue
-        mat_index.setdefault(m["name"], len(sc.materials))
-        sc.materials.append(rec)
-    if any(r.type in (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL) for r in sc.materials) and ov.get("luts", True):
-        sc.luts = capi.load_luts()
+        mat_index.setdefault(m["name"], len(mat_descs))
+        mat_descs.append(m)
     sc.mediums, med_index, process_mediums, global_medium = _medium_records(d)
     if "process_mediums" in ov:
         process_mediums = ov["process_mediums"]
     gm = med_index.get(global_medium, VB_INVALID_ID)
     # shapes -> meshes, instances, area lights (Scene::load_shapes / add_shape)
+    area_lights = []                                                # (emission block, instance index)
     for sh in d["shapes"]:
         prm = sh["param"]
         if sh["type"] == "quad":
@@ -516,8 +578,6 @@ def build_scene(path, overrides=None) -> SceneRecords:
         else:
             raise NotImplementedError(sh["type"])
         mat_name = ov.get("shape_material", {}).get(sh["name"], prm.get("material"))
-        if mat_name in mat_index and mat_index[mat_name] is None:
-            raise NotImplementedError(f"material {mat_name} of {sh['name']}")
         mid = mat_index.get(mat_name, VB_INVALID_ID)                # unknown / empty name: no material (medium boundary)
         o2w = transform_matrix(prm.get("transform")).astype(f32).T.reshape(-1)       # column-major
         inst = {"mesh_id": len(sc.meshes), "material_id": mid, "light_id": VB_INVALID_ID, "o2w": o2w}
@@ -527,54 +587,48 @@ def build_scene(path, overrides=None) -> SceneRecords:
         else:
             inst["inside_medium"] = inst["outside_medium"] = gm
         sc.meshes.append(mesh)
-        em = prm.get("emission")
-        if em:
-            ep = em["param"]
-            l = capi.vb_light_rec()
-            l.type = capi.VB_LIGHT_AREA
-            l.inst_id = len(sc.instances)
-            l.two_sided = 1 if ep.get("two_sided", False) else 0
-            col = ep["color"]["node"] if isinstance(ep["color"], dict) else ep["color"]
-            col = [float(f32(c)) for c in col]
-            scale = ep.get("scale", 1.0)
-            if isinstance(scale, dict):
-                scale = scale["node"]["param"]["value"] if isinstance(scale["node"], dict) else scale["node"]
-            scale = f32(scale)
-            mx = max(col)                                   # Light::initialize_slots -> color_->normalize()
-            if mx >= 1.0:
-                col = [float(f32(f32(c) / f32(mx))) for c in col]
-                scale = f32(scale * f32(mx))
-            l.color = make_slot(col)
-            l.scale = float(scale)
-            table, func, integral = alias_build(triangle_areas(mesh))
-            l.alias_offset, l.alias_size, l.alias_integral = len(sc.alias_table), len(table), integral
-            sc.alias_table += table; sc.alias_func += func
-            inst["light_id"] = len(sc.lights)
-            sc.lights.append(l)
+        if prm.get("emission"):
+            area_lights.append((prm["emission"], len(sc.instances)))
         sc.instances.append(inst)
-    # Scene::remove_unused_materials (scene.cpp:79-91): drop materials no instance refers to, re-index the rest
+    # Scene::remove_unused_materials (scene.cpp:79-91): drop materials no instance refers to, re-index the rest;
+    # records (and their textures) are made in the new index order
     used = sorted({i["material_id"] for i in sc.instances if i["material_id"] != VB_INVALID_ID})
     remap = {old: new for new, old in enumerate(used)}
-    sc.materials = [sc.materials[i] for i in used]
+    for old in used:
+        rec = _material_record(mat_descs[old], sc.textures, base)
+        if rec is None:
+            raise NotImplementedError(f"material {mat_descs[old]['name']} ({mat_descs[old]['type']})")
+        sc.materials.append(rec)
     for i in sc.instances:
         if i["material_id"] != VB_INVALID_ID:
             i["material_id"] = remap[i["material_id"]]
-    if not any(r.type in (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL) for r in sc.materials):
-        sc.luts = {}
+    if any(r.type in (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL) for r in sc.materials) and ov.get("luts", True):
+        sc.luts = capi.load_luts()
     # LightSampler ctor (lightsampler.cpp:11-27): listed lights come first, the shapes' emissions follow; tidy_up
-    # (lightsampler.cpp:67-77) then groups them by type in first-seen order
+    # (lightsampler.cpp:67-77) groups them by type in first-seen order; records are made in that order
     free = [] if ov.get("drop_lights", False) else d.get("light_sampler", {}).get("param", {}).get("lights", [])
-    if free:
-        wd = world_diameter(sc, d.get("render_setting", {}).get("min_world_radius", 10.0))
-        lights = [_free_light_record(ld, sc, base, wd) for ld in free] + sc.lights
-        first = {}
-        for l in lights:
-            first.setdefault(l.type, len(first))
-        order = sorted(range(len(lights)), key=lambda i: first[lights[i].type])
-        sc.lights = [lights[i] for i in order]
-        for new, l in enumerate(sc.lights):
-            if l.type == capi.VB_LIGHT_AREA:
-                sc.instances[l.inst_id]["light_id"] = new
+    type_of = {"point": capi.VB_LIGHT_POINT, "spot": capi.VB_LIGHT_SPOT, "spherical": capi.VB_LIGHT_ENV}
+    pending = [(type_of.get(ld["type"], -1), ld, None) for ld in free] + [(capi.VB_LIGHT_AREA, em, ii) for em, ii in area_lights]
+    first = {}
+    for t, _, _ in pending:
+        first.setdefault(t, len(first))
+    pending.sort(key=lambda x: first[x[0]])                          # stable
+    wd = world_diameter(sc, d.get("render_setting", {}).get("min_world_radius", 10.0)) if free else 0.0
+    for t, ld, ii in pending:
+        if t != capi.VB_LIGHT_AREA:
+            sc.lights.append(_free_light_record(ld, sc, base, wd))
+            continue
+        ep = ld["param"]
+        l = capi.vb_light_rec()
+        l.type = capi.VB_LIGHT_AREA
+        l.inst_id = ii
+        l.two_sided = 1 if ep.get("two_sided", False) else 0
+        _light_common(l, ep, sc.textures, base, default_color=[0.5, 0.5, 0.5])
+        table, func, integral = alias_build(triangle_areas(sc.meshes[sc.instances[ii]["mesh_id"]]))
+        l.alias_offset, l.alias_size, l.alias_integral = len(sc.alias_table), len(table), integral
+        sc.alias_table += table; sc.alias_func += func
+        sc.instances[ii]["light_id"] = len(sc.lights)
+        sc.lights.append(l)
     # camera
     cam = d["camera"]["param"]
     res = ov.get("resolution") or d.get("pipeline", {}).get("param", {}).get("frame_buffer", {}).get("param", {}).get("resolution", [1280, 720])
