@@ -44,6 +44,7 @@ def parse():
     p.add_argument("--no-pt", action="store_true")
     p.add_argument("--classroom-spp", type=int, default=16)
     p.add_argument("--no-classroom", action="store_true")
+    p.add_argument("--opt", action="append", default=[], help="library option key=value (vb_ctx_set_option), e.g. build.ploc=0")
     return p.parse_args()
 
 
@@ -147,6 +148,8 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
         sc = scene_py.build_scene(ROOT / "scenes" / "classroom" / "vision_scene.json", {})
         spp_rank, label = a.classroom_spp, "classroom (sky stand-in env map)"
     ctx = Context(local_rank)
+    for kv in a.opt:
+        ctx.set_option(kv.split("=")[0], float(kv.split("=")[1]))
     ctx.set_stream(stream.cuda_stream)
     ctx.upload_scene(sc)
     w, h = sc.resolution
@@ -225,6 +228,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     ctx = Context(local_rank)
+    for kv in a.opt:
+        ctx.set_option(kv.split("=")[0], float(kv.split("=")[1]))
     stream = torch.cuda.Stream(device=local_rank)      # a real (non-default) stream shared with the library
     torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)

@@ -13,10 +13,17 @@ reps = int(sys.argv[5]) if len(sys.argv) > 5 else 1
 ov = {"resolution": [w, h], "spp": spp}
 if len(sys.argv) > 6:
     ov["process_mediums"] = bool(int(sys.argv[6]))
-sc = scene_py.build_scene(path, ov)
-ctx = Context(0)
-ctx.upload_scene(sc)
 import os
+if "VB_MAX_DEPTH" in os.environ:
+    ov["max_depth"] = int(os.environ["VB_MAX_DEPTH"])
+sc = scene_py.build_scene(path, ov)
+import os
+ctx = Context(0)
+if "VB_PLOC" in os.environ:
+    ctx.set_option("build.ploc", int(os.environ["VB_PLOC"]))
+if "VB_SIZE_CLASSES" in os.environ:
+    ctx.set_option("build.size_classes", int(os.environ["VB_SIZE_CLASSES"]))
+ctx.upload_scene(sc)
 ctx.set_option("pt.schedule", int(os.environ.get("VB_SCHED", "0")))
 if "VB_MAX_PATHS" in os.environ:
     ctx.set_option("pt.max_paths", int(os.environ["VB_MAX_PATHS"]))

@@ -35,7 +35,8 @@ struct BuildBufs {
     uint32_t *left, *right, *first, *last;   // T-1
     uint32_t *parent;      // 2T-1
     uint32_t *flags;       // T-1
-    double *moments;       // 6    sum and sum of squares of the normalised triangle centroids (ray-sort box)
+    uint32_t *cls_count;   // 4    triangles per size class (k_morton)
+    double *moments;       // 6    sum and sum of squares of the triangle centroids (ray-sort box, size classes)
 };
 
 // normative world transform: FMA chain identical to oracle vo::transform_point
@@ -54,6 +55,7 @@ __global__ void __launch_bounds__(256) k_flatten(const InstGeom *inst, const uin
                                                  uint32_t T, BuildBufs b) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     float3 lo = make_float3(FLT_MAX, FLT_MAX, FLT_MAX), hi = make_float3(-FLT_MAX, -FLT_MAX, -FLT_MAX);
+    double m[6] = {0, 0, 0, 0, 0, 0};
     if (g < T) {
         uint32_t a = 0, c = n_inst;               // largest a with offsets[a] <= g
         while (c - a > 1) { uint32_t m = (a + c) >> 1; if (offsets[m] <= g) a = m; else c = m; }
@@ -81,6 +83,13 @@ __global__ void __launch_bounds__(256) k_flatten(const InstGeom *inst, const uin
                          fmaxf(p0.z, fmaxf(fmaxf(p1.z, q1.z), fmaxf(p2.z, q2.z))));
         b.blo[g] = make_float4(lo.x, lo.y, lo.z, 0.f);
         b.bhi[g] = make_float4(hi.x, hi.y, hi.z, 0.f);
+        m[0] = 0.5 * ((double)lo.x + (double)hi.x); m[1] = 0.5 * ((double)lo.y + (double)hi.y); m[2] = 0.5 * ((double)lo.z + (double)hi.z);
+        m[3] = m[0] * m[0]; m[4] = m[1] * m[1]; m[5] = m[2] * m[2];
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        for (int o = 16; o > 0; o >>= 1) m[k] += __shfl_xor_sync(~0u, m[k], o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(b.moments + k, m[k]);
     }
     // warp reduce then one atomic per warp per component
     for (int o = 16; o > 0; o >>= 1) {
@@ -105,34 +114,39 @@ __device__ __forceinline__ uint64_t expand21(uint32_t v) {   // spread 21 bits t
     return x;
 }
 
-__global__ void __launch_bounds__(256) k_morton(uint32_t T, BuildBufs b) {
+// Sort key = [2-bit size class][60-bit Morton code of the centroid]. The size class (triangle box diagonal against
+// the spread of the centroids, 5 sigma) goes on top, so the radix tree splits the few large triangles of a scene
+// (walls, floors, ground planes) from the many small ones before it splits space: each class is an LBVH over
+// similar-sized boxes, and a huge box no longer inflates every ancestor of a leaf deep inside the fine geometry
+// (extended Morton codes, Vinkler et al. 2017, reduced to a prefix). Uniform meshes fall into one class.
+__global__ void __launch_bounds__(256) k_morton(uint32_t T, BuildBufs b, int size_classes) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    double m[6] = {0, 0, 0, 0, 0, 0};
-    if (g < T) {
-        float3 slo = make_float3(ord2f(b.scene[0]), ord2f(b.scene[1]), ord2f(b.scene[2]));
-        float3 shi = make_float3(ord2f(b.scene[3]), ord2f(b.scene[4]), ord2f(b.scene[5]));
-        float4 lo = b.blo[g], hi = b.bhi[g];
-        m[0] = (0.5f * (lo.x + hi.x) - slo.x) / fmaxf(shi.x - slo.x, 1e-30f);
-        m[1] = (0.5f * (lo.y + hi.y) - slo.y) / fmaxf(shi.y - slo.y, 1e-30f);
-        m[2] = (0.5f * (lo.z + hi.z) - slo.z) / fmaxf(shi.z - slo.z, 1e-30f);
-        m[3] = m[0] * m[0]; m[4] = m[1] * m[1]; m[5] = m[2] * m[2];
-    }
-#pragma unroll
-    for (int k = 0; k < 6; ++k) {
-        for (int o = 16; o > 0; o >>= 1) m[k] += __shfl_xor_sync(~0u, m[k], o);
-        if ((threadIdx.x & 31) == 0) atomicAdd(b.moments + k, m[k]);
-    }
-    if (g >= T) return;
+    if (g >= T) return;                                   // (the last warp may be partial: __activemask below)
     float3 slo = make_float3(ord2f(b.scene[0]), ord2f(b.scene[1]), ord2f(b.scene[2]));
     float3 shi = make_float3(ord2f(b.scene[3]), ord2f(b.scene[4]), ord2f(b.scene[5]));
     float4 lo = b.blo[g], hi = b.bhi[g];
     float ex = fmaxf(shi.x - slo.x, 1e-30f), ey = fmaxf(shi.y - slo.y, 1e-30f), ez = fmaxf(shi.z - slo.z, 1e-30f);
     float cx = (0.5f * (lo.x + hi.x) - slo.x) / ex, cy = (0.5f * (lo.y + hi.y) - slo.y) / ey,
           cz = (0.5f * (lo.z + hi.z) - slo.z) / ez;
-    const float S = 2097152.f;   // 2^21
+    const float S = 1048576.f;   // 2^20
     uint32_t ix = (uint32_t)fminf(fmaxf(cx * S, 0.f), S - 1.f), iy = (uint32_t)fminf(fmaxf(cy * S, 0.f), S - 1.f),
              iz = (uint32_t)fminf(fmaxf(cz * S, 0.f), S - 1.f);
-    b.keys[g] = (expand21(ix) << 2) | (expand21(iy) << 1) | expand21(iz);
+    uint64_t cls = 0;
+    {
+        double var = 0.0;
+        for (int k = 0; k < 3; ++k) { double mean = b.moments[k] / T; var += fmax(0.0, b.moments[3 + k] / T - mean * mean); }
+        float D = 5.0f * (float)sqrt(var);                       // spread of the geometry (robust against a few far-out triangles)
+        float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+        float diag = sqrtf(dx * dx + dy * dy + dz * dz);
+        cls = diag > 0.5f * D ? 3u : (diag > 0.125f * D ? 2u : (diag > 0.03125f * D ? 1u : 0u));
+        unsigned act = __activemask();
+        for (uint32_t k = 1; k < 4; ++k) {
+            unsigned m = __ballot_sync(act, cls == k);
+            if (m && (threadIdx.x & 31) == (unsigned)(__ffs(m) - 1)) atomicAdd(b.cls_count + k, (uint32_t)__popc(m));
+        }
+        if (!size_classes) cls = 0;
+    }
+    b.keys[g] = (cls << 60) | (expand21(ix) << 2) | (expand21(iy) << 1) | expand21(iz);
     b.vals[g] = g;
 }
 
@@ -201,4 +215,5 @@ __global__ void __launch_bounds__(256) k_refit(uint32_t T, BuildBufs b) {
 
 }  // namespace
 
+#include "vb_bvh_ploc.cuh"
 #include "vb_bvh_collapse.cuh"

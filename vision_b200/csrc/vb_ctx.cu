@@ -113,6 +113,8 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     if (k == "trace.refill_thr") ctx->opt_refill_thr = (int)value;
     else if (k == "trace.tri_thr") ctx->opt_tri_thr = (int)value;
     else if (k == "build.max_leaf") ctx->opt_max_leaf = (int)value;
+    else if (k == "build.ploc") ctx->opt_ploc = value < 0 ? -1 : (value != 0 ? 1 : 0);
+    else if (k == "build.size_classes") ctx->opt_size_classes = value != 0 ? 1 : 0;
     else if (k == "trace.sort_rays") ctx->opt_sort_rays = (int)value;
     else if (k == "trace.sort_min_rays") ctx->opt_sort_min_rays = std::max(1, (int)value);
     else if (k == "pt.schedule") ctx->opt_pt_schedule = value != 0 ? 1 : 0;

@@ -75,6 +75,9 @@ struct vb_ctx {
     // tunables (vb_ctx_set_option)
     int opt_refill_thr = 28, opt_tri_thr = 12, opt_blocks_per_sm = 8;
     int opt_max_leaf = 1;
+    int opt_ploc = -1;                       // build: 1 = PLOC clustering (vb_bvh_ploc.cuh), 0 = radix tree, -1 = automatic
+    bool last_build_ploc = false;
+    int opt_size_classes = 1;                // build: triangle size class as the top bits of the Morton sort key
     int opt_sort_rays = 1, opt_sort_min_rays = 1 << 16;
     int opt_pt_schedule = 0;                 // 0 = wavefront (default), 1 = megakernel
     int opt_pt_sort_material = 1;            // wavefront: order shading entries by material
