@@ -95,7 +95,11 @@ VB_API int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n,
 
 /* ---- sensor + filter (reference src/base/sensor/sensor.cpp:44-78,153-162, thin_lens.cpp:34-42,
  *      filter/box.cpp:16-20, filter/triangle.cpp:16-18) ------------------------------------------- */
-enum { VB_FILTER_BOX = 0, VB_FILTER_TRIANGLE = 1 };
+/* VB_FILTER_FITTED = FittedCurveFilter (filter/fitted_curve.h:16-107: gaussian, mitchell, sinc): pixel offsets are drawn
+ * from a 20x20 AliasTable2D over |f| on the positive quadrant; its tables live in the alias arrays given to
+ * vb_lights_set: 20 marginal entries at filter_table_offset, then 400 conditional entries (row-major) */
+enum { VB_FILTER_BOX = 0, VB_FILTER_TRIANGLE = 1, VB_FILTER_FITTED = 2 };
+#define VB_FILTER_TABLE_SIZE 20
 typedef struct vb_camera {
     float c2w[16];             /* camera_to_world(), column-major */
     float tan_fov_y_over_2;
@@ -104,7 +108,7 @@ typedef struct vb_camera {
     float screen_lo[2], screen_hi[2];   /* FrameBuffer::screen_window (frame_buffer.cpp:93-102) */
     uint32_t filter_type;
     float filter_radius[2];
-    uint32_t pad;
+    uint32_t filter_table_offset;   /* VB_FILTER_FITTED only */
 } vb_camera;
 VB_API int vb_camera_set(vb_ctx *ctx, const vb_camera *cam);
 

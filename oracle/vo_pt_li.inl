@@ -311,6 +311,16 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
             return u < 0.5f ? -r * sample_linear10((0.5f - u) * 2.f) : r * sample_linear10((u - 0.5f) * 2.f);
         };
         fp = {tent(uf.x, camera.filter_radius[0]), tent(uf.y, camera.filter_radius[1])};
+    } else if (camera.filter_type == VB_FILTER_FITTED) {   // FilterSampler::sample, fitted_curve.h:83-91 (the weight is not used on this path)
+        float2 u{uf.x * 2.f - 1.f, uf.y * 2.f - 1.f};
+        const uint32_t N = VB_FILTER_TABLE_SIZE, off = camera.filter_table_offset;
+        float ur;
+        uint32_t iv = alias_offset_remap(*this, off, N, std::fabs(u.y), ur);
+        float fv = ((float)iv + ur) / (float)N;
+        uint32_t iu = alias_offset_remap(*this, off + N + N * iv, N, std::fabs(u.x), ur);
+        float fu = ((float)iu + ur) / (float)N;
+        auto sign = [](float x) { return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f); };
+        fp = {fu * sign(u.x) * camera.filter_radius[0], fv * sign(u.y) * camera.filter_radius[1]};
     } else {
         float rx = camera.filter_radius[0], ry = camera.filter_radius[1];
         fp = {-rx + uf.x * (rx - (-rx)), -ry + uf.y * (ry - (-ry))};

@@ -84,7 +84,7 @@ def test_host_records_equal_python_twin_materials_and_mediums(name):
         assert want in names, want
 
 
-@pytest.mark.parametrize("rel", ["scenes/cbox/cbox_lights.json", "scenes/classroom/vision_scene.json"])
+@pytest.mark.parametrize("rel", ["scenes/cbox/cbox_lights.json", "scenes/classroom/vision_scene.json", "scenes/cbox/cbox_sphere.json"])
 def test_host_records_equal_python_twin_lights_and_models(rel):
     """model shape (OBJ), point / spot / spherical lights, AliasTable2D, world diameter, Euler transforms, light order"""
     path = ROOT / rel
@@ -104,6 +104,7 @@ def test_host_records_equal_python_twin_lights_and_models(rel):
     assert [_bytes(x) for x in a.lights] == [_bytes(x) for x in b.lights]
     assert a.alias_table == [(float(np.float32(p)), i) for p, i in b.alias_table] and a.alias_func == b.alias_func
     assert _bytes(a.params) == _bytes(b.params) and a.camera.medium_id == b.camera.medium_id
+    assert a.camera.filter_type == b.camera.filter_type and a.camera.filter_table_offset == b.camera.filter_table_offset
     assert len(a.textures) == len(b.textures)
     for x, y in zip(a.textures, b.textures):
         assert x.shape == y.shape
@@ -113,13 +114,40 @@ def test_host_records_equal_python_twin_lights_and_models(rel):
         env = a.lights[0]
         assert env.type == capi.VB_LIGHT_ENV and list(env.env_res) == [512, 256] and env.alias_size == 256 and env.cond_offset == 256
         assert env.params[0] > 300.0            # the scaled ground plane sets the world diameter
+    elif "sphere" in rel:
+        assert a.camera.filter_type == capi.VB_FILTER_FITTED and a.camera.filter_table_offset == 2      # after the area light's 2 entries
+        sph = a.meshes[a.instances[5]["mesh_id"]]
+        assert len(sph["tri"]) == 48 * 2 + 22 * 48 * 2 and len(sph["pos"]) == 2 + 23 * 48               # sphere.cpp:55, sub_div 24
     else:
         assert [l.type for l in a.lights] == [capi.VB_LIGHT_POINT, capi.VB_LIGHT_SPOT, capi.VB_LIGHT_ENV, capi.VB_LIGHT_AREA]
         assert a.instances[-1]["light_id"] == 3
     names = host_api.plugin_names()
     for want in ("vision-shape-model#constructor", "vision-light-point#constructor", "vision-light-spot#constructor",
-                 "vision-light-spherical#constructor"):
+                 "vision-light-spherical#constructor", "vision-shape-sphere#constructor", "vision-filter-gaussian#constructor",
+                 "vision-filter-mitchell#constructor", "vision-filter-sinc#constructor"):
         assert want in names, want
+
+
+@pytest.mark.parametrize("flt", [{"type": "mitchell", "param": {"radius": 2.0}}, {"type": "sinc", "param": {"radius": 3.0, "tau": 3.0}},
+                                 {"type": "gaussian", "param": {"radius": 1.0, "sigma": 0.3}}, {"type": "mitchell", "param": {"radius": 1.5, "b": 0.5, "c": 0.25}}])
+def test_fitted_filter_tables_equal_python_twin(tmp_path, flt):
+    """FittedCurveFilter plugins (gaussian / mitchell / sinc): the 20x20 AliasTable2D the host builds == the twin's"""
+    import json
+    d = scene_py.load_json_with_comments(SCENE)
+    d["camera"]["param"]["filter"] = flt
+    p = tmp_path / "f.json"
+    p.write_text(json.dumps(d))
+    import shutil
+    shutil.copy(ROOT / "scenes" / "cbox" / "checker.jpg", tmp_path / "checker.jpg")
+    shutil.copy(ROOT / "scenes" / "cbox" / "checker.jpg.ppm", tmp_path / "checker.jpg.ppm")
+    hp = host_api.HostPipeline(p)
+    hp.prepare_records()
+    a, b = hp.records(), scene_py.build_scene(p)
+    assert a.camera.filter_type == b.camera.filter_type == capi.VB_FILTER_FITTED
+    assert a.camera.filter_table_offset == b.camera.filter_table_offset and list(a.camera.filter_radius) == list(b.camera.filter_radius)
+    assert len(a.alias_table) == a.camera.filter_table_offset + 420
+    assert a.alias_table == [(float(np.float32(pr)), i) for pr, i in b.alias_table] and a.alias_func == b.alias_func
+    assert any(x > 0 for x in a.alias_func[-400:])
 
 
 def test_desc_defaults_and_errors(tmp_path):
@@ -140,7 +168,7 @@ def test_desc_defaults_and_errors(tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("SCENE", [SCENE, ROOT / "scenes" / "cbox" / "cbox_materials.json", ROOT / "scenes" / "cbox" / "cbox_fog.json",
-                                   ROOT / "scenes" / "cbox" / "cbox_lights.json"])
+                                   ROOT / "scenes" / "cbox" / "cbox_lights.json", ROOT / "scenes" / "cbox" / "cbox_sphere.json"])
 def test_host_pipeline_renders_like_python_path(vbctx, SCENE):
     hp = host_api.HostPipeline(SCENE)
     hp.prepare(0)

@@ -68,4 +68,15 @@ with open(root / "env_small.pfm", "wb") as f:
     f.write(b"PF\n%d %d\n-1.0\n" % (w, h))
     f.write(img[::-1].astype("<f4").tobytes())
 (root / "cbox_lights.json").write_text(json.dumps(c, indent=1))
-print("wrote", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json")
+
+# cbox_sphere.json: the short box becomes a glass sphere (sphere.cpp tessellation, sub_div 24), gaussian pixel filter
+e = copy.deepcopy(base)
+e["materials"] += extra[:1]
+for i, s_ in enumerate(e["shapes"]):
+    if s_["name"] == "shape_5":
+        e["shapes"][i] = {"type": "sphere", "name": "shape_5", "param": {"radius": 0.3, "sub_div": 24, "material": "Glass2",
+                          "transform": {"type": "matrix4x4", "param": {"matrix4x4": [[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, 0], [0.33, 0.3, 0.35, 1]]}}}}
+e["camera"]["param"]["filter"] = {"type": "gaussian", "name": "gaussianFilter", "param": {"radius": 1.5, "sigma": 0.5}}
+e["integrator"]["param"]["max_depth"] = 8
+(root / "cbox_sphere.json").write_text(json.dumps(e, indent=1))
+print("wrote", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json", root / "cbox_sphere.json")

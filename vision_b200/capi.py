@@ -315,7 +315,7 @@ class vb_camera(C.Structure):
     _fields_ = [("c2w", C.c_float * 16), ("tan_fov_y_over_2", C.c_float), ("lens_radius", C.c_float),
                 ("focal_distance", C.c_float), ("medium_id", C.c_uint32), ("screen_lo", C.c_float * 2),
                 ("screen_hi", C.c_float * 2), ("filter_type", C.c_uint32), ("filter_radius", C.c_float * 2),
-                ("pad", C.c_uint32)]
+                ("filter_table_offset", C.c_uint32)]
 
 
 class vb_pt_params(C.Structure):
@@ -326,7 +326,8 @@ class vb_pt_params(C.Structure):
 
 VB_MAT_DIFFUSE, VB_MAT_MIRROR, VB_MAT_GLASS, VB_MAT_METAL, VB_MAT_SUBSTRATE, VB_MAT_PRINCIPLED, VB_MAT_BLACK_BODY = range(7)
 VB_LIGHT_AREA, VB_LIGHT_POINT, VB_LIGHT_SPOT, VB_LIGHT_ENV = range(4)
-VB_FILTER_BOX, VB_FILTER_TRIANGLE = 0, 1
+VB_FILTER_BOX, VB_FILTER_TRIANGLE, VB_FILTER_FITTED = 0, 1, 2
+VB_FILTER_TABLE_SIZE = 20
 VB_ACCUM_LERP, VB_ACCUM_SUM = 0, 1
 VB_FILM_RT, VB_FILM_ACCUM, VB_FILM_OUTPUT = 0, 1, 2
 VB_TONEMAP_LINEAR, VB_TONEMAP_ACES, VB_TONEMAP_REINHARD = 0, 1, 2

@@ -366,7 +366,17 @@ __device__ VbRay generate_camera_ray(const PtScene &S, Sampler &sampler, uint32_
     f2 uf = sampler.next_2d();
     f2 fp;
     if (cam.filter_type == VB_FILTER_TRIANGLE) fp = {sample_tent(uf.x, cam.filter_radius[0]), sample_tent(uf.y, cam.filter_radius[1])};
-    else {
+    else if (cam.filter_type == VB_FILTER_FITTED) {        // FilterSampler::sample, fitted_curve.h:83-91
+        f2 u{uf.x * 2.f - 1.f, uf.y * 2.f - 1.f};
+        const uint32_t N = VB_FILTER_TABLE_SIZE, off = cam.filter_table_offset;
+        float ur;
+        uint32_t iv = alias_offset_remap(S, off, N, fabsf(u.y), ur);
+        float fv = ((float)iv + ur) / (float)N;
+        uint32_t iu = alias_offset_remap(S, off + N + N * iv, N, fabsf(u.x), ur);
+        float fu = ((float)iu + ur) / (float)N;
+        float sx_ = u.x > 0.f ? 1.f : (u.x < 0.f ? -1.f : 0.f), sy_ = u.y > 0.f ? 1.f : (u.y < 0.f ? -1.f : 0.f);
+        fp = {fu * sx_ * cam.filter_radius[0], fv * sy_ * cam.filter_radius[1]};
+    } else {
         float rx = cam.filter_radius[0], ry = cam.filter_radius[1];
         fp = {-rx + uf.x * (rx - (-rx)), -ry + uf.y * (ry - (-ry))};
     }

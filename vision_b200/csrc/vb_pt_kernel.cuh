@@ -126,6 +126,7 @@ struct vb_pt_state {
     vb_wf_buffers *wf = nullptr;       // queues of the wavefront schedule (allocated on first use)
     uint32_t n_mat_types = 0;          // distinct material models in use (one: ordering the shading queue is pointless)
     uint64_t work[4] = {0, 0, 0, 0};
+    uint32_t n_alias = 0;
     std::vector<DevMesh> h_meshes;
     DevMesh *d_meshes = nullptr;
     DevInst *d_inst = nullptr;
@@ -296,7 +297,7 @@ int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n, const vb_
         }
     }
     cudaFree(p->d_lights); cudaFree(p->d_alias); cudaFree(p->d_func);
-    p->d_lights = nullptr; p->d_alias = nullptr; p->d_func = nullptr; p->n_lights = n;
+    p->d_lights = nullptr; p->d_alias = nullptr; p->d_func = nullptr; p->n_lights = n; p->n_alias = n_alias;
     p->env_light = VB_INVALID_ID;
     for (uint32_t i = 0; i < n; ++i) if (lights[i].type == VB_LIGHT_ENV) p->env_light = i;
     if (n) {
@@ -375,6 +376,10 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
         for (auto &in : ctx->instances)
             if (bad(in.inside_medium) || bad(in.outside_medium)) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": instance medium id out of range");
     }
+    if (p->cam.filter_type == VB_FILTER_FITTED &&
+        (uint64_t)p->cam.filter_table_offset + VB_FILTER_TABLE_SIZE * (VB_FILTER_TABLE_SIZE + 1) > p->n_alias)
+        return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": filter table out of bounds of the alias arrays");
+    if (p->cam.filter_type > VB_FILTER_FITTED) return ctx->fail(VB_ERR_UNSUPPORTED, std::string(fn) + ": unknown filter type");
     S.cam = p->cam; S.params = p->params; S.width = p->w; S.height = p->h;
     if (S.params.ray_offset_factor == 0.f) S.params.ray_offset_factor = 1.f;
     uint32_t n_pix = p->w * p->h;

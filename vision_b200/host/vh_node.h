@@ -9,6 +9,7 @@
 // `extern "C" <plugin_name_with_underscores>__<construct_name>()` returning its INodeConstructor.
 #pragma once
 #include "vh_desc.h"
+#include <cmath>
 #include "../../include/vision_b200.h"
 #include <functional>
 #include <memory>
@@ -145,7 +146,25 @@ public:
 };
 
 class Sampler : public Node { public: using Desc = SamplerDesc; uint32_t spp; explicit Sampler(const SamplerDesc &d) : spp(d["spp"].as_uint(1u)) {} virtual uint32_t device_tag() const = 0; };
-class Filter : public Node { public: using Desc = FilterDesc; float radius[2]; explicit Filter(const FilterDesc &d) { radius[0] = radius[1] = d["radius"].as_float(0.5f); } virtual uint32_t device_tag() const = 0; };
+class Filter : public Node {
+public:
+    using Desc = FilterDesc;
+    float radius[2];
+    explicit Filter(const FilterDesc &d) { radius[0] = radius[1] = d["radius"].as_float(0.5f); }
+    virtual uint32_t device_tag() const = 0;
+    virtual float evaluate(float, float) const { return 0.f; }      // FittedCurveFilter subclasses (filter.h:60)
+    // FilterSampler::build (fitted_curve.h:36-58): |f| at the 20x20 cell centres of the positive quadrant
+    std::vector<float> table_weights() const {
+        const int N = VB_FILTER_TABLE_SIZE;
+        std::vector<float> w((size_t)N * N);
+        for (int i = 0; i < N * N; ++i) {
+            int x = i % N, y = i / N;
+            float px = ((float)x + 0.5f) / (float)N * radius[0], py = ((float)y + 0.5f) / (float)N * radius[1];
+            w[i] = std::fabs(evaluate(px, py));
+        }
+        return w;
+    }
+};
 class Spectrum : public Node { public: using Desc = SpectrumDesc; explicit Spectrum(const SpectrumDesc &) {} virtual uint32_t device_tag() const = 0; };
 class ToneMapper : public Node { public: using Desc = ToneMapperDesc; explicit ToneMapper(const ToneMapperDesc &) {} virtual int device_tag() const = 0; };
 class Warper : public Node {

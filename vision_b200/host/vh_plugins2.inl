@@ -26,6 +26,52 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(TriangleFilter, filter, triangle, constructor)
 
+// reference src/render_core/filter/gaussian.cpp:24-53 + math/util.h:37-42
+class GaussianFilter : public Filter {
+    float sigma_, exp_;
+    float gaussian(float x) const {
+        float a = 1.0f / std::sqrt((2.0f * 3.14159265358979323846f) * (sigma_ * sigma_));
+        return a * std::exp(-(x * x) / (2.0f * (sigma_ * sigma_)));
+    }
+public:
+    explicit GaussianFilter(const FilterDesc &d) : Filter(d), sigma_(d["sigma"].as_float(1.f)) { exp_ = gaussian(radius[0]); }
+    std::string impl_type() const override { return "gaussian"; }
+    uint32_t device_tag() const override { return VB_FILTER_FITTED; }
+    float evaluate(float x, float y) const override { return std::max(0.f, gaussian(x) - exp_) * std::max(0.f, gaussian(y) - exp_); }
+};
+VH_MAKE_CLASS_CREATOR(GaussianFilter, filter, gaussian, constructor)
+
+// reference src/render_core/filter/mitchell.cpp:19-52
+class MitchellFilter : public Filter {
+    float b_, c_;
+    float mitchell_1d(float x) const {
+        x = std::fabs(x);
+        float x2 = x * x, x3 = x2 * x, s6 = 1.0f / 6.0f;
+        if (x <= 1) return ((((12.f - 9.f * b_) - 6.f * c_) * x3 + ((-18.f + 12.f * b_) + 6.f * c_) * x2) + (6.f - 2.f * b_)) * s6;
+        if (x <= 2) return (((((-b_ - 6.f * c_) * x3 + (6.f * b_ + 30.f * c_) * x2)) + (-12.f * b_ - 48.f * c_) * x) + (8.f * b_ + 24.f * c_)) * s6;
+        return 0.f;
+    }
+public:
+    explicit MitchellFilter(const FilterDesc &d) : Filter(d), b_(d["b"].as_float(1.f / 3.f)), c_(d["c"].as_float(1.f / 3.f)) {}
+    std::string impl_type() const override { return "mitchell"; }
+    uint32_t device_tag() const override { return VB_FILTER_FITTED; }
+    float evaluate(float x, float y) const override { return mitchell_1d(2.f * x / radius[0]) * mitchell_1d(2.f * y / radius[1]); }
+};
+VH_MAKE_CLASS_CREATOR(MitchellFilter, filter, mitchell, constructor)
+
+// reference src/render_core/filter/sinc.cpp:17-30 + math/util.h:51-66
+class LanczosSincFilter : public Filter {
+    float tau_;
+    static float sinc(float x) { x = 3.14159265358979323846f * x; return 1.0f + x * x == 1.0f ? 1.0f : std::sin(x) / x; }
+    float windowed(float x, float r) const { return std::fabs(x) > r ? 0.f : sinc(x) * sinc(x / tau_); }
+public:
+    explicit LanczosSincFilter(const FilterDesc &d) : Filter(d), tau_(d["tau"].as_float(3.f)) {}
+    std::string impl_type() const override { return "sinc"; }
+    uint32_t device_tag() const override { return VB_FILTER_FITTED; }
+    float evaluate(float x, float y) const override { return (windowed(x, radius[0]) * windowed(y, radius[1])) * 4.0f; }
+};
+VH_MAKE_CLASS_CREATOR(LanczosSincFilter, filter, sinc, constructor)
+
 // reference src/render_core/spectrum/srgb.cpp:16-57
 class SRGBSpectrum : public Spectrum {
 public:

@@ -117,6 +117,51 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(Model, shape, model, constructor)
 
+// reference src/render_core/shape/sphere.cpp:20-88: theta_div = sub_div rings, phi_div = 2 * sub_div segments
+class Sphere : public ShapeGroup {
+public:
+    explicit Sphere(const ShapeDesc &desc) : ShapeGroup(desc) {
+        name_ = desc.name;
+        const float Pi = 3.14159265358979323846f, TwoPi = 6.283185307179586f;
+        float radius = desc["radius"].as_float(1.f);
+        uint32_t theta_div = desc["sub_div"].as_uint(60u), phi_div = 2 * theta_div;
+        MeshData m;
+        auto push = [&](float x, float y, float z, float nx, float ny, float nz, float u, float v) {
+            m.pos.insert(m.pos.end(), {x, y, z}); m.nrm.insert(m.nrm.end(), {nx, ny, nz}); m.uv.insert(m.uv.end(), {u, v});
+        };
+        auto push_unit = [&](float x, float y, float z, float u, float v) {
+            float l = std::sqrt((x * x + y * y) + z * z);
+            push(x, y, z, x / l, y / l, z / l, u, v);
+        };
+        push(0, radius, 0, 0, 1, 0, 0, 0);
+        for (uint32_t i = 1; i < theta_div; ++i) {
+            float v = (float)i / (float)theta_div, theta = Pi * v;
+            float y = radius * std::cos(theta), r = radius * std::sin(theta);
+            push_unit(r, y, 0.f, 0.f, v);
+            for (uint32_t j = 1; j < phi_div; ++j) {
+                float u = (float)j / (float)phi_div, phi = u * TwoPi;
+                push_unit(std::cos(phi) * r, y, std::sin(phi) * r, u, v);
+            }
+        }
+        push(0, -radius, 0, 0, -1, 0, 0, 1);
+        for (uint32_t i = 0; i < phi_div; ++i) m.tri.insert(m.tri.end(), {0u, (i + 1) % phi_div + 1, i + 1});
+        for (uint32_t i = 0; i + 2 < theta_div; ++i) {
+            uint32_t vs = 1 + i * phi_div;
+            for (uint32_t j = 0; j < phi_div; ++j) {
+                if (j != phi_div - 1) { m.tri.insert(m.tri.end(), {vs, vs + 1, vs + phi_div}); m.tri.insert(m.tri.end(), {vs + 1, vs + phi_div + 1, vs + phi_div}); }
+                else { m.tri.insert(m.tri.end(), {vs, vs + 1 - phi_div, vs + phi_div}); m.tri.insert(m.tri.end(), {vs + 1 - phi_div, vs + 1, vs + phi_div}); }
+                vs++;
+            }
+        }
+        uint32_t ve = m.nv() - 1;
+        for (uint32_t i = 0; i < phi_div; ++i) m.tri.insert(m.tri.end(), {ve, ve - ((1 + i) % phi_div + 1), ve - (i + 1)});
+        add_instance(std::move(m));
+        post_init(desc);
+    }
+    std::string impl_type() const override { return "sphere"; }
+};
+VH_MAKE_CLASS_CREATOR(Sphere, shape, sphere, constructor)
+
 // ---- lights ------------------------------------------------------------------------------------
 // Light ctor + initialize_slots (light.cpp:10-24): colour slot, scale, constant colours normalised into the scale
 static void light_common(vb_light_rec &r, const LightDesc &d, float3 def, const SlotContext &ctx) {

@@ -209,6 +209,24 @@ void Scene::prepare(SceneRecords &out) {
     }
     out.width = frame_buffer->width; out.height = frame_buffer->height;
     sensor->fill_record(out.camera, out.width, out.height);
+    if (out.camera.filter_type == VB_FILTER_FITTED) {       // FilterSampler: AliasTable2D over the 20x20 table, after the lights' tables
+        const uint32_t N = VB_FILTER_TABLE_SIZE;
+        std::vector<float> w = sensor->filter->table_weights(), marginal, cf;
+        std::vector<vb_alias_entry> ct;
+        for (uint32_t v = 0; v < N; ++v) {
+            std::vector<float> row(w.begin() + (size_t)v * N, w.begin() + (size_t)(v + 1) * N);
+            bool any = false;
+            for (float x : row) any |= x != 0.f;
+            float integral = 0.f;
+            if (any) warper->build(row, ct, cf, integral);
+            else for (uint32_t i = 0; i < N; ++i) { ct.push_back({1.0f, i}); cf.push_back(0.f); }
+            marginal.push_back(integral);
+        }
+        out.camera.filter_table_offset = (uint32_t)out.alias_table.size();
+        float mi;
+        warper->build(marginal, out.alias_table, out.alias_func, mi);
+        out.alias_table.insert(out.alias_table.end(), ct.begin(), ct.end()); out.alias_func.insert(out.alias_func.end(), cf.begin(), cf.end());
+    }
     // the flag only matters when some medium exists (all ids are invalid otherwise): keep the kernel's fast path
     bool mediums_on = process_mediums && !mediums.empty();
     out.camera.medium_id = VB_INVALID_ID;               // Photosensory ctor, photosensory.cpp:15-33

@@ -524,6 +524,93 @@ def world_diameter(sc, min_world_radius):
     return float(f32(2.0 * max(radius, float(min_world_radius))))
 
 
+def sphere_mesh(radius=1.0, sub_div=60):
+    """Sphere shape (sphere.cpp:20-88): theta_div = sub_div rings, phi_div = 2 * sub_div segments; vertex and
+    triangle order as the reference emits them; trigonometry in float via glibc cosf / sinf like the C++ host"""
+    radius = f32(radius); theta_div = int(sub_div); phi_div = 2 * theta_div
+    pos, nrm, uv, tri = [[0.0, float(radius), 0.0]], [[0.0, 1.0, 0.0]], [[0.0, 0.0]], []
+    def unit(p):
+        p = np.asarray(p, f32)
+        l = f32(np.sqrt(f32(f32(f32(p[0] * p[0]) + f32(p[1] * p[1])) + f32(p[2] * p[2]))))
+        return [float(f32(x / l)) for x in p]
+    two_pi = f32(6.283185307179586)
+    for i in range(1, theta_div):
+        v = f32(f32(i) / f32(theta_div))
+        theta = f32(f32(math.pi) * v)
+        y = f32(radius * _cfun("cosf", theta)); r = f32(radius * _cfun("sinf", theta))
+        p0 = [float(r), float(y), 0.0]
+        pos.append(p0); nrm.append(unit(p0)); uv.append([0.0, float(v)])
+        for j in range(1, phi_div):
+            u = f32(f32(j) / f32(phi_div))
+            phi = f32(u * two_pi)
+            p = [float(f32(_cfun("cosf", phi) * r)), float(y), float(f32(_cfun("sinf", phi) * r))]
+            pos.append(p); nrm.append(unit(p)); uv.append([float(u), float(v)])
+    pos.append([0.0, float(-radius), 0.0]); nrm.append([0.0, -1.0, 0.0]); uv.append([0.0, 1.0])
+    for i in range(phi_div):
+        tri.append([0, (i + 1) % phi_div + 1, i + 1])
+    for i in range(theta_div - 2):
+        vs = 1 + i * phi_div
+        for j in range(phi_div):
+            if j != phi_div - 1:
+                tri.append([vs, vs + 1, vs + phi_div]); tri.append([vs + 1, vs + phi_div + 1, vs + phi_div])
+            else:
+                tri.append([vs, vs + 1 - phi_div, vs + phi_div]); tri.append([vs + 1 - phi_div, vs + 1, vs + phi_div])
+            vs += 1
+    ve = len(pos) - 1
+    for i in range(phi_div):
+        tri.append([ve, ve - ((1 + i) % phi_div + 1), ve - (i + 1)])
+    return {"pos": np.asarray(pos, f32), "nrm": np.asarray(nrm, f32), "uv": np.asarray(uv, f32), "tri": np.asarray(tri, np.uint32)}
+
+
+def _expf(x):
+    global _libm
+    _cfun("sinf", 0.0)
+    import ctypes
+    _libm.expf.restype = ctypes.c_float; _libm.expf.argtypes = [ctypes.c_float]
+    return f32(_libm.expf(float(f32(x))))
+
+
+def fitted_filter_weights(flt):
+    """FilterSampler::build (fitted_curve.h:36-58): |f| at the 20x20 cell centres of the positive quadrant.
+    gaussian.cpp:49-53, mitchell.cpp:33-52, sinc.cpp:27-30 + math/util.h:37-66; float arithmetic as in the C++ host"""
+    t, prm = flt["type"], flt.get("param", {})
+    r = prm.get("radius", 0.5); r = f32(r[0] if isinstance(r, (list, tuple)) else r)
+    N = capi.VB_FILTER_TABLE_SIZE
+    PI = f32(math.pi)
+    if t == "gaussian":
+        sigma = f32(prm.get("sigma", 1.0))
+        def g(x):
+            a = f32(f32(1.0) / f32(np.sqrt(f32(f32(f32(2.0) * PI) * f32(sigma * sigma)))))
+            return f32(a * _expf(f32(f32(-f32(x * x)) / f32(f32(2.0) * f32(sigma * sigma)))))
+        ex = g(r)
+        f = lambda x, y: f32(max(f32(0.0), f32(g(x) - ex)) * max(f32(0.0), f32(g(y) - ex)))
+    elif t == "mitchell":
+        b, c = f32(prm.get("b", f32(1.0) / f32(3.0))), f32(prm.get("c", f32(1.0) / f32(3.0)))
+        def m1(x):
+            x = f32(abs(x)); x2 = f32(x * x); x3 = f32(x2 * x); s6 = f32(f32(1.0) / f32(6.0))
+            if x <= 1:
+                return f32(f32(f32(f32(f32(f32(12) - f32(9 * b)) - f32(6 * c)) * x3) + f32(f32(f32(f32(-18) + f32(12 * b)) + f32(6 * c)) * x2) + f32(f32(6) - f32(2 * b))) * s6)
+            if x <= 2:
+                return f32(f32(f32(f32(f32(f32(-b) - f32(6 * c)) * x3) + f32(f32(f32(6 * b) + f32(30 * c)) * x2)) + f32(f32(f32(-12 * b) - f32(48 * c)) * x) + f32(f32(8 * b) + f32(24 * c))) * s6)
+            return f32(0.0)
+        f = lambda x, y: f32(m1(f32(f32(2 * x) / r)) * m1(f32(f32(2 * y) / r)))
+    elif t == "sinc":
+        tau = f32(prm.get("tau", 3.0))
+        def sinc(x):
+            x = f32(PI * x)
+            return f32(1.0) if f32(f32(1.0) + f32(x * x)) == 1 else f32(_cfun("sinf", x) / x)
+        ws = lambda x: f32(0.0) if abs(x) > r else f32(sinc(x) * sinc(f32(x / tau)))
+        f = lambda x, y: f32(f32(ws(x) * ws(y)) * f32(4.0))
+    else:
+        raise NotImplementedError(f"filter {t}")
+    out = []
+    for i in range(N * N):
+        x, y = i % N, i // N
+        px, py = f32(f32(f32(x + f32(0.5)) / f32(N)) * r), f32(f32(f32(y + f32(0.5)) / f32(N)) * r)
+        out.append(float(abs(f(px, py))))
+    return out
+
+
 def _medium_records(d):
     """MediumsDesc (scene_desc.cpp:24-34) + MediumDesc::init (node_desc.cpp:182-197) + HomogeneousMedium ctor"""
     md = d.get("mediums")
@@ -573,6 +660,8 @@ def build_scene(path, overrides=None) -> SceneRecords:
             mesh = quad_mesh(prm.get("width", 1.0), prm.get("height", 1.0))
         elif sh["type"] == "cube":
             mesh = cube_mesh(prm.get("x", 1.0), prm.get("y", 1.0), prm.get("z", 1.0))
+        elif sh["type"] == "sphere":
+            mesh = sphere_mesh(prm.get("radius", 1.0), prm.get("sub_div", 60))
         elif sh["type"] == "model":
             mesh = obj_mesh(base / prm["fn"], smooth=bool(prm.get("smooth", False)), flip_uv=bool(prm.get("flip_uv", True)))
         else:
@@ -652,7 +741,12 @@ def build_scene(path, overrides=None) -> SceneRecords:
         lo[1], hi[1] = -float(f32(1.0) / ratio), float(f32(1.0) / ratio)
     sc.camera.screen_lo[:] = lo; sc.camera.screen_hi[:] = hi
     flt = cam.get("filter", {"type": "gaussian", "param": {}})
-    sc.camera.filter_type = capi.VB_FILTER_TRIANGLE if flt["type"] == "triangle" else capi.VB_FILTER_BOX
+    sc.camera.filter_type = {"triangle": capi.VB_FILTER_TRIANGLE, "box": capi.VB_FILTER_BOX}.get(flt["type"], capi.VB_FILTER_FITTED)
+    if sc.camera.filter_type == capi.VB_FILTER_FITTED:
+        N = capi.VB_FILTER_TABLE_SIZE
+        mt, mf, _, ct, cf = alias2d_build(fitted_filter_weights(flt), N, N)
+        sc.camera.filter_table_offset = len(sc.alias_table)
+        sc.alias_table += mt + ct; sc.alias_func += mf + cf
     r = flt.get("param", {}).get("radius", 0.5)
     r = r if isinstance(r, (list, tuple)) else [r, r]
     sc.camera.filter_radius[:] = [float(r[0]), float(r[0])]        # Filter ctor reads as_float: x only (filter.h:43)
