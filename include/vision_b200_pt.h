@@ -40,7 +40,12 @@ typedef struct vb_material_rec {
     vb_slot ior;               /* x; glass */
     vb_slot sigma;             /* diffuse Oren-Nayar */
     float eta[4], k[4];        /* metal: complex ior at the 3 sRGB peak wavelengths */
-    float params[16];          /* [0] anisotropic (mirror/glass/metal/substrate); principled: metallic, spec_tint, ... */
+    /* [0] anisotropic (mirror/glass/metal/substrate/principled). principled (principled_bsdf.cpp:234-290; colour slot =
+     * color, roughness slot = roughness, spec slot = spec_tint, ior slot = ior; the remaining slots are constants):
+     * [1] metallic, [2] sheen_weight, [3] sheen_roughness, [4..6] sheen_tint, [7] coat_weight, [8] coat_roughness,
+     * [9] coat_ior, [10..12] coat_tint, [13] transmission_weight, [14] sheen mode (0 volumetric, 1 approximate = default),
+     * [15] lobe switches bit mask (bit order sheen, coat, metallic, transmission, specular, diffuse; 63 = all) */
+    float params[16];
 } vb_material_rec;
 VB_API int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n);
 
@@ -49,7 +54,10 @@ VB_API int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n)
  * samples them with normalised coordinates; here they are plain float arrays, x fastest, sampled in
  * software (linear, clamp). PURE_REFLECTION: 32x32x1, 1 channel (lobe.cpp:716-735);
  * DIELECTRIC / DIELECTRIC_INV: 32x32x32, 2 channels (lobe.cpp:253-306). A missing table = no compensation. */
-enum { VB_LUT_PURE_REFLECTION = 0, VB_LUT_DIELECTRIC = 1, VB_LUT_DIELECTRIC_INV = 2, VB_LUT_COUNT = 3 };
+enum { VB_LUT_PURE_REFLECTION = 0, VB_LUT_DIELECTRIC = 1, VB_LUT_DIELECTRIC_INV = 2,
+       /* principled BSDF: SpecularLobe / CoatLobe albedo tables (32^3 x 1, precomputed_table.h) and the sheen LTC fits
+        * (32 x 32 x float4, ltc_sheen_table.h) */
+       VB_LUT_SPECULAR = 3, VB_LUT_COAT = 4, VB_LUT_SHEEN_VOLUME = 5, VB_LUT_SHEEN_APPROX = 6, VB_LUT_COUNT = 7 };
 VB_API int vb_luts_set(vb_ctx *ctx, int which, const float *data, uint32_t nx, uint32_t ny, uint32_t nz, uint32_t channels);
 
 /* ---- mediums (reference src/render_core/medium/homogeneous.cpp:11-70) ------------------------------ */

@@ -314,6 +314,8 @@ inline float3 cosine_hemisphere(float2 u, float woz) {               // bxdf.cpp
     return {dx, dy, z};
 }
 
+#include "vo_principled.inl"
+
 // Lobe::sample (lobe.cpp:111-119) with each lobe's sample_wi_local_impl; draws in the reference's order
 inline BSDFSample lobe_sample(const Scene &sc, const Lobe &lb, float3 world_wo, Sampler &sampler) {
     float3 wo = lb.frame.to_local(world_wo);
@@ -410,6 +412,24 @@ inline Lobe create_lobe(const Scene &sc, const Interaction &it) {
 }
 
 // MaterialEvaluator (individual_ns branch), reference material.cpp:132-142,163-175
+struct PrincipledEvaluator {
+    PrincipledSet set;
+    float3 ng;
+    ScatterEval evaluate(const Scene &sc, float3 wo, float3 wi) const {
+        ScatterEval se = principled_evaluate(sc, set, wo, wi, nullptr);
+        bool same = dot(wo, ng) * dot(wi, ng) > 0.f;
+        bool is_trans = (se.flags & FlagTransmission) != 0;
+        if (same == is_trans) se.pdf = 0.f;
+        return se;
+    }
+    BSDFSample sample(const Scene &sc, float3 wo, Sampler &sampler) const {
+        BSDFSample bs = principled_sample(sc, set, wo, sampler);
+        bool same = dot(wo, ng) * dot(bs.wi, ng) > 0.f;
+        bool is_trans = (bs.eval.flags & FlagTransmission) != 0;
+        if (same == is_trans) bs.eval.pdf = 0.f;
+        return bs;
+    }
+};
 struct Evaluator {
     Lobe lobe;
     float3 ng;

@@ -433,6 +433,10 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
             float f = phase_HG(dot(it.wo, wi), it.g);
             se.f = float3{f, f, f}; se.pdf = f; se.flags = 0;
             bs = phase_sample(it.g, it.wo, sampler);
+        } else if (materials[it.mat_id].type == VB_MAT_PRINCIPLED) {
+            PrincipledEvaluator evaluator{principled_create(*this, it), it.ng};
+            se = evaluator.evaluate(*this, it.wo, wi);
+            bs = evaluator.sample(*this, it.wo, sampler);
         } else {
             Evaluator evaluator{create_lobe(*this, it), it.ng};
             se = evaluator.evaluate(*this, it.wo, wi);

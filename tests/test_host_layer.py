@@ -54,7 +54,7 @@ def test_host_records_equal_python_twin():
     assert any("denoiser" in s or "ignored" in s for s in hp.log()) or True
 
 
-@pytest.mark.parametrize("name", ["cbox_materials", "cbox_fog"])
+@pytest.mark.parametrize("name", ["cbox_materials", "cbox_fog", "cbox_principled"])
 def test_host_records_equal_python_twin_materials_and_mediums(name):
     """mirror / glass / metal / substrate plugins, homogeneous medium, per-shape and global medium ids, LUT loading"""
     path = ROOT / "scenes" / "cbox" / f"{name}.json"
@@ -79,6 +79,9 @@ def test_host_records_equal_python_twin_materials_and_mediums(name):
         assert a.instances[5]["inside_medium"] == 0 and a.instances[5]["outside_medium"] == 1 and a.instances[0]["inside_medium"] == 1
         np.testing.assert_allclose(list(a.mediums[0].sigma_s)[:3], [0.74, 0.88, 1.01], rtol=1e-6)     # Skin1
     names = host_api.plugin_names()
+    if name == "cbox_principled":
+        assert sorted(a.luts) == list(range(7)) and sum(m.type == capi.VB_MAT_PRINCIPLED for m in a.materials) == 5
+        assert "vision-material-principled_bsdf#constructor" in host_api.plugin_names()
     for want in ("vision-material-mirror#constructor", "vision-material-glass#constructor", "vision-material-metal#constructor",
                  "vision-material-substrate#constructor", "vision-medium-homogeneous#constructor"):
         assert want in names, want
@@ -168,7 +171,8 @@ def test_desc_defaults_and_errors(tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("SCENE", [SCENE, ROOT / "scenes" / "cbox" / "cbox_materials.json", ROOT / "scenes" / "cbox" / "cbox_fog.json",
-                                   ROOT / "scenes" / "cbox" / "cbox_lights.json", ROOT / "scenes" / "cbox" / "cbox_sphere.json"])
+                                   ROOT / "scenes" / "cbox" / "cbox_lights.json", ROOT / "scenes" / "cbox" / "cbox_sphere.json",
+                                   ROOT / "scenes" / "cbox" / "cbox_principled.json"])
 def test_host_pipeline_renders_like_python_path(vbctx, SCENE):
     hp = host_api.HostPipeline(SCENE)
     hp.prepare(0)

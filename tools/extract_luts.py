@@ -14,11 +14,17 @@ out = Path(__file__).resolve().parent.parent / "vision_b200" / "data"
 out.mkdir(exist_ok=True)
 want = {"PureReflectionLobe_Table": ("lut_pure_reflection_32x32x1x1.f32", 1024, 1),
         "DielectricLobe_Table": ("lut_dielectric_32x32x32x2.f32", 32768, 2),
-        "DielectricInvLobe_Table": ("lut_dielectric_inv_32x32x32x2.f32", 32768, 2)}
+        "DielectricInvLobe_Table": ("lut_dielectric_inv_32x32x32x2.f32", 32768, 2),
+        "SpecularLobe_Table": ("lut_specular_32x32x32x1.f32", 32768, 1),
+        "CoatLobe_Table": ("lut_coat_32x32x32x1.f32", 32768, 1),
+        # principled sheen (Zeltner et al. 2022 LTC fits), src/render_core/material/ltc_sheen_table.h
+        "SheenLTCTableVolume": ("lut_sheen_volume_32x32x1x4.f32", 1024, 4),
+        "SheenLTCTableApprox": ("lut_sheen_approx_32x32x1x4.f32", 1024, 4)}
+src += (ref / "src/render_core/material/ltc_sheen_table.h").read_text()
 for name, (fn, count, ch) in want.items():
     m = re.search(r"const\s+\w+\s+" + name + r"\[(\d+)\]\s*=\s*\{(.*?)\};", src, re.S)
     assert m and int(m.group(1)) == count, name
-    nums = re.findall(r"[-+]?(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?", re.sub(r"float\d", "", m.group(2)))
+    nums = re.findall(r"[-+]?(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?", re.sub(r"(\d)f\b", r"\1", re.sub(r"float\d", "", m.group(2))))
     a = np.array([float(x) for x in nums], np.float32)
     assert a.size == count * ch, (name, a.size)
     a.tofile(out / fn)

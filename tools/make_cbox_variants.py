@@ -79,4 +79,22 @@ for i, s_ in enumerate(e["shapes"]):
 e["camera"]["param"]["filter"] = {"type": "gaussian", "name": "gaussianFilter", "param": {"radius": 1.5, "sigma": 0.5}}
 e["integrator"]["param"]["max_depth"] = 8
 (root / "cbox_sphere.json").write_text(json.dumps(e, indent=1))
-print("wrote", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json", root / "cbox_sphere.json")
+
+# cbox_principled.json: PrincipledBSDF (principled_bsdf.cpp) on every lobe combination: coated metal (tall box),
+# transmissive (short box), sheen cloth (floor), plain dielectric plastic with a textured colour (back wall), rough
+# tinted specular (right wall)
+g = copy.deepcopy(base)
+back_color = next(m for m in g["materials"] if m["name"] == next(s_["param"]["material"] for s_ in g["shapes"] if s_["name"] == "shape_2"))["param"]["color"]
+g["materials"] += [
+    {"type": "principled_bsdf", "name": "P_metal", "param": {"color": [0.95, 0.64, 0.54], "metallic": 1.0, "roughness": 0.35, "spec_tint": [0.9, 0.8, 0.7],
+                                                              "coat_weight": 0.8, "coat_roughness": 0.1, "coat_ior": 1.6, "coat_tint": [1, 0.9, 0.8], "anisotropic": 0.5}},
+    {"type": "principled_bsdf", "name": "P_trans", "param": {"color": [0.8, 0.95, 0.9], "transmission_weight": 0.9, "roughness": 0.15, "ior": 1.45}},
+    {"type": "principled_bsdf", "name": "P_sheen", "param": {"color": [0.3, 0.1, 0.4], "sheen_weight": 1.0, "sheen_roughness": 0.4, "sheen_tint": [1, 0.8, 0.9], "roughness": 0.8}},
+    {"type": "principled_bsdf", "name": "P_plastic", "param": {"color": back_color, "roughness": 0.3, "ior": 1.5}},
+    {"type": "principled_bsdf", "name": "P_mix", "param": {"color": [0.1, 0.5, 0.1], "metallic": 0.5, "roughness": 0.6, "spec_tint": [1, 0.7, 0.7], "coat_weight": 0.3,
+                                                            "sheen_weight": 0.5, "transmission_weight": 0.2}},
+]
+assign(g, {"shape_6": "P_metal", "shape_5": "P_trans", "shape_0": "P_sheen", "shape_2": "P_plastic", "shape_4": "P_mix"})
+g["integrator"]["param"]["max_depth"] = 8
+(root / "cbox_principled.json").write_text(json.dumps(g, indent=1))
+print("wrote", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json", root / "cbox_sphere.json", root / "cbox_principled.json")

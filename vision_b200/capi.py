@@ -286,17 +286,23 @@ class vb_medium_rec(C.Structure):
                 ("sigma_a", C.c_float * 4), ("sigma_s", C.c_float * 4)]
 
 
-VB_LUT_PURE_REFLECTION, VB_LUT_DIELECTRIC, VB_LUT_DIELECTRIC_INV = 0, 1, 2
+VB_LUT_PURE_REFLECTION, VB_LUT_DIELECTRIC, VB_LUT_DIELECTRIC_INV, VB_LUT_SPECULAR, VB_LUT_COAT, VB_LUT_SHEEN_VOLUME, VB_LUT_SHEEN_APPROX = range(7)
+VB_LUT_COUNT = 7
 LUT_FILES = {VB_LUT_PURE_REFLECTION: ("lut_pure_reflection_32x32x1x1.f32", (32, 32, 1, 1)),
              VB_LUT_DIELECTRIC: ("lut_dielectric_32x32x32x2.f32", (32, 32, 32, 2)),
-             VB_LUT_DIELECTRIC_INV: ("lut_dielectric_inv_32x32x32x2.f32", (32, 32, 32, 2))}
+             VB_LUT_DIELECTRIC_INV: ("lut_dielectric_inv_32x32x32x2.f32", (32, 32, 32, 2)),
+             VB_LUT_SPECULAR: ("lut_specular_32x32x32x1.f32", (32, 32, 32, 1)),
+             VB_LUT_COAT: ("lut_coat_32x32x32x1.f32", (32, 32, 32, 1)),
+             VB_LUT_SHEEN_VOLUME: ("lut_sheen_volume_32x32x1x4.f32", (32, 32, 1, 4)),
+             VB_LUT_SHEEN_APPROX: ("lut_sheen_approx_32x32x1x4.f32", (32, 32, 1, 4))}
 
 
-def load_luts() -> dict:
-    """the energy-compensation tables shipped under vision_b200/data (tools/extract_luts.py)"""
+def load_luts(principled=False) -> dict:
+    """the energy-compensation tables shipped under vision_b200/data (tools/extract_luts.py): the three microfacet
+    tables, plus the principled BSDF's specular / coat / sheen tables when asked"""
     from pathlib import Path
     d = Path(__file__).resolve().parent / "data"
-    return {k: (np.fromfile(d / fn, np.float32), dims) for k, (fn, dims) in LUT_FILES.items()}
+    return {k: (np.fromfile(d / fn, np.float32), dims) for k, (fn, dims) in LUT_FILES.items() if principled or k <= VB_LUT_DIELECTRIC_INV}
 
 
 class vb_alias_entry(C.Structure):
@@ -405,7 +411,7 @@ def _pt_methods():
         self._check(self.lib.vb_textures_set(self.h, texs, len(sc.textures)), "vb_textures_set")
         mats = (vb_material_rec * max(1, len(sc.materials)))(*sc.materials)
         self._check(self.lib.vb_materials_set(self.h, mats, len(sc.materials)), "vb_materials_set")
-        for which in range(3):
+        for which in range(VB_LUT_COUNT):
             if which in sc.luts:
                 a, (nx, ny, nz, ch) = sc.luts[which]
                 a = np.ascontiguousarray(a, np.float32)

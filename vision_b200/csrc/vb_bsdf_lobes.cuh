@@ -258,3 +258,4 @@ __device__ __forceinline__ void hemisphere_discard(ScatterEval &se, f3 wo, f3 wi
 }
 
 }  // namespace
+#include "vb_principled.cuh"

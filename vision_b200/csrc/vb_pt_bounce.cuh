@@ -30,6 +30,9 @@ enum : int { PT_CONTINUE = 1, PT_SHADOW = 2, PT_VERTEX = 4, PT_LIGHT = 8 };
 // surface interaction was computed, PT_LIGHT -> a light was sampled (statistics: a PT_LIGHT vertex without
 // PT_SHADOW is a shadow ray the reference traces although its contribution is zero; it is culled here). Without PT_CONTINUE the path is finished: ps.ret
 // (+ pending) is the sample's radiance.
+// PRINCIPLED = the scene uses the principled BSDF: its LobeSet code (stack frame, out-of-line calls) is compiled
+// into a separate kernel instantiation so that scenes without it keep the lean kernel
+template <bool PRINCIPLED>
 __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay &ray, const VbHit &hit, VbRay &shadow, f3 &pending) {
     Sampler &sampler = ps.sampler;
     const bool mediums = S.params.process_mediums != 0;
@@ -124,6 +127,12 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         float f = phase_HG(dot(it.wo, wi), it.g);
         se.f = f3{f, f, f}; se.pdf = f; se.flags = 0;
         bs = phase_sample(it.g, it.wo, sampler);
+    } else if (PRINCIPLED && S.materials[it.mat_id].type == VB_MAT_PRINCIPLED) {
+        PrincipledSet set = principled_create(S, it);
+        se = principled_evaluate(S, set, it.wo, wi, nullptr);
+        hemisphere_discard(se, it.wo, wi, it.ng);
+        bs = principled_sample(S, set, it.wo, sampler);
+        hemisphere_discard(bs.eval, it.wo, bs.wi, it.ng);
     } else {
         Lobe lobe = create_lobe(S, it);
         se = lobe_evaluate(S, lobe, it.wo, wi, false, nullptr);

@@ -11,7 +11,7 @@ struct PtCounters { unsigned long long closest, any, vertices, culled; };
 // any-hit call site whatever bounce or frame each of them is at, and a lane whose path ended starts
 // its next frame in the same iteration instead of waiting for the longest path of the warp. The
 // running film value stays in registers and is written once per launch.
-template <bool DUMP_PRIMARY>
+template <bool DUMP_PRIMARY, bool PRINCIPLED>
 __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t first_frame, uint32_t n_frames, uint32_t stride, int mode,
                                                          uint32_t frames_done, float4 *rt, float4 *accum, PtCounters *counters,
                                                          uint32_t *h_inst, uint32_t *h_prim, float *h_u, float *h_v, float *h_t) {
@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
         int flags = 0;
         VbRay shadow;
         f3 pending{0, 0, 0};
-        if (run) flags = pt_bounce(S, ps, ray, hit, shadow, pending);
+        if (run) flags = pt_bounce<PRINCIPLED>(S, ps, ray, hit, shadow, pending);
         if (flags & PT_VERTEX) c_vert++;
         if ((flags & PT_LIGHT) && !(flags & PT_SHADOW)) c_culled++;
         if (flags & PT_SHADOW) {
@@ -127,6 +127,7 @@ struct vb_pt_state {
     uint32_t n_mat_types = 0;          // distinct material models in use (one: ordering the shading queue is pointless)
     uint64_t work[4] = {0, 0, 0, 0};
     uint32_t n_alias = 0;
+    bool has_principled = false;
     std::vector<DevMesh> h_meshes;
     DevMesh *d_meshes = nullptr;
     DevInst *d_inst = nullptr;
@@ -235,12 +236,13 @@ int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n) {
     cudaSetDevice(ctx->device);
     vb_pt_state *p = pt_state(ctx);
     for (uint32_t i = 0; i < n; ++i)
-        if (mat[i].type == VB_MAT_PRINCIPLED || mat[i].type > VB_MAT_BLACK_BODY)
+        if (mat[i].type > VB_MAT_BLACK_BODY)
             return ctx->fail(VB_ERR_UNSUPPORTED, "vb_materials_set: material type " + std::to_string(mat[i].type) + " not implemented yet");
     cudaFree(p->d_mat); p->d_mat = nullptr; p->n_mat = n;
     uint32_t types = 0;
     for (uint32_t i = 0; i < n; ++i) types |= 1u << mat[i].type;
     p->n_mat_types = (uint32_t)__builtin_popcount(types);
+    p->has_principled = (types >> VB_MAT_PRINCIPLED) & 1u;
     if (n) {
         VB_CUDA(cudaMalloc(&p->d_mat, sizeof(vb_material_rec) * n));
         VB_CUDA(cudaMemcpy(p->d_mat, mat, sizeof(vb_material_rec) * n, cudaMemcpyHostToDevice));
@@ -408,9 +410,11 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     unsigned grid = (n_pix + PT_BLOCK - 1) / PT_BLOCK;
     VB_CUDA(cudaMemsetAsync(p->d_counters, 0, sizeof(PtCounters), ctx->stream));
     ctx->prof_begin("path_trace", 1);
-    if (dump) k_path_trace<true><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, 1, 1, mode, 0, p->rt, p->accum, p->d_counters, hi, hp, hu, hv, ht);
-    else k_path_trace<false><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum, p->d_counters,
-                                                                nullptr, nullptr, nullptr, nullptr, nullptr);
+    if (dump) k_path_trace<true, false><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, 1, 1, mode, 0, p->rt, p->accum, p->d_counters, hi, hp, hu, hv, ht);
+    else if (p->has_principled) k_path_trace<false, true><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum,
+                                                                                           p->d_counters, nullptr, nullptr, nullptr, nullptr, nullptr);
+    else k_path_trace<false, false><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum, p->d_counters,
+                                                                       nullptr, nullptr, nullptr, nullptr, nullptr);
     ctx->prof_end();
     VB_CHECK_LAUNCH();
     VB_CUDA(cudaMemcpyAsync(&p->last, p->d_counters, sizeof(PtCounters), cudaMemcpyDeviceToHost, ctx->stream));

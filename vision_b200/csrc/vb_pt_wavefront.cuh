@@ -82,7 +82,8 @@ __global__ void __launch_bounds__(256) k_wf_material_keys(PtScene S, uint32_t n,
 }
 
 // one Li vertex per queue entry; entry i of the launch is queue position order[i] (low word)
-__global__ void __launch_bounds__(128) k_wf_shade(PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
+template <bool PRINCIPLED>
+__global__ void __launch_bounds__(128, 4) k_wf_shade(PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
                                                   WfState st, WfQueue Qout, WfQueue Qsh, float4 *sh_pend, WfSortBox B, WfCounters *cnt) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
@@ -103,7 +104,7 @@ __global__ void __launch_bounds__(128) k_wf_shade(PtScene S, uint32_t n, WfQueue
         ps.throughput = f3{a.x, a.y, a.z}; ps.eta_scale = a.w;
         ps.ret = f3{b.x, b.y, b.z}; ps.scatter_pdf = b.w;
         ps.sampler.state = c.x; ps.ray_medium = c.y; ps.bounces = c.z;
-        flags = pt_bounce(S, ps, ray, hit, shadow, pending);
+        flags = pt_bounce<PRINCIPLED>(S, ps, ray, hit, shadow, pending);
         if ((flags & PT_CONTINUE) && ps.bounces >= S.params.max_depth) flags &= ~PT_CONTINUE;
         st.b[slot] = make_float4(ps.ret.x, ps.ret.y, ps.ret.z, ps.scatter_pdf);
         if (flags & PT_CONTINUE) {

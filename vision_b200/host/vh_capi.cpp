@@ -62,10 +62,10 @@ VB_API uint64_t vh_records_blob(vh_pipeline *h, int which, void *dst, uint64_t c
         case 5: src = &r.camera; n = sizeof(vb_camera); break;
         case 6: src = &r.params; n = sizeof(vb_pt_params); break;
         case 7: src = r.mediums.data(); n = r.mediums.size() * sizeof(vb_medium_rec); break;
-        case 8: src = r.luts[0].data.data(); n = r.luts[0].data.size() * 4; break;
-        case 9: src = r.luts[1].data.data(); n = r.luts[1].data.size() * 4; break;
-        case 10: src = r.luts[2].data.data(); n = r.luts[2].data.size() * 4; break;
-        default: return 0;
+        default:
+            if (which < 8 || which >= 8 + VB_LUT_COUNT) return 0;           // 8 + k: LUT k
+            src = r.luts[which - 8].data.data(); n = r.luts[which - 8].data.size() * 4;
+            break;
     }
     if (dst && cap >= n && n) std::memcpy(dst, src, n);
     return n;

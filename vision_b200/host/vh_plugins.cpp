@@ -236,6 +236,41 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(SubstrateMaterial, material, substrate, constructor)
 
+// reference src/render_core/material/principled_bsdf.cpp:216-461 (slot names and defaults :264-290). Colour-like slots that
+// scenes texture (color, spec_tint) and roughness / ior stay slots; the remaining inputs are constants in params[]
+class PrincipledMaterial : public Material {
+    MaterialDesc desc_;
+public:
+    explicit PrincipledMaterial(const MaterialDesc &d) : Material(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "principled_bsdf"; }
+    void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
+        init_material_record(r);
+        r.type = VB_MAT_PRINCIPLED;
+        r.color = make_slot(desc_["color"], {1.f, 1.f, 1.f}, ctx);
+        r.spec = make_slot(desc_["spec_tint"], {1.f, 1.f, 1.f}, ctx);
+        auto number = [&](const char *key, float def) { return desc_.has_attr(key) ? make_slot(desc_[key], {def, def, def}, ctx).value[0] : def; };
+        auto const3 = [&](const char *key, float *dst) {
+            vb_slot s = make_slot(desc_[key], {1.f, 1.f, 1.f}, ctx);
+            if (s.tex_id != VB_INVALID_ID) throw std::runtime_error(std::string("principled_bsdf: textured ") + key + " is not supported");
+            dst[0] = s.value[0]; dst[1] = s.value[1]; dst[2] = s.value[2];
+        };
+        float rough = number("roughness", 0.5f), ior = number("ior", 1.5f);
+        r.roughness.value[0] = r.roughness.value[1] = r.roughness.value[2] = rough; r.roughness.value[3] = 1.f;
+        r.ior.value[0] = r.ior.value[1] = r.ior.value[2] = ior; r.ior.value[3] = 1.f;
+        float *P = r.params;
+        P[0] = number("anisotropic", 0.f);
+        P[1] = number("metallic", 0.f);
+        P[2] = number("sheen_weight", 0.f); P[3] = number("sheen_roughness", 0.5f);
+        const3("sheen_tint", P + 4);
+        P[7] = number("coat_weight", 0.f); P[8] = number("coat_roughness", 0.2f); P[9] = number("coat_ior", 1.5f);
+        const3("coat_tint", P + 10);
+        P[13] = number("transmission_weight", 0.f);
+        P[14] = 1.f;                 // sheen_mode_ = Approximate
+        P[15] = 63.f;                // all lobe switches on
+    }
+};
+VH_MAKE_CLASS_CREATOR(PrincipledMaterial, material, principled_bsdf, constructor)
+
 // reference src/render_core/medium/homogeneous.cpp:11-28 + MediumDesc::init (node_desc.cpp:182-197)
 class HomogeneousMedium : public Medium {
     MediumDesc desc_;

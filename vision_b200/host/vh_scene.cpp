@@ -200,9 +200,15 @@ void Scene::prepare(SceneRecords &out) {
     out.textures = image_pool.images;
     out.mediums.resize(mediums.size());
     for (auto &m : mediums) m->fill_record(out.mediums[m->index]);
-    bool need_luts = false;
-    for (auto &m : out.materials) need_luts |= m.type == VB_MAT_MIRROR || m.type == VB_MAT_GLASS || m.type == VB_MAT_METAL;
-    if (need_luts) {             // PureReflectionLobe::prepare / DielectricLobe::prepare (lobe.cpp:253-260,731-735)
+    bool need_luts = false, principled = false;
+    for (auto &m : out.materials) { principled |= m.type == VB_MAT_PRINCIPLED; need_luts |= m.type == VB_MAT_MIRROR || m.type == VB_MAT_GLASS || m.type == VB_MAT_METAL; }
+    if (principled) {            // PrincipledBSDF::prepare (principled_bsdf.cpp:324-330): coat, sheen, specular tables
+        load_lut(out.luts[VB_LUT_SPECULAR], "lut_specular_32x32x32x1.f32", 32, 32, 32, 1);
+        load_lut(out.luts[VB_LUT_COAT], "lut_coat_32x32x32x1.f32", 32, 32, 32, 1);
+        load_lut(out.luts[VB_LUT_SHEEN_VOLUME], "lut_sheen_volume_32x32x1x4.f32", 32, 32, 1, 4);
+        load_lut(out.luts[VB_LUT_SHEEN_APPROX], "lut_sheen_approx_32x32x1x4.f32", 32, 32, 1, 4);
+    }
+    if (need_luts || principled) {             // PureReflectionLobe::prepare / DielectricLobe::prepare (lobe.cpp:253-260,731-735)
         load_lut(out.luts[VB_LUT_PURE_REFLECTION], "lut_pure_reflection_32x32x1x1.f32", 32, 32, 1, 1);
         load_lut(out.luts[VB_LUT_DIELECTRIC], "lut_dielectric_32x32x32x2.f32", 32, 32, 32, 2);
         load_lut(out.luts[VB_LUT_DIELECTRIC_INV], "lut_dielectric_inv_32x32x32x2.f32", 32, 32, 32, 2);

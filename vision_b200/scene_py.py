@@ -419,6 +419,27 @@ def _material_record(m, textures, base, spectrum_complete=False):
         rec.color = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
         rec.spec = _color_slot(prm.get("spec", [0.05, 0.05, 0.05]), textures, base)
         rec.roughness = make_slot([_number(prm.get("roughness"), 0.5)] * 3)
+    elif t == "principled_bsdf":                                   # principled_bsdf.cpp:264-290 (slot defaults)
+        rec.type = capi.VB_MAT_PRINCIPLED
+        rec.flags = 0
+        rec.color = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
+        rec.roughness = make_slot([_number(prm.get("roughness"), 0.5)] * 3)
+        rec.spec = _color_slot(prm.get("spec_tint", [1, 1, 1]), textures, base)
+        rec.ior = make_slot([_number(prm.get("ior"), 1.5)] * 3)
+        def const3(key, default):
+            s = _color_slot(prm.get(key, default), textures, base)
+            if s.tex_id != VB_INVALID_ID:
+                raise NotImplementedError(f"principled_bsdf: textured {key}")
+            return [float(s.value[0]), float(s.value[1]), float(s.value[2])]
+        P = rec.params
+        P[1] = _number(prm.get("metallic"), 0.0)
+        P[2] = _number(prm.get("sheen_weight"), 0.0); P[3] = _number(prm.get("sheen_roughness"), 0.5)
+        P[4], P[5], P[6] = const3("sheen_tint", [1, 1, 1])
+        P[7] = _number(prm.get("coat_weight"), 0.0); P[8] = _number(prm.get("coat_roughness"), 0.2); P[9] = _number(prm.get("coat_ior"), 1.5)
+        P[10], P[11], P[12] = const3("coat_tint", [1, 1, 1])
+        P[13] = _number(prm.get("transmission_weight"), 0.0)
+        P[14] = 1.0                                                # sheen_mode_ = Approximate (principled_bsdf.cpp:260)
+        P[15] = 63.0                                               # all lobe switches on (principled_bsdf.cpp:261-265)
     else:
         return None
     return rec
@@ -691,8 +712,9 @@ def build_scene(path, overrides=None) -> SceneRecords:
     for i in sc.instances:
         if i["material_id"] != VB_INVALID_ID:
             i["material_id"] = remap[i["material_id"]]
-    if any(r.type in (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL) for r in sc.materials) and ov.get("luts", True):
-        sc.luts = capi.load_luts()
+    lut_users = (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL, capi.VB_MAT_PRINCIPLED)
+    if any(r.type in lut_users for r in sc.materials) and ov.get("luts", True):
+        sc.luts = capi.load_luts(principled=any(r.type == capi.VB_MAT_PRINCIPLED for r in sc.materials))
     # LightSampler ctor (lightsampler.cpp:11-27): listed lights come first, the shapes' emissions follow; tidy_up
     # (lightsampler.cpp:67-77) groups them by type in first-seen order; records are made in that order
     free = [] if ov.get("drop_lights", False) else d.get("light_sampler", {}).get("param", {}).get("lights", [])
