@@ -79,6 +79,7 @@ struct vb_ctx {
     bool last_build_ploc = false;
     int opt_size_classes = 1;                // build: triangle size class as the top bits of the Morton sort key
     int opt_sort_rays = 1, opt_sort_min_rays = 1 << 16;
+    int opt_sort_oct_shift = 0;              // ray sort key: direction octant above this many low Morton bits (vb_ray_sort_key)
     int opt_pt_schedule = 0;                 // 0 = wavefront (default), 1 = megakernel
     int opt_pt_sort_material = 1;            // wavefront: order shading entries by material
     int opt_pt_count_work = 0;               // wavefront: instrumented traversal (nodes / triangles per ray), never timed

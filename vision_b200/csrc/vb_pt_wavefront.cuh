@@ -33,12 +33,12 @@ struct WfState {
 // a ray queue: AoS ray records (o.xyz, tmin)(d.xyz, tmax), the sort record (vb_ray_sort_key << 32 | queue index)
 // the trace kernel orders its fetches by, and the path slot each entry belongs to
 struct WfQueue { float4 *rays; uint64_t *keyidx; uint32_t *slot; };
-struct WfSortBox { float3 lo, inv_ext; };
+struct WfSortBox { float3 lo, inv_ext; uint32_t oct_shift; };
 
 __device__ __forceinline__ void wf_push_ray(const WfQueue &Q, const WfSortBox &B, uint32_t i, const VbRay &r) {
     Q.rays[2 * (size_t)i] = make_float4(r.ox, r.oy, r.oz, r.tmin);
     Q.rays[2 * (size_t)i + 1] = make_float4(r.dx, r.dy, r.dz, r.tmax);
-    Q.keyidx[i] = ((uint64_t)vb_ray_sort_key(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, B.lo, B.inv_ext) << 32) | i;
+    Q.keyidx[i] = ((uint64_t)vb_ray_sort_key(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, B.lo, B.inv_ext, B.oct_shift) << 32) | i;
 }
 __device__ __forceinline__ VbRay wf_load_ray(const float4 *rays, uint32_t i) {
     float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);

@@ -77,6 +77,7 @@ static int wf_render_batch(vb_ctx *ctx, vb_pt_state *p, vb_wf_buffers &w, const 
     B.lo = make_float3(ctx->sort_lo[0], ctx->sort_lo[1], ctx->sort_lo[2]);
     B.inv_ext = make_float3(1.f / fmaxf(ctx->sort_hi[0] - ctx->sort_lo[0], 1e-30f), 1.f / fmaxf(ctx->sort_hi[1] - ctx->sort_lo[1], 1e-30f),
                             1.f / fmaxf(ctx->sort_hi[2] - ctx->sort_lo[2], 1e-30f));
+    B.oct_shift = (uint32_t)ctx->opt_sort_oct_shift;
     ctx->prof_begin("pt_generate", 1);
     k_wf_generate<<<(P + 255) / 256, 256, 0, st>>>(S, first, stride, fi0, P, WfQueue{w.rays[0], w.keys[0], w.slot_q[0]}, B, w.st);
     ctx->prof_end();

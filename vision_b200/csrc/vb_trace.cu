@@ -29,8 +29,15 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                                                        int REFILL_THR, int TRI_THR,
                                                        const float4 *__restrict__ RS, const uint32_t *__restrict__ perm, int perm_stride,
                                                        uint4 *H4) {
-    __shared__ uint2 s_stack_all[VB_SM_STACK * TRACE_BLOCK];
-    uint2 *s_stack = s_stack_all + threadIdx.x;
+    // traversal stack: VB_SM_STACK entries per thread in shared memory, [entry][thread] (conflict-free), 1 KB per entry row.
+    // The stack pointer is kept as a 32-bit SHARED ADDRESS spa = s0 + 8 * tid + 1024 * depth (s0 1 KB aligned, uniform):
+    // push / pop are one ld/st.shared and one add, and "depth > 0" is one compare against a uniform register.
+    __shared__ __align__(1024) uint2 s_stack_all[VB_SM_STACK * TRACE_BLOCK];
+    static_assert(TRACE_BLOCK * sizeof(uint2) == 1024, "stack row = 1 KB");
+    uint32_t s0;        // through an asm so that ptxas keeps it in a register instead of re-deriving it (S2R + 3 ALU) at every use
+    asm volatile("mov.u32 %0, %1;" : "=r"(s0) : "r"((uint32_t)__cvta_generic_to_shared(s_stack_all)));
+    const uint32_t s_row1 = s0 + 1024u, s_end = s0 + 1024u * VB_SM_STACK;
+    uint32_t spa = s0 + 8u * threadIdx.x;
     uint2 l_stack[VB_LOCAL_STACK];
     const uint32_t mg = vb_qf_magic_init();
     const unsigned lane = threadIdx.x & 31u;
@@ -38,27 +45,37 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
     uint32_t nn = 0, nt = 0;
 
     bool active = false, exhausted = false;
-    uint64_t idx = 0;
+    constexpr uint64_t NO_RESULT = ~0ull;
+    uint64_t idx = NO_RESULT;
     VbRay r{};
     float idx_ = 0.f, idy_ = 0.f, idz_ = 0.f, tmax = 0.f;
     uint32_t oct_inv4 = 0;
     VbHit hit{};
     uint2 G = make_uint2(0u, 0u), Tg = make_uint2(0u, 0u), Td = make_uint2(0u, 0u);
-    int sp = 0;
     bool occluded = false;
 
     for (;;) {
+        // ---------------- results of the rays that finished since the last refill ----------------
+        // (stored here, several lanes at a time, instead of one by one inside the traversal loop)
+        if (!active && idx != NO_RESULT) {
+            if (ANY) occ[idx] = occluded ? 1 : 0;
+            else if (H4) H4[idx] = make_uint4(hit.inst, hit.prim, __float_as_uint(hit.u), __float_as_uint(hit.v));   // queue form: one 16-byte record
+            else { H.inst[idx] = hit.inst; H.prim[idx] = hit.prim; H.u[idx] = hit.u; H.v[idx] = hit.v; H.t[idx] = hit.t; }
+            idx = NO_RESULT;
+        }
         // ---------------- refill idle lanes ----------------
         unsigned idle = __ballot_sync(~0u, !active);
         if (idle && !exhausted) {
             unsigned long long base = 0;
             int leader = __ffs(idle) - 1;
-            if ((int)lane == leader) base = atomicAdd(next_ray, (unsigned long long)__popc(idle));
+            if ((int)lane == leader)        // plain atom: the compiler's own warp aggregation around atomicAdd is wasted on one lane
+                asm volatile("atom.global.add.u64 %0, [%1], %2;" : "=l"(base) : "l"(next_ray), "l"((unsigned long long)__popc(idle)) : "memory");
             base = __shfl_sync(~0u, base, leader);
             if (base + __popc(idle) >= n) exhausted = true;
             if (!active) {
-                idx = base + __popc(idle & lt_mask);
-                if (idx < n) {
+                uint64_t q = base + __popc(idle & lt_mask);
+                if (q < n) {
+                    idx = q;
                     if (RS) {       // sorted order: gather ray perm[idx] from the AoS copy (one 32-byte sector); results go back to that slot
                         if (perm) idx = __ldg(perm + idx * perm_stride);      // stride 2: low word of a 64-bit (key << 32 | index) record
                         float4 a = __ldg(RS + 2 * idx), b = __ldg(RS + 2 * idx + 1);
@@ -73,7 +90,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                     tmax = r.tmax;
                     hit.inst = 0xffffffffu; hit.prim = 0xffffffffu; hit.u = 0.f; hit.v = 0.f; hit.t = 0.f;
                     occluded = false;
-                    sp = 0; Tg = make_uint2(0u, 0u); Td = make_uint2(0u, 0u);
+                    spa = s0 | (spa & 1023u); Tg = make_uint2(0u, 0u); Td = make_uint2(0u, 0u);
                     // root group; an empty interval (or NaN bounds) never enters the tree
                     G = make_uint2(0u, (r.tmin < r.tmax) ? 0x80000000u : 0u);
                     active = true;
@@ -86,24 +103,29 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
         unsigned act;
         do {
             bool has_node = false;
-            if (active) {
-                if (!(G.y & 0xff000000u) && sp > 0 && !(Tg.y && Td.y)) {       // fetch the next node group
-                    sp--;
-                    if (sp < VB_SM_STACK) G = s_stack[sp * TRACE_BLOCK];
-                    else if (sp < VB_SM_STACK + VB_LOCAL_STACK) G = l_stack[sp - VB_SM_STACK];
-                    else G = make_uint2(0u, 0u);
+            if (active && !(Tg.y && Td.y)) {                  // both triangle slots full: a triangle round has to run first
+                if (G.y < 0x01000000u && spa >= s_row1) {     // fetch the next node group
+                    spa -= 1024u;
+                    if (spa < s_end) G = vb_lds64(spa);
+                    else {
+                        uint32_t e = (spa - s_end) >> 10;
+                        G = e < VB_LOCAL_STACK ? l_stack[e] : make_uint2(0u, 0u);
+                    }
                 }
-                has_node = (G.y & 0xff000000u) && !(Tg.y && Td.y);
+                has_node = G.y >= 0x01000000u;
             }
             // ---- phase N: one child box-test per lane ----
             if (has_node) {
                 uint32_t hits_imask = G.y;
                 uint32_t bit = 31u - __clz(hits_imask);
                 G.y &= ~(1u << bit);
-                if (G.y & 0xff000000u) {
-                    if (sp < VB_SM_STACK) s_stack[sp * TRACE_BLOCK] = G;
-                    else if (sp < VB_SM_STACK + VB_LOCAL_STACK) l_stack[sp - VB_SM_STACK] = G;
-                    sp++;
+                if (G.y >= 0x01000000u) {
+                    if (spa < s_end) vb_sts64(spa, G);
+                    else {
+                        uint32_t e = (spa - s_end) >> 10;
+                        if (e < VB_LOCAL_STACK) l_stack[e] = G;
+                    }
+                    spa += 1024u;
                 }
                 uint32_t slot = (bit - 24u) ^ (oct_inv4 & 0xffu);
                 uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot) & 0xffu);
@@ -134,7 +156,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                         if (COUNT) nt++;
                         float t, u, v;
                         if (vb_intersect_triangle(r, a, b, c, r.tmax, t, u, v)) {
-                            if (ANY) { occluded = true; Tg.y = 0; Td.y = 0; G.y = 0; sp = 0; }
+                            if (ANY) { occluded = true; Tg.y = 0; Td.y = 0; G.y = 0; spa = s0 | (spa & 1023u); }
                             else vb_commit_hit(hit, tmax, a, b, t, u, v);
                         }
                         if (!Tg.y) { Tg = Td; Td = make_uint2(0u, 0u); }
@@ -143,13 +165,8 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                     tm = __ballot_sync(~0u, tri);
                 }
             }
-            // ---- retire finished rays ----
-            if (active && !(G.y & 0xff000000u) && sp == 0 && !Tg.y) {
-                if (ANY) occ[idx] = occluded ? 1 : 0;
-                else if (H4) H4[idx] = make_uint4(hit.inst, hit.prim, __float_as_uint(hit.u), __float_as_uint(hit.v));   // queue form: one 16-byte record
-                else { H.inst[idx] = hit.inst; H.prim[idx] = hit.prim; H.u[idx] = hit.u; H.v[idx] = hit.v; H.t[idx] = hit.t; }
-                active = false;
-            }
+            // ---- finished rays leave the loop; their results are stored at the next refill ----
+            if (active && G.y < 0x01000000u && spa < s_row1 && !Tg.y) active = false;
             act = __ballot_sync(~0u, active);
         } while (act && (exhausted || __popc(act) >= REFILL_THR));
     }
@@ -164,13 +181,13 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
 // Incoherent rays become spatially coherent batches: consecutive rays walk the same subtrees, so
 // node/triangle fetches hit in L1/L2 instead of going to HBM as random 80/48-byte gathers.
 __global__ void __launch_bounds__(256) k_ray_keys(RaysDev R, uint32_t n, float3 lo, float3 inv_ext, uint32_t *keys, uint32_t *vals,
-                                                  float4 *aos) {
+                                                  float4 *aos, uint32_t oct_shift) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float ox = __ldg(R.ox + i), oy = __ldg(R.oy + i), oz = __ldg(R.oz + i);
     float dx = __ldg(R.dx + i), dy = __ldg(R.dy + i), dz = __ldg(R.dz + i);
     // fminf/fmaxf drop NaN operands, so NaN origins land in cell 0
-    keys[i] = vb_ray_sort_key(ox, oy, oz, dx, dy, dz, lo, inv_ext);
+    keys[i] = vb_ray_sort_key(ox, oy, oz, dx, dy, dz, lo, inv_ext, oct_shift);
     vals[i] = i;
     // SoA -> AoS copy (streaming) so that the post-sort gather touches ONE 32-byte sector per ray
     aos[2 * (size_t)i] = make_float4(ox, oy, oz, __ldg(R.tmin + i));
@@ -250,7 +267,7 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
         float3 ie = make_float3(1.f / fmaxf(ctx->sort_hi[0] - ctx->sort_lo[0], 1e-30f), 1.f / fmaxf(ctx->sort_hi[1] - ctx->sort_lo[1], 1e-30f),
                                 1.f / fmaxf(ctx->sort_hi[2] - ctx->sort_lo[2], 1e-30f));
         unsigned g2 = (unsigned)((n + 255) / 256);
-        k_ray_keys<<<g2, 256, 0, st>>>(R, (uint32_t)n, lo, ie, k0, v0, d_aos);
+        k_ray_keys<<<g2, 256, 0, st>>>(R, (uint32_t)n, lo, ie, k0, v0, d_aos, (uint32_t)ctx->opt_sort_oct_shift);
         cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
         cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)n, 0, 24, st);
         if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }

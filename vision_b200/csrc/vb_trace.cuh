@@ -144,6 +144,16 @@ __device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1,
     return hitmask;
 }
 
+// 64-bit shared-memory access by 32-bit shared address (no generic -> shared conversion at the access)
+__device__ __forceinline__ uint2 vb_lds64(uint32_t a) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void vb_sts64(uint32_t a, uint2 v) {
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(v.x), "r"(v.y) : "memory");
+}
+
 // closest-hit bookkeeping with the normative tie rule (smallest t, then smallest (inst, prim))
 __device__ __forceinline__ void vb_commit_hit(VbHit &hit, float &tmax, float4 a, float4 b, float t, float u, float v) {
     uint32_t inst = __float_as_uint(b.w), prim = __float_as_uint(a.w);
@@ -219,10 +229,13 @@ __device__ __forceinline__ uint32_t vb_expand8(uint32_t v) {      // 8 bits -> e
     v = (v | (v << 2)) & 0x249249u;
     return v;
 }
-__device__ __forceinline__ uint32_t vb_ray_sort_key(float ox, float oy, float oz, float dx, float dy, float dz, float3 lo, float3 inv_ext) {
+// oct_shift s: the octant sits ABOVE the low s Morton bits, so runs of 2^s neighbouring cells share one octant
+__device__ __forceinline__ uint32_t vb_ray_sort_key(float ox, float oy, float oz, float dx, float dy, float dz, float3 lo, float3 inv_ext,
+                                                    uint32_t oct_shift = 0) {
     uint32_t ix = (uint32_t)fminf(fmaxf((ox - lo.x) * inv_ext.x * 128.f, 0.f), 127.f);
     uint32_t iy = (uint32_t)fminf(fmaxf((oy - lo.y) * inv_ext.y * 128.f, 0.f), 127.f);
     uint32_t iz = (uint32_t)fminf(fmaxf((oz - lo.z) * inv_ext.z * 128.f, 0.f), 127.f);
     uint32_t oct = (dx < 0.f ? 4u : 0u) | (dy < 0.f ? 2u : 0u) | (dz < 0.f ? 1u : 0u);
-    return (((vb_expand8(ix) << 2) | (vb_expand8(iy) << 1) | vb_expand8(iz)) << 3) | oct;
+    uint32_t m = (vb_expand8(ix) << 2) | (vb_expand8(iy) << 1) | vb_expand8(iz);
+    return ((m >> oct_shift) << (oct_shift + 3)) | (oct << oct_shift) | (m & ((1u << oct_shift) - 1u));
 }
