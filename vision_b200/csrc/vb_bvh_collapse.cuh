@@ -96,11 +96,11 @@ __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n
     N.ex = (uint8_t)ex; N.ey = (uint8_t)ey; N.ez = (uint8_t)ez; N.imask = (uint8_t)imask;
     N.child_base = child_base; N.tri_base = tri_base;
     float isx = 1.0f / __uint_as_float(ex << 23), isy = 1.0f / __uint_as_float(ey << 23), isz = 1.0f / __uint_as_float(ez << 23);
-    uint32_t tri_off = 0, inner_rel = 0;
+    uint32_t tri_off = 0, inner_rel = 0, leaf8 = 0;
+    for (int s = 0; s < 8; ++s) N.meta[s] = 0;
     for (int s = 0; s < 8; ++s) {
         int j = child_in_slot[s];
         if (j < 0) {
-            N.meta[s] = 0;
             N.qlox[s] = N.qloy[s] = N.qloz[s] = 255; N.qhix[s] = N.qhiy[s] = N.qhiz[s] = 0;   // empty: inverted box
             continue;
         }
@@ -112,13 +112,12 @@ __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n
         N.qhiy[s] = (uint8_t)fminf(fmaxf(ceilf((hi.y - nlo.y) * isy + 0.015625f), 0.f), 255.f);
         N.qhiz[s] = (uint8_t)fminf(fmaxf(ceilf((hi.z - nlo.z) * isz + 0.015625f), 0.f), 255.f);
         if (imask >> s & 1) {
-            N.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
             out[out_base + inner_rel] = WorkItem{c[j], child_base + inner_rel};
             inner_rel++;
         } else {
             uint32_t cntj = tri_count(c[j]);
             uint32_t first = c[j] >= T - 1 ? c[j] - (T - 1) : b.first[c[j]];
-            N.meta[s] = (uint8_t)((((1u << cntj) - 1u) << 5) | tri_off);
+            leaf8 |= 1u << s;                        // one triangle per leaf slot, stored in slot order (vb_next_triangle)
             for (uint32_t t = 0; t < cntj; ++t) {
                 size_t src = 3 * (size_t)b.vals[first + t], dst = 3 * (size_t)(tri_base + tri_off + t);
                 tris_out[dst] = b.tri_in[src]; tris_out[dst + 1] = b.tri_in[src + 1]; tris_out[dst + 2] = b.tri_in[src + 2];
@@ -126,6 +125,7 @@ __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n
             tri_off += cntj;
         }
     }
+    N.meta[0] = (uint8_t)leaf8;
     const uint4 *src = reinterpret_cast<const uint4 *>(&N);
     uint4 *dst = reinterpret_cast<uint4 *>(nodes + it.wide);
 #pragma unroll
@@ -221,7 +221,7 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     const bool want_ploc = ctx->opt_ploc < 0 ? (h_cls[2] + h_cls[3]) > 0 : ctx->opt_ploc != 0;
     const bool ploc = want_ploc && T > 2;
     ctx->last_build_ploc = ploc;
-    const uint32_t max_leaf = ploc ? 1u : (uint32_t)std::min(3, std::max(1, ctx->opt_max_leaf));
+    const uint32_t max_leaf = 1u;        // the traversal's slot-order triangle addressing needs one triangle per leaf slot
     if (ploc) {
         DevBuf<uint32_t> cl0, cl1, nn, totals; DevBuf<uint64_t> pf, ps;
         VB_CUDA(cl0.alloc(T)); VB_CUDA(cl1.alloc(T)); VB_CUDA(nn.alloc(T)); VB_CUDA(totals.alloc(2));

@@ -112,7 +112,7 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     std::string k(key);
     if (k == "trace.refill_thr") ctx->opt_refill_thr = (int)value;
     else if (k == "trace.tri_thr") ctx->opt_tri_thr = (int)value;
-    else if (k == "build.max_leaf") ctx->opt_max_leaf = (int)value;
+    else if (k == "build.max_leaf") { if ((int)value != 1) return ctx->fail(VB_ERR_INVALID, "vb_ctx_set_option: build.max_leaf is fixed at 1 (one triangle per leaf slot)"); }
     else if (k == "build.ploc") ctx->opt_ploc = value < 0 ? -1 : (value != 0 ? 1 : 0);
     else if (k == "build.size_classes") ctx->opt_size_classes = value != 0 ? 1 : 0;
     else if (k == "trace.sort_rays") ctx->opt_sort_rays = (int)value;

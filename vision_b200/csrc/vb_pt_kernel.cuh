@@ -17,7 +17,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                                                          uint32_t *h_inst, uint32_t *h_prim, float *h_u, float *h_v, float *h_t) {
     __shared__ uint2 s_stack_all[VB_SM_STACK * PT_BLOCK];
     uint2 *s_stack = s_stack_all + threadIdx.x;
-    const uint32_t mg = vb_qf_magic_init();
+    const VbTrav mg = vb_trav_init();
     uint32_t pix = blockIdx.x * PT_BLOCK + threadIdx.x;
     uint32_t n_pix = S.width * S.height;
     uint32_t c_closest = 0, c_any = 0, c_vert = 0, c_culled = 0, dummy0 = 0, dummy1 = 0;

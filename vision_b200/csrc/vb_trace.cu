@@ -39,7 +39,8 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
     const uint32_t s_row1 = s0 + 1024u, s_end = s0 + 1024u * VB_SM_STACK;
     uint32_t spa = s0 + 8u * threadIdx.x;
     uint2 l_stack[VB_LOCAL_STACK];
-    const uint32_t mg = vb_qf_magic_init();
+    const VbTrav V = vb_trav_init();
+    const uint32_t mg = V.mg;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     uint32_t nn = 0, nt = 0;
@@ -49,7 +50,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
     uint64_t idx = NO_RESULT;
     VbRay r{};
     float idx_ = 0.f, idy_ = 0.f, idz_ = 0.f, tmax = 0.f;
-    uint32_t oct_inv4 = 0;
+    uint32_t oct_inv = 0, lut_o = 0;
     VbHit hit{};
     uint2 G = make_uint2(0u, 0u), Tg = make_uint2(0u, 0u), Td = make_uint2(0u, 0u);
     bool occluded = false;
@@ -86,7 +87,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                     }
                     idx_ = vb_safe_rcp(r.dx); idy_ = vb_safe_rcp(r.dy); idz_ = vb_safe_rcp(r.dz);
                     uint32_t oct = (r.dx < 0.f ? 4u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 1u : 0u);
-                    oct_inv4 = (7u - oct) * 0x01010101u;
+                    oct_inv = 7u - oct; lut_o = V.lut + (oct_inv << 8);
                     tmax = r.tmax;
                     hit.inst = 0xffffffffu; hit.prim = 0xffffffffu; hit.u = 0.f; hit.v = 0.f; hit.t = 0.f;
                     occluded = false;
@@ -103,7 +104,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
         unsigned act;
         do {
             bool has_node = false;
-            if (active && !(Tg.y && Td.y)) {                  // both triangle slots full: a triangle round has to run first
+            if (active && !(Tg.y > 0xffu && Td.y > 0xffu)) {                  // both triangle slots full: a triangle round has to run first
                 if (G.y < 0x01000000u && spa >= s_row1) {     // fetch the next node group
                     spa -= 1024u;
                     if (spa < s_end) G = vb_lds64(spa);
@@ -127,16 +128,14 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                     }
                     spa += 1024u;
                 }
-                uint32_t slot = (bit - 24u) ^ (oct_inv4 & 0xffu);
+                uint32_t slot = (bit - 24u) ^ oct_inv;
                 uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot) & 0xffu);
-                uint4 n0, n1, n2, n3, n4;
-                vb_load_node(A.nodes, G.x + rel, n0, n1, n2, n3, n4);
                 if (COUNT) nn++;
-                uint32_t hm = vb_node_hits(n0, n1, n2, n3, n4, r, idx_, idy_, idz_, oct_inv4, tmax, mg);
-                G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
-                if (hm & 0x00ffffffu) {
-                    if (Tg.y) Td = Tg;                     // at most one of them was occupied (has_node)
-                    Tg = make_uint2(n1.y, hm & 0x00ffffffu);
+                uint2 T;
+                vb_node_step(A.nodes, G.x + rel, r, idx_, idy_, idz_, tmax, mg, lut_o, G, T);
+                if (T.y > 0xffu) {
+                    if (Tg.y > 0xffu) Td = Tg;             // at most one of them was occupied (has_node)
+                    Tg = T;
                 }
             }
             // ---- phase T: warp-voted triangle rounds ----
@@ -144,14 +143,12 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                 // A round runs when enough lanes hold pending triangles, or when no lane of the warp
                 // could do node work this iteration (everyone is blocked on its triangles). A lane that
                 // is blocked alone just idles through phase N: cheaper than a 1-lane triangle round.
-                bool tri = active && Tg.y;
+                bool tri = active && Tg.y > 0xffu;
                 unsigned tm = __ballot_sync(~0u, tri);
                 bool force = __ballot_sync(~0u, has_node) == 0u;
                 while (tm && (force || __popc(tm) >= TRI_THR)) {
                     if (tri) {
-                        uint32_t ti = 31u - __clz(Tg.y);
-                        Tg.y &= ~(1u << ti);
-                        const float4 *tp = A.tris + (size_t)(Tg.x + ti) * 3;
+                        const float4 *tp = A.tris + (size_t)vb_next_triangle(Tg) * 3;
                         float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
                         if (COUNT) nt++;
                         float t, u, v;
@@ -159,14 +156,14 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
                             if (ANY) { occluded = true; Tg.y = 0; Td.y = 0; G.y = 0; spa = s0 | (spa & 1023u); }
                             else vb_commit_hit(hit, tmax, a, b, t, u, v);
                         }
-                        if (!Tg.y) { Tg = Td; Td = make_uint2(0u, 0u); }
-                        tri = Tg.y != 0;
+                        if (Tg.y <= 0xffu) { Tg = Td; Td = make_uint2(0u, 0u); }
+                        tri = Tg.y > 0xffu;
                     }
                     tm = __ballot_sync(~0u, tri);
                 }
             }
             // ---- finished rays leave the loop; their results are stored at the next refill ----
-            if (active && G.y < 0x01000000u && spa < s_row1 && !Tg.y) active = false;
+            if (active && G.y < 0x01000000u && spa < s_row1 && Tg.y <= 0xffu) active = false;
             act = __ballot_sync(~0u, active);
         } while (act && (exhausted || __popc(act) >= REFILL_THR));
     }

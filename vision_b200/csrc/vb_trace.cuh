@@ -80,19 +80,32 @@ __device__ __forceinline__ uint32_t vb_byte(uint32_t w, int i) { return (w >> (8
 // The 0x64646464 operand must live in a REGISTER so that the SELECTOR is the PRMT immediate (SASS
 // PRMT has one non-register operand slot). ptxas constant-folds any "mov r, imm" and then
 // re-materialises one selector register per PRMT, so the value is read back from shared memory
-// once per kernel, which ptxas cannot fold. Every kernel that traverses calls vb_qf_magic_init() first.
+// once per kernel, which ptxas cannot fold. Every kernel that traverses calls vb_trav_init() first.
 #define VB_Q_BIAS 1024.f
-__device__ __forceinline__ uint32_t vb_qf_magic_init() {
+// Per-kernel traversal constants: the PRMT operand above and the shared address of the octant permutation table
+// perm[o][m] = the 8-bit mask m with bit s moved to bit s ^ o: box-test results come out in SLOT order (one bit per
+// child), one table look-up puts the internal children's bits into the ray's front-to-back order.
+struct VbTrav { uint32_t mg, lut; };
+__device__ __forceinline__ VbTrav vb_trav_init() {
     __shared__ uint32_t s_vb_magic;
+    __shared__ __align__(16) uint8_t s_vb_perm[8 * 256];
     if (threadIdx.x == 0) s_vb_magic = 0x64646464u;
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) {
+        uint32_t o = i >> 8, m = i & 255u, q = 0;
+#pragma unroll
+        for (uint32_t b = 0; b < 8; ++b) q |= ((m >> b) & 1u) << (b ^ o);
+        s_vb_perm[i] = (uint8_t)q;
+    }
     __syncthreads();
-    return *(volatile uint32_t *)&s_vb_magic;
+    VbTrav t;
+    t.mg = *(volatile uint32_t *)&s_vb_magic;
+    t.lut = (uint32_t)__cvta_generic_to_shared(s_vb_perm);
+    return t;
 }
-// a << (b & 31): SHF.L.W, so a packed byte field can be used as the shift amount without masking
-__device__ __forceinline__ uint32_t vb_shl_wrap(uint32_t a, uint32_t b) {
-    uint32_t d;
-    asm("shf.l.wrap.b32 %0, 0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));   // high word of (a:0) << n
-    return d;
+__device__ __forceinline__ uint32_t vb_lds8(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
 }
 template <int J>
 __device__ __forceinline__ float vb_qf(uint32_t w, uint32_t magic) {
@@ -104,25 +117,21 @@ __device__ __forceinline__ float vb_qf(uint32_t w, uint32_t magic) {
     return f;
 }
 
-// Tests the 8 quantised child boxes of one node; returns the 32-bit hit mask
-// (bits 31..24: internal children in octant order, bits 23..0: triangles).
-__device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
-                                                 const uint4 n4, const VbRay &r, float idx, float idy, float idz,
-                                                 uint32_t oct_inv4, float tmax, const uint32_t mg) {
+// Tests the 8 quantised child boxes of one node; returns the 8-bit hit mask in SLOT order (bit s = child in slot s).
+// Empty slots hold an inverted box and never hit. Per child: 6 decodes + 6 FMA + 4 min/max, then the SIGN of
+// cmax - cmin is shifted into the mask (one FADD on the fma pipe + one funnel shift) - no predicate, no per-child
+// bit-position decode; slots are visited 7..0 so that the first result ends up in bit 7.
+__device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n2, const uint4 n3, const uint4 n4, const VbRay &r,
+                                                 float idx, float idy, float idz, float tmax, const uint32_t mg) {
     float adjx = __uint_as_float((n0.w & 0xffu) << 23) * idx;
     float adjy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idy;
     float adjz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idz;
     float orx = fmaf(-VB_Q_BIAS, adjx, (__uint_as_float(n0.x) - r.ox) * idx);
     float ory = fmaf(-VB_Q_BIAS, adjy, (__uint_as_float(n0.y) - r.oy) * idy);
     float orz = fmaf(-VB_Q_BIAS, adjz, (__uint_as_float(n0.z) - r.oz) * idz);
-    uint32_t hitmask = 0;
+    uint32_t miss = 0;
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        uint32_t meta4 = h ? n1.w : n1.z;
-        uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-        uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
-        uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+    for (int h = 1; h >= 0; --h) {
         uint32_t qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
         uint32_t qhx = h ? n3.w : n3.z, qhy = h ? n4.y : n4.x, qhz = h ? n4.w : n4.z;
         uint32_t nx = idx < 0.f ? qhx : qlx, fx = idx < 0.f ? qlx : qhx;
@@ -135,13 +144,33 @@ __device__ __forceinline__ uint32_t vb_node_hits(const uint4 n0, const uint4 n1,
             float tnz = fmaf(vb_qf<J>(nz, mg), adjz, orz), tfz = fmaf(vb_qf<J>(fz, mg), adjz, orz);              \
             float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tmin));                                     \
             float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));                                       \
-            /* byte J of child_bits4 with one PRMT; the shift amount needs no masking: shl wraps (bit_index < 32) */ \
-            if (cmin <= cmax) hitmask |= vb_shl_wrap(__byte_perm(child_bits4, 0u, 0x4440 | J), bit_index4 >> (8 * J)); \
+            /* sign set <=> cmax < cmin (x - x = +0; a NaN difference reads as a hit: conservative) */   \
+            miss = __funnelshift_l(__float_as_uint(__fsub_rn(cmax, cmin)), miss, 1);                     \
         }
-        VB_CHILD(0) VB_CHILD(1) VB_CHILD(2) VB_CHILD(3)
+        VB_CHILD(3) VB_CHILD(2) VB_CHILD(1) VB_CHILD(0)
 #undef VB_CHILD
     }
-    return hitmask;
+    return ~miss & 0xffu;
+}
+
+// One node step shared by every traversal loop: fetch node `index`, test its children, return
+//   G  = (first internal child, hit internal children in front-to-back order << 24 | internal-slot mask)
+//   T  = (first triangle, hit leaf slots << 8 | occupied leaf slots)      (T.y <= 0xff: no triangle hit)
+// lut_o = VbTrav::lut + (7 - octant) * 256.
+__device__ __forceinline__ void vb_node_step(const uint4 *nodes, uint32_t index, const VbRay &r, float idx, float idy, float idz, float tmax,
+                                             uint32_t mg, uint32_t lut_o, uint2 &G, uint2 &T) {
+    uint4 n0, n1, n2, n3, n4;
+    vb_load_node(nodes, index, n0, n1, n2, n3, n4);
+    uint32_t hit8 = vb_node_hits(n0, n2, n3, n4, r, idx, idy, idz, tmax, mg);
+    uint32_t imask = n0.w >> 24;
+    G = make_uint2(n1.x, (vb_lds8(lut_o + (hit8 & imask)) << 24) | imask);
+    T = make_uint2(n1.y, ((hit8 & ~imask & n1.z) << 8) | (n1.z & 0xffu));      // & leaf slots: an empty slot can never report a triangle
+}
+// next pending triangle of T: clears its bit, returns its index (triangles of a node are stored in slot order)
+__device__ __forceinline__ uint32_t vb_next_triangle(uint2 &T) {
+    uint32_t bit = 1u << (31u - __clz(T.y));       // bits 8..15
+    T.y ^= bit;
+    return T.x + __popc(T.y & ((bit - 1u) >> 8));  // occupied leaf slots below it
 }
 
 // 64-bit shared-memory access by 32-bit shared address (no generic -> shared conversion at the access)
@@ -165,12 +194,12 @@ __device__ __forceinline__ void vb_commit_hit(VbHit &hit, float &tmax, float4 a,
 // s_stack points at this thread's column of the shared stack: entry e lives at s_stack[e * stride]
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool vb_traverse(const VbAccelView &A, VbRay r, VbHit &hit, uint2 *s_stack, int stride,
-                                            uint32_t &n_nodes, uint32_t &n_tris, const uint32_t mg) {
+                                            uint32_t &n_nodes, uint32_t &n_tris, const VbTrav V) {
     uint2 l_stack[VB_LOCAL_STACK];
     int sp = 0;
     float idx = vb_safe_rcp(r.dx), idy = vb_safe_rcp(r.dy), idz = vb_safe_rcp(r.dz);
     uint32_t oct = (r.dx < 0.f ? 4u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 1u : 0u);
-    uint32_t oct_inv4 = (7u - oct) * 0x01010101u;
+    const uint32_t oct_inv = 7u - oct, lut_o = V.lut + (oct_inv << 8);
     float tmax = r.tmax;
     hit.inst = 0xffffffffu; hit.prim = 0xffffffffu; hit.u = 0.f; hit.v = 0.f; hit.t = 0.f;
     if (!(r.tmin < r.tmax)) return false;
@@ -188,19 +217,13 @@ __device__ __forceinline__ bool vb_traverse(const VbAccelView &A, VbRay r, VbHit
                 else if (sp < VB_SM_STACK + VB_LOCAL_STACK) l_stack[sp - VB_SM_STACK] = G;
                 sp++;
             }
-            uint32_t slot = (bit - 24u) ^ (oct_inv4 & 0xffu);
+            uint32_t slot = (bit - 24u) ^ oct_inv;
             uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot) & 0xffu);
-            uint4 n0, n1, n2, n3, n4;
-            vb_load_node(A.nodes, G.x + rel, n0, n1, n2, n3, n4);
             if (COUNT) n_nodes++;
-            uint32_t hm = vb_node_hits(n0, n1, n2, n3, n4, r, idx, idy, idz, oct_inv4, tmax, mg);
-            G = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
-            Tg = make_uint2(n1.y, hm & 0x00ffffffu);
+            vb_node_step(A.nodes, G.x + rel, r, idx, idy, idz, tmax, V.mg, lut_o, G, Tg);
         }
-        while (Tg.y) {
-            uint32_t ti = 31u - __clz(Tg.y);
-            Tg.y &= ~(1u << ti);
-            const float4 *tp = A.tris + (size_t)(Tg.x + ti) * 3;
+        while (Tg.y > 0xffu) {
+            const float4 *tp = A.tris + (size_t)vb_next_triangle(Tg) * 3;
             float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
             if (COUNT) n_tris++;
             float t, u, v;
