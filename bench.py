@@ -44,6 +44,8 @@ def parse():
     p.add_argument("--no-pt", action="store_true")
     p.add_argument("--classroom-spp", type=int, default=16)
     p.add_argument("--no-classroom", action="store_true")
+    p.add_argument("--dragon-spp", type=int, default=16)
+    p.add_argument("--no-dragon", action="store_true")
     p.add_argument("--opt", action="append", default=[], help="library option key=value (vb_ctx_set_option), e.g. build.ploc=0")
     return p.parse_args()
 
@@ -136,7 +138,8 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
     """secondary measurement: the path tracer, sample-partitioned across ranks (rank g renders frames g, g+G, ...)
     with ONE NCCL all-reduce of the SUM film followed by the fused resolve. Returns samples/s and Mrays/s (whole
     job). which = "cbox": cbox-matte (BASELINE.json configs[0] geometry at 1024x1024, depth 5);
-    "classroom": BASELINE.json configs[4] (1920x1080, depth 16, env map + fog + glass/metal/substrate)."""
+    "classroom": BASELINE.json configs[4] (1920x1080, depth 16, env map + fog + glass/metal/substrate);
+    "dragon": configs[2] (cbox-dragon 1024x1024, depth 16, glass model with a scattering medium inside)."""
     import torch
     import torch.distributed as dist
     from vision_b200 import Context, scene_py, capi
@@ -144,6 +147,14 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
     if which == "cbox":
         sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", dict(scene_py.CBOX_MATTE_OVERRIDES, resolution=[a.pt_res, a.pt_res]))
         spp_rank, label = a.pt_spp, "cbox matte"
+    elif which == "dragon":
+        # config C3 through the C++ host layer (871 k-triangle OBJ: the Python twin's loader is for small files)
+        from vision_b200 import host_api
+        hp = host_api.HostPipeline(ROOT / "scenes" / "cbox_dragon" / "vision_scene.json")
+        hp.prepare_records()
+        sc = hp.records()
+        hp.close()
+        spp_rank, label = a.dragon_spp, "cbox-dragon (procedural stand-in mesh, glass + Skin1 medium inside)"
     else:
         sc = scene_py.build_scene(ROOT / "scenes" / "classroom" / "vision_scene.json", {})
         spp_rank, label = a.classroom_spp, "classroom (sky stand-in env map)"
@@ -331,6 +342,7 @@ def main():
     torch.cuda.empty_cache()
     pt = None if a.no_pt else pt_section(a, rank, world, local_rank, stream)
     pt_room = None if (a.no_pt or a.no_classroom) else pt_section(a, rank, world, local_rank, stream, "classroom")
+    pt_dragon = None if (a.no_pt or a.no_dragon) else pt_section(a, rank, world, local_rank, stream, "dragon")
 
     if rank == 0:
         peaks = {}
@@ -379,6 +391,8 @@ def main():
             line["path_tracer"] = pt
         if pt_room is not None:
             line["path_tracer_classroom"] = pt_room
+        if pt_dragon is not None:
+            line["path_tracer_cbox_dragon"] = pt_dragon
         if world == 1 and not a.no_cpu_baseline:
             cb = cpu_arm(a, mesh, rays, 0, 2, 1)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}

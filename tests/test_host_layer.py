@@ -87,7 +87,8 @@ def test_host_records_equal_python_twin_materials_and_mediums(name):
         assert want in names, want
 
 
-@pytest.mark.parametrize("rel", ["scenes/cbox/cbox_lights.json", "scenes/classroom/vision_scene.json", "scenes/cbox/cbox_sphere.json"])
+@pytest.mark.parametrize("rel", ["scenes/cbox/cbox_lights.json", "scenes/classroom/vision_scene.json", "scenes/cbox/cbox_sphere.json",
+                                 "scenes/cbox_dragon/vision_scene_small.json"])
 def test_host_records_equal_python_twin_lights_and_models(rel):
     """model shape (OBJ), point / spot / spherical lights, AliasTable2D, world diameter, Euler transforms, light order"""
     path = ROOT / rel
@@ -117,6 +118,10 @@ def test_host_records_equal_python_twin_lights_and_models(rel):
         env = a.lights[0]
         assert env.type == capi.VB_LIGHT_ENV and list(env.env_res) == [512, 256] and env.alias_size == 256 and env.cond_offset == 256
         assert env.params[0] > 300.0            # the scaled ground plane sets the world diameter
+    elif "dragon" in rel:
+        inst = max(a.instances, key=lambda i: len(a.meshes[i["mesh_id"]]["tri"]))
+        assert len(a.meshes[inst["mesh_id"]]["tri"]) == 2 * 48 * 47                 # tools/make_dragon_standin.py --width 48
+        assert inst["inside_medium"] == 0 and inst["outside_medium"] == capi.VB_INVALID_ID
     elif "sphere" in rel:
         assert a.camera.filter_type == capi.VB_FILTER_FITTED and a.camera.filter_table_offset == 2      # after the area light's 2 entries
         sph = a.meshes[a.instances[5]["mesh_id"]]

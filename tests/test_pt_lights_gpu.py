@@ -22,6 +22,8 @@ CASES = [
     ("cbox_principled", "scenes/cbox/cbox_principled.json", {"resolution": [160, 160], "spp": 8}, 0.03),
     ("classroom_clear", "scenes/classroom/vision_scene.json", {"resolution": [240, 136], "spp": 4, "process_mediums": False}, 0.05),
     ("classroom_fog", "scenes/classroom/vision_scene.json", {"resolution": [240, 136], "spp": 4}, 1e-5),
+    # config C3: glass model filled with the Skin1 medium, trs transform, thin-lens camera (dragon stand-in, small version)
+    ("cbox_dragon_small", "scenes/cbox_dragon/vision_scene_small.json", {"spp": 8}, 0.03),
 ]
 
 

@@ -6,7 +6,7 @@ extent in model space) on a W x H latitude-longitude grid, displaced along the r
 sinusoids (bumps from 1/3 down to 1/60 of the body), poles closed with fans. Counter-clockwise faces
 seen from outside, positions only (the loader derives normals), file order = prim_id order.
 
-  python tools/make_dragon_standin.py                 # scenes/cbox_dragon/dragon.obj        (W = 660: 871 200 triangles)
+  python tools/make_dragon_standin.py                 # scenes/cbox_dragon/dragon.obj        (W = 660: 869 880 triangles)
   python tools/make_dragon_standin.py --width 48      # scenes/cbox_dragon/dragon_small.obj  (W = 48:    4 512 triangles)
 `convert()` is what __graft_entry__.build() calls: writes whichever of the two files is missing.
 """

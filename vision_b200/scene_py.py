@@ -264,6 +264,29 @@ def euler_matrix(prm):
     return mat4_mul_f32(m, rotation_f32("y", prm.get("yaw", 0.0)))
 
 
+def trs_matrix(prm):
+    """TransformDesc 'trs' (node_desc.cpp:48-52): translation * axis-angle rotation (x, y, z, degrees) * scale;
+    arithmetic as vh_desc.cpp (float products of the axis components, double trigonometry, float entries)"""
+    T = np.eye(4, dtype=f32); T[:3, 3] = np.asarray(prm.get("t", [0, 0, 0]), f32)
+    S = np.eye(4, dtype=f32)
+    sv = np.asarray(prm.get("s", [1, 1, 1]), f32)
+    S[0, 0], S[1, 1], S[2, 2] = sv[0], sv[1], sv[2]
+    R = np.eye(4, dtype=f32)
+    r = [f32(x) for x in prm.get("r", [1, 0, 0, 0])]
+    if len(r) == 4 and r[3] != 0:
+        l = math.sqrt(float(r[0]) * float(r[0]) + float(r[1]) * float(r[1]) + float(r[2]) * float(r[2]))
+        ax, ay, az = (f32(float(r[i]) / l) for i in range(3))
+        ang = float(r[3]) * K_DEG
+        c, sn = math.cos(ang), math.sin(ang)
+        k = 1 - c
+        p = lambda u, v: float(f32(u * v))
+        # R[row, col]; the host's column-major R[4 * col + row]
+        R[0, 0] = f32(c + p(ax, ax) * k); R[1, 0] = f32(p(ay, ax) * k + float(az) * sn); R[2, 0] = f32(p(az, ax) * k - float(ay) * sn)
+        R[0, 1] = f32(p(ax, ay) * k - float(az) * sn); R[1, 1] = f32(c + p(ay, ay) * k); R[2, 1] = f32(p(az, ay) * k + float(ax) * sn)
+        R[0, 2] = f32(p(ax, az) * k + float(ay) * sn); R[1, 2] = f32(p(ay, az) * k - float(ax) * sn); R[2, 2] = f32(c + p(az, az) * k)
+    return mat4_mul_f32(mat4_mul_f32(T, R), S)
+
+
 def transform_matrix(tr):
     """row-major numpy 4x4 from a transform block (matrix4x4 rows are columns; look_at; Euler)"""
     if not tr:
@@ -275,6 +298,8 @@ def transform_matrix(tr):
         return look_at(prm["position"], prm["target_pos"], prm.get("up", [0, 1, 0]))
     if t == "Euler":
         return euler_matrix(prm).astype(np.float64)
+    if t == "trs":
+        return trs_matrix(prm).astype(np.float64)
     raise NotImplementedError(t)
 
 
