@@ -59,4 +59,4 @@ def test_image_matches_oracle(vbctx, oracle, name, min_mean):
         vbctx.render_frames(0, sc.spp, 1, capi.VB_ACCUM_LERP)
         assert np.array_equal(g, vbctx.film_download(capi.VB_FILM_ACCUM))
     finally:
-        vbctx.set_option("pt.max_paths", 1 << 22)
+        vbctx.set_option("pt.max_paths", 1 << 25)

@@ -83,7 +83,7 @@ struct vb_ctx {
     int opt_pt_schedule = 0;                 // 0 = wavefront (default), 1 = megakernel
     int opt_pt_sort_material = 1;            // wavefront: order shading entries by material
     int opt_pt_count_work = 0;               // wavefront: instrumented traversal (nodes / triangles per ray), never timed
-    int64_t opt_pt_max_paths = 1 << 22;      // wavefront: paths in flight per batch
+    int64_t opt_pt_max_paths = 1 << 25;      // wavefront: paths in flight per batch
     void *sort_buf = nullptr; size_t sort_bytes = 0;
     vb_pt_state *pt = nullptr;
 

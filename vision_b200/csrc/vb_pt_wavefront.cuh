@@ -83,7 +83,10 @@ __global__ void __launch_bounds__(256) k_wf_material_keys(PtScene S, uint32_t n,
 
 // one Li vertex per queue entry; entry i of the launch is queue position order[i] (low word)
 template <bool PRINCIPLED>
-__global__ void __launch_bounds__(128, 4) k_wf_shade(PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
+#ifndef VB_SHADE_MIN_BLOCKS
+#define VB_SHADE_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(128, VB_SHADE_MIN_BLOCKS) k_wf_shade(PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
                                                   WfState st, WfQueue Qout, WfQueue Qsh, float4 *sh_pend, WfSortBox B, WfCounters *cnt) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
