@@ -42,7 +42,9 @@ VB_API const char *vb_last_error(vb_ctx *ctx);           /* ctx may be NULL: las
 VB_API int vb_ctx_set_stream(vb_ctx *ctx, void *cuda_stream);
 VB_API int vb_ctx_synchronize(vb_ctx *ctx);
 /* tuning knobs (defaults are the tuned values): "trace.refill_thr", "trace.tri_thr", "trace.blocks_per_sm",
- * "trace.sort_rays", "trace.sort_min_rays", "trace.sort_oct_shift", "build.max_leaf" (fixed at 1); path tracer: "pt.schedule" (0 = wavefront pipeline,
+ * "trace.sort_rays", "trace.sort_min_rays", "trace.sort_oct_shift", "trace.host_chunks" (host-buffer calls are cut into
+ * this many ray ranges, default 4, and copy-in / trace / copy-out of consecutive ranges overlap on three streams),
+ * "trace.host_chunk_min_rays", "build.max_leaf" (fixed at 1); path tracer: "pt.schedule" (0 = wavefront pipeline,
  * default; 1 = single megakernel - same results), "pt.max_paths" (wavefront paths in flight) */
 VB_API int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value);
 /* device time (ms, CUDA events on the launching stream) and launch count of the kernels this

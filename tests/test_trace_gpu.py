@@ -133,6 +133,39 @@ def test_device_resident_rays(vbctx, oracle):
     assert dev["t"].cpu().numpy().tobytes() == host["t"].tobytes()
 
 
+def test_host_buffers_pipelined_in_ranges(vbctx, oracle):
+    """host-buffer calls are cut into ray ranges (copy-in / trace / copy-out overlapped): same results as one range
+    and as device-resident rays, ragged last range included"""
+    import torch
+    mesh = synth.synth_mesh(20000, seed=61)
+    _build_soup(vbctx, mesh)
+    n = 300_001
+    rays = synth.synth_rays(n, seed=62, seed_any=63)
+    any_rays = dict(rays, tmax=rays["tmax_any"])
+    vbctx.set_option("trace.host_chunks", 1)
+    one = vbctx.trace_closest(rays); one_any = vbctx.trace_any(any_rays)
+    try:
+        vbctx.set_option("trace.host_chunk_min_rays", 1024)
+        for chunks in (3, 16):
+            vbctx.set_option("trace.host_chunks", chunks)
+            got = vbctx.trace_closest(rays)
+            for f in ("inst", "prim", "t", "u", "v"):
+                assert got[f].tobytes() == one[f].tobytes(), (chunks, f)
+            assert np.array_equal(vbctx.trace_any(any_rays), one_any)
+        # device rays -> host results and host rays -> device results take the same path
+        drays = {k: torch.from_numpy(v).cuda() for k, v in rays.items()}
+        dev = vbctx.trace_closest(drays)
+        vbctx.synchronize()
+        assert dev["prim"].cpu().numpy().view(np.uint32).tobytes() == one["prim"].tobytes()
+    finally:
+        vbctx.set_option("trace.host_chunks", 4)
+        vbctx.set_option("trace.host_chunk_min_rays", 1 << 20)
+    acc = oracle.accel()
+    acc.add_soup(mesh)
+    acc.build(oracle.hw_threads())
+    _compare_closest(one, acc.trace_closest(rays, threads=oracle.hw_threads()))
+
+
 def test_errors_are_reported(vbctx):
     from vision_b200 import VbError
     with pytest.raises(VbError):

@@ -5,6 +5,17 @@
 
 static std::string g_create_err;
 
+int vb_ctx::ensure_copy_streams() {
+    if (copy_in) return VB_OK;
+    vb_ctx *ctx = this;
+    VB_CUDA(cudaStreamCreateWithFlags(&copy_in, cudaStreamNonBlocking));
+    VB_CUDA(cudaStreamCreateWithFlags(&copy_out, cudaStreamNonBlocking));
+    for (int i = 0; i < VB_MAX_HOST_CHUNKS; ++i) {
+        VB_CUDA(cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming));
+        VB_CUDA(cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming));
+    }
+    return VB_OK;
+}
 int vb_ctx::ensure_stage(size_t bytes) {
     if (bytes <= stage_bytes) return VB_OK;
     vb_ctx *ctx = this;
@@ -89,6 +100,10 @@ int vb_ctx_destroy(vb_ctx *ctx) {
     cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
     cudaFree(ctx->stage); cudaFree(ctx->sort_buf);
     vb_pt_destroy(ctx);
+    if (ctx->copy_in) {
+        cudaStreamDestroy(ctx->copy_in); cudaStreamDestroy(ctx->copy_out);
+        for (int i = 0; i < VB_MAX_HOST_CHUNKS; ++i) { cudaEventDestroy(ctx->ev_in[i]); cudaEventDestroy(ctx->ev_out[i]); }
+    }
     cudaStreamDestroy(ctx->own_stream);
     delete ctx;
     return VB_OK;
@@ -122,6 +137,8 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     else if (k == "pt.sort_material") ctx->opt_pt_sort_material = value != 0 ? 1 : 0;
     else if (k == "pt.count_work") ctx->opt_pt_count_work = value != 0 ? 1 : 0;
     else if (k == "pt.max_paths") ctx->opt_pt_max_paths = std::max<int64_t>(1, (int64_t)value);
+    else if (k == "trace.host_chunks") ctx->opt_host_chunks = std::min(VB_MAX_HOST_CHUNKS, std::max(1, (int)value));
+    else if (k == "trace.host_chunk_min_rays") ctx->opt_host_chunk_min_rays = std::max(1024, (int)value);
     else if (k == "trace.blocks_per_sm") ctx->opt_blocks_per_sm = std::max(1, (int)value);
     else return ctx->fail(VB_ERR_INVALID, "vb_ctx_set_option: unknown key " + k);
     return VB_OK;

@@ -44,6 +44,8 @@ struct __align__(32) vb_wide_node {
 };
 static_assert(sizeof(vb_wide_node) == 16 * VB_NODE_U4, "wide node slot must be 96 bytes");
 
+#define VB_MAX_HOST_CHUNKS 16
+
 struct vb_prof_slot { double ms = 0; uint64_t launches = 0; };
 
 struct vb_accel {
@@ -85,6 +87,11 @@ struct vb_ctx {
     int opt_pt_count_work = 0;               // wavefront: instrumented traversal (nodes / triangles per ray), never timed
     int64_t opt_pt_max_paths = 1 << 25;      // wavefront: paths in flight per batch
     void *sort_buf = nullptr; size_t sort_bytes = 0;
+    // host-buffer calls of vb_trace_*: ray ranges pipelined over copy-in / compute / copy-out streams (vb_trace.cu run_trace)
+    int opt_host_chunks = 4, opt_host_chunk_min_rays = 1 << 20;
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
+    cudaEvent_t ev_in[VB_MAX_HOST_CHUNKS] = {}, ev_out[VB_MAX_HOST_CHUNKS] = {};
+    int ensure_copy_streams();
     vb_pt_state *pt = nullptr;
 
     int fail(int code, const std::string &msg) { err = msg; return code; }

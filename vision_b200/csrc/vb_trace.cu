@@ -190,6 +190,9 @@ __global__ void __launch_bounds__(256) k_ray_keys(RaysDev R, uint32_t n, float3 
     aos[2 * (size_t)i] = make_float4(ox, oy, oz, __ldg(R.tmin + i));
     aos[2 * (size_t)i + 1] = make_float4(dx, dy, dz, __ldg(R.tmax + i));
 }
+// Host buffers: the call is cut into `trace.host_chunks` ray ranges and pipelined over three streams - range k+1 is
+// copied in (copy engine 1) while range k is sorted and traced (SMs) and range k-1 is copied out (copy engine 2) - so
+// the call costs about max(H2D, trace) instead of H2D + trace + D2H. Device buffers: one range, no extra streams.
 int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out, uint8_t *occ, vb_mem occ_mem,
               bool any, uint64_t *cnt_nodes, uint64_t *cnt_tris) {
     if (!ctx) return VB_ERR_INVALID;
@@ -204,21 +207,25 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
     bool rays_host = rays->mem == VB_MEM_HOST;
     bool out_host = any ? (occ_mem == VB_MEM_HOST) : (out->mem == VB_MEM_HOST);
 
-    // staging layout: [8 ray arrays][hit arrays or occlusion bytes][2 counters]
+    // ranges: multiples of 1024 rays so that every sub-array keeps its alignment
+    int C = 1;
+    if ((rays_host || out_host) && ctx->opt_host_chunks > 1 && n >= (uint64_t)ctx->opt_host_chunk_min_rays * 2)
+        C = (int)std::min<uint64_t>((uint64_t)std::min(ctx->opt_host_chunks, VB_MAX_HOST_CHUNKS), n / (uint64_t)ctx->opt_host_chunk_min_rays);
+    const uint64_t per = C > 1 ? (((n + C - 1) / C + 1023) & ~1023ull) : n;
+    if (C > 1) { int rc = ctx->ensure_copy_streams(); if (rc) return rc; }
+    cudaStream_t s_in = C > 1 ? ctx->copy_in : st, s_out = C > 1 ? ctx->copy_out : st;
+
+    // staging layout: [8 ray arrays][hit arrays or occlusion bytes][counters: nodes, tris, pad, pad, next_ray per range]
     size_t ray_bytes = rays_host ? 8 * n * sizeof(float) : 0;
     size_t out_bytes = out_host ? (any ? ((n + 15) & ~15ull) : 5 * n * 4) : 0;
-    size_t need = ray_bytes + out_bytes + 128;
+    size_t need = ray_bytes + out_bytes + 128 + 8 * (size_t)VB_MAX_HOST_CHUNKS;
     int rc = ctx->ensure_stage(need);
     if (rc) return rc;
     char *base = (char *)ctx->stage;
     RaysDev R{rays->ox, rays->oy, rays->oz, rays->tmin, rays->dx, rays->dy, rays->dz, rays->tmax};
-    if (rays_host) {
-        float *d = (float *)base;
-        const float *src[8] = {rays->ox, rays->oy, rays->oz, rays->tmin, rays->dx, rays->dy, rays->dz, rays->tmax};
-        for (int k = 0; k < 8; ++k)
-            VB_CUDA(cudaMemcpyAsync(d + k * n, src[k], n * sizeof(float), cudaMemcpyHostToDevice, st));
-        R = RaysDev{d, d + n, d + 2 * n, d + 3 * n, d + 4 * n, d + 5 * n, d + 6 * n, d + 7 * n};
-    }
+    const float *h_src[8] = {rays->ox, rays->oy, rays->oz, rays->tmin, rays->dx, rays->dy, rays->dz, rays->tmax};
+    float *d_rays = (float *)base;
+    if (rays_host) R = RaysDev{d_rays, d_rays + n, d_rays + 2 * n, d_rays + 3 * n, d_rays + 4 * n, d_rays + 5 * n, d_rays + 6 * n, d_rays + 7 * n};
     HitsDev H{};
     uint8_t *d_occ = occ;
     if (any) { if (out_host) d_occ = (uint8_t *)(base + ray_bytes); }
@@ -231,74 +238,96 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
     }
     unsigned long long *d_cnt = (unsigned long long *)(base + ray_bytes + out_bytes);
     d_cnt = (unsigned long long *)(((uintptr_t)d_cnt + 15) & ~(uintptr_t)15);
-    VB_CUDA(cudaMemsetAsync(d_cnt, 0, 32, st));       // [nodes, tris, next_ray, pad]
-    unsigned long long *d_next = d_cnt + 2;
+    VB_CUDA(cudaMemsetAsync(d_cnt, 0, 32 + 8 * (size_t)VB_MAX_HOST_CHUNKS, st));
+    if (C > 1) {        // the copy streams start after whatever the caller queued on the context's stream
+        VB_CUDA(cudaEventRecord(ctx->ev_in[0], st));
+        VB_CUDA(cudaStreamWaitEvent(s_in, ctx->ev_in[0], 0));
+        VB_CUDA(cudaStreamWaitEvent(s_out, ctx->ev_in[0], 0));
+    }
 
     VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
-    // persistent grid: a multiple of the SM count, never more threads than rays
-    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctx->opt_blocks_per_sm, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
-    const float4 *RS = nullptr; const uint32_t *perm = nullptr;
-    bool do_sort = ctx->opt_sort_rays && n >= (uint64_t)ctx->opt_sort_min_rays && n < (1ull << 32);
-    uint64_t launches = 1;
-    size_t cub_bytes = 0;
-    uint32_t *k0 = nullptr, *k1 = nullptr, *v0 = nullptr, *v1 = nullptr; float4 *d_aos = nullptr; void *cub_tmp = nullptr;
-    if (do_sort) {
-        cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
-        VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk, dv, (int)n, 0, 24, st));
-        size_t nb = ((n * 4 + 255) & ~255ull);
-        size_t total = 4 * nb + 32 * n + cub_bytes + 256;
-        if (total > ctx->sort_bytes) {
-            if (ctx->sort_buf) cudaFree(ctx->sort_buf);
-            ctx->sort_buf = nullptr; ctx->sort_bytes = 0;
-            VB_CUDA(cudaMalloc(&ctx->sort_buf, total));
-            ctx->sort_bytes = total;
-        }
-        char *sb = (char *)ctx->sort_buf;
-        k0 = (uint32_t *)sb; k1 = (uint32_t *)(sb + nb); v0 = (uint32_t *)(sb + 2 * nb); v1 = (uint32_t *)(sb + 3 * nb);
-        d_aos = (float4 *)(sb + 4 * nb); cub_tmp = sb + 4 * nb + 32 * n;
-        cub_tmp = (void *)(((uintptr_t)cub_tmp + 255) & ~(uintptr_t)255);
-    }
+    uint64_t launches = 0;
     ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
-    if (do_sort) {
-        float3 lo = make_float3(ctx->sort_lo[0], ctx->sort_lo[1], ctx->sort_lo[2]);
-        float3 ie = make_float3(1.f / fmaxf(ctx->sort_hi[0] - ctx->sort_lo[0], 1e-30f), 1.f / fmaxf(ctx->sort_hi[1] - ctx->sort_lo[1], 1e-30f),
-                                1.f / fmaxf(ctx->sort_hi[2] - ctx->sort_lo[2], 1e-30f));
-        unsigned g2 = (unsigned)((n + 255) / 256);
-        k_ray_keys<<<g2, 256, 0, st>>>(R, (uint32_t)n, lo, ie, k0, v0, d_aos, (uint32_t)ctx->opt_sort_oct_shift);
-        cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
-        cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)n, 0, 24, st);
-        if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }
-        perm = dv.Current();
-        RS = d_aos;                 // k_trace gathers ray perm[i] itself: no separate reorder pass
-        launches += 5;
-    }
-    if (any) {
-        if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
-        else k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
-    } else {
-        if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
-        else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, d_occ, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+    for (int c = 0; c < C; ++c) {
+        const uint64_t r0 = (uint64_t)c * per;
+        if (r0 >= n) break;
+        const uint64_t m = std::min(per, n - r0);
+        if (rays_host) {
+            for (int k = 0; k < 8; ++k)
+                VB_CUDA(cudaMemcpyAsync(d_rays + k * n + r0, h_src[k] + r0, m * sizeof(float), cudaMemcpyHostToDevice, s_in));
+            if (C > 1) { VB_CUDA(cudaEventRecord(ctx->ev_in[c], s_in)); VB_CUDA(cudaStreamWaitEvent(st, ctx->ev_in[c], 0)); }
+        }
+        RaysDev Rc{R.ox + r0, R.oy + r0, R.oz + r0, R.tmin + r0, R.dx + r0, R.dy + r0, R.dz + r0, R.tmax + r0};
+        HitsDev Hc{};
+        if (!any) Hc = HitsDev{H.inst + r0, H.prim + r0, H.u + r0, H.v + r0, H.t + r0};
+        uint8_t *occ_c = any ? d_occ + r0 : nullptr;
+        unsigned long long *d_next = d_cnt + 4 + c;
+
+        // persistent grid: a multiple of the SM count, never more threads than rays
+        unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctx->opt_blocks_per_sm, (m + TRACE_BLOCK - 1) / TRACE_BLOCK);
+        const float4 *RS = nullptr; const uint32_t *perm = nullptr;
+        bool do_sort = ctx->opt_sort_rays && m >= (uint64_t)ctx->opt_sort_min_rays && m < (1ull << 32);
+        launches += 1;
+        if (do_sort) {
+            size_t cub_bytes = 0;
+            cub::DoubleBuffer<uint32_t> dk0(nullptr, nullptr), dv0(nullptr, nullptr);
+            VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk0, dv0, (int)m, 0, 24, st));
+            size_t nb = ((m * 4 + 255) & ~255ull);
+            size_t total = 4 * nb + 32 * m + cub_bytes + 256;
+            if (total > ctx->sort_bytes) {
+                VB_CUDA(cudaStreamSynchronize(st));            // an earlier range may still be using the old buffer
+                if (ctx->sort_buf) cudaFree(ctx->sort_buf);
+                ctx->sort_buf = nullptr; ctx->sort_bytes = 0;
+                VB_CUDA(cudaMalloc(&ctx->sort_buf, total));
+                ctx->sort_bytes = total;
+            }
+            char *sb = (char *)ctx->sort_buf;
+            uint32_t *k0 = (uint32_t *)sb, *k1 = (uint32_t *)(sb + nb), *v0 = (uint32_t *)(sb + 2 * nb), *v1 = (uint32_t *)(sb + 3 * nb);
+            float4 *d_aos = (float4 *)(sb + 4 * nb);
+            void *cub_tmp = (void *)(((uintptr_t)(sb + 4 * nb + 32 * m) + 255) & ~(uintptr_t)255);
+            float3 lo = make_float3(ctx->sort_lo[0], ctx->sort_lo[1], ctx->sort_lo[2]);
+            float3 ie = make_float3(1.f / fmaxf(ctx->sort_hi[0] - ctx->sort_lo[0], 1e-30f), 1.f / fmaxf(ctx->sort_hi[1] - ctx->sort_lo[1], 1e-30f),
+                                    1.f / fmaxf(ctx->sort_hi[2] - ctx->sort_lo[2], 1e-30f));
+            unsigned g2 = (unsigned)((m + 255) / 256);
+            k_ray_keys<<<g2, 256, 0, st>>>(Rc, (uint32_t)m, lo, ie, k0, v0, d_aos, (uint32_t)ctx->opt_sort_oct_shift);
+            cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
+            cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)m, 0, 24, st);
+            if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }
+            perm = dv.Current();
+            RS = d_aos;                 // k_trace gathers ray perm[i] itself: no separate reorder pass
+            launches += 5;
+        }
+        if (any) {
+            if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+            else k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+        } else {
+            if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+            else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+        }
+        if (out_host) {
+            if (C > 1) { VB_CUDA(cudaEventRecord(ctx->ev_out[c], st)); VB_CUDA(cudaStreamWaitEvent(s_out, ctx->ev_out[c], 0)); }
+            if (any) VB_CUDA(cudaMemcpyAsync(occ + r0, d_occ + r0, m, cudaMemcpyDeviceToHost, s_out));
+            else {
+                void *dst[5] = {out->inst + r0, out->prim + r0, out->u + r0, out->v + r0, out->t + r0};
+                const void *srcp[5] = {Hc.inst, Hc.prim, Hc.u, Hc.v, Hc.t};
+                for (int k = 0; k < 5; ++k) VB_CUDA(cudaMemcpyAsync(dst[k], srcp[k], m * 4, cudaMemcpyDeviceToHost, s_out));
+            }
+        }
     }
     ctx->cur_launches = launches;
     ctx->prof_end();
     VB_CHECK_LAUNCH();
 
-    if (out_host) {
-        if (any) VB_CUDA(cudaMemcpyAsync(occ, d_occ, n, cudaMemcpyDeviceToHost, st));
-        else {
-            void *dst[5] = {out->inst, out->prim, out->u, out->v, out->t};
-            const void *srcp[5] = {H.inst, H.prim, H.u, H.v, H.t};
-            for (int k = 0; k < 5; ++k) VB_CUDA(cudaMemcpyAsync(dst[k], srcp[k], n * 4, cudaMemcpyDeviceToHost, st));
-        }
-    }
     if (count) {
         unsigned long long hc[2];
         VB_CUDA(cudaMemcpyAsync(hc, d_cnt, 16, cudaMemcpyDeviceToHost, st));
         VB_CUDA(cudaStreamSynchronize(st));
         if (cnt_nodes) *cnt_nodes = hc[0];
         if (cnt_tris) *cnt_tris = hc[1];
-    } else if (out_host || rays_host) {
-        VB_CUDA(cudaStreamSynchronize(st));   // host buffers are valid on return
+    }
+    if (out_host || rays_host) {          // host buffers are valid (and reusable) on return
+        if (C > 1) { VB_CUDA(cudaStreamSynchronize(s_in)); VB_CUDA(cudaStreamSynchronize(s_out)); }
+        VB_CUDA(cudaStreamSynchronize(st));
     }
     return VB_OK;
 }
