@@ -127,6 +127,17 @@ def cpu_arm(a, mesh, rays, threads: int, steps: int, warmup: int):
 
 
 
+def measured_peak():
+    """(HBM GB/s, where it came from): MEASURED_PEAKS.json hbm_gbs, else the profiling recipe's fallback"""
+    pk = ROOT / "MEASURED_PEAKS.json"
+    if pk.exists():
+        try:
+            return float(json.loads(pk.read_text())["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
+        except Exception:
+            pass
+    return 6650.0, "fallback 6650 GB/s (B200_PROFILING.md)"
+
+
 class _DevPtr:
     """wraps a raw device pointer as a CUDA-array-interface object so torch can all-reduce it in place"""
 
@@ -162,7 +173,7 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
     for kv in a.opt:
         ctx.set_option(kv.split("=")[0], float(kv.split("=")[1]))
     ctx.set_stream(stream.cuda_stream)
-    ctx.upload_scene(sc)
+    build = ctx.upload_scene(sc)
     w, h = sc.resolution
     film = torch.as_tensor(_DevPtr(ctx.film_device_ptr(capi.VB_FILM_ACCUM), w * h * 4), device=torch.device("cuda", local_rank))
 
@@ -195,9 +206,33 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
     else:
         rays = float(t[1])
     out_mean = float(torch.as_tensor(_DevPtr(ctx.film_device_ptr(capi.VB_FILM_OUTPUT), w * h * 4), device=torch.device("cuda", local_rank)).mean())
-    ctx.close()
     samples = w * h * spp_rank * world
-    return {"scene": f"{label} {w}x{h}, {spp_rank} spp per GPU x {world} GPU(s), max depth {sc.params.max_depth}", "ms": ms,
+    roof = None
+    if rank == 0:
+        # bytes_per_sample = sum over traced rays of (32 + 20 | 1 + 80 nodes + 48 triangles) + 228 B per shaded
+        # vertex + 16 B film write; node / triangle counts from ONE instrumented frame (never timed), per-sample figures
+        # from this rank's counters. Denominators: HBM copy peak and the L2 read bandwidth measured here (64 MB resident set).
+        ctx.set_option("pt.count_work", 1)
+        ctx.film_clear(); ctx.render_frames(0, 1, 1, capi.VB_ACCUM_SUM); ctx.synchronize()
+        s1, wk = ctx.render_stats(), ctx.render_work()
+        ctx.set_option("pt.count_work", 0)
+        n1 = w * h
+        b_closest = s1["closest"] * (32 + 20) + 80 * wk["closest_nodes"] + 48 * wk["closest_tris"]
+        b_any = s1["any"] * (32 + 1) + 80 * wk["any_nodes"] + 48 * wk["any_tris"]
+        bytes_per_sample = (b_closest + b_any + 228 * s1["vertices"]) / n1 + 16
+        sps_gpu = samples / world / (ms * 1e-3)
+        achieved = bytes_per_sample * sps_gpu / 1e9
+        l2_gbs = ctx.probe_read_bandwidth(64 << 20, 20)
+        hbm_gbs, _ = measured_peak()
+        bvh_bytes = int(build["node_bytes"] + build["tri_bytes"])
+        roof = {"bytes_per_sample": bytes_per_sample, "achieved": achieved, "unit": "GB/s (per GPU, algorithmic)",
+                "closest_nodes_per_ray": wk["closest_nodes"] / max(s1["closest"], 1), "closest_tris_per_ray": wk["closest_tris"] / max(s1["closest"], 1),
+                "any_nodes_per_ray": wk["any_nodes"] / max(s1["any"], 1), "any_tris_per_ray": wk["any_tris"] / max(s1["any"], 1),
+                "vertices_per_sample": s1["vertices"] / n1, "bvh_bytes": bvh_bytes,
+                "bound": "l2" if bvh_bytes < (100 << 20) else "hbm", "l2_read_peak": l2_gbs, "hbm_peak": hbm_gbs,
+                "frac_l2": achieved / l2_gbs, "frac_hbm": achieved / hbm_gbs}
+    ctx.close()
+    return {"roofline": roof, "scene": f"{label} {w}x{h}, {spp_rank} spp per GPU x {world} GPU(s), max depth {sc.params.max_depth}", "ms": ms,
             "samples_per_s": samples / (ms * 1e-3), "mrays_per_s": rays / (ms * 1e-3) / 1e6, "rays_per_sample": rays / samples,
             "film_allreduce": "torch.distributed NCCL sum over the float4 film" if world > 1 else "none (1 GPU)",
             "output_mean": out_mean}
@@ -345,13 +380,7 @@ def main():
     pt_dragon = None if (a.no_pt or a.no_dragon) else pt_section(a, rank, world, local_rank, stream, "dragon")
 
     if rank == 0:
-        peaks = {}
-        pk = ROOT / "MEASURED_PEAKS.json"
-        peak_src = "fallback 6650 GB/s (B200_PROFILING.md)"
-        peak = 6650.0
-        if pk.exists():
-            peaks = json.loads(pk.read_text())
-            peak = float(peaks.get("hbm_gbs", peak)); peak_src = "MEASURED_PEAKS.json hbm_gbs (burst copy)"
+        peak, peak_src = measured_peak()
         npr, tpr = nodes_c / n, tris_c / n
         bytes_per_ray = 32 + 20 + 80 * npr + 48 * tpr
         dur_ms = k_closest_ms / a.steps          # one trace_closest call (sort + traverse) per step

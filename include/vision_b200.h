@@ -52,6 +52,10 @@ VB_API int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value);
  * "path_trace" (megakernel) | "pt_generate" | "pt_shade" | "pt_shadow_resolve" | "pt_film" (wavefront) |
  * "bvh_build" | "film" | "all" */
 VB_API int vb_profile_reset(vb_ctx *ctx);
+/* diagnostics: read bandwidth (GB/s) of `reps` grid-stride 128-bit read passes over a zero-filled buffer of `bytes`
+ * after 3 warm passes - L2 read bandwidth when the buffer fits L2 (64 MB), HBM read bandwidth when it is much larger.
+ * The denominators of the path tracer's roofline ("builder measures with a 64 MB ... kernel") */
+VB_API int vb_probe_read_bandwidth(vb_ctx *ctx, uint64_t bytes, int reps, double *gbs);
 VB_API int vb_profile_get(vb_ctx *ctx, const char *name, double *ms, uint64_t *launches);
 
 /* ---- geometry: replaces Geometry::upload + Geometry::build_accel -------------------------- */

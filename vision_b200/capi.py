@@ -70,6 +70,7 @@ def load_library() -> C.CDLL:
         "vb_ctx_synchronize": [vp],
         "vb_ctx_set_option": [vp, C.c_char_p, C.c_double],
         "vb_profile_reset": [vp],
+        "vb_probe_read_bandwidth": [vp, C.c_uint64, C.c_int, C.POINTER(C.c_double)],
         "vb_profile_get": [vp, C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_uint64)],
         "vb_mesh_upload": [vp, vp, vp, vp, C.c_uint32, vp, C.c_uint32, _u32p],
         "vb_mesh_upload_soup": [vp, vp, C.c_int, C.c_uint64, _u32p],
@@ -150,6 +151,11 @@ class Context:
 
     def profile_reset(self):
         self._check(self.lib.vb_profile_reset(self.h), "vb_profile_reset")
+
+    def probe_read_bandwidth(self, nbytes: int, reps: int = 20) -> float:
+        g = C.c_double()
+        self._check(self.lib.vb_probe_read_bandwidth(self.h, nbytes, reps, C.byref(g)), "vb_probe_read_bandwidth")
+        return g.value
 
     def profile_get(self, name: str):
         ms, n = C.c_double(), C.c_uint64()

@@ -143,6 +143,43 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     else return ctx->fail(VB_ERR_INVALID, "vb_ctx_set_option: unknown key " + k);
     return VB_OK;
 }
+// ---- read-bandwidth probe: the L2 (or HBM) denominator of the path tracer's roofline ----
+namespace {
+__global__ void __launch_bounds__(256) k_probe_read(const uint4 *__restrict__ p, uint64_t n16, uint32_t *sink) {
+    uint32_t acc = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint4 v = __ldg(p + i);
+        acc ^= v.x ^ v.y ^ v.z ^ v.w;
+    }
+    if (acc == 0x9e3779b9u) *sink = acc;       // never true for the zero-filled buffer: keeps the loads alive
+}
+}  // namespace
+int vb_probe_read_bandwidth(vb_ctx *ctx, uint64_t bytes, int reps, double *gbs) {
+    if (!ctx || !gbs || bytes < 4096 || reps < 1) return VB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    void *buf = nullptr; uint32_t *sink = nullptr;
+    VB_CUDA(cudaMalloc(&buf, bytes));
+    if (cudaMalloc(&sink, 4) != cudaSuccess) { cudaFree(buf); return ctx->fail(VB_ERR_CUDA, "vb_probe_read_bandwidth: cudaMalloc"); }
+    cudaMemsetAsync(buf, 0, bytes, st);
+    const uint64_t n16 = bytes / 16;
+    const unsigned grid = (unsigned)ctx->sm_count * 8;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    for (int w = 0; w < 3; ++w) k_probe_read<<<grid, 256, 0, st>>>((const uint4 *)buf, n16, sink);     // warm: the buffer becomes L2-resident if it fits
+    cudaEventRecord(e0, st);
+    for (int r = 0; r < reps; ++r) k_probe_read<<<grid, 256, 0, st>>>((const uint4 *)buf, n16, sink);
+    cudaEventRecord(e1, st);
+    cudaError_t ce = cudaStreamSynchronize(st);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(buf); cudaFree(sink);
+    if (ce != cudaSuccess) return ctx->fail(VB_ERR_CUDA, std::string("vb_probe_read_bandwidth: ") + cudaGetErrorString(ce));
+    *gbs = (double)n16 * 16.0 * reps / (ms * 1e-3) / 1e9;
+    return VB_OK;
+}
+
 int vb_profile_reset(vb_ctx *ctx) {
     if (!ctx) return VB_ERR_INVALID;
     cudaStreamSynchronize(ctx->stream);
