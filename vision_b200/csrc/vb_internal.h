@@ -106,5 +106,5 @@ struct vb_ctx {
 
 int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out);
 int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *keyidx_alt, uint32_t n, uint4 *hits4, uint8_t *occ,
-                   unsigned long long *work = nullptr);
+                   unsigned long long *work = nullptr, bool coherent = false);
 void vb_pt_destroy(vb_ctx *ctx);

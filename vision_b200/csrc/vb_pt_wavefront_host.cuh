@@ -91,7 +91,7 @@ static int wf_render_batch(vb_ctx *ctx, vb_pt_state *p, vb_wf_buffers &w, const 
         WfQueue Qout{w.rays[cur ^ 1], w.keys[2 * (cur ^ 1)], w.slot_q[cur ^ 1]};
         WfQueue Qsh{w.rays[2], w.keys[4], nullptr};
         unsigned long long *work = ctx->opt_pt_count_work ? w.d_work : nullptr;
-        int rc = vb_trace_queue(ctx, Qin.rays, k0, k1, n, w.hits4, nullptr, work);
+        int rc = vb_trace_queue(ctx, Qin.rays, k0, k1, n, w.hits4, nullptr, work, iter == 0);      // camera rays: pixel order is coherent
         if (rc) return rc;
         total.closest += n;
         VB_CUDA(cudaMemsetAsync(w.d_cnt, 0, sizeof(WfCounters), st));

@@ -337,9 +337,10 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
 // ---- queue form used by the wavefront path tracer (vb_pt_wavefront_host.cuh) -----------------------
 // rays: AoS records (o.xyz, tmin)(d.xyz, tmax); keyidx: (vb_ray_sort_key << 32 | queue index) per ray, written
 // by the producer kernel, sorted here on its 24 key bits (keyidx_alt = same-size scratch); results go to
-// hits4[index] = (inst, prim, u, v) or occ[index]. No staging, no host synchronisation.
+// hits4[index] = (inst, prim, u, v) or occ[index]. No staging, no host synchronisation. coherent = the queue is already in
+// a traversal-friendly order (camera rays in pixel order: one origin, smoothly varying direction): no sort.
 int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *keyidx_alt, uint32_t n, uint4 *hits4, uint8_t *occ,
-                   unsigned long long *work) {
+                   unsigned long long *work, bool coherent) {
     if (n == 0) return VB_OK;
     const bool any = occ != nullptr;
     cudaStream_t st = ctx->stream;
@@ -350,7 +351,7 @@ int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *
     const uint32_t *perm = nullptr;
     uint64_t launches = 1;
     ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
-    if (ctx->opt_sort_rays && n >= (uint32_t)ctx->opt_sort_min_rays) {
+    if (ctx->opt_sort_rays && !coherent && n >= (uint32_t)ctx->opt_sort_min_rays) {
         size_t cub_bytes = 0;
         cub::DoubleBuffer<uint64_t> dk(keyidx, keyidx_alt);
         VB_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, cub_bytes, dk, (int)n, 32, 56, st));
