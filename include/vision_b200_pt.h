@@ -74,7 +74,7 @@ typedef struct vb_medium_rec {
 VB_API int vb_mediums_set(vb_ctx *ctx, const vb_medium_rec *med, uint32_t n);
 
 /* ---- lights (reference src/render_core/light/<name>.cpp) + alias tables (warper/alias.h:86-122) ---- */
-enum { VB_LIGHT_AREA = 0, VB_LIGHT_POINT = 1, VB_LIGHT_SPOT = 2, VB_LIGHT_ENV = 3 };
+enum { VB_LIGHT_AREA = 0, VB_LIGHT_POINT = 1, VB_LIGHT_SPOT = 2, VB_LIGHT_ENV = 3, VB_LIGHT_PROJECTOR = 4 };
 typedef struct vb_alias_entry { float prob; uint32_t alias; } vb_alias_entry;
 typedef struct vb_light_rec {
     uint32_t type;
@@ -86,9 +86,10 @@ typedef struct vb_light_rec {
     float scale;               /* Light::scale_ after colour normalisation (light.cpp:19-24) */
     float pad0;
     vb_slot color;
-    float position[4];         /* point/spot */
+    float position[4];         /* point/spot; projector: o2w[3] */
     float direction[4];        /* spot */
-    float params[8];           /* spot: cos_falloff_start, cos_total_width; env: [0] Scene::world_diameter() (scene.h:108-109) */
+    float params[8];           /* spot: cos_falloff_start, cos_total_width; projector (light/projector.cpp:33-113): [0] tan(angle_y), [1] ratio
+                                * (0 in the file = image width / height), image = color slot, w2o / o2w = the light's transform; env: [0] Scene::world_diameter() (scene.h:108-109) */
     /* env ("spherical", environments/spherical.cpp:26-211): lat-long map = color slot texture, importance
      * sampled through AliasTable2D (alias2d.cpp:31-129): marginal table over rows at alias_offset /
      * alias_size (= env_res[1]) / alias_integral, conditional row tables (env_res[0] entries per row)

@@ -128,7 +128,18 @@ inline LightSample point_sample_wi(const Scene &sc, const vb_light_rec &l, const
     float3 value = eval_slot3(sc, l.color, float2{0, 0}) * l.scale;
     float3 w_un = ref.pos - pos;
     if (l.type == VB_LIGHT_POINT) ls.eval.L = value / length_squared(w_un);
-    else {
+    else if (l.type == VB_LIGHT_PROJECTOR) {                       // projector.cpp:99-112: image projected along the light's +z
+        float4x4 w2o; std::memcpy(&w2o, l.w2o, 64);
+        float3 p = transform_point(w2o, ref.pos);
+        float d2 = length_squared(p);
+        bool valid = p.z > 0.f;
+        p = p / p.z;
+        float tan_y = l.params[0], tan_x = l.params[1] * tan_y;
+        float2 uv{(p.x + tan_x) / (2.f * tan_x), (p.y + tan_y) / (2.f * tan_y)};
+        valid = valid && uv.x >= 0.f && uv.x <= 1.f && uv.y >= 0.f && uv.y <= 1.f;
+        if (!valid) uv = float2{0.f, 0.f};                         // the select() discards the sample; keep the fetch in range
+        ls.eval.L = eval_slot3(sc, l.color, uv) * (valid ? 1.f : 0.f) / d2 * l.scale;
+    } else {
         float3 w = normalize(w_un);
         float3 dir{l.direction[0], l.direction[1], l.direction[2]};
         float cos_angle = l.params[0], cos_falloff_start = l.params[1];

@@ -88,7 +88,7 @@ def test_host_records_equal_python_twin_materials_and_mediums(name):
 
 
 @pytest.mark.parametrize("rel", ["scenes/cbox/cbox_lights.json", "scenes/classroom/vision_scene.json", "scenes/cbox/cbox_sphere.json",
-                                 "scenes/cbox_dragon/vision_scene_small.json"])
+                                 "scenes/cbox_dragon/vision_scene_small.json", "scenes/cbox/cbox_projector.json"])
 def test_host_records_equal_python_twin_lights_and_models(rel):
     """model shape (OBJ), point / spot / spherical lights, AliasTable2D, world diameter, Euler transforms, light order"""
     path = ROOT / rel
@@ -118,6 +118,9 @@ def test_host_records_equal_python_twin_lights_and_models(rel):
         env = a.lights[0]
         assert env.type == capi.VB_LIGHT_ENV and list(env.env_res) == [512, 256] and env.alias_size == 256 and env.cond_offset == 256
         assert env.params[0] > 300.0            # the scaled ground plane sets the world diameter
+    elif "projector" in rel:
+        assert [l.type for l in a.lights] == [capi.VB_LIGHT_PROJECTOR, capi.VB_LIGHT_AREA] and len(a.textures) == 1     # one checker.jpg for wall + light
+        assert a.lights[0].color.tex_id == 0 and abs(a.lights[0].params[0] - np.tan(np.radians(6.0))) < 1e-6
     elif "dragon" in rel:
         inst = max(a.instances, key=lambda i: len(a.meshes[i["mesh_id"]]["tri"]))
         assert len(a.meshes[inst["mesh_id"]]["tri"]) == 2 * 48 * 47                 # tools/make_dragon_standin.py --width 48

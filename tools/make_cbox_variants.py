@@ -6,6 +6,7 @@ cbox-dragon.json medium "fog").
                         right wall = metal (Cu)
   cbox_fog.json       : short box = glass boundary filled with the Skin1 medium (scale 20), global thin fog,
                         mediums.process = true
+  cbox_projector.json : adds the projector light of the reference's cbox scene (image = checker.jpg), area light at 20 %
   cbox_lights.json    : the ceiling quad keeps its emission; adds a point light, a spot light (the reference's
                         commented examples in point.cpp:11-20 / spot.cpp:10-18) and a spherical environment
                         map (spherical.cpp:12-25) over scenes/cbox/env_small.pfm (64x32 analytic gradient with a
@@ -97,4 +98,14 @@ g["materials"] += [
 assign(g, {"shape_6": "P_metal", "shape_5": "P_trans", "shape_0": "P_sheen", "shape_2": "P_plastic", "shape_4": "P_mix"})
 g["integrator"]["param"]["max_depth"] = 8
 (root / "cbox_principled.json").write_text(json.dumps(g, indent=1))
-print("wrote", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json", root / "cbox_sphere.json", root / "cbox_principled.json")
+# cbox_projector.json: the reference's projector light (projector.cpp:11-31 example block, as in cbox/vision_scene.json) over
+# the checker image, dimmed area light so that the projected image dominates the back wall
+pj = copy.deepcopy(base)
+pj["light_sampler"]["param"]["lights"] = [
+    {"type": "projector", "param": {"angle": 6, "color": {"channels": "xyz", "node": {"fn": "checker.jpg", "color_space": "srgb"}}, "ratio": 1,
+                                    "o2w": {"type": "look_at", "param": {"position": [0, 1, 6.8], "up": [0, 1, 0], "target_pos": [0, 1, 0]}}, "scale": 300}}]
+for s_ in pj["shapes"]:
+    if "emission" in s_["param"]:
+        s_["param"]["emission"]["param"]["scale"] = 0.2
+(root / "cbox_projector.json").write_text(json.dumps(pj, indent=1))
+print("wrote", root / "cbox_projector.json", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json", root / "cbox_sphere.json", root / "cbox_principled.json")

@@ -337,7 +337,7 @@ class vb_pt_params(C.Structure):
 
 
 VB_MAT_DIFFUSE, VB_MAT_MIRROR, VB_MAT_GLASS, VB_MAT_METAL, VB_MAT_SUBSTRATE, VB_MAT_PRINCIPLED, VB_MAT_BLACK_BODY = range(7)
-VB_LIGHT_AREA, VB_LIGHT_POINT, VB_LIGHT_SPOT, VB_LIGHT_ENV = range(4)
+VB_LIGHT_AREA, VB_LIGHT_POINT, VB_LIGHT_SPOT, VB_LIGHT_ENV, VB_LIGHT_PROJECTOR = range(5)
 VB_FILTER_BOX, VB_FILTER_TRIANGLE, VB_FILTER_FITTED = 0, 1, 2
 VB_FILTER_TABLE_SIZE = 20
 VB_ACCUM_LERP, VB_ACCUM_SUM = 0, 1

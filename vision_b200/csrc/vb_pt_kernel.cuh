@@ -289,7 +289,7 @@ int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n, const vb_
     cudaSetDevice(ctx->device);
     vb_pt_state *p = pt_state(ctx);
     for (uint32_t i = 0; i < n; ++i) {
-        if (lights[i].type > VB_LIGHT_ENV) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_lights_set: light type not implemented yet");
+        if (lights[i].type > VB_LIGHT_PROJECTOR) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_lights_set: light type not implemented yet");
         bool tabled = lights[i].type == VB_LIGHT_AREA || lights[i].type == VB_LIGHT_ENV;
         if (tabled && lights[i].alias_offset + lights[i].alias_size > n_alias) return ctx->fail(VB_ERR_INVALID, "vb_lights_set: alias range out of bounds");
         if (lights[i].type == VB_LIGHT_ENV) {

@@ -277,6 +277,36 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(SphericalMap, light, spherical, constructor)
 
+// reference src/render_core/light/projector.cpp:33-52,96-113: a point light at o2w[3] that projects its colour image along
+// the local +z axis; angle clamped to [1, 89] deg, ratio 0 = image width / height
+class Projector : public Light {
+    LightDesc desc_;
+public:
+    explicit Projector(const LightDesc &d) : Light(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "projector"; }
+    int type_order() const override { return VB_LIGHT_PROJECTOR; }
+    void fill_record(vb_light_rec &r, const Scene &, const SlotContext &ctx, std::vector<vb_alias_entry> &, std::vector<float> &) const override {
+        light_common(r, desc_, {1.f, 1.f, 1.f}, ctx);
+        r.type = VB_LIGHT_PROJECTOR;
+        const Mat4 &M = desc_.o2w.mat;
+        double Of[16], I[16];
+        for (int i = 0; i < 16; ++i) { r.o2w[i] = M[i]; Of[i] = M[i]; }
+        if (!invert4(Of, I)) throw std::runtime_error("projector light: singular o2w");
+        for (int i = 0; i < 16; ++i) r.w2o[i] = (float)I[i];
+        r.position[0] = M[12]; r.position[1] = M[13]; r.position[2] = M[14];
+        r.direction[0] = M[8]; r.direction[1] = M[9]; r.direction[2] = M[10];          // transform_vector(o2w, (0, 0, 1))
+        float ratio = desc_["ratio"].as_float(1.f);
+        if (ratio == 0.f && r.color.tex_id != VB_INVALID_ID) {
+            const Image &im = ctx.images->images[r.color.tex_id];
+            ratio = (float)im.w / (float)im.h;
+        }
+        float angle = (float)((double)std::min(std::max(desc_["angle"].as_float(45.f), 1.f), 89.f) * 3.14159265358979323846 / 180.0);
+        r.params[0] = std::tan(angle);
+        r.params[1] = ratio;
+    }
+};
+VH_MAKE_CLASS_CREATOR(Projector, light, projector, constructor)
+
 // Gauss-Jordan with partial pivoting, column-major in/out
 static bool invert4(const double *m, double *inv) {
     double a[4][8];

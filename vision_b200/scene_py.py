@@ -131,6 +131,9 @@ def camera_to_world(m):
     return tr @ sc @ ry @ rx
 
 
+_TEX_KEYS = {}          # id(texture list) -> {(path, colour space): index}; reset per build_scene
+
+
 def _color_slot(v, textures, base_dir):
     """a colour attribute: [r,g,b] | {"channels","node":[..]} | {"node":{"type":"image","param":{"fn"}}} | {"type":"number"}"""
     if isinstance(v, dict):
@@ -140,8 +143,13 @@ def _color_slot(v, textures, base_dir):
             return _color_slot(v["param"]["value"], textures, base_dir)
         if v.get("type") == "image" or "fn" in v:
             prm = v.get("param", v)
-            textures.append(load_image(Path(base_dir) / prm["fn"], prm.get("color_space", "srgb")))
-            return make_slot([1, 1, 1, 1], len(textures) - 1)
+            # ImagePool::obtain_image (image_pool.cpp:13-35): one texture per (file, colour space)
+            keys = _TEX_KEYS.setdefault(id(textures), {})
+            key = (str(Path(base_dir) / prm["fn"]), prm.get("color_space", "srgb"))
+            if key not in keys or keys[key] >= len(textures):
+                textures.append(load_image(Path(base_dir) / prm["fn"], prm.get("color_space", "srgb")))
+                keys[key] = len(textures) - 1
+            return make_slot([1, 1, 1, 1], keys[key])
     if isinstance(v, (int, float)):
         v = [v, v, v]
     return make_slot([float(x) for x in v])
@@ -479,7 +487,7 @@ def _cfun(name, x):
     if _libm is None:
         import ctypes
         _libm = ctypes.CDLL("libm.so.6")
-        for n in ("sinf", "cosf"):
+        for n in ("sinf", "cosf", "tanf"):
             getattr(_libm, n).restype = ctypes.c_float
             getattr(_libm, n).argtypes = [ctypes.c_float]
     return f32(getattr(_libm, name)(float(f32(x))))
@@ -550,6 +558,22 @@ def _free_light_record(ld, sc, base, world_diameter):
         sc.alias_table += ct; sc.alias_func += cf
         l.env_res[:] = [rx, ry]
         l.params[0] = world_diameter
+    elif t == "projector":
+        # projector.cpp:33-52: point light at o2w[3] projecting its image along local +z
+        l.type = capi.VB_LIGHT_PROJECTOR
+        o2w = transform_matrix(prm.get("o2w")).astype(f32)
+        w2o = invert4(o2w.astype(np.float64)).astype(f32)
+        l.o2w[:] = [float(x) for x in o2w.T.reshape(-1)]
+        l.w2o[:] = [float(x) for x in w2o.T.reshape(-1)]
+        l.position[:3] = [float(x) for x in o2w[:3, 3]]
+        l.direction[:3] = [float(x) for x in o2w[:3, 2]]
+        ratio = f32(_number(prm.get("ratio", 1.0), 1.0))
+        if ratio == 0 and l.color.tex_id != VB_INVALID_ID:
+            th, tw = sc.textures[l.color.tex_id].shape[:2]
+            ratio = f32(f32(tw) / f32(th))
+        angle = f32(math.radians(float(np.clip(f32(prm.get("angle", 45.0)), f32(1.0), f32(89.0)))))
+        l.params[0] = float(_cfun("tanf", angle))
+        l.params[1] = float(ratio)
     else:
         raise NotImplementedError(f"light {t}")
     return l
@@ -689,6 +713,7 @@ def build_scene(path, overrides=None) -> SceneRecords:
     d = load_json_with_comments(path)
     base = Path(path).parent
     sc = SceneRecords()
+    _TEX_KEYS.pop(id(sc.textures), None)
     # materials (Scene::load_materials): records are made further down, for the materials in use only
     mat_descs, mat_index = [], {}
     for m in d.get("materials", []):
@@ -743,7 +768,7 @@ def build_scene(path, overrides=None) -> SceneRecords:
     # LightSampler ctor (lightsampler.cpp:11-27): listed lights come first, the shapes' emissions follow; tidy_up
     # (lightsampler.cpp:67-77) groups them by type in first-seen order; records are made in that order
     free = [] if ov.get("drop_lights", False) else d.get("light_sampler", {}).get("param", {}).get("lights", [])
-    type_of = {"point": capi.VB_LIGHT_POINT, "spot": capi.VB_LIGHT_SPOT, "spherical": capi.VB_LIGHT_ENV}
+    type_of = {"point": capi.VB_LIGHT_POINT, "spot": capi.VB_LIGHT_SPOT, "spherical": capi.VB_LIGHT_ENV, "projector": capi.VB_LIGHT_PROJECTOR}
     pending = [(type_of.get(ld["type"], -1), ld, None) for ld in free] + [(capi.VB_LIGHT_AREA, em, ii) for em, ii in area_lights]
     first = {}
     for t, _, _ in pending:
