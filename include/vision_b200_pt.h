@@ -32,8 +32,10 @@ enum { VB_MAT_DIFFUSE = 0, VB_MAT_MIRROR = 1, VB_MAT_GLASS = 2, VB_MAT_METAL = 3
        VB_MAT_PRINCIPLED = 5, VB_MAT_BLACK_BODY = 6 };
 typedef struct vb_material_rec {
     uint32_t type;
-    uint32_t flags;            /* bit0: has sigma (Oren-Nayar, diffuse.cpp:26-29), bit1: remapping_roughness */
-    uint32_t pad[2];
+    uint32_t flags;            /* bit0: has sigma (Oren-Nayar, diffuse.cpp:26-29), bit1: remapping_roughness,
+                                * bit2: hero spectrum only - glass ior (glass.cpp:216-234, dispersive) / metal eta, k
+                                * (metal.cpp:117-121) are "spd" slots: spd[0] = ior | eta, spd[1] = k, indices into the SPD pool */
+    uint32_t spd[2];
     vb_slot color;             /* diffuse.cpp:23, glass/mirror color, substrate diff */
     vb_slot roughness;         /* xy */
     vb_slot spec;              /* substrate spec / principled */
@@ -102,6 +104,25 @@ typedef struct vb_light_rec {
 VB_API int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n,
                          const vb_alias_entry *alias_table, const float *alias_func, uint32_t n_alias);
 
+/* ---- spectrum (reference src/render_core/spectrum/srgb.cpp:16-57, hero.cpp:15-348; src/base/color/spd.cpp) ---- */
+/* SPD pool: tabulated spectral distributions over 360..830 nm, SPD::eval semantics (spd.cpp:50,57-76: linear
+ * interpolation with sample_interval = 471 / size). SPD i = values[offsets[i] .. offsets[i+1]). */
+VB_API int vb_spds_set(vb_ctx *ctx, const float *values, const uint32_t *offsets /* n + 1 */, uint32_t n);
+/* VB_SPECTRUM_HERO = HeroWavelengthSpectrum with dimension 3 (the default): hero-wavelength sampling at sampler
+ * dimension -1, RGB -> sigmoid-polynomial uplifting of albedo / unbound / illumination colours through the
+ * coefficient table (float[3][res][res][res][4], hero.cpp:53-54), CIE XYZ -> linear sRGB at every accumulation,
+ * secondary wavelengths invalidated by dispersive glass. Selected by vb_pt_params.spectrum. */
+enum { VB_SPECTRUM_SRGB = 0, VB_SPECTRUM_HERO = 1 };
+typedef struct vb_spectrum_rec {
+    uint32_t type;
+    uint32_t dimension;        /* hero: 3 (anything else is VB_ERR_UNSUPPORTED) */
+    uint32_t spd_x, spd_y, spd_z, spd_d65;   /* SPD pool indices: CIE 1931 observer and D65, 5 nm (SPD::create_cie_*, spd.cpp:89-103) */
+    float cie_y_integral;      /* SPD::cie_y_integral(), spd.cpp:105-108 */
+    uint32_t rgb2spec_res;     /* 64 */
+    const float *rgb2spec;     /* host pointer, 3 * res^3 * 4 floats */
+} vb_spectrum_rec;
+VB_API int vb_spectrum_set(vb_ctx *ctx, const vb_spectrum_rec *spec);
+
 /* ---- sensor + filter (reference src/base/sensor/sensor.cpp:44-78,153-162, thin_lens.cpp:34-42,
  *      filter/box.cpp:16-20, filter/triangle.cpp:16-18) ------------------------------------------- */
 /* VB_FILTER_FITTED = FittedCurveFilter (filter/fitted_curve.h:16-107: gaussian, mitchell, sinc): pixel offsets are drawn
@@ -126,7 +147,7 @@ typedef struct vb_pt_params {
     uint32_t max_depth, min_depth;
     float rr_threshold;
     uint32_t mis_mode;         /* 0 both, 1 light, 2 bsdf (integrator.h:116-120) */
-    uint32_t spectrum;         /* 0 = srgb */
+    uint32_t spectrum;         /* VB_SPECTRUM_SRGB | VB_SPECTRUM_HERO (needs vb_spectrum_set + vb_spds_set) */
     uint32_t sampler;          /* 0 = independent (TEA + LCG) */
     uint32_t process_mediums;
     float ray_offset_factor;   /* Interaction::s_ray_offset_factor, node_desc.cpp:375 */

@@ -173,7 +173,9 @@ struct Lobe {
     float3 rs{0, 0, 0};        // substrate Rs | metal eta
     float3 kk{0, 0, 0};        // metal k
     GGX mf{1.f, 1.f};
-    float eta = 1.f;           // glass: corrected relative ior (Interaction::correct_eta)
+    float eta = 1.f;           // glass: corrected relative ior (Interaction::correct_eta); dispersive: of the hero wavelength (eta[0])
+    float3 eta3{1, 1, 1};      // dispersive glass (hero spectrum, ior slot = "spd", glass.cpp:221-234): corrected ior per wavelength
+    bool dispersive = false;
     bool oren_nayar = false; float on_A = 1.f, on_B = 0.f;
 };
 
@@ -197,10 +199,16 @@ inline float dielectric_compensate(const Scene &sc, const Lobe &lb, float3 wo) {
     float z = lb.eta > 1.0f ? (lb.eta - lo) / (hi - lo) : (1.0f / lb.eta - lo) / (hi - lo);
     return 1.0f / lut_sample3d_ch0(L, x, y, z);
 }
-inline float dielectric_refl_prob(const Lobe &lb, float F) {
-    float T = 1.0f - F;
-    float3 total = lb.kr * T + splat(F);
-    return F / average3(total);
+// FresnelDielectric::evaluate (fresnel.h:84-89): one value per entry of the ior array - a scalar slot gives a
+// 1-dimensional spectrum (F.average() == F), the dispersive "spd" slot one value per wavelength
+inline float3 dielectric_F(const Lobe &lb, float cos_theta) {
+    if (!lb.dispersive) return splat(fresnel_dielectric(cos_theta, lb.eta));
+    return {fresnel_dielectric(cos_theta, lb.eta3.x), fresnel_dielectric(cos_theta, lb.eta3.y), fresnel_dielectric(cos_theta, lb.eta3.z)};
+}
+inline float dielectric_refl_prob(const Lobe &lb, float3 F) {
+    float3 T = splat(1.0f) - F;
+    float3 total = lb.kr * T + F;
+    return (lb.dispersive ? average3(F) : F.x) / average3(total);
 }
 inline ScatterEval dielectric_evaluate_local(const Scene &sc, const Lobe &lb, float3 wo, float3 wi, bool flip_wh, float *eta_out) {
     bool reflect_ = same_hemisphere(wo, wi);
@@ -208,17 +216,17 @@ inline ScatterEval dielectric_evaluate_local(const Scene &sc, const Lobe &lb, fl
     if (eta_out) *eta_out = eta_p;
     float3 wh = normalize(wo + wi * eta_p);
     if (flip_wh) wh = face_forward(wh, wo);
-    float F = fresnel_dielectric(abs_dot(wh, wo), lb.eta);
+    float3 F = dielectric_F(lb, abs_dot(wh, wo));
     ScatterEval se;
     if (reflect_) {
-        se.f = splat(ggx_brdf_div_fr(lb.mf, wo, wh, wi) * F);
+        se.f = F * ggx_brdf_div_fr(lb.mf, wo, wh, wi);
         se.pdf = ggx_pdf_wi_reflection(lb.mf, wo, wh) * dielectric_refl_prob(lb, F);
         se.flags = FlagGlossy | FlagReflection;
         se.f = se.f * dielectric_compensate(sc, lb, wo);
     } else {
         float3 new_wh = face_forward(wh, wo);
         float3 wh2 = normalize(wo + wi * lb.eta);                         // Microfacet::BTDF(wo, wi, ...) recomputes wh
-        float tr = ggx_btdf_div_ft(lb.mf, wo, wh2, wi, lb.eta) * (1.0f - F);
+        float3 tr = (splat(1.0f) - F) * ggx_btdf_div_ft(lb.mf, wo, wh2, wi, lb.eta);
         se.f = lb.kr * tr;
         se.pdf = ggx_pdf_wi_transmission(lb.mf, wo, new_wh, wi, lb.eta) * (1.0f - dielectric_refl_prob(lb, F));
         se.flags = FlagGlossy | FlagTransmission;
@@ -325,7 +333,7 @@ inline BSDFSample lobe_sample(const Scene &sc, const Lobe &lb, float3 world_wo, 
         case VB_MAT_GLASS: {                                           // lobe.cpp:431-449
             float3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
             float d = dot(wo, wh);
-            float F = fresnel_dielectric(std::fabs(d), lb.eta);
+            float3 F = dielectric_F(lb, std::fabs(d));
             float uc = sampler.next_1d();
             if (uc < dielectric_refl_prob(lb, F)) {
                 wi = reflect(wo, wh);
@@ -363,7 +371,7 @@ inline BSDFSample lobe_sample(const Scene &sc, const Lobe &lb, float3 world_wo, 
 
 // Material::create_evaluator -> create_lobe_set of the plugin (diffuse.cpp:21-30, mirror.cpp:60-74,
 // glass.cpp:240-257, metal.cpp:137-156, substrate.cpp:126-149)
-inline Lobe create_lobe(const Scene &sc, const Interaction &it) {
+inline Lobe create_lobe(const Scene &sc, const Swl &swl, const Interaction &it) {
     const vb_material_rec &m = sc.materials[it.mat_id];
     Lobe lb;
     lb.type = m.type;
@@ -373,7 +381,7 @@ inline Lobe create_lobe(const Scene &sc, const Interaction &it) {
     float anis = clampf(m.params[0], -0.9f, 0.9f);
     switch (m.type) {
         case VB_MAT_DIFFUSE:
-            lb.kr = eval_slot3(sc, m.color, it.uv);
+            lb.kr = spec_albedo(sc, swl, eval_slot3(sc, m.color, it.uv));
             if (m.flags & 1u) {                                        // OrenNayar ctor, bxdf.cpp:94-101
                 float sigma = eval_slot3(sc, m.sigma, it.uv).x * PiOver2;
                 float sigma2 = sqr(sigma * sigma);
@@ -383,23 +391,33 @@ inline Lobe create_lobe(const Scene &sc, const Interaction &it) {
             }
             break;
         case VB_MAT_MIRROR: case VB_MAT_METAL: {
-            lb.kr = m.type == VB_MAT_MIRROR ? eval_slot3(sc, m.color, it.uv) : splat(1.f);
+            lb.kr = m.type == VB_MAT_MIRROR ? spec_albedo(sc, swl, eval_slot3(sc, m.color, it.uv)) : splat(1.f);
             float r = clampf(eval_slot3(sc, m.roughness, it.uv).x, 0.0001f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
             lb.rs = {m.eta[0], m.eta[1], m.eta[2]}; lb.kk = {m.k[0], m.k[1], m.k[2]};
+            if (m.type == VB_MAT_METAL && (m.flags & 4u) && swl.hero) {   // metal.cpp:117-121: eta / k are "spd" slots under a complete spectrum
+                lb.rs = spd_eval3(sc, m.spd[0], swl); lb.kk = spd_eval3(sc, m.spd[1], swl);
+            }
         } break;
         case VB_MAT_GLASS: {
-            lb.kr = eval_slot3(sc, m.color, it.uv);
+            lb.kr = spec_albedo(sc, swl, eval_slot3(sc, m.color, it.uv));
             float ior = eval_slot3(sc, m.ior, it.uv).x;
             lb.eta = dot(it.wo, it.ng) > 0.f ? ior : 1.0f / ior;      // Interaction::correct_eta
+            if ((m.flags & 4u) && swl.hero) {                          // glass.cpp:216-234: "material_name" curve sampled into an "spd" slot
+                float3 iors = spd_eval3(sc, m.spd[0], swl);
+                bool front = dot(it.wo, it.ng) > 0.f;
+                lb.eta3 = front ? iors : float3{1.0f / iors.x, 1.0f / iors.y, 1.0f / iors.z};
+                lb.eta = lb.eta3.x;
+                lb.dispersive = true;
+            }
             float r = clampf(eval_slot3(sc, m.roughness, it.uv).x, 0.01f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
         } break;
         case VB_MAT_SUBSTRATE: {
-            lb.kr = eval_slot3(sc, m.color, it.uv);
-            lb.rs = eval_slot3(sc, m.spec, it.uv);
+            lb.kr = spec_albedo(sc, swl, eval_slot3(sc, m.color, it.uv));
+            lb.rs = spec_albedo(sc, swl, eval_slot3(sc, m.spec, it.uv));
             float r = clampf(eval_slot3(sc, m.roughness, it.uv).x, 0.0001f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);

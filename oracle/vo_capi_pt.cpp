@@ -49,6 +49,18 @@ void vo_scene_set_lut(void *h, int which, const float *data, uint32_t nx, uint32
     l.data.assign(data, data + (size_t)nx * ny * nz * ch);
 }
 void vo_scene_set_mediums(void *h, const vb_medium_rec *m, uint32_t n) { ((Scene *)h)->mediums.assign(m, m + n); }
+void vo_scene_set_spds(void *h, const float *values, const uint32_t *offsets, uint32_t n) {
+    Scene &s = *(Scene *)h;
+    s.spd_offsets.assign(offsets, offsets + n + 1);
+    s.spd_values.assign(values, values + offsets[n]);
+}
+void vo_scene_set_spectrum(void *h, const vb_spectrum_rec *r) {
+    Scene &s = *(Scene *)h;
+    s.spectrum = *r;
+    s.rgb2spec_res = r->rgb2spec_res;
+    if (r->rgb2spec) s.rgb2spec.assign(r->rgb2spec, r->rgb2spec + (size_t)3 * r->rgb2spec_res * r->rgb2spec_res * r->rgb2spec_res * 4);
+    s.spectrum.rgb2spec = nullptr;
+}
 void vo_scene_set_camera(void *h, const vb_camera *c) { ((Scene *)h)->camera = *c; }
 void vo_scene_set_integrator(void *h, const vb_pt_params *p) { ((Scene *)h)->params = *p; }
 void vo_scene_build(void *h, int threads, int brute) {
@@ -139,5 +151,11 @@ void vo_offset_ray_origin(const float *p, const float *n, float *out) {
     float3 r = offset_ray_origin({p[0], p[1], p[2]}, {n[0], n[1], n[2]});
     out[0] = r.x; out[1] = r.y; out[2] = r.z;
 }
+
+
+// hero spectrum probes (vo_pt.cpp): out = lambda[3], pdf[3]
+void vo_hero_wavelengths(uint32_t u24, float *out);
+// kind 0 albedo, 1 unbound, 2 illumination; then back to linear sRGB: out_sp[3], out_rgb[3]
+void vo_hero_decode(void *h, uint32_t u24, int kind, const float *rgb, float *out_sp, float *out_rgb);
 
 }  // extern "C"

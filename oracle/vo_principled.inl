@@ -57,17 +57,17 @@ inline float3 layering_weight(float3 layer_albedo, float3 weight) {
     return weight * saturate(1.f - max_comp);
 }
 
-inline PrincipledSet principled_create(const Scene &sc, const Interaction &it) {
+inline PrincipledSet principled_create(const Scene &sc, const Swl &swl, const Interaction &it) {
     const vb_material_rec &m = sc.materials[it.mat_id];
     PrincipledSet ps;
     ps.frame = it.shading;
     auto clampf = [](float v, float lo, float hi) { return std::min(std::max(v, lo), hi); };
     const uint32_t switches = (uint32_t)m.params[15];
-    float3 color = eval_slot3(sc, m.color, it.uv);
+    float3 color = spec_albedo(sc, swl, eval_slot3(sc, m.color, it.uv));
     float ior = eval_slot3(sc, m.ior, it.uv).x;
     float roughness = clampf(eval_slot3(sc, m.roughness, it.uv).x, 0.0001f, 1.f);
     float anisotropic = m.params[0];
-    float3 specular_tint = eval_slot3(sc, m.spec, it.uv);
+    float3 specular_tint = spec_albedo(sc, swl, eval_slot3(sc, m.spec, it.uv));
     float aspect = std::sqrt(1.f - anisotropic * 0.9f);
     GGX mf{std::max(0.001f, sqr(roughness) / aspect), std::max(0.001f, sqr(roughness) * aspect)};
     float3 weight = splat(1.f);
@@ -77,7 +77,7 @@ inline PrincipledSet principled_create(const Scene &sc, const Interaction &it) {
     if (switches & (1u << SL_SHEEN)) {
         SubLobe &l = ps.s[ps.n++];
         l.kind = SL_SHEEN;
-        float3 sheen_tint{m.params[4], m.params[5], m.params[6]};
+        float3 sheen_tint = spec_albedo(sc, swl, float3{m.params[4], m.params[5], m.params[6]});
         float sheen_weight = m.params[2] * front;
         float sheen_roughness = m.params[3];
         l.kr = sheen_tint * sheen_weight * weight;
@@ -96,7 +96,7 @@ inline PrincipledSet principled_create(const Scene &sc, const Interaction &it) {
         float cc_weight = m.params[7] * front;
         float cc_roughness = sqr(clampf(m.params[8], 0.0001f, 1.f));
         float cc_ior = m.params[9];
-        float3 cc_tint{m.params[10], m.params[11], m.params[12]};
+        float3 cc_tint = spec_albedo(sc, swl, float3{m.params[10], m.params[11], m.params[12]});
         l.fresnel = FR_DIELECTRIC; l.eta = cc_ior;
         l.mf = GGX{cc_roughness, cc_roughness};
         l.kr = weight * cc_weight * cc_tint;

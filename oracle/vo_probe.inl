@@ -41,8 +41,8 @@ void vo_probe_bsdf_eval(void *scene, uint32_t mat_id, const float *wo, const flo
     const vo::Scene &sc = *(const vo::Scene *)scene;
     vo::Interaction it = probe_interaction(mat_id, wo);
     vo::ScatterEval se;
-    if (sc.materials[mat_id].type == VB_MAT_PRINCIPLED) se = vo::PrincipledEvaluator{vo::principled_create(sc, it), it.ng}.evaluate(sc, it.wo, {wi[0], wi[1], wi[2]});
-    else se = vo::Evaluator{vo::create_lobe(sc, it), it.ng}.evaluate(sc, it.wo, {wi[0], wi[1], wi[2]});
+    if (sc.materials[mat_id].type == VB_MAT_PRINCIPLED) se = vo::PrincipledEvaluator{vo::principled_create(sc, vo::Swl{}, it), it.ng}.evaluate(sc, it.wo, {wi[0], wi[1], wi[2]});
+    else se = vo::Evaluator{vo::create_lobe(sc, vo::Swl{}, it), it.ng}.evaluate(sc, it.wo, {wi[0], wi[1], wi[2]});
     out[0] = se.f.x; out[1] = se.f.y; out[2] = se.f.z; out[3] = se.pdf; out[4] = (float)se.flags;
 }
 // n samples with the LCG seeded by `state`; out per sample: wi.xyz, f.xyz, pdf, eta  (8 floats)
@@ -50,8 +50,8 @@ void vo_probe_bsdf_sample(void *scene, uint32_t mat_id, const float *wo, uint32_
     const vo::Scene &sc = *(const vo::Scene *)scene;
     vo::Interaction it = probe_interaction(mat_id, wo);
     const bool principled = sc.materials[mat_id].type == VB_MAT_PRINCIPLED;
-    vo::Evaluator ev{principled ? vo::Lobe{} : vo::create_lobe(sc, it), it.ng};
-    vo::PrincipledEvaluator pev{principled ? vo::principled_create(sc, it) : vo::PrincipledSet{}, it.ng};
+    vo::Evaluator ev{principled ? vo::Lobe{} : vo::create_lobe(sc, vo::Swl{}, it), it.ng};
+    vo::PrincipledEvaluator pev{principled ? vo::principled_create(sc, vo::Swl{}, it) : vo::PrincipledSet{}, it.ng};
     vo::Sampler sampler; sampler.state = state;
     for (uint32_t k = 0; k < n; ++k) {
         vo::BSDFSample bs = principled ? pev.sample(sc, it.wo, sampler) : ev.sample(sc, it.wo, sampler);

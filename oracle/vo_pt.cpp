@@ -225,3 +225,20 @@ bool Scene::trace_any(const Ray &r, PathStats *st) const {
 
 #include "vo_pt_li.inl"
 #include "vo_probe.inl"
+
+// known-answer probes of the hero spectrum (tests/test_oracle_spectrum.py)
+extern "C" void vo_hero_wavelengths(uint32_t u24, float *out) {
+    vo::Scene sc;
+    sc.params.spectrum = 1;
+    vo::Swl w = vo::swl_make(sc, u24);
+    for (int i = 0; i < 3; ++i) { out[i] = w.lambda[i]; out[3 + i] = w.pdf[i]; }
+}
+extern "C" void vo_hero_decode(void *h, uint32_t u24, int kind, const float *rgb, float *out_sp, float *out_rgb) {
+    const vo::Scene &sc = *(const vo::Scene *)h;
+    vo::Swl w = vo::swl_make(sc, u24);
+    vo::float3 c{rgb[0], rgb[1], rgb[2]};
+    vo::float3 sp = kind == 0 ? vo::spec_albedo(sc, w, c) : (kind == 1 ? vo::spec_unbound(sc, w, c) : vo::spec_illum(sc, w, c));
+    vo::float3 o = vo::spec_to_srgb(sc, w, sp);
+    out_sp[0] = sp.x; out_sp[1] = sp.y; out_sp[2] = sp.z;
+    out_rgb[0] = o.x; out_rgb[1] = o.y; out_rgb[2] = o.z;
+}

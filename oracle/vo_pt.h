@@ -45,6 +45,11 @@ struct Scene {
     std::vector<Texture> textures;
     Lut luts[VB_LUT_COUNT];
     std::vector<vb_medium_rec> mediums;
+    std::vector<float> spd_values;          // SPD pool (vb_spds_set)
+    std::vector<uint32_t> spd_offsets;
+    vb_spectrum_rec spectrum{};             // rgb2spec points into the copy below
+    std::vector<float> rgb2spec;
+    uint32_t rgb2spec_res = 0;
     vb_camera camera{};
     vb_pt_params params{};
     Accel accel;

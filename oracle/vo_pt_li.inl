@@ -1,4 +1,5 @@
 // ORACLE — test infrastructure only. Included by vo_pt.cpp (same translation unit).
+#include "vo_spectrum.inl"
 // Interaction, lights, materials, Li and the per-pixel-sample driver.
 namespace vo {
 namespace {
@@ -93,10 +94,10 @@ inline uint32_t alias_sample(const Scene &sc, const vb_light_rec &l, float u, fl
 }
 
 // ---- area light, reference render_core/light/area.cpp:92-149, light.h:126-130, warp.h:88-94 ----
-inline LightEval area_evaluate_wi(const Scene &sc, const vb_light_rec &l, float3 ref_pos, const LightEvalCtx &pl) {
+inline LightEval area_evaluate_wi(const Scene &sc, const Swl &swl, const vb_light_rec &l, float3 ref_pos, const LightEvalCtx &pl) {
     LightEval ev;
     float3 w = ref_pos - pl.pos;
-    float3 color = eval_slot3(sc, l.color, pl.uv);
+    float3 color = spec_illum(sc, swl, eval_slot3(sc, l.color, pl.uv));
     float s = (dot(w, pl.ng) > 0.f || l.two_sided) ? 1.f : 0.f;
     ev.L = color * l.scale * s;
     float cos_theta = std::fabs(dot(pl.ng, normalize(w)));
@@ -105,7 +106,7 @@ inline LightEval area_evaluate_wi(const Scene &sc, const vb_light_rec &l, float3
     return ev;
 }
 
-inline LightSample area_sample_wi(const Scene &sc, const vb_light_rec &l, const Interaction &ref, float2 u) {
+inline LightSample area_sample_wi(const Scene &sc, const Swl &swl, const vb_light_rec &l, const Interaction &ref, float2 u) {
     float pmf, ux;
     uint32_t prim = alias_sample(sc, l, u.x, pmf, ux);
     float su0 = std::sqrt(ux);
@@ -114,7 +115,7 @@ inline LightSample area_sample_wi(const Scene &sc, const vb_light_rec &l, const 
     LightEvalCtx pl{li.pos, li.ng, li.uv, 1.0f / li.prim_area};
     pl.pdf_pos *= pmf;
     LightSample ls;
-    ls.eval = area_evaluate_wi(sc, l, ref.pos, pl);
+    ls.eval = area_evaluate_wi(sc, swl, l, ref.pos, pl);
     float3 dir = ref.pos - pl.pos;
     float factor = dot(pl.ng, dir) > 0.f ? 1.f : -1.f;           // SpacePoint::robust_pos
     ls.p_light = offset_ray_origin(pl.pos, pl.ng * factor * sc.params.ray_offset_factor);
@@ -122,10 +123,10 @@ inline LightSample area_sample_wi(const Scene &sc, const vb_light_rec &l, const 
 }
 
 // ---- point / spot lights, reference render_core/light/point.cpp:36-42, spot.cpp:47-70, light.cpp:49-58 ----
-inline LightSample point_sample_wi(const Scene &sc, const vb_light_rec &l, const Interaction &ref) {
+inline LightSample point_sample_wi(const Scene &sc, const Swl &swl, const vb_light_rec &l, const Interaction &ref) {
     LightSample ls;
     float3 pos{l.position[0], l.position[1], l.position[2]};
-    float3 value = eval_slot3(sc, l.color, float2{0, 0}) * l.scale;
+    float3 value = spec_illum(sc, swl, eval_slot3(sc, l.color, float2{0, 0})) * l.scale;
     float3 w_un = ref.pos - pos;
     if (l.type == VB_LIGHT_POINT) ls.eval.L = value / length_squared(w_un);
     else if (l.type == VB_LIGHT_PROJECTOR) {                       // projector.cpp:99-112: image projected along the light's +z
@@ -138,7 +139,7 @@ inline LightSample point_sample_wi(const Scene &sc, const vb_light_rec &l, const
         float2 uv{(p.x + tan_x) / (2.f * tan_x), (p.y + tan_y) / (2.f * tan_y)};
         valid = valid && uv.x >= 0.f && uv.x <= 1.f && uv.y >= 0.f && uv.y <= 1.f;
         if (!valid) uv = float2{0.f, 0.f};                         // the select() discards the sample; keep the fetch in range
-        ls.eval.L = eval_slot3(sc, l.color, uv) * (valid ? 1.f : 0.f) / d2 * l.scale;
+        ls.eval.L = spec_illum(sc, swl, eval_slot3(sc, l.color, uv)) * (valid ? 1.f : 0.f) / d2 * l.scale;
     } else {
         float3 w = normalize(w_un);
         float3 dir{l.direction[0], l.direction[1], l.direction[2]};
@@ -192,10 +193,10 @@ inline float2 env_calculate_uv(float3 local_dir) {                  // spherical
     float theta = vatan2(safe_sqrt(1.0f - cz * cz), cz);
     return {phi * Inv2Pi, theta * InvPi};
 }
-inline float3 env_L(const Scene &sc, const vb_light_rec &l, float3 local_dir) {
-    return eval_slot3(sc, l.color, env_calculate_uv(local_dir)) * l.scale;
+inline float3 env_L(const Scene &sc, const Swl &swl, const vb_light_rec &l, float3 local_dir) {
+    return spec_illum(sc, swl, eval_slot3(sc, l.color, env_calculate_uv(local_dir))) * l.scale;
 }
-inline LightEval env_evaluate_wi(const Scene &sc, const vb_light_rec &l, float3 ref_pos, float3 light_pos) {
+inline LightEval env_evaluate_wi(const Scene &sc, const Swl &swl, const vb_light_rec &l, float3 ref_pos, float3 light_pos) {
     LightEval ev;
     float4x4 w2o; std::memcpy(&w2o, l.w2o, 64);
     float3 world_dir = normalize(light_pos - ref_pos);
@@ -203,12 +204,12 @@ inline LightEval env_evaluate_wi(const Scene &sc, const vb_light_rec &l, float3 
     float2 uv = env_calculate_uv(local_dir);
     float s, c;
     sincos_2pi(uv.y * 0.5f, s, c);                                  // sin(theta), theta = uv.y * pi
-    ev.L = env_L(sc, l, local_dir);
+    ev.L = env_L(sc, swl, l, local_dir);
     float pdf = env_map_pdf(sc, l, uv) / (2.0f * Pi * Pi * s);
     ev.pdf = s == 0.f ? 0.f : pdf;
     return ev;
 }
-inline LightSample env_sample_wi(const Scene &sc, const vb_light_rec &l, const Interaction &ref, float2 u) {
+inline LightSample env_sample_wi(const Scene &sc, const Swl &swl, const vb_light_rec &l, const Interaction &ref, float2 u) {
     LightSample ls;
     float pdf_map;
     float2 uv = env_sample_continuous(sc, l, u, pdf_map);
@@ -220,13 +221,13 @@ inline LightSample env_sample_wi(const Scene &sc, const vb_light_rec &l, const I
     float3 world_dir = normalize(transform_vector(o2w, local_dir));
     float pdf_dir = pdf_map / (2.0f * Pi * Pi * st);
     ls.eval.pdf = std::isinf(pdf_dir) ? 0.f : pdf_dir;
-    ls.eval.L = env_L(sc, l, local_dir);
+    ls.eval.L = env_L(sc, swl, l, local_dir);
     ls.p_light = ref.pos + world_dir * l.params[0];
     return ls;
 }
 
 // reference lightsampler.cpp:210-216 + uniform.cpp:24-33
-inline LightSample sample_light(const Scene &sc, const Interaction &it, Sampler &sampler) {
+inline LightSample sample_light(const Scene &sc, const Swl &swl, const Interaction &it, Sampler &sampler) {
     float u_light = sampler.next_1d();
     float2 u_surface = sampler.next_2d();
     LightSample ls;
@@ -235,21 +236,21 @@ inline LightSample sample_light(const Scene &sc, const Interaction &it, Sampler 
     uint32_t index = (uint32_t)std::min(u_light * (float)n, (float)n - 1.0f);
     float pmf = 1.0f / (float)n;
     const vb_light_rec &l = sc.lights[index];
-    if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(sc, l, it, u_surface);
-    else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(sc, l, it, u_surface);
-    else ls = point_sample_wi(sc, l, it);
+    if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(sc, swl, l, it, u_surface);
+    else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(sc, swl, l, it, u_surface);
+    else ls = point_sample_wi(sc, swl, l, it);
     ls.eval.pdf *= pmf;
     return ls;
 }
 
 // reference lightsampler.cpp:252-267
-inline LightEval evaluate_hit_wi(const Scene &sc, float3 ref_pos, const Interaction &it) {
+inline LightEval evaluate_hit_wi(const Scene &sc, const Swl &swl, float3 ref_pos, const Interaction &it) {
     LightEval ev;
     const vb_light_rec &l = sc.lights[it.light_id];
     if (l.type != VB_LIGHT_AREA) return ev;
     LightEvalCtx pl{it.pos, it.ng, it.uv, 1.0f / it.prim_area};
     pl.pdf_pos *= alias_pmf(sc, l, it.prim_id);
-    ev = area_evaluate_wi(sc, l, ref_pos, pl);
+    ev = area_evaluate_wi(sc, swl, l, ref_pos, pl);
     ev.pdf *= 1.0f / (float)sc.lights.size();
     return ev;
 }
@@ -263,18 +264,18 @@ namespace {
 inline float mis_weight(float f, float g) { return (1.0f * f) / (1.0f * f + 1.0f * g); }   // warp.h:148-153,187-199
 
 // ---- homogeneous medium, reference render_core/medium/homogeneous.cpp:30-70 ----
-inline float3 medium_sigma_t(const vb_medium_rec &m) {
-    return float3{m.sigma_a[0] + m.sigma_s[0], m.sigma_a[1] + m.sigma_s[1], m.sigma_a[2] + m.sigma_s[2]} * m.scale;
+inline float3 medium_sigma_t(const Scene &sc, const Swl &swl, const vb_medium_rec &m) {
+    return spec_unbound(sc, swl, float3{m.sigma_a[0] + m.sigma_s[0], m.sigma_a[1] + m.sigma_s[1], m.sigma_a[2] + m.sigma_s[2]} * m.scale);
 }
-inline float3 medium_Tr(const vb_medium_rec &m, float t) {
-    float3 st = medium_sigma_t(m);
+inline float3 medium_Tr(const Scene &sc, const Swl &swl, const vb_medium_rec &m, float t) {
+    float3 st = medium_sigma_t(sc, swl, m);
     float tt = std::min(RayTMax, t);
     return {vexp(-st.x * tt), vexp(-st.y * tt), vexp(-st.z * tt)};
 }
 // Geometry::Tr (geometry.cpp:187-199) for a ray inside medium `id`
-inline float3 ray_Tr(const Scene &sc, uint32_t medium, const Ray &ray) {
+inline float3 ray_Tr(const Scene &sc, const Swl &swl, uint32_t medium, const Ray &ray) {
     if (!sc.params.process_mediums || medium == VB_INVALID_ID) return float3{1, 1, 1};
-    return medium_Tr(sc.mediums[medium], length(ray.d) * ray.tmax);
+    return medium_Tr(sc, swl, sc.mediums[medium], length(ray.d) * ray.tmax);
 }
 // coordinate_system (pbrt v3 form)
 inline void coordinate_system(float3 n, float3 &a, float3 &b) {
@@ -359,6 +360,9 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
     if (primary) *primary = ph;
 
     // ---- path_tracing kernel: reference integrator.cpp:85-99 ----
+    uint32_t swl_packed = 0;                                        // RenderEnv::initial, integrator.cpp:48-57: dim -1, state restored after
+    if (params.spectrum == 1) { sampler.start(px, py, frame, 0xffffffffu); (void)sampler.next_1d(); swl_packed = sampler.state & 0x00ffffffu; }
+    Swl swl = swl_make(*this, swl_packed);
     sampler.start(px, py, frame, 1u);
     const bool mediums = params.process_mediums != 0;
     uint32_t ray_medium = mediums ? camera.medium_id : VB_INVALID_ID;          // RayData::dir_medium.w
@@ -375,13 +379,13 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
             if (env_light != VB_INVALID_ID) {
                 const vb_light_rec &l = lights[env_light];
                 float3 tr{1, 1, 1};
-                if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(*this, ray_medium, ray); }
-                LightEval ev = env_evaluate_wi(*this, l, ray.o, ray.o + ray.d);
+                if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(*this, swl, ray_medium, ray); }
+                LightEval ev = env_evaluate_wi(*this, swl, l, ray.o, ray.o + ray.d);
                 ev.pdf *= 1.0f / (float)lights.size();
                 float weight = mis_weight(scatter_pdf, ev.pdf);
                 if (params.mis_mode == 2) weight = 1.f;
                 else if (params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
-                ret += ev.L * tr * weight * throughput;
+                ret += spec_to_srgb(*this, swl, ev.L * tr * weight * throughput);
             }
             break;
         }
@@ -391,8 +395,8 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
         if (st) st->vertices++;
         if (mediums && ray_medium != VB_INVALID_ID) {              // integrator.cpp:199-206, homogeneous.cpp:50-70
             const vb_medium_rec &md = this->mediums[ray_medium];
-            float3 sigma_t = medium_sigma_t(md);
-            float3 sigma_s{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale};
+            float3 sigma_t = medium_sigma_t(*this, swl, md);
+            float3 sigma_s = spec_unbound(*this, swl, float3{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale});
             uint32_t channel = std::min((uint32_t)(sampler.next_1d() * 3.0f), 2u);
             float sc_t = channel == 0 ? sigma_t.x : (channel == 1 ? sigma_t.y : sigma_t.z);
             float dist = -vlog(1.0f - sampler.next_1d()) / sc_t;
@@ -409,7 +413,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
                 mi.inside = ray_medium; mi.outside = ray_medium;
                 it = mi;
             }
-            float3 tr = medium_Tr(md, t);
+            float3 tr = medium_Tr(*this, swl, md, t);
             float3 density = sampled_medium ? sigma_t * tr : tr;
             float pdf = average3(density);
             float3 mt = sampled_medium ? tr * sigma_s / pdf : tr / pdf;
@@ -422,20 +426,20 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
             continue;
         }
         if (it.light_id != VB_INVALID_ID) {                        // integrator.cpp:221-231
-            LightEval ev = evaluate_hit_wi(*this, ray.o, it);
-            float3 tr = ray_Tr(*this, ray_medium, ray);
+            LightEval ev = evaluate_hit_wi(*this, swl, ray.o, it);
+            float3 tr = ray_Tr(*this, swl, ray_medium, ray);
             float weight = mis_weight(scatter_pdf, ev.pdf);
             if (params.mis_mode == 2) weight = 1.f;
             else if (params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
-            ret += ev.L * throughput * weight * tr;
+            ret += spec_to_srgb(*this, swl, ev.L * throughput * weight * tr);
         }
         prev_surface_ng = it.ng;
         // light sampling + shadow ray, integrator.cpp:241-244
-        LightSample ls = sample_light(*this, it, sampler);
+        LightSample ls = sample_light(*this, swl, it, sampler);
         Ray shadow = spawn_ray_to(it, ls.p_light);
         uint32_t shadow_medium = mediums ? (dot(it.ng, shadow.d) > 0.f ? it.outside : it.inside) : VB_INVALID_ID;
         bool occluded = trace_any(shadow, st);
-        float3 tr = ray_Tr(*this, shadow_medium, shadow);
+        float3 tr = ray_Tr(*this, swl, shadow_medium, shadow);
         // material / phase function, integrator.cpp:246-283 + direct_lighting :20-37
         float3 wi = normalize(ls.p_light - it.pos);
         ScatterEval se;
@@ -445,11 +449,15 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
             se.f = float3{f, f, f}; se.pdf = f; se.flags = 0;
             bs = phase_sample(it.g, it.wo, sampler);
         } else if (materials[it.mat_id].type == VB_MAT_PRINCIPLED) {
-            PrincipledEvaluator evaluator{principled_create(*this, it), it.ng};
+            PrincipledEvaluator evaluator{principled_create(*this, swl, it), it.ng};
             se = evaluator.evaluate(*this, it.wo, wi);
             bs = evaluator.sample(*this, it.wo, sampler);
         } else {
-            Evaluator evaluator{create_lobe(*this, it), it.ng};
+            Evaluator evaluator{create_lobe(*this, swl, it), it.ng};
+            if (evaluator.lobe.dispersive && swl.hero) {            // SampledWavelengths::check_dispersive, integrator.cpp:264 + spectrum.cpp:21-38
+                swl_packed |= SwlInvalidBit;
+                swl.pdf[1] = 0.f; swl.pdf[2] = 0.f;
+            }
             se = evaluator.evaluate(*this, it.wo, wi);
             bs = evaluator.sample(*this, it.wo, sampler);
         }
@@ -460,7 +468,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
         float3 Ld{0, 0, 0};
         if (!occluded && se.pdf > 0.f && lpdf > 0.f) Ld = ls.eval.L * se.f * weight / lpdf;
         if (params.mis_mode == 2) Ld = Ld * 0.f;
-        ret += throughput * Ld * tr;
+        ret += spec_to_srgb(*this, swl, throughput * Ld * tr);
         eta_scale *= sqr(bs.eta);
         float lum = max_comp(throughput);
         if (!(bs.eval.pdf > 0.f) || lum == 0.f) break;

@@ -184,6 +184,16 @@ class OracleScene:
         if meds:
             arr = (capi.vb_medium_rec * len(meds))(*meds)
             lib.vo_scene_set_mediums(self.h, C.cast(arr, vp), len(meds))
+        if getattr(sc, "spds", None):
+            vals, offs = capi.pack_spds(sc.spds)
+            lib.vo_scene_set_spds.argtypes = [vp, vp, vp, C.c_uint32]; lib.vo_scene_set_spds.restype = None
+            lib.vo_scene_set_spds(self.h, _p(vals), _p(offs), len(sc.spds))
+        if getattr(sc, "rgb2spec", None) is not None:
+            spec = capi.vb_spectrum_rec.from_buffer_copy(sc.spectrum)
+            t = np.ascontiguousarray(sc.rgb2spec, np.float32)
+            spec.rgb2spec = t.ctypes.data
+            lib.vo_scene_set_spectrum.argtypes = [vp, vp]; lib.vo_scene_set_spectrum.restype = None
+            lib.vo_scene_set_spectrum(self.h, C.addressof(spec))
         lib.vo_scene_set_camera(self.h, C.addressof(sc.camera))
         lib.vo_scene_set_integrator(self.h, C.addressof(sc.params))
         lib.vo_scene_build(self.h, threads, 1 if brute else 0)

@@ -35,5 +35,11 @@ for m in re.finditer(r"ocarina::array\s+(\w+)\s*\{(.*?)\};", src, re.S):
     out[m.group(1)] = {"eta": [spd_eval(eta, l) for l in PEAKS], "k": [spd_eval(k, l) for l in PEAKS], "samples": len(pairs)}
 dst = Path(__file__).resolve().parent.parent / "vision_b200" / "data" / "metal_ior_srgb.json"
 dst.write_text(json.dumps(out, indent=1))
+# the full tables, for the "spd" eta / k slots MetalMaterial creates under a complete (hero) spectrum (metal.cpp:117-121)
+full = {}
+for m in re.finditer(r"ocarina::array\s+(\w+)\s*\{(.*?)\};", src, re.S):
+    pairs = re.findall(r"make_float2\(\s*([-+0-9.eE]+)f?\s*,\s*([-+0-9.eE]+)f?\s*\)", m.group(2))
+    full[m.group(1)] = {"eta": [float(f32(a)) for a, _ in pairs], "k": [float(f32(b)) for _, b in pairs]}
+(dst.parent / "metal_ior_spd.json").write_text(json.dumps(full))
 for k_, v in out.items():
     print(k_, v)

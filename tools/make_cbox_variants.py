@@ -6,6 +6,7 @@ cbox-dragon.json medium "fog").
                         right wall = metal (Cu)
   cbox_fog.json       : short box = glass boundary filled with the Skin1 medium (scale 20), global thin fog,
                         mediums.process = true
+  cbox_dispersion.json: hero-wavelength spectrum (hero.cpp) + dispersive BK7 glass + principled + spectral metal (config C4)
   cbox_projector.json : adds the projector light of the reference's cbox scene (image = checker.jpg), area light at 20 %
   cbox_lights.json    : the ceiling quad keeps its emission; adds a point light, a spot light (the reference's
                         commented examples in point.cpp:11-20 / spot.cpp:10-18) and a spherical environment
@@ -108,4 +109,13 @@ for s_ in pj["shapes"]:
     if "emission" in s_["param"]:
         s_["param"]["emission"]["param"]["scale"] = 0.2
 (root / "cbox_projector.json").write_text(json.dumps(pj, indent=1))
-print("wrote", root / "cbox_projector.json", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json", root / "cbox_sphere.json", root / "cbox_principled.json")
+# cbox_dispersion.json (config C4 "cbox-glass / dispersion spectral glass + Disney"): hero-wavelength spectrum, the short box is
+# BK7 glass (material_name -> dispersive "spd" ior slot, glass.cpp:216-234), the tall box the coated principled metal, metal (Cu,
+# spectral eta / k) right wall, substrate floor
+ds = copy.deepcopy(a)
+ds["materials"] += [m for m in g["materials"] if m["name"] == "P_metal"]
+assign(ds, {"shape_6": "P_metal"})
+ds["spectrum"] = {"type": "hero", "param": {"dimension": 3}}
+ds["integrator"]["param"]["max_depth"] = 16
+(root / "cbox_dispersion.json").write_text(json.dumps(ds, indent=1))
+print("wrote", root / "cbox_dispersion.json", root / "cbox_projector.json", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json", root / "cbox_sphere.json", root / "cbox_principled.json")

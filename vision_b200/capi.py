@@ -282,7 +282,7 @@ class vb_texture(C.Structure):
 
 
 class vb_material_rec(C.Structure):
-    _fields_ = [("type", C.c_uint32), ("flags", C.c_uint32), ("pad", C.c_uint32 * 2),
+    _fields_ = [("type", C.c_uint32), ("flags", C.c_uint32), ("spd", C.c_uint32 * 2),
                 ("color", vb_slot), ("roughness", vb_slot), ("spec", vb_slot), ("ior", vb_slot), ("sigma", vb_slot),
                 ("eta", C.c_float * 4), ("k", C.c_float * 4), ("params", C.c_float * 16)]
 
@@ -336,6 +336,32 @@ class vb_pt_params(C.Structure):
                 ("process_mediums", C.c_uint32), ("ray_offset_factor", C.c_float)]
 
 
+class vb_spectrum_rec(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("dimension", C.c_uint32), ("spd_x", C.c_uint32), ("spd_y", C.c_uint32),
+                ("spd_z", C.c_uint32), ("spd_d65", C.c_uint32), ("cie_y_integral", C.c_float), ("rgb2spec_res", C.c_uint32),
+                ("rgb2spec", C.c_void_p)]
+
+
+VB_SPECTRUM_SRGB, VB_SPECTRUM_HERO = 0, 1
+RGB2SPEC_FILE, RGB2SPEC_RES = "rgb2spec_srgb_3x64x64x64x4.f32", 64
+
+
+def load_rgb2spec() -> np.ndarray:
+    """the sRGB -> sigmoid-polynomial coefficient table of the hero spectrum, float[3][64][64][64][4]; written by
+    build() (tools/rgb2spec_opt.c - the reference's srgb2spec.h is not in its tree)"""
+    from pathlib import Path
+    f = Path(__file__).resolve().parent / "data" / RGB2SPEC_FILE
+    if not f.exists():
+        raise FileNotFoundError(f"{f} is missing: run __graft_entry__.build() (tools/rgb2spec_opt.c) first")
+    return np.fromfile(f, np.float32)
+
+
+def load_cie_1nm() -> np.ndarray:
+    """CIE 1931 X, Y, Z and D65 at 1 nm, 360..830 nm (4, 471) float32 (tools/extract_cie.py)"""
+    from pathlib import Path
+    return np.fromfile(Path(__file__).resolve().parent / "data" / "cie_1nm_4x471.f32", np.float32).reshape(4, 471)
+
+
 VB_MAT_DIFFUSE, VB_MAT_MIRROR, VB_MAT_GLASS, VB_MAT_METAL, VB_MAT_SUBSTRATE, VB_MAT_PRINCIPLED, VB_MAT_BLACK_BODY = range(7)
 VB_LIGHT_AREA, VB_LIGHT_POINT, VB_LIGHT_SPOT, VB_LIGHT_ENV, VB_LIGHT_PROJECTOR = range(5)
 VB_FILTER_BOX, VB_FILTER_TRIANGLE, VB_FILTER_FITTED = 0, 1, 2
@@ -360,6 +386,8 @@ def _bind_pt(lib):
         "vb_materials_set": [vp, C.POINTER(vb_material_rec), C.c_uint32],
         "vb_luts_set": [vp, C.c_int, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32],
         "vb_mediums_set": [vp, C.POINTER(vb_medium_rec), C.c_uint32],
+        "vb_spds_set": [vp, vp, vp, C.c_uint32],
+        "vb_spectrum_set": [vp, C.POINTER(vb_spectrum_rec)],
         "vb_lights_set": [vp, C.POINTER(vb_light_rec), C.c_uint32, C.POINTER(vb_alias_entry), vp, C.c_uint32],
         "vb_camera_set": [vp, C.POINTER(vb_camera)],
         "vb_integrator_set": [vp, C.POINTER(vb_pt_params)],
@@ -391,6 +419,9 @@ class SceneRecords:
         self.alias_func = []    # float
         self.textures = []      # (h, w, 4) float32 arrays
         self.mediums = []       # vb_medium_rec
+        self.spds = []          # SPD pool: float32 arrays (hero spectrum: CIE x, y, z, D65 first, then material curves)
+        self.spectrum = vb_spectrum_rec()   # rgb2spec is filled at upload time from `rgb2spec` below
+        self.rgb2spec = None    # float32 array 3 * res^3 * 4 (hero spectrum)
         self.luts = {}          # which -> (float32 array, (nx, ny, nz, channels)); filled when a material needs them
         self.camera = vb_camera()
         self.params = vb_pt_params()
@@ -398,6 +429,15 @@ class SceneRecords:
         self.exposure = 1.0
         self.tonemap = VB_TONEMAP_LINEAR
         self.spp = 1
+
+
+def pack_spds(spds):
+    """SPD pool -> (values float32, offsets uint32[n + 1]) as vb_spds_set takes them"""
+    offs = np.zeros(len(spds) + 1, np.uint32)
+    for i, s in enumerate(spds):
+        offs[i + 1] = offs[i] + len(s)
+    vals = np.ascontiguousarray(np.concatenate([np.asarray(s, np.float32) for s in spds]) if spds else np.zeros(1, np.float32), np.float32)
+    return vals, offs
 
 
 def _pt_methods():
@@ -426,6 +466,14 @@ def _pt_methods():
                 self._check(self.lib.vb_luts_set(self.h, which, None, 0, 0, 0, 0), "vb_luts_set")
         meds = (vb_medium_rec * max(1, len(sc.mediums)))(*sc.mediums)
         self._check(self.lib.vb_mediums_set(self.h, meds, len(sc.mediums)), "vb_mediums_set")
+        vals, offs = pack_spds(sc.spds)
+        self._check(self.lib.vb_spds_set(self.h, vals.ctypes.data, offs.ctypes.data, len(sc.spds)), "vb_spds_set")
+        spec = vb_spectrum_rec.from_buffer_copy(sc.spectrum)
+        t = None
+        if sc.rgb2spec is not None:
+            t = np.ascontiguousarray(sc.rgb2spec, np.float32)
+            spec.rgb2spec = t.ctypes.data
+        self._check(self.lib.vb_spectrum_set(self.h, C.byref(spec)), "vb_spectrum_set")
         lights = (vb_light_rec * max(1, len(sc.lights)))(*sc.lights)
         na = len(sc.alias_table)
         tab = (vb_alias_entry * max(1, na))(*[vb_alias_entry(p, a) for p, a in sc.alias_table])

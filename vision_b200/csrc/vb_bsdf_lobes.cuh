@@ -12,7 +12,9 @@ struct Lobe {
     f3 rs;                     // substrate Rs | metal eta
     f3 kk;                     // metal k
     GGX mf;
-    float eta;                 // glass: corrected relative ior (Interaction::correct_eta)
+    float eta;                 // glass: corrected relative ior (Interaction::correct_eta); dispersive: of the hero wavelength (eta[0])
+    f3 eta3;                   // dispersive glass (hero spectrum, ior slot = "spd", glass.cpp:221-234): corrected ior per wavelength
+    bool dispersive;
     bool oren_nayar; float on_A, on_B;
 };
 
@@ -36,10 +38,16 @@ __device__ float dielectric_compensate(const PtScene &S, const Lobe &lb, f3 wo) 
     float z = lb.eta > 1.0f ? (lb.eta - lo) / (hi - lo) : (1.0f / lb.eta - lo) / (hi - lo);
     return 1.0f / lut_sample3d_ch0(L, x, y, z);
 }
-__device__ __forceinline__ float dielectric_refl_prob(const Lobe &lb, float F) {
-    float T = 1.0f - F;
-    f3 total = lb.kr * T + splat(F);
-    return F / average3(total);
+// FresnelDielectric::evaluate (fresnel.h:84-89): a scalar ior slot gives a 1-dimensional spectrum (F.average() == F),
+// the dispersive "spd" slot one value per wavelength
+__device__ __forceinline__ f3 dielectric_F(const Lobe &lb, float cos_theta) {
+    if (!lb.dispersive) return splat(fresnel_dielectric(cos_theta, lb.eta));
+    return {fresnel_dielectric(cos_theta, lb.eta3.x), fresnel_dielectric(cos_theta, lb.eta3.y), fresnel_dielectric(cos_theta, lb.eta3.z)};
+}
+__device__ __forceinline__ float dielectric_refl_prob(const Lobe &lb, f3 F) {
+    f3 T = splat(1.0f) - F;
+    f3 total = lb.kr * T + F;
+    return (lb.dispersive ? average3(F) : F.x) / average3(total);
 }
 __device__ ScatterEval dielectric_evaluate_local(const PtScene &S, const Lobe &lb, f3 wo, f3 wi, bool flip_wh, float *eta_out) {
     bool reflect_ = same_hemisphere(wo, wi);
@@ -47,17 +55,17 @@ __device__ ScatterEval dielectric_evaluate_local(const PtScene &S, const Lobe &l
     if (eta_out) *eta_out = eta_p;
     f3 wh = normalize(wo + wi * eta_p);
     if (flip_wh) wh = face_forward(wh, wo);
-    float F = fresnel_dielectric(abs_dot(wh, wo), lb.eta);
+    f3 F = dielectric_F(lb, abs_dot(wh, wo));
     ScatterEval se;
     if (reflect_) {
-        se.f = splat(ggx_brdf_div_fr(lb.mf, wo, wh, wi) * F);
+        se.f = F * ggx_brdf_div_fr(lb.mf, wo, wh, wi);
         se.pdf = ggx_pdf_wi_reflection(lb.mf, wo, wh) * dielectric_refl_prob(lb, F);
         se.flags = FlagGlossy | FlagReflection;
         se.f = se.f * dielectric_compensate(S, lb, wo);
     } else {
         f3 new_wh = face_forward(wh, wo);
         f3 wh2 = normalize(wo + wi * lb.eta);
-        float tr = ggx_btdf_div_ft(lb.mf, wo, wh2, wi, lb.eta) * (1.0f - F);
+        f3 tr = (splat(1.0f) - F) * ggx_btdf_div_ft(lb.mf, wo, wh2, wi, lb.eta);
         se.f = lb.kr * tr;
         se.pdf = ggx_pdf_wi_transmission(lb.mf, wo, new_wh, wi, lb.eta) * (1.0f - dielectric_refl_prob(lb, F));
         se.flags = FlagGlossy | FlagTransmission;
@@ -161,7 +169,7 @@ __device__ BSDFSample lobe_sample(const PtScene &S, const Lobe &lb, f3 world_wo,
         case VB_MAT_GLASS: {
             f3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
             float d = dot(wo, wh);
-            float F = fresnel_dielectric(fabsf(d), lb.eta);
+            f3 F = dielectric_F(lb, fabsf(d));
             float uc = sampler.next_1d();
             if (uc < dielectric_refl_prob(lb, F)) {
                 wi = reflect(wo, wh);
@@ -201,18 +209,18 @@ __device__ BSDFSample lobe_sample(const PtScene &S, const Lobe &lb, f3 world_wo,
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fmin_(fmax_(v, lo), hi); }
 
 // Material::create_evaluator -> create_lobe_set of the plugin
-__device__ Lobe create_lobe(const PtScene &S, const Interaction &it) {
+__device__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction &it) {
     const vb_material_rec &m = S.materials[it.mat_id];
     Lobe lb;
     lb.type = m.type;
     lb.frame = it.shading;
     lb.kr = f3{0, 0, 0}; lb.rs = f3{0, 0, 0}; lb.kk = f3{0, 0, 0};
-    lb.mf = GGX{1.f, 1.f}; lb.eta = 1.f; lb.oren_nayar = false; lb.on_A = 1.f; lb.on_B = 0.f;
+    lb.mf = GGX{1.f, 1.f}; lb.eta = 1.f; lb.eta3 = f3{1, 1, 1}; lb.dispersive = false; lb.oren_nayar = false; lb.on_A = 1.f; lb.on_B = 0.f;
     bool remap = (m.flags & 2u) != 0;
     float anis = clampf(m.params[0], -0.9f, 0.9f);
     switch (m.type) {
         case VB_MAT_DIFFUSE:
-            lb.kr = eval_slot3(S, m.color, it.uv);
+            lb.kr = spec_albedo(S.spec, swl, eval_slot3(S, m.color, it.uv));
             if (m.flags & 1u) {
                 float sigma = eval_slot3(S, m.sigma, it.uv).x * PiOver2;
                 float sigma2 = sqr(sigma * sigma);
@@ -222,23 +230,33 @@ __device__ Lobe create_lobe(const PtScene &S, const Interaction &it) {
             }
             break;
         case VB_MAT_MIRROR: case VB_MAT_METAL: {
-            lb.kr = m.type == VB_MAT_MIRROR ? eval_slot3(S, m.color, it.uv) : splat(1.f);
+            lb.kr = m.type == VB_MAT_MIRROR ? spec_albedo(S.spec, swl, eval_slot3(S, m.color, it.uv)) : splat(1.f);
             float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
             lb.rs = f3{m.eta[0], m.eta[1], m.eta[2]}; lb.kk = f3{m.k[0], m.k[1], m.k[2]};
+            if (m.type == VB_MAT_METAL && (m.flags & 4u) && swl) {       // metal.cpp:117-121: "spd" eta / k slots
+                lb.rs = spd_eval3(S.spec, m.spd[0], *swl); lb.kk = spd_eval3(S.spec, m.spd[1], *swl);
+            }
         } break;
         case VB_MAT_GLASS: {
-            lb.kr = eval_slot3(S, m.color, it.uv);
+            lb.kr = spec_albedo(S.spec, swl, eval_slot3(S, m.color, it.uv));
             float ior = eval_slot3(S, m.ior, it.uv).x;
             lb.eta = dot(it.wo, it.ng) > 0.f ? ior : 1.0f / ior;
+            if ((m.flags & 4u) && swl) {                                 // glass.cpp:216-234: "material_name" curve in an "spd" slot
+                f3 iors = spd_eval3(S.spec, m.spd[0], *swl);
+                bool front = dot(it.wo, it.ng) > 0.f;
+                lb.eta3 = front ? iors : f3{1.0f / iors.x, 1.0f / iors.y, 1.0f / iors.z};
+                lb.eta = lb.eta3.x;
+                lb.dispersive = true;
+            }
             float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.01f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
         } break;
         case VB_MAT_SUBSTRATE: {
-            lb.kr = eval_slot3(S, m.color, it.uv);
-            lb.rs = eval_slot3(S, m.spec, it.uv);
+            lb.kr = spec_albedo(S.spec, swl, eval_slot3(S, m.color, it.uv));
+            lb.rs = spec_albedo(S.spec, swl, eval_slot3(S, m.spec, it.uv));
             float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);

@@ -22,6 +22,10 @@ struct DevInst {
 struct DevTex { const float4 *texels; uint32_t w, h; };
 struct DevLut { const float *data; uint32_t nx, ny, nz, channels; };
 
+}  // namespace
+#include "vb_spectrum.cuh"
+namespace {
+
 struct PtScene {
     VbAccelView accel;
     const DevMesh *meshes;
@@ -35,6 +39,7 @@ struct PtScene {
     const DevTex *textures;
     DevLut luts[VB_LUT_COUNT];
     const vb_medium_rec *mediums;
+    DevSpectrum spec;
     vb_camera cam;
     vb_pt_params params;
     uint32_t width, height;
@@ -176,10 +181,10 @@ __device__ uint32_t alias_sample(const PtScene &S, const vb_light_rec &l, float 
     return out;
 }
 
-__device__ LightEval area_evaluate_wi(const PtScene &S, const vb_light_rec &l, f3 ref_pos, const LightEvalCtx &pl) {
+__device__ LightEval area_evaluate_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, f3 ref_pos, const LightEvalCtx &pl) {
     LightEval ev;
     f3 w = ref_pos - pl.pos;
-    f3 color = eval_slot3(S, l.color, pl.uv);
+    f3 color = spec_illum(S.spec, swl, eval_slot3(S, l.color, pl.uv));
     float s = (dot(w, pl.ng) > 0.f || l.two_sided) ? 1.f : 0.f;
     ev.L = color * l.scale * s;
     float cos_theta = fabsf(dot(pl.ng, normalize(w)));
@@ -188,7 +193,7 @@ __device__ LightEval area_evaluate_wi(const PtScene &S, const vb_light_rec &l, f
     return ev;
 }
 
-__device__ LightSample area_sample_wi(const PtScene &S, const vb_light_rec &l, const Interaction &ref, f2 u) {
+__device__ LightSample area_sample_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, const Interaction &ref, f2 u) {
     float pmf, ux;
     uint32_t prim = alias_sample(S, l, u.x, pmf, ux);
     float su0 = __fsqrt_rn(ux);
@@ -197,7 +202,7 @@ __device__ LightSample area_sample_wi(const PtScene &S, const vb_light_rec &l, c
     LightEvalCtx pl{li.pos, li.ng, li.uv, 1.0f / li.prim_area};
     pl.pdf_pos *= pmf;
     LightSample ls;
-    ls.eval = area_evaluate_wi(S, l, ref.pos, pl);
+    ls.eval = area_evaluate_wi(S, swl, l, ref.pos, pl);
     f3 dir = ref.pos - pl.pos;
     float factor = dot(pl.ng, dir) > 0.f ? 1.f : -1.f;
     ls.p_light = offset_ray_origin(pl.pos, pl.ng * factor * S.params.ray_offset_factor);
@@ -205,10 +210,10 @@ __device__ LightSample area_sample_wi(const PtScene &S, const vb_light_rec &l, c
 }
 
 // ---- point / spot lights: render_core/light/point.cpp:36-42, spot.cpp:47-70, light.cpp:49-58 ----
-__device__ LightSample point_sample_wi(const PtScene &S, const vb_light_rec &l, const Interaction &ref) {
+__device__ LightSample point_sample_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, const Interaction &ref) {
     LightSample ls;
     f3 pos{l.position[0], l.position[1], l.position[2]};
-    f3 value = eval_slot3(S, l.color, f2{0, 0}) * l.scale;
+    f3 value = spec_illum(S.spec, swl, eval_slot3(S, l.color, f2{0, 0})) * l.scale;
     f3 w_un = ref.pos - pos;
     if (l.type == VB_LIGHT_POINT) ls.eval.L = value / length_squared(w_un);
     else if (l.type == VB_LIGHT_PROJECTOR) {                       // projector.cpp:99-112
@@ -220,7 +225,7 @@ __device__ LightSample point_sample_wi(const PtScene &S, const vb_light_rec &l, 
         f2 uv{(p.x + tan_x) / (2.f * tan_x), (p.y + tan_y) / (2.f * tan_y)};
         valid = valid && uv.x >= 0.f && uv.x <= 1.f && uv.y >= 0.f && uv.y <= 1.f;
         if (!valid) uv = f2{0.f, 0.f};
-        ls.eval.L = eval_slot3(S, l.color, uv) * (valid ? 1.f : 0.f) / d2 * l.scale;
+        ls.eval.L = spec_illum(S.spec, swl, eval_slot3(S, l.color, uv)) * (valid ? 1.f : 0.f) / d2 * l.scale;
     } else {
         f3 w = normalize(w_un);
         f3 dir{l.direction[0], l.direction[1], l.direction[2]};
@@ -274,22 +279,22 @@ __device__ __forceinline__ f2 env_calculate_uv(f3 local_dir) {
     float theta = vatan2(safe_sqrt(1.0f - cz * cz), cz);
     return {phi * Inv2Pi, theta * InvPi};
 }
-__device__ __forceinline__ f3 env_L(const PtScene &S, const vb_light_rec &l, f3 local_dir) {
-    return eval_slot3(S, l.color, env_calculate_uv(local_dir)) * l.scale;
+__device__ __forceinline__ f3 env_L(const PtScene &S, const Swl *swl, const vb_light_rec &l, f3 local_dir) {
+    return spec_illum(S.spec, swl, eval_slot3(S, l.color, env_calculate_uv(local_dir))) * l.scale;
 }
-__device__ LightEval env_evaluate_wi(const PtScene &S, const vb_light_rec &l, f3 ref_pos, f3 light_pos) {
+__device__ LightEval env_evaluate_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, f3 ref_pos, f3 light_pos) {
     LightEval ev;
     f3 world_dir = normalize(light_pos - ref_pos);
     f3 local_dir = transform_vector(l.w2o, world_dir);
     f2 uv = env_calculate_uv(local_dir);
     float s, c;
     sincos_2pi(uv.y * 0.5f, s, c);
-    ev.L = env_L(S, l, local_dir);
+    ev.L = env_L(S, swl, l, local_dir);
     float pdf = env_map_pdf(S, l, uv) / (2.0f * Pi * Pi * s);
     ev.pdf = s == 0.f ? 0.f : pdf;
     return ev;
 }
-__device__ LightSample env_sample_wi(const PtScene &S, const vb_light_rec &l, const Interaction &ref, f2 u) {
+__device__ LightSample env_sample_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, const Interaction &ref, f2 u) {
     LightSample ls;
     float pdf_map;
     f2 uv = env_sample_continuous(S, l, u, pdf_map);
@@ -300,7 +305,7 @@ __device__ LightSample env_sample_wi(const PtScene &S, const vb_light_rec &l, co
     f3 world_dir = normalize(transform_vector(l.o2w, local_dir));
     float pdf_dir = pdf_map / (2.0f * Pi * Pi * st);
     ls.eval.pdf = isinf(pdf_dir) ? 0.f : pdf_dir;
-    ls.eval.L = env_L(S, l, local_dir);
+    ls.eval.L = env_L(S, swl, l, local_dir);
     ls.p_light = ref.pos + world_dir * l.params[0];
     return ls;
 }
@@ -317,18 +322,18 @@ struct Sampler {
 namespace {
 
 // ---- homogeneous medium, reference render_core/medium/homogeneous.cpp:30-70 ----
-__device__ __forceinline__ f3 medium_sigma_t(const vb_medium_rec &m) {
-    return f3{m.sigma_a[0] + m.sigma_s[0], m.sigma_a[1] + m.sigma_s[1], m.sigma_a[2] + m.sigma_s[2]} * m.scale;
+__device__ __forceinline__ f3 medium_sigma_t(const PtScene &S, const Swl *swl, const vb_medium_rec &m) {
+    return spec_unbound(S.spec, swl, f3{m.sigma_a[0] + m.sigma_s[0], m.sigma_a[1] + m.sigma_s[1], m.sigma_a[2] + m.sigma_s[2]} * m.scale);
 }
-__device__ __forceinline__ f3 medium_Tr(const vb_medium_rec &m, float t) {
-    f3 st = medium_sigma_t(m);
+__device__ __forceinline__ f3 medium_Tr(const PtScene &S, const Swl *swl, const vb_medium_rec &m, float t) {
+    f3 st = medium_sigma_t(S, swl, m);
     float tt = fmin_(RayTMax, t);
     return {vexp(-st.x * tt), vexp(-st.y * tt), vexp(-st.z * tt)};
 }
 // Geometry::Tr (geometry.cpp:187-199)
-__device__ __forceinline__ f3 ray_Tr(const PtScene &S, uint32_t medium, const VbRay &ray) {
+__device__ __forceinline__ f3 ray_Tr(const PtScene &S, const Swl *swl, uint32_t medium, const VbRay &ray) {
     if (!S.params.process_mediums || medium == VB_INVALID_ID) return f3{1, 1, 1};
-    return medium_Tr(S.mediums[medium], length(f3{ray.dx, ray.dy, ray.dz}) * ray.tmax);
+    return medium_Tr(S, swl, S.mediums[medium], length(f3{ray.dx, ray.dy, ray.dz}) * ray.tmax);
 }
 __device__ __forceinline__ void coordinate_system(f3 n, f3 &a, f3 &b) {
     if (fabsf(n.x) > fabsf(n.y)) a = f3{-n.z, 0.f, n.x} / __fsqrt_rn(n.x * n.x + n.z * n.z);

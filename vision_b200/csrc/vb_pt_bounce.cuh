@@ -11,9 +11,16 @@ struct PathState {
     f3 throughput, ret;
     float eta_scale, scatter_pdf;
     uint32_t ray_medium, bounces;
+    uint32_t swl;              // hero spectrum: bits 0..23 wavelength draw, bit 31 secondary wavelengths invalidated (vb_spectrum.cuh)
 };
 
 __device__ __forceinline__ void path_begin(const PtScene &S, PathState &ps, uint32_t px, uint32_t py, uint32_t frame) {
+    ps.swl = 0;
+    if (S.params.spectrum == VB_SPECTRUM_HERO) {                  // RenderEnv::initial, integrator.cpp:48-57: sampler dimension -1
+        ps.sampler.start(px, py, frame, 0xffffffffu);
+        (void)ps.sampler.next_1d();
+        ps.swl = ps.sampler.state & 0x00ffffffu;
+    }
     ps.sampler.start(px, py, frame, 1u);
     ps.ray_medium = S.params.process_mediums != 0 ? S.cam.medium_id : VB_INVALID_ID;
     ps.scatter_pdf = 1e16f;
@@ -31,9 +38,16 @@ enum : int { PT_CONTINUE = 1, PT_SHADOW = 2, PT_VERTEX = 4, PT_LIGHT = 8 };
 // PT_SHADOW is a shadow ray the reference traces although its contribution is zero; it is culled here). Without PT_CONTINUE the path is finished: ps.ret
 // (+ pending) is the sample's radiance.
 // PRINCIPLED = the scene uses the principled BSDF: its LobeSet code (stack frame, out-of-line calls) is compiled
-// into a separate kernel instantiation so that scenes without it keep the lean kernel
-template <bool PRINCIPLED>
+// into a separate kernel instantiation so that scenes without it keep the lean kernel.
+// VARIANT: 0 = lean (srgb spectrum, no principled BSDF), 1 = + principled, 2 = hero spectrum (+ principled): only
+// variant 2 carries the path's wavelengths; in 0 and 1 `swl` is a compile-time nullptr and every spec_* call folds away.
+enum : int { PT_LEAN = 0, PT_PRINCIPLED = 1, PT_HERO = 2 };
+template <int VARIANT>
 __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay &ray, const VbHit &hit, VbRay &shadow, f3 &pending) {
+    constexpr bool PRINCIPLED = VARIANT >= PT_PRINCIPLED, HERO = VARIANT == PT_HERO;
+    Swl wl;
+    const Swl *swl = nullptr;
+    if (HERO) { wl = swl_make(ps.swl); swl = &wl; }
     Sampler &sampler = ps.sampler;
     const bool mediums = S.params.process_mediums != 0;
     const uint32_t bounces = ps.bounces;
@@ -41,14 +55,14 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         if (S.env_light != VB_INVALID_ID) {
             const vb_light_rec &l = S.lights[S.env_light];
             f3 tr{1, 1, 1};
-            if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(S, ps.ray_medium, ray); }
+            if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(S, swl, ps.ray_medium, ray); }
             f3 ro{ray.ox, ray.oy, ray.oz}, rd{ray.dx, ray.dy, ray.dz};
-            LightEval ev = env_evaluate_wi(S, l, ro, ro + rd);
+            LightEval ev = env_evaluate_wi(S, swl, l, ro, ro + rd);
             ev.pdf *= 1.0f / (float)S.n_lights;
             float weight = mis_weight(ps.scatter_pdf, ev.pdf);
             if (S.params.mis_mode == 2) weight = 1.f;
             else if (S.params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
-            ps.ret = ps.ret + ev.L * tr * weight * ps.throughput;
+            ps.ret = ps.ret + spec_to_srgb(S.spec, swl, ev.L * tr * weight * ps.throughput);
         }
         return 0;
     }
@@ -58,8 +72,8 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
     ray.tmax = length(it.pos - ro) / length(rd);             // geometry.h:64-69
     if (mediums && ps.ray_medium != VB_INVALID_ID) {         // integrator.cpp:199-206, homogeneous.cpp:50-70
         const vb_medium_rec &md = S.mediums[ps.ray_medium];
-        f3 sigma_t = medium_sigma_t(md);
-        f3 sigma_s{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale};
+        f3 sigma_t = medium_sigma_t(S, swl, md);
+        f3 sigma_s = spec_unbound(S.spec, swl, f3{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale});
         uint32_t channel = min((uint32_t)(sampler.next_1d() * 3.0f), 2u);
         float sc_t = channel == 0 ? sigma_t.x : (channel == 1 ? sigma_t.y : sigma_t.z);
         float dist = -vlog(1.0f - sampler.next_1d()) / sc_t;
@@ -76,7 +90,7 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
             it.has_phase = true; it.g = md.g;
             it.inside = ps.ray_medium; it.outside = ps.ray_medium;
         }
-        f3 tr = medium_Tr(md, t);
+        f3 tr = medium_Tr(S, swl, md, t);
         f3 density = sampled_medium ? sigma_t * tr : tr;
         float pdf = average3(density);
         f3 mt = sampled_medium ? tr * sigma_s / pdf : tr / pdf;
@@ -93,15 +107,15 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         if (l.type == VB_LIGHT_AREA) {
             LightEvalCtx pl{it.pos, it.ng, it.uv, 1.0f / it.prim_area};
             pl.pdf_pos *= alias_pmf(S, l, it.prim_id);
-            ev = area_evaluate_wi(S, l, ro, pl);
+            ev = area_evaluate_wi(S, swl, l, ro, pl);
             ev.pdf *= 1.0f / (float)S.n_lights;
         }
-        f3 tr = ray_Tr(S, ps.ray_medium, ray);
+        f3 tr = ray_Tr(S, swl, ps.ray_medium, ray);
         float weight = mis_weight(ps.scatter_pdf, ev.pdf);
         if (S.params.mis_mode == 2) weight = 1.f;
         else if (S.params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
         f3 d = ev.L * ps.throughput * weight * tr;
-        ps.ret = ps.ret + d;
+        ps.ret = ps.ret + spec_to_srgb(S.spec, swl, d);
     }
     // light sampling
     float u_light = sampler.next_1d();
@@ -111,14 +125,14 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         uint32_t n = S.n_lights;
         uint32_t index = (uint32_t)fmin_(u_light * (float)n, (float)n - 1.0f);
         const vb_light_rec &l = S.lights[index];
-        if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(S, l, it, u_surface);
-        else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(S, l, it, u_surface);
-        else ls = point_sample_wi(S, l, it);
+        if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(S, swl, l, it, u_surface);
+        else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(S, swl, l, it, u_surface);
+        else ls = point_sample_wi(S, swl, l, it);
         ls.eval.pdf *= 1.0f / (float)n;
     }
     shadow = spawn_ray_to(it, ls.p_light);
     uint32_t shadow_medium = mediums ? (dot(it.ng, f3{shadow.dx, shadow.dy, shadow.dz}) > 0.f ? it.outside : it.inside) : VB_INVALID_ID;
-    f3 tr = ray_Tr(S, shadow_medium, shadow);
+    f3 tr = ray_Tr(S, swl, shadow_medium, shadow);
     // material / phase function, integrator.cpp:246-283 + direct_lighting :20-37
     f3 wi = normalize(ls.p_light - it.pos);
     ScatterEval se;
@@ -128,13 +142,17 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         se.f = f3{f, f, f}; se.pdf = f; se.flags = 0;
         bs = phase_sample(it.g, it.wo, sampler);
     } else if (PRINCIPLED && S.materials[it.mat_id].type == VB_MAT_PRINCIPLED) {
-        PrincipledSet set = principled_create(S, it);
+        PrincipledSet set = principled_create(S, swl, it);
         se = principled_evaluate(S, set, it.wo, wi, nullptr);
         hemisphere_discard(se, it.wo, wi, it.ng);
         bs = principled_sample(S, set, it.wo, sampler);
         hemisphere_discard(bs.eval, it.wo, bs.wi, it.ng);
     } else {
-        Lobe lobe = create_lobe(S, it);
+        Lobe lobe = create_lobe(S, swl, it);
+        if (HERO && lobe.dispersive) {                             // SampledWavelengths::check_dispersive, integrator.cpp:264 + spectrum.cpp:21-38
+            ps.swl |= SwlInvalidBit;
+            wl.pdf[1] = 0.f; wl.pdf[2] = 0.f;
+        }
         se = lobe_evaluate(S, lobe, it.wo, wi, false, nullptr);
         hemisphere_discard(se, it.wo, wi, it.ng);
         bs = lobe_sample(S, lobe, it.wo, sampler);
@@ -149,7 +167,7 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
     pending = f3{0, 0, 0};
     if (se.pdf > 0.f && lpdf > 0.f && S.params.mis_mode != 2) {
         f3 Ld = ls.eval.L * se.f * weight / lpdf;
-        pending = ps.throughput * Ld * tr;
+        pending = spec_to_srgb(S.spec, swl, ps.throughput * Ld * tr);
         if (pending.x != 0.f || pending.y != 0.f || pending.z != 0.f) flags |= PT_SHADOW;      // ret + 0 == ret
     }
     ps.eta_scale *= sqr(bs.eta);

@@ -11,7 +11,7 @@ struct PtCounters { unsigned long long closest, any, vertices, culled; };
 // any-hit call site whatever bounce or frame each of them is at, and a lane whose path ended starts
 // its next frame in the same iteration instead of waiting for the longest path of the warp. The
 // running film value stays in registers and is written once per launch.
-template <bool DUMP_PRIMARY, bool PRINCIPLED>
+template <bool DUMP_PRIMARY, int VARIANT>
 __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t first_frame, uint32_t n_frames, uint32_t stride, int mode,
                                                          uint32_t frames_done, float4 *rt, float4 *accum, PtCounters *counters,
                                                          uint32_t *h_inst, uint32_t *h_prim, float *h_u, float *h_v, float *h_t) {
@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
         int flags = 0;
         VbRay shadow;
         f3 pending{0, 0, 0};
-        if (run) flags = pt_bounce<PRINCIPLED>(S, ps, ray, hit, shadow, pending);
+        if (run) flags = pt_bounce<VARIANT>(S, ps, ray, hit, shadow, pending);
         if (flags & PT_VERTEX) c_vert++;
         if ((flags & PT_LIGHT) && !(flags & PT_SHADOW)) c_culled++;
         if (flags & PT_SHADOW) {
@@ -137,6 +137,9 @@ struct vb_pt_state {
     DevTex *d_tex = nullptr; std::vector<float4 *> tex_mem;
     DevLut luts[VB_LUT_COUNT] = {};
     vb_medium_rec *d_mediums = nullptr; uint32_t n_mediums = 0;
+    float *d_spd_values = nullptr; uint32_t *d_spd_offsets = nullptr; uint32_t n_spds = 0;
+    float *d_rgb2spec = nullptr; vb_spectrum_rec spectrum{}; bool have_spectrum = false;
+    std::vector<vb_material_rec> h_mat;            // kept for the SPD index checks at render time
     vb_camera cam{}; bool have_cam = false;
     vb_pt_params params{}; bool have_params = false;
     uint32_t w = 0, h = 0;
@@ -162,6 +165,7 @@ void vb_pt_destroy(vb_ctx *ctx) {
     for (auto t : p->tex_mem) cudaFree(t);
     for (auto &l : p->luts) cudaFree((void *)l.data);
     cudaFree(p->d_mediums);
+    cudaFree(p->d_spd_values); cudaFree(p->d_spd_offsets); cudaFree(p->d_rgb2spec);
     cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output); cudaFree(p->d_counters);
     if (p->wf) { wf_free(*p->wf); delete p->wf; }
     delete p;
@@ -243,6 +247,7 @@ int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n) {
     for (uint32_t i = 0; i < n; ++i) types |= 1u << mat[i].type;
     p->n_mat_types = (uint32_t)__builtin_popcount(types);
     p->has_principled = (types >> VB_MAT_PRINCIPLED) & 1u;
+    p->h_mat.assign(mat, mat + n);
     if (n) {
         VB_CUDA(cudaMalloc(&p->d_mat, sizeof(vb_material_rec) * n));
         VB_CUDA(cudaMemcpy(p->d_mat, mat, sizeof(vb_material_rec) * n, cudaMemcpyHostToDevice));
@@ -278,6 +283,42 @@ int vb_mediums_set(vb_ctx *ctx, const vb_medium_rec *med, uint32_t n) {
     if (n) {
         VB_CUDA(cudaMalloc(&p->d_mediums, sizeof(vb_medium_rec) * n));
         VB_CUDA(cudaMemcpy(p->d_mediums, med, sizeof(vb_medium_rec) * n, cudaMemcpyHostToDevice));
+    }
+    return VB_OK;
+}
+
+int vb_spds_set(vb_ctx *ctx, const float *values, const uint32_t *offsets, uint32_t n) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (n && (!values || !offsets)) return ctx->fail(VB_ERR_INVALID, "vb_spds_set: null argument");
+    cudaSetDevice(ctx->device);
+    vb_pt_state *p = pt_state(ctx);
+    for (uint32_t i = 0; i < n; ++i)
+        if (offsets[i + 1] < offsets[i] + 2) return ctx->fail(VB_ERR_INVALID, "vb_spds_set: an SPD needs at least 2 samples and ascending offsets");
+    cudaFree(p->d_spd_values); cudaFree(p->d_spd_offsets);
+    p->d_spd_values = nullptr; p->d_spd_offsets = nullptr; p->n_spds = n;
+    if (n) {
+        VB_CUDA(cudaMalloc(&p->d_spd_values, sizeof(float) * offsets[n]));
+        VB_CUDA(cudaMemcpy(p->d_spd_values, values, sizeof(float) * offsets[n], cudaMemcpyHostToDevice));
+        VB_CUDA(cudaMalloc(&p->d_spd_offsets, sizeof(uint32_t) * (n + 1)));
+        VB_CUDA(cudaMemcpy(p->d_spd_offsets, offsets, sizeof(uint32_t) * (n + 1), cudaMemcpyHostToDevice));
+    }
+    return VB_OK;
+}
+
+int vb_spectrum_set(vb_ctx *ctx, const vb_spectrum_rec *spec) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (!spec) return ctx->fail(VB_ERR_INVALID, "vb_spectrum_set: null argument");
+    cudaSetDevice(ctx->device);
+    vb_pt_state *p = pt_state(ctx);
+    if (spec->type > VB_SPECTRUM_HERO) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_spectrum_set: unknown spectrum type");
+    cudaFree(p->d_rgb2spec); p->d_rgb2spec = nullptr;
+    p->spectrum = *spec; p->spectrum.rgb2spec = nullptr; p->have_spectrum = true;
+    if (spec->type == VB_SPECTRUM_HERO) {
+        if (spec->dimension != 3) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_spectrum_set: hero spectrum is implemented for dimension 3 only");
+        if (!spec->rgb2spec || spec->rgb2spec_res < 2) return ctx->fail(VB_ERR_INVALID, "vb_spectrum_set: hero spectrum needs the rgb2spec coefficient table");
+        size_t bytes = sizeof(float) * 3 * 4 * (size_t)spec->rgb2spec_res * spec->rgb2spec_res * spec->rgb2spec_res;
+        VB_CUDA(cudaMalloc(&p->d_rgb2spec, bytes));
+        VB_CUDA(cudaMemcpy(p->d_rgb2spec, spec->rgb2spec, bytes, cudaMemcpyHostToDevice));
     }
     return VB_OK;
 }
@@ -324,7 +365,7 @@ int vb_camera_set(vb_ctx *ctx, const vb_camera *cam) {
 int vb_integrator_set(vb_ctx *ctx, const vb_pt_params *prm) {
     if (!ctx || !prm) return VB_ERR_INVALID;
     vb_pt_state *p = pt_state(ctx);
-    if (prm->spectrum != 0 || prm->sampler != 0) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_integrator_set: only srgb spectrum + independent sampler");
+    if (prm->spectrum > VB_SPECTRUM_HERO || prm->sampler != 0) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_integrator_set: srgb / hero spectrum + independent sampler only");
     p->params = *prm; p->have_params = true;
     return VB_OK;
 }
@@ -372,6 +413,17 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     S.alias_table = p->d_alias; S.alias_func = p->d_func; S.textures = p->d_tex;
     for (int k = 0; k < VB_LUT_COUNT; ++k) S.luts[k] = p->luts[k];
     S.mediums = p->d_mediums;
+    if (p->params.spectrum > VB_SPECTRUM_HERO) return ctx->fail(VB_ERR_UNSUPPORTED, std::string(fn) + ": unknown spectrum type");
+    if (p->params.spectrum == VB_SPECTRUM_HERO) {
+        const vb_spectrum_rec &sp = p->spectrum;
+        if (!p->have_spectrum || sp.type != VB_SPECTRUM_HERO || !p->d_rgb2spec) return ctx->fail(VB_ERR_STATE, std::string(fn) + ": hero spectrum selected but vb_spectrum_set was not called with it");
+        if (sp.spd_x >= p->n_spds || sp.spd_y >= p->n_spds || sp.spd_z >= p->n_spds || sp.spd_d65 >= p->n_spds)
+            return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": spectrum SPD index out of range (vb_spds_set)");
+        for (auto &m : p->h_mat)
+            if ((m.flags & 4u) && (m.spd[0] >= p->n_spds || (m.type == VB_MAT_METAL && m.spd[1] >= p->n_spds)))
+                return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": material SPD index out of range (vb_spds_set)");
+        S.spec = DevSpectrum{p->d_rgb2spec, sp.rgb2spec_res, p->d_spd_values, p->d_spd_offsets, sp.spd_x, sp.spd_y, sp.spd_z, sp.spd_d65, sp.cie_y_integral};
+    }
     if (p->params.process_mediums) {
         auto bad = [&](uint32_t id) { return id != VB_INVALID_ID && id >= p->n_mediums; };
         if (bad(p->cam.medium_id)) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": camera medium_id out of range");
@@ -410,10 +462,12 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     unsigned grid = (n_pix + PT_BLOCK - 1) / PT_BLOCK;
     VB_CUDA(cudaMemsetAsync(p->d_counters, 0, sizeof(PtCounters), ctx->stream));
     ctx->prof_begin("path_trace", 1);
-    if (dump) k_path_trace<true, false><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, 1, 1, mode, 0, p->rt, p->accum, p->d_counters, hi, hp, hu, hv, ht);
-    else if (p->has_principled) k_path_trace<false, true><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum,
+    if (dump) k_path_trace<true, PT_LEAN><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, 1, 1, mode, 0, p->rt, p->accum, p->d_counters, hi, hp, hu, hv, ht);
+    else if (S.params.spectrum == VB_SPECTRUM_HERO) k_path_trace<false, PT_HERO><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt,
+                                                                                                               p->accum, p->d_counters, nullptr, nullptr, nullptr, nullptr, nullptr);
+    else if (p->has_principled) k_path_trace<false, PT_PRINCIPLED><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum,
                                                                                            p->d_counters, nullptr, nullptr, nullptr, nullptr, nullptr);
-    else k_path_trace<false, false><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum, p->d_counters,
+    else k_path_trace<false, PT_LEAN><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum, p->d_counters,
                                                                        nullptr, nullptr, nullptr, nullptr, nullptr);
     ctx->prof_end();
     VB_CHECK_LAUNCH();

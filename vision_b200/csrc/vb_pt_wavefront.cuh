@@ -28,7 +28,7 @@ struct WfCounters { uint32_t n_next, n_shadow, pad0, pad1; unsigned long long ve
 struct WfState {
     float4 *a;      // throughput.xyz, eta_scale
     float4 *b;      // ret.xyz, scatter_pdf
-    uint4 *c;       // sampler state, ray_medium, bounces, -
+    uint4 *c;       // sampler state, ray_medium, bounces, hero wavelength word (PathState::swl)
 };
 // a ray queue: AoS ray records (o.xyz, tmin)(d.xyz, tmax), the sort record (vb_ray_sort_key << 32 | queue index)
 // the trace kernel orders its fetches by, and the path slot each entry belongs to
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(256) k_wf_generate(PtScene S, uint32_t first_f
     Q.slot[slot] = slot;
     st.a[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.eta_scale);
     st.b[slot] = make_float4(ps.ret.x, ps.ret.y, ps.ret.z, ps.scatter_pdf);
-    st.c[slot] = make_uint4(ps.sampler.state, ps.ray_medium, ps.bounces, 0u);
+    st.c[slot] = make_uint4(ps.sampler.state, ps.ray_medium, ps.bounces, ps.swl);
 }
 
 // shading order: entries with the same material run in the same warps (one 8-bit radix pass over these records)
@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(256) k_wf_material_keys(PtScene S, uint32_t n,
 }
 
 // one Li vertex per queue entry; entry i of the launch is queue position order[i] (low word)
-template <bool PRINCIPLED>
+template <int VARIANT>
 #ifndef VB_SHADE_MIN_BLOCKS
 #define VB_SHADE_MIN_BLOCKS 4
 #endif
@@ -106,13 +106,13 @@ __global__ void __launch_bounds__(128, VB_SHADE_MIN_BLOCKS) k_wf_shade(PtScene S
         PathState ps;
         ps.throughput = f3{a.x, a.y, a.z}; ps.eta_scale = a.w;
         ps.ret = f3{b.x, b.y, b.z}; ps.scatter_pdf = b.w;
-        ps.sampler.state = c.x; ps.ray_medium = c.y; ps.bounces = c.z;
-        flags = pt_bounce<PRINCIPLED>(S, ps, ray, hit, shadow, pending);
+        ps.sampler.state = c.x; ps.ray_medium = c.y; ps.bounces = c.z; ps.swl = c.w;
+        flags = pt_bounce<VARIANT>(S, ps, ray, hit, shadow, pending);
         if ((flags & PT_CONTINUE) && ps.bounces >= S.params.max_depth) flags &= ~PT_CONTINUE;
         st.b[slot] = make_float4(ps.ret.x, ps.ret.y, ps.ret.z, ps.scatter_pdf);
         if (flags & PT_CONTINUE) {
             st.a[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.eta_scale);
-            st.c[slot] = make_uint4(ps.sampler.state, ps.ray_medium, ps.bounces, 0u);
+            st.c[slot] = make_uint4(ps.sampler.state, ps.ray_medium, ps.bounces, ps.swl);
         }
     }
     // queue appends: one atomic per warp and queue

@@ -102,8 +102,9 @@ static int wf_render_batch(vb_ctx *ctx, vb_pt_state *p, vb_wf_buffers &w, const 
             rc = wf_sort_by_material(ctx, w, k0, k1, n, &order);
             if (rc) { ctx->prof_end(); return rc; }
         }
-        if (p->has_principled) k_wf_shade<true><<<(n + 127) / 128, 128, 0, st>>>(S, n, Qin, order, w.hits4, w.st, Qout, Qsh, w.sh_pend, B, w.d_cnt);
-        else k_wf_shade<false><<<(n + 127) / 128, 128, 0, st>>>(S, n, Qin, order, w.hits4, w.st, Qout, Qsh, w.sh_pend, B, w.d_cnt);
+        if (S.params.spectrum == VB_SPECTRUM_HERO) k_wf_shade<PT_HERO><<<(n + 127) / 128, 128, 0, st>>>(S, n, Qin, order, w.hits4, w.st, Qout, Qsh, w.sh_pend, B, w.d_cnt);
+        else if (p->has_principled) k_wf_shade<PT_PRINCIPLED><<<(n + 127) / 128, 128, 0, st>>>(S, n, Qin, order, w.hits4, w.st, Qout, Qsh, w.sh_pend, B, w.d_cnt);
+        else k_wf_shade<PT_LEAN><<<(n + 127) / 128, 128, 0, st>>>(S, n, Qin, order, w.hits4, w.st, Qout, Qsh, w.sh_pend, B, w.d_cnt);
         ctx->prof_end();
         VB_CHECK_LAUNCH();
         VB_CUDA(cudaMemcpyAsync(w.h_cnt, w.d_cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, st));

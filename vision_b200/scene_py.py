@@ -411,7 +411,27 @@ def glass_ior(name, lam=602.785):
     return float(f32(np.sqrt(f32(acc + f32(1)))))
 
 
-def _material_record(m, textures, base, spectrum_complete=False):
+def setup_hero_spectrum(sc, dimension=3):
+    """HeroWavelengthSpectrum ctor (hero.cpp:235-245): 5 nm SPDs of the CIE observer and D65 (SPD::create_cie_*, spd.cpp:24-30,89-103:
+    every 5th of the 1 nm samples, ceil(470 / 5) = 94 of them), SPD::cie_y_integral (spd.cpp:11-21,105-108) and the coefficient table"""
+    if dimension != 3:
+        raise NotImplementedError("hero spectrum: dimension 3 only")
+    cie = capi.load_cie_1nm()
+    n = int(np.ceil(f32(470.0) / f32(5.0)))
+    sc.spds = [np.ascontiguousarray(cie[k][0:n * 5:5], np.float32) for k in range(4)]
+    s = f32(0.0)
+    for i in range(int(f32(470.0) / f32(5.0))):
+        s = f32(s + f32(f32(0.5) * f32(cie[1][i * 5] + cie[1][(i + 1) * 5])))
+    sp = sc.spectrum
+    sp.type, sp.dimension = capi.VB_SPECTRUM_HERO, 3
+    sp.spd_x, sp.spd_y, sp.spd_z, sp.spd_d65 = 0, 1, 2, 3
+    sp.cie_y_integral = float(f32(s * f32(5.0)))
+    sp.rgb2spec_res = capi.RGB2SPEC_RES
+    sc.rgb2spec = capi.load_rgb2spec()
+    sc.params.spectrum = capi.VB_SPECTRUM_HERO
+
+
+def _material_record(m, textures, base, spectrum_complete=False, spds=None):
     """plugin -> POD record: diffuse.cpp:36-42, mirror.cpp:35-41, glass.cpp:183-238, metal.cpp:59-133, substrate.cpp:113-124"""
     prm = m.get("param", {})
     rec = capi.vb_material_rec()
@@ -439,6 +459,13 @@ def _material_record(m, textures, base, spectrum_complete=False):
         name = prm.get("material_name", "")
         ior = _number(prm.get("ior"), 1.5) if not name else glass_ior(name)
         rec.ior = make_slot([ior] * 3)
+        if name and spectrum_complete:                             # glass.cpp:221-224: SPD::to_list(curve): 360, 365, ... < 830 nm
+            rec.flags |= 4
+            rec.spd[0] = len(spds)
+            lst, lam = [], f32(360.0)
+            while lam < f32(830.0):
+                lst.append(glass_ior(name, lam)); lam = f32(lam + f32(5.0))
+            spds.append(np.asarray(lst, np.float32))
     elif t == "metal":
         rec.type = capi.VB_MAT_METAL
         rec.roughness = make_slot([_number(prm.get("roughness"), 0.01)] * 3)
@@ -447,6 +474,11 @@ def _material_record(m, textures, base, spectrum_complete=False):
         names = sorted(table)                                  # std::map order; unknown name -> first key (metal.cpp:106-108)
         e = table[name if name in table else names[0]]
         rec.eta[:3] = e["eta"]; rec.k[:3] = e["k"]
+        if spectrum_complete:                                      # metal.cpp:117-121: the full measured tables as "spd" slots
+            full = json.loads((_DATA / "metal_ior_spd.json").read_text())[name if name in table else names[0]]
+            rec.flags |= 4
+            rec.spd[0] = len(spds); spds.append(np.asarray(full["eta"], np.float32))
+            rec.spd[1] = len(spds); spds.append(np.asarray(full["k"], np.float32))
     elif t == "substrate":
         rec.type = capi.VB_MAT_SUBSTRATE
         rec.color = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
@@ -720,6 +752,12 @@ def build_scene(path, overrides=None) -> SceneRecords:
         mat_index.setdefault(m["name"], len(mat_descs))
         mat_descs.append(m)
     sc.mediums, med_index, process_mediums, global_medium = _medium_records(d)
+    spec_type = ov.get("spectrum", d.get("spectrum", {}).get("type", "srgb"))       # SpectrumDesc, scene_desc.cpp:39
+    hero = spec_type == "hero"
+    if hero:
+        setup_hero_spectrum(sc, int(d.get("spectrum", {}).get("param", {}).get("dimension", 3)))
+    elif spec_type != "srgb":
+        raise NotImplementedError(f"spectrum {spec_type}")
     if "process_mediums" in ov:
         process_mediums = ov["process_mediums"]
     gm = med_index.get(global_medium, VB_INVALID_ID)
@@ -755,7 +793,7 @@ def build_scene(path, overrides=None) -> SceneRecords:
     used = sorted({i["material_id"] for i in sc.instances if i["material_id"] != VB_INVALID_ID})
     remap = {old: new for new, old in enumerate(used)}
     for old in used:
-        rec = _material_record(mat_descs[old], sc.textures, base)
+        rec = _material_record(mat_descs[old], sc.textures, base, hero, sc.spds)
         if rec is None:
             raise NotImplementedError(f"material {mat_descs[old]['name']} ({mat_descs[old]['type']})")
         sc.materials.append(rec)
