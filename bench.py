@@ -46,6 +46,8 @@ def parse():
     p.add_argument("--no-classroom", action="store_true")
     p.add_argument("--dragon-spp", type=int, default=16)
     p.add_argument("--no-dragon", action="store_true")
+    p.add_argument("--dispersion-spp", type=int, default=64)
+    p.add_argument("--no-dispersion", action="store_true")
     p.add_argument("--opt", action="append", default=[], help="library option key=value (vb_ctx_set_option), e.g. build.ploc=0")
     return p.parse_args()
 
@@ -150,7 +152,8 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
     with ONE NCCL all-reduce of the SUM film followed by the fused resolve. Returns samples/s and Mrays/s (whole
     job). which = "cbox": cbox-matte (BASELINE.json configs[0] geometry at 1024x1024, depth 5);
     "classroom": BASELINE.json configs[4] (1920x1080, depth 16, env map + fog + glass/metal/substrate);
-    "dragon": configs[2] (cbox-dragon 1024x1024, depth 16, glass model with a scattering medium inside)."""
+    "dragon": configs[2] (cbox-dragon 1024x1024, depth 16, glass model with a scattering medium inside);
+    "dispersion": configs[3] (hero-wavelength spectrum, dispersive BK7 glass + principled + spectral metal, 1024x1024, depth 16)."""
     import torch
     import torch.distributed as dist
     from vision_b200 import Context, scene_py, capi
@@ -158,6 +161,9 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
     if which == "cbox":
         sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", dict(scene_py.CBOX_MATTE_OVERRIDES, resolution=[a.pt_res, a.pt_res]))
         spp_rank, label = a.pt_spp, "cbox matte"
+    elif which == "dispersion":
+        sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_dispersion.json", {"resolution": [a.pt_res, a.pt_res]})
+        spp_rank, label = a.dispersion_spp, "cbox dispersion (hero spectrum, BK7 glass + principled + Cu)"
     elif which == "dragon":
         # config C3 through the C++ host layer (871 k-triangle OBJ: the Python twin's loader is for small files)
         from vision_b200 import host_api
@@ -378,6 +384,7 @@ def main():
     pt = None if a.no_pt else pt_section(a, rank, world, local_rank, stream)
     pt_room = None if (a.no_pt or a.no_classroom) else pt_section(a, rank, world, local_rank, stream, "classroom")
     pt_dragon = None if (a.no_pt or a.no_dragon) else pt_section(a, rank, world, local_rank, stream, "dragon")
+    pt_disp = None if (a.no_pt or a.no_dispersion) else pt_section(a, rank, world, local_rank, stream, "dispersion")
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -422,6 +429,8 @@ def main():
             line["path_tracer_classroom"] = pt_room
         if pt_dragon is not None:
             line["path_tracer_cbox_dragon"] = pt_dragon
+        if pt_disp is not None:
+            line["path_tracer_cbox_dispersion"] = pt_disp
         if world == 1 and not a.no_cpu_baseline:
             cb = cpu_arm(a, mesh, rays, 0, 2, 1)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}

@@ -54,7 +54,7 @@ def test_host_records_equal_python_twin():
     assert any("denoiser" in s or "ignored" in s for s in hp.log()) or True
 
 
-@pytest.mark.parametrize("name", ["cbox_materials", "cbox_fog", "cbox_principled"])
+@pytest.mark.parametrize("name", ["cbox_materials", "cbox_fog", "cbox_principled", "cbox_dispersion"])
 def test_host_records_equal_python_twin_materials_and_mediums(name):
     """mirror / glass / metal / substrate plugins, homogeneous medium, per-shape and global medium ids, LUT loading"""
     path = ROOT / "scenes" / "cbox" / f"{name}.json"
@@ -74,6 +74,15 @@ def test_host_records_equal_python_twin_materials_and_mediums(name):
     assert sorted(a.luts) == sorted(b.luts)
     for k in a.luts:
         assert a.luts[k][1] == b.luts[k][1] and np.array_equal(a.luts[k][0], b.luts[k][0])
+    # spectrum plugin: srgb = empty pool; hero (cbox_dispersion) = CIE x, y, z, D65 + the BK7 curve + Cu eta, k
+    sa, sb = capi.vb_spectrum_rec.from_buffer_copy(a.spectrum), capi.vb_spectrum_rec.from_buffer_copy(b.spectrum)
+    sa.rgb2spec = sb.rgb2spec = None
+    assert _bytes(sa) == _bytes(sb)
+    assert len(a.spds) == len(b.spds) and all(np.array_equal(x, y) for x, y in zip(a.spds, b.spds))
+    if name == "cbox_dispersion":
+        assert a.params.spectrum == capi.VB_SPECTRUM_HERO and len(a.spds) == 7 and [len(s) for s in a.spds[:5]] == [94] * 5
+        assert abs(a.spectrum.cie_y_integral - 106.857) < 0.01          # integral of the CIE 1931 y-bar, 360..830 nm
+        assert "vision-spectrum-hero#constructor" in host_api.plugin_names()
     if name == "cbox_fog":
         assert a.params.process_mediums == 1 and a.camera.medium_id == 1 and len(a.mediums) == 2
         assert a.instances[5]["inside_medium"] == 0 and a.instances[5]["outside_medium"] == 1 and a.instances[0]["inside_medium"] == 1
@@ -180,7 +189,7 @@ def test_desc_defaults_and_errors(tmp_path):
 @pytest.mark.gpu
 @pytest.mark.parametrize("SCENE", [SCENE, ROOT / "scenes" / "cbox" / "cbox_materials.json", ROOT / "scenes" / "cbox" / "cbox_fog.json",
                                    ROOT / "scenes" / "cbox" / "cbox_lights.json", ROOT / "scenes" / "cbox" / "cbox_sphere.json",
-                                   ROOT / "scenes" / "cbox" / "cbox_principled.json"])
+                                   ROOT / "scenes" / "cbox" / "cbox_principled.json", ROOT / "scenes" / "cbox" / "cbox_dispersion.json"])
 def test_host_pipeline_renders_like_python_path(vbctx, SCENE):
     hp = host_api.HostPipeline(SCENE)
     hp.prepare(0)
@@ -194,4 +203,6 @@ def test_host_pipeline_renders_like_python_path(vbctx, SCENE):
     err = float(np.mean((a[..., :3] - b[..., :3]) ** 2 / (b[..., :3] ** 2 + 1e-2)))
     assert err < 1e-6, err
     out = hp.final_picture()
-    assert out.shape == (256, 256, 4) and 0.0 <= out[..., :3].min() and out[..., :3].max() <= 1.0
+    assert out.shape == (256, 256, 4) and out[..., :3].max() <= 1.0
+    # the hero spectrum's CIE -> sRGB can leave the gamut per sample (no clamp in the reference either)
+    assert 0.0 <= out[..., :3].min() or "dispersion" in str(SCENE)

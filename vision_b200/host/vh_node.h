@@ -104,7 +104,9 @@ public:
 };
 
 class ImagePool;
-struct SlotContext { ImagePool *images; std::string scene_path; };
+// spectrum_complete / spds: Spectrum::is_complete() (hero) makes glass / metal create "spd" slots (glass.cpp:221-224,
+// metal.cpp:117-121); their curves are appended to the scene's SPD pool
+struct SlotContext { ImagePool *images; std::string scene_path; bool spectrum_complete = false; std::vector<std::vector<float>> *spds = nullptr; };
 
 class Material : public Node {
 public:
@@ -165,7 +167,15 @@ public:
         return w;
     }
 };
-class Spectrum : public Node { public: using Desc = SpectrumDesc; explicit Spectrum(const SpectrumDesc &) {} virtual uint32_t device_tag() const = 0; };
+struct SceneRecords;
+class Spectrum : public Node {
+public:
+    using Desc = SpectrumDesc;
+    explicit Spectrum(const SpectrumDesc &) {}
+    virtual uint32_t device_tag() const = 0;
+    virtual bool is_complete() const { return false; }          // spectrum.h:265
+    virtual void prepare(SceneRecords &) const {}                // SPDs / tables the device side needs
+};
 class ToneMapper : public Node { public: using Desc = ToneMapperDesc; explicit ToneMapper(const ToneMapperDesc &) {} virtual int device_tag() const = 0; };
 class Warper : public Node {
 public:

@@ -193,6 +193,13 @@ public:
         // non-spectral spectrum: the curve is evaluated at rgb_spectrum_peak_wavelengths.x (glass.cpp:225-229)
         float ior = name.empty() ? make_slot(desc_["ior"], {1.5f, 1.5f, 1.5f}, ctx).value[0] : curve(name, 602.785f);
         r.ior = vb_slot{{ior, ior, ior, 1.f}, VB_INVALID_ID, {0, 0, 0}};
+        if (!name.empty() && ctx.spectrum_complete) {              // glass.cpp:221-224: SPD::to_list(curve) -> dispersive "spd" ior slot
+            std::vector<float> lst;
+            for (float lambda = 360.f; lambda < 830.f; lambda += 5.f) lst.push_back(curve(name, lambda));
+            r.flags |= 4u;
+            r.spd[0] = (uint32_t)ctx.spds->size();
+            ctx.spds->push_back(std::move(lst));
+        }
     }
 };
 VH_MAKE_CLASS_CREATOR(GlassMaterial, material, glass, constructor)
@@ -217,6 +224,16 @@ public:
         }
         const Json &e = table.at(name);
         for (int i = 0; i < 3; ++i) { r.eta[i] = (float)e.at("eta").arr[i].num; r.k[i] = (float)e.at("k").arr[i].num; }
+        if (ctx.spectrum_complete) {                               // metal.cpp:117-121: the measured tables as "spd" eta / k slots
+            Json full = Json::parse_file(data_dir() + "/metal_ior_spd.json");
+            const Json &fe = full.at(name);
+            std::vector<float> eta, k;
+            for (auto &v : fe.at("eta").arr) eta.push_back((float)v.num);
+            for (auto &v : fe.at("k").arr) k.push_back((float)v.num);
+            r.flags |= 4u;
+            r.spd[0] = (uint32_t)ctx.spds->size(); ctx.spds->push_back(std::move(eta));
+            r.spd[1] = (uint32_t)ctx.spds->size(); ctx.spds->push_back(std::move(k));
+        }
     }
 };
 VH_MAKE_CLASS_CREATOR(MetalMaterial, material, metal, constructor)

@@ -81,6 +81,43 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(SRGBSpectrum, spectrum, srgb, constructor)
 
+// reference src/render_core/spectrum/hero.cpp:227-348 (dimension 3 = its default). The RGB -> spectrum coefficient table the
+// reference compiles in (srgb2spec.h, not in its tree) is read from data/rgb2spec_srgb_3x64x64x64x4.f32 (tools/rgb2spec_opt.c);
+// the CIE observer / D65 SPDs are every 5th sample of the 1 nm tables (SPD::create_cie_*, spd.cpp:24-30,89-103)
+class HeroWavelengthSpectrum : public Spectrum {
+    uint32_t dimension_;
+public:
+    explicit HeroWavelengthSpectrum(const SpectrumDesc &d) : Spectrum(d), dimension_(d["dimension"].as_uint(3u)) {
+        if (dimension_ != 3) throw std::runtime_error("hero spectrum: only dimension 3 is implemented");
+    }
+    std::string impl_type() const override { return "hero"; }
+    uint32_t device_tag() const override { return VB_SPECTRUM_HERO; }
+    bool is_complete() const override { return true; }
+    void prepare(SceneRecords &out) const override {
+        std::vector<float> cie(4 * 471);
+        FILE *f = std::fopen((data_dir() + "/cie_1nm_4x471.f32").c_str(), "rb");
+        if (!f || std::fread(cie.data(), 4, cie.size(), f) != cie.size()) throw std::runtime_error("cannot read data/cie_1nm_4x471.f32 (tools/extract_cie.py writes it)");
+        std::fclose(f);
+        const uint32_t interval = 5, n = (uint32_t)std::ceil((830.f - 360.f) / (float)interval);
+        out.spds.assign(4, std::vector<float>(n));
+        for (int k = 0; k < 4; ++k) for (uint32_t x = 0; x < n; ++x) out.spds[k][x] = cie[k * 471 + x * interval];
+        float sum = 0.f;                                            // densely_sampled_spectrum_integral, spd.cpp:11-21
+        uint32_t nn = (uint32_t)((830.f - 360.f) / (float)interval) + 1u;
+        for (uint32_t i = 0; i + 1 < nn; ++i) sum += 0.5f * (cie[471 + i * interval] + cie[471 + (i + 1) * interval]);
+        out.spectrum = vb_spectrum_rec{};
+        out.spectrum.type = VB_SPECTRUM_HERO; out.spectrum.dimension = dimension_;
+        out.spectrum.spd_x = 0; out.spectrum.spd_y = 1; out.spectrum.spd_z = 2; out.spectrum.spd_d65 = 3;
+        out.spectrum.cie_y_integral = sum * (float)interval;
+        out.spectrum.rgb2spec_res = 64;
+        out.rgb2spec.resize((size_t)3 * 64 * 64 * 64 * 4);
+        f = std::fopen((data_dir() + "/rgb2spec_srgb_3x64x64x64x4.f32").c_str(), "rb");
+        if (!f || std::fread(out.rgb2spec.data(), 4, out.rgb2spec.size(), f) != out.rgb2spec.size())
+            throw std::runtime_error("cannot read data/rgb2spec_srgb_3x64x64x64x4.f32 (written by __graft_entry__.build() / tools/rgb2spec_opt.c)");
+        std::fclose(f);
+    }
+};
+VH_MAKE_CLASS_CREATOR(HeroWavelengthSpectrum, spectrum, hero, constructor)
+
 // reference src/render_core/tonemapper/impl.cpp:9-52: one module "vision-tonemapper-impl", three constructors
 class LinearToneMapper : public ToneMapper { public: explicit LinearToneMapper(const ToneMapperDesc &d) : ToneMapper(d) {} std::string impl_type() const override { return "linear"; } int device_tag() const override { return VB_TONEMAP_LINEAR; } };
 class ACESToneMapper : public ToneMapper { public: explicit ACESToneMapper(const ToneMapperDesc &d) : ToneMapper(d) {} std::string impl_type() const override { return "aces"; } int device_tag() const override { return VB_TONEMAP_ACES; } };

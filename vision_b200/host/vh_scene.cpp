@@ -174,7 +174,8 @@ void Scene::prepare(SceneRecords &out) {
     }
     materials = used;
     light_sampler->tidy_up();
-    SlotContext sctx{&image_pool, desc.scene_path};
+    spectrum->prepare(out);
+    SlotContext sctx{&image_pool, desc.scene_path, spectrum->is_complete(), &out.spds};
     out.materials.resize(materials.size());
     for (auto &m : materials) m->fill_record(out.materials[m->index], sctx);
     std::map<uint64_t, uint32_t> mesh_ids;
@@ -279,6 +280,14 @@ void Pipeline::prepare(int device) {
         check(vb_luts_set(ctx, k, l.data.empty() ? nullptr : l.data.data(), l.nx, l.ny, l.nz, l.channels), "vb_luts_set");
     }
     check(vb_mediums_set(ctx, records.mediums.data(), (uint32_t)records.mediums.size()), "vb_mediums_set");
+    {
+        std::vector<float> values; std::vector<uint32_t> offsets{0};
+        for (auto &s : records.spds) { values.insert(values.end(), s.begin(), s.end()); offsets.push_back((uint32_t)values.size()); }
+        check(vb_spds_set(ctx, values.data(), offsets.data(), (uint32_t)records.spds.size()), "vb_spds_set");
+        vb_spectrum_rec sp = records.spectrum;
+        sp.rgb2spec = records.rgb2spec.empty() ? nullptr : records.rgb2spec.data();
+        check(vb_spectrum_set(ctx, &sp), "vb_spectrum_set");
+    }
     check(vb_lights_set(ctx, records.lights.data(), (uint32_t)records.lights.size(), records.alias_table.data(), records.alias_func.data(),
                         (uint32_t)records.alias_table.size()), "vb_lights_set");
     check(vb_camera_set(ctx, &records.camera), "vb_camera_set");

@@ -32,6 +32,9 @@ struct SceneRecords {
     std::vector<float> alias_func;
     std::vector<Image> textures;
     std::vector<vb_medium_rec> mediums;
+    std::vector<std::vector<float>> spds;          // SPD pool (vb_spds_set): hero spectrum's CIE x, y, z, D65 first, then material curves
+    vb_spectrum_rec spectrum{};                    // rgb2spec is set at upload time from the vector below
+    std::vector<float> rgb2spec;
     struct Lut { std::vector<float> data; uint32_t nx = 0, ny = 0, nz = 0, channels = 0; } luts[VB_LUT_COUNT];
     vb_camera camera{};
     vb_pt_params params{};

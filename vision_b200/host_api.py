@@ -145,6 +145,11 @@ class HostPipeline:
             vals = self._blob(8 + which, C.c_float)
             if vals:
                 sc.luts[which] = (np.array(vals, np.float32), dims)
+        sc.spectrum = self._blob(100, capi.vb_spectrum_rec)[0]
+        sc.spectrum.rgb2spec = None
+        sc.spds = [np.array(self._blob(200 + k, C.c_float), np.float32) for k in range(self._blob(101, C.c_uint64)[0])]
+        if sc.spectrum.type == capi.VB_SPECTRUM_HERO:
+            sc.rgb2spec = capi.load_rgb2spec()                      # the same data file the host layer reads
         for t in range(i["n_textures"]):
             w, h = C.c_uint32(), C.c_uint32()
             self.lib.vh_texture_info(self.h, t, C.byref(w), C.byref(h))
