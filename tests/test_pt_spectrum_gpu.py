@@ -63,3 +63,21 @@ def test_hero_needs_its_tables(vbctx):
         vbctx.render_frames(0, 1, 1, capi.VB_ACCUM_LERP)
     sc.params.spectrum = capi.VB_SPECTRUM_SRGB
     vbctx._check(vbctx.lib.vb_integrator_set(vbctx.h, C.byref(sc.params)), "vb_integrator_set")
+
+
+@pytest.mark.parametrize("name,spectrum", [("cbox_principled", "srgb"), ("cbox_dispersion", "hero")])
+def test_split_principled_launches_give_the_same_film(vbctx, name, spectrum):
+    """scenes with the principled BSDF shade each bounce with two launches (lean kernel + principled instantiation, filtered by
+    the material key of the ordered queue): same film and counters as the single principled launch"""
+    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / f"{name}.json", {"resolution": [160, 160], "spp": 4, "spectrum": spectrum})
+    vbctx.upload_scene(sc)
+    films, stats = [], []
+    try:
+        for split in (1, 0):
+            vbctx.set_option("pt.split_principled", split)
+            vbctx.film_clear()
+            vbctx.render_frames(0, sc.spp, 1, capi.VB_ACCUM_LERP)
+            films.append(vbctx.film_download(capi.VB_FILM_ACCUM)); stats.append(vbctx.render_stats())
+    finally:
+        vbctx.set_option("pt.split_principled", 1)
+    assert np.array_equal(films[0], films[1]) and stats[0] == stats[1]

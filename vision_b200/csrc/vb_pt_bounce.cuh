@@ -39,12 +39,12 @@ enum : int { PT_CONTINUE = 1, PT_SHADOW = 2, PT_VERTEX = 4, PT_LIGHT = 8 };
 // (+ pending) is the sample's radiance.
 // PRINCIPLED = the scene uses the principled BSDF: its LobeSet code (stack frame, out-of-line calls) is compiled
 // into a separate kernel instantiation so that scenes without it keep the lean kernel.
-// VARIANT: 0 = lean (srgb spectrum, no principled BSDF), 1 = + principled, 2 = hero spectrum (+ principled): only
-// variant 2 carries the path's wavelengths; in 0 and 1 `swl` is a compile-time nullptr and every spec_* call folds away.
+// VARIANT = bit flags: PT_PRINCIPLED = the principled BSDF's code is compiled in, PT_HERO = hero spectrum: only those
+// variants carry the path's wavelengths; without the flag `swl` is a compile-time nullptr and every spec_* call folds away.
 enum : int { PT_LEAN = 0, PT_PRINCIPLED = 1, PT_HERO = 2 };
 template <int VARIANT>
 __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay &ray, const VbHit &hit, VbRay &shadow, f3 &pending) {
-    constexpr bool PRINCIPLED = VARIANT >= PT_PRINCIPLED, HERO = VARIANT == PT_HERO;
+    constexpr bool PRINCIPLED = (VARIANT & PT_PRINCIPLED) != 0, HERO = (VARIANT & PT_HERO) != 0;
     Swl wl;
     const Swl *swl = nullptr;
     if (HERO) { wl = swl_make(ps.swl); swl = &wl; }

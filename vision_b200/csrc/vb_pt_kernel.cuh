@@ -463,7 +463,7 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     VB_CUDA(cudaMemsetAsync(p->d_counters, 0, sizeof(PtCounters), ctx->stream));
     ctx->prof_begin("path_trace", 1);
     if (dump) k_path_trace<true, PT_LEAN><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, 1, 1, mode, 0, p->rt, p->accum, p->d_counters, hi, hp, hu, hv, ht);
-    else if (S.params.spectrum == VB_SPECTRUM_HERO) k_path_trace<false, PT_HERO><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt,
+    else if (S.params.spectrum == VB_SPECTRUM_HERO) k_path_trace<false, PT_HERO | PT_PRINCIPLED><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt,
                                                                                                                p->accum, p->d_counters, nullptr, nullptr, nullptr, nullptr, nullptr);
     else if (p->has_principled) k_path_trace<false, PT_PRINCIPLED><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum,
                                                                                            p->d_counters, nullptr, nullptr, nullptr, nullptr, nullptr);

@@ -81,21 +81,36 @@ __global__ void __launch_bounds__(256) k_wf_material_keys(PtScene S, uint32_t n,
     keyidx[q] = ((uint64_t)key << 32) | q;
 }
 
-// one Li vertex per queue entry; entry i of the launch is queue position order[i] (low word)
+// one Li vertex per queue entry; entry i of the launch is queue position order[i] (low word).
+// filter (needs `order`, whose high word is the material key of k_wf_material_keys): 0 = every entry, 1 = all but the
+// principled-BSDF entries, 2 = only those. Scenes that use the principled BSDF shade each bounce with TWO launches over the
+// material-ordered queue - the lean kernel (no stack frame, no spills) for everything else, the principled instantiation for its
+// own entries; warps whose entries all belong to the other launch exit at once.
 template <int VARIANT>
 #ifndef VB_SHADE_MIN_BLOCKS
 #define VB_SHADE_MIN_BLOCKS 4
 #endif
 __global__ void __launch_bounds__(128, VB_SHADE_MIN_BLOCKS) k_wf_shade(PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
-                                                  WfState st, WfQueue Qout, WfQueue Qsh, float4 *sh_pend, WfSortBox B, WfCounters *cnt) {
+                                                  WfState st, WfQueue Qout, WfQueue Qsh, float4 *sh_pend, WfSortBox B, WfCounters *cnt, int filter) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
     int flags = 0;
     VbRay ray{}, shadow{};
     f3 pending{0, 0, 0};
     uint32_t slot = 0;
-    if (i < n) {
-        uint32_t q = order ? (uint32_t)__ldg(order + i) : i;
+    bool mine = i < n;
+    uint32_t q = i;
+    if (mine && order) {
+        uint64_t o = __ldg(order + i);
+        q = (uint32_t)o;
+        if (filter) {
+            uint32_t key = (uint32_t)(o >> 32);
+            bool principled = key < 254u && ((key >> 5) & 7u) == VB_MAT_PRINCIPLED;
+            mine = principled == (filter == 2);
+        }
+    }
+    if (!__any_sync(~0u, mine)) return;
+    if (mine) {
         slot = __ldg(Qin.slot + q);
         ray = wf_load_ray(Qin.rays, q);
         uint4 h = __ldg(hits4 + q);

@@ -102,9 +102,24 @@ static int wf_render_batch(vb_ctx *ctx, vb_pt_state *p, vb_wf_buffers &w, const 
             rc = wf_sort_by_material(ctx, w, k0, k1, n, &order);
             if (rc) { ctx->prof_end(); return rc; }
         }
-        if (S.params.spectrum == VB_SPECTRUM_HERO) k_wf_shade<PT_HERO><<<(n + 127) / 128, 128, 0, st>>>(S, n, Qin, order, w.hits4, w.st, Qout, Qsh, w.sh_pend, B, w.d_cnt);
-        else if (p->has_principled) k_wf_shade<PT_PRINCIPLED><<<(n + 127) / 128, 128, 0, st>>>(S, n, Qin, order, w.hits4, w.st, Qout, Qsh, w.sh_pend, B, w.d_cnt);
-        else k_wf_shade<PT_LEAN><<<(n + 127) / 128, 128, 0, st>>>(S, n, Qin, order, w.hits4, w.st, Qout, Qsh, w.sh_pend, B, w.d_cnt);
+        {
+            const bool hero = S.params.spectrum == VB_SPECTRUM_HERO;
+            const unsigned grid = (n + 127) / 128;
+            auto shade = [&](int variant, int filter) {
+#define VB_SHADE(V) k_wf_shade<V><<<grid, 128, 0, st>>>(S, n, Qin, order, w.hits4, w.st, Qout, Qsh, w.sh_pend, B, w.d_cnt, filter)
+                switch (variant) {
+                    case PT_LEAN: VB_SHADE(PT_LEAN); break;
+                    case PT_PRINCIPLED: VB_SHADE(PT_PRINCIPLED); break;
+                    case PT_HERO: VB_SHADE(PT_HERO); break;
+                    default: VB_SHADE(PT_HERO | PT_PRINCIPLED); break;
+                }
+#undef VB_SHADE
+            };
+            const int base = hero ? PT_HERO : PT_LEAN;
+            if (!p->has_principled) shade(base, 0);
+            else if (order && ctx->opt_pt_split_principled) { shade(base, 1); shade(base | PT_PRINCIPLED, 2); }   // material-ordered queue: two launches
+            else shade(base | PT_PRINCIPLED, 0);
+        }
         ctx->prof_end();
         VB_CHECK_LAUNCH();
         VB_CUDA(cudaMemcpyAsync(w.h_cnt, w.d_cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, st));
