@@ -137,7 +137,7 @@ struct vb_pt_state {
     DevTex *d_tex = nullptr; std::vector<float4 *> tex_mem;
     DevLut luts[VB_LUT_COUNT] = {};
     vb_medium_rec *d_mediums = nullptr; uint32_t n_mediums = 0;
-    float *d_spd_values = nullptr; uint32_t *d_spd_offsets = nullptr; uint32_t n_spds = 0;
+    float *d_spd_values = nullptr; float4 *d_spd_meta = nullptr; uint32_t n_spds = 0; std::vector<uint32_t> h_spd_sizes;
     float *d_rgb2spec = nullptr; vb_spectrum_rec spectrum{}; bool have_spectrum = false;
     std::vector<vb_material_rec> h_mat;            // kept for the SPD index checks at render time
     vb_camera cam{}; bool have_cam = false;
@@ -165,7 +165,7 @@ void vb_pt_destroy(vb_ctx *ctx) {
     for (auto t : p->tex_mem) cudaFree(t);
     for (auto &l : p->luts) cudaFree((void *)l.data);
     cudaFree(p->d_mediums);
-    cudaFree(p->d_spd_values); cudaFree(p->d_spd_offsets); cudaFree(p->d_rgb2spec);
+    cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta); cudaFree(p->d_rgb2spec);
     cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output); cudaFree(p->d_counters);
     if (p->wf) { wf_free(*p->wf); delete p->wf; }
     delete p;
@@ -294,13 +294,24 @@ int vb_spds_set(vb_ctx *ctx, const float *values, const uint32_t *offsets, uint3
     vb_pt_state *p = pt_state(ctx);
     for (uint32_t i = 0; i < n; ++i)
         if (offsets[i + 1] < offsets[i] + 2) return ctx->fail(VB_ERR_INVALID, "vb_spds_set: an SPD needs at least 2 samples and ascending offsets");
-    cudaFree(p->d_spd_values); cudaFree(p->d_spd_offsets);
-    p->d_spd_values = nullptr; p->d_spd_offsets = nullptr; p->n_spds = n;
+    cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta);
+    p->d_spd_values = nullptr; p->d_spd_meta = nullptr; p->n_spds = n;
+    p->h_spd_sizes.resize(n);
     if (n) {
+        std::vector<float4> meta(n);
+        for (uint32_t i = 0; i < n; ++i) {                       // SPD::init / SPD::eval constants (spd.cpp:50,70-72)
+            uint32_t size = offsets[i + 1] - offsets[i];
+            p->h_spd_sizes[i] = size;
+            float interval = 471.0f / (float)size;
+            uint32_t sample_count = (uint32_t)((830.f - 360.f) / interval) + 1u;
+            float off_bits; std::memcpy(&off_bits, &offsets[i], 4);
+            meta[i] = make_float4(off_bits, interval, (float)(sample_count - 2u), 0.f);
+            if (sample_count > size) return ctx->fail(VB_ERR_INVALID, "vb_spds_set: SPD too short for its sampling interval");
+        }
         VB_CUDA(cudaMalloc(&p->d_spd_values, sizeof(float) * offsets[n]));
         VB_CUDA(cudaMemcpy(p->d_spd_values, values, sizeof(float) * offsets[n], cudaMemcpyHostToDevice));
-        VB_CUDA(cudaMalloc(&p->d_spd_offsets, sizeof(uint32_t) * (n + 1)));
-        VB_CUDA(cudaMemcpy(p->d_spd_offsets, offsets, sizeof(uint32_t) * (n + 1), cudaMemcpyHostToDevice));
+        VB_CUDA(cudaMalloc(&p->d_spd_meta, sizeof(float4) * n));
+        VB_CUDA(cudaMemcpy(p->d_spd_meta, meta.data(), sizeof(float4) * n, cudaMemcpyHostToDevice));
     }
     return VB_OK;
 }
@@ -422,7 +433,9 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
         for (auto &m : p->h_mat)
             if ((m.flags & 4u) && (m.spd[0] >= p->n_spds || (m.type == VB_MAT_METAL && m.spd[1] >= p->n_spds)))
                 return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": material SPD index out of range (vb_spds_set)");
-        S.spec = DevSpectrum{p->d_rgb2spec, sp.rgb2spec_res, p->d_spd_values, p->d_spd_offsets, sp.spd_x, sp.spd_y, sp.spd_z, sp.spd_d65, sp.cie_y_integral};
+        if (p->h_spd_sizes[sp.spd_x] != p->h_spd_sizes[sp.spd_y] || p->h_spd_sizes[sp.spd_x] != p->h_spd_sizes[sp.spd_z])
+            return ctx->fail(VB_ERR_UNSUPPORTED, std::string(fn) + ": the CIE x, y, z SPDs must have the same number of samples");
+        S.spec = DevSpectrum{p->d_rgb2spec, sp.rgb2spec_res, p->d_spd_values, p->d_spd_meta, sp.spd_x, sp.spd_y, sp.spd_z, sp.spd_d65, sp.cie_y_integral};
     }
     if (p->params.process_mediums) {
         auto bad = [&](uint32_t id) { return id != VB_INVALID_ID && id >= p->n_mediums; };

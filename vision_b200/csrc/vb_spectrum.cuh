@@ -16,7 +16,8 @@ struct DevSpectrum {
     const float *rgb2spec;         // float[3][res][res][res][4]
     uint32_t res;
     const float *spd_values;       // SPD pool
-    const uint32_t *spd_offsets;
+    const float4 *spd_meta;        // per SPD: (offset as uint bits, sample_interval = 471 / size, float(sample_count - 2), -) - the
+                                   // per-SPD constants of SPD::eval, divided once on the host (same IEEE operations, same bits)
     uint32_t spd_x, spd_y, spd_z, spd_d65;
     float cie_y_integral;
 };
@@ -45,15 +46,19 @@ __device__ __forceinline__ Swl swl_make(uint32_t packed) {
 }
 
 // SPD::eval (spd.cpp:68-76), sample_interval_ = 471 / size (spd.cpp:50)
-__device__ float spd_eval(const DevSpectrum &P, uint32_t id, float lambda) {
-    uint32_t o0 = __ldg(P.spd_offsets + id), o1 = __ldg(P.spd_offsets + id + 1);
-    const float *func = P.spd_values + o0;
-    float interval = 471.0f / (float)(o1 - o0);
-    float t = (fmin_(fmax_(lambda, 360.f), 830.f) - 360.f) / interval;
-    uint32_t sample_count = (uint32_t)((830.f - 360.f) / interval) + 1u;
-    uint32_t i = (uint32_t)fmin_(t, (float)(sample_count - 2u));
-    float l = __ldg(func + i), r = __ldg(func + i + 1);
-    return lerp(vfract(t), l, r);
+struct SpdPos { uint32_t i; float frac; };
+__device__ __forceinline__ SpdPos spd_locate(float4 meta, float lambda) {
+    float t = (fmin_(fmax_(lambda, 360.f), 830.f) - 360.f) / meta.y;
+    return SpdPos{(uint32_t)fmin_(t, meta.z), vfract(t)};
+}
+__device__ __forceinline__ float spd_at(const DevSpectrum &P, float4 meta, SpdPos p) {
+    const float *func = P.spd_values + __float_as_uint(meta.x);
+    float l = __ldg(func + p.i), r = __ldg(func + p.i + 1);
+    return lerp(p.frac, l, r);
+}
+__device__ __forceinline__ float spd_eval(const DevSpectrum &P, uint32_t id, float lambda) {
+    float4 meta = __ldg(P.spd_meta + id);
+    return spd_at(P, meta, spd_locate(meta, lambda));
 }
 __device__ __forceinline__ f3 spd_eval3(const DevSpectrum &P, uint32_t id, const Swl &w) {
     return {spd_eval(P, id, w.lambda[0]), spd_eval(P, id, w.lambda[1]), spd_eval(P, id, w.lambda[2])};
@@ -128,10 +133,13 @@ __device__ f3 spec_to_srgb(const DevSpectrum &P, const Swl *w, f3 sp) {
     const float v[3] = {sp.x, sp.y, sp.z};
     f3 sum{0, 0, 0};
     uint32_t valid = 0;
+    // the three observer curves have the same sampling (checked by vb_render_frames): one table position per wavelength
+    const float4 mx = __ldg(P.spd_meta + P.spd_x), my = __ldg(P.spd_meta + P.spd_y), mz = __ldg(P.spd_meta + P.spd_z);
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         float p = w->pdf[i];
-        f3 xyz{spd_eval(P, P.spd_x, w->lambda[i]) * v[i], spd_eval(P, P.spd_y, w->lambda[i]) * v[i], spd_eval(P, P.spd_z, w->lambda[i]) * v[i]};
+        SpdPos pos = spd_locate(mx, w->lambda[i]);
+        f3 xyz{spd_at(P, mx, pos) * v[i], spd_at(P, my, pos) * v[i], spd_at(P, mz, pos) * v[i]};
         if (p != 0.f) sum = sum + xyz / p;
         if (p > 0.f) valid++;
     }
