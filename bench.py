@@ -197,12 +197,15 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     reps = 3
+    ctx.profile_reset()
     e0.record(stream)
     for _ in range(reps):
         run()
     e1.record(stream)
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
+    # per-stage device time of the timed runs (the library's own CUDA events around its launches, always on)
+    stage_ms = {k: ctx.profile_get(k)[0] / reps for k in ("trace_closest", "trace_any", "pt_generate", "pt_shade", "pt_shadow_resolve", "pt_film")}
     st = ctx.render_stats()
     t = torch.tensor([ms, float(st["closest"] + st["any"])], dtype=torch.float64, device=torch.device("cuda", local_rank))
     if world > 1:
@@ -231,12 +234,23 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
         l2_gbs = ctx.probe_read_bandwidth(64 << 20, 20)
         hbm_gbs, _ = measured_peak()
         bvh_bytes = int(build["node_bytes"] + build["tri_bytes"])
+        # traversal alone (north_star: "fraction of the memory-bound traversal roofline" on the named scenes): algorithmic bytes of the
+        # closest-hit / any-hit rays of the timed frames over the time spent in vb_trace_queue (ray sort + k_trace)
+        f_closest = st["closest"] / max(s1["closest"], 1)
+        f_any = st["any"] / max(s1["any"], 1)
+        trav = {}
+        for name, b1, f in (("closest", b_closest, f_closest), ("any", b_any, f_any)):
+            t_ms = stage_ms["trace_" + name]
+            gbs = b1 * f / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0
+            trav[name] = {"ms": t_ms, "achieved_gbs": gbs, "frac_l2": gbs / l2_gbs, "frac_hbm": gbs / hbm_gbs}
         roof = {"bytes_per_sample": bytes_per_sample, "achieved": achieved, "unit": "GB/s (per GPU, algorithmic)",
                 "closest_nodes_per_ray": wk["closest_nodes"] / max(s1["closest"], 1), "closest_tris_per_ray": wk["closest_tris"] / max(s1["closest"], 1),
                 "any_nodes_per_ray": wk["any_nodes"] / max(s1["any"], 1), "any_tris_per_ray": wk["any_tris"] / max(s1["any"], 1),
                 "vertices_per_sample": s1["vertices"] / n1, "bvh_bytes": bvh_bytes,
                 "bound": "l2" if bvh_bytes < (100 << 20) else "hbm", "l2_read_peak": l2_gbs, "hbm_peak": hbm_gbs,
                 "frac_l2": achieved / l2_gbs, "frac_hbm": achieved / hbm_gbs}
+        roof["traversal_only"] = trav
+        roof["stage_ms"] = stage_ms
     ctx.close()
     return {"roofline": roof, "scene": f"{label} {w}x{h}, {spp_rank} spp per GPU x {world} GPU(s), max depth {sc.params.max_depth}", "ms": ms,
             "samples_per_s": samples / (ms * 1e-3), "mrays_per_s": rays / (ms * 1e-3) / 1e6, "rays_per_sample": rays / samples,

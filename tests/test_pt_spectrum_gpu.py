@@ -81,3 +81,21 @@ def test_split_principled_launches_give_the_same_film(vbctx, name, spectrum):
     finally:
         vbctx.set_option("pt.split_principled", 1)
     assert np.array_equal(films[0], films[1]) and stats[0] == stats[1]
+
+
+@pytest.mark.parametrize("name", ["cbox_dispersion", "cbox_fog", "cbox_lights"])
+def test_cached_constant_slot_coefficients_give_the_same_film(vbctx, name):
+    """hero spectrum: the coefficients of constant colour slots (materials, lights, medium sigma) are decoded once per scene by
+    k_spec_cache; the per-vertex decode (pt.spec_cache = 0) must give the same bits"""
+    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / f"{name}.json", {"resolution": [128, 128], "spp": 4, "spectrum": "hero"})
+    vbctx.upload_scene(sc)
+    films = []
+    try:
+        for cache in (1, 0):
+            vbctx.set_option("pt.spec_cache", cache)
+            vbctx.film_clear()
+            vbctx.render_frames(0, sc.spp, 1, capi.VB_ACCUM_LERP)
+            films.append(vbctx.film_download(capi.VB_FILM_ACCUM))
+    finally:
+        vbctx.set_option("pt.spec_cache", 1)
+    assert np.array_equal(films[0], films[1])

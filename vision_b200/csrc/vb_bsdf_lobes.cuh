@@ -208,6 +208,11 @@ __device__ BSDFSample lobe_sample(const PtScene &S, const Lobe &lb, f3 world_wo,
 
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fmin_(fmax_(v, lo), hi); }
 
+// a colour slot of the hit's material as an albedo spectrum (eval_albedo_spectrum, shader_node.cpp:317-321)
+__device__ __forceinline__ f3 material_color(const PtScene &S, const Swl *swl, const vb_slot &slot, const Interaction &it, uint32_t which) {
+    return spec_albedo_c(S.spec, swl, eval_slot3(S, slot, it.uv), slot.tex_id == VB_INVALID_ID, 4u * it.mat_id + which);
+}
+
 // Material::create_evaluator -> create_lobe_set of the plugin
 __device__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction &it) {
     const vb_material_rec &m = S.materials[it.mat_id];
@@ -220,7 +225,7 @@ __device__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction 
     float anis = clampf(m.params[0], -0.9f, 0.9f);
     switch (m.type) {
         case VB_MAT_DIFFUSE:
-            lb.kr = spec_albedo(S.spec, swl, eval_slot3(S, m.color, it.uv));
+            lb.kr = material_color(S, swl, m.color, it, SC_COLOR);
             if (m.flags & 1u) {
                 float sigma = eval_slot3(S, m.sigma, it.uv).x * PiOver2;
                 float sigma2 = sqr(sigma * sigma);
@@ -230,7 +235,7 @@ __device__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction 
             }
             break;
         case VB_MAT_MIRROR: case VB_MAT_METAL: {
-            lb.kr = m.type == VB_MAT_MIRROR ? spec_albedo(S.spec, swl, eval_slot3(S, m.color, it.uv)) : splat(1.f);
+            lb.kr = m.type == VB_MAT_MIRROR ? material_color(S, swl, m.color, it, SC_COLOR) : splat(1.f);
             float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
@@ -240,7 +245,7 @@ __device__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction 
             }
         } break;
         case VB_MAT_GLASS: {
-            lb.kr = spec_albedo(S.spec, swl, eval_slot3(S, m.color, it.uv));
+            lb.kr = material_color(S, swl, m.color, it, SC_COLOR);
             float ior = eval_slot3(S, m.ior, it.uv).x;
             lb.eta = dot(it.wo, it.ng) > 0.f ? ior : 1.0f / ior;
             if ((m.flags & 4u) && swl) {                                 // glass.cpp:216-234: "material_name" curve in an "spd" slot
@@ -255,8 +260,8 @@ __device__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction 
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
         } break;
         case VB_MAT_SUBSTRATE: {
-            lb.kr = spec_albedo(S.spec, swl, eval_slot3(S, m.color, it.uv));
-            lb.rs = spec_albedo(S.spec, swl, eval_slot3(S, m.spec, it.uv));
+            lb.kr = material_color(S, swl, m.color, it, SC_COLOR);
+            lb.rs = material_color(S, swl, m.spec, it, SC_SPEC);
             float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);

@@ -136,6 +136,7 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     else if (k == "pt.schedule") ctx->opt_pt_schedule = value != 0 ? 1 : 0;
     else if (k == "pt.sort_material") ctx->opt_pt_sort_material = value != 0 ? 1 : 0;
     else if (k == "pt.split_principled") ctx->opt_pt_split_principled = value != 0 ? 1 : 0;
+    else if (k == "pt.spec_cache") ctx->opt_pt_spec_cache = value != 0 ? 1 : 0;
     else if (k == "pt.count_work") ctx->opt_pt_count_work = value != 0 ? 1 : 0;
     else if (k == "pt.max_paths") ctx->opt_pt_max_paths = std::max<int64_t>(1, (int64_t)value);
     else if (k == "trace.host_chunks") ctx->opt_host_chunks = std::min(VB_MAX_HOST_CHUNKS, std::max(1, (int)value));

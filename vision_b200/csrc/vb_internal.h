@@ -84,6 +84,7 @@ struct vb_ctx {
     int opt_sort_oct_shift = 0;              // ray sort key: direction octant above this many low Morton bits (vb_ray_sort_key)
     int opt_pt_schedule = 0;                 // 0 = wavefront (default), 1 = megakernel
     int opt_pt_sort_material = 1;            // wavefront: order shading entries by material
+    int opt_pt_spec_cache = 1;               // hero spectrum: constant colour slots decoded once per scene (k_spec_cache)
     int opt_pt_split_principled = 1;         // wavefront: principled-BSDF entries shaded by their own launch, the rest by the lean kernel
     int opt_pt_count_work = 0;               // wavefront: instrumented traversal (nodes / triangles per ray), never timed
     int64_t opt_pt_max_paths = 1 << 25;      // wavefront: paths in flight per batch

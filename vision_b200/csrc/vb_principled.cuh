@@ -66,11 +66,11 @@ __device__ __noinline__ PrincipledSet principled_create(const PtScene &S, const 
     ps.frame = it.shading;
     auto clampf = [](float v, float lo, float hi) { return fmin_(fmax_(v, lo), hi); };
     const uint32_t switches = (uint32_t)m.params[15];
-    f3 color = spec_albedo(S.spec, swl, eval_slot3(S, m.color, it.uv));
+    f3 color = material_color(S, swl, m.color, it, SC_COLOR);
     float ior = eval_slot3(S, m.ior, it.uv).x;
     float roughness = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
     float anisotropic = m.params[0];
-    f3 specular_tint = spec_albedo(S.spec, swl, eval_slot3(S, m.spec, it.uv));
+    f3 specular_tint = material_color(S, swl, m.spec, it, SC_SPEC);
     float aspect = __fsqrt_rn(1.f - anisotropic * 0.9f);
     GGX mf{fmax_(0.001f, sqr(roughness) / aspect), fmax_(0.001f, sqr(roughness) * aspect)};
     f3 weight = splat(1.f);
@@ -80,7 +80,7 @@ __device__ __noinline__ PrincipledSet principled_create(const PtScene &S, const 
     if (switches & (1u << SL_SHEEN)) {
         SubLobe &l = ps.s[ps.n++];
         l.kind = SL_SHEEN;
-        f3 sheen_tint = spec_albedo(S.spec, swl, f3{m.params[4], m.params[5], m.params[6]});
+        f3 sheen_tint = spec_albedo_c(S.spec, swl, f3{m.params[4], m.params[5], m.params[6]}, true, 4u * it.mat_id + SC_SHEEN);
         float sheen_weight = m.params[2] * front;
         float sheen_roughness = m.params[3];
         l.kr = sheen_tint * sheen_weight * weight;
@@ -99,7 +99,7 @@ __device__ __noinline__ PrincipledSet principled_create(const PtScene &S, const 
         float cc_weight = m.params[7] * front;
         float cc_roughness = sqr(clampf(m.params[8], 0.0001f, 1.f));
         float cc_ior = m.params[9];
-        f3 cc_tint = spec_albedo(S.spec, swl, f3{m.params[10], m.params[11], m.params[12]});
+        f3 cc_tint = spec_albedo_c(S.spec, swl, f3{m.params[10], m.params[11], m.params[12]}, true, 4u * it.mat_id + SC_COAT);
         l.fresnel = FR_DIELECTRIC; l.eta = cc_ior;
         l.mf = GGX{cc_roughness, cc_roughness};
         l.kr = weight * cc_weight * cc_tint;

@@ -161,6 +161,10 @@ __device__ f3 eval_slot3(const PtScene &S, const vb_slot &s, f2 uv) {
     return v;
 }
 
+// Light::color_ as an illumination spectrum (eval_illumination_spectrum, shader_node.cpp:329-333); `l` is an element of S.lights
+__device__ __forceinline__ f3 light_color(const PtScene &S, const Swl *swl, const vb_light_rec &l, f2 uv) {
+    return spec_illum_c(S.spec, swl, eval_slot3(S, l.color, uv), l.color.tex_id == VB_INVALID_ID, S.spec.cache_lights + (uint32_t)(&l - S.lights));
+}
 struct LightEvalCtx { f3 pos, ng; f2 uv; float pdf_pos; };
 struct LightEval { f3 L; float pdf; };
 struct LightSample { LightEval eval; f3 p_light; };
@@ -184,7 +188,7 @@ __device__ uint32_t alias_sample(const PtScene &S, const vb_light_rec &l, float 
 __device__ LightEval area_evaluate_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, f3 ref_pos, const LightEvalCtx &pl) {
     LightEval ev;
     f3 w = ref_pos - pl.pos;
-    f3 color = spec_illum(S.spec, swl, eval_slot3(S, l.color, pl.uv));
+    f3 color = light_color(S, swl, l, pl.uv);
     float s = (dot(w, pl.ng) > 0.f || l.two_sided) ? 1.f : 0.f;
     ev.L = color * l.scale * s;
     float cos_theta = fabsf(dot(pl.ng, normalize(w)));
@@ -213,7 +217,7 @@ __device__ LightSample area_sample_wi(const PtScene &S, const Swl *swl, const vb
 __device__ LightSample point_sample_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, const Interaction &ref) {
     LightSample ls;
     f3 pos{l.position[0], l.position[1], l.position[2]};
-    f3 value = spec_illum(S.spec, swl, eval_slot3(S, l.color, f2{0, 0})) * l.scale;
+    f3 value = light_color(S, swl, l, f2{0, 0}) * l.scale;
     f3 w_un = ref.pos - pos;
     if (l.type == VB_LIGHT_POINT) ls.eval.L = value / length_squared(w_un);
     else if (l.type == VB_LIGHT_PROJECTOR) {                       // projector.cpp:99-112
@@ -225,7 +229,7 @@ __device__ LightSample point_sample_wi(const PtScene &S, const Swl *swl, const v
         f2 uv{(p.x + tan_x) / (2.f * tan_x), (p.y + tan_y) / (2.f * tan_y)};
         valid = valid && uv.x >= 0.f && uv.x <= 1.f && uv.y >= 0.f && uv.y <= 1.f;
         if (!valid) uv = f2{0.f, 0.f};
-        ls.eval.L = spec_illum(S.spec, swl, eval_slot3(S, l.color, uv)) * (valid ? 1.f : 0.f) / d2 * l.scale;
+        ls.eval.L = light_color(S, swl, l, uv) * (valid ? 1.f : 0.f) / d2 * l.scale;
     } else {
         f3 w = normalize(w_un);
         f3 dir{l.direction[0], l.direction[1], l.direction[2]};
@@ -280,7 +284,7 @@ __device__ __forceinline__ f2 env_calculate_uv(f3 local_dir) {
     return {phi * Inv2Pi, theta * InvPi};
 }
 __device__ __forceinline__ f3 env_L(const PtScene &S, const Swl *swl, const vb_light_rec &l, f3 local_dir) {
-    return spec_illum(S.spec, swl, eval_slot3(S, l.color, env_calculate_uv(local_dir))) * l.scale;
+    return light_color(S, swl, l, env_calculate_uv(local_dir)) * l.scale;
 }
 __device__ LightEval env_evaluate_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, f3 ref_pos, f3 light_pos) {
     LightEval ev;
@@ -323,7 +327,8 @@ namespace {
 
 // ---- homogeneous medium, reference render_core/medium/homogeneous.cpp:30-70 ----
 __device__ __forceinline__ f3 medium_sigma_t(const PtScene &S, const Swl *swl, const vb_medium_rec &m) {
-    return spec_unbound(S.spec, swl, f3{m.sigma_a[0] + m.sigma_s[0], m.sigma_a[1] + m.sigma_s[1], m.sigma_a[2] + m.sigma_s[2]} * m.scale);
+    return spec_unbound_c(S.spec, swl, f3{m.sigma_a[0] + m.sigma_s[0], m.sigma_a[1] + m.sigma_s[1], m.sigma_a[2] + m.sigma_s[2]} * m.scale, true,
+                          S.spec.cache_mediums + 2u * (uint32_t)(&m - S.mediums));
 }
 __device__ __forceinline__ f3 medium_Tr(const PtScene &S, const Swl *swl, const vb_medium_rec &m, float t) {
     f3 st = medium_sigma_t(S, swl, m);

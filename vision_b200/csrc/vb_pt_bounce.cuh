@@ -73,7 +73,8 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
     if (mediums && ps.ray_medium != VB_INVALID_ID) {         // integrator.cpp:199-206, homogeneous.cpp:50-70
         const vb_medium_rec &md = S.mediums[ps.ray_medium];
         f3 sigma_t = medium_sigma_t(S, swl, md);
-        f3 sigma_s = spec_unbound(S.spec, swl, f3{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale});
+        f3 sigma_s = spec_unbound_c(S.spec, swl, f3{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale}, true,
+                                    S.spec.cache_mediums + 2u * ps.ray_medium + 1u);
         uint32_t channel = min((uint32_t)(sampler.next_1d() * 3.0f), 2u);
         float sc_t = channel == 0 ? sigma_t.x : (channel == 1 ? sigma_t.y : sigma_t.z);
         float dist = -vlog(1.0f - sampler.next_1d()) / sc_t;

@@ -96,6 +96,34 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
 }
 
 // reference frame_buffer.cpp:72-74,135-144 + tonemapper/impl.cpp:21-46
+// hero spectrum: sigmoid-polynomial coefficients of every CONSTANT colour slot, decoded once per scene with the same device functions
+// the per-vertex path uses (DevSpectrum::cache). Entries of textured slots are written too but never read.
+__global__ void __launch_bounds__(128) k_spec_cache(PtScene S, uint32_t n_mat, uint32_t n_lights, uint32_t n_med, float4 *out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 4u * n_mat) {
+        const vb_material_rec &m = S.materials[i >> 2];
+        const uint32_t k = i & 3u;
+        f3 rgb = k == SC_COLOR ? f3{m.color.value[0], m.color.value[1], m.color.value[2]}
+               : k == SC_SPEC  ? f3{m.spec.value[0], m.spec.value[1], m.spec.value[2]}
+               : k == SC_SHEEN ? f3{m.params[4], m.params[5], m.params[6]} : f3{m.params[10], m.params[11], m.params[12]};
+        out[i] = spec_coefs_albedo(S.spec, rgb);
+        return;
+    }
+    i -= 4u * n_mat;
+    if (i < n_lights) {
+        const vb_light_rec &l = S.lights[i];
+        out[4u * n_mat + i] = spec_coefs_unbound(S.spec, f3{l.color.value[0], l.color.value[1], l.color.value[2]});
+        return;
+    }
+    i -= n_lights;
+    if (i < 2u * n_med) {
+        const vb_medium_rec &m = S.mediums[i >> 1];
+        f3 rgb = (i & 1u) ? f3{m.sigma_s[0] * m.scale, m.sigma_s[1] * m.scale, m.sigma_s[2] * m.scale}
+                          : f3{m.sigma_a[0] + m.sigma_s[0], m.sigma_a[1] + m.sigma_s[1], m.sigma_a[2] + m.sigma_s[2]} * m.scale;
+        out[4u * n_mat + n_lights + i] = spec_coefs_unbound(S.spec, rgb);
+    }
+}
+
 __global__ void __launch_bounds__(256) k_film_resolve(const float4 *accum, float4 *out, uint32_t n, int mode, float exposure, int tonemap) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -139,6 +167,7 @@ struct vb_pt_state {
     vb_medium_rec *d_mediums = nullptr; uint32_t n_mediums = 0;
     float *d_spd_values = nullptr; float4 *d_spd_meta = nullptr; uint32_t n_spds = 0; std::vector<uint32_t> h_spd_sizes;
     float *d_rgb2spec = nullptr; vb_spectrum_rec spectrum{}; bool have_spectrum = false;
+    float4 *d_spec_cache = nullptr; size_t spec_cache_n = 0; bool spec_dirty = true;   // hero: decoded constant colour slots (k_spec_cache)
     std::vector<vb_material_rec> h_mat;            // kept for the SPD index checks at render time
     vb_camera cam{}; bool have_cam = false;
     vb_pt_params params{}; bool have_params = false;
@@ -165,7 +194,7 @@ void vb_pt_destroy(vb_ctx *ctx) {
     for (auto t : p->tex_mem) cudaFree(t);
     for (auto &l : p->luts) cudaFree((void *)l.data);
     cudaFree(p->d_mediums);
-    cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta); cudaFree(p->d_rgb2spec);
+    cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta); cudaFree(p->d_rgb2spec); cudaFree(p->d_spec_cache);
     cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output); cudaFree(p->d_counters);
     if (p->wf) { wf_free(*p->wf); delete p->wf; }
     delete p;
@@ -248,6 +277,7 @@ int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n) {
     p->n_mat_types = (uint32_t)__builtin_popcount(types);
     p->has_principled = (types >> VB_MAT_PRINCIPLED) & 1u;
     p->h_mat.assign(mat, mat + n);
+    p->spec_dirty = true;
     if (n) {
         VB_CUDA(cudaMalloc(&p->d_mat, sizeof(vb_material_rec) * n));
         VB_CUDA(cudaMemcpy(p->d_mat, mat, sizeof(vb_material_rec) * n, cudaMemcpyHostToDevice));
@@ -280,6 +310,7 @@ int vb_mediums_set(vb_ctx *ctx, const vb_medium_rec *med, uint32_t n) {
     for (uint32_t i = 0; i < n; ++i)
         if (med[i].type != VB_MEDIUM_HOMOGENEOUS) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_mediums_set: medium type not implemented");
     cudaFree(p->d_mediums); p->d_mediums = nullptr; p->n_mediums = n;
+    p->spec_dirty = true;
     if (n) {
         VB_CUDA(cudaMalloc(&p->d_mediums, sizeof(vb_medium_rec) * n));
         VB_CUDA(cudaMemcpy(p->d_mediums, med, sizeof(vb_medium_rec) * n, cudaMemcpyHostToDevice));
@@ -296,6 +327,7 @@ int vb_spds_set(vb_ctx *ctx, const float *values, const uint32_t *offsets, uint3
         if (offsets[i + 1] < offsets[i] + 2) return ctx->fail(VB_ERR_INVALID, "vb_spds_set: an SPD needs at least 2 samples and ascending offsets");
     cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta);
     p->d_spd_values = nullptr; p->d_spd_meta = nullptr; p->n_spds = n;
+    p->spec_dirty = true;
     p->h_spd_sizes.resize(n);
     if (n) {
         std::vector<float4> meta(n);
@@ -324,6 +356,7 @@ int vb_spectrum_set(vb_ctx *ctx, const vb_spectrum_rec *spec) {
     if (spec->type > VB_SPECTRUM_HERO) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_spectrum_set: unknown spectrum type");
     cudaFree(p->d_rgb2spec); p->d_rgb2spec = nullptr;
     p->spectrum = *spec; p->spectrum.rgb2spec = nullptr; p->have_spectrum = true;
+    p->spec_dirty = true;
     if (spec->type == VB_SPECTRUM_HERO) {
         if (spec->dimension != 3) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_spectrum_set: hero spectrum is implemented for dimension 3 only");
         if (!spec->rgb2spec || spec->rgb2spec_res < 2) return ctx->fail(VB_ERR_INVALID, "vb_spectrum_set: hero spectrum needs the rgb2spec coefficient table");
@@ -352,6 +385,7 @@ int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n, const vb_
     }
     cudaFree(p->d_lights); cudaFree(p->d_alias); cudaFree(p->d_func);
     p->d_lights = nullptr; p->d_alias = nullptr; p->d_func = nullptr; p->n_lights = n; p->n_alias = n_alias;
+    p->spec_dirty = true;
     p->env_light = VB_INVALID_ID;
     for (uint32_t i = 0; i < n; ++i) if (lights[i].type == VB_LIGHT_ENV) p->env_light = i;
     if (n) {
@@ -435,7 +469,20 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
                 return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": material SPD index out of range (vb_spds_set)");
         if (p->h_spd_sizes[sp.spd_x] != p->h_spd_sizes[sp.spd_y] || p->h_spd_sizes[sp.spd_x] != p->h_spd_sizes[sp.spd_z])
             return ctx->fail(VB_ERR_UNSUPPORTED, std::string(fn) + ": the CIE x, y, z SPDs must have the same number of samples");
-        S.spec = DevSpectrum{p->d_rgb2spec, sp.rgb2spec_res, p->d_spd_values, p->d_spd_meta, sp.spd_x, sp.spd_y, sp.spd_z, sp.spd_d65, sp.cie_y_integral};
+        S.spec = DevSpectrum{p->d_rgb2spec, sp.rgb2spec_res, p->d_spd_values, p->d_spd_meta, sp.spd_x, sp.spd_y, sp.spd_z, sp.spd_d65, sp.cie_y_integral, nullptr, 0u, 0u};
+        if (ctx->opt_pt_spec_cache) {
+            const uint32_t n_entries = 4u * p->n_mat + p->n_lights + 2u * p->n_mediums;
+            if (p->spec_dirty || p->spec_cache_n != n_entries) {
+                cudaFree(p->d_spec_cache); p->d_spec_cache = nullptr; p->spec_cache_n = n_entries;
+                if (n_entries) {
+                    VB_CUDA(cudaMalloc(&p->d_spec_cache, sizeof(float4) * n_entries));
+                    k_spec_cache<<<(n_entries + 127) / 128, 128, 0, ctx->stream>>>(S, p->n_mat, p->n_lights, p->n_mediums, p->d_spec_cache);
+                    VB_CHECK_LAUNCH();
+                }
+                p->spec_dirty = false;
+            }
+            S.spec.cache = p->d_spec_cache; S.spec.cache_lights = 4u * p->n_mat; S.spec.cache_mediums = 4u * p->n_mat + p->n_lights;
+        }
     }
     if (p->params.process_mediums) {
         auto bad = [&](uint32_t id) { return id != VB_INVALID_ID && id >= p->n_mediums; };

@@ -20,7 +20,13 @@ struct DevSpectrum {
                                    // per-SPD constants of SPD::eval, divided once on the host (same IEEE operations, same bits)
     uint32_t spd_x, spd_y, spd_z, spd_d65;
     float cie_y_integral;
+    // decoded coefficients of the CONSTANT colour slots (c0, c1, c2, scale), filled once per scene by k_spec_cache with the same device
+    // functions the per-vertex path uses (identical bits): [4 * material + {0 color, 1 spec, 2 sheen tint, 3 coat tint}],
+    // [cache_lights + light], [cache_mediums + 2 * medium + {0 sigma_t, 1 sigma_s}]. Textured slots are decoded per texel as before.
+    const float4 *cache;
+    uint32_t cache_lights, cache_mediums;
 };
+enum : uint32_t { SC_COLOR = 0, SC_SPEC = 1, SC_SHEEN = 2, SC_COAT = 3 };
 
 struct Swl { float lambda[3], pdf[3]; };
 
@@ -121,10 +127,38 @@ __device__ __forceinline__ f3 spec_unbound(const DevSpectrum &P, const Swl *w, f
     f3 c = rgb2spec_decode(P, scale == 0.f ? f3{0, 0, 0} : rgb / scale);
     return sigmoid3(c, *w) * scale;
 }
+// the (c0, c1, c2, scale) record of decode_albedo / decode_unbound, as cached by k_spec_cache
+__device__ __forceinline__ float4 spec_coefs_albedo(const DevSpectrum &P, f3 rgb) {
+    f3 c = rgb2spec_decode(P, rgb);
+    return make_float4(c.x, c.y, c.z, 1.f);
+}
+__device__ __forceinline__ float4 spec_coefs_unbound(const DevSpectrum &P, f3 rgb_in) {
+    f3 rgb{fmax_(rgb_in.x, 0.f), fmax_(rgb_in.y, 0.f), fmax_(rgb_in.z, 0.f)};
+    float scale = 2.f * max_comp(rgb);
+    f3 c = rgb2spec_decode(P, scale == 0.f ? f3{0, 0, 0} : rgb / scale);
+    return make_float4(c.x, c.y, c.z, scale);
+}
+// cached variants: `constant` = the slot has no texture, so its coefficients are entry `idx` of the cache
+__device__ __forceinline__ f3 spec_albedo_c(const DevSpectrum &P, const Swl *w, f3 rgb, bool constant, uint32_t idx) {
+    if (!w) return rgb;
+    if (constant && P.cache) { float4 c = __ldg(P.cache + idx); return sigmoid3(f3{c.x, c.y, c.z}, *w); }
+    return spec_albedo(P, w, rgb);
+}
+__device__ __forceinline__ f3 spec_unbound_c(const DevSpectrum &P, const Swl *w, f3 rgb, bool constant, uint32_t idx) {
+    if (!w) return rgb;
+    if (constant && P.cache) { float4 c = __ldg(P.cache + idx); return sigmoid3(f3{c.x, c.y, c.z}, *w) * c.w; }
+    return spec_unbound(P, w, rgb);
+}
+__device__ __forceinline__ f3 spec_illum_c(const DevSpectrum &P, const Swl *w, f3 rgb, bool constant, uint32_t idx);
 // Spectrum::decode_to_illumination (hero.cpp:339-342,306-313): unbound x D65
 __device__ __forceinline__ f3 spec_illum(const DevSpectrum &P, const Swl *w, f3 rgb) {
     if (!w) return rgb;
     return spec_unbound(P, w, rgb) * spd_eval3(P, P.spd_d65, *w);
+}
+
+__device__ __forceinline__ f3 spec_illum_c(const DevSpectrum &P, const Swl *w, f3 rgb, bool constant, uint32_t idx) {
+    if (!w) return rgb;
+    return spec_unbound_c(P, w, rgb, constant, idx) * spd_eval3(P, P.spd_d65, *w);
 }
 
 // Spectrum::linear_srgb (hero.cpp:259-261,275-284; cie.h:413-420)
