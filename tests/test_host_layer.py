@@ -97,7 +97,8 @@ def test_host_records_equal_python_twin_materials_and_mediums(name):
 
 
 @pytest.mark.parametrize("rel", ["scenes/cbox/cbox_lights.json", "scenes/classroom/vision_scene.json", "scenes/cbox/cbox_sphere.json",
-                                 "scenes/cbox_dragon/vision_scene_small.json", "scenes/cbox/cbox_projector.json"])
+                                 "scenes/cbox_dragon/vision_scene_small.json", "scenes/cbox/cbox_projector.json",
+                                 "scenes/cbox_stock/vision_scene.json"])
 def test_host_records_equal_python_twin_lights_and_models(rel):
     """model shape (OBJ), point / spot / spherical lights, AliasTable2D, world diameter, Euler transforms, light order"""
     path = ROOT / rel
@@ -138,6 +139,13 @@ def test_host_records_equal_python_twin_lights_and_models(rel):
         assert a.camera.filter_type == capi.VB_FILTER_FITTED and a.camera.filter_table_offset == 2      # after the area light's 2 entries
         sph = a.meshes[a.instances[5]["mesh_id"]]
         assert len(sph["tri"]) == 48 * 2 + 22 * 48 * 2 and len(sph["pos"]) == 2 + 23 * 48               # sphere.cpp:55, sub_div 24
+    elif "cbox_stock" in rel:
+        # the stock file: lights in first-seen type order (spot, point, spherical, projector, then the shape's emission); the unused
+        # "mix" material is constructed (placeholder plugin) and dropped by remove_unused_materials
+        assert [l.type for l in a.lights] == [capi.VB_LIGHT_SPOT, capi.VB_LIGHT_POINT, capi.VB_LIGHT_ENV, capi.VB_LIGHT_PROJECTOR, capi.VB_LIGHT_AREA]
+        assert a.params.max_depth == 16 and a.camera.filter_type == capi.VB_FILTER_TRIANGLE and a.params.spectrum == capi.VB_SPECTRUM_SRGB
+        assert capi.VB_MAT_GLASS in [m.type for m in a.materials] and len(a.materials) == 8       # 8 of the 16 defined materials are used
+        assert "vision-material-mix#constructor" in host_api.plugin_names()
     else:
         assert [l.type for l in a.lights] == [capi.VB_LIGHT_POINT, capi.VB_LIGHT_SPOT, capi.VB_LIGHT_ENV, capi.VB_LIGHT_AREA]
         assert a.instances[-1]["light_id"] == 3

@@ -25,6 +25,10 @@ CASES = [
     ("classroom_fog", "scenes/classroom/vision_scene.json", {"resolution": [240, 136], "spp": 4}, 1e-5),
     # config C3: glass model filled with the Skin1 medium, trs transform, thin-lens camera (dragon stand-in, small version)
     ("cbox_dragon_small", "scenes/cbox_dragon/vision_scene_small.json", {"spp": 8}, 0.03),
+    # the reference's STOCK cbox file (tools/import_cbox_stock.py: only the stripped .hdr replaced): glass box, spot + point +
+    # spherical + projector + area lights, triangle filter, depth 16; under both spectra (its "spectrum" block has the type commented out)
+    ("cbox_stock", "scenes/cbox_stock/vision_scene.json", {"resolution": [160, 160], "spp": 4}, 0.05),
+    ("cbox_stock_hero", "scenes/cbox_stock/vision_scene.json", {"resolution": [160, 160], "spp": 4, "spectrum": "hero"}, 0.05),
 ]
 
 

@@ -324,6 +324,28 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(BlackBodyMaterial, material, black_body, constructor)
 
+// reference src/render_core/material/{mix,add,plastic,metallic,subsurface,multi_layered}.cpp: scene files may DEFINE these (the stock
+// cbox/vision_scene.json defines an unused "mix"); Scene::load_materials constructs every listed material and
+// remove_unused_materials (scene.cpp:79-91) drops the unused ones. They construct here so such files load; USING one is refused
+// loudly when its record is asked for (their lobes are not built - SURVEY.md 8f N3).
+#define VH_UNBUILT_MATERIAL(Class, tag)                                                                              \
+    class Class : public Material {                                                                                  \
+    public:                                                                                                          \
+        explicit Class(const MaterialDesc &d) : Material(d) { name_ = d.name; }                                      \
+        std::string impl_type() const override { return #tag; }                                                      \
+        void fill_record(vb_material_rec &, const SlotContext &) const override {                                    \
+            throw std::runtime_error("material '" + name_ + "' (" #tag "): this material type is not implemented");  \
+        }                                                                                                            \
+    };                                                                                                               \
+    VH_MAKE_CLASS_CREATOR(Class, material, tag, constructor)
+VH_UNBUILT_MATERIAL(MixMaterial, mix)
+VH_UNBUILT_MATERIAL(AddMaterial, add)
+VH_UNBUILT_MATERIAL(PlasticMaterial, plastic)
+VH_UNBUILT_MATERIAL(MetallicMaterial, metallic)
+VH_UNBUILT_MATERIAL(SubsurfaceMaterial, subsurface)
+VH_UNBUILT_MATERIAL(MultiLayeredMaterial, multi_layered)
+#undef VH_UNBUILT_MATERIAL
+
 // ---- warper ------------------------------------------------------------------------------------
 // reference src/render_core/warper/alias.h:86-122 (sum in double, probabilities in float, LIFO stacks)
 class AliasTable : public Warper {
