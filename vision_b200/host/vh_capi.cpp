@@ -100,4 +100,17 @@ VB_API uint64_t vh_scene_log(vh_pipeline *h, char *dst, uint64_t cap) {
     return s.size() + 1;
 }
 
+/* image files (vh_image.cpp): save by extension (.png / .ppm with the display gamma, .hdr / .pfm linear); load (.hdr natively, .pfm,
+ * .ppm, other LDR formats through their side-cars) - first call with dst = null to get the size */
+VB_API int vh_save_image(const char *path, const float *rgba, uint32_t w, uint32_t h) { VH_TRY(save_image(path, rgba, w, h)) }
+VB_API int vh_load_image(const char *path, int srgb_to_linear, uint32_t *w, uint32_t *h, float *dst, uint64_t cap_floats) {
+    VH_TRY({
+        Image im = load_image(path, srgb_to_linear != 0);
+        *w = im.w; *h = im.h;
+        if (dst && cap_floats >= im.rgba.size()) std::memcpy(dst, im.rgba.data(), im.rgba.size() * 4);
+    })
+}
+VB_API void vh_rgbe_encode(const float *rgb, unsigned char *out4) { rgbe_encode(rgb, out4); }
+VB_API void vh_rgbe_decode(const unsigned char *in4, float *rgb) { rgbe_decode(in4, rgb); }
+
 }  // extern "C"

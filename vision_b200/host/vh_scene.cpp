@@ -27,6 +27,7 @@ static bool read_pnm_token(std::istream &f, std::string &tok) {
 Image load_image(const std::string &path, bool to_linear) {
     std::string p = path;
     auto ends = [&](const char *e) { size_t n = strlen(e); return p.size() >= n && strcasecmp(p.c_str() + p.size() - n, e) == 0; };
+    if (ends(".hdr") && std::ifstream(path, std::ios::binary)) return load_hdr(path);      // native reader; linear by definition (image_pool.cpp:18-24)
     if (!ends(".pfm") && !ends(".ppm")) {                          // decoded side-car (tools/convert_textures.py): 8-bit .ppm, else float .pfm
         p = path + ".ppm";
         if (!std::ifstream(p, std::ios::binary)) p = path + ".pfm";
@@ -55,15 +56,24 @@ Image load_image(const std::string &path, bool to_linear) {
     if (to_linear) for (size_t i = 0; i < (size_t)im.w * im.h; ++i) for (int c = 0; c < 3; ++c) im.rgba[4 * i + c] = srgb_to_linear(im.rgba[4 * i + c]);
     return im;
 }
+// writers use C stdio (no iostream number formatting: no locale dependence when loaded into a foreign process)
 void save_pfm(const std::string &path, const float *rgba, uint32_t w, uint32_t h) {
-    std::ofstream f(path, std::ios::binary);
-    f << "PF\n" << w << " " << h << "\n-1.0\n";
-    for (uint32_t y = 0; y < h; ++y) for (uint32_t x = 0; x < w; ++x) f.write((const char *)&rgba[((size_t)(h - 1 - y) * w + x) * 4], 12);
+    FILE *f = std::fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    std::fprintf(f, "PF\n%u %u\n-1.0\n", w, h);
+    for (uint32_t y = 0; y < h; ++y) for (uint32_t x = 0; x < w; ++x) std::fwrite(&rgba[((size_t)(h - 1 - y) * w + x) * 4], 4, 3, f);
+    std::fclose(f);
 }
 void save_ppm(const std::string &path, const float *rgba01, uint32_t w, uint32_t h) {
-    std::ofstream f(path, std::ios::binary);
-    f << "P6\n" << w << " " << h << "\n255\n";
-    for (size_t i = 0; i < (size_t)w * h; ++i) for (int c = 0; c < 3; ++c) { unsigned char b = (unsigned char)(linear_to_srgb(rgba01[4 * i + c]) * 255.f + 0.5f); f.put((char)b); }
+    FILE *f = std::fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    std::fprintf(f, "P6\n%u %u\n255\n", w, h);
+    std::vector<unsigned char> row((size_t)w * 3);
+    for (uint32_t y = 0; y < h; ++y) {
+        for (size_t i = 0; i < (size_t)w; ++i) for (int c = 0; c < 3; ++c) row[3 * i + c] = (unsigned char)(linear_to_srgb(rgba01[4 * ((size_t)y * w + i) + c]) * 255.f + 0.5f);
+        std::fwrite(row.data(), 1, row.size(), f);
+    }
+    std::fclose(f);
 }
 // reference image_pool.cpp:13-35: .exr/.hdr are linear, everything else follows color_space (default srgb)
 uint32_t ImagePool::obtain(const std::string &path, const std::string &color_space) {

@@ -14,6 +14,13 @@ struct Image { uint32_t w = 0, h = 0; std::vector<float> rgba; };
 Image load_image(const std::string &path, bool srgb_to_linear);
 void save_pfm(const std::string &path, const float *rgba, uint32_t w, uint32_t h);
 void save_ppm(const std::string &path, const float *rgba01, uint32_t w, uint32_t h);   // applies linear_to_srgb
+// vh_image.cpp: Radiance .hdr read / write, PNG write, output dispatch by extension ("gamma unless exr / hdr", pipeline.cpp:337-354)
+Image load_hdr(const std::string &path);
+void save_hdr(const std::string &path, const float *rgba, uint32_t w, uint32_t h);
+void save_png(const std::string &path, const float *rgba01, uint32_t w, uint32_t h, bool gamma);
+void save_image(const std::string &path, const float *rgba, uint32_t w, uint32_t h);
+void rgbe_encode(const float *rgb, unsigned char *out);
+void rgbe_decode(const unsigned char *in, float *rgb);
 
 class ImagePool {
 public:

@@ -18,7 +18,7 @@ int main(int argc, char **argv) {
         else if (a == "--spp") spp = (uint32_t)std::stoul(next());
         else if (a == "-d" || a == "--device") device = next();
         else if (a == "--device-index") dev_index = std::stoi(next());
-        else if (a == "-h" || a == "--help") { printf("vision-cli -s scene.json [-o out.ppm] [--pfm out.pfm] [--spp N] [-d cuda]\n"); return 0; }
+        else if (a == "-h" || a == "--help") { printf("vision-cli -s scene.json [-o out.png|.ppm|.hdr|.pfm] [--pfm out.pfm] [--spp N] [-d cuda]\n"); return 0; }
         else fprintf(stderr, "ignored argument %s\n", a.c_str());
     }
     if (scene.empty()) { fprintf(stderr, "vision-cli: -s <scene file> is required\n"); return 2; }
@@ -38,7 +38,7 @@ int main(int argc, char **argv) {
                 p->records.width, p->records.height, n, (unsigned long long)p->build_stats.n_triangles,
                 (unsigned long long)p->build_stats.n_nodes, p->build_stats.build_ms,
                 std::chrono::duration<double, std::milli>(t1 - t0).count(), std::chrono::duration<double, std::milli>(t2 - t1).count());
-        vh::save_ppm(out, img.data(), p->records.width, p->records.height);
+        vh::save_image(out, img.data(), p->records.width, p->records.height);      // .png / .ppm (display gamma) or .hdr / .pfm (linear)
         if (!pfm.empty()) {
             std::vector<float> acc((size_t)p->records.width * p->records.height * 4);
             p->check(vb_film_download(p->ctx, acc.data(), VB_FILM_ACCUM), "vb_film_download");

@@ -31,6 +31,10 @@ def load():
         lib.vh_download_accum.argtypes = [vp, vp]
         lib.vh_info.argtypes = [vp, vp, vp]; lib.vh_info.restype = None
         lib.vh_records_blob.argtypes = [vp, C.c_int, vp, C.c_uint64]; lib.vh_records_blob.restype = C.c_uint64
+        lib.vh_save_image.argtypes = [C.c_char_p, vp, C.c_uint32, C.c_uint32]; lib.vh_save_image.restype = C.c_int
+        lib.vh_load_image.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), vp, C.c_uint64]; lib.vh_load_image.restype = C.c_int
+        lib.vh_rgbe_encode.argtypes = [vp, vp]; lib.vh_rgbe_encode.restype = None
+        lib.vh_rgbe_decode.argtypes = [vp, vp]; lib.vh_rgbe_decode.restype = None
         lib.vh_mesh_info.argtypes = [vp, C.c_uint32, vp, vp]; lib.vh_mesh_info.restype = None
         lib.vh_mesh_copy.argtypes = [vp, C.c_uint32, vp, vp, vp, vp]; lib.vh_mesh_copy.restype = None
         lib.vh_texture_info.argtypes = [vp, C.c_uint32, vp, vp]; lib.vh_texture_info.restype = None
@@ -158,3 +162,26 @@ class HostPipeline:
             sc.textures.append(a)
         sc.resolution = (i["width"], i["height"]); sc.spp = i["spp"]; sc.exposure = i["exposure"]; sc.tonemap = i["tonemap"]
         return sc
+
+
+def save_image(path, rgba) -> None:
+    """host layer's output writer: .png / .ppm get the display gamma, .hdr / .pfm stay linear (pipeline.cpp:337-354)"""
+    a = np.ascontiguousarray(rgba, np.float32)
+    if load().vh_save_image(str(path).encode(), a.ctypes.data, a.shape[1], a.shape[0]) != 0:
+        raise capi.VbError(load().vh_last_error().decode())
+
+
+def load_image(path, srgb_to_linear=False) -> np.ndarray:
+    lib = load()
+    w, h = C.c_uint32(), C.c_uint32()
+    if lib.vh_load_image(str(path).encode(), int(srgb_to_linear), C.byref(w), C.byref(h), None, 0) != 0:
+        raise capi.VbError(lib.vh_last_error().decode())
+    a = np.empty((h.value, w.value, 4), np.float32)
+    lib.vh_load_image(str(path).encode(), int(srgb_to_linear), C.byref(w), C.byref(h), a.ctypes.data, a.size)
+    return a
+
+
+def rgbe_encode(rgb) -> bytes:
+    a = np.ascontiguousarray(rgb, np.float32); out = (C.c_ubyte * 4)()
+    load().vh_rgbe_encode(a.ctypes.data, out)
+    return bytes(out)

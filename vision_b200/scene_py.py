@@ -366,9 +366,42 @@ def alias2d_build(weights, rx, ry):
     return mt, mf, mi, cond_table, cond_func
 
 
+def read_hdr(path):
+    """Radiance RGBE (.hdr): flat and new-style run-length scanlines -> (h, w, 4) float32, linear"""
+    data = Path(path).read_bytes()
+    pos = data.index(b"\n\n") + 2
+    assert data.startswith(b"#?") and b"FORMAT=32-bit_rle_rgbe" in data[:pos], path
+    end = data.index(b"\n", pos)
+    tok = data[pos:end].split()
+    assert tok[0] == b"-Y" and tok[2] == b"+X", tok
+    h, w = int(tok[1]), int(tok[3])
+    pos = end + 1
+    out = np.zeros((h, w, 4), np.uint8)
+    for y in range(h):
+        head = data[pos:pos + 4]
+        if 8 <= w < 32768 and head[0] == 2 and head[1] == 2 and (head[2] << 8 | head[3]) == w:
+            pos += 4
+            for c in range(4):
+                x = 0
+                while x < w:
+                    n = data[pos]; pos += 1
+                    if n > 128:
+                        out[y, x:x + n - 128, c] = data[pos]; pos += 1; x += n - 128
+                    else:
+                        out[y, x:x + n, c] = np.frombuffer(data, np.uint8, n, pos); pos += n; x += n
+        else:
+            out[y] = np.frombuffer(data, np.uint8, 4 * w, pos).reshape(w, 4); pos += 4 * w
+    e = out[..., 3].astype(np.int32)
+    scale = np.where(e == 0, f32(0), np.ldexp(f32(1.0), e - 136)).astype(f32)
+    rgb = out[..., :3].astype(f32) * scale[..., None]
+    return np.ascontiguousarray(np.concatenate([rgb, np.ones((h, w, 1), f32)], axis=-1), f32)
+
+
 def load_image(path, color_space):
     if Path(path).suffix.lower() == ".pfm":
         return read_pfm(path)
+    if Path(path).suffix.lower() == ".hdr":
+        return read_hdr(path)
     from PIL import Image
     im = np.asarray(Image.open(path).convert("RGBA"), np.float32) / f32(255.0)
     if color_space == "srgb" and Path(path).suffix.lower() not in (".exr", ".hdr"):
