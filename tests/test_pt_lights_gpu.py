@@ -74,3 +74,38 @@ def test_image_matches_oracle(vbctx, oracle, name, path, ov, min_mean):
         assert np.array_equal(g, vbctx.film_download(capi.VB_FILM_ACCUM))
     finally:
         vbctx.set_option("pt.max_paths", 1 << 25)
+
+
+@pytest.mark.parametrize("name,path,ov", [
+    ("classroom_full", "scenes/classroom/vision_scene.json", {"spp": 2}),                                  # config C5: 1920x1080
+    ("dispersion_full", "scenes/cbox/cbox_dispersion.json", {"resolution": [1024, 1024], "spp": 2}),       # config C4: hero spectrum
+])
+def test_full_size_schedules_and_partitions_agree(vbctx, name, path, ov):
+    """BASELINE.json configs at their full resolution, through properties that need no oracle run: the wavefront and megakernel
+    schedules give bit-identical films and counters; the frames rendered as one batch, as single frames, and as two strided
+    halves (the multi-GPU partition, SUM films added) give the same film."""
+    sc = scene_py.build_scene(ROOT / path, ov)
+    vbctx.upload_scene(sc)
+    vbctx.film_clear()
+    vbctx.render_frames(0, 2, 1, capi.VB_ACCUM_SUM)
+    g = vbctx.film_download(capi.VB_FILM_ACCUM)
+    st = vbctx.render_stats()
+    assert g.shape[:2] == (sc.resolution[1], sc.resolution[0]) and np.isfinite(g).all() and (g[..., 3] == 2).all()
+    assert st["closest"] >= 2 * g.shape[0] * g.shape[1]
+    vbctx.set_option("pt.schedule", 1)
+    try:
+        vbctx.film_clear()
+        vbctx.render_frames(0, 2, 1, capi.VB_ACCUM_SUM)
+        assert np.array_equal(vbctx.film_download(capi.VB_FILM_ACCUM), g) and vbctx.render_stats() == st
+    finally:
+        vbctx.set_option("pt.schedule", 0)
+    vbctx.film_clear()
+    vbctx.render_frames(0, 1, 1, capi.VB_ACCUM_SUM)
+    vbctx.render_frames(1, 1, 1, capi.VB_ACCUM_SUM)
+    assert np.array_equal(vbctx.film_download(capi.VB_FILM_ACCUM), g)
+    halves = []
+    for rank in (0, 1):                                            # rank r of 2 renders frames r, r + 2, ...
+        vbctx.film_clear()
+        vbctx.render_frames(rank, 1, 2, capi.VB_ACCUM_SUM)
+        halves.append(vbctx.film_download(capi.VB_FILM_ACCUM))
+    assert np.array_equal(halves[0] + halves[1], g)

@@ -172,3 +172,37 @@ def test_errors_are_reported(vbctx):
         vbctx.instances_set([{"mesh_id": 10_000}])
     with pytest.raises(VbError):
         vbctx.mesh_upload(np.zeros((3, 3), np.float32), np.array([[0, 1, 7]], np.uint32))
+
+
+def test_full_size_properties_16Mi_rays_10M_triangles(vbctx, oracle):
+    """BASELINE.json configs[1] at its full size, through size-independent properties (the oracle would need minutes here):
+    (1) closest / any consistency: no triangle lies in front of the reported closest hit (any-hit with t_max just below t is
+        free) and the hit triangle itself occludes (any-hit with t_max just above t is occluded); rays that miss are free;
+    (2) order independence: the answer of a ray does not depend on where it sits in the batch (reversed batch -> reversed answers);
+    (3) a 1/64 sample of the rays agrees bit for bit with the oracle's own BVH over the same 10 M triangles."""
+    n_tri, n_rays = 10_000_000, 1 << 24
+    mesh = oracle.synth_mesh(n_tri, seed=1, threads=oracle.hw_threads())
+    rays = oracle.synth_rays(n_rays, seed=2, seed_any=3, threads=oracle.hw_threads())
+    st = _build_soup(vbctx, mesh)
+    assert st["n_triangles"] == n_tri
+    g = vbctx.trace_closest(rays)
+    hit = g["inst"] != MISS
+    assert 0.85 < hit.mean() < 0.97
+    t = g["t"]
+    assert np.all(t[hit] > 0) and np.all(np.isfinite(t[hit])) and np.all(g["u"][hit] >= 0) and np.all(g["u"][hit] + g["v"][hit] <= 1.0 + 1e-6)
+    below = dict(rays, tmax=np.where(hit, t * np.float32(1 - 1e-4), rays["tmax"]).astype(np.float32))
+    above = dict(rays, tmax=np.where(hit, t * np.float32(1 + 1e-4), rays["tmax"]).astype(np.float32))
+    occ_below, occ_above = vbctx.trace_any(below), vbctx.trace_any(above)
+    assert not occ_below.any()                                   # nothing in front of the closest hit; misses stay free
+    assert np.array_equal(occ_above.astype(bool), hit)           # the hit triangle occludes; misses stay free
+    rev = {k: np.ascontiguousarray(v[::-1]) for k, v in rays.items()}
+    gr = vbctx.trace_closest(rev)
+    for f in ("inst", "prim", "u", "v", "t"):
+        assert np.array_equal(gr[f][::-1], g[f]), f
+    sub = {k: np.ascontiguousarray(v[::64]) for k, v in rays.items()}
+    acc = oracle.accel()
+    acc.add_soup(mesh)
+    acc.build(oracle.hw_threads())
+    o = acc.trace_closest(sub, threads=oracle.hw_threads())
+    for f in ("inst", "prim", "u", "v", "t"):
+        assert np.array_equal(o[f], g[f][::64]), f
