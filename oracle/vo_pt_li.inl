@@ -369,6 +369,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
     float scatter_pdf = 1e16f;
     float3 throughput{1, 1, 1}, ret{0, 0, 0};
     float3 prev_surface_ng = ray.d;
+    const float3 primary_dir = ray.d;
     float eta_scale = 1.f;
     const uint32_t max_depth = params.max_depth;
     uint32_t env_light = VB_INVALID_ID;                             // LightSampler::env_light_ (lightsampler.cpp:18-25): the last one wins
@@ -482,6 +483,58 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
         scatter_pdf = bs.eval.pdf;
         ray = spawn_ray(it, bs.wi);
         if (mediums) ray_medium = dot(it.ng, bs.wi) > 0.f ? it.outside : it.inside;
+    }
+    // "Supplement only direct light BSDF sampling" (integrator.cpp:176-233,303-309): with max_depth < 2 and MIS mode "both", ONE more
+    // mis_bsdf(inner = false): the last spawned ray is traced and emission / environment gathered with the BSDF-side MIS weight
+    if (max_depth < 2 && params.mis_mode == 0) {
+        for (uint32_t bounce = 0; bounce < 1u; ++bounce) {
+            Hit hit = trace_closest(ray, st);
+            if (ray.d.x == primary_dir.x && ray.d.y == primary_dir.y && ray.d.z == primary_dir.z) break;      // primary_miss: nothing was scattered
+            if (hit.is_miss()) {
+                if (env_light != VB_INVALID_ID) {
+                    const vb_light_rec &l = lights[env_light];
+                    float3 tr{1, 1, 1};
+                    if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(*this, swl, ray_medium, ray); }
+                    LightEval ev = env_evaluate_wi(*this, swl, l, ray.o, ray.o + ray.d);
+                    ev.pdf *= 1.0f / (float)lights.size();
+                    float weight = mis_weight(scatter_pdf, ev.pdf);
+                    ret += spec_to_srgb(*this, swl, ev.L * tr * weight * throughput);
+                }
+                break;
+            }
+            Interaction it = compute_surface_interaction(*this, hit.inst, hit.prim, hit.u, hit.v, true);
+            it.wo = normalize(-ray.d);
+            ray.tmax = length(it.pos - ray.o) / length(ray.d);
+            if (st) st->vertices++;
+            if (mediums && ray_medium != VB_INVALID_ID) {
+                const vb_medium_rec &md = this->mediums[ray_medium];
+                float3 sigma_t = medium_sigma_t(*this, swl, md);
+                float3 sigma_s = spec_unbound(*this, swl, float3{md.sigma_s[0] * md.scale, md.sigma_s[1] * md.scale, md.sigma_s[2] * md.scale});
+                uint32_t channel = std::min((uint32_t)(sampler.next_1d() * 3.0f), 2u);
+                float sc_t = channel == 0 ? sigma_t.x : (channel == 1 ? sigma_t.y : sigma_t.z);
+                float dist = -vlog(1.0f - sampler.next_1d()) / sc_t;
+                float t = std::min(dist / length(ray.d), ray.tmax);
+                bool sampled_medium = t < ray.tmax;
+                if (sampled_medium) { Interaction mi; mi.has_phase = true; mi.inside = ray_medium; mi.outside = ray_medium; it = mi; }
+                float3 tr = medium_Tr(*this, swl, md, t);
+                float3 density = sampled_medium ? sigma_t * tr : tr;
+                float pdf = average3(density);
+                float3 mt = sampled_medium ? tr * sigma_s / pdf : tr / pdf;
+                throughput *= mt;
+            }
+            if (it.mat_id == VB_INVALID_ID && !it.has_phase) {
+                ray = spawn_ray(it, ray.d);
+                if (mediums) ray_medium = dot(it.ng, ray.d) > 0.f ? it.outside : it.inside;
+                bounce -= 1;
+                continue;
+            }
+            if (it.light_id != VB_INVALID_ID) {
+                LightEval ev = evaluate_hit_wi(*this, swl, ray.o, it);
+                float3 tr = ray_Tr(*this, swl, ray_medium, ray);
+                float weight = mis_weight(scatter_pdf, ev.pdf);
+                ret += spec_to_srgb(*this, swl, ev.L * throughput * weight * tr);
+            }
+        }
     }
     (void)prev_surface_ng;
     return ret;

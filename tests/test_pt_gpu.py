@@ -104,3 +104,35 @@ def test_resolve_tonemap(vbctx, cbox):
     ref = np.clip((x * (2.51 * x + 0.03)) / (x * (2.43 * x + 0.59) + 0.14), 0, 1)
     np.testing.assert_allclose(out[..., :3], ref, atol=2e-6)
     assert (out[..., 3] == 1).all()
+
+
+@pytest.mark.parametrize("name,ov", [("cbox_matte", {}), ("cbox_lights", {}), ("cbox_fog", {}), ("cbox_materials", {"spectrum": "hero"})])
+@pytest.mark.parametrize("max_depth", [0, 1])
+def test_only_direct_supplement_matches_oracle(vbctx, oracle, name, ov, max_depth):
+    """Li with max_depth < 2 (only_direct, integrator.cpp:303-309): after the single bounce ONE more mis_bsdf(inner = false) gathers
+    emission / environment along the BSDF-sampled ray with the BSDF-side MIS weight. max_depth 0 renders black. Both schedules."""
+    import oracle_lib
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    sc = scene_py.build_scene(root / "scenes" / "cbox" / f"{name}.json", dict(ov, resolution=[128, 128], spp=8, max_depth=max_depth))
+    assert sc.params.max_depth == max_depth and sc.params.mis_mode == 0
+    vbctx.upload_scene(sc)
+    osc = oracle_lib.OracleScene(oracle, sc, threads=oracle.hw_threads())
+    o, _ = osc.render(0, sc.spp, threads=oracle.hw_threads())
+    films = []
+    for sched in (0, 1):
+        vbctx.set_option("pt.schedule", sched)
+        try:
+            vbctx.film_clear()
+            vbctx.render_frames(0, sc.spp, 1, capi.VB_ACCUM_LERP)
+            films.append(vbctx.film_download(capi.VB_FILM_ACCUM))
+        finally:
+            vbctx.set_option("pt.schedule", 0)
+    assert np.array_equal(films[0], films[1])
+    assert np.array_equal(films[0][..., :3], o[..., :3])
+    if max_depth == 0:
+        assert not films[0][..., :3].any()
+    else:
+        # the supplement adds light: the same scene rendered with MIS mode "light" only (no supplement) is darker where BSDF
+        # sampling finds the emitter
+        assert films[0][..., :3].mean() > 0.0

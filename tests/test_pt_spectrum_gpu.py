@@ -99,3 +99,19 @@ def test_cached_constant_slot_coefficients_give_the_same_film(vbctx, name):
     finally:
         vbctx.set_option("pt.spec_cache", 1)
     assert np.array_equal(films[0], films[1])
+
+
+def test_spectrum_api_rejects_bad_input(vbctx):
+    import ctypes as C
+    capi._bind_pt(vbctx.lib)
+    vals = np.arange(6, dtype=np.float32)
+    for offs in ([0, 1, 6], [0, 4, 3]):                                   # an SPD with one sample; descending offsets
+        o = np.asarray(offs, np.uint32)
+        assert vbctx.lib.vb_spds_set(vbctx.h, vals.ctypes.data, o.ctypes.data, 2) != 0
+    rec = capi.vb_spectrum_rec()
+    rec.type, rec.dimension, rec.rgb2spec_res = capi.VB_SPECTRUM_HERO, 4, 64
+    assert vbctx.lib.vb_spectrum_set(vbctx.h, C.byref(rec)) != 0           # dimension 4: not implemented, said so
+    rec.dimension = 3
+    assert vbctx.lib.vb_spectrum_set(vbctx.h, C.byref(rec)) != 0           # no coefficient table
+    rec.type = 7
+    assert vbctx.lib.vb_spectrum_set(vbctx.h, C.byref(rec)) != 0           # unknown spectrum

@@ -138,7 +138,7 @@ __device__ ScatterEval diffuse_evaluate_local(const Lobe &lb, f3 wo, f3 wi) {
 }
 
 // Lobe::evaluate_impl (lobe.cpp:53-77): world -> local, f *= |cos(wi)|
-__device__ ScatterEval lobe_evaluate(const PtScene &S, const Lobe &lb, f3 world_wo, f3 world_wi, bool with_eta, float *eta_out) {
+__device__ __forceinline__ ScatterEval lobe_evaluate(const PtScene &S, const Lobe &lb, f3 world_wo, f3 world_wi, bool with_eta, float *eta_out) {
     f3 wo = lb.frame.to_local(world_wo), wi = lb.frame.to_local(world_wi);
     ScatterEval se;
     switch (lb.type) {
@@ -161,7 +161,7 @@ __device__ __forceinline__ f3 cosine_hemisphere(f2 u, float woz) {
 }
 
 // Lobe::sample (lobe.cpp:111-119) with each lobe's sample_wi_local_impl; draws in the reference's order
-__device__ BSDFSample lobe_sample(const PtScene &S, const Lobe &lb, f3 world_wo, Sampler &sampler) {
+__device__ __forceinline__ BSDFSample lobe_sample(const PtScene &S, const Lobe &lb, f3 world_wo, Sampler &sampler) {
     f3 wo = lb.frame.to_local(world_wo);
     f3 wi;
     bool valid = true;
@@ -214,7 +214,7 @@ __device__ __forceinline__ f3 material_color(const PtScene &S, const Swl *swl, c
 }
 
 // Material::create_evaluator -> create_lobe_set of the plugin
-__device__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction &it) {
+__device__ __forceinline__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction &it) {
     const vb_material_rec &m = S.materials[it.mat_id];
     Lobe lb;
     lb.type = m.type;

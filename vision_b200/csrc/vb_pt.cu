@@ -78,7 +78,7 @@ __device__ __forceinline__ f3 lerp3(float u, float v, f3 a, f3 b, f3 c) {
 __device__ __forceinline__ bool is_zero(f3 v) { return v.x == 0.f && v.y == 0.f && v.z == 0.f; }
 
 // reference src/base/mgr/geometry.cpp:79-166
-__device__ Interaction compute_surface_interaction(const PtScene &S, uint32_t inst_id, uint32_t prim_id, float bu, float bv,
+__device__ __forceinline__ Interaction compute_surface_interaction(const PtScene &S, uint32_t inst_id, uint32_t prim_id, float bu, float bv,
                                                    bool is_complete) {
     Interaction it;
     it.prim_id = prim_id;

@@ -11,7 +11,8 @@ struct PathState {
     f3 throughput, ret;
     float eta_scale, scatter_pdf;
     uint32_t ray_medium, bounces;
-    uint32_t swl;              // hero spectrum: bits 0..23 wavelength draw, bit 31 secondary wavelengths invalidated (vb_spectrum.cuh)
+    uint32_t swl;              // hero spectrum: bits 0..23 wavelength draw, bit 31 secondary wavelengths invalidated (vb_spectrum.cuh);
+                               // bit 30: the "only direct" supplement step (Li with max_depth < 2, integrator.cpp:303-309)
 };
 
 __device__ __forceinline__ void path_begin(const PtScene &S, PathState &ps, uint32_t px, uint32_t py, uint32_t frame) {
@@ -31,8 +32,9 @@ __device__ __forceinline__ void path_begin(const PtScene &S, PathState &ps, uint
 
 enum : int { PT_CONTINUE = 1, PT_SHADOW = 2, PT_VERTEX = 4, PT_LIGHT = 8 };
 
+
 // in: the ray that was traced and its closest hit. out (by flag): PT_CONTINUE -> `ray` holds the next ray
-// and ps.bounces is advanced (the caller checks bounces < max_depth before tracing it); PT_SHADOW ->
+// and ps.bounces is advanced (max_depth is enforced here); PT_SHADOW ->
 // `shadow` must be tested for occlusion and `pending` added to ps.ret when it is free; PT_VERTEX -> a
 // surface interaction was computed, PT_LIGHT -> a light was sampled (statistics: a PT_LIGHT vertex without
 // PT_SHADOW is a shadow ray the reference traces although its contribution is zero; it is culled here). Without PT_CONTINUE the path is finished: ps.ret
@@ -118,6 +120,12 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         f3 d = ev.L * ps.throughput * weight * tr;
         ps.ret = ps.ret + spec_to_srgb(S.spec, swl, d);
     }
+    // Li with max_depth < 2 and MIS "both" appends ONE mis_bsdf(inner = false) (integrator.cpp:176-233,303-309): the BSDF-sampled ray
+    // is traced and only emission / environment are gathered with the BSDF-side MIS weight - no light sample, no further scatter.
+    // The reference starts that step whenever the final ray's direction differs from the primary ray's (:179-184); here the bit is
+    // set exactly when a scatter produced that ray, which is the same thing unless a sampled direction equals the primary
+    // direction bit for bit (the oracle applies the reference's rule; the parity tests would show such a path)
+    if (ps.swl & PathSupplementBit) return PT_VERTEX;
     // light sampling
     float u_light = sampler.next_1d();
     f2 u_surface = sampler.next_2d();
@@ -185,6 +193,10 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
     ray = spawn_ray(it, bs.wi);
     if (mediums) ps.ray_medium = dot(it.ng, bs.wi) > 0.f ? it.outside : it.inside;
     ps.bounces = bounces + 1;
+    if (ps.bounces >= S.params.max_depth) {                       // depth exhausted: the path ends here ...
+        if (!(S.params.max_depth < 2 && S.params.mis_mode == 0)) return flags;
+        ps.swl |= PathSupplementBit;                              // ... unless Li's only_direct supplement applies
+    }
     return flags | PT_CONTINUE;
 }
 

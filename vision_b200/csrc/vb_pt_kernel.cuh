@@ -12,7 +12,7 @@ struct PtCounters { unsigned long long closest, any, vertices, culled; };
 // its next frame in the same iteration instead of waiting for the longest path of the warp. The
 // running film value stays in registers and is written once per launch.
 template <bool DUMP_PRIMARY, int VARIANT>
-__global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t first_frame, uint32_t n_frames, uint32_t stride, int mode,
+__global__ void __launch_bounds__(PT_BLOCK) k_path_trace(const __grid_constant__ PtScene S, uint32_t first_frame, uint32_t n_frames, uint32_t stride, int mode,
                                                          uint32_t frames_done, float4 *rt, float4 *accum, PtCounters *counters,
                                                          uint32_t *h_inst, uint32_t *h_prim, float *h_u, float *h_v, float *h_t) {
     __shared__ uint2 s_stack_all[VB_SM_STACK * PT_BLOCK];
@@ -52,7 +52,15 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
                 ray = generate_camera_ray(S, sampler, px, py);
                 path_begin(S, ps, px, py, frame);
                 need_new = max_depth == 0;
-                if (need_new) { fi++; last = make_float4(0.f, 0.f, 0.f, 1.f); }      // no bounce: black sample
+                if (need_new) {                                                      // no bounce: a black sample (L, 1) = (0, 0, 0, 1)
+                    last = make_float4(0.f, 0.f, 0.f, 1.f);
+                    if (mode == VB_ACCUM_LERP) {
+                        float t = 1.0f / (float)(frames_done + fi + 1);
+                        acc.x = acc.x + t * (last.x - acc.x); acc.y = acc.y + t * (last.y - acc.y);
+                        acc.z = acc.z + t * (last.z - acc.z); acc.w = acc.w + t * (last.w - acc.w);
+                    } else acc.w += 1.f;
+                    fi++;
+                }
             }
         }
         if (__all_sync(~0u, done)) break;
@@ -71,7 +79,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(PtScene S, uint32_t fir
             c_any++;
             if (!occluded) ps.ret = ps.ret + pending;
         }
-        if (run && (!(flags & PT_CONTINUE) || ps.bounces >= max_depth)) {
+        if (run && !(flags & PT_CONTINUE)) {
             last = make_float4(ps.ret.x, ps.ret.y, ps.ret.z, 1.f);
             if (mode == VB_ACCUM_LERP) {
                 float t = 1.0f / (float)(frames_done + fi + 1);
@@ -323,28 +331,29 @@ int vb_spds_set(vb_ctx *ctx, const float *values, const uint32_t *offsets, uint3
     if (n && (!values || !offsets)) return ctx->fail(VB_ERR_INVALID, "vb_spds_set: null argument");
     cudaSetDevice(ctx->device);
     vb_pt_state *p = pt_state(ctx);
-    for (uint32_t i = 0; i < n; ++i)
+    std::vector<float4> meta(n);
+    std::vector<uint32_t> sizes(n);
+    for (uint32_t i = 0; i < n; ++i) {                           // validate everything before touching the current pool
         if (offsets[i + 1] < offsets[i] + 2) return ctx->fail(VB_ERR_INVALID, "vb_spds_set: an SPD needs at least 2 samples and ascending offsets");
+        uint32_t size = offsets[i + 1] - offsets[i];             // SPD::init / SPD::eval constants (spd.cpp:50,70-72)
+        sizes[i] = size;
+        float interval = 471.0f / (float)size;
+        uint32_t sample_count = (uint32_t)((830.f - 360.f) / interval) + 1u;      // <= size for every size >= 2
+        if (sample_count > size || sample_count < 2) return ctx->fail(VB_ERR_INVALID, "vb_spds_set: SPD too short for its sampling interval");
+        float off_bits; std::memcpy(&off_bits, &offsets[i], 4);
+        meta[i] = make_float4(off_bits, interval, (float)(sample_count - 2u), 0.f);
+    }
     cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta);
-    p->d_spd_values = nullptr; p->d_spd_meta = nullptr; p->n_spds = n;
+    p->d_spd_values = nullptr; p->d_spd_meta = nullptr; p->n_spds = 0;           // stays empty if an upload below fails
     p->spec_dirty = true;
-    p->h_spd_sizes.resize(n);
+    p->h_spd_sizes.clear();
     if (n) {
-        std::vector<float4> meta(n);
-        for (uint32_t i = 0; i < n; ++i) {                       // SPD::init / SPD::eval constants (spd.cpp:50,70-72)
-            uint32_t size = offsets[i + 1] - offsets[i];
-            p->h_spd_sizes[i] = size;
-            float interval = 471.0f / (float)size;
-            uint32_t sample_count = (uint32_t)((830.f - 360.f) / interval) + 1u;
-            float off_bits; std::memcpy(&off_bits, &offsets[i], 4);
-            meta[i] = make_float4(off_bits, interval, (float)(sample_count - 2u), 0.f);
-            if (sample_count > size) return ctx->fail(VB_ERR_INVALID, "vb_spds_set: SPD too short for its sampling interval");
-        }
         VB_CUDA(cudaMalloc(&p->d_spd_values, sizeof(float) * offsets[n]));
         VB_CUDA(cudaMemcpy(p->d_spd_values, values, sizeof(float) * offsets[n], cudaMemcpyHostToDevice));
         VB_CUDA(cudaMalloc(&p->d_spd_meta, sizeof(float4) * n));
         VB_CUDA(cudaMemcpy(p->d_spd_meta, meta.data(), sizeof(float4) * n, cudaMemcpyHostToDevice));
     }
+    p->h_spd_sizes = sizes; p->n_spds = n;
     return VB_OK;
 }
 
@@ -354,12 +363,15 @@ int vb_spectrum_set(vb_ctx *ctx, const vb_spectrum_rec *spec) {
     cudaSetDevice(ctx->device);
     vb_pt_state *p = pt_state(ctx);
     if (spec->type > VB_SPECTRUM_HERO) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_spectrum_set: unknown spectrum type");
+    if (spec->type == VB_SPECTRUM_HERO) {
+        if (spec->dimension != 3) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_spectrum_set: hero spectrum is implemented for dimension 3 only");
+        if (!spec->rgb2spec || spec->rgb2spec_res < 2) return ctx->fail(VB_ERR_INVALID, "vb_spectrum_set: hero spectrum needs the rgb2spec coefficient table");
+        if (!(spec->cie_y_integral > 0.f)) return ctx->fail(VB_ERR_INVALID, "vb_spectrum_set: cie_y_integral must be positive");
+    }
     cudaFree(p->d_rgb2spec); p->d_rgb2spec = nullptr;
     p->spectrum = *spec; p->spectrum.rgb2spec = nullptr; p->have_spectrum = true;
     p->spec_dirty = true;
     if (spec->type == VB_SPECTRUM_HERO) {
-        if (spec->dimension != 3) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_spectrum_set: hero spectrum is implemented for dimension 3 only");
-        if (!spec->rgb2spec || spec->rgb2spec_res < 2) return ctx->fail(VB_ERR_INVALID, "vb_spectrum_set: hero spectrum needs the rgb2spec coefficient table");
         size_t bytes = sizeof(float) * 3 * 4 * (size_t)spec->rgb2spec_res * spec->rgb2spec_res * spec->rgb2spec_res;
         VB_CUDA(cudaMalloc(&p->d_rgb2spec, bytes));
         VB_CUDA(cudaMemcpy(p->d_rgb2spec, spec->rgb2spec, bytes, cudaMemcpyHostToDevice));

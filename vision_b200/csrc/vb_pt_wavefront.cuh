@@ -48,7 +48,7 @@ __device__ __forceinline__ VbRay wf_load_ray(const float4 *rays, uint32_t i) {
 }
 
 // camera rays of frames [fi0, fi0 + nf) of the batch; queue position == slot for the first bounce
-__global__ void __launch_bounds__(256) k_wf_generate(PtScene S, uint32_t first_frame, uint32_t stride, uint32_t fi0, uint32_t n_paths,
+__global__ void __launch_bounds__(256) k_wf_generate(const __grid_constant__ PtScene S, uint32_t first_frame, uint32_t stride, uint32_t fi0, uint32_t n_paths,
                                                      WfQueue Q, WfSortBox B, WfState st) {
     uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= n_paths) return;
@@ -90,7 +90,7 @@ template <int VARIANT>
 #ifndef VB_SHADE_MIN_BLOCKS
 #define VB_SHADE_MIN_BLOCKS 4
 #endif
-__global__ void __launch_bounds__(128, VB_SHADE_MIN_BLOCKS) k_wf_shade(PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
+__global__ void __launch_bounds__(128, VB_SHADE_MIN_BLOCKS) k_wf_shade(const __grid_constant__ PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
                                                   WfState st, WfQueue Qout, WfQueue Qsh, float4 *sh_pend, WfSortBox B, WfCounters *cnt, int filter) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
@@ -123,7 +123,6 @@ __global__ void __launch_bounds__(128, VB_SHADE_MIN_BLOCKS) k_wf_shade(PtScene S
         ps.ret = f3{b.x, b.y, b.z}; ps.scatter_pdf = b.w;
         ps.sampler.state = c.x; ps.ray_medium = c.y; ps.bounces = c.z; ps.swl = c.w;
         flags = pt_bounce<VARIANT>(S, ps, ray, hit, shadow, pending);
-        if ((flags & PT_CONTINUE) && ps.bounces >= S.params.max_depth) flags &= ~PT_CONTINUE;
         st.b[slot] = make_float4(ps.ret.x, ps.ret.y, ps.ret.z, ps.scatter_pdf);
         if (flags & PT_CONTINUE) {
             st.a[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.eta_scale);

@@ -11,6 +11,8 @@
 namespace {
 
 constexpr uint32_t SwlInvalidBit = 0x80000000u;
+// bit 30 of the same path word (PathState::swl): the path is in the "only direct" supplement step of Li (vb_pt_bounce.cuh)
+constexpr uint32_t PathSupplementBit = 0x40000000u;
 
 struct DevSpectrum {
     const float *rgb2spec;         // float[3][res][res][res][4]
@@ -162,7 +164,7 @@ __device__ __forceinline__ f3 spec_illum_c(const DevSpectrum &P, const Swl *w, f
 }
 
 // Spectrum::linear_srgb (hero.cpp:259-261,275-284; cie.h:413-420)
-__device__ f3 spec_to_srgb(const DevSpectrum &P, const Swl *w, f3 sp) {
+__device__ __forceinline__ f3 spec_to_srgb(const DevSpectrum &P, const Swl *w, f3 sp) {
     if (!w) return sp;
     const float v[3] = {sp.x, sp.y, sp.z};
     f3 sum{0, 0, 0};
