@@ -420,7 +420,11 @@ void LightSampler::tidy_up() {
 // reference src/render_core/lightsampler/uniform.cpp:12-34 (device part: index = min(u*N, N-1), PMF 1/N)
 class UniformLightSampler : public LightSampler {
 public:
-    explicit UniformLightSampler(const LightSamplerDesc &d) : LightSampler(d) {}
+    explicit UniformLightSampler(const LightSamplerDesc &d) : LightSampler(d) {
+        // LightSampler ctor (lightsampler.cpp:11-14): env_separate (default false) samples the environment light with its own
+        // probability env_prob; that selection rule (lightsampler.cpp:159-197) is not built - refuse instead of rendering differently
+        if (d["env_separate"].as_bool(false)) throw std::runtime_error("light_sampler.env_separate = true is not implemented");
+    }
     std::string impl_type() const override { return "uniform"; }
 };
 VH_MAKE_CLASS_CREATOR(UniformLightSampler, lightsampler, uniform, constructor)

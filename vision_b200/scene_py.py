@@ -838,6 +838,10 @@ def build_scene(path, overrides=None) -> SceneRecords:
         sc.luts = capi.load_luts(principled=any(r.type == capi.VB_MAT_PRINCIPLED for r in sc.materials))
     # LightSampler ctor (lightsampler.cpp:11-27): listed lights come first, the shapes' emissions follow; tidy_up
     # (lightsampler.cpp:67-77) groups them by type in first-seen order; records are made in that order
+    if d.get("light_sampler", {}).get("param", {}).get("env_separate", False):      # lightsampler.cpp:11-14,159-197: not built
+        raise NotImplementedError("light_sampler.env_separate = true is not implemented")
+    if d.get("light_sampler", {}).get("type", "uniform") != "uniform":
+        raise NotImplementedError("light sampler " + d["light_sampler"]["type"])
     free = [] if ov.get("drop_lights", False) else d.get("light_sampler", {}).get("param", {}).get("lights", [])
     type_of = {"point": capi.VB_LIGHT_POINT, "spot": capi.VB_LIGHT_SPOT, "spherical": capi.VB_LIGHT_ENV, "projector": capi.VB_LIGHT_PROJECTOR}
     pending = [(type_of.get(ld["type"], -1), ld, None) for ld in free] + [(capi.VB_LIGHT_AREA, em, ii) for em, ii in area_lights]
