@@ -170,6 +170,14 @@ VB_API int vb_film_download(vb_ctx *ctx, float *rgba, int which);
 /* device address of a film plane (w*h float4), for the NCCL all-reduce of the SUM film across GPUs */
 VB_API int vb_film_device_ptr(vb_ctx *ctx, int which, void **ptr);
 
+/* ---- G-buffer of the camera stage (reference rt_geom, src/base/sensor/frame_buffer.cpp:156-219) ---------------------------- */
+/* denoiser / AOV planes of the primary hit for ONE frame index, w*h float4 each, all colours through Spectrum::linear_srgb:
+ * NORMAL (shading normal, 1) - zero where the camera ray misses; ALBEDO (MaterialEvaluator::albedo(wo), 1); EMISSION
+ * (LightSampler::evaluate_hit_wi L, 1); GEOM (Sensor::linear_depth, p_film.x, p_film.y, hit ? 1 : 0). Motion vectors are not produced. */
+enum { VB_AOV_NORMAL = 0, VB_AOV_ALBEDO = 1, VB_AOV_EMISSION = 2, VB_AOV_GEOM = 3, VB_AOV_COUNT = 4 };
+VB_API int vb_gbuffer_render(vb_ctx *ctx, uint32_t frame_index);
+VB_API int vb_gbuffer_download(vb_ctx *ctx, int which, float *rgba);
+
 /* ---- debug / parity surface ------------------------------------------------------------------- */
 /* primary hit of every pixel for one frame index (== reference rt_compute_pixel, frame_buffer.cpp:277-291) */
 VB_API int vb_dump_primary_hits(vb_ctx *ctx, uint32_t frame_index, const vb_hits_soa *out);

@@ -429,6 +429,45 @@ inline Lobe create_lobe(const Scene &sc, const Swl &swl, const Interaction &it) 
     return lb;
 }
 
+// Lobe::albedo(cos_theta) of the single-lobe materials (lobe.h:167 diffuse = Kr; lobe.cpp:208-210 microfacet = kr * F(cos);
+// lobe.cpp:308-313 dielectric = kt (1 - F(|cos|)) + F; substrate.cpp:22 = Rd); consumed by rt_geom's albedo plane
+inline float3 lobe_albedo(const Lobe &lb, float cos_theta) {
+    switch (lb.type) {
+        case VB_MAT_DIFFUSE: case VB_MAT_SUBSTRATE: return lb.kr;
+        case VB_MAT_MIRROR: case VB_MAT_METAL: return lb.kr * lobe_fresnel(lb, cos_theta);
+        case VB_MAT_GLASS: { float3 F = dielectric_F(lb, std::fabs(cos_theta)); return lb.kr * (splat(1.0f) - F) + F; }
+        default: return float3{0, 0, 0};
+    }
+}
+// LobeSet::albedo (lobe.cpp:564-570) over the principled BSDF's sub-lobes: sheen = tint (principled_bsdf.cpp:54-56), coat / specular =
+// their albedo tables at cos_theta (:154-161,198-206), metallic = kr F82(cos) (MicrofacetLobe::albedo), transmission = dielectric form
+inline float3 principled_albedo(const Scene &sc, const PrincipledSet &ps, float cos_theta) {
+    float3 ret{0, 0, 0};
+    for (int i = 0; i < ps.n; ++i) {
+        const SubLobe &l = ps.s[i];
+        float3 a{0, 0, 0};
+        auto to_ratio_x = [](const GGX &g) { return std::sqrt(std::sqrt(g.ax * g.ay)); };
+        switch (l.kind) {
+            case SL_SHEEN: case SL_DIFFUSE: a = l.kr; break;
+            case SL_COAT: {
+                const Lut &L = sc.luts[VB_LUT_COAT];
+                float s = L.data.empty() ? 1.f : lut_sample3d_ch0(L, to_ratio_x(l.mf), cos_theta, (l.eta - 1.003f) / (4.f - 1.003f));
+                a = l.kr * s;
+            } break;
+            case SL_METALLIC: a = l.kr * sub_fresnel(l, cos_theta); break;
+            case SL_TRANS: { float3 F = sub_fresnel(l, std::fabs(cos_theta)); a = l.kr * (splat(1.0f) - F) + F; } break;
+            case SL_SPEC: {
+                const Lut &L = sc.luts[VB_LUT_SPECULAR];
+                float z = std::sqrt(std::fabs((l.eta - 1.0f) / (l.eta + 1.0f)));
+                float s = L.data.empty() ? 1.f : lut_sample3d_ch0(L, to_ratio_x(l.mf), cos_theta, z);
+                a = lerp3v(s, l.F0, splat(1.f)) * l.kr;
+            } break;
+        }
+        ret += a * l.weight;
+    }
+    return ret;
+}
+
 // MaterialEvaluator (individual_ns branch), reference material.cpp:132-142,163-175
 struct PrincipledEvaluator {
     PrincipledSet set;

@@ -140,6 +140,28 @@ void vo_primary_hits(void *h, uint32_t w, uint32_t hgt, uint32_t frame, uint32_t
     ms->params.max_depth = saved;
 }
 
+// rt_geom's G-buffer planes for one frame index: out = 4 planes of w*h float4 (normal, albedo, emission, geom)
+void vo_gbuffer(void *h, uint32_t w, uint32_t hgt, uint32_t frame, float *out, int threads) {
+    const Scene &s = *(Scene *)h;
+    std::atomic<uint32_t> next_row{0};
+    auto work = [&]() {
+        for (;;) {
+            uint32_t y = next_row.fetch_add(1);
+            if (y >= hgt) break;
+            for (uint32_t x = 0; x < w; ++x) {
+                float a[16];
+                s.render_sample(x, y, w, hgt, frame, nullptr, nullptr, a);
+                size_t i = (size_t)y * w + x, n = (size_t)w * hgt;
+                for (int p = 0; p < 4; ++p) for (int c = 0; c < 4; ++c) out[(p * n + i) * 4 + c] = a[4 * p + c];
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (int k = 1; k < std::max(1, threads); ++k) th.emplace_back(work);
+    work();
+    for (auto &x : th) x.join();
+}
+
 // known-answer helpers
 uint32_t vo_tea4(uint32_t a, uint32_t b) { return tea4(a, b); }
 float vo_lcg(uint32_t *state) { return lcg(*state); }

@@ -61,7 +61,9 @@ struct Scene {
     bool trace_any(const Ray &r, PathStats *st) const;
 
     // one pixel-sample: returns L (linear sRGB), optionally the primary hit
-    float3 render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st) const;
+    // aov (nullable, 16 floats): rt_geom's G-buffer planes for this pixel-sample (frame_buffer.cpp:156-219) - normal.xyz 1 | albedo.rgb 1 |
+    // emission.rgb 1 | linear depth, p_film.x, p_film.y, hit flag; when given, the function returns after the camera stage
+    float3 render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st, float *aov = nullptr) const;
 };
 
 // ---- shared small functions (unit-tested against known answers) ----

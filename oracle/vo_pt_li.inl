@@ -307,7 +307,7 @@ inline BSDFSample phase_sample(float g, float3 wo, Sampler &sampler) {
 
 }  // namespace
 
-float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st) const {
+float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st, float *aov) const {
     Sampler sampler;
     // ---- rt_geom: camera ray, reference frame_buffer.cpp:172-182, sampler.h:65-73 ----
     sampler.start(px, py, frame, 0u);
@@ -358,6 +358,38 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
     Ray ray{transform_point(c2w, org), 0.f, transform_vector(c2w, dir), RayTMax};
     Hit ph = trace_closest(ray, st);          // rt_geom's own primary trace (frame_buffer.cpp:179)
     if (primary) *primary = ph;
+    if (aov) {                                                      // rt_geom's G-buffer outputs, frame_buffer.cpp:184-218
+        uint32_t wp = 0;                                            // RenderEnv::initial precedes sampler.start(pixel, frame, 0) (:168-172)
+        if (params.spectrum == 1) { Sampler ws; ws.start(px, py, frame, 0xffffffffu); (void)ws.next_1d(); wp = ws.state & 0x00ffffffu; }
+        Swl gw = swl_make(*this, wp);
+        for (int i = 0; i < 16; ++i) aov[i] = 0.f;
+        aov[7] = 1.f; aov[11] = 1.f;                                // albedo / emission are written for every pixel as (0, 0, 0, 1)
+        aov[13] = p_film.x; aov[14] = p_film.y;
+        if (!ph.is_miss()) {
+            Interaction it = compute_surface_interaction(*this, ph.inst, ph.prim, ph.u, ph.v, true);
+            it.wo = normalize(-ray.d);
+            float3 ns = it.shading.z;
+            aov[0] = ns.x; aov[1] = ns.y; aov[2] = ns.z; aov[3] = 1.f;
+            // Sensor::linear_depth (sensor.cpp:192-195): z of the camera-space position; c2w is a rigid transform (sensor.cpp:153-162),
+            // so that is the projection of (pos - camera position) on c2w's third column
+            float3 fwd{c2w.m[2][0], c2w.m[2][1], c2w.m[2][2]}, cpos{c2w.m[3][0], c2w.m[3][1], c2w.m[3][2]};
+            aov[12] = dot(fwd, it.pos - cpos);
+            aov[15] = 1.f;
+            if (it.mat_id != VB_INVALID_ID) {
+                float cos_theta = dot(it.shading.z, it.wo);          // MaterialEvaluator::albedo, material.cpp:91-98
+                float3 a = materials[it.mat_id].type == VB_MAT_PRINCIPLED ? principled_albedo(*this, principled_create(*this, gw, it), cos_theta)
+                                                                          : lobe_albedo(create_lobe(*this, gw, it), cos_theta);
+                a = spec_to_srgb(*this, gw, a);
+                aov[4] = a.x; aov[5] = a.y; aov[6] = a.z;
+            }
+            if (it.light_id != VB_INVALID_ID) {
+                LightEval ev = evaluate_hit_wi(*this, gw, ray.o, it);
+                float3 e = spec_to_srgb(*this, gw, ev.L);
+                aov[8] = e.x; aov[9] = e.y; aov[10] = e.z;
+            }
+        }
+        return float3{0, 0, 0};
+    }
 
     // ---- path_tracing kernel: reference integrator.cpp:85-99 ----
     uint32_t swl_packed = 0;                                        // RenderEnv::initial, integrator.cpp:48-57: dim -1, state restored after

@@ -220,3 +220,14 @@ class OracleScene:
                "v": np.empty(n, np.float32), "t": np.empty(n, np.float32)}
         self.o.lib.vo_primary_hits(self.h, w, h, frame, *[_p(out[f]) for f in ("inst", "prim", "u", "v", "t")], threads)
         return out
+
+
+def oracle_gbuffer(osc, frame, threads=8):
+    """rt_geom's G-buffer planes from the oracle: {"normal", "albedo", "emission", "geom"} -> (h, w, 4) float32"""
+    w, h = osc.sc.resolution
+    out = np.empty((4, h, w, 4), np.float32)
+    lib = osc.o.lib
+    lib.vo_gbuffer.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int]
+    lib.vo_gbuffer.restype = None
+    lib.vo_gbuffer(osc.h, w, h, frame, _p(out), threads)
+    return dict(zip(("normal", "albedo", "emission", "geom"), out))

@@ -399,6 +399,8 @@ def _bind_pt(lib):
         "vb_film_device_ptr": [vp, C.c_int, C.POINTER(vp)],
         "vb_dump_primary_hits": [vp, C.c_uint32, C.POINTER(vb_hits_soa)],
         "vb_render_stats": [vp, C.POINTER(C.c_uint64)],
+        "vb_gbuffer_render": [vp, C.c_uint32],
+        "vb_gbuffer_download": [vp, C.c_int, vp],
         "vb_render_work": [vp, C.POINTER(C.c_uint64)],
     }
     for name, args in sigs.items():
@@ -505,6 +507,17 @@ def _pt_methods():
         self._check(self.lib.vb_film_device_ptr(self.h, which, C.byref(p)), "vb_film_device_ptr")
         return p.value
 
+    def gbuffer(self, frame) -> dict:
+        """rt_geom's G-buffer planes of one frame index: {"normal", "albedo", "emission", "geom"} -> (h, w, 4) float32"""
+        self._check(self.lib.vb_gbuffer_render(self.h, frame), "vb_gbuffer_render")
+        w, h = self._res
+        out = {}
+        for which, name in enumerate(("normal", "albedo", "emission", "geom")):
+            a = np.empty((h, w, 4), np.float32)
+            self._check(self.lib.vb_gbuffer_download(self.h, which, a.ctypes.data), "vb_gbuffer_download")
+            out[name] = a
+        return out
+
     def dump_primary_hits(self, frame):
         w, h = self._res
         n = w * h
@@ -528,7 +541,7 @@ def _pt_methods():
         return {"closest_nodes": w[0], "closest_tris": w[1], "any_nodes": w[2], "any_tris": w[3]}
 
     for f in (render_work, upload_scene, render_frames, film_clear, film_resolve, film_download, film_device_ptr,
-              dump_primary_hits, render_stats):
+              dump_primary_hits, render_stats, gbuffer):
         setattr(Context, f.__name__, f)
 
 

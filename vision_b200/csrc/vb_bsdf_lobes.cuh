@@ -273,6 +273,16 @@ __device__ __forceinline__ Lobe create_lobe(const PtScene &S, const Swl *swl, co
     return lb;
 }
 
+// Lobe::albedo(cos_theta) of the single-lobe materials (lobe.h:167, lobe.cpp:208-210,308-313, substrate.cpp:22): rt_geom's albedo plane
+__device__ __forceinline__ f3 lobe_albedo(const Lobe &lb, float cos_theta) {
+    switch (lb.type) {
+        case VB_MAT_DIFFUSE: case VB_MAT_SUBSTRATE: return lb.kr;
+        case VB_MAT_MIRROR: case VB_MAT_METAL: return lb.kr * lobe_fresnel(lb, cos_theta);
+        case VB_MAT_GLASS: { f3 F = dielectric_F(lb, fabsf(cos_theta)); return lb.kr * (splat(1.0f) - F) + F; }
+        default: return f3{0, 0, 0};
+    }
+}
+
 // MaterialEvaluator (individual_ns branch), material.cpp:132-142,163-175
 __device__ __forceinline__ void hemisphere_discard(ScatterEval &se, f3 wo, f3 wi, f3 ng) {
     bool same = dot(wo, ng) * dot(wi, ng) > 0.f;

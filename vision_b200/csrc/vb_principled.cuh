@@ -295,4 +295,33 @@ __device__ __noinline__ BSDFSample principled_sample(const PtScene &S, const Pri
     return bs;
 }
 
+// LobeSet::albedo (lobe.cpp:564-570) over the sub-lobes: sheen = tint (principled_bsdf.cpp:54-56), coat / specular = their albedo
+// tables at cos_theta (:154-161,198-206), metallic = kr F82(cos), transmission = the dielectric form
+__device__ __noinline__ f3 principled_albedo(const PtScene &S, const PrincipledSet &ps, float cos_theta) {
+    f3 ret{0, 0, 0};
+    for (int i = 0; i < ps.n; ++i) {
+        const SubLobe &l = ps.s[i];
+        f3 a{0, 0, 0};
+        float rx = __fsqrt_rn(__fsqrt_rn(l.mf.ax * l.mf.ay));
+        switch (l.kind) {
+            case SL_SHEEN: case SL_DIFFUSE: a = l.kr; break;
+            case SL_COAT: {
+                const DevLut &L = S.luts[VB_LUT_COAT];
+                float s = (L.data == nullptr) ? 1.f : lut_sample3d_ch0(L, rx, cos_theta, (l.eta - 1.003f) / (4.f - 1.003f));
+                a = l.kr * s;
+            } break;
+            case SL_METALLIC: a = l.kr * sub_fresnel(l, cos_theta); break;
+            case SL_TRANS: { f3 F = sub_fresnel(l, fabsf(cos_theta)); a = l.kr * (splat(1.0f) - F) + F; } break;
+            case SL_SPEC: {
+                const DevLut &L = S.luts[VB_LUT_SPECULAR];
+                float z = __fsqrt_rn(fabsf((l.eta - 1.0f) / (l.eta + 1.0f)));
+                float s = (L.data == nullptr) ? 1.f : lut_sample3d_ch0(L, rx, cos_theta, z);
+                a = lerp3v(s, l.F0, splat(1.f)) * l.kr;
+            } break;
+        }
+        ret = ret + a * l.weight;
+    }
+    return ret;
+}
+
 }  // namespace

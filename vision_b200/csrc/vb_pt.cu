@@ -381,7 +381,7 @@ __device__ __forceinline__ float sample_tent(float u, float r) {
 }
 
 // camera ray: reference sampler.h:65-73, sensor.cpp:44-56, thin_lens.cpp:34-42
-__device__ VbRay generate_camera_ray(const PtScene &S, Sampler &sampler, uint32_t px, uint32_t py) {
+__device__ VbRay generate_camera_ray(const PtScene &S, Sampler &sampler, uint32_t px, uint32_t py, f2 *p_film_out = nullptr) {
     const vb_camera &cam = S.cam;
     f2 uf = sampler.next_2d();
     f2 fp;
@@ -401,6 +401,7 @@ __device__ VbRay generate_camera_ray(const PtScene &S, Sampler &sampler, uint32_
         fp = {-rx + uf.x * (rx - (-rx)), -ry + uf.y * (ry - (-ry))};
     }
     f2 p_film{(float)px + 0.5f + fp.x, (float)py + 0.5f + fp.y};
+    if (p_film_out) *p_film_out = p_film;
     f2 u_lens = sampler.next_2d();
     (void)sampler.next_1d();
     float sx = cam.screen_lo[0] + p_film.x / (float)S.width * (cam.screen_hi[0] - cam.screen_lo[0]);

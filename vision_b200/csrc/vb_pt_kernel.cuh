@@ -103,6 +103,64 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(const __grid_constant__
     }
 }
 
+// rt_geom's G-buffer outputs for one frame index (reference frame_buffer.cpp:156-219): shading normal, material albedo, emission of
+// the primary hit (all through Spectrum::linear_srgb), linear depth + film position. Planes: out[plane * n_pix + pix] (float4);
+// normal: (ns, 1) on a hit, zero otherwise (the reference leaves a missed pixel's normal unwritten); albedo / emission: (rgb, 1) for every
+// pixel; geom: (Sensor::linear_depth, p_film.x, p_film.y, hit ? 1 : 0). Motion vectors need a previous camera and are not produced.
+template <int VARIANT>
+__global__ void __launch_bounds__(PT_BLOCK) k_gbuffer(const __grid_constant__ PtScene S, uint32_t frame, float4 *out) {
+    constexpr bool PRINCIPLED = (VARIANT & PT_PRINCIPLED) != 0, HERO = (VARIANT & PT_HERO) != 0;
+    __shared__ uint2 s_stack_all[VB_SM_STACK * PT_BLOCK];
+    uint2 *s_stack = s_stack_all + threadIdx.x;
+    const VbTrav mg = vb_trav_init();
+    uint32_t pix = blockIdx.x * PT_BLOCK + threadIdx.x;
+    uint32_t n_pix = S.width * S.height;
+    if (pix >= n_pix) return;
+    const uint32_t px = pix % S.width, py = pix / S.width;
+    Swl wl;
+    const Swl *swl = nullptr;
+    Sampler sampler;
+    if (HERO) { sampler.start(px, py, frame, 0xffffffffu); (void)sampler.next_1d(); wl = swl_make(sampler.state & 0x00ffffffu); swl = &wl; }
+    sampler.start(px, py, frame, 0u);
+    f2 p_film;
+    VbRay ray = generate_camera_ray(S, sampler, px, py, &p_film);
+    VbHit hit;
+    uint32_t d0 = 0, d1 = 0;
+    vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, d0, d1, mg);
+    float4 normal = make_float4(0.f, 0.f, 0.f, 0.f), albedo = make_float4(0.f, 0.f, 0.f, 1.f), emission = make_float4(0.f, 0.f, 0.f, 1.f);
+    float4 geom = make_float4(0.f, p_film.x, p_film.y, 0.f);
+    if (hit.inst != VB_INVALID_ID) {
+        Interaction it = compute_surface_interaction(S, hit.inst, hit.prim, hit.u, hit.v, true);
+        f3 rd{ray.dx, ray.dy, ray.dz}, ro{ray.ox, ray.oy, ray.oz};
+        it.wo = normalize(-rd);
+        f3 ns = it.shading.z;
+        normal = make_float4(ns.x, ns.y, ns.z, 1.f);
+        const float *m = S.cam.c2w;                                  // Sensor::linear_depth: rigid c2w -> projection on its third column
+        geom.x = dot(f3{m[8], m[9], m[10]}, it.pos - f3{m[12], m[13], m[14]});
+        geom.w = 1.f;
+        if (it.mat_id != VB_INVALID_ID) {
+            float cos_theta = dot(it.shading.z, it.wo);              // MaterialEvaluator::albedo, material.cpp:91-98
+            f3 a;
+            if (PRINCIPLED && S.materials[it.mat_id].type == VB_MAT_PRINCIPLED) a = principled_albedo(S, principled_create(S, swl, it), cos_theta);
+            else a = lobe_albedo(create_lobe(S, swl, it), cos_theta);
+            a = spec_to_srgb(S.spec, swl, a);
+            albedo = make_float4(a.x, a.y, a.z, 1.f);
+        }
+        if (it.light_id != VB_INVALID_ID) {                          // LightSampler::evaluate_hit_wi, lightsampler.cpp:252-267
+            const vb_light_rec &l = S.lights[it.light_id];
+            LightEval ev{f3{0, 0, 0}, 0.f};
+            if (l.type == VB_LIGHT_AREA) {
+                LightEvalCtx pl{it.pos, it.ng, it.uv, 1.0f / it.prim_area};
+                pl.pdf_pos *= alias_pmf(S, l, it.prim_id);
+                ev = area_evaluate_wi(S, swl, l, ro, pl);
+            }
+            f3 e = spec_to_srgb(S.spec, swl, ev.L);
+            emission = make_float4(e.x, e.y, e.z, 1.f);
+        }
+    }
+    out[pix] = normal; out[(size_t)n_pix + pix] = albedo; out[2 * (size_t)n_pix + pix] = emission; out[3 * (size_t)n_pix + pix] = geom;
+}
+
 // reference frame_buffer.cpp:72-74,135-144 + tonemapper/impl.cpp:21-46
 // hero spectrum: sigmoid-polynomial coefficients of every CONSTANT colour slot, decoded once per scene with the same device functions
 // the per-vertex path uses (DevSpectrum::cache). Entries of textured slots are written too but never read.
@@ -175,6 +233,7 @@ struct vb_pt_state {
     vb_medium_rec *d_mediums = nullptr; uint32_t n_mediums = 0;
     float *d_spd_values = nullptr; float4 *d_spd_meta = nullptr; uint32_t n_spds = 0; std::vector<uint32_t> h_spd_sizes;
     float *d_rgb2spec = nullptr; vb_spectrum_rec spectrum{}; bool have_spectrum = false;
+    float4 *d_gbuffer = nullptr; size_t gbuffer_n = 0;       // 4 planes of w*h float4 (vb_gbuffer_render)
     float4 *d_spec_cache = nullptr; size_t spec_cache_n = 0; bool spec_dirty = true;   // hero: decoded constant colour slots (k_spec_cache)
     std::vector<vb_material_rec> h_mat;            // kept for the SPD index checks at render time
     vb_camera cam{}; bool have_cam = false;
@@ -202,7 +261,7 @@ void vb_pt_destroy(vb_ctx *ctx) {
     for (auto t : p->tex_mem) cudaFree(t);
     for (auto &l : p->luts) cudaFree((void *)l.data);
     cudaFree(p->d_mediums);
-    cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta); cudaFree(p->d_rgb2spec); cudaFree(p->d_spec_cache);
+    cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta); cudaFree(p->d_rgb2spec); cudaFree(p->d_spec_cache); cudaFree(p->d_gbuffer);
     cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output); cudaFree(p->d_counters);
     if (p->wf) { wf_free(*p->wf); delete p->wf; }
     delete p;
@@ -453,7 +512,7 @@ int vb_film_clear(vb_ctx *ctx) {
 }
 
 static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_frames, uint32_t stride, int mode, bool dump,
-                     uint32_t *hi, uint32_t *hp, float *hu, float *hv, float *ht) {
+                     uint32_t *hi, uint32_t *hp, float *hu, float *hv, float *ht, float4 *gbuf = nullptr) {
     vb_pt_state *p = pt_state(ctx);
     if (!ctx->accel.built) return ctx->fail(VB_ERR_STATE, std::string(fn) + ": accel not built");
     if (!p->accum) return ctx->fail(VB_ERR_STATE, std::string(fn) + ": no film (vb_film_create)");
@@ -509,6 +568,18 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     S.cam = p->cam; S.params = p->params; S.width = p->w; S.height = p->h;
     if (S.params.ray_offset_factor == 0.f) S.params.ray_offset_factor = 1.f;
     uint32_t n_pix = p->w * p->h;
+    if (gbuf) {                                                      // rt_geom's G-buffer planes for frame index `first`
+        unsigned g = (n_pix + PT_BLOCK - 1) / PT_BLOCK;
+        ctx->prof_begin("gbuffer", 1);
+        const bool hero = S.params.spectrum == VB_SPECTRUM_HERO;
+        if (hero && p->has_principled) k_gbuffer<PT_HERO | PT_PRINCIPLED><<<g, PT_BLOCK, 0, ctx->stream>>>(S, first, gbuf);
+        else if (hero) k_gbuffer<PT_HERO><<<g, PT_BLOCK, 0, ctx->stream>>>(S, first, gbuf);
+        else if (p->has_principled) k_gbuffer<PT_PRINCIPLED><<<g, PT_BLOCK, 0, ctx->stream>>>(S, first, gbuf);
+        else k_gbuffer<PT_LEAN><<<g, PT_BLOCK, 0, ctx->stream>>>(S, first, gbuf);
+        ctx->prof_end();
+        VB_CHECK_LAUNCH();
+        return VB_OK;
+    }
     if (!dump && ctx->opt_pt_schedule == 0) {
         // wavefront schedule: batches of whole frames, at most opt_pt_max_paths paths in flight
         if (!p->wf) p->wf = new vb_wf_buffers();
@@ -586,6 +657,31 @@ int vb_film_device_ptr(vb_ctx *ctx, int which, void **ptr) {
     vb_pt_state *p = pt_state(ctx);
     if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_film_device_ptr: no film");
     *ptr = which == VB_FILM_RT ? (void *)p->rt : (which == VB_FILM_OUTPUT ? (void *)p->output : (void *)p->accum);
+    return VB_OK;
+}
+
+int vb_gbuffer_render(vb_ctx *ctx, uint32_t frame_index) {
+    if (!ctx) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_gbuffer_render: no film (vb_film_create)");
+    cudaSetDevice(ctx->device);
+    size_t n = (size_t)p->w * p->h;
+    if (p->gbuffer_n != n) {
+        cudaFree(p->d_gbuffer); p->d_gbuffer = nullptr; p->gbuffer_n = 0;
+        VB_CUDA(cudaMalloc(&p->d_gbuffer, sizeof(float4) * VB_AOV_COUNT * n));
+        p->gbuffer_n = n;
+    }
+    return pt_launch(ctx, "vb_gbuffer_render", frame_index, 1, 1, VB_ACCUM_SUM, false, nullptr, nullptr, nullptr, nullptr, nullptr, p->d_gbuffer);
+}
+
+int vb_gbuffer_download(vb_ctx *ctx, int which, float *rgba) {
+    if (!ctx || !rgba) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (which < 0 || which >= VB_AOV_COUNT) return ctx->fail(VB_ERR_INVALID, "vb_gbuffer_download: unknown plane");
+    if (!p->d_gbuffer || p->gbuffer_n != (size_t)p->w * p->h) return ctx->fail(VB_ERR_STATE, "vb_gbuffer_download: no G-buffer (vb_gbuffer_render)");
+    cudaSetDevice(ctx->device);
+    VB_CUDA(cudaMemcpyAsync(rgba, p->d_gbuffer + (size_t)which * p->gbuffer_n, sizeof(float4) * p->gbuffer_n, cudaMemcpyDeviceToHost, ctx->stream));
+    VB_CUDA(cudaStreamSynchronize(ctx->stream));
     return VB_OK;
 }
 

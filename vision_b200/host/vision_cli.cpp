@@ -7,7 +7,7 @@
 #include <cstring>
 
 int main(int argc, char **argv) {
-    std::string scene, out = "output.ppm", pfm, device = "cuda";
+    std::string scene, out = "output.ppm", pfm, aov, device = "cuda";
     uint32_t spp = 0; int dev_index = 0;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
@@ -15,10 +15,11 @@ int main(int argc, char **argv) {
         if (a == "-s" || a == "--scene") scene = next();
         else if (a == "-o" || a == "--output") out = next();
         else if (a == "--pfm") pfm = next();
+        else if (a == "--aov") aov = next();
         else if (a == "--spp") spp = (uint32_t)std::stoul(next());
         else if (a == "-d" || a == "--device") device = next();
         else if (a == "--device-index") dev_index = std::stoi(next());
-        else if (a == "-h" || a == "--help") { printf("vision-cli -s scene.json [-o out.png|.ppm|.hdr|.pfm] [--pfm out.pfm] [--spp N] [-d cuda]\n"); return 0; }
+        else if (a == "-h" || a == "--help") { printf("vision-cli -s scene.json [-o out.png|.ppm|.hdr|.pfm] [--pfm out.pfm] [--aov prefix] [--spp N] [-d cuda]\n"); return 0; }
         else fprintf(stderr, "ignored argument %s\n", a.c_str());
     }
     if (scene.empty()) { fprintf(stderr, "vision-cli: -s <scene file> is required\n"); return 2; }
@@ -43,6 +44,15 @@ int main(int argc, char **argv) {
             std::vector<float> acc((size_t)p->records.width * p->records.height * 4);
             p->check(vb_film_download(p->ctx, acc.data(), VB_FILM_ACCUM), "vb_film_download");
             vh::save_pfm(pfm, acc.data(), p->records.width, p->records.height);
+        }
+        if (!aov.empty()) {       // rt_geom's G-buffer planes of frame 0 (the denoiser inputs): <prefix>_normal.pfm, _albedo.pfm, _emission.pfm, _geom.pfm
+            std::vector<float> plane((size_t)p->records.width * p->records.height * 4);
+            const char *names[VB_AOV_COUNT] = {"normal", "albedo", "emission", "geom"};
+            p->check(vb_gbuffer_render(p->ctx, 0), "vb_gbuffer_render");
+            for (int k = 0; k < VB_AOV_COUNT; ++k) {
+                p->check(vb_gbuffer_download(p->ctx, k, plane.data()), "vb_gbuffer_download");
+                vh::save_pfm(aov + "_" + names[k] + ".pfm", plane.data(), p->records.width, p->records.height);
+            }
         }
     } catch (const std::exception &e) {
         fprintf(stderr, "vision-cli: %s\n", e.what());
