@@ -103,6 +103,13 @@ typedef struct vb_light_rec {
 } vb_light_rec;
 VB_API int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n,
                          const vb_alias_entry *alias_table, const float *alias_func, uint32_t n_alias);
+/* Light selection rule (reference src/render_core/lightsampler/uniform.cpp:12-34, power.cpp:11-56). UNIFORM: index = min(u N, N - 1),
+ * PMF 1 / N (the default; the table arguments are ignored). POWER: an alias table over luminance(light->power()), one entry per
+ * light in light order, stored in vb_lights_set's shared arrays at alias_offset (alias_size must equal the light count;
+ * alias_integral = sum(weights) / N, alias.h:119): select = Warper::sample_discrete(u), PMF = Warper::PMF(index).
+ * Call after vb_lights_set (which resets the rule to UNIFORM). */
+enum { VB_LIGHT_SAMPLER_UNIFORM = 0, VB_LIGHT_SAMPLER_POWER = 1 };
+VB_API int vb_light_sampler_set(vb_ctx *ctx, uint32_t kind, uint32_t alias_offset, uint32_t alias_size, float alias_integral);
 
 /* ---- spectrum (reference src/render_core/spectrum/srgb.cpp:16-57, hero.cpp:15-348; src/base/color/spd.cpp) ---- */
 /* SPD pool: tabulated spectral distributions over 360..830 nm, SPD::eval semantics (spd.cpp:50,57-76: linear

@@ -34,6 +34,11 @@ void vo_scene_set_lights(void *h, const vb_light_rec *l, uint32_t n, const vb_al
     s.alias_table.assign(t, t + na);
     s.alias_func.assign(f, f + na);
 }
+void vo_scene_set_light_sampler(void *h, uint32_t kind, uint32_t offset, uint32_t size, float integral) {
+    Scene &s = *(Scene *)h;
+    if (kind == VB_LIGHT_SAMPLER_POWER) { s.lsel_offset = offset; s.lsel_size = size; s.lsel_integral = integral; }
+    else { s.lsel_offset = s.lsel_size = 0; s.lsel_integral = 0.f; }
+}
 void vo_scene_set_textures(void *h, const vb_texture *t, uint32_t n) {
     Scene &s = *(Scene *)h;
     s.textures.resize(n);

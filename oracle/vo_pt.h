@@ -42,6 +42,7 @@ struct Scene {
     std::vector<vb_light_rec> lights;
     std::vector<vb_alias_entry> alias_table;
     std::vector<float> alias_func;
+    uint32_t lsel_offset = 0, lsel_size = 0; float lsel_integral = 0.f;      // "power" light sampler table (size 0 = uniform)
     std::vector<Texture> textures;
     Lut luts[VB_LUT_COUNT];
     std::vector<vb_medium_rec> mediums;

@@ -226,15 +226,31 @@ inline LightSample env_sample_wi(const Scene &sc, const Swl &swl, const vb_light
     return ls;
 }
 
-// reference lightsampler.cpp:210-216 + uniform.cpp:24-33
+// LightSampler::PMF / select_light: uniform.cpp:14-33, or power.cpp:16-31 = Warper::PMF / sample_discrete of an alias table over
+// luminance(light->power()) (alias.h:148-181)
+inline float light_pmf(const Scene &sc, uint32_t index) {
+    if (sc.lsel_size == 0) return 1.0f / (float)sc.lights.size();
+    return sc.lsel_integral > 0.f ? sc.alias_func[sc.lsel_offset + index] / (sc.lsel_integral * (float)sc.lsel_size) : 0.f;
+}
+inline uint32_t light_select(const Scene &sc, float u) {
+    uint32_t n = (uint32_t)sc.lights.size();
+    if (sc.lsel_size == 0) return (uint32_t)std::min(u * (float)n, (float)n - 1.0f);
+    u = u * (float)n;
+    uint32_t idx = std::min((uint32_t)u, n - 1);
+    u = std::min(u - (float)idx, OneMinusEpsilon);
+    vb_alias_entry e = sc.alias_table[sc.lsel_offset + idx];
+    return u < e.prob ? idx : e.alias;
+}
+
+// reference lightsampler.cpp:210-216 + uniform.cpp:24-33 / power.cpp:26-31
 inline LightSample sample_light(const Scene &sc, const Swl &swl, const Interaction &it, Sampler &sampler) {
     float u_light = sampler.next_1d();
     float2 u_surface = sampler.next_2d();
     LightSample ls;
     uint32_t n = (uint32_t)sc.lights.size();
     if (n == 0) return ls;
-    uint32_t index = (uint32_t)std::min(u_light * (float)n, (float)n - 1.0f);
-    float pmf = 1.0f / (float)n;
+    uint32_t index = light_select(sc, u_light);
+    float pmf = light_pmf(sc, index);
     const vb_light_rec &l = sc.lights[index];
     if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(sc, swl, l, it, u_surface);
     else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(sc, swl, l, it, u_surface);
@@ -251,7 +267,7 @@ inline LightEval evaluate_hit_wi(const Scene &sc, const Swl &swl, float3 ref_pos
     LightEvalCtx pl{it.pos, it.ng, it.uv, 1.0f / it.prim_area};
     pl.pdf_pos *= alias_pmf(sc, l, it.prim_id);
     ev = area_evaluate_wi(sc, swl, l, ref_pos, pl);
-    ev.pdf *= 1.0f / (float)sc.lights.size();
+    ev.pdf *= light_pmf(sc, it.light_id);
     return ev;
 }
 
@@ -414,7 +430,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
                 float3 tr{1, 1, 1};
                 if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(*this, swl, ray_medium, ray); }
                 LightEval ev = env_evaluate_wi(*this, swl, l, ray.o, ray.o + ray.d);
-                ev.pdf *= 1.0f / (float)lights.size();
+                ev.pdf *= light_pmf(*this, env_light);
                 float weight = mis_weight(scatter_pdf, ev.pdf);
                 if (params.mis_mode == 2) weight = 1.f;
                 else if (params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
@@ -528,7 +544,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
                     float3 tr{1, 1, 1};
                     if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(*this, swl, ray_medium, ray); }
                     LightEval ev = env_evaluate_wi(*this, swl, l, ray.o, ray.o + ray.d);
-                    ev.pdf *= 1.0f / (float)lights.size();
+                    ev.pdf *= light_pmf(*this, env_light);
                     float weight = mis_weight(scatter_pdf, ev.pdf);
                     ret += spec_to_srgb(*this, swl, ev.L * tr * weight * throughput);
                 }

@@ -171,6 +171,9 @@ class OracleScene:
         tab = (capi.vb_alias_entry * max(1, na))(*[capi.vb_alias_entry(p, a) for p, a in sc.alias_table])
         func = np.ascontiguousarray(sc.alias_func if na else [0.0], np.float32)
         lib.vo_scene_set_lights(self.h, C.cast(lights, vp), len(sc.lights), C.cast(tab, vp), _p(func), na)
+        lib.vo_scene_set_light_sampler.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float]
+        lib.vo_scene_set_light_sampler.restype = None
+        lib.vo_scene_set_light_sampler(self.h, *getattr(sc, "light_sampler", (0, 0, 0, 0.0)))
         texs = (capi.vb_texture * max(1, len(sc.textures)))()
         keep = []
         for i, t in enumerate(sc.textures):

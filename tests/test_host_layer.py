@@ -44,6 +44,7 @@ def test_host_records_equal_python_twin():
     assert [_bytes(x) for x in a.materials] == [_bytes(x) for x in b.materials]
     assert [_bytes(x) for x in a.lights] == [_bytes(x) for x in b.lights]
     assert a.alias_table == [(float(np.float32(p)), i) for p, i in b.alias_table] and a.alias_func == b.alias_func
+    assert tuple(a.light_sampler) == tuple(b.light_sampler)
     assert _bytes(a.params) == _bytes(b.params)
     ca, cb = a.camera, b.camera
     np.testing.assert_allclose(list(ca.c2w), list(cb.c2w), atol=1e-6)
@@ -97,7 +98,7 @@ def test_host_records_equal_python_twin_materials_and_mediums(name):
 
 
 @pytest.mark.parametrize("rel", ["scenes/cbox/cbox_lights.json", "scenes/classroom/vision_scene.json", "scenes/cbox/cbox_sphere.json",
-                                 "scenes/cbox_dragon/vision_scene_small.json", "scenes/cbox/cbox_projector.json",
+                                 "scenes/cbox_dragon/vision_scene_small.json", "scenes/cbox/cbox_projector.json", "scenes/cbox/cbox_lights_power.json",
                                  "scenes/cbox_stock/vision_scene.json"])
 def test_host_records_equal_python_twin_lights_and_models(rel):
     """model shape (OBJ), point / spot / spherical lights, AliasTable2D, world diameter, Euler transforms, light order"""
@@ -117,6 +118,7 @@ def test_host_records_equal_python_twin_lights_and_models(rel):
     assert [_bytes(x) for x in a.materials] == [_bytes(x) for x in b.materials]
     assert [_bytes(x) for x in a.lights] == [_bytes(x) for x in b.lights]
     assert a.alias_table == [(float(np.float32(p)), i) for p, i in b.alias_table] and a.alias_func == b.alias_func
+    assert tuple(a.light_sampler) == tuple(b.light_sampler)
     assert _bytes(a.params) == _bytes(b.params) and a.camera.medium_id == b.camera.medium_id
     assert a.camera.filter_type == b.camera.filter_type and a.camera.filter_table_offset == b.camera.filter_table_offset
     assert len(a.textures) == len(b.textures)
@@ -146,6 +148,10 @@ def test_host_records_equal_python_twin_lights_and_models(rel):
         assert a.params.max_depth == 16 and a.camera.filter_type == capi.VB_FILTER_TRIANGLE and a.params.spectrum == capi.VB_SPECTRUM_SRGB
         assert capi.VB_MAT_GLASS in [m.type for m in a.materials] and len(a.materials) == 8       # 8 of the 16 defined materials are used
         assert "vision-material-mix#constructor" in host_api.plugin_names()
+    elif "power" in rel:
+        assert [l.type for l in a.lights] == [capi.VB_LIGHT_POINT, capi.VB_LIGHT_SPOT, capi.VB_LIGHT_ENV, capi.VB_LIGHT_PROJECTOR, capi.VB_LIGHT_AREA]
+        assert a.light_sampler[0] == capi.VB_LIGHT_SAMPLER_POWER and a.light_sampler[2] == 5
+        assert "vision-lightsampler-power#constructor" in host_api.plugin_names()
     else:
         assert [l.type for l in a.lights] == [capi.VB_LIGHT_POINT, capi.VB_LIGHT_SPOT, capi.VB_LIGHT_ENV, capi.VB_LIGHT_AREA]
         assert a.instances[-1]["light_id"] == 3
@@ -214,3 +220,26 @@ def test_host_pipeline_renders_like_python_path(vbctx, SCENE):
     assert out.shape == (256, 256, 4) and out[..., :3].max() <= 1.0
     # the hero spectrum's CIE -> sRGB can leave the gamut per sample (no clamp in the reference either)
     assert 0.0 <= out[..., :3].min() or "dispersion" in str(SCENE)
+
+
+def test_power_light_sampler_weights_known_answers():
+    """PowerLightSampler::prepare (power.cpp:33-53): one alias entry per light over luminance(power()); point.cpp:32-34 and
+    spot.cpp:44-46 in closed form; PMFs sum to 1; the uniform sampler leaves the selection table empty"""
+    import math
+    b = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_lights_power.json")
+    kind, off, n, integral = b.light_sampler
+    assert kind == capi.VB_LIGHT_SAMPLER_POWER and n == len(b.lights) == 5 and off + n <= len(b.alias_func)
+    w = b.alias_func[off:off + n]
+    lum = lambda c: 0.212671 * c[0] + 0.715160 * c[1] + 0.072169 * c[2]
+    by_type = {l.type: i for i, l in enumerate(b.lights)}
+    assert w[by_type[capi.VB_LIGHT_POINT]] == pytest.approx(4 * math.pi * 0.2 * lum([1, 0.8, 0.6]), rel=1e-6)
+    a = math.radians(20)
+    f = math.radians(min(2.0, a))          # spot.cpp:31-32 clamps the falloff in DEGREES against the angle in RADIANS
+    assert w[by_type[capi.VB_LIGHT_SPOT]] == pytest.approx(2 * math.pi * lum([0.4, 0.6, 2]) * (1 - 0.5 * (2 * a + f)), rel=1e-6)
+    area = b.lights[by_type[capi.VB_LIGHT_AREA]]
+    tri_area = sum(b.alias_func[area.alias_offset:area.alias_offset + area.alias_size])
+    assert w[by_type[capi.VB_LIGHT_AREA]] == pytest.approx(math.pi * tri_area * area.scale * lum(list(area.color.value[:3])), rel=1e-6)
+    assert integral == pytest.approx(sum(w) / n, rel=1e-6)
+    assert sum(x / (integral * n) for x in w) == pytest.approx(1.0, rel=1e-6)
+    u = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_lights.json")
+    assert tuple(u.light_sampler) == (capi.VB_LIGHT_SAMPLER_UNIFORM, 0, 0, 0.0)

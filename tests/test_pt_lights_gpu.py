@@ -19,6 +19,9 @@ MAX_DIFF_PIXELS = 2e-3
 CASES = [
     ("cbox_lights", "scenes/cbox/cbox_lights.json", {"resolution": [160, 160], "spp": 8}, 0.05),
     ("cbox_projector", "scenes/cbox/cbox_projector.json", {"resolution": [160, 160], "spp": 8}, 0.02),
+    # "power" light sampler (lightsampler/power.cpp): alias table over luminance(power()) of point, spot, spherical, projector, area
+    ("cbox_lights_power", "scenes/cbox/cbox_lights_power.json", {"resolution": [160, 160], "spp": 8}, 0.05),
+    ("cbox_lights_power_hero", "scenes/cbox/cbox_lights_power.json", {"resolution": [128, 128], "spp": 4, "spectrum": "hero"}, 0.05),
     ("cbox_sphere_gaussian_filter", "scenes/cbox/cbox_sphere.json", {"resolution": [160, 160], "spp": 8}, 0.03),
     ("cbox_principled", "scenes/cbox/cbox_principled.json", {"resolution": [160, 160], "spp": 8}, 0.03),
     ("classroom_clear", "scenes/classroom/vision_scene.json", {"resolution": [240, 136], "spp": 4, "process_mediums": False}, 0.05),

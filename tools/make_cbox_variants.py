@@ -109,6 +109,11 @@ for s_ in pj["shapes"]:
     if "emission" in s_["param"]:
         s_["param"]["emission"]["param"]["scale"] = 0.2
 (root / "cbox_projector.json").write_text(json.dumps(pj, indent=1))
+# cbox_lights_power.json: cbox_lights + the projector under the "power" light sampler (lightsampler/power.cpp): every light type's power()
+pw = copy.deepcopy(c)
+pw["light_sampler"]["type"] = "power"
+pw["light_sampler"]["param"]["lights"] = pw["light_sampler"]["param"]["lights"] + copy.deepcopy(pj["light_sampler"]["param"]["lights"])
+(root / "cbox_lights_power.json").write_text(json.dumps(pw, indent=1))
 # cbox_dispersion.json (config C4 "cbox-glass / dispersion spectral glass + Disney"): hero-wavelength spectrum, the short box is
 # BK7 glass (material_name -> dispersive "spd" ior slot, glass.cpp:216-234), the tall box the coated principled metal, metal (Cu,
 # spectral eta / k) right wall, substrate floor

@@ -364,6 +364,7 @@ def load_cie_1nm() -> np.ndarray:
 
 VB_MAT_DIFFUSE, VB_MAT_MIRROR, VB_MAT_GLASS, VB_MAT_METAL, VB_MAT_SUBSTRATE, VB_MAT_PRINCIPLED, VB_MAT_BLACK_BODY = range(7)
 VB_LIGHT_AREA, VB_LIGHT_POINT, VB_LIGHT_SPOT, VB_LIGHT_ENV, VB_LIGHT_PROJECTOR = range(5)
+VB_LIGHT_SAMPLER_UNIFORM, VB_LIGHT_SAMPLER_POWER = 0, 1
 VB_FILTER_BOX, VB_FILTER_TRIANGLE, VB_FILTER_FITTED = 0, 1, 2
 VB_FILTER_TABLE_SIZE = 20
 VB_ACCUM_LERP, VB_ACCUM_SUM = 0, 1
@@ -389,6 +390,7 @@ def _bind_pt(lib):
         "vb_spds_set": [vp, vp, vp, C.c_uint32],
         "vb_spectrum_set": [vp, C.POINTER(vb_spectrum_rec)],
         "vb_lights_set": [vp, C.POINTER(vb_light_rec), C.c_uint32, C.POINTER(vb_alias_entry), vp, C.c_uint32],
+        "vb_light_sampler_set": [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float],
         "vb_camera_set": [vp, C.POINTER(vb_camera)],
         "vb_integrator_set": [vp, C.POINTER(vb_pt_params)],
         "vb_film_create": [vp, C.c_uint32, C.c_uint32],
@@ -419,6 +421,7 @@ class SceneRecords:
         self.lights = []        # vb_light_rec
         self.alias_table = []   # (prob, alias)
         self.alias_func = []    # float
+        self.light_sampler = (0, 0, 0, 0.0)   # (kind, alias_offset, alias_size, alias_integral): vb_light_sampler_set
         self.textures = []      # (h, w, 4) float32 arrays
         self.mediums = []       # vb_medium_rec
         self.spds = []          # SPD pool: float32 arrays (hero spectrum: CIE x, y, z, D65 first, then material curves)
@@ -481,6 +484,8 @@ def _pt_methods():
         tab = (vb_alias_entry * max(1, na))(*[vb_alias_entry(p, a) for p, a in sc.alias_table])
         func = np.ascontiguousarray(sc.alias_func if na else [0.0], np.float32)
         self._check(self.lib.vb_lights_set(self.h, lights, len(sc.lights), tab, func.ctypes.data, na), "vb_lights_set")
+        k, off, size, integral = sc.light_sampler
+        self._check(self.lib.vb_light_sampler_set(self.h, k, off, size, integral), "vb_light_sampler_set")
         self._check(self.lib.vb_camera_set(self.h, C.byref(sc.camera)), "vb_camera_set")
         self._check(self.lib.vb_integrator_set(self.h, C.byref(sc.params)), "vb_integrator_set")
         self._check(self.lib.vb_film_create(self.h, sc.resolution[0], sc.resolution[1]), "vb_film_create")

@@ -36,6 +36,8 @@ struct PtScene {
     uint32_t env_light;            // LightSampler::env_light_ (index of the last Infinite light) or VB_INVALID_ID
     const vb_alias_entry *alias_table;
     const float *alias_func;
+    uint32_t lsel_offset, lsel_size;   // light selection table of the "power" light sampler (vb_light_sampler_set); size 0 = uniform
+    float lsel_integral;
     const DevTex *textures;
     DevLut luts[VB_LUT_COUNT];
     const vb_medium_rec *mediums;
@@ -183,6 +185,22 @@ __device__ uint32_t alias_sample(const PtScene &S, const vb_light_rec &l, float 
     u_remapped = keep ? fmin_(u / e.prob, OneMinusEpsilon) : fmin_((1.0f - u) / (1.0f - e.prob), OneMinusEpsilon);
     pmf = alias_pmf(S, l, out);
     return out;
+}
+
+// LightSampler::PMF / select_light: uniform.cpp:14-33 (1 / N, index = min(u N, N - 1)) or power.cpp:16-31 (alias table over
+// luminance(light->power()): Warper::PMF / sample_discrete)
+__device__ __forceinline__ float light_pmf(const PtScene &S, uint32_t index) {
+    if (S.lsel_size == 0) return 1.0f / (float)S.n_lights;
+    return S.lsel_integral > 0.f ? __ldg(S.alias_func + S.lsel_offset + index) / (S.lsel_integral * (float)S.lsel_size) : 0.f;
+}
+__device__ __forceinline__ uint32_t light_select(const PtScene &S, float u) {
+    uint32_t n = S.n_lights;
+    if (S.lsel_size == 0) return (uint32_t)fmin_(u * (float)n, (float)n - 1.0f);
+    u = u * (float)n;
+    uint32_t idx = min((uint32_t)u, n - 1);
+    u = fmin_(u - (float)idx, OneMinusEpsilon);
+    vb_alias_entry e = S.alias_table[S.lsel_offset + idx];
+    return u < e.prob ? idx : e.alias;
 }
 
 __device__ LightEval area_evaluate_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, f3 ref_pos, const LightEvalCtx &pl) {

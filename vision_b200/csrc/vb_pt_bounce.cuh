@@ -60,7 +60,7 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
             if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(S, swl, ps.ray_medium, ray); }
             f3 ro{ray.ox, ray.oy, ray.oz}, rd{ray.dx, ray.dy, ray.dz};
             LightEval ev = env_evaluate_wi(S, swl, l, ro, ro + rd);
-            ev.pdf *= 1.0f / (float)S.n_lights;
+            ev.pdf *= light_pmf(S, S.env_light);
             float weight = mis_weight(ps.scatter_pdf, ev.pdf);
             if (S.params.mis_mode == 2) weight = 1.f;
             else if (S.params.mis_mode == 1) weight = bounces == 0 ? weight : 0.f;
@@ -111,7 +111,7 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
             LightEvalCtx pl{it.pos, it.ng, it.uv, 1.0f / it.prim_area};
             pl.pdf_pos *= alias_pmf(S, l, it.prim_id);
             ev = area_evaluate_wi(S, swl, l, ro, pl);
-            ev.pdf *= 1.0f / (float)S.n_lights;
+            ev.pdf *= light_pmf(S, it.light_id);
         }
         f3 tr = ray_Tr(S, swl, ps.ray_medium, ray);
         float weight = mis_weight(ps.scatter_pdf, ev.pdf);
@@ -131,13 +131,12 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
     f2 u_surface = sampler.next_2d();
     LightSample ls{{f3{0, 0, 0}, 0.f}, f3{0, 0, 0}};
     if (S.n_lights) {
-        uint32_t n = S.n_lights;
-        uint32_t index = (uint32_t)fmin_(u_light * (float)n, (float)n - 1.0f);
+        uint32_t index = light_select(S, u_light);
         const vb_light_rec &l = S.lights[index];
         if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(S, swl, l, it, u_surface);
         else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(S, swl, l, it, u_surface);
         else ls = point_sample_wi(S, swl, l, it);
-        ls.eval.pdf *= 1.0f / (float)n;
+        ls.eval.pdf *= light_pmf(S, index);
     }
     shadow = spawn_ray_to(it, ls.p_light);
     uint32_t shadow_medium = mediums ? (dot(it.ng, f3{shadow.dx, shadow.dy, shadow.dz}) > 0.f ? it.outside : it.inside) : VB_INVALID_ID;

@@ -221,6 +221,7 @@ struct vb_pt_state {
     uint32_t n_mat_types = 0;          // distinct material models in use (one: ordering the shading queue is pointless)
     uint64_t work[4] = {0, 0, 0, 0};
     uint32_t n_alias = 0;
+    uint32_t lsel_offset = 0, lsel_size = 0; float lsel_integral = 0.f;     // vb_light_sampler_set
     bool has_principled = false;
     std::vector<DevMesh> h_meshes;
     DevMesh *d_meshes = nullptr;
@@ -456,6 +457,7 @@ int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n, const vb_
     }
     cudaFree(p->d_lights); cudaFree(p->d_alias); cudaFree(p->d_func);
     p->d_lights = nullptr; p->d_alias = nullptr; p->d_func = nullptr; p->n_lights = n; p->n_alias = n_alias;
+    p->lsel_offset = p->lsel_size = 0; p->lsel_integral = 0.f;
     p->spec_dirty = true;
     p->env_light = VB_INVALID_ID;
     for (uint32_t i = 0; i < n; ++i) if (lights[i].type == VB_LIGHT_ENV) p->env_light = i;
@@ -472,6 +474,16 @@ int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n, const vb_
     return VB_OK;
 }
 
+int vb_light_sampler_set(vb_ctx *ctx, uint32_t kind, uint32_t alias_offset, uint32_t alias_size, float alias_integral) {
+    if (!ctx) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (kind == VB_LIGHT_SAMPLER_UNIFORM) { p->lsel_offset = p->lsel_size = 0; p->lsel_integral = 0.f; return VB_OK; }
+    if (kind != VB_LIGHT_SAMPLER_POWER) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_light_sampler_set: light sampler kind not implemented");
+    if (alias_size == 0 || alias_size != p->n_lights) return ctx->fail(VB_ERR_INVALID, "vb_light_sampler_set: the selection table needs one entry per light (call vb_lights_set first)");
+    if ((uint64_t)alias_offset + alias_size > p->n_alias) return ctx->fail(VB_ERR_INVALID, "vb_light_sampler_set: alias range out of bounds");
+    p->lsel_offset = alias_offset; p->lsel_size = alias_size; p->lsel_integral = alias_integral;
+    return VB_OK;
+}
 int vb_camera_set(vb_ctx *ctx, const vb_camera *cam) {
     if (!ctx || !cam) return VB_ERR_INVALID;
     vb_pt_state *p = pt_state(ctx);
@@ -526,6 +538,7 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     PtScene S{};
     S.accel = VbAccelView{ctx->accel.nodes, ctx->accel.tris};
     S.meshes = p->d_meshes; S.instances = p->d_inst; S.materials = p->d_mat; S.lights = p->d_lights; S.n_lights = p->n_lights; S.env_light = p->env_light;
+    S.lsel_offset = p->lsel_offset; S.lsel_size = p->lsel_size; S.lsel_integral = p->lsel_integral;
     S.alias_table = p->d_alias; S.alias_func = p->d_func; S.textures = p->d_tex;
     for (int k = 0; k < VB_LUT_COUNT; ++k) S.luts[k] = p->luts[k];
     S.mediums = p->d_mediums;

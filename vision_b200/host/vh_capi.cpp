@@ -50,7 +50,7 @@ VB_API void vh_info(vh_pipeline *h, uint32_t *info, float *exposure) {
     if (exposure) *exposure = r.exposure;
 }
 /* which: 0 instances, 1 materials, 2 lights, 3 alias_table, 4 alias_func, 5 camera, 6 params, 7 mediums, 8 + k LUT k,
- * 100 spectrum record, 101 number of SPDs (uint64), 200 + i SPD i; returns bytes copied */
+ * 100 spectrum record, 101 number of SPDs (uint64), 102 light sampler record, 200 + i SPD i; returns bytes copied */
 VB_API uint64_t vh_records_blob(vh_pipeline *h, int which, void *dst, uint64_t cap) {
     const SceneRecords &r = h->p->records;
     const void *src = nullptr; uint64_t n = 0;
@@ -63,6 +63,7 @@ VB_API uint64_t vh_records_blob(vh_pipeline *h, int which, void *dst, uint64_t c
         case 5: src = &r.camera; n = sizeof(vb_camera); break;
         case 6: src = &r.params; n = sizeof(vb_pt_params); break;
         case 7: src = r.mediums.data(); n = r.mediums.size() * sizeof(vb_medium_rec); break;
+        case 102: src = &r.light_sampler; n = sizeof(r.light_sampler); break;
         case 100: src = &r.spectrum; n = sizeof(vb_spectrum_rec); break;
         case 101: { uint64_t c = r.spds.size(); if (dst && cap >= 8) std::memcpy(dst, &c, 8); return 8; }
         default:

@@ -132,6 +132,7 @@ public:
     using Desc = LightDesc;
     uint32_t index = VB_INVALID_ID;
     uint32_t inst_idx = VB_INVALID_ID;               // IAreaLight::inst_idx_
+    mutable float shape_angle = 0.f, shape_falloff = 0.f;   // spot: radians, kept by fill_record for power()
     explicit Light(const LightDesc &desc) : inst_idx(desc["inst_id"].as_uint(VB_INVALID_ID)) {}
     virtual int type_order() const = 0;              // Polymorphic topology order = first-seen type
     virtual void fill_record(vb_light_rec &rec, const Scene &scene, const SlotContext &ctx,
@@ -145,6 +146,7 @@ public:
     explicit LightSampler(const LightSamplerDesc &) {}
     void add_light(std::shared_ptr<Light> l) { lights.push_back(std::move(l)); }
     void tidy_up();                                   // lightsampler.cpp:64-74
+    virtual uint32_t kind() const { return VB_LIGHT_SAMPLER_UNIFORM; }
 };
 
 class Sampler : public Node { public: using Desc = SamplerDesc; uint32_t spp; explicit Sampler(const SamplerDesc &d) : spp(d["spp"].as_uint(1u)) {} virtual uint32_t device_tag() const = 0; };

@@ -429,6 +429,62 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(UniformLightSampler, lightsampler, uniform, constructor)
 
+// luminance(light->power()), the weight PowerLightSampler::prepare gives each light (power.cpp:35-50): area.cpp:87-89, point.cpp:32-34,
+// spot.cpp:44-46, projector.cpp:58-91, spherical.cpp:56-59; Light::average (light.h:80-83) = slot average x scale. A texture's average
+// (ocarina Image::average_vector, absent from the tree) = per-channel mean summed in double in pixel order; luminance = Rec.709.
+float light_power_luminance(const vb_light_rec &l, const SceneRecords &rec, float spot_angle, float spot_falloff) {
+    const float Pi = 3.14159265358979323846f;
+    float avg[3];
+    if (l.color.tex_id == VB_INVALID_ID) for (int c = 0; c < 3; ++c) avg[c] = l.color.value[c];
+    else {
+        const Image &im = rec.textures[l.color.tex_id];
+        size_t n = (size_t)im.w * im.h;
+        for (int c = 0; c < 3; ++c) { double s = 0.0; for (size_t i = 0; i < n; ++i) s += (double)im.rgba[i * 4 + c]; avg[c] = (float)(s / (double)n); }
+    }
+    for (float &a : avg) a = a * l.scale;
+    float p[3];
+    if (l.type == VB_LIGHT_AREA) {
+        float area = 0.f;
+        for (uint32_t i = 0; i < l.alias_size; ++i) area += rec.alias_func[l.alias_offset + i];
+        float k = l.two_sided ? 2.f : 1.f;
+        for (int c = 0; c < 3; ++c) p[c] = k * avg[c] * area * Pi;
+    } else if (l.type == VB_LIGHT_POINT) {
+        float k = 4.f * Pi;
+        for (int c = 0; c < 3; ++c) p[c] = k * avg[c];
+    } else if (l.type == VB_LIGHT_SPOT) {
+        float k = 2.f * Pi, s = 1.f - .5f * (spot_angle * 2.f + spot_falloff);
+        for (int c = 0; c < 3; ++c) p[c] = k * avg[c] * s;
+    } else if (l.type == VB_LIGHT_ENV) {
+        float r = l.params[0] / 2.f, k = Pi * (r * r);
+        for (int c = 0; c < 3; ++c) p[c] = k * avg[c];
+    } else {                                                           // projector: Girard's theorem on the frustum corner directions
+        float ratio = l.params[1];
+        float y = std::sqrt(1.f / (ratio * ratio + 1.f)), x = ratio * y, z = std::sqrt(x * x + y * y);
+        float3 p0{x, y, z}, p1{x, -y, z}, p2{-x, -y, z};
+        auto crs = [](float3 a, float3 b) { return float3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; };
+        auto dt = [](float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; };
+        auto nrm = [&](float3 a) { float l2 = dt(a, a); if (!(l2 > 0.f)) return a; float inv = 1.f / std::sqrt(l2); return float3{a.x * inv, a.y * inv, a.z * inv}; };
+        auto neg = [](float3 a) { return float3{-a.x, -a.y, -a.z}; };
+        auto ac = [&](float3 a, float3 b) { return std::acos(std::min(std::max(dt(a, b), -1.f), 1.f)); };
+        float3 c01 = nrm(crs(p0, p1)), c12 = nrm(crs(p1, p2)), c20 = nrm(crs(p2, p0));
+        float solid = std::fabs(ac(c01, neg(c12)) + ac(c12, neg(c20)) + ac(c20, neg(c01)) - Pi);
+        float k = (2.f * solid) / (4.f * Pi);
+        for (int c = 0; c < 3; ++c) p[c] = k * avg[c];
+    }
+    return 0.212671f * p[0] + 0.715160f * p[1] + 0.072169f * p[2];
+}
+
+// reference src/render_core/lightsampler/power.cpp:11-56: lights are drawn from an alias table over luminance(light->power())
+class PowerLightSampler : public LightSampler {
+public:
+    explicit PowerLightSampler(const LightSamplerDesc &d) : LightSampler(d) {
+        if (d["env_separate"].as_bool(false)) throw std::runtime_error("light_sampler.env_separate = true is not implemented");
+    }
+    std::string impl_type() const override { return "power"; }
+    uint32_t kind() const override { return VB_LIGHT_SAMPLER_POWER; }
+};
+VH_MAKE_CLASS_CREATOR(PowerLightSampler, lightsampler, power, constructor)
+
 }  // namespace vh
 
 #include "vh_plugins2.inl"

@@ -209,6 +209,7 @@ public:
         float inv = 1.0f / std::sqrt((d.x * d.x + d.y * d.y) + d.z * d.z);
         r.direction[0] = d.x * inv; r.direction[1] = d.y * inv; r.direction[2] = d.z * inv;
         r.params[0] = std::cos(angle);
+        shape_angle = angle; shape_falloff = falloff;
         r.params[1] = std::cos(std::max(0.f, angle - falloff));
     }
 };

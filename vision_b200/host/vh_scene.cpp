@@ -209,6 +209,13 @@ void Scene::prepare(SceneRecords &out) {
     out.lights.resize(light_sampler->lights.size());
     for (auto &l : light_sampler->lights) l->fill_record(out.lights[l->index], *this, sctx, out.alias_table, out.alias_func);
     out.textures = image_pool.images;
+    if (light_sampler->kind() == VB_LIGHT_SAMPLER_POWER && !out.lights.empty()) {      // PowerLightSampler::prepare (power.cpp:33-53)
+        std::vector<float> weights(out.lights.size());
+        for (auto &l : light_sampler->lights) weights[l->index] = light_power_luminance(out.lights[l->index], out, l->shape_angle, l->shape_falloff);
+        out.light_sampler.kind = VB_LIGHT_SAMPLER_POWER;
+        out.light_sampler.alias_offset = (uint32_t)out.alias_table.size(); out.light_sampler.alias_size = (uint32_t)weights.size();
+        warper->build(weights, out.alias_table, out.alias_func, out.light_sampler.alias_integral);
+    }
     out.mediums.resize(mediums.size());
     for (auto &m : mediums) m->fill_record(out.mediums[m->index]);
     bool need_luts = false, principled = false;
@@ -300,6 +307,8 @@ void Pipeline::prepare(int device) {
     }
     check(vb_lights_set(ctx, records.lights.data(), (uint32_t)records.lights.size(), records.alias_table.data(), records.alias_func.data(),
                         (uint32_t)records.alias_table.size()), "vb_lights_set");
+    check(vb_light_sampler_set(ctx, records.light_sampler.kind, records.light_sampler.alias_offset, records.light_sampler.alias_size,
+                               records.light_sampler.alias_integral), "vb_light_sampler_set");
     check(vb_camera_set(ctx, &records.camera), "vb_camera_set");
     check(vb_integrator_set(ctx, &records.params), "vb_integrator_set");
     check(vb_film_create(ctx, records.width, records.height), "vb_film_create");

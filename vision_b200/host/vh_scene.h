@@ -30,6 +30,8 @@ public:
 };
 
 // POD view of a prepared scene: exactly what is pushed through the C ABI (and what tests feed the oracle)
+struct SceneRecords;
+float light_power_luminance(const vb_light_rec &l, const SceneRecords &rec, float spot_angle, float spot_falloff);   // vh_plugins.cpp
 struct SceneRecords {
     std::vector<std::shared_ptr<MeshData>> meshes;
     std::vector<vb_instance> instances;
@@ -37,6 +39,7 @@ struct SceneRecords {
     std::vector<vb_light_rec> lights;
     std::vector<vb_alias_entry> alias_table;
     std::vector<float> alias_func;
+    struct LightSamplerRec { uint32_t kind = VB_LIGHT_SAMPLER_UNIFORM, alias_offset = 0, alias_size = 0; float alias_integral = 0.f; } light_sampler;   // vb_light_sampler_set
     std::vector<Image> textures;
     std::vector<vb_medium_rec> mediums;
     std::vector<std::vector<float>> spds;          // SPD pool (vb_spds_set): hero spectrum's CIE x, y, z, D65 first, then material curves

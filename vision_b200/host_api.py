@@ -53,6 +53,10 @@ def plugin_names():
     return [s for s in buf.value.decode().split("\n") if s]
 
 
+class _LightSamplerRec(C.Structure):       # SceneRecords::LightSamplerRec (vh_scene.h)
+    _fields_ = [("kind", C.c_uint32), ("alias_offset", C.c_uint32), ("alias_size", C.c_uint32), ("alias_integral", C.c_float)]
+
+
 class HostPipeline:
     """Importer::import_scene + Pipeline::prepare/render/final_picture of the reference, through libvision_host"""
 
@@ -142,6 +146,8 @@ class HostPipeline:
         sc.lights = self._blob(2, capi.vb_light_rec)
         sc.alias_table = [(e.prob, e.alias) for e in self._blob(3, capi.vb_alias_entry)]
         sc.alias_func = [float(x) for x in self._blob(4, C.c_float)]
+        ls = self._blob(102, _LightSamplerRec)[0]
+        sc.light_sampler = (ls.kind, ls.alias_offset, ls.alias_size, ls.alias_integral)
         sc.camera = self._blob(5, capi.vb_camera)[0]
         sc.params = self._blob(6, capi.vb_pt_params)[0]
         sc.mediums = self._blob(7, capi.vb_medium_rec)

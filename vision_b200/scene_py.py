@@ -552,7 +552,7 @@ def _cfun(name, x):
     if _libm is None:
         import ctypes
         _libm = ctypes.CDLL("libm.so.6")
-        for n in ("sinf", "cosf", "tanf"):
+        for n in ("sinf", "cosf", "tanf", "acosf", "sqrtf"):
             getattr(_libm, n).restype = ctypes.c_float
             getattr(_libm, n).argtypes = [ctypes.c_float]
     return f32(getattr(_libm, name)(float(f32(x))))
@@ -587,6 +587,65 @@ def env_weights(tex):
     return (lum * sin_t).astype(f32)
 
 
+PI_F = f32(3.14159265358979323846)
+
+
+def _light_power_luminance(l, sc, shape=None):
+    """luminance(light->power()), the PowerLightSampler weight (power.cpp:35-50): area.cpp:87-89, point.cpp:32-34, spot.cpp:44-46,
+    projector.cpp:58-91, spherical.cpp:56-59; Light::average (light.h:80-83) = slot average x scale; a texture's average
+    (ocarina Image::average_vector, absent) = per-channel mean, summed in double in pixel order; luminance = Rec.709 (SURVEY A1).
+    `shape` carries what the record does not keep: spot (angle, falloff) in radians."""
+    if l.color.tex_id == VB_INVALID_ID:
+        avg = [f32(l.color.value[i]) for i in range(3)]
+    else:
+        t = np.asarray(sc.textures[l.color.tex_id], np.float32)
+        px = t.reshape(-1, t.shape[-1])[:, :3].astype(np.float64)
+        avg = [f32(np.add.accumulate(px[:, c])[-1] / len(px)) for c in range(3)]
+    avg = [f32(a * f32(l.scale)) for a in avg]
+    if l.type == capi.VB_LIGHT_AREA:
+        area = f32(0.0)
+        for w in sc.alias_func[l.alias_offset:l.alias_offset + l.alias_size]:
+            area = f32(area + f32(w))
+        k = f32(2.0 if l.two_sided else 1.0)
+        p = [f32(f32(f32(k * a) * area) * PI_F) for a in avg]
+    elif l.type == capi.VB_LIGHT_POINT:
+        p = [f32(f32(f32(4.0) * PI_F) * a) for a in avg]
+    elif l.type == capi.VB_LIGHT_SPOT:
+        angle, falloff = shape
+        s = f32(f32(1.0) - f32(f32(0.5) * f32(f32(angle * f32(2.0)) + falloff)))
+        p = [f32(f32(f32(f32(2.0) * PI_F) * a) * s) for a in avg]
+    elif l.type == capi.VB_LIGHT_ENV:
+        r = f32(f32(l.params[0]) / f32(2.0))
+        p = [f32(f32(PI_F * f32(r * r)) * a) for a in avg]
+    else:                                                              # projector: Girard's theorem on the frustum corner directions
+        ratio = f32(l.params[1])
+        y = _cfun("sqrtf", f32(f32(1.0) / f32(f32(ratio * ratio) + f32(1.0))))
+        x = f32(ratio * y)
+        z = _cfun("sqrtf", f32(f32(x * x) + f32(y * y)))
+        P0, P1, P2 = (x, y, z), (x, f32(-y), z), (f32(-x), f32(-y), z)
+
+        def cross(a, b):
+            return (f32(f32(a[1] * b[2]) - f32(a[2] * b[1])), f32(f32(a[2] * b[0]) - f32(a[0] * b[2])), f32(f32(a[0] * b[1]) - f32(a[1] * b[0])))
+
+        def dot(a, b):
+            return f32(f32(f32(a[0] * b[0]) + f32(a[1] * b[1])) + f32(a[2] * b[2]))
+
+        def norm(a):
+            l2 = dot(a, a)
+            if not l2 > 0:
+                return a
+            inv = f32(f32(1.0) / _cfun("sqrtf", l2))
+            return tuple(f32(c * inv) for c in a)
+
+        c01, c12, c20 = norm(cross(P0, P1)), norm(cross(P1, P2)), norm(cross(P2, P0))
+        neg = lambda a: tuple(f32(-c) for c in a)
+        ac = lambda a, b: _cfun("acosf", min(max(dot(a, b), f32(-1.0)), f32(1.0)))
+        solid = f32(abs(f32(f32(f32(ac(c01, neg(c12)) + ac(c12, neg(c20))) + ac(c20, neg(c01))) - PI_F)))
+        k = f32(f32(f32(2.0) * solid) / f32(f32(4.0) * PI_F))
+        p = [f32(k * a) for a in avg]
+    return f32(f32(f32(f32(0.212671) * p[0]) + f32(f32(0.715160) * p[1])) + f32(f32(0.072169) * p[2]))
+
+
 def _free_light_record(ld, sc, base, world_diameter):
     """lights listed under light_sampler.param.lights: point.cpp:24-27, spot.cpp:29-35, spherical.cpp:36-45,199-211"""
     t, prm = ld["type"], ld.get("param", {})
@@ -604,6 +663,7 @@ def _free_light_record(ld, sc, base, world_diameter):
             l.direction[:3] = [float(f32(x * inv)) for x in dv]
             l.params[0] = float(_cfun("cosf", angle))
             l.params[1] = float(_cfun("cosf", max(f32(0.0), f32(angle - falloff))))
+            l._shape = (angle, falloff)
     elif t == "spherical":
         l.type = capi.VB_LIGHT_ENV
         o2w, w2o = env_o2w(prm)
@@ -840,8 +900,9 @@ def build_scene(path, overrides=None) -> SceneRecords:
     # (lightsampler.cpp:67-77) groups them by type in first-seen order; records are made in that order
     if d.get("light_sampler", {}).get("param", {}).get("env_separate", False):      # lightsampler.cpp:11-14,159-197: not built
         raise NotImplementedError("light_sampler.env_separate = true is not implemented")
-    if d.get("light_sampler", {}).get("type", "uniform") != "uniform":
-        raise NotImplementedError("light sampler " + d["light_sampler"]["type"])
+    ls_type = d.get("light_sampler", {}).get("type", "uniform")
+    if ls_type not in ("uniform", "power"):
+        raise NotImplementedError("light sampler " + ls_type)
     free = [] if ov.get("drop_lights", False) else d.get("light_sampler", {}).get("param", {}).get("lights", [])
     type_of = {"point": capi.VB_LIGHT_POINT, "spot": capi.VB_LIGHT_SPOT, "spherical": capi.VB_LIGHT_ENV, "projector": capi.VB_LIGHT_PROJECTOR}
     pending = [(type_of.get(ld["type"], -1), ld, None) for ld in free] + [(capi.VB_LIGHT_AREA, em, ii) for em, ii in area_lights]
@@ -865,6 +926,11 @@ def build_scene(path, overrides=None) -> SceneRecords:
         sc.alias_table += table; sc.alias_func += func
         sc.instances[ii]["light_id"] = len(sc.lights)
         sc.lights.append(l)
+    if ls_type == "power" and sc.lights:                             # PowerLightSampler::prepare (power.cpp:33-53)
+        weights = [_light_power_luminance(l, sc, getattr(l, "_shape", None)) for l in sc.lights]
+        table, func, integral = alias_build(weights)
+        sc.light_sampler = (capi.VB_LIGHT_SAMPLER_POWER, len(sc.alias_table), len(table), integral)
+        sc.alias_table += table; sc.alias_func += func
     # camera
     cam = d["camera"]["param"]
     res = ov.get("resolution") or d.get("pipeline", {}).get("param", {}).get("frame_buffer", {}).get("param", {}).get("resolution", [1280, 720])
