@@ -41,6 +41,7 @@ def load():
         lib.vh_texture_copy.argtypes = [vp, C.c_uint32, vp]; lib.vh_texture_copy.restype = None
         lib.vh_plugin_names.argtypes = [vp, C.c_uint64]; lib.vh_plugin_names.restype = C.c_uint64
         lib.vh_scene_log.argtypes = [vp, vp, C.c_uint64]; lib.vh_scene_log.restype = C.c_uint64
+        lib.vh_ctx.argtypes = [vp]; lib.vh_ctx.restype = vp
         _lib = lib
     return _lib
 
@@ -113,6 +114,20 @@ class HostPipeline:
         out = np.empty((i["height"], i["width"], 4), np.float32)
         self._check(self.lib.vh_final_picture(self.h, out.ctypes.data), "vh_final_picture")
         return out
+
+    def context(self) -> "capi.Context":
+        """the pipeline's own vb_ctx (after prepare()), BORROWED: valid while this HostPipeline lives, never closed by the view"""
+        h = self.lib.vh_ctx(self.h)
+        if not h:
+            raise capi.VbError("HostPipeline.context(): prepare() has not run")
+        view = capi.Context.__new__(capi.Context)
+        view.lib = capi.load_library()
+        view.h = C.c_void_p(h)
+        view.device = 0
+        i = self.info()
+        view._res = (i["width"], i["height"])
+        view.close = lambda: None
+        return view
 
     def log(self):
         n = self.lib.vh_scene_log(self.h, None, 0)
