@@ -177,6 +177,27 @@ VB_API int vb_film_download(vb_ctx *ctx, float *rgba, int which);
 /* device address of a film plane (w*h float4), for the NCCL all-reduce of the SUM film across GPUs */
 VB_API int vb_film_device_ptr(vb_ctx *ctx, int which, void **ptr);
 
+/* ---- multi-GPU film (the reference's accumulation, frame_buffer.cpp:117-126, is single-GPU) -------------------
+ * Partition: rank g of G renders frames g, g + G, ... with vb_render_frames(ctx, g, n, G, VB_ACCUM_SUM); the SUM film
+ * (sum of radiance, w = sample count) is then made whole by ONE of the two calls below and resolved with VB_ACCUM_SUM.
+ *
+ * One process per GPU: vb_film_allreduce = ncclAllReduce(sum, fp32, w*h*4 floats) of the ACCUM film in place on the context's
+ * stream. `nccl_comm` is a ncclComm_t whose rank lives on this context's device: the caller's own, or one made by
+ * vb_nccl_comm_create (ncclGetUniqueId on rank 0 -> vb_nccl_unique_id, ship the 128 bytes to every rank by any means,
+ * ncclCommInitRank -> vb_nccl_comm_create). NCCL is bound at run time: the libnccl.so.2 already loaded in the process is used,
+ * else the system one (override: environment VB_NCCL_LIB); VB_ERR_UNSUPPORTED when none is found. */
+#define VB_NCCL_UNIQUE_ID_BYTES 128
+VB_API int vb_nccl_unique_id(void *id128);
+VB_API int vb_nccl_comm_create(vb_ctx *ctx, const void *id128, int n_ranks, int rank, void **nccl_comm);
+VB_API int vb_nccl_comm_destroy(vb_ctx *ctx, void *nccl_comm);
+VB_API int vb_film_allreduce(vb_ctx *ctx, void *nccl_comm);
+/* One process, n contexts on n different GPUs with peer access (NVLink): a fused reduce + resolve kernel per GPU. GPU g reads
+ * pixel slice g of all n ACCUM films over peer memory, adds them in RANK ORDER (deterministic), and writes the sum into the
+ * root's ACCUM film and the resolved picture (mean -> 1-exp(-x*exposure) -> tone map) into the root's OUTPUT film. Stream-ordered
+ * after the work queued on every context's stream; the root's stream is ordered after the whole reduction. */
+#define VB_MAX_PEERS 16
+VB_API int vb_film_reduce_peers(vb_ctx *const *ctxs, uint32_t n, uint32_t root, float exposure, int tonemap);
+
 /* ---- G-buffer of the camera stage (reference rt_geom, src/base/sensor/frame_buffer.cpp:156-219) ---------------------------- */
 /* denoiser / AOV planes of the primary hit for ONE frame index, w*h float4 each, all colours through Spectrum::linear_srgb:
  * NORMAL (shading normal, 1) - zero where the camera ray misses; ALBEDO (MaterialEvaluator::albedo(wo), 1); EMISSION

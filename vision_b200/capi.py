@@ -404,6 +404,11 @@ def _bind_pt(lib):
         "vb_gbuffer_render": [vp, C.c_uint32],
         "vb_gbuffer_download": [vp, C.c_int, vp],
         "vb_render_work": [vp, C.POINTER(C.c_uint64)],
+        "vb_nccl_unique_id": [vp],
+        "vb_nccl_comm_create": [vp, vp, C.c_int, C.c_int, C.POINTER(vp)],
+        "vb_nccl_comm_destroy": [vp, vp],
+        "vb_film_allreduce": [vp, vp],
+        "vb_film_reduce_peers": [C.POINTER(vp), C.c_uint32, C.c_uint32, C.c_float, C.c_int],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
@@ -535,6 +540,18 @@ def _pt_methods():
         self._check(self.lib.vb_dump_primary_hits(self.h, frame, C.byref(hs)), "vb_dump_primary_hits")
         return out
 
+    def nccl_comm_create(self, unique_id: bytes, n_ranks: int, rank: int) -> int:
+        comm = C.c_void_p()
+        buf = (C.c_ubyte * 128).from_buffer_copy(unique_id)
+        self._check(self.lib.vb_nccl_comm_create(self.h, buf, n_ranks, rank, C.byref(comm)), "vb_nccl_comm_create")
+        return comm.value
+
+    def nccl_comm_destroy(self, comm: int):
+        self._check(self.lib.vb_nccl_comm_destroy(self.h, C.c_void_p(comm)), "vb_nccl_comm_destroy")
+
+    def film_allreduce(self, comm: int):
+        self._check(self.lib.vb_film_allreduce(self.h, C.c_void_p(comm)), "vb_film_allreduce")
+
     def render_stats(self):
         st = (C.c_uint64 * 4)()
         self._check(self.lib.vb_render_stats(self.h, st), "vb_render_stats")
@@ -546,8 +563,26 @@ def _pt_methods():
         return {"closest_nodes": w[0], "closest_tris": w[1], "any_nodes": w[2], "any_tris": w[3]}
 
     for f in (render_work, upload_scene, render_frames, film_clear, film_resolve, film_download, film_device_ptr,
-              dump_primary_hits, render_stats, gbuffer):
+              dump_primary_hits, render_stats, gbuffer, nccl_comm_create, nccl_comm_destroy, film_allreduce):
         setattr(Context, f.__name__, f)
 
 
 _pt_methods()
+
+
+def nccl_unique_id() -> bytes:
+    """ncclGetUniqueId through the library's run-time NCCL binding (rank 0 calls it and ships the 128 bytes to every rank)"""
+    lib = load_library()
+    buf = (C.c_ubyte * 128)()
+    if lib.vb_nccl_unique_id(buf) != 0:
+        raise VbError("vb_nccl_unique_id: NCCL unavailable")
+    return bytes(buf)
+
+
+def film_reduce_peers(ctxs, root=0, exposure=1.0, tonemap=VB_TONEMAP_LINEAR):
+    """one process, several contexts on different GPUs: fused peer-memory reduce + resolve into ctxs[root]'s films"""
+    lib = load_library()
+    arr = (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+    rc = lib.vb_film_reduce_peers(arr, len(ctxs), root, exposure, tonemap)
+    if rc != 0:
+        raise VbError(f"vb_film_reduce_peers failed ({rc}): {lib.vb_last_error(ctxs[root].h).decode()}")

@@ -740,3 +740,5 @@ int vb_render_work(vb_ctx *ctx, uint64_t work[4]) {
 }
 
 }  // extern "C"
+
+#include "vb_pt_dist.cuh"

@@ -40,6 +40,23 @@ VB_API int vh_final_picture(vh_pipeline *h, float *rgba) {
 }
 VB_API int vh_download_accum(vh_pipeline *h, float *rgba) { VH_TRY(h->p->check(vb_film_download(h->p->ctx, rgba, VB_FILM_ACCUM), "vb_film_download")) }
 VB_API void *vh_ctx(vh_pipeline *h) { return h->p->ctx; }
+/* multi-GPU, one process per GPU: vh_set_partition before vh_prepare; then vh_nccl_init with the 128-byte id rank 0 got from
+ * vb_nccl_unique_id (every rank calls it; it blocks until all have). vh_final_picture then all-reduces the SUM film first. */
+VB_API int vh_set_partition(vh_pipeline *h, uint32_t rank, uint32_t world) { VH_TRY(h->p->set_partition(rank, world)) }
+VB_API int vh_nccl_init(vh_pipeline *h, const void *id128) { VH_TRY(h->p->nccl_init(id128)) }
+/* the all-reduce alone (what vh_final_picture does first), so that a harness can time it by itself */
+VB_API int vh_film_allreduce(vh_pipeline *h) { VH_TRY(h->p->check(vb_film_allreduce(h->p->ctx, h->p->nccl_comm), "vb_film_allreduce")) }
+VB_API int vh_synchronize(vh_pipeline *h) { VH_TRY(h->p->check(vb_ctx_synchronize(h->p->ctx), "vb_ctx_synchronize")) }
+/* one process, n GPUs: see vh::render_on_gpus. times_ms[3] = prepare, render, reduce + resolve + download (may be null) */
+VB_API vh_pipeline *vh_render_on_gpus(const char *path, uint32_t n_gpus, uint32_t spp, int use_nccl, float *rgba, uint64_t cap_floats, double *times_ms) {
+    try {
+        std::vector<float> pic; MultiGpuTimes t;
+        auto p = render_on_gpus(path, n_gpus, spp, use_nccl != 0, pic, &t);
+        if (rgba && cap_floats >= pic.size()) std::memcpy(rgba, pic.data(), pic.size() * 4);
+        if (times_ms) { times_ms[0] = t.prepare_ms; times_ms[1] = t.render_ms; times_ms[2] = t.reduce_ms; }
+        return new vh_pipeline{p};
+    } catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
 
 /* info[0..9] = width, height, spp, n_meshes, n_instances, n_materials, n_lights, n_alias, n_textures, tonemap */
 VB_API void vh_info(vh_pipeline *h, uint32_t *info, float *exposure) {

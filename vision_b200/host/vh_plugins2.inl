@@ -195,7 +195,9 @@ public:
     void render(Pipeline &p, uint32_t n_frames) override {
         // reference: per frame GBuffer -> path_tracing -> accumulate -> tone map, frame_index_++ ;
         // here one launch renders the whole batch of frame indices (film kept in registers)
-        p.check(vb_render_frames(p.ctx, frame_index, n_frames, 1, VB_ACCUM_LERP), "vb_render_frames");
+        // multi-GPU: of the n_frames indices this call covers, this rank takes frame_index + rank, + world, ... into a SUM film
+        uint32_t mine = n_frames > p.dist_rank ? (n_frames - p.dist_rank + p.dist_world - 1) / p.dist_world : 0;
+        if (mine) p.check(vb_render_frames(p.ctx, frame_index + p.dist_rank, mine, p.dist_world, p.accumulate_mode()), "vb_render_frames");
         frame_index += n_frames;
     }
 };

@@ -1,4 +1,6 @@
 #include "vh_scene.h"
+#include <chrono>
+#include <thread>
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -271,7 +273,19 @@ void Scene::prepare(SceneRecords &out) {
 void Pipeline::check(int rc, const char *what) const {
     if (rc != VB_OK) throw std::runtime_error(std::string(what) + " failed: " + vb_last_error(ctx));
 }
-Pipeline::~Pipeline() { if (ctx) vb_ctx_destroy(ctx); }
+Pipeline::~Pipeline() {
+    if (ctx && nccl_comm) vb_nccl_comm_destroy(ctx, nccl_comm);
+    if (ctx) vb_ctx_destroy(ctx);
+}
+void Pipeline::set_partition(uint32_t rank, uint32_t world) {
+    if (world == 0 || rank >= world) throw std::runtime_error("Pipeline::set_partition: rank out of range");
+    if (scene.integrator && scene.integrator->frame_index != 0) throw std::runtime_error("Pipeline::set_partition: frames already rendered");
+    dist_rank = rank; dist_world = world;
+}
+void Pipeline::nccl_init(const void *id128) {
+    if (!ctx) throw std::runtime_error("Pipeline::nccl_init: prepare() first");
+    check(vb_nccl_comm_create(ctx, id128, (int)dist_world, (int)dist_rank, &nccl_comm), "vb_nccl_comm_create");
+}
 void Pipeline::init_scene(const SceneDesc &d) { scene.init(d); }
 
 // FixedRenderPipeline::prepare (fixed/pipeline.cpp:14-23) + Pipeline::prepare_geometry (pipeline.cpp:272-277)
@@ -315,9 +329,58 @@ void Pipeline::prepare(int device) {
 }
 void Pipeline::render(uint32_t n_frames) { scene.integrator->render(*this, n_frames); }
 void Pipeline::final_picture(std::vector<float> &rgba) {
-    check(vb_film_resolve(ctx, VB_ACCUM_LERP, records.exposure, records.tonemap), "vb_film_resolve");
+    if (dist_world > 1) {
+        if (!nccl_comm) throw std::runtime_error("Pipeline::final_picture: partitioned render without a communicator (nccl_init)");
+        check(vb_film_allreduce(ctx, nccl_comm), "vb_film_allreduce");
+    }
+    check(vb_film_resolve(ctx, accumulate_mode(), records.exposure, records.tonemap), "vb_film_resolve");
     rgba.resize((size_t)records.width * records.height * 4);
     check(vb_film_download(ctx, rgba.data(), VB_FILM_OUTPUT), "vb_film_download");
+}
+
+std::shared_ptr<Pipeline> render_on_gpus(const std::string &scene_path, uint32_t n_gpus, uint32_t spp, bool use_nccl,
+                                         std::vector<float> &rgba, MultiGpuTimes *times, int first_device) {
+    if (n_gpus == 0 || n_gpus > VB_MAX_PEERS) throw std::runtime_error("render_on_gpus: bad GPU count");
+    using clk = std::chrono::steady_clock;
+    auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    std::vector<std::shared_ptr<Pipeline>> pipes(n_gpus);
+    std::vector<std::string> errors(n_gpus);
+    unsigned char id[VB_NCCL_UNIQUE_ID_BYTES] = {};
+    if (use_nccl && n_gpus > 1 && vb_nccl_unique_id(id) != VB_OK) throw std::runtime_error("render_on_gpus: NCCL unavailable");
+    auto each = [&](auto fn) {                      // one host thread per GPU (contexts are independent; NCCL init / collectives need all ranks)
+        std::vector<std::thread> th;
+        for (uint32_t g = 0; g < n_gpus; ++g)
+            th.emplace_back([&, g] { try { fn(g); } catch (const std::exception &e) { errors[g] = e.what(); } });
+        for (auto &t : th) t.join();
+        for (uint32_t g = 0; g < n_gpus; ++g)
+            if (!errors[g].empty()) throw std::runtime_error("GPU " + std::to_string(g) + ": " + errors[g]);
+    };
+    auto t0 = clk::now();
+    each([&](uint32_t g) {
+        pipes[g] = import_scene(scene_path);
+        pipes[g]->set_partition(g, n_gpus);
+        pipes[g]->prepare(first_device + (int)g);
+        if (use_nccl && n_gpus > 1) pipes[g]->nccl_init(id);
+    });
+    uint32_t n = spp ? spp : pipes[0]->records.spp;
+    auto t1 = clk::now();
+    each([&](uint32_t g) { pipes[g]->render(n); pipes[g]->check(vb_ctx_synchronize(pipes[g]->ctx), "vb_ctx_synchronize"); });
+    auto t2 = clk::now();
+    Pipeline &root = *pipes[0];
+    if (n_gpus == 1 || use_nccl) {
+        std::vector<std::vector<float>> pics(n_gpus);
+        each([&](uint32_t g) { pipes[g]->final_picture(pics[g]); });
+        rgba = std::move(pics[0]);
+    } else {
+        std::vector<vb_ctx *> ctxs;
+        for (auto &p : pipes) ctxs.push_back(p->ctx);
+        root.check(vb_film_reduce_peers(ctxs.data(), n_gpus, 0, root.records.exposure, root.records.tonemap), "vb_film_reduce_peers");
+        rgba.resize((size_t)root.records.width * root.records.height * 4);
+        root.check(vb_film_download(root.ctx, rgba.data(), VB_FILM_OUTPUT), "vb_film_download");
+    }
+    auto t3 = clk::now();
+    if (times) { times->prepare_ms = ms(t0, t1); times->render_ms = ms(t1, t2); times->reduce_ms = ms(t2, t3); }
+    return pipes[0];                                // the other pipelines (contexts, communicators) are released here
 }
 
 std::shared_ptr<Pipeline> import_scene(const std::string &path) {

@@ -89,13 +89,28 @@ public:
     explicit Pipeline(const PipelineDesc &) {}
     std::string impl_type() const override { return "fixed"; }
     void init_scene(const SceneDesc &d);
+    // multi-GPU: this pipeline is rank `dist_rank` of `dist_world`; it renders frame indices rank, rank + world, ...
+    // of every render(n) call into a SUM film; final_picture() first makes the film whole (NCCL all-reduce over `nccl_comm`,
+    // one process per GPU) - or render_on_gpus() below does it over peer memory (one process, several GPUs)
+    uint32_t dist_rank = 0, dist_world = 1;
+    void *nccl_comm = nullptr;
+    void set_partition(uint32_t rank, uint32_t world);
+    void nccl_init(const void *id128);                // after prepare(): vb_nccl_comm_create on this pipeline's context
+    int accumulate_mode() const { return dist_world > 1 ? VB_ACCUM_SUM : VB_ACCUM_LERP; }
     void prepare(int device);                         // uploads through the C ABI, builds the BVH
     void render(uint32_t n_frames);                   // integrator->render
-    void final_picture(std::vector<float> &rgba);     // resolve + download (pipeline.cpp:337-354)
+    void final_picture(std::vector<float> &rgba);     // [all-reduce +] resolve + download (pipeline.cpp:337-354)
     ~Pipeline() override;
     void check(int rc, const char *what) const;
 };
 
 std::shared_ptr<Pipeline> import_scene(const std::string &path);   // Importer::import_scene (importer.cpp:23-26)
+
+// One process, n GPUs (devices first_device .. first_device + n - 1): one pipeline + host thread per GPU, frames partitioned by
+// index, films reduced and resolved by vb_film_reduce_peers (use_nccl = false) or vb_film_allreduce (true). Returns rank 0's
+// pipeline (its OUTPUT / ACCUM films hold the whole picture); `rgba` gets the final picture.
+struct MultiGpuTimes { double prepare_ms = 0, render_ms = 0, reduce_ms = 0; };
+std::shared_ptr<Pipeline> render_on_gpus(const std::string &scene_path, uint32_t n_gpus, uint32_t spp, bool use_nccl,
+                                         std::vector<float> &rgba, MultiGpuTimes *times = nullptr, int first_device = 0);
 
 }  // namespace vh

@@ -1,6 +1,8 @@
 // vision-cli: headless stand-in for the reference's GUI-only driver (src/apps/vision-gui/main.cpp:10-14,
 // application.cpp:37-49,174-199; CLI flags of src/base/cli_parser.cpp:18-43 that this path uses).
-//   vision-cli -s <scene.json> [-o out.ppm] [--spp N] [-d cuda] [--device-index I] [--pfm out.pfm]
+//   vision-cli -s <scene.json> [-o out.ppm] [--spp N] [-d cuda] [--device-index I] [--pfm out.pfm] [--gpus N [--nccl]]
+// --gpus N: the spp frame indices are split over N GPUs of this box (rank g renders g, g + N, ...), films reduced + resolved over
+// NVLink peer memory (vb_film_reduce_peers) or, with --nccl, by ncclAllReduce (vb_film_allreduce).
 #include "vh_scene.h"
 #include <chrono>
 #include <cstdio>
@@ -8,7 +10,7 @@
 
 int main(int argc, char **argv) {
     std::string scene, out = "output.ppm", pfm, aov, device = "cuda";
-    uint32_t spp = 0; int dev_index = 0;
+    uint32_t spp = 0, gpus = 1; int dev_index = 0; bool nccl = false;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
         auto next = [&]() { if (i + 1 >= argc) { fprintf(stderr, "missing value for %s\n", a.c_str()); exit(2); } return std::string(argv[++i]); };
@@ -19,12 +21,33 @@ int main(int argc, char **argv) {
         else if (a == "--spp") spp = (uint32_t)std::stoul(next());
         else if (a == "-d" || a == "--device") device = next();
         else if (a == "--device-index") dev_index = std::stoi(next());
-        else if (a == "-h" || a == "--help") { printf("vision-cli -s scene.json [-o out.png|.ppm|.hdr|.pfm] [--pfm out.pfm] [--aov prefix] [--spp N] [-d cuda]\n"); return 0; }
+        else if (a == "--gpus") gpus = (uint32_t)std::stoul(next());
+        else if (a == "--nccl") nccl = true;
+        else if (a == "-h" || a == "--help") { printf("vision-cli -s scene.json [-o out.png|.ppm|.hdr|.pfm] [--pfm out.pfm] [--aov prefix] [--spp N] [-d cuda] [--gpus N [--nccl]]\n"); return 0; }
         else fprintf(stderr, "ignored argument %s\n", a.c_str());
     }
     if (scene.empty()) { fprintf(stderr, "vision-cli: -s <scene file> is required\n"); return 2; }
     if (device != "cuda") { fprintf(stderr, "vision-cli: only -d cuda exists (no CPU backend)\n"); return 2; }
     try {
+        if (gpus > 1) {
+            std::vector<float> img; vh::MultiGpuTimes t;
+            auto p = vh::render_on_gpus(scene, gpus, spp, nccl, img, &t, dev_index);
+            uint32_t n = spp ? spp : p->records.spp;
+            fprintf(stderr, "[vision] %ux%u, %u spp over %u GPUs (%s), init %.1f ms, render %.1f ms (%.1f Msamples/s), reduce + resolve + download %.2f ms\n",
+                    p->records.width, p->records.height, n, gpus, nccl ? "ncclAllReduce" : "peer-memory reduce",
+                    t.prepare_ms, t.render_ms, 1e-3 * p->records.width * p->records.height * n / t.render_ms, t.reduce_ms);
+            vh::save_image(out, img.data(), p->records.width, p->records.height);
+            if (!pfm.empty()) {
+                std::vector<float> acc((size_t)p->records.width * p->records.height * 4);
+                p->check(vb_film_download(p->ctx, acc.data(), VB_FILM_ACCUM), "vb_film_download");
+                for (size_t i = 0; i < acc.size(); i += 4) {      // SUM film -> mean, like the single-GPU --pfm
+                    float inv = acc[i + 3] > 0.f ? 1.f / acc[i + 3] : 0.f;
+                    acc[i] *= inv; acc[i + 1] *= inv; acc[i + 2] *= inv; acc[i + 3] = 1.f;
+                }
+                vh::save_pfm(pfm, acc.data(), p->records.width, p->records.height);
+            }
+            return 0;
+        }
         auto t0 = std::chrono::steady_clock::now();
         auto p = vh::import_scene(scene);
         p->prepare(dev_index);

@@ -42,6 +42,11 @@ def load():
         lib.vh_plugin_names.argtypes = [vp, C.c_uint64]; lib.vh_plugin_names.restype = C.c_uint64
         lib.vh_scene_log.argtypes = [vp, vp, C.c_uint64]; lib.vh_scene_log.restype = C.c_uint64
         lib.vh_ctx.argtypes = [vp]; lib.vh_ctx.restype = vp
+        lib.vh_set_partition.argtypes = [vp, C.c_uint32, C.c_uint32]
+        lib.vh_nccl_init.argtypes = [vp, vp]
+        lib.vh_film_allreduce.argtypes = [vp]
+        lib.vh_synchronize.argtypes = [vp]
+        lib.vh_render_on_gpus.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, vp, C.c_uint64, vp]; lib.vh_render_on_gpus.restype = vp
         _lib = lib
     return _lib
 
@@ -115,6 +120,21 @@ class HostPipeline:
         self._check(self.lib.vh_final_picture(self.h, out.ctypes.data), "vh_final_picture")
         return out
 
+    # -- multi-GPU (one process per GPU): partition before prepare(), communicator after it ------------------------------
+    def set_partition(self, rank, world):
+        self._check(self.lib.vh_set_partition(self.h, rank, world), "vh_set_partition")
+
+    def nccl_init(self, unique_id: bytes):
+        """every rank calls this with the 128 bytes rank 0 got from capi.nccl_unique_id(); blocks until all ranks have"""
+        buf = (C.c_ubyte * 128).from_buffer_copy(unique_id)
+        self._check(self.lib.vh_nccl_init(self.h, buf), "vh_nccl_init")
+
+    def film_allreduce(self):
+        self._check(self.lib.vh_film_allreduce(self.h), "vh_film_allreduce")
+
+    def synchronize(self):
+        self._check(self.lib.vh_synchronize(self.h), "vh_synchronize")
+
     def context(self) -> "capi.Context":
         """the pipeline's own vb_ctx (after prepare()), BORROWED: valid while this HostPipeline lives, never closed by the view"""
         h = self.lib.vh_ctx(self.h)
@@ -183,6 +203,23 @@ class HostPipeline:
             sc.textures.append(a)
         sc.resolution = (i["width"], i["height"]); sc.spp = i["spp"]; sc.exposure = i["exposure"]; sc.tonemap = i["tonemap"]
         return sc
+
+
+def render_on_gpus(scene_path, n_gpus, spp=0, use_nccl=False):
+    """one process, n GPUs (vh::render_on_gpus): returns (rank 0's HostPipeline, final picture (h, w, 4), times in ms)"""
+    lib = load()
+    probe = HostPipeline(scene_path)
+    probe.prepare_records()
+    i = probe.info()
+    probe.close()
+    pic = np.empty((i["height"], i["width"], 4), np.float32)
+    times = (C.c_double * 3)()
+    h = lib.vh_render_on_gpus(str(scene_path).encode(), n_gpus, spp, int(use_nccl), pic.ctypes.data, pic.size, times)
+    if not h:
+        raise capi.VbError("vh_render_on_gpus: " + lib.vh_last_error().decode())
+    hp = HostPipeline.__new__(HostPipeline)
+    hp.lib, hp.h = lib, C.c_void_p(h)
+    return hp, pic, {"prepare_ms": times[0], "render_ms": times[1], "reduce_ms": times[2]}
 
 
 def save_image(path, rgba) -> None:
