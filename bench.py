@@ -39,14 +39,13 @@ def parse():
     p.add_argument("--rays", type=int, default=1 << 24)
     p.add_argument("--cpu-sample-rays", type=int, default=1 << 18)
     p.add_argument("--no-cpu-baseline", action="store_true")
-    p.add_argument("--pt-res", type=int, default=1024)
-    p.add_argument("--pt-spp", type=int, default=64)
+    p.add_argument("--pt-spp", type=int, default=0, help="total spp of the cbox job (0 = the BASELINE config's: 16)")
     p.add_argument("--no-pt", action="store_true")
-    p.add_argument("--classroom-spp", type=int, default=16)
+    p.add_argument("--classroom-spp", type=int, default=0, help="total spp of the classroom job, split over the ranks (0 = 1024)")
     p.add_argument("--no-classroom", action="store_true")
-    p.add_argument("--dragon-spp", type=int, default=16)
+    p.add_argument("--dragon-spp", type=int, default=0, help="0 = 64")
     p.add_argument("--no-dragon", action="store_true")
-    p.add_argument("--dispersion-spp", type=int, default=64)
+    p.add_argument("--dispersion-spp", type=int, default=0, help="0 = 256")
     p.add_argument("--no-dispersion", action="store_true")
     p.add_argument("--opt", action="append", default=[], help="library option key=value (vb_ctx_set_option), e.g. build.ploc=0")
     return p.parse_args()
@@ -141,62 +140,67 @@ def measured_peak():
 
 
 class _DevPtr:
-    """wraps a raw device pointer as a CUDA-array-interface object so torch can all-reduce it in place"""
+    """wraps a raw device pointer as a CUDA-array-interface object (read-back of a film plane's mean, untimed)"""
 
     def __init__(self, ptr, n_floats):
         self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 2}
 
 
+# BASELINE.json configs run AS STATED (SURVEY.md section 8 table), loaded by the C++ host layer (libvision_host):
+#   key: (scene file, host overrides, total spp of the job, label)
+PT_CONFIGS = {
+    "cbox": ("scenes/cbox/cbox_matte.json", {}, 16,
+             "C1 cbox matte 256x256, 16 spp, max depth 5"),
+    "dragon": ("scenes/cbox_dragon/vision_scene.json", {}, 64,
+               "C3 cbox-dragon 1024x1024, 64 spp, depth 16 (procedural stand-in mesh, glass + Skin1 medium inside)"),
+    "dispersion": ("scenes/cbox/cbox_dispersion.json", {"resolution": [1024, 1024]}, 256,
+                   "C4 cbox dispersion 1024x1024, 256 spp, depth 16 (hero spectrum, BK7 glass + principled + Cu)"),
+    "classroom": ("scenes/classroom/vision_scene.json", {"resolution": [1920, 1080]}, 1024,
+                  "C5 classroom 1920x1080, 1024 spp, depth 16 (sky stand-in env map, fog, 79 models)"),
+}
+
+
 def pt_section(a, rank, world, local_rank, stream, which="cbox"):
-    """secondary measurement: the path tracer, sample-partitioned across ranks (rank g renders frames g, g+G, ...)
-    with ONE NCCL all-reduce of the SUM film followed by the fused resolve. Returns samples/s and Mrays/s (whole
-    job). which = "cbox": cbox-matte (BASELINE.json configs[0] geometry at 1024x1024, depth 5);
-    "classroom": BASELINE.json configs[4] (1920x1080, depth 16, env map + fog + glass/metal/substrate);
-    "dragon": configs[2] (cbox-dragon 1024x1024, depth 16, glass model with a scattering medium inside);
-    "dispersion": configs[3] (hero-wavelength spectrum, dispersive BK7 glass + principled + spectral metal, 1024x1024, depth 16)."""
+    """the path tracer on one BASELINE config, STRONG scaling: the job's total spp is fixed, rank g of G renders frame indices
+    g, g + G, ... (Pipeline::set_partition) into a SUM film, ONE vb_film_allreduce (ncclAllReduce inside the product, timed by
+    itself too) and the resolve. Everything goes through the C++ host layer: scene import, plugins, C ABI."""
     import torch
     import torch.distributed as dist
-    from vision_b200 import Context, scene_py, capi
-    from vision_b200.dist import frames_for_rank
-    if which == "cbox":
-        sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", dict(scene_py.CBOX_MATTE_OVERRIDES, resolution=[a.pt_res, a.pt_res]))
-        spp_rank, label = a.pt_spp, "cbox matte"
-    elif which == "dispersion":
-        sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_dispersion.json", {"resolution": [a.pt_res, a.pt_res]})
-        spp_rank, label = a.dispersion_spp, "cbox dispersion (hero spectrum, BK7 glass + principled + Cu)"
-    elif which == "dragon":
-        # config C3 through the C++ host layer (871 k-triangle OBJ: the Python twin's loader is for small files)
-        from vision_b200 import host_api
-        hp = host_api.HostPipeline(ROOT / "scenes" / "cbox_dragon" / "vision_scene.json")
-        hp.prepare_records()
-        sc = hp.records()
-        hp.close()
-        spp_rank, label = a.dragon_spp, "cbox-dragon (procedural stand-in mesh, glass + Skin1 medium inside)"
-    else:
-        sc = scene_py.build_scene(ROOT / "scenes" / "classroom" / "vision_scene.json", {})
-        spp_rank, label = a.classroom_spp, "classroom (sky stand-in env map)"
-    ctx = Context(local_rank)
+    from vision_b200 import capi, host_api
+    path, ov, spp_total, label = PT_CONFIGS[which]
+    spp_total = {"cbox": a.pt_spp, "dragon": a.dragon_spp, "dispersion": a.dispersion_spp, "classroom": a.classroom_spp}[which] or spp_total
+    hp = host_api.HostPipeline(ROOT / path, ov)
+    hp.set_partition(rank, world)
+    hp.prepare(local_rank)
+    ctx = hp.context()
     for kv in a.opt:
         ctx.set_option(kv.split("=")[0], float(kv.split("=")[1]))
     ctx.set_stream(stream.cuda_stream)
-    build = ctx.upload_scene(sc)
-    w, h = sc.resolution
-    film = torch.as_tensor(_DevPtr(ctx.film_device_ptr(capi.VB_FILM_ACCUM), w * h * 4), device=torch.device("cuda", local_rank))
+    if world > 1:
+        uid = [capi.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        hp.nccl_init(uid[0])
+    info = hp.info()
+    w, h = info["width"], info["height"]
+    dev = torch.device("cuda", local_rank)
 
     def run():
-        ctx.film_clear()
-        first, n_fr, stride = frames_for_rank(rank, world, spp_rank * world)      # rank g: frames g, g+G, ...
-        ctx.render_frames(first, n_fr, stride, capi.VB_ACCUM_SUM)
+        hp.invalidate()
+        hp.render(spp_total)                   # this rank's share of the frame indices
         if world > 1:
-            dist.all_reduce(film)
-        ctx.film_resolve(capi.VB_ACCUM_SUM, sc.exposure, sc.tonemap)
+            hp.film_allreduce()
+        ctx.film_resolve(capi.VB_ACCUM_SUM if world > 1 else capi.VB_ACCUM_LERP, info["exposure"], info["tonemap"])
 
-    run()
+    # warm-up: one small job (allocations, first-launch costs), not the whole config
+    hp.invalidate(); hp.render(min(spp_total, 2 * world))
+    if world > 1:
+        hp.film_allreduce()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
+    samples = w * h * spp_total
+    reps = max(1, min(20, int(4e8 // samples)))          # small configs are repeated; classroom (2.1 G samples) runs once
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    reps = 3
     ctx.profile_reset()
     e0.record(stream)
     for _ in range(reps):
@@ -204,23 +208,32 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
     e1.record(stream)
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
-    # per-stage device time of the timed runs (the library's own CUDA events around its launches, always on)
-    stage_ms = {k: ctx.profile_get(k)[0] / reps for k in ("trace_closest", "trace_any", "pt_generate", "pt_shade", "pt_shadow_resolve", "pt_film")}
-    st = ctx.render_stats()
-    t = torch.tensor([ms, float(st["closest"] + st["any"])], dtype=torch.float64, device=torch.device("cuda", local_rank))
+    stage_ms = {k: ctx.profile_get(k)[0] / reps for k in ("trace_closest", "trace_any", "pt_generate", "pt_shade", "pt_shadow_resolve", "pt_film", "film_allreduce")}
+    st = ctx.render_stats()                    # counters of the LAST vb_render_frames call = the whole share of this rank when it fits one call
+    out_mean = float(torch.as_tensor(_DevPtr(ctx.film_device_ptr(capi.VB_FILM_OUTPUT), w * h * 4), device=dev).mean())
+    # the all-reduce by itself: CUDA events around vb_film_allreduce alone, ranks aligned by a barrier first
+    ar_ms = None
+    if world > 1:
+        dist.barrier(); torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record(stream)
+        for _ in range(5):
+            hp.film_allreduce()
+        a1.record(stream)
+        torch.cuda.synchronize()
+        ar_ms = a0.elapsed_time(a1) / 5
+    t = torch.tensor([ms, float(st["closest"] + st["any"]), ar_ms or 0.0], dtype=torch.float64, device=dev)
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        ms, rays = float(tmax[0]), float(tsum[1])
+        ms, rays, ar_ms = float(tmax[0]), float(tsum[1]), float(tmax[2])
     else:
         rays = float(t[1])
-    out_mean = float(torch.as_tensor(_DevPtr(ctx.film_device_ptr(capi.VB_FILM_OUTPUT), w * h * 4), device=torch.device("cuda", local_rank)).mean())
-    samples = w * h * spp_rank * world
     roof = None
     if rank == 0:
         # bytes_per_sample = sum over traced rays of (32 + 20 | 1 + 80 nodes + 48 triangles) + 228 B per shaded
-        # vertex + 16 B film write; node / triangle counts from ONE instrumented frame (never timed), per-sample figures
-        # from this rank's counters. Denominators: HBM copy peak and the L2 read bandwidth measured here (64 MB resident set).
+        # vertex + 16 B film write; node / triangle counts from ONE instrumented frame (never timed).
+        # Denominators: HBM copy peak and the L2 read bandwidth measured here (64 MB resident set).
         ctx.set_option("pt.count_work", 1)
         ctx.film_clear(); ctx.render_frames(0, 1, 1, capi.VB_ACCUM_SUM); ctx.synchronize()
         s1, wk = ctx.render_stats(), ctx.render_work()
@@ -233,29 +246,33 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
         achieved = bytes_per_sample * sps_gpu / 1e9
         l2_gbs = ctx.probe_read_bandwidth(64 << 20, 20)
         hbm_gbs, _ = measured_peak()
-        bvh_bytes = int(build["node_bytes"] + build["tri_bytes"])
-        # traversal alone (north_star: "fraction of the memory-bound traversal roofline" on the named scenes): algorithmic bytes of the
-        # closest-hit / any-hit rays of the timed frames over the time spent in vb_trace_queue (ray sort + k_trace)
-        f_closest = st["closest"] / max(s1["closest"], 1)
-        f_any = st["any"] / max(s1["any"], 1)
+        frames_rank = max(1, (spp_total - rank + world - 1) // world)
         trav = {}
-        for name, b1, f in (("closest", b_closest, f_closest), ("any", b_any, f_any)):
+        for name, b1 in (("closest", b_closest), ("any", b_any)):
             t_ms = stage_ms["trace_" + name]
-            gbs = b1 * f / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0
+            gbs = b1 * frames_rank / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0      # frame 0's per-frame bytes x this rank's frames
             trav[name] = {"ms": t_ms, "achieved_gbs": gbs, "frac_l2": gbs / l2_gbs, "frac_hbm": gbs / hbm_gbs}
+        bs = hp.build_stats()
+        bvh_bytes = int(bs["node_bytes"] + bs["tri_bytes"])
         roof = {"bytes_per_sample": bytes_per_sample, "achieved": achieved, "unit": "GB/s (per GPU, algorithmic)",
                 "closest_nodes_per_ray": wk["closest_nodes"] / max(s1["closest"], 1), "closest_tris_per_ray": wk["closest_tris"] / max(s1["closest"], 1),
                 "any_nodes_per_ray": wk["any_nodes"] / max(s1["any"], 1), "any_tris_per_ray": wk["any_tris"] / max(s1["any"], 1),
-                "vertices_per_sample": s1["vertices"] / n1, "bvh_bytes": bvh_bytes,
+                "vertices_per_sample": s1["vertices"] / n1, "rays_per_sample": (s1["closest"] + s1["any"]) / n1, "bvh_bytes": bvh_bytes,
+                "bvh_build_ms": bs["build_ms"],
                 "bound": "l2" if bvh_bytes < (100 << 20) else "hbm", "l2_read_peak": l2_gbs, "hbm_peak": hbm_gbs,
                 "frac_l2": achieved / l2_gbs, "frac_hbm": achieved / hbm_gbs}
         roof["traversal_only"] = trav
         roof["stage_ms"] = stage_ms
-    ctx.close()
-    return {"roofline": roof, "scene": f"{label} {w}x{h}, {spp_rank} spp per GPU x {world} GPU(s), max depth {sc.params.max_depth}", "ms": ms,
-            "samples_per_s": samples / (ms * 1e-3), "mrays_per_s": rays / (ms * 1e-3) / 1e6, "rays_per_sample": rays / samples,
-            "film_allreduce": "torch.distributed NCCL sum over the float4 film" if world > 1 else "none (1 GPU)",
-            "output_mean": out_mean}
+        rays_per_sample = roof["rays_per_sample"]
+    hp.close()
+    out = {"config": label, "loaded_by": "C++ host layer (libvision_host: scene JSON -> plugins -> C ABI)",
+           "resolution": [w, h], "spp_total": spp_total, "n_gpus": world, "scaling": "strong (frame indices g, g + G, ... per rank)",
+           "ms": ms, "reps": reps, "samples_per_s": samples / (ms * 1e-3),
+           "film_allreduce": "vb_film_allreduce (ncclAllReduce of the float4 SUM film inside the product)" if world > 1 else "none (1 GPU)",
+           "film_allreduce_ms": ar_ms, "film_bytes": w * h * 16, "output_mean": out_mean, "roofline": roof}
+    if roof is not None:
+        out["mrays_per_s"] = rays_per_sample * samples / (ms * 1e-3) / 1e6
+    return out
 
 
 def main():
@@ -271,11 +288,14 @@ def main():
         mesh = synth.synth_mesh(a.tris, seed=1)
         ns = min(a.cpu_sample_rays, a.rays)
         rays = synth.synth_rays(ns, seed=2, seed_any=3)
-        cb = cpu_arm(a, mesh, rays, 0, max(1, min(a.steps, 5)), min(a.warmup, 1))
+        ran_steps, ran_warmup = max(1, min(a.steps, 5)), min(a.warmup, 1)      # bounded: a CPU step is ~0.1 s per 262144-ray sample
+        cb = cpu_arm(a, mesh, rays, 0, ran_steps, ran_warmup)
         line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "Mrays/s", "n_gpus": a.gpus,
-                "steps": a.steps, "warmup": a.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+                "steps": ran_steps, "warmup": ran_warmup, "steps_requested": a.steps, "warmup_requested": a.warmup,
+                "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": workload_name(a)},
+                "config": {"workload": workload_name(a), "rays_per_gpu": a.rays, "triangles": a.tris,
+                           "sample": f"each step traces the first {ns} rays of the {a.rays}-ray workload (closest + any)"},
                 "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": cb["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "note": "reference has no CPU backend and its compute layer (ocarina+OptiX) is absent: this arm is the "
@@ -406,13 +426,16 @@ def main():
         bytes_per_ray = 32 + 20 + 80 * npr + 48 * tpr
         dur_ms = k_closest_ms / a.steps          # one trace_closest call (sort + traverse) per step
         achieved = bytes_per_ray * n / (dur_ms * 1e-3) / 1e9
-        prof_traffic = None
+        # ncu figures of this kernel come from the committed capture profiles/traffic.json points at (a profiler cannot run inside
+        # the timed region); they are labelled as such and sit beside the live algorithmic-bytes fraction
+        prof = {}
         tf = ROOT / "profiles" / "traffic.json"
         if tf.exists():
             try:
-                prof_traffic = json.loads(tf.read_text()).get("trace_closest_bytes_per_launch")
+                prof = json.loads(tf.read_text())
             except Exception:
-                prof_traffic = None
+                prof = {}
+        prof_traffic = prof.get("trace_closest_bytes_per_launch")
         bpa = 32 + 1 + 80 * nodes_a / n + 48 * tris_a / n
         line = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -426,8 +449,12 @@ def main():
                     "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "vb_trace_closest = k_ray_keys + 3-pass radix sort + k_trace<closest> (timed together; k_trace is 95 % of it)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": prof_traffic, "peak_source": peak_src,
+            "roofline": {"bound": prof.get("measured_bound", "hbm"), "bound_contract": "hbm (algorithmic node + triangle bytes over the HBM copy peak, SURVEY.md 8d)",
+                         "kernel": "vb_trace_closest = k_ray_keys + 3-pass radix sort + k_trace<closest> (timed together; k_trace is 95 % of it)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": prof_traffic, "traffic_source": prof.get("source"),
+                         "ncu": {k: prof.get(k) for k in ("l1tex_throughput_pct", "issue_active_pct", "l1_hit_pct", "trace_closest_dram_gbs")},
+                         "dram_frac_of_peak": (prof_traffic / (dur_ms * 1e-3) / 1e9 / peak) if prof_traffic else None,
+                         "peak_source": peak_src,
                          "bytes_per_ray": bytes_per_ray, "nodes_per_ray": npr, "tris_per_ray": tpr,
                          "kernel_ms": dur_ms, "rays_per_launch": n},
             "kernels": {"trace_closest": {"ms": dur_ms, "mrays_s": n / dur_ms / 1e3, "hit_frac": hit_frac},
@@ -441,6 +468,8 @@ def main():
             line["path_tracer"] = pt
         if pt_room is not None:
             line["path_tracer_classroom"] = pt_room
+            # the workload north_star's multi-GPU target names (>= 7x at 8 GPUs on classroom 1920x1080): strong scaling over N
+            line["classroom"] = {k: pt_room[k] for k in ("config", "n_gpus", "spp_total", "samples_per_s", "ms", "film_allreduce_ms", "film_bytes", "scaling")}
         if pt_dragon is not None:
             line["path_tracer_cbox_dragon"] = pt_dragon
         if pt_disp is not None:

@@ -40,12 +40,17 @@ VB_API int vh_final_picture(vh_pipeline *h, float *rgba) {
 }
 VB_API int vh_download_accum(vh_pipeline *h, float *rgba) { VH_TRY(h->p->check(vb_film_download(h->p->ctx, rgba, VB_FILM_ACCUM), "vb_film_download")) }
 VB_API void *vh_ctx(vh_pipeline *h) { return h->p->ctx; }
+VB_API void vh_build_stats(vh_pipeline *h, vb_build_stats *out) { *out = h->p->build_stats; }
 /* multi-GPU, one process per GPU: vh_set_partition before vh_prepare; then vh_nccl_init with the 128-byte id rank 0 got from
  * vb_nccl_unique_id (every rank calls it; it blocks until all have). vh_final_picture then all-reduces the SUM film first. */
 VB_API int vh_set_partition(vh_pipeline *h, uint32_t rank, uint32_t world) { VH_TRY(h->p->set_partition(rank, world)) }
 VB_API int vh_nccl_init(vh_pipeline *h, const void *id128) { VH_TRY(h->p->nccl_init(id128)) }
 /* the all-reduce alone (what vh_final_picture does first), so that a harness can time it by itself */
 VB_API int vh_film_allreduce(vh_pipeline *h) { VH_TRY(h->p->check(vb_film_allreduce(h->p->ctx, h->p->nccl_comm), "vb_film_allreduce")) }
+/* start over: empty film, frame index 0 (Pipeline::invalidate, pipeline.h:96: frame_index_ = 0) */
+VB_API int vh_invalidate(vh_pipeline *h) {
+    VH_TRY({ h->p->check(vb_film_clear(h->p->ctx), "vb_film_clear"); h->p->scene.integrator->frame_index = 0; })
+}
 VB_API int vh_synchronize(vh_pipeline *h) { VH_TRY(h->p->check(vb_ctx_synchronize(h->p->ctx), "vb_ctx_synchronize")) }
 /* one process, n GPUs: see vh::render_on_gpus. times_ms[3] = prepare, render, reduce + resolve + download (may be null) */
 VB_API vh_pipeline *vh_render_on_gpus(const char *path, uint32_t n_gpus, uint32_t spp, int use_nccl, float *rgba, uint64_t cap_floats, double *times_ms) {
@@ -117,6 +122,27 @@ VB_API uint64_t vh_scene_log(vh_pipeline *h, char *dst, uint64_t cap) {
     if (dst && cap > s.size()) std::memcpy(dst, s.c_str(), s.size() + 1);
     return s.size() + 1;
 }
+
+/* model import by itself (the `model` plugin's loader): importer 1 = the reference's (vendored assimp, reference vertex / triangle
+ * order), 0 = the in-tree OBJ loader (file order). Returns a handle to the imported meshes or null. */
+struct vh_model { std::vector<MeshData> meshes; };
+VB_API int vh_assimp_available() { return assimp_available() ? 1 : 0; }
+VB_API vh_model *vh_model_load(const char *path, int importer, int swap_handed, int smooth, int flip_uv) {
+    try {
+        auto m = new vh_model();
+        if (importer) m->meshes = load_model_assimp(path, swap_handed != 0, smooth != 0, flip_uv != 0, 0);
+        else m->meshes.push_back(load_obj(path, smooth != 0, flip_uv != 0));
+        return m;
+    } catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+VB_API uint32_t vh_model_count(vh_model *m) { return (uint32_t)m->meshes.size(); }
+VB_API void vh_model_mesh_info(vh_model *m, uint32_t i, uint32_t *nv, uint32_t *nt) { *nv = m->meshes[i].nv(); *nt = m->meshes[i].nt(); }
+VB_API void vh_model_mesh_copy(vh_model *m, uint32_t i, float *pos, float *nrm, float *uv, uint32_t *tri) {
+    const MeshData &d = m->meshes[i];
+    std::memcpy(pos, d.pos.data(), d.pos.size() * 4); std::memcpy(nrm, d.nrm.data(), d.nrm.size() * 4);
+    std::memcpy(uv, d.uv.data(), d.uv.size() * 4); std::memcpy(tri, d.tri.data(), d.tri.size() * 4);
+}
+VB_API void vh_model_free(vh_model *m) { delete m; }
 
 /* image files (vh_image.cpp): save by extension (.png / .ppm with the display gamma, .hdr / .pfm linear); load (.hdr natively, .pfm,
  * .ppm, other LDR formats through their side-cars) - first call with dst = null to get the size */

@@ -102,15 +102,25 @@ MeshData load_obj(const std::string &path, bool smooth, bool flip_uv) {
     return m;
 }
 
-// reference src/render_core/shape/model.cpp:27-36 ("fn", "smooth", "flip_uv" default true, "swap_handed" unsupported here)
+// reference src/render_core/shape/model.cpp:27-36 ("fn", "swap_handed", "smooth", "flip_uv" default true, "subdiv_level"): one
+// instance per imported mesh, in the importer's order. "importer": "obj" forces the in-tree loader (file-order primitive ids).
 class Model : public ShapeGroup {
 public:
+    bool used_assimp = false;
     explicit Model(const ShapeDesc &desc) : ShapeGroup(desc) {
         name_ = desc.name;
         std::string fn = desc["fn"].as_string();
         if (fn.empty()) throw std::runtime_error("model shape " + desc.name + ": no \"fn\"");
         std::string full = fn[0] == '/' ? fn : desc["scene_path"].as_string(".") + "/" + fn;
-        add_instance(load_obj(full, desc["smooth"].as_bool(false), desc["flip_uv"].as_bool(true)));
+        bool smooth = desc["smooth"].as_bool(false), flip_uv = desc["flip_uv"].as_bool(true);
+        if (assimp_available() && desc["importer"].as_string("assimp") != "obj") {
+            for (auto &m : load_model_assimp(full, desc["swap_handed"].as_bool(false), smooth, flip_uv, desc["subdiv_level"].as_uint(0u)))
+                add_instance(std::move(m));
+            used_assimp = true;
+        } else {
+            if (desc["swap_handed"].as_bool(false)) throw std::runtime_error("model shape " + desc.name + ": swap_handed needs the assimp importer");
+            add_instance(load_obj(full, smooth, flip_uv));
+        }
         post_init(desc);
     }
     std::string impl_type() const override { return "model"; }

@@ -22,6 +22,11 @@ void save_image(const std::string &path, const float *rgba, uint32_t w, uint32_t
 void rgbe_encode(const float *rgb, unsigned char *out);
 void rgbe_decode(const unsigned char *in, float *rgb);
 
+// vh_assimp.cpp: the reference's importer (vendored assimp) behind the `model` shape; vh_plugins3.inl: in-tree OBJ loader (file order)
+bool assimp_available();
+std::vector<MeshData> load_model_assimp(const std::string &path, bool swap_handed, bool smooth, bool flip_uv, uint32_t subdiv_level);
+MeshData load_obj(const std::string &path, bool smooth, bool flip_uv);
+
 class ImagePool {
 public:
     std::vector<Image> images;

@@ -46,6 +46,14 @@ def load():
         lib.vh_nccl_init.argtypes = [vp, vp]
         lib.vh_film_allreduce.argtypes = [vp]
         lib.vh_synchronize.argtypes = [vp]
+        lib.vh_invalidate.argtypes = [vp]
+        lib.vh_build_stats.argtypes = [vp, vp]; lib.vh_build_stats.restype = None
+        lib.vh_assimp_available.restype = C.c_int
+        lib.vh_model_load.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int]; lib.vh_model_load.restype = vp
+        lib.vh_model_count.argtypes = [vp]; lib.vh_model_count.restype = C.c_uint32
+        lib.vh_model_mesh_info.argtypes = [vp, C.c_uint32, vp, vp]; lib.vh_model_mesh_info.restype = None
+        lib.vh_model_mesh_copy.argtypes = [vp, C.c_uint32, vp, vp, vp, vp]; lib.vh_model_mesh_copy.restype = None
+        lib.vh_model_free.argtypes = [vp]; lib.vh_model_free.restype = None
         lib.vh_render_on_gpus.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, vp, C.c_uint64, vp]; lib.vh_render_on_gpus.restype = vp
         _lib = lib
     return _lib
@@ -135,6 +143,15 @@ class HostPipeline:
     def synchronize(self):
         self._check(self.lib.vh_synchronize(self.h), "vh_synchronize")
 
+    def build_stats(self) -> dict:
+        st = capi.vb_build_stats()
+        self.lib.vh_build_stats(self.h, C.byref(st))
+        return {"n_triangles": st.n_triangles, "n_nodes": st.n_nodes, "node_bytes": st.node_bytes, "tri_bytes": st.tri_bytes, "build_ms": st.build_ms}
+
+    def invalidate(self):
+        """Pipeline::invalidate: empty film, frame index 0"""
+        self._check(self.lib.vh_invalidate(self.h), "vh_invalidate")
+
     def context(self) -> "capi.Context":
         """the pipeline's own vb_ctx (after prepare()), BORROWED: valid while this HostPipeline lives, never closed by the view"""
         h = self.lib.vh_ctx(self.h)
@@ -220,6 +237,31 @@ def render_on_gpus(scene_path, n_gpus, spp=0, use_nccl=False):
     hp = HostPipeline.__new__(HostPipeline)
     hp.lib, hp.h = lib, C.c_void_p(h)
     return hp, pic, {"prepare_ms": times[0], "render_ms": times[1], "reduce_ms": times[2]}
+
+
+def assimp_available() -> bool:
+    return bool(load().vh_assimp_available())
+
+
+def load_model(path, importer="assimp", swap_handed=False, smooth=False, flip_uv=True):
+    """the `model` plugin's loader by itself: list of {"pos", "nrm", "uv", "tri"} meshes. importer = "assimp" (the reference's
+    importer library: reference vertex / triangle order) or "obj" (in-tree loader: file order)"""
+    lib = load()
+    h = lib.vh_model_load(str(path).encode(), int(importer == "assimp"), int(swap_handed), int(smooth), int(flip_uv))
+    if not h:
+        raise capi.VbError("vh_model_load: " + lib.vh_last_error().decode())
+    out = []
+    try:
+        for i in range(lib.vh_model_count(h)):
+            nv, nt = C.c_uint32(), C.c_uint32()
+            lib.vh_model_mesh_info(h, i, C.byref(nv), C.byref(nt))
+            pos = np.empty((nv.value, 3), np.float32); nrm = np.empty((nv.value, 3), np.float32)
+            uv = np.empty((nv.value, 2), np.float32); tri = np.empty((nt.value, 3), np.uint32)
+            lib.vh_model_mesh_copy(h, i, pos.ctypes.data, nrm.ctypes.data, uv.ctypes.data, tri.ctypes.data)
+            out.append({"pos": pos, "nrm": nrm, "uv": uv, "tri": tri})
+    finally:
+        lib.vh_model_free(h)
+    return out
 
 
 def save_image(path, rgba) -> None:

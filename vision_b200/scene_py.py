@@ -167,6 +167,18 @@ def read_pfm(path):
     return np.ascontiguousarray(np.concatenate([a, np.ones((h, w, 1), np.float32)], axis=-1), np.float32)
 
 
+def model_meshes(path, prm):
+    """Model shape (model.cpp:27-36): the meshes of one model file, in the importer's order. With the reference's importer library
+    built into the host layer (tools/build_assimp.py) they come from it - the twin does not restate assimp's post-processing, only
+    the in-tree OBJ loader below ("importer": "obj", or no assimp: file-order primitive ids)."""
+    if prm.get("importer", "assimp") != "obj":
+        from . import host_api
+        if host_api.assimp_available():
+            return host_api.load_model(path, "assimp", bool(prm.get("swap_handed", False)), bool(prm.get("smooth", False)),
+                                       bool(prm.get("flip_uv", True)))
+    return [obj_mesh(path, smooth=bool(prm.get("smooth", False)), flip_uv=bool(prm.get("flip_uv", True)))]
+
+
 def obj_mesh(path, smooth=False, flip_uv=True):
     """Model shape (model.cpp:27-36). The reference imports through assimp with JoinIdenticalVertices |
     GenNormals | ImproveCacheLocality | FindDegenerates | OptimizeMeshes | Triangulate | FlipUVs
@@ -865,22 +877,23 @@ def build_scene(path, overrides=None) -> SceneRecords:
         elif sh["type"] == "sphere":
             mesh = sphere_mesh(prm.get("radius", 1.0), prm.get("sub_div", 60))
         elif sh["type"] == "model":
-            mesh = obj_mesh(base / prm["fn"], smooth=bool(prm.get("smooth", False)), flip_uv=bool(prm.get("flip_uv", True)))
+            mesh = model_meshes(base / prm["fn"], prm)
         else:
             raise NotImplementedError(sh["type"])
         mat_name = ov.get("shape_material", {}).get(sh["name"], prm.get("material"))
         mid = mat_index.get(mat_name, VB_INVALID_ID)                # unknown / empty name: no material (medium boundary)
         o2w = transform_matrix(prm.get("transform")).astype(f32).T.reshape(-1)       # column-major
-        inst = {"mesh_id": len(sc.meshes), "material_id": mid, "light_id": VB_INVALID_ID, "o2w": o2w}
-        if "medium" in prm:                                       # ShapeGroup::post_init, shape.cpp:245-270
-            inst["inside_medium"] = med_index.get(prm["medium"].get("inside", ""), VB_INVALID_ID)
-            inst["outside_medium"] = med_index.get(prm["medium"].get("outside", ""), VB_INVALID_ID)
-        else:
-            inst["inside_medium"] = inst["outside_medium"] = gm
-        sc.meshes.append(mesh)
-        if prm.get("emission"):
-            area_lights.append((prm["emission"], len(sc.instances)))
-        sc.instances.append(inst)
+        for one in (mesh if isinstance(mesh, list) else [mesh]):   # a model yields one instance per imported mesh (model.cpp:34-35)
+            inst = {"mesh_id": len(sc.meshes), "material_id": mid, "light_id": VB_INVALID_ID, "o2w": o2w}
+            if "medium" in prm:                                       # ShapeGroup::post_init, shape.cpp:245-270
+                inst["inside_medium"] = med_index.get(prm["medium"].get("inside", ""), VB_INVALID_ID)
+                inst["outside_medium"] = med_index.get(prm["medium"].get("outside", ""), VB_INVALID_ID)
+            else:
+                inst["inside_medium"] = inst["outside_medium"] = gm
+            sc.meshes.append(one)
+            if prm.get("emission"):
+                area_lights.append((prm["emission"], len(sc.instances)))
+            sc.instances.append(inst)
     # Scene::remove_unused_materials (scene.cpp:79-91): drop materials no instance refers to, re-index the rest;
     # records (and their textures) are made in the new index order
     used = sorted({i["material_id"] for i in sc.instances if i["material_id"] != VB_INVALID_ID})
