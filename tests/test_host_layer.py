@@ -173,7 +173,6 @@ def test_fitted_filter_tables_equal_python_twin(tmp_path, flt):
     p.write_text(json.dumps(d))
     import shutil
     shutil.copy(ROOT / "scenes" / "cbox" / "checker.jpg", tmp_path / "checker.jpg")
-    shutil.copy(ROOT / "scenes" / "cbox" / "checker.jpg.ppm", tmp_path / "checker.jpg.ppm")
     hp = host_api.HostPipeline(p)
     hp.prepare_records()
     a, b = hp.records(), scene_py.build_scene(p)

@@ -94,5 +94,6 @@ def test_classroom_full_size_vs_reference_render_and_oracle(oracle):
     err = float(np.mean((film[..., :3] - ofilm[..., :3]) ** 2 / (ofilm[..., :3] ** 2 + 1e-2)))
     print(f"classroom 1920x1080 x 2 spp: bit-identical pixels {same:.6f}, relMSE {err:.3e}, closest rays {stats['closest']} vs {ost['closest']}")
     assert err <= 1e-5 and same >= 0.998
-    assert stats["closest"] == ost["closest"]
+    # the reference (and the oracle) trace the camera ray twice, in rt_geom and again as bounce 0 of Li; the CUDA path traces it once
+    assert stats["closest"] + 2 * 1920 * 1080 == ost["closest"]
     hp.close()

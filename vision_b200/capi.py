@@ -90,6 +90,7 @@ def load_library() -> C.CDLL:
         fn.restype = C.c_int
     lib.vb_last_error.argtypes = [vp]
     lib.vb_last_error.restype = C.c_char_p
+    _bind_pt(lib)                       # path-tracer / film / multi-GPU signatures (defined below)
     _lib = lib
     return lib
 

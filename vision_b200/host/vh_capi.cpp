@@ -144,8 +144,8 @@ VB_API void vh_model_mesh_copy(vh_model *m, uint32_t i, float *pos, float *nrm, 
 }
 VB_API void vh_model_free(vh_model *m) { delete m; }
 
-/* image files (vh_image.cpp): save by extension (.png / .ppm with the display gamma, .hdr / .pfm linear); load (.hdr natively, .pfm,
- * .ppm, other LDR formats through their side-cars) - first call with dst = null to get the size */
+/* image files (vh_image.cpp): save by extension (.png / .ppm with the display gamma, .hdr / .pfm linear); load (.jpg / .png / .exr / .hdr / .pfm /
+ * .ppm decoded in the host layer) - first call with dst = null to get the size */
 VB_API int vh_save_image(const char *path, const float *rgba, uint32_t w, uint32_t h) { VH_TRY(save_image(path, rgba, w, h)) }
 VB_API int vh_load_image(const char *path, int srgb_to_linear, uint32_t *w, uint32_t *h, float *dst, uint64_t cap_floats) {
     VH_TRY({

@@ -2,7 +2,7 @@
 //   Radiance .hdr (RGBE; flat and new-style run-length scanlines) read + write, PNG write (8-bit RGB, zlib "stored" blocks: no
 //   compressor needed), dispatch by extension with the reference's rule "gamma unless exr / hdr"
 //   (reference src/base/mgr/pipeline.cpp:337-354 final_picture; src/base/mgr/image_pool.cpp:18-24 .exr / .hdr are linear on load).
-// JPG / PNG / EXR *decoding* stays with the build-time side-cars (tools/convert_textures.py): no codec library in this image.
+// JPG / PNG / EXR decoding and EXR writing: vh_codecs.cpp.
 #include "vh_scene.h"
 #include <cmath>
 #include <cstdio>
@@ -149,7 +149,8 @@ void save_image(const std::string &path, const float *rgba, uint32_t w, uint32_t
     else if (ends_with_ci(path, ".pfm")) save_pfm(path, rgba, w, h);
     else if (ends_with_ci(path, ".png")) save_png(path, rgba, w, h, true);
     else if (ends_with_ci(path, ".ppm")) save_ppm(path, rgba, w, h);
-    else throw std::runtime_error("save_image: unsupported output format '" + path + "' (.png, .ppm, .hdr, .pfm)");
+    else if (ends_with_ci(path, ".exr")) save_exr(path, rgba, w, h, false);      // linear, like .hdr (pipeline.cpp:337-354)
+    else throw std::runtime_error("save_image: unsupported output format '" + path + "' (.png, .ppm, .exr, .hdr, .pfm)");
 }
 
 }  // namespace vh

@@ -30,12 +30,15 @@ Image load_image(const std::string &path, bool to_linear) {
     std::string p = path;
     auto ends = [&](const char *e) { size_t n = strlen(e); return p.size() >= n && strcasecmp(p.c_str() + p.size() - n, e) == 0; };
     if (ends(".hdr") && std::ifstream(path, std::ios::binary)) return load_hdr(path);      // native reader; linear by definition (image_pool.cpp:18-24)
-    if (!ends(".pfm") && !ends(".ppm")) {                          // decoded side-car (tools/convert_textures.py): 8-bit .ppm, else float .pfm
-        p = path + ".ppm";
-        if (!std::ifstream(p, std::ios::binary)) p = path + ".pfm";
+    if (ends(".jpg") || ends(".jpeg") || ends(".png") || ends(".exr")) {                    // vh_codecs.cpp
+        Image im = decode_image_file(path);
+        if (to_linear && !ends(".exr"))
+            for (size_t i = 0; i < (size_t)im.w * im.h; ++i) for (int c = 0; c < 3; ++c) im.rgba[4 * i + c] = srgb_to_linear(im.rgba[4 * i + c]);
+        return im;
     }
+    if (!ends(".pfm") && !ends(".ppm")) throw std::runtime_error("unsupported image format " + path + " (.jpg, .png, .exr, .hdr, .pfm, .ppm)");
     std::ifstream f(p, std::ios::binary);
-    if (!f) throw std::runtime_error("cannot open image " + path + " (run tools/convert_textures.py to write " + p + ")");
+    if (!f) throw std::runtime_error("cannot open image " + path);
     std::string magic, tw, th, ts;
     read_pnm_token(f, magic); read_pnm_token(f, tw); read_pnm_token(f, th); read_pnm_token(f, ts);
     Image im; im.w = (uint32_t)std::stoul(tw); im.h = (uint32_t)std::stoul(th);
@@ -82,7 +85,6 @@ uint32_t ImagePool::obtain(const std::string &path, const std::string &color_spa
     std::string key = path + "|" + color_space;
     for (uint32_t i = 0; i < keys.size(); ++i) if (keys[i] == key) return i;
     auto ends = [&](const char *e) { size_t n = strlen(e); return path.size() >= n && strcasecmp(path.c_str() + path.size() - n, e) == 0; };
-    // side-car .pfm files written by tools/convert_textures.py hold the decoded 8-bit values / 255 of LDR sources
     bool to_linear = color_space == "srgb" && !ends(".exr") && !ends(".hdr");
     images.push_back(load_image(path, to_linear));
     keys.push_back(key);

@@ -9,9 +9,14 @@
 namespace vh {
 
 struct Image { uint32_t w = 0, h = 0; std::vector<float> rgba; };
-// .pfm / .ppm natively; other formats through a decoded side-car "<file>.pfm" written by
-// tools/convert_textures.py (image decoding is a §8f "next" row; no image library in this image)
+// Image::load of the reference (image_pool.cpp:13-35): .jpg / .png / .exr (vh_codecs.cpp), .hdr (vh_image.cpp), .pfm / .ppm;
+// srgb_to_linear applies the sRGB EOTF to LDR sources ("color_space": "srgb"; never to .exr / .hdr)
 Image load_image(const std::string &path, bool srgb_to_linear);
+Image decode_image_file(const std::string &path);     // .jpg / .png / .exr as stored (8-bit values / 255), no colour-space conversion
+void decode_jpeg(const unsigned char *data, size_t size, uint32_t &w, uint32_t &h, std::vector<unsigned char> &rgb);
+void decode_png(const unsigned char *data, size_t size, uint32_t &w, uint32_t &h, std::vector<float> &rgba);
+void decode_exr(const unsigned char *data, size_t size, uint32_t &w, uint32_t &h, std::vector<float> &rgba);
+void save_exr(const std::string &path, const float *rgba, uint32_t w, uint32_t h, bool half);    // scan-line, ZIP, channels B G R
 void save_pfm(const std::string &path, const float *rgba, uint32_t w, uint32_t h);
 void save_ppm(const std::string &path, const float *rgba01, uint32_t w, uint32_t h);   // applies linear_to_srgb
 // vh_image.cpp: Radiance .hdr read / write, PNG write, output dispatch by extension ("gamma unless exr / hdr", pipeline.cpp:337-354)
