@@ -372,6 +372,43 @@ def main():
     launches = k_closest_n + k_any_n
 
     # ---- e2e: pinned host buffers through the C ABI, H2D + D2H inside the timed region -------------
+    # record form (the reference's Ray / TriangleHit shapes): one 32-byte record per ray in, one 16-byte hit record (or 1 byte) out,
+    # calls queued asynchronously ("trace.async") so that step k+1's H2D runs under step k's traversal and D2H; the timed region
+    # ends with vb_ctx_synchronize (all results in host memory). The SoA synchronous form is timed beside it.
+    from vision_b200 import capi as _capi
+    pin = lambda arr: torch.from_numpy(arr).pin_memory()
+    rec_t, rec_any_t = pin(_capi.rays_to_records(rays)), pin(_capi.rays_to_records(rays, "tmax_any"))
+    h_rec_hits_t, h_rec_occ_t = pin(np.zeros((n, 4), np.uint32).view(np.int32)), pin(np.zeros(n, np.uint8))
+    rec, rec_any = rec_t.numpy(), rec_any_t.numpy()
+    h_rec_hits, h_rec_occ = h_rec_hits_t.numpy().view(np.uint32), h_rec_occ_t.numpy()
+    e2e_steps = max(1, min(a.steps, 10))
+
+    def e2e_run(step_fn, steps):
+        step_fn(); ctx.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for _ in range(steps):
+            step_fn()
+        ctx.synchronize()                    # every result is in host memory
+        f1.record(stream)
+        barrier()
+        wall = 1e3 * (time.perf_counter() - t0)
+        return max(f0.elapsed_time(f1), wall)    # device bracket vs host wall clock: the slower one
+
+    def e2e_step():
+        ctx.trace_closest_records(rec, h_rec_hits)
+        ctx.trace_any_records(rec_any, h_rec_occ)
+
+    ctx.set_option("trace.async", 1)
+    e2e_ms = e2e_run(e2e_step, e2e_steps)
+    ctx.set_option("trace.async", 0)
+    assert np.array_equal(h_rec_hits[:, 1], d_hits["prim"].cpu().numpy().view(np.uint32)), "e2e result differs"
+    assert np.array_equal(h_rec_occ, d_occ.cpu().numpy()), "e2e any-hit result differs"
+    h2d = 2 * 32 * n
+    d2h = 16 * n + n
+    # the SoA form (8 + 5 arrays per call, synchronous calls) for comparison
     h_rays = {k: torch.from_numpy(v).pin_memory() for k, v in rays.items()}
     hr = {k: v.numpy() for k, v in h_rays.items()}
     hr_any = dict(hr, tmax=hr["tmax_any"])
@@ -382,38 +419,26 @@ def main():
     h_hits["inst"] = h_hits["inst"].view(np.uint32); h_hits["prim"] = h_hits["prim"].view(np.uint32)
     h_occ_t = torch.empty(n, dtype=torch.uint8).pin_memory()
     h_occ = h_occ_t.numpy()
-    e2e_steps = max(1, min(a.steps, 5))
 
-    def e2e_step():
+    def e2e_soa_step():
         ctx.trace_closest(hr, h_hits)
         ctx.trace_any(hr_any, h_occ)
 
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record(stream)
-    for _ in range(e2e_steps):
-        e2e_step()
-    f1.record(stream)
-    barrier()
-    wall_ms = 1e3 * (time.perf_counter() - t0)
-    e2e_ms = max(f0.elapsed_time(f1), wall_ms)   # device bracket vs host wall clock: the slower one
-    assert np.array_equal(h_hits["prim"], d_hits["prim"].cpu().numpy().view(np.uint32)), "e2e result differs"
-    h2d = 2 * 8 * n * 4
-    d2h = 5 * n * 4 + n
+    soa_steps = max(1, min(a.steps, 3))
+    e2e_soa_ms = e2e_run(e2e_soa_step, soa_steps)
+    assert np.array_equal(h_hits["prim"], d_hits["prim"].cpu().numpy().view(np.uint32)), "e2e (SoA) result differs"
 
     # ---- reduce over ranks -------------------------------------------------------------------------
-    t = torch.tensor([ms_total, e2e_ms, k_closest_ms, k_any_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, e2e_ms, k_closest_ms, k_any_ms, e2e_soa_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms, k_closest_ms_max, k_any_ms_max = [float(x) for x in t.tolist()]
+    ms_total, e2e_ms, k_closest_ms_max, k_any_ms_max, e2e_soa_ms = [float(x) for x in t.tolist()]
     total_rays_step = 2 * n * world
     value = total_rays_step * a.steps / (ms_total * 1e-3) / 1e6
     e2e_value = total_rays_step * e2e_steps / (e2e_ms * 1e-3) / 1e6
 
     # free the microbench buffers, then the secondary path-tracing measurement (all ranks)
-    del d_rays, d_any, d_hits, d_occ, h_rays, h_hits_t, h_occ_t
+    del d_rays, d_any, d_hits, d_occ, h_rays, h_hits_t, h_occ_t, rec_t, rec_any_t, h_rec_hits_t, h_rec_occ_t
     torch.cuda.empty_cache()
     pt = None if a.no_pt else pt_section(a, rank, world, local_rank, stream)
     pt_room = None if (a.no_pt or a.no_classroom) else pt_section(a, rank, world, local_rank, stream, "classroom")
@@ -446,7 +471,12 @@ def main():
                            (bst["node_bytes"] + bst["tri_bytes"]) / 1e6, 32 * n / 1e6),
                        "partition": "rays sharded per rank, BVH replicated, no data-path collective"},
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
+                    "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
+                    "api": "vb_trace_closest_records + vb_trace_any_records (Ray / TriangleHit records, pinned host buffers, trace.async = 1, "
+                           "timed to vb_ctx_synchronize)",
+                    "soa_sync": {"value": total_rays_step * soa_steps / (e2e_soa_ms * 1e-3) / 1e6, "ms_per_step": e2e_soa_ms / soa_steps,
+                                 "h2d_bytes_per_step": 2 * 8 * n * 4, "d2h_bytes_per_step": 5 * n * 4 + n,
+                                 "api": "vb_trace_closest + vb_trace_any (SoA arrays, synchronous calls)"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": prof.get("measured_bound", "hbm"), "bound_contract": "hbm (algorithmic node + triangle bytes over the HBM copy peak, SURVEY.md 8d)",

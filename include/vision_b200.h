@@ -110,6 +110,15 @@ typedef struct vb_hits_soa {
 } vb_hits_soa;
 VB_API int vb_trace_closest(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out);
 VB_API int vb_trace_any(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, uint8_t *occluded, vb_mem out_mem);
+/* Record form: the reference's own data shapes at this boundary. vb_ray = ocarina Ray {org_min, dir_max} (32 bytes: geometry.h:64-69,
+ * frame_buffer.h:88-91), vb_hit = TriangleHit {inst_id, prim_id, bary} (16 bytes: geometry.cpp:81-85,215-219); no distance, as in the
+ * reference (compute_surface_interaction re-derives it). Same answers as the SoA form. Host buffers (mem = VB_MEM_HOST, ideally
+ * pinned) move as one copy per range each way, pipelined over copy-in / compute / copy-out streams. With option "trace.async" = 1
+ * a host-buffer call returns once queued - consecutive calls overlap - and results are valid after vb_ctx_synchronize. */
+typedef struct vb_ray { float ox, oy, oz, tmin, dx, dy, dz, tmax; } vb_ray;
+typedef struct vb_hit { uint32_t inst, prim; float u, v; } vb_hit;
+VB_API int vb_trace_closest_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits, vb_mem mem);
+VB_API int vb_trace_any_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, uint8_t *occluded, vb_mem mem);
 /* instrumented variants (never timed): per-call totals of wide nodes popped and triangles tested */
 VB_API int vb_trace_closest_counted(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out,
                                     uint64_t *nodes_popped, uint64_t *tris_tested);

@@ -206,3 +206,55 @@ def test_full_size_properties_16Mi_rays_10M_triangles(vbctx, oracle):
     o = acc.trace_closest(sub, threads=oracle.hw_threads())
     for f in ("inst", "prim", "u", "v", "t"):
         assert np.array_equal(o[f], g[f][::64]), f
+
+
+def test_record_form_equals_soa_form(vbctx):
+    """vb_trace_*_records (reference Ray / TriangleHit records): same answers as the SoA form from device buffers,
+    from host buffers (one range and pipelined ranges), and with "trace.async" = 1 (consecutive calls overlapping over the two
+    staging sets, completed by vb_ctx_synchronize)"""
+    import torch
+    from vision_b200 import capi
+    mesh = synth.synth_mesh(200_000, seed=11)
+    n = 3 * (1 << 20) + 1234
+    rays = synth.synth_rays(n, seed=12, seed_any=13)
+    mid = vbctx.mesh_upload_soup(mesh)
+    vbctx.instances_set([{"mesh_id": mid}])
+    vbctx.accel_build()
+    want = vbctx.trace_closest(rays)
+    want_occ = vbctx.trace_any(dict(rays, tmax=rays["tmax_any"]))
+    rec = capi.rays_to_records(rays)
+    rec_any = capi.rays_to_records(rays, "tmax_any")
+
+    def check(h, o):
+        h = np.asarray(h).view(np.uint32)
+        assert np.array_equal(h[:, 0], want["inst"]) and np.array_equal(h[:, 1], want["prim"])
+        assert h[:, 2].tobytes() == want["u"].tobytes() and h[:, 3].tobytes() == want["v"].tobytes()
+        assert np.array_equal(np.asarray(o), want_occ)
+    # host buffers, synchronous: one range, then pipelined ranges
+    for chunks in (1, 3):
+        vbctx.set_option("trace.host_chunks", chunks)
+        vbctx.set_option("trace.host_chunk_min_rays", 1 << 19)
+        check(vbctx.trace_closest_records(rec), vbctx.trace_any_records(rec_any))
+    # device buffers
+    d = torch.from_numpy(rec).cuda(); d_any = torch.from_numpy(rec_any).cuda()
+    check(vbctx.trace_closest_records(d).cpu().numpy(), vbctx.trace_any_records(d_any).cpu().numpy())
+    # asynchronous host calls: several in flight, different outputs each
+    vbctx.set_option("trace.async", 1)
+    try:
+        pin = lambda a: torch.from_numpy(a).pin_memory().numpy()
+        hr, hr_any = pin(rec), pin(rec_any)
+        outs = [(pin(np.zeros((n, 4), np.uint32)), pin(np.zeros(n, np.uint8))) for _ in range(3)]
+        for h, o in outs:
+            vbctx.trace_closest_records(hr, h)
+            vbctx.trace_any_records(hr_any, o)
+        vbctx.synchronize()
+        for h, o in outs:
+            check(h, o)
+    finally:
+        vbctx.set_option("trace.async", 0)
+        vbctx.set_option("trace.host_chunks", 4)
+        vbctx.set_option("trace.host_chunk_min_rays", 1 << 20)
+    # empty and tiny inputs
+    assert vbctx.trace_closest_records(rec[:0]).shape == (0, 4)
+    check_small = vbctx.trace_closest_records(np.ascontiguousarray(rec[:5])).view(np.uint32)
+    assert np.array_equal(check_small[:, 1], want["prim"][:5])

@@ -79,6 +79,8 @@ def load_library() -> C.CDLL:
         "vb_accel_download": [vp, vp, vp],
         "vb_trace_closest": [vp, C.POINTER(vb_rays_soa), C.c_uint64, C.POINTER(vb_hits_soa)],
         "vb_trace_any": [vp, C.POINTER(vb_rays_soa), C.c_uint64, vp, C.c_int],
+        "vb_trace_closest_records": [vp, vp, C.c_uint64, vp, C.c_int],
+        "vb_trace_any_records": [vp, vp, C.c_uint64, vp, C.c_int],
         "vb_trace_closest_counted": [vp, C.POINTER(vb_rays_soa), C.c_uint64, C.POINTER(vb_hits_soa),
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)],
         "vb_trace_any_counted": [vp, C.POINTER(vb_rays_soa), C.c_uint64, vp, C.c_int,
@@ -269,6 +271,42 @@ class Context:
             return out, a.value, b.value
         self._check(self.lib.vb_trace_any(self.h, C.byref(r), n, _ptr(out), mem), "vb_trace_any")
         return out
+
+
+    # -- record form: rays (n, 8) float32 = vb_ray, hits (n, 4) uint32 = vb_hit {inst, prim, u bits, v bits} ---------------
+    def trace_closest_records(self, rays, hits=None):
+        """rays: (n, 8) float32 numpy array (host, ideally pinned) or CUDA torch tensor; returns hits (n, 4) uint32 / int32"""
+        n = rays.shape[0]
+        dev = _is_device(rays)
+        if hits is None:
+            if dev:
+                import torch
+                hits = torch.empty((n, 4), dtype=torch.int32, device=rays.device)
+            else:
+                hits = np.empty((n, 4), np.uint32)
+        assert _is_device(hits) == dev, "rays and hits must live in the same memory space"
+        self._check(self.lib.vb_trace_closest_records(self.h, _ptr(rays), n, _ptr(hits), VB_MEM_DEVICE if dev else VB_MEM_HOST),
+                    "vb_trace_closest_records")
+        return hits
+
+    def trace_any_records(self, rays, occ=None):
+        n = rays.shape[0]
+        dev = _is_device(rays)
+        if occ is None:
+            if dev:
+                import torch
+                occ = torch.empty(n, dtype=torch.uint8, device=rays.device)
+            else:
+                occ = np.empty(n, np.uint8)
+        assert _is_device(occ) == dev, "rays and occlusion bytes must live in the same memory space"
+        self._check(self.lib.vb_trace_any_records(self.h, _ptr(rays), n, _ptr(occ), VB_MEM_DEVICE if dev else VB_MEM_HOST),
+                    "vb_trace_any_records")
+        return occ
+
+
+def rays_to_records(rays: dict, tmax_key="tmax") -> np.ndarray:
+    """SoA dict -> (n, 8) float32 vb_ray records"""
+    return np.ascontiguousarray(np.stack([rays[k] for k in ("ox", "oy", "oz", "tmin", "dx", "dy", "dz")] + [rays[tmax_key]], axis=1), np.float32)
 
 
 # ---------------------------------------------------------------------------------------------

@@ -94,6 +94,10 @@ struct vb_ctx {
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t ev_in[VB_MAX_HOST_CHUNKS] = {}, ev_out[VB_MAX_HOST_CHUNKS] = {};
     int ensure_copy_streams();
+    // record-form host calls (vb_trace_*_records): two alternating staging sets, "done" event of the call that last used each
+    void *rec_stage[2] = {nullptr, nullptr}; size_t rec_bytes[2] = {0, 0}; cudaEvent_t rec_done[2] = {nullptr, nullptr};
+    unsigned rec_call = 0; bool rec_pending = false;
+    int opt_trace_async = 0;                 // 1: host-buffer record calls return once queued; vb_ctx_synchronize completes them
     vb_pt_state *pt = nullptr;
 
     int fail(int code, const std::string &msg) { err = msg; return code; }

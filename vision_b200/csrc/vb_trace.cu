@@ -332,6 +332,131 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
     return VB_OK;
 }
 
+// ---- record form: the reference's own data shapes (Ray = {org_min, dir_max} 32 B in, TriangleHit = {inst, prim, bary} 16 B out) ----
+// Host buffers move as ONE copy per range each way (the SoA form needs 8 + 5) and 16 instead of 20 bytes come back per closest
+// hit; the AoS rays are traced in place (no SoA -> AoS pass). With option "trace.async" = 1 a host-buffer call returns once its
+// copies and kernels are queued: consecutive calls then overlap (call k+1's H2D runs under call k's traversal and D2H) over two
+// alternating staging sets; results are valid after vb_ctx_synchronize.
+__global__ void __launch_bounds__(256) k_ray_keys_aos(const float4 *__restrict__ aos, uint32_t n, float3 lo, float3 inv_ext,
+                                                      uint32_t *keys, uint32_t *vals, uint32_t oct_shift) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = __ldg(aos + 2 * (size_t)i), b = __ldg(aos + 2 * (size_t)i + 1);
+    keys[i] = vb_ray_sort_key(a.x, a.y, a.z, b.x, b.y, b.z, lo, inv_ext, oct_shift);
+    vals[i] = i;
+}
+
+int run_trace_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits, uint8_t *occ, vb_mem mem, bool any) {
+    if (!ctx) return VB_ERR_INVALID;
+    const char *fn = any ? "vb_trace_any_records" : "vb_trace_closest_records";
+    if (!ctx->accel.built) return ctx->fail(VB_ERR_STATE, std::string(fn) + ": accel not built");
+    if (!rays || (!any && !hits) || (any && !occ)) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": null argument");
+    if (n == 0) return VB_OK;
+    if (n >= (1ull << 32)) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": too many rays in one call");
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    const bool host = mem == VB_MEM_HOST;
+    int C = 1;
+    if (host && ctx->opt_host_chunks > 1 && n >= (uint64_t)ctx->opt_host_chunk_min_rays * 2)
+        C = (int)std::min<uint64_t>((uint64_t)std::min(ctx->opt_host_chunks, VB_MAX_HOST_CHUNKS), n / (uint64_t)ctx->opt_host_chunk_min_rays);
+    const uint64_t per = C > 1 ? (((n + C - 1) / C + 1023) & ~1023ull) : n;
+    if (host) { int rc = ctx->ensure_copy_streams(); if (rc) return rc; }
+    cudaStream_t s_in = host ? ctx->copy_in : st, s_out = host ? ctx->copy_out : st;
+
+    // staging set of this call (host buffers only): [rays 32 n][hits 16 n | occlusion n]; two sets alternate between calls
+    const int set = host ? (ctx->rec_call++ & 1) : 0;
+    const float4 *d_rays = (const float4 *)rays;
+    uint4 *d_hits = (uint4 *)hits; uint8_t *d_occ = occ;
+    if (host) {
+        size_t need = 32 * n + (any ? ((n + 255) & ~255ull) : 16 * n) + 256;
+        if (need > ctx->rec_bytes[set]) {
+            VB_CUDA(cudaDeviceSynchronize());                         // rare (first call / larger batch): nothing may still use the old set
+            if (ctx->rec_stage[set]) cudaFree(ctx->rec_stage[set]);
+            ctx->rec_stage[set] = nullptr; ctx->rec_bytes[set] = 0;
+            VB_CUDA(cudaMalloc(&ctx->rec_stage[set], need));
+            ctx->rec_bytes[set] = need;
+        }
+        if (!ctx->rec_done[set]) VB_CUDA(cudaEventCreateWithFlags(&ctx->rec_done[set], cudaEventDisableTiming));
+        else VB_CUDA(cudaStreamWaitEvent(s_in, ctx->rec_done[set], 0));      // the call that used this set two calls ago has drained
+        char *base = (char *)ctx->rec_stage[set];
+        d_rays = (const float4 *)base;
+        if (any) d_occ = (uint8_t *)(base + 32 * n); else d_hits = (uint4 *)(base + 32 * n);
+        // the copy streams start after whatever the caller queued on the context's stream
+        VB_CUDA(cudaEventRecord(ctx->ev_in[0], st));
+        VB_CUDA(cudaStreamWaitEvent(s_in, ctx->ev_in[0], 0));
+    }
+    int rc = ctx->ensure_stage(256 + 8 * (size_t)VB_MAX_HOST_CHUNKS * 2);
+    if (rc) return rc;
+    // per-call ray counters: a ring of 2 x VB_MAX_HOST_CHUNKS slots so that an async call never resets its predecessor's
+    unsigned long long *d_cnt = (unsigned long long *)ctx->stage;
+    unsigned long long *d_next0 = d_cnt + 4 + (size_t)set * VB_MAX_HOST_CHUNKS;
+    VB_CUDA(cudaMemsetAsync(d_next0, 0, 8 * (size_t)VB_MAX_HOST_CHUNKS, st));
+
+    VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
+    uint64_t launches = 0;
+    ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
+    for (int c = 0; c < C; ++c) {
+        const uint64_t r0 = (uint64_t)c * per;
+        if (r0 >= n) break;
+        const uint64_t m = std::min(per, n - r0);
+        if (host) {
+            VB_CUDA(cudaMemcpyAsync((void *)(d_rays + 2 * r0), rays + r0, m * sizeof(vb_ray), cudaMemcpyHostToDevice, s_in));
+            VB_CUDA(cudaEventRecord(ctx->ev_in[c], s_in));
+            VB_CUDA(cudaStreamWaitEvent(st, ctx->ev_in[c], 0));
+        }
+        const float4 *RS = d_rays + 2 * r0;
+        unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctx->opt_blocks_per_sm, (m + TRACE_BLOCK - 1) / TRACE_BLOCK);
+        const uint32_t *perm = nullptr;
+        launches += 1;
+        if (ctx->opt_sort_rays && m >= (uint64_t)ctx->opt_sort_min_rays) {
+            size_t cub_bytes = 0;
+            cub::DoubleBuffer<uint32_t> dk0(nullptr, nullptr), dv0(nullptr, nullptr);
+            VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk0, dv0, (int)m, 0, 24, st));
+            size_t nb = ((m * 4 + 255) & ~255ull);
+            size_t total = 4 * nb + cub_bytes + 256;
+            if (total > ctx->sort_bytes) {
+                VB_CUDA(cudaStreamSynchronize(st));
+                if (ctx->sort_buf) cudaFree(ctx->sort_buf);
+                ctx->sort_buf = nullptr; ctx->sort_bytes = 0;
+                VB_CUDA(cudaMalloc(&ctx->sort_buf, total));
+                ctx->sort_bytes = total;
+            }
+            char *sb = (char *)ctx->sort_buf;
+            uint32_t *k0 = (uint32_t *)sb, *k1 = (uint32_t *)(sb + nb), *v0 = (uint32_t *)(sb + 2 * nb), *v1 = (uint32_t *)(sb + 3 * nb);
+            void *cub_tmp = (void *)(((uintptr_t)(sb + 4 * nb) + 255) & ~(uintptr_t)255);
+            float3 lo = make_float3(ctx->sort_lo[0], ctx->sort_lo[1], ctx->sort_lo[2]);
+            float3 ie = make_float3(1.f / fmaxf(ctx->sort_hi[0] - ctx->sort_lo[0], 1e-30f), 1.f / fmaxf(ctx->sort_hi[1] - ctx->sort_lo[1], 1e-30f),
+                                    1.f / fmaxf(ctx->sort_hi[2] - ctx->sort_lo[2], 1e-30f));
+            k_ray_keys_aos<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(RS, (uint32_t)m, lo, ie, k0, v0, (uint32_t)ctx->opt_sort_oct_shift);
+            cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
+            cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)m, 0, 24, st);
+            if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }
+            perm = dv.Current();
+            launches += 5;
+        }
+        RaysDev R0{};
+        HitsDev H0{};
+        // perm == nullptr with RS set: k_trace reads ray i of the AoS array directly
+        if (any) k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R0, m, H0, d_occ + r0, d_cnt, d_next0 + c, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+        else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R0, m, H0, nullptr, d_cnt, d_next0 + c, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, d_hits + r0);
+        if (host) {
+            VB_CUDA(cudaEventRecord(ctx->ev_out[c], st));
+            VB_CUDA(cudaStreamWaitEvent(s_out, ctx->ev_out[c], 0));
+            if (any) VB_CUDA(cudaMemcpyAsync(occ + r0, d_occ + r0, m, cudaMemcpyDeviceToHost, s_out));
+            else VB_CUDA(cudaMemcpyAsync(hits + r0, d_hits + r0, m * sizeof(vb_hit), cudaMemcpyDeviceToHost, s_out));
+        }
+    }
+    ctx->cur_launches = launches;
+    ctx->prof_end();
+    VB_CHECK_LAUNCH();
+    if (host) {
+        VB_CUDA(cudaEventRecord(ctx->rec_done[set], s_out));
+        ctx->rec_pending = true;
+        if (!ctx->opt_trace_async) return vb_ctx_synchronize(ctx);       // host buffers are valid (and reusable) on return
+    }
+    return VB_OK;
+}
+
 }  // namespace
 
 // ---- queue form used by the wavefront path tracer (vb_pt_wavefront_host.cuh) -----------------------
@@ -388,6 +513,12 @@ int vb_trace_closest(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_
 }
 int vb_trace_any(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, uint8_t *occluded, vb_mem out_mem) {
     return run_trace(ctx, rays, n, nullptr, occluded, out_mem, true, nullptr, nullptr);
+}
+int vb_trace_closest_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits, vb_mem mem) {
+    return run_trace_records(ctx, rays, n, hits, nullptr, mem, false);
+}
+int vb_trace_any_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, uint8_t *occluded, vb_mem mem) {
+    return run_trace_records(ctx, rays, n, nullptr, occluded, mem, true);
 }
 int vb_trace_closest_counted(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out,
                              uint64_t *nodes_popped, uint64_t *tris_tested) {
