@@ -237,7 +237,9 @@ def test_record_form_equals_soa_form(vbctx):
         check(vbctx.trace_closest_records(rec), vbctx.trace_any_records(rec_any))
     # device buffers
     d = torch.from_numpy(rec).cuda(); d_any = torch.from_numpy(rec_any).cuda()
-    check(vbctx.trace_closest_records(d).cpu().numpy(), vbctx.trace_any_records(d_any).cpu().numpy())
+    dh, do = vbctx.trace_closest_records(d), vbctx.trace_any_records(d_any)
+    vbctx.synchronize()                      # device-buffer calls are stream-ordered on the context's stream, not torch's
+    check(dh.cpu().numpy(), do.cpu().numpy())
     # asynchronous host calls: several in flight, different outputs each
     vbctx.set_option("trace.async", 1)
     try:

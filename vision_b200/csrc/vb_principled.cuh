@@ -26,7 +26,37 @@ struct SubLobe {
     float eta = 1.f;
     float a = 1.f, b = 0.f;                        // sheen LTC coefficients
 };
-struct PrincipledSet { int n = 0; SubLobe s[6]; Frame3 frame; };
+// The lobe set lives in REGISTERS: no array is ever indexed with a run-time value. A lobe kind occurs at most once and always in
+// the order sheen, coat, metallic, transmission, specular, diffuse (principled_bsdf.cpp:352-461), so the set is a bit mask plus
+// per-kind fields; every loop over the lobes is six compile-time blocks (VB_EACH_SUBLOBE), and a SubLobe is re-assembled from the
+// fields on the spot. (Before: SubLobe s[6] indexed by a run-time count - a 1.2 KB stack frame in k_wf_shade, 240 B of spills.)
+struct PrincipledSet {
+    uint32_t switches = 0;                      // bit k: lobe kind k is present
+    Frame3 frame;
+    float sw[6] = {0, 0, 0, 0, 0, 0};           // sample weights (normalised by principled_create), constant indices only
+    f3 kr[6];
+    GGX mf{1.f, 1.f};
+    float ior = 1.f, eta_t = 1.f, trans_w = 1.f, cc_a = 1.f, cc_ior = 1.f, sheen_a = 1.f, sheen_b = 0.f;
+    f3 F0_met{0, 0, 0}, B_met{0, 0, 0}, F0_t{0, 0, 0}, F0_s{0, 0, 0};
+};
+
+template <int K>
+__device__ __forceinline__ SubLobe sub_lobe(const PrincipledSet &ps) {
+    SubLobe l;
+    l.kind = K; l.sample_weight = ps.sw[K]; l.kr = ps.kr[K];
+    if (K == SL_SHEEN) { l.a = ps.sheen_a; l.b = ps.sheen_b; }
+    if (K == SL_COAT) { l.fresnel = FR_DIELECTRIC; l.eta = ps.cc_ior; l.mf = GGX{ps.cc_a, ps.cc_a}; }
+    if (K == SL_METALLIC) { l.fresnel = FR_F82; l.F0 = ps.F0_met; l.B = ps.B_met; l.mf = ps.mf; }
+    if (K == SL_TRANS) { l.fresnel = FR_SCHLICK; l.eta = ps.eta_t; l.F0 = ps.F0_t; l.mf = ps.mf; l.weight = ps.trans_w; }
+    if (K == SL_SPEC) { l.fresnel = FR_SCHLICK; l.eta = ps.ior; l.F0 = ps.F0_s; l.mf = ps.mf; }
+    return l;
+}
+// BODY sees `const SubLobe l` and `constexpr int K`, once per present lobe, in lobe order
+#define VB_SUBLOBE_BLOCK(ps, KK, ...) if ((ps).switches & (1u << (KK))) { constexpr int K = (KK); const SubLobe l = sub_lobe<K>(ps); (void)K; __VA_ARGS__ }
+#define VB_EACH_SUBLOBE(ps, ...)                                                                                                          \
+    VB_SUBLOBE_BLOCK(ps, SL_SHEEN, __VA_ARGS__) VB_SUBLOBE_BLOCK(ps, SL_COAT, __VA_ARGS__) VB_SUBLOBE_BLOCK(ps, SL_METALLIC, __VA_ARGS__) \
+    VB_SUBLOBE_BLOCK(ps, SL_TRANS, __VA_ARGS__) VB_SUBLOBE_BLOCK(ps, SL_SPEC, __VA_ARGS__) VB_SUBLOBE_BLOCK(ps, SL_DIFFUSE, __VA_ARGS__)
+
 
 __device__ float saturate(float x) { return fmin_(fmax_(x, 0.f), 1.f); }
 __device__ f3 lerp3v(float t, f3 a, f3 b) { return {lerp(t, a.x, b.x), lerp(t, a.y, b.y), lerp(t, a.z, b.z)}; }
@@ -59,10 +89,9 @@ __device__ f3 layering_weight(f3 layer_albedo, f3 weight) {
     return weight * saturate(1.f - max_comp);
 }
 
-__device__ __noinline__ PrincipledSet principled_create(const PtScene &S, const Swl *swl, const Interaction &it) {
+__device__ __forceinline__ PrincipledSet principled_create(const PtScene &S, const Swl *swl, const Interaction &it) {
     const vb_material_rec &m = S.materials[it.mat_id];
     PrincipledSet ps;
-    ps.n = 0;
     ps.frame = it.shading;
     auto clampf = [](float v, float lo, float hi) { return fmin_(fmax_(v, lo), hi); };
     const uint32_t switches = (uint32_t)m.params[15];
@@ -78,8 +107,8 @@ __device__ __noinline__ PrincipledSet principled_create(const PtScene &S, const 
     float front = cos_theta > 0.f ? 1.f : 0.f;
     auto to_ratio_x = [](const GGX &g) { return __fsqrt_rn(__fsqrt_rn(g.ax * g.ay)); };
     if (switches & (1u << SL_SHEEN)) {
-        SubLobe &l = ps.s[ps.n++];
-        l.kind = SL_SHEEN;
+        SubLobe l;
+        ps.switches |= 1u << SL_SHEEN;
         f3 sheen_tint = spec_albedo_c(S.spec, swl, f3{m.params[4], m.params[5], m.params[6]}, true, 4u * it.mat_id + SC_SHEEN);
         float sheen_weight = m.params[2] * front;
         float sheen_roughness = m.params[3];
@@ -90,12 +119,12 @@ __device__ __noinline__ PrincipledSet principled_create(const PtScene &S, const 
         l.a = cx; l.b = cy;
         l.kr = l.kr * cz;
         f3 albedo = l.kr;
-        l.sample_weight = average3(albedo);
+        ps.sw[SL_SHEEN] = average3(albedo); ps.kr[SL_SHEEN] = l.kr; ps.sheen_a = l.a; ps.sheen_b = l.b;
         weight = layering_weight(albedo, weight);
     }
     if (switches & (1u << SL_COAT)) {
-        SubLobe &l = ps.s[ps.n++];
-        l.kind = SL_COAT;
+        SubLobe l;
+        ps.switches |= 1u << SL_COAT;
         float cc_weight = m.params[7] * front;
         float cc_roughness = sqr(clampf(m.params[8], 0.0001f, 1.f));
         float cc_ior = m.params[9];
@@ -106,12 +135,12 @@ __device__ __noinline__ PrincipledSet principled_create(const PtScene &S, const 
         const DevLut &L = S.luts[VB_LUT_COAT];
         float s = (L.data == nullptr) ? 1.f : lut_sample3d_ch0(L, to_ratio_x(l.mf), cos_theta, (cc_ior - 1.003f) / (4.f - 1.003f));
         f3 albedo = l.kr * s;
-        l.sample_weight = average3(albedo);
+        ps.sw[SL_COAT] = average3(albedo); ps.kr[SL_COAT] = l.kr; ps.cc_a = cc_roughness; ps.cc_ior = cc_ior;
         weight = layering_weight(albedo, weight);
     }
     if (switches & (1u << SL_METALLIC)) {
-        SubLobe &l = ps.s[ps.n++];
-        l.kind = SL_METALLIC;
+        SubLobe l;
+        ps.switches |= 1u << SL_METALLIC;
         float metallic = m.params[1] * front;
         l.fresnel = FR_F82; l.F0 = color;
         const float f = 6.f / 7.f, f5 = ((f * f) * (f * f)) * f;
@@ -119,24 +148,24 @@ __device__ __noinline__ PrincipledSet principled_create(const PtScene &S, const 
         l.B = f_schlick * (7.f / (f5 * f)) * (splat(1.f) - specular_tint);
         l.mf = mf;
         l.kr = weight * metallic;
-        l.sample_weight = metallic * average3(weight);
+        ps.sw[SL_METALLIC] = metallic * average3(weight); ps.kr[SL_METALLIC] = l.kr; ps.F0_met = l.F0; ps.B_met = l.B;
         weight = weight * (1.0f - metallic);
     }
     if (switches & (1u << SL_TRANS)) {
-        SubLobe &l = ps.s[ps.n++];
-        l.kind = SL_TRANS;
+        SubLobe l;
+        ps.switches |= 1u << SL_TRANS;
         float trans_weight = m.params[13];
         float eta = cos_theta > 0.f ? ior : 1.0f / ior;                   // Interaction::correct_eta
         l.fresnel = FR_SCHLICK; l.eta = eta; l.F0 = specular_tint * schlick_F0_from_ior(eta);
         l.mf = mf;
         l.kr = color;
         f3 t_weight = weight * trans_weight;
-        l.sample_weight = average3(t_weight); l.weight = average3(t_weight);
+        ps.sw[SL_TRANS] = average3(t_weight); ps.trans_w = average3(t_weight); ps.kr[SL_TRANS] = l.kr; ps.eta_t = eta; ps.F0_t = l.F0;
         weight = weight * (1.0f - trans_weight);
     }
     if (switches & (1u << SL_SPEC)) {
-        SubLobe &l = ps.s[ps.n++];
-        l.kind = SL_SPEC;
+        SubLobe l;
+        ps.switches |= 1u << SL_SPEC;
         l.fresnel = FR_SCHLICK; l.eta = ior; l.F0 = specular_tint * schlick_F0_from_ior(ior);
         l.mf = mf;
         l.kr = weight;
@@ -144,18 +173,20 @@ __device__ __noinline__ PrincipledSet principled_create(const PtScene &S, const 
         float z = __fsqrt_rn(fabsf((ior - 1.0f) / (ior + 1.0f)));
         float s = (L.data == nullptr) ? 1.f : lut_sample3d_ch0(L, to_ratio_x(l.mf), cos_theta, z);
         f3 albedo = lerp3v(s, l.F0, splat(1.f)) * l.kr;
-        l.sample_weight = average3(albedo);
+        ps.sw[SL_SPEC] = average3(albedo); ps.kr[SL_SPEC] = l.kr; ps.F0_s = l.F0;
         weight = layering_weight(albedo, weight);
     }
     if (switches & (1u << SL_DIFFUSE)) {
-        SubLobe &l = ps.s[ps.n++];
-        l.kind = SL_DIFFUSE;
-        l.kr = color * weight * front;
-        l.sample_weight = average3(l.kr);
+        ps.switches |= 1u << SL_DIFFUSE;
+        ps.kr[SL_DIFFUSE] = color * weight * front;
+        ps.sw[SL_DIFFUSE] = average3(ps.kr[SL_DIFFUSE]);
     }
+    ps.mf = mf; ps.ior = ior;
     float sum = 0.f;                                                     // LobeSet::normalize_sampled_weight
-    for (int i = 0; i < ps.n; ++i) sum += ps.s[i].sample_weight;
-    for (int i = 0; i < ps.n; ++i) ps.s[i].sample_weight = ps.s[i].sample_weight / sum;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) if (ps.switches & (1u << k)) sum += ps.sw[k];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) if (ps.switches & (1u << k)) ps.sw[k] = ps.sw[k] / sum;
     return ps;
 }
 
@@ -169,7 +200,7 @@ __device__ float sheen_eval_ltc(const SubLobe &l, f3 wi) {
     return w.z * InvPi * jacobian;
 }
 
-__device__ ScatterEval sub_evaluate_local(const PtScene &S, const SubLobe &l, f3 wo, f3 wi, float *eta_out) {
+__device__ __forceinline__ ScatterEval sub_evaluate_local(const PtScene &S, const SubLobe &l, f3 wo, f3 wi, float *eta_out) {
     ScatterEval se{f3{0, 0, 0}, 0.f, 0u};
     switch (l.kind) {
         case SL_SHEEN: {
@@ -233,11 +264,10 @@ __device__ ScatterEval sub_evaluate_local(const PtScene &S, const SubLobe &l, f3
 }
 
 // LobeSet::evaluate_impl (world), lobe.cpp:667-683
-__device__ __noinline__ ScatterEval principled_evaluate(const PtScene &S, const PrincipledSet &ps, f3 world_wo, f3 world_wi, float *eta_out) {
+__device__ __forceinline__ ScatterEval principled_evaluate(const PtScene &S, const PrincipledSet &ps, f3 world_wo, f3 world_wi, float *eta_out) {
     f3 wo = ps.frame.to_local(world_wo), wi = ps.frame.to_local(world_wi);
     ScatterEval ret{f3{0, 0, 0}, 0.f, 0u};
-    for (int i = 0; i < ps.n; ++i) {
-        const SubLobe &l = ps.s[i];
+    VB_EACH_SUBLOBE(ps, {
         ScatterEval se = sub_evaluate_local(S, l, wo, wi, eta_out);
         se.f = se.f * fabsf(wi.z);                                    // Lobe::evaluate_impl
         // valid_world_factor: same side of the shading normal (1 for the dielectric lobe)
@@ -247,22 +277,25 @@ __device__ __noinline__ ScatterEval principled_evaluate(const PtScene &S, const 
         ret.f = ret.f + se.f;
         ret.pdf = ret.pdf + se.pdf;
         ret.flags |= se.flags;
-    }
+    })
     return ret;
 }
 
 // Lobe::sample with LobeSet::sample_wi_impl, lobe.cpp:111-119,616-649
-__device__ __noinline__ BSDFSample principled_sample(const PtScene &S, const PrincipledSet &ps, f3 world_wo, Sampler &sampler) {
+// samples the direction only (the caller evaluates the set at it)
+__device__ __forceinline__ f3 principled_sample_wi(const PrincipledSet &ps, f3 world_wo, Sampler &sampler, bool &valid) {
     float uc = sampler.next_1d();
     (void)sampler.next_2d();                                              // drawn and unused by the reference
-    int strategy = 0;
+    int strategy = -1;                                                    // kind of the chosen lobe (the first present one to begin with)
     float sum_weights = 0.f;
-    for (int i = 0; i < ps.n; ++i) { strategy = uc > sum_weights ? i : strategy; sum_weights += ps.s[i].sample_weight; }
-    const SubLobe &l = ps.s[strategy];
-    f3 wo = ps.frame.to_local(world_wo), wi;
-    bool valid = true;
-    switch (l.kind) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+        if (ps.switches & (1u << k)) { strategy = (strategy < 0 || uc > sum_weights) ? k : strategy; sum_weights += ps.sw[k]; }
+    f3 wo = ps.frame.to_local(world_wo), wi{0, 0, 1};
+    valid = true;
+    switch (strategy) {
         case SL_SHEEN: {
+            const SubLobe l = sub_lobe<SL_SHEEN>(ps);
             f2 u = sampler.next_2d();
             float r = __fsqrt_rn(u.x), s, c;
             sincos_2pi(u.y, s, c);
@@ -271,6 +304,7 @@ __device__ __noinline__ BSDFSample principled_sample(const PtScene &S, const Pri
             wi = normalize(f3{w.x / l.a - w.z * l.b / l.a, w.y / l.a, w.z});      // M
         } break;
         case SL_TRANS: {
+            const SubLobe l = sub_lobe<SL_TRANS>(ps);
             f3 wh = ggx_sample_wh(l.mf, wo, sampler.next_2d());
             float d = dot(wo, wh);
             f3 F = sub_fresnel(l, fabsf(d));
@@ -281,26 +315,40 @@ __device__ __noinline__ BSDFSample principled_sample(const PtScene &S, const Pri
             else { bool ok = refract(wo, wh, l.eta, wi); valid = ok && !same_hemisphere(wo, wi); }
         } break;
         case SL_DIFFUSE: wi = cosine_hemisphere(sampler.next_2d(), wo.z); break;
-        default: {
-            f3 wh = ggx_sample_wh(l.mf, wo, sampler.next_2d());
+        default: {                                                        // coat / metallic / specular: the coat has its own roughness
+            const GGX mf = strategy == SL_COAT ? GGX{ps.cc_a, ps.cc_a} : ps.mf;
+            f3 wh = ggx_sample_wh(mf, wo, sampler.next_2d());
             wi = reflect(wo, wh);
             valid = same_hemisphere(wo, wi);
         } break;
     }
-    BSDFSample bs;
+    return ps.frame.to_world(wi);
+}
+
+// One call per shaded vertex: create the set once, evaluate it at the light direction, sample a direction, evaluate it there
+// (integrator.cpp:20-37,246-283 with MaterialEvaluator on a LobeSet). The two evaluations share ONE copy of the lobe code (a
+// two-trip loop), and the set never crosses a call boundary, so it stays in registers.
+__device__ __noinline__ void principled_shade(const PtScene &S, const Swl *swl, const Interaction &it, f3 wi_light, Sampler &sampler,
+                                              ScatterEval &se, BSDFSample &bs) {
+    const PrincipledSet ps = principled_create(S, swl, it);
+    f3 wi = wi_light;
+    bool valid = true;
     bs.eta = 1.f;
-    bs.wi = ps.frame.to_world(wi);
-    bs.eval = principled_evaluate(S, ps, world_wo, bs.wi, &bs.eta);
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        if (pass == 1) { wi = principled_sample_wi(ps, it.wo, sampler, valid); bs.wi = wi; }
+        ScatterEval e = principled_evaluate(S, ps, it.wo, wi, pass == 1 ? &bs.eta : nullptr);
+        if (pass == 0) se = e; else bs.eval = e;
+    }
     if (!valid) bs.eval.pdf *= 0.f;
-    return bs;
 }
 
 // LobeSet::albedo (lobe.cpp:564-570) over the sub-lobes: sheen = tint (principled_bsdf.cpp:54-56), coat / specular = their albedo
 // tables at cos_theta (:154-161,198-206), metallic = kr F82(cos), transmission = the dielectric form
-__device__ __noinline__ f3 principled_albedo(const PtScene &S, const PrincipledSet &ps, float cos_theta) {
+__device__ __noinline__ f3 principled_albedo(const PtScene &S, const Swl *swl, const Interaction &it, float cos_theta) {
+    const PrincipledSet ps = principled_create(S, swl, it);
     f3 ret{0, 0, 0};
-    for (int i = 0; i < ps.n; ++i) {
-        const SubLobe &l = ps.s[i];
+    VB_EACH_SUBLOBE(ps, {
         f3 a{0, 0, 0};
         float rx = __fsqrt_rn(__fsqrt_rn(l.mf.ax * l.mf.ay));
         switch (l.kind) {
@@ -320,7 +368,7 @@ __device__ __noinline__ f3 principled_albedo(const PtScene &S, const PrincipledS
             } break;
         }
         ret = ret + a * l.weight;
-    }
+    })
     return ret;
 }
 

@@ -150,10 +150,8 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         se.f = f3{f, f, f}; se.pdf = f; se.flags = 0;
         bs = phase_sample(it.g, it.wo, sampler);
     } else if (PRINCIPLED && S.materials[it.mat_id].type == VB_MAT_PRINCIPLED) {
-        PrincipledSet set = principled_create(S, swl, it);
-        se = principled_evaluate(S, set, it.wo, wi, nullptr);
+        principled_shade(S, swl, it, wi, sampler, se, bs);
         hemisphere_discard(se, it.wo, wi, it.ng);
-        bs = principled_sample(S, set, it.wo, sampler);
         hemisphere_discard(bs.eval, it.wo, bs.wi, it.ng);
     } else {
         Lobe lobe = create_lobe(S, swl, it);

@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_gbuffer(const __grid_constant__ Pt
         if (it.mat_id != VB_INVALID_ID) {
             float cos_theta = dot(it.shading.z, it.wo);              // MaterialEvaluator::albedo, material.cpp:91-98
             f3 a;
-            if (PRINCIPLED && S.materials[it.mat_id].type == VB_MAT_PRINCIPLED) a = principled_albedo(S, principled_create(S, swl, it), cos_theta);
+            if (PRINCIPLED && S.materials[it.mat_id].type == VB_MAT_PRINCIPLED) a = principled_albedo(S, swl, it, cos_theta);
             else a = lobe_albedo(create_lobe(S, swl, it), cos_theta);
             a = spec_to_srgb(S.spec, swl, a);
             albedo = make_float4(a.x, a.y, a.z, 1.f);
