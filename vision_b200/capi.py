@@ -13,6 +13,8 @@ import numpy as np
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libvision_b200.so"
+if os.environ.get("VISION_B200_LIB"):       # experiments only (tools/sweep_*.py): an alternative build of the same library
+    LIB_PATH = Path(os.environ["VISION_B200_LIB"])
 
 VB_MEM_HOST, VB_MEM_DEVICE = 0, 1
 VB_INVALID_ID = 0xFFFFFFFF

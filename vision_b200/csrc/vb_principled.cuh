@@ -325,10 +325,13 @@ __device__ __forceinline__ f3 principled_sample_wi(const PrincipledSet &ps, f3 w
     return ps.frame.to_world(wi);
 }
 
+#ifndef VB_PRINCIPLED_INLINE
+#define VB_PRINCIPLED_INLINE __noinline__
+#endif
 // One call per shaded vertex: create the set once, evaluate it at the light direction, sample a direction, evaluate it there
 // (integrator.cpp:20-37,246-283 with MaterialEvaluator on a LobeSet). The two evaluations share ONE copy of the lobe code (a
 // two-trip loop), and the set never crosses a call boundary, so it stays in registers.
-__device__ __noinline__ void principled_shade(const PtScene &S, const Swl *swl, const Interaction &it, f3 wi_light, Sampler &sampler,
+__device__ VB_PRINCIPLED_INLINE void principled_shade(const PtScene &S, const Swl *swl, const Interaction &it, f3 wi_light, Sampler &sampler,
                                               ScatterEval &se, BSDFSample &bs) {
     const PrincipledSet ps = principled_create(S, swl, it);
     f3 wi = wi_light;

@@ -90,7 +90,10 @@ template <int VARIANT>
 #ifndef VB_SHADE_MIN_BLOCKS
 #define VB_SHADE_MIN_BLOCKS 4
 #endif
-__global__ void __launch_bounds__(128, VB_SHADE_MIN_BLOCKS) k_wf_shade(const __grid_constant__ PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
+#ifndef VB_SHADE_MIN_BLOCKS_PRINCIPLED
+#define VB_SHADE_MIN_BLOCKS_PRINCIPLED 3      /* the principled instantiations trade resident warps (12 instead of 16 per SM) for 168 registers */
+#endif
+__global__ void __launch_bounds__(128, (VARIANT & PT_PRINCIPLED) ? VB_SHADE_MIN_BLOCKS_PRINCIPLED : VB_SHADE_MIN_BLOCKS) k_wf_shade(const __grid_constant__ PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
                                                   WfState st, WfQueue Qout, WfQueue Qsh, float4 *sh_pend, WfSortBox B, WfCounters *cnt, int filter) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
