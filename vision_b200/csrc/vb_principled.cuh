@@ -326,7 +326,7 @@ __device__ __forceinline__ f3 principled_sample_wi(const PrincipledSet &ps, f3 w
 }
 
 #ifndef VB_PRINCIPLED_INLINE
-#define VB_PRINCIPLED_INLINE __noinline__
+#define VB_PRINCIPLED_INLINE __forceinline__
 #endif
 // One call per shaded vertex: create the set once, evaluate it at the light direction, sample a direction, evaluate it there
 // (integrator.cpp:20-37,246-283 with MaterialEvaluator on a LobeSet). The two evaluations share ONE copy of the lobe code (a
