@@ -29,7 +29,16 @@ VB_API int vb_textures_set(vb_ctx *ctx, const vb_texture *tex, uint32_t n);
 
 /* ---- materials (reference src/render_core/material/<name>.cpp) ------------------------------------- */
 enum { VB_MAT_DIFFUSE = 0, VB_MAT_MIRROR = 1, VB_MAT_GLASS = 2, VB_MAT_METAL = 3, VB_MAT_SUBSTRATE = 4,
-       VB_MAT_PRINCIPLED = 5, VB_MAT_BLACK_BODY = 6 };
+       VB_MAT_PRINCIPLED = 5, VB_MAT_BLACK_BODY = 6,
+       /* plastic.cpp:12-133 (PlasticLobe: Lambert under a Schlick-Fresnel GGX coat; color = Rd, spec = Rs, ior slot, roughness slot,
+        * params[0] anisotropic, flags bit1 remapping_roughness) and metallic.cpp:12-63 (MetallicLobe: GGX reflection with the F82-tint
+        * Fresnel; color = F0 and reflection colour, spec = edge_tint, roughness slot, params[0] anisotropic, flags bit1) */
+       VB_MAT_PLASTIC = 7, VB_MAT_METALLIC = 8,
+       /* mix.cpp:52-57 / add.cpp:50-53: a LobeSet over the lobes of two CHILD materials (LobeSet::create_mix / create_add + flatten,
+        * lobe.cpp:495-562). spd[0], spd[1] = indices of the children in this same table (children are ordinary records that no
+        * instance refers to; they may be any single-lobe material or a principled BSDF, not another mix / add); MIX: sigma slot .x =
+        * frac (weights 1 - frac, frac); ADD: both weights 1, sample weights 1/2. */
+       VB_MAT_MIX = 9, VB_MAT_ADD = 10 };
 typedef struct vb_material_rec {
     uint32_t type;
     uint32_t flags;            /* bit0: has sigma (Oren-Nayar, diffuse.cpp:26-29), bit1: remapping_roughness,

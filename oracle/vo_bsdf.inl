@@ -170,8 +170,8 @@ struct Lobe {
     uint32_t type = VB_MAT_DIFFUSE;
     Frame frame;               // shading frame (Material::compute_shading_frame without a normal map)
     float3 kr{0, 0, 0};        // diffuse Kr | mirror kr | glass kt | substrate Rd
-    float3 rs{0, 0, 0};        // substrate Rs | metal eta
-    float3 kk{0, 0, 0};        // metal k
+    float3 rs{0, 0, 0};        // substrate Rs | metal eta | plastic / metallic Fresnel F0
+    float3 kk{0, 0, 0};        // metal k | metallic F82-tint B
     GGX mf{1.f, 1.f};
     float eta = 1.f;           // glass: corrected relative ior (Interaction::correct_eta); dispersive: of the hero wavelength (eta[0])
     float3 eta3{1, 1, 1};      // dispersive glass (hero spectrum, ior slot = "spd", glass.cpp:221-234): corrected ior per wavelength
@@ -179,8 +179,26 @@ struct Lobe {
     bool oren_nayar = false; float on_A = 1.f, on_B = 0.f;
 };
 
+// FresnelSchlick::evaluate (fresnel.h:44-52) and FresnelF82Tint::evaluate (fresnel.h:118-124) over plain colour triples
+inline float3 fresnel_schlick3(float3 F0, float eta, float cos_theta) {
+    float F_real = fresnel_dielectric(cos_theta, eta);
+    float F0_real = sqr((eta - 1.0f) / (eta + 1.0f));
+    float t = (F_real - F0_real) / (1.f - F0_real);
+    t = std::min(std::max(t, 0.f), 1.f);
+    return {lerp(t, F0.x, 1.f), lerp(t, F0.y, 1.f), lerp(t, F0.z, 1.f)};
+}
+inline float3 fresnel_f82(float3 F0, float3 B, float cos_theta) {
+    float mu = std::min(std::max(1.f - cos_theta, 0.f), 1.f);
+    float mu5 = pow5(mu);
+    float3 f_schlick{lerp(mu5, F0.x, 1.f), lerp(mu5, F0.y, 1.f), lerp(mu5, F0.z, 1.f)};
+    float3 r = f_schlick - B * cos_theta * mu5 * mu;
+    return {std::min(std::max(r.x, 0.f), 1.f), std::min(std::max(r.y, 0.f), 1.f), std::min(std::max(r.z, 0.f), 1.f)};
+}
+
 inline float3 lobe_fresnel(const Lobe &lb, float cos_theta) {
     switch (lb.type) {
+        case VB_MAT_PLASTIC: return fresnel_schlick3(lb.rs, lb.eta, cos_theta);
+        case VB_MAT_METALLIC: return fresnel_f82(lb.rs, lb.kk, cos_theta);
         case VB_MAT_METAL: return {fresnel_complex(cos_theta, lb.rs.x, lb.kk.x), fresnel_complex(cos_theta, lb.rs.y, lb.kk.y),
                                    fresnel_complex(cos_theta, lb.rs.z, lb.kk.z)};
         case VB_MAT_GLASS: return splat(fresnel_dielectric(cos_theta, lb.eta));
@@ -299,14 +317,26 @@ inline ScatterEval diffuse_evaluate_local(const Lobe &lb, float3 wo, float3 wi) 
     return se;
 }
 
+// -- PlasticLobe::evaluate_local_impl, plastic.cpp:37-50 (no hemisphere test of its own; flags stay at the ScatterEval default) --
+inline ScatterEval plastic_evaluate_local(const Lobe &lb, float3 wo, float3 wi) {
+    ScatterEval se;
+    float3 wh = normalize(wo + wi);
+    float3 F = lobe_fresnel(lb, abs_dot(wh, wo));
+    se.f = lb.kr * InvPi * (splat(1.f) - F);
+    se.f = se.f + F * ggx_brdf_div_fr(lb.mf, wo, wh, wi);
+    se.pdf = lerp(average3(F), std::fabs(wi.z) * InvPi, ggx_pdf_wi_reflection(lb.mf, wo, wh));
+    return se;
+}
+
 // Lobe::evaluate_impl (lobe.cpp:53-77): world -> local, f *= |cos(wi)|
 inline ScatterEval lobe_evaluate(const Scene &sc, const Lobe &lb, float3 world_wo, float3 world_wi, bool with_eta, float *eta_out) {
     float3 wo = lb.frame.to_local(world_wo), wi = lb.frame.to_local(world_wi);
     ScatterEval se;
     switch (lb.type) {
         case VB_MAT_GLASS: se = dielectric_evaluate_local(sc, lb, wo, wi, with_eta, eta_out); break;
-        case VB_MAT_MIRROR: case VB_MAT_METAL: se = microfacet_refl_evaluate_local(sc, lb, wo, wi); break;
+        case VB_MAT_MIRROR: case VB_MAT_METAL: case VB_MAT_METALLIC: se = microfacet_refl_evaluate_local(sc, lb, wo, wi); break;
         case VB_MAT_SUBSTRATE: se = fresnel_blend_evaluate_local(lb, wo, wi); break;
+        case VB_MAT_PLASTIC: se = plastic_evaluate_local(lb, wo, wi); break;
         default: se = diffuse_evaluate_local(lb, wo, wi); break;
     }
     se.f = se.f * std::fabs(wi.z);
@@ -325,10 +355,11 @@ inline float3 cosine_hemisphere(float2 u, float woz) {               // bxdf.cpp
 #include "vo_principled.inl"
 
 // Lobe::sample (lobe.cpp:111-119) with each lobe's sample_wi_local_impl; draws in the reference's order
-inline BSDFSample lobe_sample(const Scene &sc, const Lobe &lb, float3 world_wo, Sampler &sampler) {
+// the direction only (sample_wi_local_impl of the lobe, in world space); `valid` = SampledDirection::valid
+inline float3 lobe_sample_wi(const Lobe &lb, float3 world_wo, Sampler &sampler, bool &valid) {
     float3 wo = lb.frame.to_local(world_wo);
     float3 wi;
-    bool valid = true;
+    valid = true;
     switch (lb.type) {
         case VB_MAT_GLASS: {                                           // lobe.cpp:431-449
             float3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
@@ -343,7 +374,16 @@ inline BSDFSample lobe_sample(const Scene &sc, const Lobe &lb, float3 world_wo, 
                 valid = ok && !same_hemisphere(wo, wi);
             }
         } break;
-        case VB_MAT_MIRROR: case VB_MAT_METAL: {                       // bxdf.cpp:79-83
+        case VB_MAT_PLASTIC: {                                         // plastic.cpp:52-66
+            float3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
+            float3 F = lobe_fresnel(lb, std::fabs(wo.z));
+            float uc = sampler.next_1d();
+            if (uc < average3(F)) {
+                wi = reflect(wo, wh);
+                valid = same_hemisphere(wo, wi);
+            } else wi = cosine_hemisphere(sampler.next_2d(), 1.f);     // square_to_cosine_hemisphere: always the +z side
+        } break;
+        case VB_MAT_MIRROR: case VB_MAT_METAL: case VB_MAT_METALLIC: {  // bxdf.cpp:79-83
             float3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
             wi = reflect(wo, wh);
             valid = same_hemisphere(wo, wi);
@@ -362,8 +402,12 @@ inline BSDFSample lobe_sample(const Scene &sc, const Lobe &lb, float3 world_wo, 
         } break;
         default: wi = cosine_hemisphere(sampler.next_2d(), wo.z); break;
     }
+    return lb.frame.to_world(wi);
+}
+inline BSDFSample lobe_sample(const Scene &sc, const Lobe &lb, float3 world_wo, Sampler &sampler) {
+    bool valid = true;
     BSDFSample bs;
-    bs.wi = lb.frame.to_world(wi);
+    bs.wi = lobe_sample_wi(lb, world_wo, sampler, valid);
     bs.eval = lobe_evaluate(sc, lb, world_wo, bs.wi, true, &bs.eta);
     if (!valid) bs.eval.pdf *= 0.f;
     return bs;
@@ -371,8 +415,8 @@ inline BSDFSample lobe_sample(const Scene &sc, const Lobe &lb, float3 world_wo, 
 
 // Material::create_evaluator -> create_lobe_set of the plugin (diffuse.cpp:21-30, mirror.cpp:60-74,
 // glass.cpp:240-257, metal.cpp:137-156, substrate.cpp:126-149)
-inline Lobe create_lobe(const Scene &sc, const Swl &swl, const Interaction &it) {
-    const vb_material_rec &m = sc.materials[it.mat_id];
+inline Lobe create_lobe_of(const Scene &sc, const Swl &swl, const Interaction &it, uint32_t mat_id) {
+    const vb_material_rec &m = sc.materials[mat_id];
     Lobe lb;
     lb.type = m.type;
     lb.frame = it.shading;
@@ -424,46 +468,161 @@ inline Lobe create_lobe(const Scene &sc, const Swl &swl, const Interaction &it) 
             if (remap) { lb.mf.ax = sqr(lb.mf.ax); lb.mf.ay = sqr(lb.mf.ay); }
             lb.mf.ax = clampf(lb.mf.ax, 0.0001f, 1.f); lb.mf.ay = clampf(lb.mf.ay, 0.0001f, 1.f);
         } break;
+        case VB_MAT_PLASTIC: {                                         // plastic.cpp:109-129
+            lb.kr = spec_albedo(sc, swl, eval_slot3(sc, m.color, it.uv));
+            float3 Rs = spec_albedo(sc, swl, eval_slot3(sc, m.spec, it.uv));
+            float ior = eval_slot3(sc, m.ior, it.uv).x;
+            float r = clampf(eval_slot3(sc, m.roughness, it.uv).x, 0.0001f, 1.f);
+            r = remap ? sqr(r) : r;
+            calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
+            if (remap) { lb.mf.ax = sqr(lb.mf.ax); lb.mf.ay = sqr(lb.mf.ay); }
+            lb.mf.ax = clampf(lb.mf.ax, 0.0001f, 1.f); lb.mf.ay = clampf(lb.mf.ay, 0.0001f, 1.f);
+            lb.eta = ior;
+            lb.rs = Rs * sqr((ior - 1.0f) / (ior + 1.0f));             // schlick_F0_from_ior(iors[0]) * Rs
+        } break;
+        case VB_MAT_METALLIC: {                                        // metallic.cpp:44-60
+            lb.kr = spec_albedo(sc, swl, eval_slot3(sc, m.color, it.uv));
+            float3 edge_tint = spec_albedo(sc, swl, eval_slot3(sc, m.spec, it.uv));
+            float r = clampf(eval_slot3(sc, m.roughness, it.uv).x, 0.01f, 1.f);
+            r = remap ? sqr(r) : r;
+            calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
+            lb.rs = lb.kr;                                             // FresnelF82Tint(color) + init_from_F82(edge_tint), fresnel.h:110-116
+            const float f = 6.f / 7.f, f5 = ((f * f) * (f * f)) * f;
+            float3 f_schlick{lerp(f5, lb.rs.x, 1.f), lerp(f5, lb.rs.y, 1.f), lerp(f5, lb.rs.z, 1.f)};
+            lb.kk = f_schlick * (7.f / (f5 * f)) * (splat(1.f) - edge_tint);
+        } break;
         default: break;                                                // black body etc.: zero lobe
     }
     return lb;
 }
+inline Lobe create_lobe(const Scene &sc, const Swl &swl, const Interaction &it) { return create_lobe_of(sc, swl, it, it.mat_id); }
 
 // Lobe::albedo(cos_theta) of the single-lobe materials (lobe.h:167 diffuse = Kr; lobe.cpp:208-210 microfacet = kr * F(cos);
 // lobe.cpp:308-313 dielectric = kt (1 - F(|cos|)) + F; substrate.cpp:22 = Rd); consumed by rt_geom's albedo plane
 inline float3 lobe_albedo(const Lobe &lb, float cos_theta) {
     switch (lb.type) {
         case VB_MAT_DIFFUSE: case VB_MAT_SUBSTRATE: return lb.kr;
-        case VB_MAT_MIRROR: case VB_MAT_METAL: return lb.kr * lobe_fresnel(lb, cos_theta);
+        case VB_MAT_MIRROR: case VB_MAT_METAL: case VB_MAT_METALLIC: return lb.kr * lobe_fresnel(lb, cos_theta);
+        case VB_MAT_PLASTIC: return lobe_fresnel(lb, cos_theta);      // MicrofacetLobe::albedo with a unit reflection colour (plastic.cpp:127)
         case VB_MAT_GLASS: { float3 F = dielectric_F(lb, std::fabs(cos_theta)); return lb.kr * (splat(1.0f) - F) + F; }
         default: return float3{0, 0, 0};
     }
 }
 // LobeSet::albedo (lobe.cpp:564-570) over the principled BSDF's sub-lobes: sheen = tint (principled_bsdf.cpp:54-56), coat / specular =
 // their albedo tables at cos_theta (:154-161,198-206), metallic = kr F82(cos) (MicrofacetLobe::albedo), transmission = dielectric form
+inline float3 sub_albedo(const Scene &sc, const SubLobe &l, float cos_theta) {
+    float3 a{0, 0, 0};
+    auto to_ratio_x = [](const GGX &g) { return std::sqrt(std::sqrt(g.ax * g.ay)); };
+    switch (l.kind) {
+        case SL_SHEEN: case SL_DIFFUSE: a = l.kr; break;
+        case SL_COAT: {
+            const Lut &L = sc.luts[VB_LUT_COAT];
+            float s = L.data.empty() ? 1.f : lut_sample3d_ch0(L, to_ratio_x(l.mf), cos_theta, (l.eta - 1.003f) / (4.f - 1.003f));
+            a = l.kr * s;
+        } break;
+        case SL_METALLIC: a = l.kr * sub_fresnel(l, cos_theta); break;
+        case SL_TRANS: { float3 F = sub_fresnel(l, std::fabs(cos_theta)); a = l.kr * (splat(1.0f) - F) + F; } break;
+        case SL_SPEC: {
+            const Lut &L = sc.luts[VB_LUT_SPECULAR];
+            float z = std::sqrt(std::fabs((l.eta - 1.0f) / (l.eta + 1.0f)));
+            float s = L.data.empty() ? 1.f : lut_sample3d_ch0(L, to_ratio_x(l.mf), cos_theta, z);
+            a = lerp3v(s, l.F0, splat(1.f)) * l.kr;
+        } break;
+    }
+    return a;
+}
 inline float3 principled_albedo(const Scene &sc, const PrincipledSet &ps, float cos_theta) {
     float3 ret{0, 0, 0};
-    for (int i = 0; i < ps.n; ++i) {
-        const SubLobe &l = ps.s[i];
-        float3 a{0, 0, 0};
-        auto to_ratio_x = [](const GGX &g) { return std::sqrt(std::sqrt(g.ax * g.ay)); };
-        switch (l.kind) {
-            case SL_SHEEN: case SL_DIFFUSE: a = l.kr; break;
-            case SL_COAT: {
-                const Lut &L = sc.luts[VB_LUT_COAT];
-                float s = L.data.empty() ? 1.f : lut_sample3d_ch0(L, to_ratio_x(l.mf), cos_theta, (l.eta - 1.003f) / (4.f - 1.003f));
-                a = l.kr * s;
-            } break;
-            case SL_METALLIC: a = l.kr * sub_fresnel(l, cos_theta); break;
-            case SL_TRANS: { float3 F = sub_fresnel(l, std::fabs(cos_theta)); a = l.kr * (splat(1.0f) - F) + F; } break;
-            case SL_SPEC: {
-                const Lut &L = sc.luts[VB_LUT_SPECULAR];
-                float z = std::sqrt(std::fabs((l.eta - 1.0f) / (l.eta + 1.0f)));
-                float s = L.data.empty() ? 1.f : lut_sample3d_ch0(L, to_ratio_x(l.mf), cos_theta, z);
-                a = lerp3v(s, l.F0, splat(1.f)) * l.kr;
-            } break;
+    for (int i = 0; i < ps.n; ++i) ret += sub_albedo(sc, ps.s[i], cos_theta) * ps.s[i].weight;
+    return ret;
+}
+
+// ---- mix / add materials: a LobeSet over the lobes of two child materials --------------------------------------------------------
+// LobeSet::create_mix (lobe.cpp:495-508): children weighted (1 - frac, frac) in both weight and sample weight; create_add (:510-521):
+// weights 1, sample weights normalised to 1/2. flatten (:533-562): the sub-lobes of a child that is itself a set (the principled
+// BSDF) are pulled up with sample_weight *= parent sample weight and weight *= parent SAMPLE weight (sic). Evaluation and sampling
+// are LobeSet::evaluate_impl / sample_wi_impl over the flattened list (:598-683): every lobe in its own shading frame, f scaled by
+// weight * valid_world_factor, pdf by sample_weight * valid_world_factor. LobeSet has no is_dispersive (lobe.h:104): a dispersive
+// glass child never invalidates the secondary wavelengths.
+struct MixEntry { bool sub = false; float sw = 0.f, w = 1.f; Lobe lobe; SubLobe sl; Frame frame; };
+struct MixSet { int n = 0; MixEntry e[12]; };
+
+inline MixSet mixset_create(const Scene &sc, const Swl &swl, const Interaction &it) {
+    const vb_material_rec &m = sc.materials[it.mat_id];
+    float psw[2], pw[2];
+    if (m.type == VB_MAT_MIX) {
+        float frac = eval_slot3(sc, m.sigma, it.uv).x;
+        psw[0] = pw[0] = 1 - frac; psw[1] = pw[1] = frac;
+    } else {
+        float sum = 0.f; sum += 1.f; sum += 1.f;                        // normalize_sampled_weight
+        psw[0] = 1.f / sum; psw[1] = 1.f / sum; pw[0] = pw[1] = 1.f;
+    }
+    MixSet ms;
+    for (int c = 0; c < 2; ++c) {
+        uint32_t child = m.spd[c];
+        if (sc.materials[child].type == VB_MAT_PRINCIPLED) {
+            PrincipledSet ps = principled_create_of(sc, swl, it, child);
+            for (int i = 0; i < ps.n; ++i) {
+                MixEntry &e = ms.e[ms.n++];
+                e.sub = true; e.sl = ps.s[i]; e.frame = ps.frame;
+                e.sl.sample_weight = e.sl.sample_weight * psw[c];
+                e.sl.weight = e.sl.weight * psw[c];
+                e.sw = e.sl.sample_weight; e.w = e.sl.weight;
+            }
+        } else {
+            MixEntry &e = ms.e[ms.n++];
+            e.lobe = create_lobe_of(sc, swl, it, child);
+            e.sw = psw[c]; e.w = pw[c];
         }
-        ret += a * l.weight;
+    }
+    return ms;
+}
+
+inline ScatterEval mixset_evaluate(const Scene &sc, const MixSet &ms, float3 world_wo, float3 world_wi, float *eta_out) {
+    ScatterEval ret;
+    ret.flags = 0;
+    for (int i = 0; i < ms.n; ++i) {
+        const MixEntry &e = ms.e[i];
+        ScatterEval se;
+        float factor;
+        if (e.sub) {
+            float3 wo = e.frame.to_local(world_wo), wi = e.frame.to_local(world_wi);
+            se = sub_evaluate_local(sc, e.sl, wo, wi, eta_out);
+            se.f = se.f * std::fabs(wi.z);
+            factor = e.sl.kind == SL_TRANS ? 1.f : (dot(world_wo, e.frame.z) * dot(world_wi, e.frame.z) > 0.f ? 1.f : 0.f);
+        } else {
+            se = lobe_evaluate(sc, e.lobe, world_wo, world_wi, true, eta_out);
+            factor = e.lobe.type == VB_MAT_GLASS ? 1.f : (dot(world_wo, e.lobe.frame.z) * dot(world_wi, e.lobe.frame.z) > 0.f ? 1.f : 0.f);
+        }
+        se.f = se.f * (e.w * factor);
+        se.pdf = se.pdf * (e.sw * factor);
+        ret.f = ret.f + se.f;
+        ret.pdf = ret.pdf + se.pdf;
+        ret.flags |= se.flags;
+    }
+    return ret;
+}
+
+inline BSDFSample mixset_sample(const Scene &sc, const MixSet &ms, float3 world_wo, Sampler &sampler) {
+    float uc = sampler.next_1d();
+    (void)sampler.next_2d();
+    int strategy = 0;
+    float sum_weights = 0.f;
+    for (int i = 0; i < ms.n; ++i) { strategy = uc > sum_weights ? i : strategy; sum_weights += ms.e[i].sw; }
+    const MixEntry &e = ms.e[strategy];
+    bool valid = true;
+    BSDFSample bs;
+    bs.wi = e.sub ? sub_sample_wi(e.sl, e.frame, world_wo, sampler, valid) : lobe_sample_wi(e.lobe, world_wo, sampler, valid);
+    bs.eval = mixset_evaluate(sc, ms, world_wo, bs.wi, &bs.eta);
+    if (!valid) bs.eval.pdf *= 0.f;
+    return bs;
+}
+
+inline float3 mixset_albedo(const Scene &sc, const MixSet &ms, float cos_theta) {
+    float3 ret{0, 0, 0};
+    for (int i = 0; i < ms.n; ++i) {
+        const MixEntry &e = ms.e[i];
+        ret += (e.sub ? sub_albedo(sc, e.sl, cos_theta) : lobe_albedo(e.lobe, cos_theta)) * e.w;
     }
     return ret;
 }
@@ -481,6 +640,24 @@ struct PrincipledEvaluator {
     }
     BSDFSample sample(const Scene &sc, float3 wo, Sampler &sampler) const {
         BSDFSample bs = principled_sample(sc, set, wo, sampler);
+        bool same = dot(wo, ng) * dot(bs.wi, ng) > 0.f;
+        bool is_trans = (bs.eval.flags & FlagTransmission) != 0;
+        if (same == is_trans) bs.eval.pdf = 0.f;
+        return bs;
+    }
+};
+struct MixEvaluator {
+    MixSet set;
+    float3 ng;
+    ScatterEval evaluate(const Scene &sc, float3 wo, float3 wi) const {
+        ScatterEval se = mixset_evaluate(sc, set, wo, wi, nullptr);
+        bool same = dot(wo, ng) * dot(wi, ng) > 0.f;
+        bool is_trans = (se.flags & FlagTransmission) != 0;
+        if (same == is_trans) se.pdf = 0.f;
+        return se;
+    }
+    BSDFSample sample(const Scene &sc, float3 wo, Sampler &sampler) const {
+        BSDFSample bs = mixset_sample(sc, set, wo, sampler);
         bool same = dot(wo, ng) * dot(bs.wi, ng) > 0.f;
         bool is_trans = (bs.eval.flags & FlagTransmission) != 0;
         if (same == is_trans) bs.eval.pdf = 0.f;

@@ -57,8 +57,10 @@ inline float3 layering_weight(float3 layer_albedo, float3 weight) {
     return weight * saturate(1.f - max_comp);
 }
 
-inline PrincipledSet principled_create(const Scene &sc, const Swl &swl, const Interaction &it) {
-    const vb_material_rec &m = sc.materials[it.mat_id];
+inline PrincipledSet principled_create_of(const Scene &sc, const Swl &swl, const Interaction &it, uint32_t mat_id);
+inline PrincipledSet principled_create(const Scene &sc, const Swl &swl, const Interaction &it) { return principled_create_of(sc, swl, it, it.mat_id); }
+inline PrincipledSet principled_create_of(const Scene &sc, const Swl &swl, const Interaction &it, uint32_t mat_id) {
+    const vb_material_rec &m = sc.materials[mat_id];
     PrincipledSet ps;
     ps.frame = it.shading;
     auto clampf = [](float v, float lo, float hi) { return std::min(std::max(v, lo), hi); };
@@ -249,16 +251,10 @@ inline ScatterEval principled_evaluate(const Scene &sc, const PrincipledSet &ps,
     return ret;
 }
 
-// Lobe::sample with LobeSet::sample_wi_impl, lobe.cpp:111-119,616-649
-inline BSDFSample principled_sample(const Scene &sc, const PrincipledSet &ps, float3 world_wo, Sampler &sampler) {
-    float uc = sampler.next_1d();
-    (void)sampler.next_2d();                                              // drawn and unused by the reference
-    int strategy = 0;
-    float sum_weights = 0.f;
-    for (int i = 0; i < ps.n; ++i) { strategy = uc > sum_weights ? i : strategy; sum_weights += ps.s[i].sample_weight; }
-    const SubLobe &l = ps.s[strategy];
-    float3 wo = ps.frame.to_local(world_wo), wi;
-    bool valid = true;
+// sample_wi_local_impl of one sub-lobe (in world space)
+inline float3 sub_sample_wi(const SubLobe &l, const Frame &frame, float3 world_wo, Sampler &sampler, bool &valid) {
+    float3 wo = frame.to_local(world_wo), wi;
+    valid = true;
     switch (l.kind) {
         case SL_SHEEN: {
             float2 u = sampler.next_2d();
@@ -285,9 +281,22 @@ inline BSDFSample principled_sample(const Scene &sc, const PrincipledSet &ps, fl
             valid = same_hemisphere(wo, wi);
         } break;
     }
+    return frame.to_world(wi);
+}
+
+// Lobe::sample with LobeSet::sample_wi_impl, lobe.cpp:111-119,616-649
+inline BSDFSample principled_sample(const Scene &sc, const PrincipledSet &ps, float3 world_wo, Sampler &sampler) {
+    float uc = sampler.next_1d();
+    (void)sampler.next_2d();                                              // drawn and unused by the reference
+    int strategy = 0;
+    float sum_weights = 0.f;
+    for (int i = 0; i < ps.n; ++i) { strategy = uc > sum_weights ? i : strategy; sum_weights += ps.s[i].sample_weight; }
+    bool valid = true;
     BSDFSample bs;
-    bs.wi = ps.frame.to_world(wi);
+    bs.wi = sub_sample_wi(ps.s[strategy], ps.frame, world_wo, sampler, valid);
     bs.eval = principled_evaluate(sc, ps, world_wo, bs.wi, &bs.eta);
     if (!valid) bs.eval.pdf *= 0.f;
     return bs;
 }
+
+

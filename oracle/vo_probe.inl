@@ -41,7 +41,9 @@ void vo_probe_bsdf_eval(void *scene, uint32_t mat_id, const float *wo, const flo
     const vo::Scene &sc = *(const vo::Scene *)scene;
     vo::Interaction it = probe_interaction(mat_id, wo);
     vo::ScatterEval se;
-    if (sc.materials[mat_id].type == VB_MAT_PRINCIPLED) se = vo::PrincipledEvaluator{vo::principled_create(sc, vo::Swl{}, it), it.ng}.evaluate(sc, it.wo, {wi[0], wi[1], wi[2]});
+    const uint32_t mt = sc.materials[mat_id].type;
+    if (mt == VB_MAT_MIX || mt == VB_MAT_ADD) se = vo::MixEvaluator{vo::mixset_create(sc, vo::Swl{}, it), it.ng}.evaluate(sc, it.wo, {wi[0], wi[1], wi[2]});
+    else if (sc.materials[mat_id].type == VB_MAT_PRINCIPLED) se = vo::PrincipledEvaluator{vo::principled_create(sc, vo::Swl{}, it), it.ng}.evaluate(sc, it.wo, {wi[0], wi[1], wi[2]});
     else se = vo::Evaluator{vo::create_lobe(sc, vo::Swl{}, it), it.ng}.evaluate(sc, it.wo, {wi[0], wi[1], wi[2]});
     out[0] = se.f.x; out[1] = se.f.y; out[2] = se.f.z; out[3] = se.pdf; out[4] = (float)se.flags;
 }
@@ -50,11 +52,13 @@ void vo_probe_bsdf_sample(void *scene, uint32_t mat_id, const float *wo, uint32_
     const vo::Scene &sc = *(const vo::Scene *)scene;
     vo::Interaction it = probe_interaction(mat_id, wo);
     const bool principled = sc.materials[mat_id].type == VB_MAT_PRINCIPLED;
-    vo::Evaluator ev{principled ? vo::Lobe{} : vo::create_lobe(sc, vo::Swl{}, it), it.ng};
+    vo::Evaluator ev{(principled || sc.materials[mat_id].type >= VB_MAT_MIX) ? vo::Lobe{} : vo::create_lobe(sc, vo::Swl{}, it), it.ng};
     vo::PrincipledEvaluator pev{principled ? vo::principled_create(sc, vo::Swl{}, it) : vo::PrincipledSet{}, it.ng};
+    const bool lobe_set = sc.materials[mat_id].type == VB_MAT_MIX || sc.materials[mat_id].type == VB_MAT_ADD;
+    vo::MixEvaluator mev{lobe_set ? vo::mixset_create(sc, vo::Swl{}, it) : vo::MixSet{}, it.ng};
     vo::Sampler sampler; sampler.state = state;
     for (uint32_t k = 0; k < n; ++k) {
-        vo::BSDFSample bs = principled ? pev.sample(sc, it.wo, sampler) : ev.sample(sc, it.wo, sampler);
+        vo::BSDFSample bs = lobe_set ? mev.sample(sc, it.wo, sampler) : principled ? pev.sample(sc, it.wo, sampler) : ev.sample(sc, it.wo, sampler);
         float *o = out + 8 * (size_t)k;
         o[0] = bs.wi.x; o[1] = bs.wi.y; o[2] = bs.wi.z; o[3] = bs.eval.f.x; o[4] = bs.eval.f.y; o[5] = bs.eval.f.z;
         o[6] = bs.eval.pdf; o[7] = bs.eta;

@@ -393,7 +393,9 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
             aov[15] = 1.f;
             if (it.mat_id != VB_INVALID_ID) {
                 float cos_theta = dot(it.shading.z, it.wo);          // MaterialEvaluator::albedo, material.cpp:91-98
-                float3 a = materials[it.mat_id].type == VB_MAT_PRINCIPLED ? principled_albedo(*this, principled_create(*this, gw, it), cos_theta)
+                const uint32_t mt = materials[it.mat_id].type;
+                float3 a = (mt == VB_MAT_MIX || mt == VB_MAT_ADD) ? mixset_albedo(*this, mixset_create(*this, gw, it), cos_theta)
+                           : mt == VB_MAT_PRINCIPLED ? principled_albedo(*this, principled_create(*this, gw, it), cos_theta)
                                                                           : lobe_albedo(create_lobe(*this, gw, it), cos_theta);
                 a = spec_to_srgb(*this, gw, a);
                 aov[4] = a.x; aov[5] = a.y; aov[6] = a.z;
@@ -497,6 +499,10 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
             float f = phase_HG(dot(it.wo, wi), it.g);
             se.f = float3{f, f, f}; se.pdf = f; se.flags = 0;
             bs = phase_sample(it.g, it.wo, sampler);
+        } else if (materials[it.mat_id].type == VB_MAT_MIX || materials[it.mat_id].type == VB_MAT_ADD) {
+            MixEvaluator evaluator{mixset_create(*this, swl, it), it.ng};
+            se = evaluator.evaluate(*this, it.wo, wi);
+            bs = evaluator.sample(*this, it.wo, sampler);
         } else if (materials[it.mat_id].type == VB_MAT_PRINCIPLED) {
             PrincipledEvaluator evaluator{principled_create(*this, swl, it), it.ng};
             se = evaluator.evaluate(*this, it.wo, wi);

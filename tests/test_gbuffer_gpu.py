@@ -12,7 +12,7 @@ ROOT = Path(__file__).resolve().parent.parent
 
 
 @pytest.mark.parametrize("name,ov", [("cbox_matte", {}), ("cbox_materials", {}), ("cbox_principled", {}), ("cbox_lights", {}),
-                                     ("cbox_dispersion", {}), ("cbox_principled", {"spectrum": "hero"})])
+                                     ("cbox_dispersion", {}), ("cbox_principled", {"spectrum": "hero"}), ("cbox_lobesets", {})])
 def test_gbuffer_matches_oracle(vbctx, oracle, name, ov):
     import oracle_lib
     sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / f"{name}.json", dict(ov, resolution=[160, 160], spp=1))

@@ -55,7 +55,7 @@ def test_host_records_equal_python_twin():
     assert any("denoiser" in s or "ignored" in s for s in hp.log()) or True
 
 
-@pytest.mark.parametrize("name", ["cbox_materials", "cbox_fog", "cbox_principled", "cbox_dispersion"])
+@pytest.mark.parametrize("name", ["cbox_materials", "cbox_fog", "cbox_principled", "cbox_dispersion", "cbox_lobesets"])
 def test_host_records_equal_python_twin_materials_and_mediums(name):
     """mirror / glass / metal / substrate plugins, homogeneous medium, per-shape and global medium ids, LUT loading"""
     path = ROOT / "scenes" / "cbox" / f"{name}.json"
@@ -84,6 +84,13 @@ def test_host_records_equal_python_twin_materials_and_mediums(name):
         assert a.params.spectrum == capi.VB_SPECTRUM_HERO and len(a.spds) == 7 and [len(s) for s in a.spds[:5]] == [94] * 5
         assert abs(a.spectrum.cie_y_integral - 106.857) < 0.01          # integral of the CIE 1931 y-bar, 360..830 nm
         assert "vision-spectrum-hero#constructor" in host_api.plugin_names()
+    if name == "cbox_lobesets":          # plastic, metallic, mix x 2, add: five scene materials + six child records appended after them
+        T = capi
+        assert [m.type for m in a.materials][3:8] == [T.VB_MAT_PLASTIC, T.VB_MAT_METALLIC, T.VB_MAT_MIX, T.VB_MAT_MIX, T.VB_MAT_ADD]
+        assert [list(m.spd) for m in a.materials[5:8]] == [[8, 9], [10, 11], [12, 13]] and len(a.materials) == 14
+        assert abs(a.materials[5].sigma.value[0] - 0.35) < 1e-7 and len(a.textures) == 1
+        for want in ("plastic", "metallic", "mix", "add"):
+            assert f"vision-material-{want}#constructor" in host_api.plugin_names()
     if name == "cbox_fog":
         assert a.params.process_mediums == 1 and a.camera.medium_id == 1 and len(a.mediums) == 2
         assert a.instances[5]["inside_medium"] == 0 and a.instances[5]["outside_medium"] == 1 and a.instances[0]["inside_medium"] == 1
@@ -202,7 +209,8 @@ def test_desc_defaults_and_errors(tmp_path):
 @pytest.mark.gpu
 @pytest.mark.parametrize("SCENE", [SCENE, ROOT / "scenes" / "cbox" / "cbox_materials.json", ROOT / "scenes" / "cbox" / "cbox_fog.json",
                                    ROOT / "scenes" / "cbox" / "cbox_lights.json", ROOT / "scenes" / "cbox" / "cbox_sphere.json",
-                                   ROOT / "scenes" / "cbox" / "cbox_principled.json", ROOT / "scenes" / "cbox" / "cbox_dispersion.json"])
+                                   ROOT / "scenes" / "cbox" / "cbox_principled.json", ROOT / "scenes" / "cbox" / "cbox_dispersion.json",
+                                   ROOT / "scenes" / "cbox" / "cbox_lobesets.json"])
 def test_host_pipeline_renders_like_python_path(vbctx, SCENE):
     hp = host_api.HostPipeline(SCENE)
     hp.prepare(0)

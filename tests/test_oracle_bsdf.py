@@ -197,3 +197,99 @@ def test_principled_lobe_set_energy_and_consistency(lib, oracle):
     # sheen cloth (third principled material): brighter at grazing view than at normal incidence in the sheen tint
     sheen = mids[2]
     assert sc.materials[sheen].params[2] == 1.0
+
+
+# ---- plastic, metallic, and the LobeSet materials mix / add ------------------------------------------------------
+def _lobeset_scene(oracle, tmp_path, materials):
+    """cbox_matte with `materials` appended and assigned to successive shapes (so none is dropped as unused); returns name -> record index"""
+    import json
+    import shutil
+    import oracle_lib
+    d = scene_py.load_json_with_comments(ROOT / "scenes" / "cbox" / "cbox_matte.json")
+    d["materials"] += materials
+    for m, s in zip(materials, d["shapes"]):
+        s["param"]["material"] = m["name"]
+    p = tmp_path / "s.json"
+    p.write_text(json.dumps(d))
+    shutil.copy(ROOT / "scenes" / "cbox" / "checker.jpg", tmp_path / "checker.jpg")
+    sc = scene_py.build_scene(p, {"resolution": [8, 8], "spp": 1})
+    order = [s["param"]["material"] for s in d["shapes"]]
+    listed = [m["name"] for m in d["materials"]]
+    used = [n for n in listed if n in order]          # remove_unused_materials keeps the file's list order
+    return sc, oracle_lib.OracleScene(oracle, sc, threads=1), {n: i for i, n in enumerate(used)}
+
+
+def _eval(lib, osc, mid, wo, wi):
+    ev = np.zeros(5, f32)
+    lib.vo_probe_bsdf_eval(osc.h, mid, _p(np.asarray(wo, f32)), _p(np.asarray(wi, f32)), _p(ev))
+    return ev
+
+
+def test_plastic_and_metallic_known_answers(lib, oracle, tmp_path):
+    mats = [{"type": "plastic", "name": "pl", "param": {"color": [0.2, 0.4, 0.8], "spec": [1, 1, 1], "ior": 1.5, "roughness": 0.3}},
+            {"type": "metallic", "name": "me", "param": {"color": [0.9, 0.6, 0.5], "edge_tint": [1, 1, 1], "roughness": 0.25}}]
+    sc, osc, idx = _lobeset_scene(oracle, tmp_path, mats)
+    assert sc.materials[idx["pl"]].type == capi.VB_MAT_PLASTIC and sc.materials[idx["me"]].type == capi.VB_MAT_METALLIC
+    # plastic at normal incidence, wi = wo = n: wh = n, F = F0 = ((1.5 - 1) / 2.5)^2 = 0.04 (spec = 1); alpha = clamp((r^2)^2) = 0.0081:
+    # f cos = [Rd / pi (1 - F) + F D G / 4] with D = 1 / (pi alpha^2), G = 1; pdf = lerp(F, 1 / pi, D G1 / 4) (plastic.cpp:37-50)
+    n = [0, 0, 1]
+    ev = _eval(lib, osc, idx["pl"], n, n)
+    a = (0.3 ** 2) ** 2
+    D = 1 / (np.pi * a * a)
+    F = 0.04
+    want = np.array([0.2, 0.4, 0.8]) / np.pi * (1 - F) + F * D / 4
+    np.testing.assert_allclose(ev[:3], want, rtol=2e-5)
+    np.testing.assert_allclose(ev[3], (1 - F) / np.pi + F * D / 4, rtol=2e-5)
+    # metallic (F82 tint, edge_tint = 1 -> B = 0): at normal incidence F = F0 = color, f cos = color * F0 * D / 4 / compensation
+    ev = _eval(lib, osc, idx["me"], n, n)
+    assert ev[0] > ev[1] > ev[2] > 0 and abs(ev[1] / ev[0] - (0.6 / 0.9) ** 2) < 1e-3            # colour enters twice (kr and F0)
+    # sampled directions agree with evaluate, and the Monte-Carlo albedo stays <= 1
+    for name, hi in (("pl", 1.02), ("me", 1.02)):
+        for wo in ([0, 0, 1], [0.6, 0, 0.8]):
+            wo = np.array(wo, f32)
+            out = np.zeros((20000, 8), f32)
+            lib.vo_probe_bsdf_sample(osc.h, idx[name], _p(wo), 99, len(out), _p(out))
+            ok = out[:, 6] > 0
+            assert ok.mean() > 0.5
+            albedo = (out[ok, 3:6] / out[ok, 6:7]).sum(axis=0) / len(out)
+            assert np.isfinite(albedo).all() and (albedo <= hi).all(), (name, wo, albedo)
+            for k in np.flatnonzero(ok)[:40]:
+                ev = _eval(lib, osc, idx[name], wo, out[k, 0:3].copy())
+                np.testing.assert_allclose(ev[:3], out[k, 3:6], rtol=2e-3, atol=1e-6)
+                np.testing.assert_allclose(ev[3], out[k, 6], rtol=2e-3)
+
+
+def test_mix_and_add_are_the_weighted_lobe_sets_of_their_children(lib, oracle, tmp_path):
+    """LobeSet::create_mix / create_add + flatten (lobe.cpp:495-562): evaluate = sum_i weight_i f_i, pdf = sum_i sample_weight_i pdf_i over
+    the children's lobes; mix weights (1 - frac, frac) for both; add: weights 1, sample weights 1/2; a principled child's sub-lobes keep
+    their own weights times the parent's sample weight"""
+    diffuse = {"type": "diffuse", "name": "d", "param": {"color": [0.5, 0.3, 0.2]}}
+    mirror = {"type": "mirror", "name": "m", "param": {"color": [0.9, 0.9, 0.9], "roughness": 0.4}}
+    pr = {"type": "principled_bsdf", "name": "pr", "param": {"color": [0.8, 0.5, 0.3], "roughness": 0.3, "metallic": 0.4, "coat_weight": 0.5, "sheen_weight": 0.3}}
+    mats = [dict(diffuse, name="d_alone"), dict(mirror, name="m_alone"), dict(pr, name="pr_alone"),
+            {"type": "mix", "name": "mix", "param": {"frac": 0.25, "mat0": diffuse, "mat1": mirror}},
+            {"type": "add", "name": "add", "param": {"mat0": diffuse, "mat1": mirror}},
+            {"type": "mix", "name": "mixp", "param": {"frac": 0.7, "mat0": diffuse, "mat1": pr}}]
+    sc, osc, idx = _lobeset_scene(oracle, tmp_path, mats)
+    assert sc.materials[idx["mix"]].type == capi.VB_MAT_MIX and sc.materials[idx["add"]].type == capi.VB_MAT_ADD
+    assert len(sc.materials) == len(idx) + 6                      # six child records appended
+    for wo, wi in (([0, 0, 1], [0.3, 0.2, 0.9327379]), ([0.6, 0, 0.8], [-0.5, 0.1, 0.8602325]), ([0.1, -0.7, 0.7071068], [0.2, 0.6, 0.7745967])):
+        d, m, p = (_eval(lib, osc, idx[k], wo, wi) for k in ("d_alone", "m_alone", "pr_alone"))
+        mix, add, mixp = (_eval(lib, osc, idx[k], wo, wi) for k in ("mix", "add", "mixp"))
+        np.testing.assert_allclose(mix[:4], 0.75 * d[:4] + 0.25 * m[:4], rtol=1e-5)
+        np.testing.assert_allclose(add[:3], d[:3] + m[:3], rtol=1e-5)
+        np.testing.assert_allclose(add[3], 0.5 * (d[3] + m[3]), rtol=1e-5)
+        np.testing.assert_allclose(mixp[:4], 0.3 * d[:4] + 0.7 * p[:4], rtol=1e-5)
+    # sampling: pdf of the sampled direction is the set's pdf there; both children get chosen; albedo bounded
+    wo = np.array([0.4, 0.1, 0.9110434], f32)
+    for name in ("mix", "add", "mixp"):
+        out = np.zeros((20000, 8), f32)
+        lib.vo_probe_bsdf_sample(osc.h, idx[name], _p(wo), 321, len(out), _p(out))
+        ok = out[:, 6] > 0
+        assert ok.mean() > 0.6
+        albedo = (out[ok, 3:6] / out[ok, 6:7]).sum(axis=0) / len(out)
+        assert np.isfinite(albedo).all() and (albedo <= (2.02 if name == "add" else 1.02)).all(), (name, albedo)
+        for k in np.flatnonzero(ok)[:40]:
+            ev = _eval(lib, osc, idx[name], wo, out[k, 0:3].copy())
+            np.testing.assert_allclose(ev[:3], out[k, 3:6], rtol=2e-3, atol=1e-6)
+            np.testing.assert_allclose(ev[3], out[k, 6], rtol=2e-3)

@@ -22,7 +22,7 @@ def rel_mse(a, b):
     return float(np.mean((a - b) ** 2 / (b ** 2 + 1e-2)))
 
 
-@pytest.mark.parametrize("name,min_mean", [("cbox_materials", 0.05), ("cbox_fog", 0.005)])
+@pytest.mark.parametrize("name,min_mean", [("cbox_materials", 0.05), ("cbox_fog", 0.005), ("cbox_lobesets", 0.03)])
 def test_image_matches_oracle(vbctx, oracle, name, min_mean):
     import oracle_lib
     sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / f"{name}.json", {"resolution": [160, 160], "spp": 8})

@@ -20,7 +20,7 @@ def rel_mse(a, b):
     return float(np.mean((a - b) ** 2 / (b ** 2 + 1e-2)))
 
 
-@pytest.mark.parametrize("name", ["cbox_dispersion", "cbox_matte", "cbox_fog", "cbox_lights", "cbox_principled"])
+@pytest.mark.parametrize("name", ["cbox_dispersion", "cbox_matte", "cbox_fog", "cbox_lights", "cbox_principled", "cbox_lobesets"])
 def test_hero_image_matches_oracle(vbctx, oracle, name):
     import oracle_lib
     sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / f"{name}.json", {"resolution": [128, 128], "spp": 8, "spectrum": "hero"})

@@ -124,3 +124,27 @@ ds["spectrum"] = {"type": "hero", "param": {"dimension": 3}}
 ds["integrator"]["param"]["max_depth"] = 16
 (root / "cbox_dispersion.json").write_text(json.dumps(ds, indent=1))
 print("wrote", root / "cbox_dispersion.json", root / "cbox_projector.json", root / "cbox_materials.json", root / "cbox_fog.json", root / "cbox_lights.json", root / "cbox_sphere.json", root / "cbox_principled.json")
+
+# cbox_lobesets.json: plastic and metallic single-lobe materials, and the two LobeSet materials over child
+# materials - mix (diffuse + mirror; glass + principled with every lobe switched on) and add (diffuse + metallic). Parameter blocks
+# follow the reference's res/render_scene/cbox/cbox.json ("plastic", "metallic", "mix", "mix2").
+g = copy.deepcopy(base)
+principled = {"type": "principled_bsdf", "name": "pr", "param": {"color": [0.8, 0.5, 0.3], "ior": 1.5, "roughness": 0.3, "metallic": 0.4, "spec_tint": [1, 0.9, 0.8],
+              "sheen_weight": 0.5, "sheen_roughness": 0.4, "sheen_tint": [0.9, 0.9, 1], "coat_weight": 0.6, "coat_roughness": 0.1, "coat_ior": 1.6,
+              "coat_tint": [1, 1, 1], "transmission_weight": 0.3}}
+g["materials"] += [
+    {"type": "plastic", "name": "plastic", "param": {"color": [0.2, 0.4, 0.8], "spec": [0.9, 0.9, 0.9], "ior": 1.5, "roughness": 0.3}},
+    {"type": "metallic", "name": "metallic", "param": {"color": [0.95, 0.64, 0.54], "edge_tint": [0.98, 0.82, 0.76], "roughness": 0.25, "anisotropic": 0.3}},
+    {"type": "mix", "name": "mix_dm", "param": {"frac": 0.35,
+        "mat0": {"type": "diffuse", "name": "d0", "param": {"color": {"channels": "xyz", "node": {"type": "image", "param": {"fn": "checker.jpg", "color_space": "srgb"}}}}},
+        "mat1": {"type": "mirror", "name": "m1", "param": {"color": [0.9, 0.9, 0.9], "roughness": 0.1}}}},
+    {"type": "mix", "name": "mix_gp", "param": {"frac": 0.6,
+        "mat0": {"type": "glass", "name": "g0", "param": {"material_name": "BK7", "color": [1, 1, 1], "roughness": 0.05}},
+        "mat1": principled}},
+    {"type": "add", "name": "add_dm", "param": {
+        "mat0": {"type": "diffuse", "name": "d2", "param": {"color": [0.3, 0.3, 0.3]}},
+        "mat1": {"type": "metallic", "name": "m2", "param": {"color": [0.6, 0.6, 0.2], "edge_tint": [1, 1, 1], "roughness": 0.4}}}},
+]
+assign(g, {"shape_5": "mix_gp", "shape_6": "mix_dm", "shape_0": "plastic", "shape_4": "metallic", "shape_2": "add_dm"})
+g["integrator"]["param"]["max_depth"] = 8
+(root / "cbox_lobesets.json").write_text(json.dumps(g, indent=1))

@@ -9,8 +9,8 @@ struct Lobe {
     uint32_t type;
     Frame3 frame;              // Material::compute_shading_frame without a normal map
     f3 kr;                     // diffuse Kr | mirror kr | glass kt | substrate Rd
-    f3 rs;                     // substrate Rs | metal eta
-    f3 kk;                     // metal k
+    f3 rs;                     // substrate Rs | metal eta | plastic / metallic Fresnel F0
+    f3 kk;                     // metal k | metallic F82-tint B
     GGX mf;
     float eta;                 // glass: corrected relative ior (Interaction::correct_eta); dispersive: of the hero wavelength (eta[0])
     f3 eta3;                   // dispersive glass (hero spectrum, ior slot = "spd", glass.cpp:221-234): corrected ior per wavelength
@@ -18,8 +18,26 @@ struct Lobe {
     bool oren_nayar; float on_A, on_B;
 };
 
+// FresnelSchlick::evaluate (fresnel.h:44-52) and FresnelF82Tint::evaluate (fresnel.h:118-124) over plain colour triples
+__device__ __forceinline__ f3 fresnel_schlick3(f3 F0, float eta, float cos_theta) {
+    float F_real = fresnel_dielectric(cos_theta, eta);
+    float F0_real = sqr((eta - 1.0f) / (eta + 1.0f));
+    float t = (F_real - F0_real) / (1.f - F0_real);
+    t = fmin_(fmax_(t, 0.f), 1.f);
+    return {lerp(t, F0.x, 1.f), lerp(t, F0.y, 1.f), lerp(t, F0.z, 1.f)};
+}
+__device__ __forceinline__ f3 fresnel_f82(f3 F0, f3 B, float cos_theta) {
+    float mu = fmin_(fmax_(1.f - cos_theta, 0.f), 1.f);
+    float mu5 = pow5(mu);
+    f3 f_schlick{lerp(mu5, F0.x, 1.f), lerp(mu5, F0.y, 1.f), lerp(mu5, F0.z, 1.f)};
+    f3 r = f_schlick - B * cos_theta * mu5 * mu;
+    return {fmin_(fmax_(r.x, 0.f), 1.f), fmin_(fmax_(r.y, 0.f), 1.f), fmin_(fmax_(r.z, 0.f), 1.f)};
+}
+
 __device__ f3 lobe_fresnel(const Lobe &lb, float cos_theta) {
     switch (lb.type) {
+        case VB_MAT_PLASTIC: return fresnel_schlick3(lb.rs, lb.eta, cos_theta);
+        case VB_MAT_METALLIC: return fresnel_f82(lb.rs, lb.kk, cos_theta);
         case VB_MAT_METAL: return {fresnel_complex(cos_theta, lb.rs.x, lb.kk.x), fresnel_complex(cos_theta, lb.rs.y, lb.kk.y),
                                    fresnel_complex(cos_theta, lb.rs.z, lb.kk.z)};
         case VB_MAT_GLASS: return splat(fresnel_dielectric(cos_theta, lb.eta));
@@ -137,14 +155,27 @@ __device__ ScatterEval diffuse_evaluate_local(const Lobe &lb, f3 wo, f3 wi) {
     return se;
 }
 
+// -- PlasticLobe::evaluate_local_impl, plastic.cpp:37-50 (no hemisphere test of its own; flags stay at the ScatterEval default) --
+__device__ ScatterEval plastic_evaluate_local(const Lobe &lb, f3 wo, f3 wi) {
+    ScatterEval se;
+    f3 wh = normalize(wo + wi);
+    f3 F = lobe_fresnel(lb, abs_dot(wh, wo));
+    se.f = lb.kr * InvPi * (splat(1.f) - F);
+    se.f = se.f + F * ggx_brdf_div_fr(lb.mf, wo, wh, wi);
+    se.pdf = lerp(average3(F), fabsf(wi.z) * InvPi, ggx_pdf_wi_reflection(lb.mf, wo, wh));
+    se.flags = 1u;
+    return se;
+}
+
 // Lobe::evaluate_impl (lobe.cpp:53-77): world -> local, f *= |cos(wi)|
 __device__ __forceinline__ ScatterEval lobe_evaluate(const PtScene &S, const Lobe &lb, f3 world_wo, f3 world_wi, bool with_eta, float *eta_out) {
     f3 wo = lb.frame.to_local(world_wo), wi = lb.frame.to_local(world_wi);
     ScatterEval se;
     switch (lb.type) {
         case VB_MAT_GLASS: se = dielectric_evaluate_local(S, lb, wo, wi, with_eta, eta_out); break;
-        case VB_MAT_MIRROR: case VB_MAT_METAL: se = microfacet_refl_evaluate_local(S, lb, wo, wi); break;
+        case VB_MAT_MIRROR: case VB_MAT_METAL: case VB_MAT_METALLIC: se = microfacet_refl_evaluate_local(S, lb, wo, wi); break;
         case VB_MAT_SUBSTRATE: se = fresnel_blend_evaluate_local(lb, wo, wi); break;
+        case VB_MAT_PLASTIC: se = plastic_evaluate_local(lb, wo, wi); break;
         default: se = diffuse_evaluate_local(lb, wo, wi); break;
     }
     se.f = se.f * fabsf(wi.z);
@@ -161,10 +192,11 @@ __device__ __forceinline__ f3 cosine_hemisphere(f2 u, float woz) {
 }
 
 // Lobe::sample (lobe.cpp:111-119) with each lobe's sample_wi_local_impl; draws in the reference's order
-__device__ __forceinline__ BSDFSample lobe_sample(const PtScene &S, const Lobe &lb, f3 world_wo, Sampler &sampler) {
+// the direction only (sample_wi_local_impl of the lobe, in world space); `valid` = SampledDirection::valid
+__device__ __forceinline__ f3 lobe_sample_wi(const Lobe &lb, f3 world_wo, Sampler &sampler, bool &valid) {
     f3 wo = lb.frame.to_local(world_wo);
     f3 wi;
-    bool valid = true;
+    valid = true;
     switch (lb.type) {
         case VB_MAT_GLASS: {
             f3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
@@ -179,7 +211,16 @@ __device__ __forceinline__ BSDFSample lobe_sample(const PtScene &S, const Lobe &
                 valid = ok && !same_hemisphere(wo, wi);
             }
         } break;
-        case VB_MAT_MIRROR: case VB_MAT_METAL: {
+        case VB_MAT_PLASTIC: {                                         // plastic.cpp:52-66
+            f3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
+            f3 F = lobe_fresnel(lb, fabsf(wo.z));
+            float uc = sampler.next_1d();
+            if (uc < average3(F)) {
+                wi = reflect(wo, wh);
+                valid = same_hemisphere(wo, wi);
+            } else wi = cosine_hemisphere(sampler.next_2d(), 1.f);     // square_to_cosine_hemisphere: always the +z side
+        } break;
+        case VB_MAT_MIRROR: case VB_MAT_METAL: case VB_MAT_METALLIC: {
             f3 wh = ggx_sample_wh(lb.mf, wo, sampler.next_2d());
             wi = reflect(wo, wh);
             valid = same_hemisphere(wo, wi);
@@ -198,9 +239,13 @@ __device__ __forceinline__ BSDFSample lobe_sample(const PtScene &S, const Lobe &
         } break;
         default: wi = cosine_hemisphere(sampler.next_2d(), wo.z); break;
     }
+    return lb.frame.to_world(wi);
+}
+__device__ __forceinline__ BSDFSample lobe_sample(const PtScene &S, const Lobe &lb, f3 world_wo, Sampler &sampler) {
+    bool valid = true;
     BSDFSample bs;
     bs.eta = 1.f;
-    bs.wi = lb.frame.to_world(wi);
+    bs.wi = lobe_sample_wi(lb, world_wo, sampler, valid);
     bs.eval = lobe_evaluate(S, lb, world_wo, bs.wi, true, &bs.eta);
     if (!valid) bs.eval.pdf *= 0.f;
     return bs;
@@ -209,13 +254,16 @@ __device__ __forceinline__ BSDFSample lobe_sample(const PtScene &S, const Lobe &
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fmin_(fmax_(v, lo), hi); }
 
 // a colour slot of the hit's material as an albedo spectrum (eval_albedo_spectrum, shader_node.cpp:317-321)
+__device__ __forceinline__ f3 material_color_of(const PtScene &S, const Swl *swl, const vb_slot &slot, const Interaction &it, uint32_t mat_id, uint32_t which) {
+    return spec_albedo_c(S.spec, swl, eval_slot3(S, slot, it.uv), slot.tex_id == VB_INVALID_ID, 4u * mat_id + which);
+}
 __device__ __forceinline__ f3 material_color(const PtScene &S, const Swl *swl, const vb_slot &slot, const Interaction &it, uint32_t which) {
-    return spec_albedo_c(S.spec, swl, eval_slot3(S, slot, it.uv), slot.tex_id == VB_INVALID_ID, 4u * it.mat_id + which);
+    return material_color_of(S, swl, slot, it, it.mat_id, which);
 }
 
 // Material::create_evaluator -> create_lobe_set of the plugin
-__device__ __forceinline__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction &it) {
-    const vb_material_rec &m = S.materials[it.mat_id];
+__device__ __forceinline__ Lobe create_lobe_of(const PtScene &S, const Swl *swl, const Interaction &it, const uint32_t mat_id) {
+    const vb_material_rec &m = S.materials[mat_id];
     Lobe lb;
     lb.type = m.type;
     lb.frame = it.shading;
@@ -225,7 +273,7 @@ __device__ __forceinline__ Lobe create_lobe(const PtScene &S, const Swl *swl, co
     float anis = clampf(m.params[0], -0.9f, 0.9f);
     switch (m.type) {
         case VB_MAT_DIFFUSE:
-            lb.kr = material_color(S, swl, m.color, it, SC_COLOR);
+            lb.kr = material_color_of(S, swl, m.color, it, mat_id, SC_COLOR);
             if (m.flags & 1u) {
                 float sigma = eval_slot3(S, m.sigma, it.uv).x * PiOver2;
                 float sigma2 = sqr(sigma * sigma);
@@ -235,7 +283,7 @@ __device__ __forceinline__ Lobe create_lobe(const PtScene &S, const Swl *swl, co
             }
             break;
         case VB_MAT_MIRROR: case VB_MAT_METAL: {
-            lb.kr = m.type == VB_MAT_MIRROR ? material_color(S, swl, m.color, it, SC_COLOR) : splat(1.f);
+            lb.kr = m.type == VB_MAT_MIRROR ? material_color_of(S, swl, m.color, it, mat_id, SC_COLOR) : splat(1.f);
             float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
@@ -245,7 +293,7 @@ __device__ __forceinline__ Lobe create_lobe(const PtScene &S, const Swl *swl, co
             }
         } break;
         case VB_MAT_GLASS: {
-            lb.kr = material_color(S, swl, m.color, it, SC_COLOR);
+            lb.kr = material_color_of(S, swl, m.color, it, mat_id, SC_COLOR);
             float ior = eval_slot3(S, m.ior, it.uv).x;
             lb.eta = dot(it.wo, it.ng) > 0.f ? ior : 1.0f / ior;
             if ((m.flags & 4u) && swl) {                                 // glass.cpp:216-234: "material_name" curve in an "spd" slot
@@ -260,24 +308,50 @@ __device__ __forceinline__ Lobe create_lobe(const PtScene &S, const Swl *swl, co
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
         } break;
         case VB_MAT_SUBSTRATE: {
-            lb.kr = material_color(S, swl, m.color, it, SC_COLOR);
-            lb.rs = material_color(S, swl, m.spec, it, SC_SPEC);
+            lb.kr = material_color_of(S, swl, m.color, it, mat_id, SC_COLOR);
+            lb.rs = material_color_of(S, swl, m.spec, it, mat_id, SC_SPEC);
             float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
             r = remap ? sqr(r) : r;
             calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
             if (remap) { lb.mf.ax = sqr(lb.mf.ax); lb.mf.ay = sqr(lb.mf.ay); }
             lb.mf.ax = clampf(lb.mf.ax, 0.0001f, 1.f); lb.mf.ay = clampf(lb.mf.ay, 0.0001f, 1.f);
         } break;
+        case VB_MAT_PLASTIC: {                                         // plastic.cpp:109-129
+            lb.kr = material_color_of(S, swl, m.color, it, mat_id, SC_COLOR);
+            f3 Rs = material_color_of(S, swl, m.spec, it, mat_id, SC_SPEC);
+            float ior = eval_slot3(S, m.ior, it.uv).x;
+            float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
+            r = remap ? sqr(r) : r;
+            calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
+            if (remap) { lb.mf.ax = sqr(lb.mf.ax); lb.mf.ay = sqr(lb.mf.ay); }
+            lb.mf.ax = clampf(lb.mf.ax, 0.0001f, 1.f); lb.mf.ay = clampf(lb.mf.ay, 0.0001f, 1.f);
+            lb.eta = ior;
+            lb.rs = Rs * sqr((ior - 1.0f) / (ior + 1.0f));             // schlick_F0_from_ior(iors[0]) * Rs
+        } break;
+        case VB_MAT_METALLIC: {                                        // metallic.cpp:44-60
+            lb.kr = material_color_of(S, swl, m.color, it, mat_id, SC_COLOR);
+            f3 edge_tint = material_color_of(S, swl, m.spec, it, mat_id, SC_SPEC);
+            float r = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.01f, 1.f);
+            r = remap ? sqr(r) : r;
+            calculate_alpha(r, anis, lb.mf.ax, lb.mf.ay);
+            lb.rs = lb.kr;                                             // FresnelF82Tint(color) + init_from_F82(edge_tint), fresnel.h:110-116
+            const float f = 6.f / 7.f, f5 = ((f * f) * (f * f)) * f;
+            f3 f_schlick{lerp(f5, lb.rs.x, 1.f), lerp(f5, lb.rs.y, 1.f), lerp(f5, lb.rs.z, 1.f)};
+            lb.kk = f_schlick * (7.f / (f5 * f)) * (splat(1.f) - edge_tint);
+        } break;
         default: break;
     }
     return lb;
 }
+__device__ __forceinline__ Lobe create_lobe(const PtScene &S, const Swl *swl, const Interaction &it) { return create_lobe_of(S, swl, it, it.mat_id); }
+
 
 // Lobe::albedo(cos_theta) of the single-lobe materials (lobe.h:167, lobe.cpp:208-210,308-313, substrate.cpp:22): rt_geom's albedo plane
 __device__ __forceinline__ f3 lobe_albedo(const Lobe &lb, float cos_theta) {
     switch (lb.type) {
         case VB_MAT_DIFFUSE: case VB_MAT_SUBSTRATE: return lb.kr;
-        case VB_MAT_MIRROR: case VB_MAT_METAL: return lb.kr * lobe_fresnel(lb, cos_theta);
+        case VB_MAT_MIRROR: case VB_MAT_METAL: case VB_MAT_METALLIC: return lb.kr * lobe_fresnel(lb, cos_theta);
+        case VB_MAT_PLASTIC: return lobe_fresnel(lb, cos_theta);      // MicrofacetLobe::albedo with a unit reflection colour (plastic.cpp:127)
         case VB_MAT_GLASS: { f3 F = dielectric_F(lb, fabsf(cos_theta)); return lb.kr * (splat(1.0f) - F) + F; }
         default: return f3{0, 0, 0};
     }

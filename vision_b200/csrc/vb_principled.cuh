@@ -89,17 +89,17 @@ __device__ f3 layering_weight(f3 layer_albedo, f3 weight) {
     return weight * saturate(1.f - max_comp);
 }
 
-__device__ __forceinline__ PrincipledSet principled_create(const PtScene &S, const Swl *swl, const Interaction &it) {
-    const vb_material_rec &m = S.materials[it.mat_id];
+__device__ __forceinline__ PrincipledSet principled_create_of(const PtScene &S, const Swl *swl, const Interaction &it, const uint32_t mat_id) {
+    const vb_material_rec &m = S.materials[mat_id];
     PrincipledSet ps;
     ps.frame = it.shading;
     auto clampf = [](float v, float lo, float hi) { return fmin_(fmax_(v, lo), hi); };
     const uint32_t switches = (uint32_t)m.params[15];
-    f3 color = material_color(S, swl, m.color, it, SC_COLOR);
+    f3 color = material_color_of(S, swl, m.color, it, mat_id, SC_COLOR);
     float ior = eval_slot3(S, m.ior, it.uv).x;
     float roughness = clampf(eval_slot3(S, m.roughness, it.uv).x, 0.0001f, 1.f);
     float anisotropic = m.params[0];
-    f3 specular_tint = material_color(S, swl, m.spec, it, SC_SPEC);
+    f3 specular_tint = material_color_of(S, swl, m.spec, it, mat_id, SC_SPEC);
     float aspect = __fsqrt_rn(1.f - anisotropic * 0.9f);
     GGX mf{fmax_(0.001f, sqr(roughness) / aspect), fmax_(0.001f, sqr(roughness) * aspect)};
     f3 weight = splat(1.f);
@@ -109,7 +109,7 @@ __device__ __forceinline__ PrincipledSet principled_create(const PtScene &S, con
     if (switches & (1u << SL_SHEEN)) {
         SubLobe l;
         ps.switches |= 1u << SL_SHEEN;
-        f3 sheen_tint = spec_albedo_c(S.spec, swl, f3{m.params[4], m.params[5], m.params[6]}, true, 4u * it.mat_id + SC_SHEEN);
+        f3 sheen_tint = spec_albedo_c(S.spec, swl, f3{m.params[4], m.params[5], m.params[6]}, true, 4u * mat_id + SC_SHEEN);
         float sheen_weight = m.params[2] * front;
         float sheen_roughness = m.params[3];
         l.kr = sheen_tint * sheen_weight * weight;
@@ -128,7 +128,7 @@ __device__ __forceinline__ PrincipledSet principled_create(const PtScene &S, con
         float cc_weight = m.params[7] * front;
         float cc_roughness = sqr(clampf(m.params[8], 0.0001f, 1.f));
         float cc_ior = m.params[9];
-        f3 cc_tint = spec_albedo_c(S.spec, swl, f3{m.params[10], m.params[11], m.params[12]}, true, 4u * it.mat_id + SC_COAT);
+        f3 cc_tint = spec_albedo_c(S.spec, swl, f3{m.params[10], m.params[11], m.params[12]}, true, 4u * mat_id + SC_COAT);
         l.fresnel = FR_DIELECTRIC; l.eta = cc_ior;
         l.mf = GGX{cc_roughness, cc_roughness};
         l.kr = weight * cc_weight * cc_tint;
@@ -189,6 +189,7 @@ __device__ __forceinline__ PrincipledSet principled_create(const PtScene &S, con
     for (int k = 0; k < 6; ++k) if (ps.switches & (1u << k)) ps.sw[k] = ps.sw[k] / sum;
     return ps;
 }
+__device__ __forceinline__ PrincipledSet principled_create(const PtScene &S, const Swl *swl, const Interaction &it) { return principled_create_of(S, swl, it, it.mat_id); }
 
 // SheenLTC (principled_bsdf.cpp:61-117)
 __device__ float sheen_eval_ltc(const SubLobe &l, f3 wi) {
@@ -282,15 +283,8 @@ __device__ __forceinline__ ScatterEval principled_evaluate(const PtScene &S, con
 }
 
 // Lobe::sample with LobeSet::sample_wi_impl, lobe.cpp:111-119,616-649
-// samples the direction only (the caller evaluates the set at it)
-__device__ __forceinline__ f3 principled_sample_wi(const PrincipledSet &ps, f3 world_wo, Sampler &sampler, bool &valid) {
-    float uc = sampler.next_1d();
-    (void)sampler.next_2d();                                              // drawn and unused by the reference
-    int strategy = -1;                                                    // kind of the chosen lobe (the first present one to begin with)
-    float sum_weights = 0.f;
-#pragma unroll
-    for (int k = 0; k < 6; ++k)
-        if (ps.switches & (1u << k)) { strategy = (strategy < 0 || uc > sum_weights) ? k : strategy; sum_weights += ps.sw[k]; }
+// sample_wi_local_impl of the sub-lobe of kind `strategy` (in world space)
+__device__ __forceinline__ f3 principled_sub_wi(const PrincipledSet &ps, int strategy, f3 world_wo, Sampler &sampler, bool &valid) {
     f3 wo = ps.frame.to_local(world_wo), wi{0, 0, 1};
     valid = true;
     switch (strategy) {
@@ -324,6 +318,17 @@ __device__ __forceinline__ f3 principled_sample_wi(const PrincipledSet &ps, f3 w
     }
     return ps.frame.to_world(wi);
 }
+// samples the direction only (the caller evaluates the set at it)
+__device__ __forceinline__ f3 principled_sample_wi(const PrincipledSet &ps, f3 world_wo, Sampler &sampler, bool &valid) {
+    float uc = sampler.next_1d();
+    (void)sampler.next_2d();                                              // drawn and unused by the reference
+    int strategy = -1;                                                    // kind of the chosen lobe (the first present one to begin with)
+    float sum_weights = 0.f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+        if (ps.switches & (1u << k)) { strategy = (strategy < 0 || uc > sum_weights) ? k : strategy; sum_weights += ps.sw[k]; }
+    return principled_sub_wi(ps, strategy, world_wo, sampler, valid);
+}
 
 #ifndef VB_PRINCIPLED_INLINE
 #define VB_PRINCIPLED_INLINE __forceinline__
@@ -348,31 +353,33 @@ __device__ VB_PRINCIPLED_INLINE void principled_shade(const PtScene &S, const Sw
 
 // LobeSet::albedo (lobe.cpp:564-570) over the sub-lobes: sheen = tint (principled_bsdf.cpp:54-56), coat / specular = their albedo
 // tables at cos_theta (:154-161,198-206), metallic = kr F82(cos), transmission = the dielectric form
+__device__ __forceinline__ f3 sub_albedo(const PtScene &S, const SubLobe &l, float cos_theta) {
+    f3 a{0, 0, 0};
+    float rx = __fsqrt_rn(__fsqrt_rn(l.mf.ax * l.mf.ay));
+    switch (l.kind) {
+        case SL_SHEEN: case SL_DIFFUSE: a = l.kr; break;
+        case SL_COAT: {
+            const DevLut &L = S.luts[VB_LUT_COAT];
+            float s = (L.data == nullptr) ? 1.f : lut_sample3d_ch0(L, rx, cos_theta, (l.eta - 1.003f) / (4.f - 1.003f));
+            a = l.kr * s;
+        } break;
+        case SL_METALLIC: a = l.kr * sub_fresnel(l, cos_theta); break;
+        case SL_TRANS: { f3 F = sub_fresnel(l, fabsf(cos_theta)); a = l.kr * (splat(1.0f) - F) + F; } break;
+        case SL_SPEC: {
+            const DevLut &L = S.luts[VB_LUT_SPECULAR];
+            float z = __fsqrt_rn(fabsf((l.eta - 1.0f) / (l.eta + 1.0f)));
+            float s = (L.data == nullptr) ? 1.f : lut_sample3d_ch0(L, rx, cos_theta, z);
+            a = lerp3v(s, l.F0, splat(1.f)) * l.kr;
+        } break;
+    }
+    return a;
+}
 __device__ __noinline__ f3 principled_albedo(const PtScene &S, const Swl *swl, const Interaction &it, float cos_theta) {
     const PrincipledSet ps = principled_create(S, swl, it);
     f3 ret{0, 0, 0};
-    VB_EACH_SUBLOBE(ps, {
-        f3 a{0, 0, 0};
-        float rx = __fsqrt_rn(__fsqrt_rn(l.mf.ax * l.mf.ay));
-        switch (l.kind) {
-            case SL_SHEEN: case SL_DIFFUSE: a = l.kr; break;
-            case SL_COAT: {
-                const DevLut &L = S.luts[VB_LUT_COAT];
-                float s = (L.data == nullptr) ? 1.f : lut_sample3d_ch0(L, rx, cos_theta, (l.eta - 1.003f) / (4.f - 1.003f));
-                a = l.kr * s;
-            } break;
-            case SL_METALLIC: a = l.kr * sub_fresnel(l, cos_theta); break;
-            case SL_TRANS: { f3 F = sub_fresnel(l, fabsf(cos_theta)); a = l.kr * (splat(1.0f) - F) + F; } break;
-            case SL_SPEC: {
-                const DevLut &L = S.luts[VB_LUT_SPECULAR];
-                float z = __fsqrt_rn(fabsf((l.eta - 1.0f) / (l.eta + 1.0f)));
-                float s = (L.data == nullptr) ? 1.f : lut_sample3d_ch0(L, rx, cos_theta, z);
-                a = lerp3v(s, l.F0, splat(1.f)) * l.kr;
-            } break;
-        }
-        ret = ret + a * l.weight;
-    })
+    VB_EACH_SUBLOBE(ps, { ret = ret + sub_albedo(S, l, cos_theta) * l.weight; })
     return ret;
 }
 
 }  // namespace
+#include "vb_mixset.cuh"

@@ -149,6 +149,10 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         float f = phase_HG(dot(it.wo, wi), it.g);
         se.f = f3{f, f, f}; se.pdf = f; se.flags = 0;
         bs = phase_sample(it.g, it.wo, sampler);
+    } else if (PRINCIPLED && (S.materials[it.mat_id].type == VB_MAT_MIX || S.materials[it.mat_id].type == VB_MAT_ADD)) {
+        mixset_shade(S, swl, it, wi, sampler, se, bs);
+        hemisphere_discard(se, it.wo, wi, it.ng);
+        hemisphere_discard(bs.eval, it.wo, bs.wi, it.ng);
     } else if (PRINCIPLED && S.materials[it.mat_id].type == VB_MAT_PRINCIPLED) {
         principled_shade(S, swl, it, wi, sampler, se, bs);
         hemisphere_discard(se, it.wo, wi, it.ng);

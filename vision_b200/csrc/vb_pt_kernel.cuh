@@ -141,7 +141,9 @@ __global__ void __launch_bounds__(PT_BLOCK) k_gbuffer(const __grid_constant__ Pt
         if (it.mat_id != VB_INVALID_ID) {
             float cos_theta = dot(it.shading.z, it.wo);              // MaterialEvaluator::albedo, material.cpp:91-98
             f3 a;
-            if (PRINCIPLED && S.materials[it.mat_id].type == VB_MAT_PRINCIPLED) a = principled_albedo(S, swl, it, cos_theta);
+            const uint32_t mt = S.materials[it.mat_id].type;
+            if (PRINCIPLED && (mt == VB_MAT_MIX || mt == VB_MAT_ADD)) a = mixset_albedo(S, swl, it, cos_theta);
+            else if (PRINCIPLED && mt == VB_MAT_PRINCIPLED) a = principled_albedo(S, swl, it, cos_theta);
             else a = lobe_albedo(create_lobe(S, swl, it), cos_theta);
             a = spec_to_srgb(S.spec, swl, a);
             albedo = make_float4(a.x, a.y, a.z, 1.f);
@@ -336,14 +338,22 @@ int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n) {
     if (n && !mat) return ctx->fail(VB_ERR_INVALID, "vb_materials_set: null argument");
     cudaSetDevice(ctx->device);
     vb_pt_state *p = pt_state(ctx);
-    for (uint32_t i = 0; i < n; ++i)
-        if (mat[i].type > VB_MAT_BLACK_BODY)
-            return ctx->fail(VB_ERR_UNSUPPORTED, "vb_materials_set: material type " + std::to_string(mat[i].type) + " not implemented yet");
+    for (uint32_t i = 0; i < n; ++i) {
+        if (mat[i].type > VB_MAT_ADD)
+            return ctx->fail(VB_ERR_UNSUPPORTED, "vb_materials_set: material type " + std::to_string(mat[i].type) + " is not a known type");
+        if (mat[i].type == VB_MAT_MIX || mat[i].type == VB_MAT_ADD)
+            for (int c = 0; c < 2; ++c) {
+                uint32_t child = mat[i].spd[c];
+                if (child >= n) return ctx->fail(VB_ERR_INVALID, "vb_materials_set: mix / add child index out of range");
+                if (mat[child].type == VB_MAT_MIX || mat[child].type == VB_MAT_ADD)
+                    return ctx->fail(VB_ERR_UNSUPPORTED, "vb_materials_set: a mix / add material nested in another one is not supported (children: single-lobe materials or principled_bsdf)");
+            }
+    }
     cudaFree(p->d_mat); p->d_mat = nullptr; p->n_mat = n;
     uint32_t types = 0;
     for (uint32_t i = 0; i < n; ++i) types |= 1u << mat[i].type;
     p->n_mat_types = (uint32_t)__builtin_popcount(types);
-    p->has_principled = (types >> VB_MAT_PRINCIPLED) & 1u;
+    p->has_principled = (types & ((1u << VB_MAT_PRINCIPLED) | (1u << VB_MAT_MIX) | (1u << VB_MAT_ADD))) != 0;   // the lobe-SET materials: heavy shading launch
     p->h_mat.assign(mat, mat + n);
     p->spec_dirty = true;
     if (n) {

@@ -68,6 +68,17 @@ __global__ void __launch_bounds__(256) k_wf_generate(const __grid_constant__ PtS
     st.c[slot] = make_uint4(ps.sampler.state, ps.ray_medium, ps.bounces, ps.swl);
 }
 
+// 3-bit class of the shading sort key: the lobe-SET materials (principled, mix, add) share class 5 = the heavy launch; class 7 is
+// never used (keys 254 / 255 are "no material" / "miss")
+enum : uint32_t { WF_CLASS_SET = 5u };
+__device__ __forceinline__ uint32_t wf_material_class(uint32_t type) {
+    switch (type) {
+        case VB_MAT_PRINCIPLED: case VB_MAT_MIX: case VB_MAT_ADD: return WF_CLASS_SET;
+        case VB_MAT_PLASTIC: return VB_MAT_SUBSTRATE;
+        case VB_MAT_METALLIC: return VB_MAT_METAL;
+        default: return type & 7u;
+    }
+}
 // shading order: entries with the same material run in the same warps (one 8-bit radix pass over these records)
 __global__ void __launch_bounds__(256) k_wf_material_keys(PtScene S, uint32_t n, const uint4 *__restrict__ hits4, uint64_t *keyidx) {
     uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
@@ -76,7 +87,7 @@ __global__ void __launch_bounds__(256) k_wf_material_keys(PtScene S, uint32_t n,
     uint32_t key = 255u;                                            // miss
     if (inst != VB_INVALID_ID) {
         uint32_t mat = S.instances[inst].mat_id;
-        key = mat == VB_INVALID_ID ? 254u : ((S.materials[mat].type & 7u) << 5) | (mat & 31u);
+        key = mat == VB_INVALID_ID ? 254u : (wf_material_class(S.materials[mat].type) << 5) | (mat & 31u);
     }
     keyidx[q] = ((uint64_t)key << 32) | q;
 }
@@ -108,7 +119,7 @@ __global__ void __launch_bounds__(128, (VARIANT & PT_PRINCIPLED) ? VB_SHADE_MIN_
         q = (uint32_t)o;
         if (filter) {
             uint32_t key = (uint32_t)(o >> 32);
-            bool principled = key < 254u && ((key >> 5) & 7u) == VB_MAT_PRINCIPLED;
+            bool principled = key < 254u && ((key >> 5) & 7u) == WF_CLASS_SET;
             mine = principled == (filter == 2);
         }
     }

@@ -114,6 +114,9 @@ public:
     uint32_t index = VB_INVALID_ID;
     explicit Material(const MaterialDesc &) {}
     virtual void fill_record(vb_material_rec &rec, const SlotContext &ctx) const = 0;
+    // mix / add: the two child materials (mix.cpp:21-23, add.cpp:21-23). Scene::prepare gives them record indices after the scene's own
+    // materials; no instance refers to a child directly.
+    virtual std::vector<std::shared_ptr<Material>> children() const { return {}; }
 };
 
 class Medium : public Node {       // reference src/base/scattering/medium.h:23-50

@@ -324,24 +324,99 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(BlackBodyMaterial, material, black_body, constructor)
 
-// reference src/render_core/material/{mix,add,plastic,metallic,subsurface,multi_layered}.cpp: scene files may DEFINE these (the stock
-// cbox/vision_scene.json defines an unused "mix"); Scene::load_materials constructs every listed material and
-// remove_unused_materials (scene.cpp:79-91) drops the unused ones. They construct here so such files load; USING one is refused
-// loudly when its record is asked for (their lobes are not built - SURVEY.md 8f N3).
+// reference src/render_core/material/plastic.cpp:68-131 (slots color 1, spec 0.05, ior 1.3, roughness 0.5, anisotropic 0)
+class PlasticMaterial : public Material {
+    MaterialDesc desc_;
+public:
+    explicit PlasticMaterial(const MaterialDesc &d) : Material(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "plastic"; }
+    void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
+        fill_microfacet_common(r, desc_, 0.5f, ctx);
+        r.type = VB_MAT_PLASTIC;
+        r.color = make_slot(desc_["color"], {1.f, 1.f, 1.f}, ctx);
+        r.spec = make_slot(desc_["spec"], {0.05f, 0.05f, 0.05f}, ctx);
+        float ior = make_slot(desc_["ior"], {1.3f, 1.3f, 1.3f}, ctx).value[0];
+        r.ior = vb_slot{{ior, ior, ior, 1.f}, VB_INVALID_ID, {0, 0, 0}};
+    }
+};
+VH_MAKE_CLASS_CREATOR(PlasticMaterial, material, plastic, constructor)
+
+// reference src/render_core/material/metallic.cpp:12-61 (slots color 1, edge_tint 1, roughness 0.5, anisotropic 0; remapping_roughness_
+// is a member initialised to true and never read from the desc)
+class MetallicMaterial : public Material {
+    MaterialDesc desc_;
+public:
+    explicit MetallicMaterial(const MaterialDesc &d) : Material(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "metallic"; }
+    void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
+        fill_microfacet_common(r, desc_, 0.5f, ctx);
+        r.flags = 2u;
+        r.type = VB_MAT_METALLIC;
+        r.color = make_slot(desc_["color"], {1.f, 1.f, 1.f}, ctx);
+        r.spec = make_slot(desc_["edge_tint"], {1.f, 1.f, 1.f}, ctx);
+    }
+};
+VH_MAKE_CLASS_CREATOR(MetallicMaterial, material, metallic, constructor)
+
+// reference src/render_core/material/mix.cpp:14-58 and add.cpp:13-54: two child materials built from desc.mat0 / desc.mat1
+// (MaterialDesc::init, node_desc.cpp:170-176); mix has the "frac" slot (default 0.5)
+class LobeSetMaterial : public Material {
+protected:
+    MaterialDesc desc_;
+    std::shared_ptr<Material> mat0_, mat1_;
+public:
+    explicit LobeSetMaterial(const MaterialDesc &d) : Material(d), desc_(d) {
+        name_ = d.name;
+        for (int k = 0; k < 2; ++k) {
+            const char *key = k ? "mat1" : "mat0";
+            if (!d.parameter.contains(key)) throw std::runtime_error("material '" + d.name + "': \"" + key + "\" is missing");
+            MaterialDesc cd;
+            cd.init(d[key]);
+            if (cd.name.empty()) cd.name = d.name + "." + key;
+            (k ? mat1_ : mat0_) = create_shared<Material>(cd);
+        }
+    }
+    std::vector<std::shared_ptr<Material>> children() const override { return {mat0_, mat1_}; }
+    void fill_children(vb_material_rec &r) const {
+        if (mat0_->index == VB_INVALID_ID || mat1_->index == VB_INVALID_ID) throw std::runtime_error("material '" + name_ + "': children have no record index");
+        r.spd[0] = mat0_->index; r.spd[1] = mat1_->index;
+    }
+};
+class MixMaterial : public LobeSetMaterial {
+public:
+    explicit MixMaterial(const MaterialDesc &d) : LobeSetMaterial(d) {}
+    std::string impl_type() const override { return "mix"; }
+    void fill_record(vb_material_rec &r, const SlotContext &ctx) const override {
+        init_material_record(r);
+        r.type = VB_MAT_MIX;
+        fill_children(r);
+        // the plugin reads "frac" (default 0.5); the stock scene files write "scale", which nothing reads
+        float frac = desc_.has_attr("frac") ? make_slot(desc_["frac"], {0.5f, 0.5f, 0.5f}, ctx).value[0] : 0.5f;
+        r.sigma = vb_slot{{frac, frac, frac, 1.f}, VB_INVALID_ID, {0, 0, 0}};
+    }
+};
+VH_MAKE_CLASS_CREATOR(MixMaterial, material, mix, constructor)
+class AddMaterial : public LobeSetMaterial {
+public:
+    explicit AddMaterial(const MaterialDesc &d) : LobeSetMaterial(d) {}
+    std::string impl_type() const override { return "add"; }
+    void fill_record(vb_material_rec &r, const SlotContext &) const override { init_material_record(r); r.type = VB_MAT_ADD; fill_children(r); }
+};
+VH_MAKE_CLASS_CREATOR(AddMaterial, material, add, constructor)
+
+// reference src/render_core/material/subsurface.cpp and multi_layered.cpp are themselves unfinished: neither has a create_lobe_set nor
+// a VS_MAKE_CLASS_CREATOR, so the reference cannot instantiate them either. They construct here so that a scene file listing one
+// loads; USING one is refused loudly.
 #define VH_UNBUILT_MATERIAL(Class, tag)                                                                              \
     class Class : public Material {                                                                                  \
     public:                                                                                                          \
         explicit Class(const MaterialDesc &d) : Material(d) { name_ = d.name; }                                      \
         std::string impl_type() const override { return #tag; }                                                      \
         void fill_record(vb_material_rec &, const SlotContext &) const override {                                    \
-            throw std::runtime_error("material '" + name_ + "' (" #tag "): this material type is not implemented");  \
+            throw std::runtime_error("material '" + name_ + "' (" #tag "): the reference has no lobe set for this type either");  \
         }                                                                                                            \
     };                                                                                                               \
     VH_MAKE_CLASS_CREATOR(Class, material, tag, constructor)
-VH_UNBUILT_MATERIAL(MixMaterial, mix)
-VH_UNBUILT_MATERIAL(AddMaterial, add)
-VH_UNBUILT_MATERIAL(PlasticMaterial, plastic)
-VH_UNBUILT_MATERIAL(MetallicMaterial, metallic)
 VH_UNBUILT_MATERIAL(SubsurfaceMaterial, subsurface)
 VH_UNBUILT_MATERIAL(MultiLayeredMaterial, multi_layered)
 #undef VH_UNBUILT_MATERIAL

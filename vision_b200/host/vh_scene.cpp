@@ -190,8 +190,14 @@ void Scene::prepare(SceneRecords &out) {
     light_sampler->tidy_up();
     spectrum->prepare(out);
     SlotContext sctx{&image_pool, desc.scene_path, spectrum->is_complete(), &out.spds};
-    out.materials.resize(materials.size());
-    for (auto &m : materials) m->fill_record(out.materials[m->index], sctx);
+    std::vector<std::shared_ptr<Material>> all = materials;      // + the children of mix / add materials, appended after the scene's own
+    for (size_t k = 0; k < materials.size(); ++k)
+        for (auto &c : materials[k]->children()) {
+            if (!c->children().empty()) throw std::runtime_error("material '" + materials[k]->name() + "': a mix / add material nested in another one is not supported");
+            c->index = (uint32_t)all.size(); all.push_back(c);
+        }
+    out.materials.resize(all.size());
+    for (auto &m : all) m->fill_record(out.materials[m->index], sctx);
     std::map<uint64_t, uint32_t> mesh_ids;
     for (auto &i : instances) {
         bool known_name = false;
@@ -223,7 +229,8 @@ void Scene::prepare(SceneRecords &out) {
     out.mediums.resize(mediums.size());
     for (auto &m : mediums) m->fill_record(out.mediums[m->index]);
     bool need_luts = false, principled = false;
-    for (auto &m : out.materials) { principled |= m.type == VB_MAT_PRINCIPLED; need_luts |= m.type == VB_MAT_MIRROR || m.type == VB_MAT_GLASS || m.type == VB_MAT_METAL; }
+    for (auto &m : out.materials) { principled |= m.type == VB_MAT_PRINCIPLED;
+                                    need_luts |= m.type == VB_MAT_MIRROR || m.type == VB_MAT_GLASS || m.type == VB_MAT_METAL || m.type == VB_MAT_METALLIC; }
     if (principled) {            // PrincipledBSDF::prepare (principled_bsdf.cpp:324-330): coat, sheen, specular tables
         load_lut(out.luts[VB_LUT_SPECULAR], "lut_specular_32x32x32x1.f32", 32, 32, 32, 1);
         load_lut(out.luts[VB_LUT_COAT], "lut_coat_32x32x32x1.f32", 32, 32, 32, 1);

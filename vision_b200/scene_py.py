@@ -550,6 +550,24 @@ def _material_record(m, textures, base, spectrum_complete=False, spds=None):
         P[13] = _number(prm.get("transmission_weight"), 0.0)
         P[14] = 1.0                                                # sheen_mode_ = Approximate (principled_bsdf.cpp:260)
         P[15] = 63.0                                               # all lobe switches on (principled_bsdf.cpp:261-265)
+    elif t == "plastic":                                           # plastic.cpp:90-99
+        rec.type = capi.VB_MAT_PLASTIC
+        rec.color = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
+        rec.spec = _color_slot(prm.get("spec", [0.05, 0.05, 0.05]), textures, base)
+        rec.roughness = make_slot([_number(prm.get("roughness"), 0.5)] * 3)
+        rec.ior = make_slot([_number(prm.get("ior"), 1.3)] * 3)
+    elif t == "metallic":                                          # metallic.cpp:28-36; remapping_roughness_ is not a desc attribute
+        rec.type = capi.VB_MAT_METALLIC
+        rec.flags = 2
+        rec.color = _color_slot(prm.get("color", [1, 1, 1]), textures, base)
+        rec.spec = _color_slot(prm.get("edge_tint", [1, 1, 1]), textures, base)
+        rec.roughness = make_slot([_number(prm.get("roughness"), 0.5)] * 3)
+    elif t in ("mix", "add"):                                      # mix.cpp:29-36, add.cpp:25-31: children are filled in by build_scene
+        rec.type = capi.VB_MAT_MIX if t == "mix" else capi.VB_MAT_ADD
+        rec.flags = 0
+        rec.params[0] = 0.0
+        if t == "mix":
+            rec.sigma = make_slot([_number(prm.get("frac"), 0.5) if "frac" in prm else 0.5] * 3)
     else:
         return None
     return rec
@@ -903,10 +921,27 @@ def build_scene(path, overrides=None) -> SceneRecords:
         if rec is None:
             raise NotImplementedError(f"material {mat_descs[old]['name']} ({mat_descs[old]['type']})")
         sc.materials.append(rec)
+    # children of mix / add materials: records appended after the scene's own, in the order mat0, mat1 (the host layer's order)
+    for k in range(len(used)):
+        md = mat_descs[used[k]]
+        if md["type"] not in ("mix", "add"):
+            continue
+        for c, key in enumerate(("mat0", "mat1")):
+            cd = md.get("param", {}).get(key)
+            if cd is None:
+                raise ValueError(f"material {md.get('name')}: \"{key}\" is missing")
+            if cd.get("type", "diffuse") in ("mix", "add"):
+                raise NotImplementedError(f"material {md.get('name')}: a mix / add material nested in another one is not supported")
+            cd = dict(cd); cd.setdefault("type", "diffuse")
+            crec = _material_record(cd, sc.textures, base, hero, sc.spds)
+            if crec is None:
+                raise NotImplementedError(f"material {md.get('name')}.{key} ({cd['type']})")
+            sc.materials[k].spd[c] = len(sc.materials)
+            sc.materials.append(crec)
     for i in sc.instances:
         if i["material_id"] != VB_INVALID_ID:
             i["material_id"] = remap[i["material_id"]]
-    lut_users = (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL, capi.VB_MAT_PRINCIPLED)
+    lut_users = (capi.VB_MAT_MIRROR, capi.VB_MAT_GLASS, capi.VB_MAT_METAL, capi.VB_MAT_PRINCIPLED, capi.VB_MAT_METALLIC)
     if any(r.type in lut_users for r in sc.materials) and ov.get("luts", True):
         sc.luts = capi.load_luts(principled=any(r.type == capi.VB_MAT_PRINCIPLED for r in sc.materials))
     # LightSampler ctor (lightsampler.cpp:11-27): listed lights come first, the shapes' emissions follow; tidy_up
