@@ -85,7 +85,9 @@ typedef struct vb_medium_rec {
 VB_API int vb_mediums_set(vb_ctx *ctx, const vb_medium_rec *med, uint32_t n);
 
 /* ---- lights (reference src/render_core/light/<name>.cpp) + alias tables (warper/alias.h:86-122) ---- */
-enum { VB_LIGHT_AREA = 0, VB_LIGHT_POINT = 1, VB_LIGHT_SPOT = 2, VB_LIGHT_ENV = 3, VB_LIGHT_PROJECTOR = 4 };
+/* VB_LIGHT_DIRECTIONAL (environments/directional.cpp:20-80): a delta Infinite light; like VB_LIGHT_ENV it is the scene's environment
+ * light (the last Infinite light in the list wins, lightsampler.cpp:18-25), so a ray that misses evaluates it: L = color * scale, pdf -1. */
+enum { VB_LIGHT_AREA = 0, VB_LIGHT_POINT = 1, VB_LIGHT_SPOT = 2, VB_LIGHT_ENV = 3, VB_LIGHT_PROJECTOR = 4, VB_LIGHT_DIRECTIONAL = 5 };
 typedef struct vb_alias_entry { float prob; uint32_t alias; } vb_alias_entry;
 typedef struct vb_light_rec {
     uint32_t type;
@@ -98,9 +100,10 @@ typedef struct vb_light_rec {
     float pad0;
     vb_slot color;
     float position[4];         /* point/spot; projector: o2w[3] */
-    float direction[4];        /* spot */
+    float direction[4];        /* spot; directional: "direction" as written in the scene file (default -1,-1,-1; not normalised, directional.cpp:33) */
     float params[8];           /* spot: cos_falloff_start, cos_total_width; projector (light/projector.cpp:33-113): [0] tan(angle_y), [1] ratio
-                                * (0 in the file = image width / height), image = color slot, w2o / o2w = the light's transform; env: [0] Scene::world_diameter() (scene.h:108-109) */
+                                * (0 in the file = image width / height), image = color slot, w2o / o2w = the light's transform; env: [0] Scene::world_diameter() (scene.h:108-109);
+                                * directional: [0] world_diameter, [1] world_radius (directional.cpp:35-38: p_light = pos - direction * world_radius) */
     /* env ("spherical", environments/spherical.cpp:26-211): lat-long map = color slot texture, importance
      * sampled through AliasTable2D (alias2d.cpp:31-129): marginal table over rows at alias_offset /
      * alias_size (= env_res[1]) / alias_integral, conditional row tables (env_res[0] entries per row)
@@ -119,6 +122,14 @@ VB_API int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n,
  * Call after vb_lights_set (which resets the rule to UNIFORM). */
 enum { VB_LIGHT_SAMPLER_UNIFORM = 0, VB_LIGHT_SAMPLER_POWER = 1 };
 VB_API int vb_light_sampler_set(vb_ctx *ctx, uint32_t kind, uint32_t alias_offset, uint32_t alias_size, float alias_integral);
+/* LightSampler's "env_separate" / "env_prob" (reference src/base/illumination/lightsampler.cpp:11-13,28-33,159-197): when set and the
+ * scene has an environment light, select_light takes that light when u < env_prob and otherwise applies the rule above to
+ * u' = (u - env_prob) / (1 - env_prob) over the OTHER lights (uniform: min(u' (N-1), N-2), indices at or past the environment's
+ * shifted by one; power: the caller builds the table with weight 0 for the environment, power.cpp:37-45); PMF = env_prob for the
+ * environment light, (1 - env_prob) * PMF_ for the others. env_prob is used as given (the host clamps it to [0.01, 0.99] like the
+ * reference's constructor); env_separate with an environment light as the ONLY light is VB_ERR_UNSUPPORTED at render time (the
+ * reference divides by zero there). Call after vb_lights_set (which resets it to off). */
+VB_API int vb_light_sampler_env_set(vb_ctx *ctx, uint32_t env_separate, float env_prob);
 
 /* ---- spectrum (reference src/render_core/spectrum/srgb.cpp:16-57, hero.cpp:15-348; src/base/color/spd.cpp) ---- */
 /* SPD pool: tabulated spectral distributions over 360..830 nm, SPD::eval semantics (spd.cpp:50,57-76: linear

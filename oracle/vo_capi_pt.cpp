@@ -33,6 +33,13 @@ void vo_scene_set_lights(void *h, const vb_light_rec *l, uint32_t n, const vb_al
     s.lights.assign(l, l + n);
     s.alias_table.assign(t, t + na);
     s.alias_func.assign(f, f + na);
+    s.env_light = VB_INVALID_ID;
+    for (uint32_t i = 0; i < n; ++i) if (l[i].type == VB_LIGHT_ENV || l[i].type == VB_LIGHT_DIRECTIONAL) s.env_light = i;
+    s.env_separate = 0; s.env_prob = 0.f;
+}
+void vo_scene_set_light_sampler_env(void *h, uint32_t env_separate, float env_prob) {
+    Scene &s = *(Scene *)h;
+    s.env_separate = env_separate; s.env_prob = env_prob;
 }
 void vo_scene_set_light_sampler(void *h, uint32_t kind, uint32_t offset, uint32_t size, float integral) {
     Scene &s = *(Scene *)h;

@@ -66,3 +66,12 @@ void vo_probe_bsdf_sample(void *scene, uint32_t mat_id, const float *wo, uint32_
 }
 
 }  // extern "C"
+
+// LightSampler::select_light / PMF of the scene's rule at u (lightsampler.cpp:159-197): returns the light index, *pmf its PMF
+extern "C" uint32_t vo_probe_light_select(void *scene, float u, float *pmf) {
+    const vo::Scene &sc = *(const vo::Scene *)scene;
+    uint32_t i = vo::light_select(sc, u);
+    *pmf = vo::light_pmf(sc, i);
+    return i;
+}
+extern "C" float vo_probe_light_pmf(void *scene, uint32_t index) { return vo::light_pmf(*(const vo::Scene *)scene, index); }

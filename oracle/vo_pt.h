@@ -43,6 +43,8 @@ struct Scene {
     std::vector<vb_alias_entry> alias_table;
     std::vector<float> alias_func;
     uint32_t lsel_offset = 0, lsel_size = 0; float lsel_integral = 0.f;      // "power" light sampler table (size 0 = uniform)
+    uint32_t env_light = VB_INVALID_ID;      // LightSampler::env_light_ (lightsampler.cpp:18-25): the last Infinite light wins
+    uint32_t env_separate = 0; float env_prob = 0.f;                         // lightsampler.cpp:11-13,159-197
     std::vector<Texture> textures;
     Lut luts[VB_LUT_COUNT];
     std::vector<vb_medium_rec> mediums;

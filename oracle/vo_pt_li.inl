@@ -226,15 +226,53 @@ inline LightSample env_sample_wi(const Scene &sc, const Swl &swl, const vb_light
     return ls;
 }
 
-// LightSampler::PMF / select_light: uniform.cpp:14-33, or power.cpp:16-31 = Warper::PMF / sample_discrete of an alias table over
-// luminance(light->power()) (alias.h:148-181)
-inline float light_pmf(const Scene &sc, uint32_t index) {
-    if (sc.lsel_size == 0) return 1.0f / (float)sc.lights.size();
+// ---- directional light, reference render_core/light/environments/directional.cpp:46-80: a delta Infinite light ----
+inline LightEval directional_evaluate_wi(const Scene &sc, const Swl &swl, const vb_light_rec &l) {
+    LightEval ev;
+    ev.L = spec_illum(sc, swl, eval_slot3(sc, l.color, float2{0, 0})) * l.scale;
+    ev.pdf = -1.f;
+    return ev;
+}
+inline LightSample directional_sample_wi(const Scene &sc, const Swl &swl, const vb_light_rec &l, const Interaction &ref) {
+    LightSample ls;
+    float3 w_light = -float3{l.direction[0], l.direction[1], l.direction[2]};
+    ls.p_light = ref.pos + w_light * l.params[1];
+    ls.eval = directional_evaluate_wi(sc, swl, l);
+    return ls;
+}
+
+// LightSampler::PMF / select_light (lightsampler.cpp:159-197) over PMF_ / select_light_: uniform.cpp:12-33, or power.cpp:16-31 =
+// Warper::PMF / sample_discrete of an alias table over luminance(light->power()) (alias.h:148-181). With env_separate and an
+// environment light, that light is chosen with probability env_prob and the rule below is applied to the others (uniform: over
+// the punctual_light_num() other lights, index corrected past the environment's; power: the host gave the environment weight 0)
+inline float light_pmf_(const Scene &sc, uint32_t index) {
+    if (sc.lsel_size == 0) {
+        uint32_t n = (uint32_t)sc.lights.size();
+        if (sc.env_separate) n -= sc.env_light != VB_INVALID_ID ? 1u : 0u;
+        return 1.0f / (float)n;
+    }
     return sc.lsel_integral > 0.f ? sc.alias_func[sc.lsel_offset + index] / (sc.lsel_integral * (float)sc.lsel_size) : 0.f;
+}
+inline float light_pmf(const Scene &sc, uint32_t index) {
+    if (sc.env_separate && sc.env_light != VB_INVALID_ID)
+        return index == sc.env_light ? sc.env_prob : (1 - sc.env_prob) * light_pmf_(sc, index);
+    return light_pmf_(sc, index);
 }
 inline uint32_t light_select(const Scene &sc, float u) {
     uint32_t n = (uint32_t)sc.lights.size();
-    if (sc.lsel_size == 0) return (uint32_t)std::min(u * (float)n, (float)n - 1.0f);
+    const bool separate = sc.env_separate && sc.env_light != VB_INVALID_ID;
+    if (separate) {
+        if (u < sc.env_prob) return sc.env_light;
+        u = (u - sc.env_prob) / (1 - sc.env_prob);                  // remapping, warp.h:17-21
+    }
+    if (sc.lsel_size == 0) {
+        if (separate) {
+            float punctual = (float)(n - 1u);
+            uint32_t index = (uint32_t)std::min(u * punctual, punctual - 1);
+            return index < sc.env_light ? index : index + 1u;       // correct_index, lightsampler.cpp:28-33
+        }
+        return (uint32_t)std::min(u * (float)n, (float)n - 1.0f);
+    }
     u = u * (float)n;
     uint32_t idx = std::min((uint32_t)u, n - 1);
     u = std::min(u - (float)idx, OneMinusEpsilon);
@@ -254,6 +292,7 @@ inline LightSample sample_light(const Scene &sc, const Swl &swl, const Interacti
     const vb_light_rec &l = sc.lights[index];
     if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(sc, swl, l, it, u_surface);
     else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(sc, swl, l, it, u_surface);
+    else if (l.type == VB_LIGHT_DIRECTIONAL) ls = directional_sample_wi(sc, swl, l, it);
     else ls = point_sample_wi(sc, swl, l, it);
     ls.eval.pdf *= pmf;
     return ls;
@@ -422,8 +461,6 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
     const float3 primary_dir = ray.d;
     float eta_scale = 1.f;
     const uint32_t max_depth = params.max_depth;
-    uint32_t env_light = VB_INVALID_ID;                             // LightSampler::env_light_ (lightsampler.cpp:18-25): the last one wins
-    for (uint32_t i = 0; i < lights.size(); ++i) if (lights[i].type == VB_LIGHT_ENV) env_light = i;
     for (uint32_t bounces = 0; bounces < max_depth; ++bounces) {
         Hit hit = trace_closest(ray, st);
         if (hit.is_miss()) {                                        // evaluate_miss, integrator.cpp:137-158 + lightsampler.cpp:289-300
@@ -431,7 +468,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
                 const vb_light_rec &l = lights[env_light];
                 float3 tr{1, 1, 1};
                 if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(*this, swl, ray_medium, ray); }
-                LightEval ev = env_evaluate_wi(*this, swl, l, ray.o, ray.o + ray.d);
+                LightEval ev = l.type == VB_LIGHT_DIRECTIONAL ? directional_evaluate_wi(*this, swl, l) : env_evaluate_wi(*this, swl, l, ray.o, ray.o + ray.d);
                 ev.pdf *= light_pmf(*this, env_light);
                 float weight = mis_weight(scatter_pdf, ev.pdf);
                 if (params.mis_mode == 2) weight = 1.f;
@@ -549,7 +586,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
                     const vb_light_rec &l = lights[env_light];
                     float3 tr{1, 1, 1};
                     if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(*this, swl, ray_medium, ray); }
-                    LightEval ev = env_evaluate_wi(*this, swl, l, ray.o, ray.o + ray.d);
+                    LightEval ev = l.type == VB_LIGHT_DIRECTIONAL ? directional_evaluate_wi(*this, swl, l) : env_evaluate_wi(*this, swl, l, ray.o, ray.o + ray.d);
                     ev.pdf *= light_pmf(*this, env_light);
                     float weight = mis_weight(scatter_pdf, ev.pdf);
                     ret += spec_to_srgb(*this, swl, ev.L * tr * weight * throughput);

@@ -174,6 +174,9 @@ class OracleScene:
         lib.vo_scene_set_light_sampler.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float]
         lib.vo_scene_set_light_sampler.restype = None
         lib.vo_scene_set_light_sampler(self.h, *getattr(sc, "light_sampler", (0, 0, 0, 0.0)))
+        lib.vo_scene_set_light_sampler_env.argtypes = [vp, C.c_uint32, C.c_float]
+        lib.vo_scene_set_light_sampler_env.restype = None
+        lib.vo_scene_set_light_sampler_env(self.h, *getattr(sc, "light_sampler_env", (0, 0.0)))
         texs = (capi.vb_texture * max(1, len(sc.textures)))()
         keep = []
         for i, t in enumerate(sc.textures):

@@ -210,7 +210,8 @@ def test_desc_defaults_and_errors(tmp_path):
 @pytest.mark.parametrize("SCENE", [SCENE, ROOT / "scenes" / "cbox" / "cbox_materials.json", ROOT / "scenes" / "cbox" / "cbox_fog.json",
                                    ROOT / "scenes" / "cbox" / "cbox_lights.json", ROOT / "scenes" / "cbox" / "cbox_sphere.json",
                                    ROOT / "scenes" / "cbox" / "cbox_principled.json", ROOT / "scenes" / "cbox" / "cbox_dispersion.json",
-                                   ROOT / "scenes" / "cbox" / "cbox_lobesets.json"])
+                                   ROOT / "scenes" / "cbox" / "cbox_lobesets.json", ROOT / "scenes" / "cbox" / "cbox_env_separate_directional.json",
+                                   ROOT / "scenes" / "cbox" / "cbox_env_separate_power.json"])
 def test_host_pipeline_renders_like_python_path(vbctx, SCENE):
     hp = host_api.HostPipeline(SCENE)
     hp.prepare(0)

@@ -22,6 +22,12 @@ CASES = [
     # "power" light sampler (lightsampler/power.cpp): alias table over luminance(power()) of point, spot, spherical, projector, area
     ("cbox_lights_power", "scenes/cbox/cbox_lights_power.json", {"resolution": [160, 160], "spp": 8}, 0.05),
     ("cbox_lights_power_hero", "scenes/cbox/cbox_lights_power.json", {"resolution": [128, 128], "spp": 4, "spectrum": "hero"}, 0.05),
+    # directional light (a delta environment light: sampled AND evaluated on a miss), LightSampler env_separate /
+    # env_prob over the uniform and the power rule
+    ("cbox_directional", "scenes/cbox/cbox_directional.json", {"resolution": [160, 160], "spp": 8}, 0.03),
+    ("cbox_env_separate", "scenes/cbox/cbox_env_separate.json", {"resolution": [160, 160], "spp": 8}, 0.05),
+    ("cbox_env_separate_power", "scenes/cbox/cbox_env_separate_power.json", {"resolution": [160, 160], "spp": 8}, 0.05),
+    ("cbox_env_separate_directional_hero", "scenes/cbox/cbox_env_separate_directional.json", {"resolution": [128, 128], "spp": 4, "spectrum": "hero"}, 0.03),
     ("cbox_sphere_gaussian_filter", "scenes/cbox/cbox_sphere.json", {"resolution": [160, 160], "spp": 8}, 0.03),
     ("cbox_principled", "scenes/cbox/cbox_principled.json", {"resolution": [160, 160], "spp": 8}, 0.03),
     ("classroom_clear", "scenes/classroom/vision_scene.json", {"resolution": [240, 136], "spp": 4, "process_mediums": False}, 0.05),

@@ -148,3 +148,23 @@ g["materials"] += [
 assign(g, {"shape_5": "mix_gp", "shape_6": "mix_dm", "shape_0": "plastic", "shape_4": "metallic", "shape_2": "add_dm"})
 g["integrator"]["param"]["max_depth"] = 8
 (root / "cbox_lobesets.json").write_text(json.dumps(g, indent=1))
+
+# cbox_directional.json: the directional light (environments/directional.cpp:12-19 example block) shining in through the
+# open front; the back wall is removed (as in cbox_lights) so that paths also MISS into it - it is the scene's environment light.
+# cbox_env_separate*.json: LightSampler's env_separate / env_prob (lightsampler.cpp:11-13,159-197) over the uniform and the power rule,
+# with the spherical map, and over the directional light.
+dr = copy.deepcopy(c)
+dr["light_sampler"]["param"]["lights"] = [
+    {"type": "point", "param": {"color": {"channels": "xyz", "node": [1, 0.8, 0.6]}, "position": [-0.5, 1.8, 0], "scale": 0.2}},
+    {"type": "directional", "param": {"color": {"channels": "xyz", "node": [17, 12, 4]}, "scale": 0.1, "direction": [-0.35, -0.6, -1]}},
+]
+(root / "cbox_directional.json").write_text(json.dumps(dr, indent=1))
+es = copy.deepcopy(c)
+es["light_sampler"]["param"].update({"env_separate": True, "env_prob": 0.3})
+(root / "cbox_env_separate.json").write_text(json.dumps(es, indent=1))
+esp = copy.deepcopy(pw)
+esp["light_sampler"]["param"].update({"env_separate": True, "env_prob": 0.7})
+(root / "cbox_env_separate_power.json").write_text(json.dumps(esp, indent=1))
+esd = copy.deepcopy(dr)
+esd["light_sampler"]["param"].update({"env_separate": True})          # env_prob default 0.5
+(root / "cbox_env_separate_directional.json").write_text(json.dumps(esd, indent=1))

@@ -405,7 +405,7 @@ def load_cie_1nm() -> np.ndarray:
 
 VB_MAT_DIFFUSE, VB_MAT_MIRROR, VB_MAT_GLASS, VB_MAT_METAL, VB_MAT_SUBSTRATE, VB_MAT_PRINCIPLED, VB_MAT_BLACK_BODY = range(7)
 VB_MAT_PLASTIC, VB_MAT_METALLIC, VB_MAT_MIX, VB_MAT_ADD = 7, 8, 9, 10
-VB_LIGHT_AREA, VB_LIGHT_POINT, VB_LIGHT_SPOT, VB_LIGHT_ENV, VB_LIGHT_PROJECTOR = range(5)
+VB_LIGHT_AREA, VB_LIGHT_POINT, VB_LIGHT_SPOT, VB_LIGHT_ENV, VB_LIGHT_PROJECTOR, VB_LIGHT_DIRECTIONAL = range(6)
 VB_LIGHT_SAMPLER_UNIFORM, VB_LIGHT_SAMPLER_POWER = 0, 1
 VB_FILTER_BOX, VB_FILTER_TRIANGLE, VB_FILTER_FITTED = 0, 1, 2
 VB_FILTER_TABLE_SIZE = 20
@@ -433,6 +433,7 @@ def _bind_pt(lib):
         "vb_spectrum_set": [vp, C.POINTER(vb_spectrum_rec)],
         "vb_lights_set": [vp, C.POINTER(vb_light_rec), C.c_uint32, C.POINTER(vb_alias_entry), vp, C.c_uint32],
         "vb_light_sampler_set": [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float],
+        "vb_light_sampler_env_set": [vp, C.c_uint32, C.c_float],
         "vb_camera_set": [vp, C.POINTER(vb_camera)],
         "vb_integrator_set": [vp, C.POINTER(vb_pt_params)],
         "vb_film_create": [vp, C.c_uint32, C.c_uint32],
@@ -469,6 +470,7 @@ class SceneRecords:
         self.alias_table = []   # (prob, alias)
         self.alias_func = []    # float
         self.light_sampler = (0, 0, 0, 0.0)   # (kind, alias_offset, alias_size, alias_integral): vb_light_sampler_set
+        self.light_sampler_env = (0, 0.0)     # (env_separate, env_prob): vb_light_sampler_env_set
         self.textures = []      # (h, w, 4) float32 arrays
         self.mediums = []       # vb_medium_rec
         self.spds = []          # SPD pool: float32 arrays (hero spectrum: CIE x, y, z, D65 first, then material curves)
@@ -533,6 +535,8 @@ def _pt_methods():
         self._check(self.lib.vb_lights_set(self.h, lights, len(sc.lights), tab, func.ctypes.data, na), "vb_lights_set")
         k, off, size, integral = sc.light_sampler
         self._check(self.lib.vb_light_sampler_set(self.h, k, off, size, integral), "vb_light_sampler_set")
+        sep, prob = getattr(sc, "light_sampler_env", (0, 0.0))
+        self._check(self.lib.vb_light_sampler_env_set(self.h, sep, prob), "vb_light_sampler_env_set")
         self._check(self.lib.vb_camera_set(self.h, C.byref(sc.camera)), "vb_camera_set")
         self._check(self.lib.vb_integrator_set(self.h, C.byref(sc.params)), "vb_integrator_set")
         self._check(self.lib.vb_film_create(self.h, sc.resolution[0], sc.resolution[1]), "vb_film_create")

@@ -38,6 +38,8 @@ struct PtScene {
     const float *alias_func;
     uint32_t lsel_offset, lsel_size;   // light selection table of the "power" light sampler (vb_light_sampler_set); size 0 = uniform
     float lsel_integral;
+    uint32_t env_separate;         // vb_light_sampler_env_set (only set when env_light is valid)
+    float env_prob;
     const DevTex *textures;
     DevLut luts[VB_LUT_COUNT];
     const vb_medium_rec *mediums;
@@ -187,15 +189,31 @@ __device__ uint32_t alias_sample(const PtScene &S, const vb_light_rec &l, float 
     return out;
 }
 
-// LightSampler::PMF / select_light: uniform.cpp:14-33 (1 / N, index = min(u N, N - 1)) or power.cpp:16-31 (alias table over
-// luminance(light->power()): Warper::PMF / sample_discrete)
-__device__ __forceinline__ float light_pmf(const PtScene &S, uint32_t index) {
-    if (S.lsel_size == 0) return 1.0f / (float)S.n_lights;
+// LightSampler::PMF / select_light (lightsampler.cpp:159-197) over PMF_ / select_light_: uniform.cpp:12-33 (1 / N, index = min(u N, N - 1))
+// or power.cpp:16-31 (alias table over luminance(light->power()): Warper::PMF / sample_discrete). env_separate: the environment light
+// with probability env_prob, the rule over the others otherwise (mirror of oracle/vo_pt_li.inl light_pmf / light_select)
+__device__ __forceinline__ float light_pmf_(const PtScene &S, uint32_t index) {
+    if (S.lsel_size == 0) return 1.0f / (float)(S.n_lights - (S.env_separate ? 1u : 0u));
     return S.lsel_integral > 0.f ? __ldg(S.alias_func + S.lsel_offset + index) / (S.lsel_integral * (float)S.lsel_size) : 0.f;
+}
+__device__ __forceinline__ float light_pmf(const PtScene &S, uint32_t index) {
+    if (S.env_separate) return index == S.env_light ? S.env_prob : (1 - S.env_prob) * light_pmf_(S, index);
+    return light_pmf_(S, index);
 }
 __device__ __forceinline__ uint32_t light_select(const PtScene &S, float u) {
     uint32_t n = S.n_lights;
-    if (S.lsel_size == 0) return (uint32_t)fmin_(u * (float)n, (float)n - 1.0f);
+    if (S.env_separate) {
+        if (u < S.env_prob) return S.env_light;
+        u = (u - S.env_prob) / (1 - S.env_prob);
+    }
+    if (S.lsel_size == 0) {
+        if (S.env_separate) {
+            float punctual = (float)(n - 1u);
+            uint32_t index = (uint32_t)fmin_(u * punctual, punctual - 1);
+            return index < S.env_light ? index : index + 1u;
+        }
+        return (uint32_t)fmin_(u * (float)n, (float)n - 1.0f);
+    }
     u = u * (float)n;
     uint32_t idx = min((uint32_t)u, n - 1);
     u = fmin_(u - (float)idx, OneMinusEpsilon);
@@ -228,6 +246,21 @@ __device__ LightSample area_sample_wi(const PtScene &S, const Swl *swl, const vb
     f3 dir = ref.pos - pl.pos;
     float factor = dot(pl.ng, dir) > 0.f ? 1.f : -1.f;
     ls.p_light = offset_ray_origin(pl.pos, pl.ng * factor * S.params.ray_offset_factor);
+    return ls;
+}
+
+// ---- directional light: render_core/light/environments/directional.cpp:46-80 ----
+__device__ __forceinline__ LightEval directional_evaluate_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l) {
+    LightEval ev;
+    ev.L = spec_illum(S.spec, swl, eval_slot3(S, l.color, f2{0, 0})) * l.scale;
+    ev.pdf = -1.f;
+    return ev;
+}
+__device__ __forceinline__ LightSample directional_sample_wi(const PtScene &S, const Swl *swl, const vb_light_rec &l, const Interaction &ref) {
+    LightSample ls;
+    f3 w_light = -f3{l.direction[0], l.direction[1], l.direction[2]};
+    ls.p_light = ref.pos + w_light * l.params[1];
+    ls.eval = directional_evaluate_wi(S, swl, l);
     return ls;
 }
 

@@ -59,7 +59,7 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
             f3 tr{1, 1, 1};
             if (mediums) { ray.tmax = l.params[0]; tr = ray_Tr(S, swl, ps.ray_medium, ray); }
             f3 ro{ray.ox, ray.oy, ray.oz}, rd{ray.dx, ray.dy, ray.dz};
-            LightEval ev = env_evaluate_wi(S, swl, l, ro, ro + rd);
+            LightEval ev = l.type == VB_LIGHT_DIRECTIONAL ? directional_evaluate_wi(S, swl, l) : env_evaluate_wi(S, swl, l, ro, ro + rd);
             ev.pdf *= light_pmf(S, S.env_light);
             float weight = mis_weight(ps.scatter_pdf, ev.pdf);
             if (S.params.mis_mode == 2) weight = 1.f;
@@ -135,6 +135,7 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         const vb_light_rec &l = S.lights[index];
         if (l.type == VB_LIGHT_AREA) ls = area_sample_wi(S, swl, l, it, u_surface);
         else if (l.type == VB_LIGHT_ENV) ls = env_sample_wi(S, swl, l, it, u_surface);
+        else if (l.type == VB_LIGHT_DIRECTIONAL) ls = directional_sample_wi(S, swl, l, it);
         else ls = point_sample_wi(S, swl, l, it);
         ls.eval.pdf *= light_pmf(S, index);
     }

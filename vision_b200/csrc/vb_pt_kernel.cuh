@@ -224,6 +224,7 @@ struct vb_pt_state {
     uint64_t work[4] = {0, 0, 0, 0};
     uint32_t n_alias = 0;
     uint32_t lsel_offset = 0, lsel_size = 0; float lsel_integral = 0.f;     // vb_light_sampler_set
+    uint32_t env_separate = 0; float env_prob = 0.f;                        // vb_light_sampler_env_set
     bool has_principled = false;
     std::vector<DevMesh> h_meshes;
     DevMesh *d_meshes = nullptr;
@@ -239,6 +240,7 @@ struct vb_pt_state {
     float4 *d_gbuffer = nullptr; size_t gbuffer_n = 0;       // 4 planes of w*h float4 (vb_gbuffer_render)
     float4 *d_spec_cache = nullptr; size_t spec_cache_n = 0; bool spec_dirty = true;   // hero: decoded constant colour slots (k_spec_cache)
     std::vector<vb_material_rec> h_mat;            // kept for the SPD index checks at render time
+    std::vector<vb_light_rec> h_lights;            // kept for the instance / table checks at render time
     vb_camera cam{}; bool have_cam = false;
     vb_pt_params params{}; bool have_params = false;
     uint32_t w = 0, h = 0;
@@ -456,7 +458,7 @@ int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n, const vb_
     cudaSetDevice(ctx->device);
     vb_pt_state *p = pt_state(ctx);
     for (uint32_t i = 0; i < n; ++i) {
-        if (lights[i].type > VB_LIGHT_PROJECTOR) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_lights_set: light type not implemented yet");
+        if (lights[i].type > VB_LIGHT_DIRECTIONAL) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_lights_set: light type not implemented yet");
         bool tabled = lights[i].type == VB_LIGHT_AREA || lights[i].type == VB_LIGHT_ENV;
         if (tabled && lights[i].alias_offset + lights[i].alias_size > n_alias) return ctx->fail(VB_ERR_INVALID, "vb_lights_set: alias range out of bounds");
         if (lights[i].type == VB_LIGHT_ENV) {
@@ -468,9 +470,11 @@ int vb_lights_set(vb_ctx *ctx, const vb_light_rec *lights, uint32_t n, const vb_
     cudaFree(p->d_lights); cudaFree(p->d_alias); cudaFree(p->d_func);
     p->d_lights = nullptr; p->d_alias = nullptr; p->d_func = nullptr; p->n_lights = n; p->n_alias = n_alias;
     p->lsel_offset = p->lsel_size = 0; p->lsel_integral = 0.f;
+    p->env_separate = 0; p->env_prob = 0.f;
+    p->h_lights.assign(lights, lights + n);
     p->spec_dirty = true;
     p->env_light = VB_INVALID_ID;
-    for (uint32_t i = 0; i < n; ++i) if (lights[i].type == VB_LIGHT_ENV) p->env_light = i;
+    for (uint32_t i = 0; i < n; ++i) if (lights[i].type == VB_LIGHT_ENV || lights[i].type == VB_LIGHT_DIRECTIONAL) p->env_light = i;
     if (n) {
         VB_CUDA(cudaMalloc(&p->d_lights, sizeof(vb_light_rec) * n));
         VB_CUDA(cudaMemcpy(p->d_lights, lights, sizeof(vb_light_rec) * n, cudaMemcpyHostToDevice));
@@ -492,6 +496,13 @@ int vb_light_sampler_set(vb_ctx *ctx, uint32_t kind, uint32_t alias_offset, uint
     if (alias_size == 0 || alias_size != p->n_lights) return ctx->fail(VB_ERR_INVALID, "vb_light_sampler_set: the selection table needs one entry per light (call vb_lights_set first)");
     if ((uint64_t)alias_offset + alias_size > p->n_alias) return ctx->fail(VB_ERR_INVALID, "vb_light_sampler_set: alias range out of bounds");
     p->lsel_offset = alias_offset; p->lsel_size = alias_size; p->lsel_integral = alias_integral;
+    return VB_OK;
+}
+int vb_light_sampler_env_set(vb_ctx *ctx, uint32_t env_separate, float env_prob) {
+    if (!ctx) return VB_ERR_INVALID;
+    if (env_separate && !(env_prob > 0.f && env_prob < 1.f)) return ctx->fail(VB_ERR_INVALID, "vb_light_sampler_env_set: env_prob must lie inside (0, 1)");
+    vb_pt_state *p = pt_state(ctx);
+    p->env_separate = env_separate ? 1u : 0u; p->env_prob = env_prob;
     return VB_OK;
 }
 int vb_camera_set(vb_ctx *ctx, const vb_camera *cam) {
@@ -543,12 +554,23 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
         if (in.material_id != VB_INVALID_ID && in.material_id >= p->n_mat) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": instance material_id out of range");
         if (in.light_id != VB_INVALID_ID && in.light_id >= p->n_lights) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": instance light_id out of range");
     }
+    // an area light samples the triangles of ITS instance through ITS alias table (area.cpp:74-83): both must agree with the geometry
+    for (auto &l : p->h_lights) {
+        if (l.type != VB_LIGHT_AREA) continue;
+        if (l.inst_id >= ctx->instances.size()) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": area light inst_id out of range");
+        const uint32_t mesh = ctx->instances[l.inst_id].mesh_id;
+        if (mesh >= ctx->meshes.size() || (uint64_t)l.alias_size != ctx->meshes[mesh].nt)
+            return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": area light alias_size differs from its instance's triangle count");
+    }
+    if (p->env_separate && p->env_light != VB_INVALID_ID && p->n_lights < 2)
+        return ctx->fail(VB_ERR_UNSUPPORTED, std::string(fn) + ": env_separate needs a light besides the environment light");
     int rc = pt_sync_geometry(ctx);
     if (rc) return rc;
     PtScene S{};
     S.accel = VbAccelView{ctx->accel.nodes, ctx->accel.tris};
     S.meshes = p->d_meshes; S.instances = p->d_inst; S.materials = p->d_mat; S.lights = p->d_lights; S.n_lights = p->n_lights; S.env_light = p->env_light;
     S.lsel_offset = p->lsel_offset; S.lsel_size = p->lsel_size; S.lsel_integral = p->lsel_integral;
+    S.env_separate = (p->env_separate && p->env_light != VB_INVALID_ID) ? 1u : 0u; S.env_prob = p->env_prob;
     S.alias_table = p->d_alias; S.alias_func = p->d_func; S.textures = p->d_tex;
     for (int k = 0; k < VB_LUT_COUNT; ++k) S.luts[k] = p->luts[k];
     S.mediums = p->d_mediums;

@@ -146,7 +146,9 @@ class LightSampler : public Node {
 public:
     using Desc = LightSamplerDesc;
     std::vector<std::shared_ptr<Light>> lights;
-    explicit LightSampler(const LightSamplerDesc &) {}
+    bool env_separate;                                // lightsampler.cpp:11-13
+    float env_prob;
+    explicit LightSampler(const LightSamplerDesc &d);
     void add_light(std::shared_ptr<Light> l) { lights.push_back(std::move(l)); }
     void tidy_up();                                   // lightsampler.cpp:64-74
     virtual uint32_t kind() const { return VB_LIGHT_SAMPLER_UNIFORM; }

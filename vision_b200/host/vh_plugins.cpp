@@ -483,6 +483,11 @@ public:
 };
 VH_MAKE_CLASS_CREATOR(AreaLight, light, area, constructor)
 
+// LightSampler ctor (lightsampler.cpp:11-13): env_separate (default false) samples the environment light with its own probability
+// env_prob, clamped to [0.01, 0.99]; the rule itself (lightsampler.cpp:159-197) runs on the device (vb_light_sampler_env_set)
+LightSampler::LightSampler(const LightSamplerDesc &d)
+    : env_separate(d["env_separate"].as_bool(false)), env_prob(std::min(std::max(d["env_prob"].as_float(0.5f), 0.01f), 0.99f)) {}
+
 void LightSampler::tidy_up() {
     // Polymorphic topology order = order in which light TYPES were first added
     std::vector<int> first;
@@ -495,17 +500,13 @@ void LightSampler::tidy_up() {
 // reference src/render_core/lightsampler/uniform.cpp:12-34 (device part: index = min(u*N, N-1), PMF 1/N)
 class UniformLightSampler : public LightSampler {
 public:
-    explicit UniformLightSampler(const LightSamplerDesc &d) : LightSampler(d) {
-        // LightSampler ctor (lightsampler.cpp:11-14): env_separate (default false) samples the environment light with its own
-        // probability env_prob; that selection rule (lightsampler.cpp:159-197) is not built - refuse instead of rendering differently
-        if (d["env_separate"].as_bool(false)) throw std::runtime_error("light_sampler.env_separate = true is not implemented");
-    }
+    explicit UniformLightSampler(const LightSamplerDesc &d) : LightSampler(d) {}
     std::string impl_type() const override { return "uniform"; }
 };
 VH_MAKE_CLASS_CREATOR(UniformLightSampler, lightsampler, uniform, constructor)
 
 // luminance(light->power()), the weight PowerLightSampler::prepare gives each light (power.cpp:35-50): area.cpp:87-89, point.cpp:32-34,
-// spot.cpp:44-46, projector.cpp:58-91, spherical.cpp:56-59; Light::average (light.h:80-83) = slot average x scale. A texture's average
+// spot.cpp:44-46, projector.cpp:58-91, spherical.cpp:56-59, directional.cpp:44-46; Light::average (light.h:80-83) = slot average x scale. A texture's average
 // (ocarina Image::average_vector, absent from the tree) = per-channel mean summed in double in pixel order; luminance = Rec.709.
 float light_power_luminance(const vb_light_rec &l, const SceneRecords &rec, float spot_angle, float spot_falloff) {
     const float Pi = 3.14159265358979323846f;
@@ -529,9 +530,9 @@ float light_power_luminance(const vb_light_rec &l, const SceneRecords &rec, floa
     } else if (l.type == VB_LIGHT_SPOT) {
         float k = 2.f * Pi, s = 1.f - .5f * (spot_angle * 2.f + spot_falloff);
         for (int c = 0; c < 3; ++c) p[c] = k * avg[c] * s;
-    } else if (l.type == VB_LIGHT_ENV) {
+    } else if (l.type == VB_LIGHT_ENV || l.type == VB_LIGHT_DIRECTIONAL) {      // directional.cpp:44-46: average * Pi * sqr(world_radius)
         float r = l.params[0] / 2.f, k = Pi * (r * r);
-        for (int c = 0; c < 3; ++c) p[c] = k * avg[c];
+        for (int c = 0; c < 3; ++c) p[c] = l.type == VB_LIGHT_ENV ? k * avg[c] : (avg[c] * Pi) * (r * r);
     } else {                                                           // projector: Girard's theorem on the frustum corner directions
         float ratio = l.params[1];
         float y = std::sqrt(1.f / (ratio * ratio + 1.f)), x = ratio * y, z = std::sqrt(x * x + y * y);
@@ -552,9 +553,7 @@ float light_power_luminance(const vb_light_rec &l, const SceneRecords &rec, floa
 // reference src/render_core/lightsampler/power.cpp:11-56: lights are drawn from an alias table over luminance(light->power())
 class PowerLightSampler : public LightSampler {
 public:
-    explicit PowerLightSampler(const LightSamplerDesc &d) : LightSampler(d) {
-        if (d["env_separate"].as_bool(false)) throw std::runtime_error("light_sampler.env_separate = true is not implemented");
-    }
+    explicit PowerLightSampler(const LightSamplerDesc &d) : LightSampler(d) {}
     std::string impl_type() const override { return "power"; }
     uint32_t kind() const override { return VB_LIGHT_SAMPLER_POWER; }
 };

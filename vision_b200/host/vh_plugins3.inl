@@ -227,6 +227,24 @@ VH_MAKE_CLASS_CREATOR(SpotLight, light, spot, constructor)
 
 static bool invert4(const double *m, double *inv);
 
+// reference src/render_core/light/environments/directional.cpp:20-38: a delta Infinite light; "direction" is stored as written
+class DirectionalLight : public Light {
+    LightDesc desc_;
+public:
+    explicit DirectionalLight(const LightDesc &d) : Light(d), desc_(d) { name_ = d.name; }
+    std::string impl_type() const override { return "directional"; }
+    int type_order() const override { return VB_LIGHT_DIRECTIONAL; }
+    void fill_record(vb_light_rec &r, const Scene &scene, const SlotContext &ctx, std::vector<vb_alias_entry> &, std::vector<float> &) const override {
+        light_common(r, desc_, {1.f, 1.f, 1.f}, ctx);
+        r.type = VB_LIGHT_DIRECTIONAL;
+        float3 d = desc_["direction"].as_float3({-1.f, -1.f, -1.f});
+        r.direction[0] = d.x; r.direction[1] = d.y; r.direction[2] = d.z;
+        r.params[0] = scene.world_diameter();
+        r.params[1] = r.params[0] * 0.5f;                               // world_radius (scene.h:108-109: diameter = radius * 2)
+    }
+};
+VH_MAKE_CLASS_CREATOR(DirectionalLight, light, directional, constructor)
+
 // reference src/render_core/light/environments/spherical.cpp:36-45 (transform), :170-196 (weights), :199-211 +
 // warper/alias2d.cpp:32-67 (AliasTable2D::build: one table per row, marginal over the row integrals)
 class SphericalMap : public Light {

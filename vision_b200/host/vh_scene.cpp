@@ -221,11 +221,18 @@ void Scene::prepare(SceneRecords &out) {
     out.textures = image_pool.images;
     if (light_sampler->kind() == VB_LIGHT_SAMPLER_POWER && !out.lights.empty()) {      // PowerLightSampler::prepare (power.cpp:33-53)
         std::vector<float> weights(out.lights.size());
-        for (auto &l : light_sampler->lights) weights[l->index] = light_power_luminance(out.lights[l->index], out, l->shape_angle, l->shape_falloff);
+        for (auto &l : light_sampler->lights) {
+            const vb_light_rec &r = out.lights[l->index];
+            const bool infinite = r.type == VB_LIGHT_ENV || r.type == VB_LIGHT_DIRECTIONAL;
+            weights[l->index] = (light_sampler->env_separate && infinite) ? 0.f                       // power.cpp:37-45
+                                                                         : light_power_luminance(r, out, l->shape_angle, l->shape_falloff);
+        }
         out.light_sampler.kind = VB_LIGHT_SAMPLER_POWER;
         out.light_sampler.alias_offset = (uint32_t)out.alias_table.size(); out.light_sampler.alias_size = (uint32_t)weights.size();
         warper->build(weights, out.alias_table, out.alias_func, out.light_sampler.alias_integral);
     }
+    out.light_sampler.env_separate = light_sampler->env_separate ? 1u : 0u;
+    out.light_sampler.env_prob = light_sampler->env_prob;
     out.mediums.resize(mediums.size());
     for (auto &m : mediums) m->fill_record(out.mediums[m->index]);
     bool need_luts = false, principled = false;
@@ -332,6 +339,7 @@ void Pipeline::prepare(int device) {
                         (uint32_t)records.alias_table.size()), "vb_lights_set");
     check(vb_light_sampler_set(ctx, records.light_sampler.kind, records.light_sampler.alias_offset, records.light_sampler.alias_size,
                                records.light_sampler.alias_integral), "vb_light_sampler_set");
+    check(vb_light_sampler_env_set(ctx, records.light_sampler.env_separate, records.light_sampler.env_prob), "vb_light_sampler_env_set");
     check(vb_camera_set(ctx, &records.camera), "vb_camera_set");
     check(vb_integrator_set(ctx, &records.params), "vb_integrator_set");
     check(vb_film_create(ctx, records.width, records.height), "vb_film_create");

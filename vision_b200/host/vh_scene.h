@@ -49,7 +49,8 @@ struct SceneRecords {
     std::vector<vb_light_rec> lights;
     std::vector<vb_alias_entry> alias_table;
     std::vector<float> alias_func;
-    struct LightSamplerRec { uint32_t kind = VB_LIGHT_SAMPLER_UNIFORM, alias_offset = 0, alias_size = 0; float alias_integral = 0.f; } light_sampler;   // vb_light_sampler_set
+    struct LightSamplerRec { uint32_t kind = VB_LIGHT_SAMPLER_UNIFORM, alias_offset = 0, alias_size = 0; float alias_integral = 0.f;
+                             uint32_t env_separate = 0; float env_prob = 0.f; } light_sampler;       // vb_light_sampler_set, vb_light_sampler_env_set
     std::vector<Image> textures;
     std::vector<vb_medium_rec> mediums;
     std::vector<std::vector<float>> spds;          // SPD pool (vb_spds_set): hero spectrum's CIE x, y, z, D65 first, then material curves

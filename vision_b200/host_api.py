@@ -68,7 +68,8 @@ def plugin_names():
 
 
 class _LightSamplerRec(C.Structure):       # SceneRecords::LightSamplerRec (vh_scene.h)
-    _fields_ = [("kind", C.c_uint32), ("alias_offset", C.c_uint32), ("alias_size", C.c_uint32), ("alias_integral", C.c_float)]
+    _fields_ = [("kind", C.c_uint32), ("alias_offset", C.c_uint32), ("alias_size", C.c_uint32), ("alias_integral", C.c_float),
+                ("env_separate", C.c_uint32), ("env_prob", C.c_float)]
 
 
 class HostPipeline:
@@ -200,6 +201,7 @@ class HostPipeline:
         sc.alias_func = [float(x) for x in self._blob(4, C.c_float)]
         ls = self._blob(102, _LightSamplerRec)[0]
         sc.light_sampler = (ls.kind, ls.alias_offset, ls.alias_size, ls.alias_integral)
+        sc.light_sampler_env = (ls.env_separate, ls.env_prob)
         sc.camera = self._blob(5, capi.vb_camera)[0]
         sc.params = self._blob(6, capi.vb_pt_params)[0]
         sc.mediums = self._blob(7, capi.vb_medium_rec)

@@ -647,6 +647,9 @@ def _light_power_luminance(l, sc, shape=None):
     elif l.type == capi.VB_LIGHT_ENV:
         r = f32(f32(l.params[0]) / f32(2.0))
         p = [f32(f32(PI_F * f32(r * r)) * a) for a in avg]
+    elif l.type == capi.VB_LIGHT_DIRECTIONAL:                          # directional.cpp:44-46
+        r = f32(f32(l.params[0]) / f32(2.0))
+        p = [f32(f32(a * PI_F) * f32(r * r)) for a in avg]
     else:                                                              # projector: Girard's theorem on the frustum corner directions
         ratio = f32(l.params[1])
         y = _cfun("sqrtf", f32(f32(1.0) / f32(f32(ratio * ratio) + f32(1.0))))
@@ -713,6 +716,12 @@ def _free_light_record(ld, sc, base, world_diameter):
         sc.alias_table += ct; sc.alias_func += cf
         l.env_res[:] = [rx, ry]
         l.params[0] = world_diameter
+    elif t == "directional":
+        # directional.cpp:20-38: "direction" stored as written; world radius = diameter / 2 (scene.h:108-109)
+        l.type = capi.VB_LIGHT_DIRECTIONAL
+        l.direction[:3] = [float(f32(x)) for x in prm.get("direction", [-1, -1, -1])]
+        l.params[0] = world_diameter
+        l.params[1] = float(f32(f32(world_diameter) * f32(0.5)))
     elif t == "projector":
         # projector.cpp:33-52: point light at o2w[3] projecting its image along local +z
         l.type = capi.VB_LIGHT_PROJECTOR
@@ -946,13 +955,15 @@ def build_scene(path, overrides=None) -> SceneRecords:
         sc.luts = capi.load_luts(principled=any(r.type == capi.VB_MAT_PRINCIPLED for r in sc.materials))
     # LightSampler ctor (lightsampler.cpp:11-27): listed lights come first, the shapes' emissions follow; tidy_up
     # (lightsampler.cpp:67-77) groups them by type in first-seen order; records are made in that order
-    if d.get("light_sampler", {}).get("param", {}).get("env_separate", False):      # lightsampler.cpp:11-14,159-197: not built
-        raise NotImplementedError("light_sampler.env_separate = true is not implemented")
+    lsp = d.get("light_sampler", {}).get("param", {})                # lightsampler.cpp:11-13: env_separate, env_prob in [0.01, 0.99]
+    env_separate = bool(lsp.get("env_separate", False))
+    sc.light_sampler_env = (1 if env_separate else 0, float(min(max(f32(lsp.get("env_prob", 0.5)), f32(0.01)), f32(0.99))))
     ls_type = d.get("light_sampler", {}).get("type", "uniform")
     if ls_type not in ("uniform", "power"):
         raise NotImplementedError("light sampler " + ls_type)
     free = [] if ov.get("drop_lights", False) else d.get("light_sampler", {}).get("param", {}).get("lights", [])
-    type_of = {"point": capi.VB_LIGHT_POINT, "spot": capi.VB_LIGHT_SPOT, "spherical": capi.VB_LIGHT_ENV, "projector": capi.VB_LIGHT_PROJECTOR}
+    type_of = {"point": capi.VB_LIGHT_POINT, "spot": capi.VB_LIGHT_SPOT, "spherical": capi.VB_LIGHT_ENV, "projector": capi.VB_LIGHT_PROJECTOR,
+               "directional": capi.VB_LIGHT_DIRECTIONAL}
     pending = [(type_of.get(ld["type"], -1), ld, None) for ld in free] + [(capi.VB_LIGHT_AREA, em, ii) for em, ii in area_lights]
     first = {}
     for t, _, _ in pending:
@@ -975,7 +986,9 @@ def build_scene(path, overrides=None) -> SceneRecords:
         sc.instances[ii]["light_id"] = len(sc.lights)
         sc.lights.append(l)
     if ls_type == "power" and sc.lights:                             # PowerLightSampler::prepare (power.cpp:33-53)
-        weights = [_light_power_luminance(l, sc, getattr(l, "_shape", None)) for l in sc.lights]
+        infinite = (capi.VB_LIGHT_ENV, capi.VB_LIGHT_DIRECTIONAL)       # power.cpp:37-45: weight 0 when sampled separately
+        weights = [f32(0.0) if (env_separate and l.type in infinite) else _light_power_luminance(l, sc, getattr(l, "_shape", None))
+                   for l in sc.lights]
         table, func, integral = alias_build(weights)
         sc.light_sampler = (capi.VB_LIGHT_SAMPLER_POWER, len(sc.alias_table), len(table), integral)
         sc.alias_table += table; sc.alias_func += func
