@@ -24,10 +24,12 @@ CASES = [
     ("cbox_lights_power_hero", "scenes/cbox/cbox_lights_power.json", {"resolution": [128, 128], "spp": 4, "spectrum": "hero"}, 0.05),
     # directional light (a delta environment light: sampled AND evaluated on a miss), LightSampler env_separate /
     # env_prob over the uniform and the power rule
-    ("cbox_directional", "scenes/cbox/cbox_directional.json", {"resolution": [160, 160], "spp": 8}, 0.03),
+    # (min_mean None: the reference weighs a MISS into the directional light with MIS_weight(scatter_pdf, -1 * PMF), integrator.cpp:152-153
+    #  over directional.cpp:75-79 - negative wherever scatter_pdf < PMF; reproduced as is, so the film mean is not a sanity measure there)
+    ("cbox_directional", "scenes/cbox/cbox_directional.json", {"resolution": [160, 160], "spp": 8}, None),
     ("cbox_env_separate", "scenes/cbox/cbox_env_separate.json", {"resolution": [160, 160], "spp": 8}, 0.05),
     ("cbox_env_separate_power", "scenes/cbox/cbox_env_separate_power.json", {"resolution": [160, 160], "spp": 8}, 0.05),
-    ("cbox_env_separate_directional_hero", "scenes/cbox/cbox_env_separate_directional.json", {"resolution": [128, 128], "spp": 4, "spectrum": "hero"}, 0.03),
+    ("cbox_env_separate_directional_hero", "scenes/cbox/cbox_env_separate_directional.json", {"resolution": [128, 128], "spp": 4, "spectrum": "hero"}, None),
     ("cbox_sphere_gaussian_filter", "scenes/cbox/cbox_sphere.json", {"resolution": [160, 160], "spp": 8}, 0.03),
     ("cbox_principled", "scenes/cbox/cbox_principled.json", {"resolution": [160, 160], "spp": 8}, 0.03),
     ("classroom_clear", "scenes/classroom/vision_scene.json", {"resolution": [240, 136], "spp": 4, "process_mediums": False}, 0.05),
@@ -56,7 +58,7 @@ def test_image_matches_oracle(vbctx, oracle, name, path, ov, min_mean):
     g = vbctx.film_download(capi.VB_FILM_ACCUM)
     o, _, ost = osc.render(0, sc.spp, threads=oracle.hw_threads(), stats=True)
     assert np.isfinite(g).all() and np.isfinite(o).all()
-    assert g[..., :3].mean() > min_mean
+    assert min_mean is None or g[..., :3].mean() > min_mean
     err = rel_mse(g[..., :3], o[..., :3])
     diff = np.abs(g[..., :3] - o[..., :3]) > 1e-4 * (np.abs(o[..., :3]) + 1e-3)
     frac = diff.any(axis=-1).mean()
