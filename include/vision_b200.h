@@ -110,6 +110,18 @@ typedef struct vb_hits_soa {
 } vb_hits_soa;
 VB_API int vb_trace_closest(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out);
 VB_API int vb_trace_any(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, uint8_t *occluded, vb_mem out_mem);
+/* vb_trace_closest with NO allocation. This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it). Same answers as vb_trace_closest, same in-call ray sort; its scratch memory (the persistent kernel's ray counter, sort keys,
+ * permutation, AoS ray copy, radix sort storage) is a file-scope `static __device__` array of VB_TRACE_STATIC_SCRATCH_BYTES
+ * (about 13 MiB) that every GPU which loads the library holds until exit. Calls no cudaMalloc / cudaFree or allocating library
+ * routine. Limits: rays and hits must be DEVICE buffers (VB_ERR_INVALID otherwise), n <= VB_TRACE_STATIC_MAX_RAYS per call
+ * (VB_ERR_INVALID with a message naming the limit; split larger batches). Every call on a device shares the one array: it is
+ * re-initialised at the start of each call on the context's stream, and calls that OVERLAP on the same GPU (two contexts or streams
+ * of one device) race - serialise them. */
+#define VB_TRACE_STATIC_MAX_RAYS (1u << 18)
+#define VB_TRACE_STATIC_SCRATCH_BYTES (256u + 4u * 4u * VB_TRACE_STATIC_MAX_RAYS + 32u * VB_TRACE_STATIC_MAX_RAYS + (1u << 20))
+VB_API int vb_trace_closest_static(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out);
 /* Record form: the reference's own data shapes at this boundary. vb_ray = ocarina Ray {org_min, dir_max} (32 bytes: geometry.h:64-69,
  * frame_buffer.h:88-91), vb_hit = TriangleHit {inst_id, prim_id, bary} (16 bytes: geometry.cpp:81-85,215-219); no distance, as in the
  * reference (compute_surface_interaction re-derives it). Same answers as the SoA form. Host buffers (mem = VB_MEM_HOST, ideally

@@ -81,6 +81,7 @@ def load_library() -> C.CDLL:
         "vb_accel_download": [vp, vp, vp],
         "vb_trace_closest": [vp, C.POINTER(vb_rays_soa), C.c_uint64, C.POINTER(vb_hits_soa)],
         "vb_trace_any": [vp, C.POINTER(vb_rays_soa), C.c_uint64, vp, C.c_int],
+        "vb_trace_closest_static": [vp, C.POINTER(vb_rays_soa), C.c_uint64, C.POINTER(vb_hits_soa)],
         "vb_trace_closest_records": [vp, vp, C.c_uint64, vp, C.c_int],
         "vb_trace_any_records": [vp, vp, C.c_uint64, vp, C.c_int],
         "vb_trace_closest_counted": [vp, C.POINTER(vb_rays_soa), C.c_uint64, C.POINTER(vb_hits_soa),
@@ -256,6 +257,17 @@ class Context:
         self._check(self.lib.vb_trace_closest(self.h, C.byref(r), n, C.byref(h)), "vb_trace_closest")
         return out
 
+    def trace_closest_static(self, rays: dict, out: dict):
+        """vb_trace_closest_static: device buffers only, n <= VB_TRACE_STATIC_MAX_RAYS, allocates nothing (the caller passes `out`)"""
+        n = rays["ox"].shape[0]
+        r = self._rays_struct(rays)
+        h = vb_hits_soa()
+        for f in HIT_FIELDS:
+            setattr(h, f, _ptr(out[f]))
+        h.mem = VB_MEM_DEVICE if _is_device(out["inst"]) else VB_MEM_HOST
+        self._check(self.lib.vb_trace_closest_static(self.h, C.byref(r), n, C.byref(h)), "vb_trace_closest_static")
+        return out
+
     def trace_any(self, rays: dict, out=None, counted: bool = False):
         n = rays["ox"].shape[0]
         if out is None:
@@ -405,6 +417,7 @@ def load_cie_1nm() -> np.ndarray:
 
 VB_MAT_DIFFUSE, VB_MAT_MIRROR, VB_MAT_GLASS, VB_MAT_METAL, VB_MAT_SUBSTRATE, VB_MAT_PRINCIPLED, VB_MAT_BLACK_BODY = range(7)
 VB_MAT_PLASTIC, VB_MAT_METALLIC, VB_MAT_MIX, VB_MAT_ADD = 7, 8, 9, 10
+VB_TRACE_STATIC_MAX_RAYS = 1 << 18
 VB_LIGHT_AREA, VB_LIGHT_POINT, VB_LIGHT_SPOT, VB_LIGHT_ENV, VB_LIGHT_PROJECTOR, VB_LIGHT_DIRECTIONAL = range(6)
 VB_LIGHT_SAMPLER_UNIFORM, VB_LIGHT_SAMPLER_POWER = 0, 1
 VB_FILTER_BOX, VB_FILTER_TRIANGLE, VB_FILTER_FITTED = 0, 1, 2

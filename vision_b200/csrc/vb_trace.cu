@@ -4,6 +4,7 @@
 #include "vb_internal.h"
 #include "vb_trace.cuh"
 #include <algorithm>
+#include <mutex>
 #include <cub/device/device_radix_sort.cuh>
 
 namespace {
@@ -506,6 +507,43 @@ int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *
     return VB_OK;
 }
 
+// ---- vb_trace_closest_static: closest-hit batch trace that allocates nothing (include/vision_b200.h) ----
+// Everything run_trace takes from growable buffers (the persistent kernel's ray counter, and for the in-call ray sort the Morton keys,
+// the permutation, the AoS copy of the rays and the radix sort's temporary storage) lives in ONE file-scope device array of fixed
+// size. g_static_scratch names that array for DEVICE code; host code only ever passes the address cudaGetSymbolAddress returned for
+// the device that is current (the host-side symbol is a stand-in, not a device pointer).
+namespace {
+
+constexpr uint64_t STATIC_MAX_RAYS = VB_TRACE_STATIC_MAX_RAYS;
+constexpr size_t STATIC_CNT_BYTES = 256;                               // nodes, tris, pad, pad, next_ray: cleared every call
+constexpr size_t STATIC_KEY_BYTES = STATIC_MAX_RAYS * 4;               // one of k0, k1, v0, v1
+constexpr size_t STATIC_AOS_BYTES = STATIC_MAX_RAYS * 32;
+constexpr size_t STATIC_CUB_BYTES = 1u << 20;                          // radix sort temporary storage (checked against the query)
+constexpr size_t STATIC_SCRATCH_BYTES = STATIC_CNT_BYTES + 4 * STATIC_KEY_BYTES + STATIC_AOS_BYTES + STATIC_CUB_BYTES;
+static_assert(STATIC_SCRATCH_BYTES == VB_TRACE_STATIC_SCRATCH_BYTES, "include/vision_b200.h states the size of the static scratch");
+
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+std::mutex g_static_mu;
+unsigned char *g_static_ptr[STATIC_MAX_DEVICES] = {};                  // device address of g_static_scratch, per device ordinal
+
+// once per device, with that device current: the array's address on THAT device
+int static_scratch_address(vb_ctx *ctx, unsigned char **out) {
+    if (ctx->device < 0 || ctx->device >= STATIC_MAX_DEVICES) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_trace_closest_static: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[ctx->device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) return ctx->fail(VB_ERR_CUDA, std::string("vb_trace_closest_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+        g_static_ptr[ctx->device] = (unsigned char *)p;
+    }
+    *out = g_static_ptr[ctx->device];
+    return VB_OK;
+}
+
+}  // namespace
+
 extern "C" {
 
 int vb_trace_closest(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out) {
@@ -519,6 +557,52 @@ int vb_trace_closest_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit
 }
 int vb_trace_any_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, uint8_t *occluded, vb_mem mem) {
     return run_trace_records(ctx, rays, n, nullptr, occluded, mem, true);
+}
+int vb_trace_closest_static(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out) {
+    if (!ctx) return VB_ERR_INVALID;
+    const char *fn = "vb_trace_closest_static";
+    if (!ctx->accel.built) return ctx->fail(VB_ERR_STATE, std::string(fn) + ": accel not built");
+    if (!rays || !out) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": null argument");
+    if (rays->mem != VB_MEM_DEVICE || out->mem != VB_MEM_DEVICE)
+        return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": rays and hits must be device buffers (host buffers need staging memory: use vb_trace_closest)");
+    if (n > STATIC_MAX_RAYS)
+        return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": " + std::to_string(n) + " rays exceed the static scratch's maximum of " +
+                                             std::to_string(STATIC_MAX_RAYS) + " (VB_TRACE_STATIC_MAX_RAYS) per call; split the batch or use vb_trace_closest");
+    if (n == 0) return VB_OK;
+    cudaSetDevice(ctx->device);
+    unsigned char *sb = nullptr;
+    int rc = static_scratch_address(ctx, &sb);
+    if (rc) return rc;
+    cudaStream_t st = ctx->stream;
+    unsigned long long *d_cnt = (unsigned long long *)sb;
+    VB_CUDA(cudaMemsetAsync(d_cnt, 0, STATIC_CNT_BYTES, st));          // the array keeps the last call's contents: the ray counter must start at 0
+    RaysDev R{rays->ox, rays->oy, rays->oz, rays->tmin, rays->dx, rays->dy, rays->dz, rays->tmax};
+    HitsDev H{out->inst, out->prim, out->u, out->v, out->t};
+    VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctx->opt_blocks_per_sm, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+    const float4 *RS = nullptr; const uint32_t *perm = nullptr;
+    if (ctx->opt_sort_rays && n >= (uint64_t)ctx->opt_sort_min_rays) {      // same in-call ray sort as run_trace, over the static scratch
+        uint32_t *k0 = (uint32_t *)(sb + STATIC_CNT_BYTES), *k1 = (uint32_t *)(sb + STATIC_CNT_BYTES + STATIC_KEY_BYTES);
+        uint32_t *v0 = (uint32_t *)(sb + STATIC_CNT_BYTES + 2 * STATIC_KEY_BYTES), *v1 = (uint32_t *)(sb + STATIC_CNT_BYTES + 3 * STATIC_KEY_BYTES);
+        float4 *d_aos = (float4 *)(sb + STATIC_CNT_BYTES + 4 * STATIC_KEY_BYTES);
+        void *cub_tmp = sb + STATIC_CNT_BYTES + 4 * STATIC_KEY_BYTES + STATIC_AOS_BYTES;
+        size_t cub_bytes = 0;
+        cub::DoubleBuffer<uint32_t> dk0(nullptr, nullptr), dv0(nullptr, nullptr);
+        VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk0, dv0, (int)n, 0, 24, st));      // size query only
+        if (cub_bytes > STATIC_CUB_BYTES) return ctx->fail(VB_ERR_UNSUPPORTED, std::string(fn) + ": radix sort temporary storage exceeds the static reserve");
+        float3 lo = make_float3(ctx->sort_lo[0], ctx->sort_lo[1], ctx->sort_lo[2]);
+        float3 ie = make_float3(1.f / fmaxf(ctx->sort_hi[0] - ctx->sort_lo[0], 1e-30f), 1.f / fmaxf(ctx->sort_hi[1] - ctx->sort_lo[1], 1e-30f),
+                                1.f / fmaxf(ctx->sort_hi[2] - ctx->sort_lo[2], 1e-30f));
+        k_ray_keys<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(R, (uint32_t)n, lo, ie, k0, v0, d_aos, (uint32_t)ctx->opt_sort_oct_shift);
+        cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
+        cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)n, 0, 24, st);
+        if (ce != cudaSuccess) return ctx->fail(VB_ERR_CUDA, std::string(fn) + ": ray sort: " + cudaGetErrorString(ce));
+        perm = dv.Current();
+        RS = d_aos;
+    }
+    k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, nullptr, d_cnt, d_cnt + 4, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+    VB_CHECK_LAUNCH();
+    return VB_OK;
 }
 int vb_trace_closest_counted(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out,
                              uint64_t *nodes_popped, uint64_t *tris_tested) {
