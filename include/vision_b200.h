@@ -65,6 +65,10 @@ VB_API int vb_mesh_upload(vb_ctx *ctx, const float *pos3, const float *nrm3, con
                           const uint32_t *tri3, uint32_t nt, uint32_t *mesh_id);
 /* non-indexed triangle soup already resident on host or device: triangle i = vertices 3i..3i+2 */
 VB_API int vb_mesh_upload_soup(vb_ctx *ctx, const float *pos9, vb_mem mem, uint64_t nt, uint32_t *mesh_id);
+/* Releases every mesh, the instance list and the acceleration structure of the context (mesh ids start at 0 again): what
+ * Geometry::clear / a scene reload does in the reference (Pipeline::clear_geometry, src/base/mgr/pipeline.cpp:284-288). Without it a reused
+ * context keeps every scene's meshes until vb_ctx_destroy. */
+VB_API int vb_meshes_clear(vb_ctx *ctx);
 
 /* InstanceData of the reference (src/base/shape.h:21-33): encoded ids + object-to-world.
  * o2w is column-major 4x4 (m[3] = translation), as the reference's float4x4. Array index = inst_id. */
@@ -88,6 +92,8 @@ typedef struct vb_build_stats {
     uint64_t node_bytes, tri_bytes;
     double build_ms;           /* device time of the whole build */
     float scene_lo[3], scene_hi[3];
+    uint64_t n_references;     /* leaves of the BVH: n_triangles plus the extra references of triangle pre-splitting (option
+                                * "build.split_pct"); tri_bytes = 48 * n_references, and vb_accel_download's `tris` holds that many */
 } vb_build_stats;
 /* flattens instances to world space, builds the compressed 8-wide BVH on the GPU */
 VB_API int vb_accel_build(vb_ctx *ctx, const vb_build_opts *opts, vb_build_stats *out);

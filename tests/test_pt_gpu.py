@@ -136,3 +136,52 @@ def test_only_direct_supplement_matches_oracle(vbctx, oracle, name, ov, max_dept
         # the supplement adds light: the same scene rendered with MIS mode "light" only (no supplement) is darker where BSDF
         # sampling finds the emitter
         assert films[0][..., :3].mean() > 0.0
+
+
+def test_malformed_records_are_refused_at_render_time(vbctx):
+    """C-ABI validation where instances, meshes and textures are all known (pt_launch): an area light must name an existing
+    instance and carry one alias entry per triangle of its mesh; every texture slot must name an uploaded texture"""
+    import copy
+    path = ROOT / "scenes" / "cbox" / "cbox_materials.json"
+    good = scene_py.build_scene(path, {"resolution": [32, 32], "spp": 1})
+
+    def render(sc):
+        vbctx.upload_scene(sc)
+        vbctx.film_clear()
+        vbctx.render_frames(0, 1, 1, capi.VB_ACCUM_LERP)
+
+    def clone():
+        sc = scene_py.build_scene(path, {"resolution": [32, 32], "spp": 1})
+        return sc
+
+    render(good)
+    area = next(i for i, l in enumerate(good.lights) if l.type == capi.VB_LIGHT_AREA)
+    sc = clone(); sc.lights[area].inst_id = len(sc.instances) + 3
+    with pytest.raises(capi.VbError, match="area light inst_id out of range"):
+        render(sc)
+    sc = clone(); sc.lights[area].alias_size += 1
+    with pytest.raises(capi.VbError, match="alias"):
+        render(sc)
+    sc = clone(); sc.materials[0].color.tex_id = len(sc.textures) + 5
+    with pytest.raises(capi.VbError, match="material slot tex_id out of range"):
+        render(sc)
+    sc = clone(); sc.lights[area].color.tex_id = 10_000
+    with pytest.raises(capi.VbError, match="light colour tex_id out of range"):
+        render(sc)
+    render(good)                                   # and the context is still usable
+
+
+def test_reused_context_drops_the_previous_scene(vbctx):
+    """upload_scene on a reused context releases the earlier scene's meshes (vb_meshes_clear): mesh ids restart at 0, and a
+    cleared context refuses to trace until a new scene is built"""
+    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_materials.json", {"resolution": [32, 32], "spp": 1})
+    for _ in range(3):
+        vbctx.upload_scene(sc)
+        assert vbctx.mesh_upload(sc.meshes[0]["pos"], sc.meshes[0]["tri"]) == len(sc.meshes)      # ids did not grow
+    vbctx.meshes_clear()
+    with pytest.raises(capi.VbError, match="accel not built"):
+        vbctx.render_frames(0, 1, 1, capi.VB_ACCUM_LERP)
+    vbctx.upload_scene(sc)
+    vbctx.film_clear()
+    vbctx.render_frames(0, 1, 1, capi.VB_ACCUM_LERP)
+    assert vbctx.film_download(capi.VB_FILM_ACCUM)[..., :3].mean() > 0.01

@@ -260,3 +260,34 @@ def test_record_form_equals_soa_form(vbctx):
     assert vbctx.trace_closest_records(rec[:0]).shape == (0, 4)
     check_small = vbctx.trace_closest_records(np.ascontiguousarray(rec[:5])).view(np.uint32)
     assert np.array_equal(check_small[:, 1], want["prim"][:5])
+
+
+def test_trees_deeper_than_the_traversal_stack_are_refused(vbctx, oracle):
+    """The traversal stack holds 64 entries, one per wide level in the worst case; a deeper tree would drop pushes and skip subtrees
+    silently. The build therefore checks the depth: a clustering (PLOC) tree that is too deep is rebuilt as a radix tree (bounded
+    depth), and a tree that is still too deep is refused. "build.max_levels" lowers the accepted depth so that both steps can be
+    exercised (no float geometry makes a 64-level wide tree: an agglomerative chain needs positions growing by 2x per element)."""
+    from vision_b200 import capi
+    mesh = oracle.synth_mesh(20000, seed=51)
+    rays = oracle.synth_rays(20000, seed=52, seed_any=53)
+    acc = oracle.accel()
+    acc.add_soup(mesh)
+    acc.build(4)
+    want = acc.trace_closest(rays, threads=8)
+    try:
+        vbctx.set_option("build.ploc", 1)
+        vbctx.set_option("build.max_levels", 3)                      # 8^3 < 20000 leaves: no tree fits
+        vbctx.profile_reset()
+        with pytest.raises(capi.VbError, match="deeper than the traversal stack"):
+            _build_soup(vbctx, mesh)
+        assert vbctx.profile_get("bvh_build_radix_fallback")[1] == 1         # clustering first, then the radix tree, then refused
+        with pytest.raises(capi.VbError, match="accel not built"):
+            vbctx.trace_closest(rays)
+        vbctx.set_option("build.max_levels", 64)
+        vbctx.profile_reset()
+        _build_soup(vbctx, mesh)
+        assert vbctx.profile_get("bvh_build_radix_fallback")[1] == 0
+        _compare_closest(vbctx.trace_closest(rays), want)
+    finally:
+        vbctx.set_option("build.ploc", -1)
+        vbctx.set_option("build.max_levels", 64)

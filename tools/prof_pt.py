@@ -21,9 +21,12 @@ import os
 ctx = Context(0)
 if "VB_PLOC" in os.environ:
     ctx.set_option("build.ploc", int(os.environ["VB_PLOC"]))
+if "VB_SPLIT" in os.environ:
+    ctx.set_option("build.split_pct", int(os.environ["VB_SPLIT"]))
 if "VB_SIZE_CLASSES" in os.environ:
     ctx.set_option("build.size_classes", int(os.environ["VB_SIZE_CLASSES"]))
-ctx.upload_scene(sc)
+bst = ctx.upload_scene(sc)
+print("build:", bst)
 ctx.set_option("pt.schedule", int(os.environ.get("VB_SCHED", "0")))
 if "VB_MAX_PATHS" in os.environ:
     ctx.set_option("pt.max_paths", int(os.environ["VB_MAX_PATHS"]))

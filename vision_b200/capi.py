@@ -41,7 +41,7 @@ class vb_build_opts(C.Structure):
 class vb_build_stats(C.Structure):
     _fields_ = [("n_triangles", C.c_uint64), ("n_nodes", C.c_uint64), ("node_bytes", C.c_uint64),
                 ("tri_bytes", C.c_uint64), ("build_ms", C.c_double),
-                ("scene_lo", C.c_float * 3), ("scene_hi", C.c_float * 3)]
+                ("scene_lo", C.c_float * 3), ("scene_hi", C.c_float * 3), ("n_references", C.c_uint64)]
 
 
 class vb_rays_soa(C.Structure):
@@ -77,6 +77,7 @@ def load_library() -> C.CDLL:
         "vb_mesh_upload": [vp, vp, vp, vp, C.c_uint32, vp, C.c_uint32, _u32p],
         "vb_mesh_upload_soup": [vp, vp, C.c_int, C.c_uint64, _u32p],
         "vb_instances_set": [vp, C.POINTER(vb_instance), C.c_uint32],
+        "vb_meshes_clear": [vp],
         "vb_accel_build": [vp, C.POINTER(vb_build_opts), C.POINTER(vb_build_stats)],
         "vb_accel_download": [vp, vp, vp],
         "vb_trace_closest": [vp, C.POINTER(vb_rays_soa), C.c_uint64, C.POINTER(vb_hits_soa)],
@@ -169,6 +170,9 @@ class Context:
         return ms.value, n.value
 
     # -- geometry ---------------------------------------------------------------------
+    def meshes_clear(self):
+        self._check(self.lib.vb_meshes_clear(self.h), "vb_meshes_clear")
+
     def mesh_upload(self, pos, tri, nrm=None, uv=None) -> int:
         pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
         tri = np.ascontiguousarray(tri, np.uint32).reshape(-1, 3)
@@ -210,7 +214,7 @@ class Context:
         opts = vb_build_opts(0)
         self._check(self.lib.vb_accel_build(self.h, C.byref(opts), C.byref(st)), "vb_accel_build")
         return {"n_triangles": st.n_triangles, "n_nodes": st.n_nodes, "node_bytes": st.node_bytes,
-                "tri_bytes": st.tri_bytes, "build_ms": st.build_ms,
+                "tri_bytes": st.tri_bytes, "build_ms": st.build_ms, "n_references": st.n_references,
                 "scene_lo": list(st.scene_lo), "scene_hi": list(st.scene_hi)}
 
     def accel_download(self, n_nodes: int, n_tris: int):
@@ -511,6 +515,7 @@ def _pt_methods():
     def upload_scene(self, sc: SceneRecords):
         """meshes + instances + BVH + tables + camera + film"""
         _bind_pt(self.lib)
+        self.meshes_clear()                  # a reused context drops the previous scene's meshes (mesh ids restart at 0)
         ids = [self.mesh_upload(m["pos"], m["tri"], m.get("nrm"), m.get("uv")) for m in sc.meshes]
         inst = [dict(d, mesh_id=ids[d["mesh_id"]]) for d in sc.instances]
         self.instances_set(inst)

@@ -27,7 +27,7 @@ __host__ __device__ __forceinline__ float ord2f(uint32_t u) {
 
 struct BuildBufs {
     float4 *tri_in;        // 3*T  flattened triangles (unsorted)
-    float4 *blo, *bhi;     // T    triangle bounds (unpadded)
+    float4 *blo, *bhi;     // T    leaf bounds (unpadded): a triangle, or one piece of it (vb_bvh_split.cuh); blo.w = bits of the triangle index
     uint32_t *scene;       // 6    ordered-uint scene bounds: lo xyz, hi xyz
     uint64_t *keys, *keys2;
     uint32_t *vals, *vals2;
@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(256) k_flatten(const InstGeom *inst, const uin
         hi = make_float3(fmaxf(p0.x, fmaxf(fmaxf(p1.x, q1.x), fmaxf(p2.x, q2.x))),
                          fmaxf(p0.y, fmaxf(fmaxf(p1.y, q1.y), fmaxf(p2.y, q2.y))),
                          fmaxf(p0.z, fmaxf(fmaxf(p1.z, q1.z), fmaxf(p2.z, q2.z))));
-        b.blo[g] = make_float4(lo.x, lo.y, lo.z, 0.f);
+        b.blo[g] = make_float4(lo.x, lo.y, lo.z, __uint_as_float(g));
         b.bhi[g] = make_float4(hi.x, hi.y, hi.z, 0.f);
         m[0] = 0.5 * ((double)lo.x + (double)hi.x); m[1] = 0.5 * ((double)lo.y + (double)hi.y); m[2] = 0.5 * ((double)lo.z + (double)hi.z);
         m[3] = m[0] * m[0]; m[4] = m[1] * m[1]; m[5] = m[2] * m[2];
@@ -119,7 +119,7 @@ __device__ __forceinline__ uint64_t expand21(uint32_t v) {   // spread 21 bits t
 // (walls, floors, ground planes) from the many small ones before it splits space: each class is an LBVH over
 // similar-sized boxes, and a huge box no longer inflates every ancestor of a leaf deep inside the fine geometry
 // (extended Morton codes, Vinkler et al. 2017, reduced to a prefix). Uniform meshes fall into one class.
-__global__ void __launch_bounds__(256) k_morton(uint32_t T, BuildBufs b, int size_classes) {
+__global__ void __launch_bounds__(256) k_morton(uint32_t T, uint32_t n_moments, BuildBufs b, int size_classes) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= T) return;                                   // (the last warp may be partial: __activemask below)
     float3 slo = make_float3(ord2f(b.scene[0]), ord2f(b.scene[1]), ord2f(b.scene[2]));
@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(256) k_morton(uint32_t T, BuildBufs b, int siz
     uint64_t cls = 0;
     {
         double var = 0.0;
-        for (int k = 0; k < 3; ++k) { double mean = b.moments[k] / T; var += fmax(0.0, b.moments[3 + k] / T - mean * mean); }
+        for (int k = 0; k < 3; ++k) { double mean = b.moments[k] / n_moments; var += fmax(0.0, b.moments[3 + k] / n_moments - mean * mean); }
         float D = 5.0f * (float)sqrt(var);                       // spread of the geometry (robust against a few far-out triangles)
         float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
         float diag = sqrtf(dx * dx + dy * dy + dz * dz);
@@ -215,5 +215,6 @@ __global__ void __launch_bounds__(256) k_refit(uint32_t T, BuildBufs b) {
 
 }  // namespace
 
+#include "vb_bvh_split.cuh"
 #include "vb_bvh_ploc.cuh"
 #include "vb_bvh_collapse.cuh"

@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n
             uint32_t first = c[j] >= T - 1 ? c[j] - (T - 1) : b.first[c[j]];
             leaf8 |= 1u << s;                        // one triangle per leaf slot, stored in slot order (vb_next_triangle)
             for (uint32_t t = 0; t < cntj; ++t) {
-                size_t src = 3 * (size_t)b.vals[first + t], dst = 3 * (size_t)(tri_base + tri_off + t);
+                size_t src = 3 * (size_t)__float_as_uint(b.blo[b.vals[first + t]].w), dst = 3 * (size_t)(tri_base + tri_off + t);   // reference -> its triangle
                 tris_out[dst] = b.tri_in[src]; tris_out[dst + 1] = b.tri_in[src + 1]; tris_out[dst + 2] = b.tri_in[src + 2];
             }
             tri_off += cntj;
@@ -140,7 +140,10 @@ template <class T> struct DevBuf {
 
 }  // namespace
 
-int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
+// One build. *too_deep = the wide tree has more levels than the traversal stack has entries (VB_TRAVERSAL_STACK_ENTRIES: one entry
+// per level is the worst case of vb_traverse); nothing is installed in that case.
+static int accel_build_once(vb_ctx *ctx, vb_build_stats *out, bool allow_ploc, bool *too_deep) {
+    *too_deep = false;
     cudaStream_t st = ctx->stream;
     uint32_t n_inst = (uint32_t)ctx->instances.size();
     if (n_inst == 0) return ctx->fail(VB_ERR_STATE, "vb_accel_build: no instances set");
@@ -163,41 +166,78 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     ctx->accel = vb_accel();
 
     DevBuf<InstGeom> d_geom; DevBuf<uint32_t> d_off;
-    DevBuf<float4> tri_in, blo, bhi, nlo, nhi;
+    DevBuf<float4> tri_in, blo, bhi, rlo, rhi, nlo, nhi;
     DevBuf<uint32_t> scene, vals, vals2, left, right, first, last, parent, flags;
     DevBuf<uint64_t> keys, keys2;
     DevBuf<double> moments; DevBuf<uint32_t> cls_count;
     DevBuf<WorkItem> q0, q1; DevBuf<Counters> cnt;
     VB_CUDA(d_geom.alloc(n_inst)); VB_CUDA(d_off.alloc(n_inst + 1));
     VB_CUDA(tri_in.alloc(3 * (size_t)T)); VB_CUDA(blo.alloc(T)); VB_CUDA(bhi.alloc(T));
-    VB_CUDA(nlo.alloc(2 * (size_t)T)); VB_CUDA(nhi.alloc(2 * (size_t)T));
-    VB_CUDA(scene.alloc(8)); VB_CUDA(vals.alloc(T)); VB_CUDA(vals2.alloc(T));
-    VB_CUDA(left.alloc(T)); VB_CUDA(right.alloc(T)); VB_CUDA(first.alloc(T)); VB_CUDA(last.alloc(T));
-    VB_CUDA(parent.alloc(2 * (size_t)T)); VB_CUDA(flags.alloc(T));
-    VB_CUDA(keys.alloc(T)); VB_CUDA(keys2.alloc(T));
-    VB_CUDA(moments.alloc(6)); VB_CUDA(cls_count.alloc(4));
-    VB_CUDA(q0.alloc(T)); VB_CUDA(q1.alloc(T)); VB_CUDA(cnt.alloc(1));
-    // worst case one wide node per 2 triangles is never reached; T+1 nodes is a safe bound
+    VB_CUDA(scene.alloc(8)); VB_CUDA(moments.alloc(8)); VB_CUDA(cls_count.alloc(4)); VB_CUDA(cnt.alloc(1));
     vb_wide_node *d_nodes = nullptr; float4 *d_tris = nullptr;
-    VB_CUDA(cudaMalloc(&d_nodes, ((size_t)T + 1) * sizeof(vb_wide_node)));
-    VB_CUDA(cudaMalloc(&d_tris, 3 * (size_t)T * sizeof(float4)));
 
-    BuildBufs b{tri_in.p, blo.p, bhi.p, scene.p, keys.p, keys2.p, vals.p, vals2.p, nlo.p, nhi.p,
-                left.p, right.p, first.p, last.p, parent.p, flags.p, cls_count.p, moments.p};
+    // the per-leaf buffers are sized after the pre-splitting pass (R references >= T triangles)
+    BuildBufs b{tri_in.p, blo.p, bhi.p, scene.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, cls_count.p, moments.p};
 
     cudaEvent_t e0 = ctx->get_event(), e1 = ctx->get_event();
     VB_CUDA(cudaMemcpyAsync(d_geom.p, hg.data(), sizeof(InstGeom) * n_inst, cudaMemcpyHostToDevice, st));
     VB_CUDA(cudaMemcpyAsync(d_off.p, off.data(), sizeof(uint32_t) * (n_inst + 1), cudaMemcpyHostToDevice, st));
     uint32_t scene_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
     VB_CUDA(cudaMemcpyAsync(scene.p, scene_init, sizeof(scene_init), cudaMemcpyHostToDevice, st));
-    VB_CUDA(cudaMemsetAsync(moments.p, 0, 6 * sizeof(double), st));
     VB_CUDA(cudaMemsetAsync(cls_count.p, 0, 4 * sizeof(uint32_t), st));
     VB_CUDA(cudaEventRecord(e0, st));
     uint64_t launches = 0;
     uint32_t grid = (T + 255) / 256;
+    VB_CUDA(cudaMemsetAsync(moments.p, 0, 8 * sizeof(double), st));
     k_flatten<<<grid, 256, 0, st>>>(d_geom.p, d_off.p, n_inst, T, b); launches++;
     VB_CHECK_LAUNCH();
-    k_morton<<<grid, 256, 0, st>>>(T, b, ctx->opt_size_classes); launches++;
+    // ---- triangle pre-splitting (vb_bvh_split.cuh): T triangles -> R references ----
+    const uint32_t T_tris = T;
+    if (ctx->opt_split_pct > 0 && T >= 8) {
+        DevBuf<float> prio; DevBuf<uint32_t> s_count, s_offs;
+        VB_CUDA(prio.alloc(T)); VB_CUDA(s_count.alloc(T)); VB_CUDA(s_offs.alloc(T));
+        k_split_priority<<<grid, 256, 0, st>>>(T, b, prio.p, moments.p + 6); launches++;
+        VB_CHECK_LAUNCH();
+        double psum = 0.0;
+        VB_CUDA(cudaMemcpyAsync(&psum, moments.p + 6, sizeof(double), cudaMemcpyDeviceToHost, st));
+        VB_CUDA(cudaStreamSynchronize(st));
+        if (psum > 0.0 && std::isfinite(psum)) {
+            const double budget = (double)T * ctx->opt_split_pct / 100.0;
+            k_split_count<<<grid, 256, 0, st>>>(T, prio.p, (float)(budget / psum), s_count.p); launches++;
+            size_t tmp_bytes = 0;
+            VB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, s_count.p, s_offs.p, (int)T, st));
+            int rc = ctx->ensure_stage(tmp_bytes);
+            if (rc) return rc;
+            VB_CUDA(cub::DeviceScan::ExclusiveSum(ctx->stage, tmp_bytes, s_count.p, s_offs.p, (int)T, st)); launches += 2;
+            uint32_t tail2[2];
+            VB_CUDA(cudaMemcpyAsync(&tail2[0], s_offs.p + (T - 1), 4, cudaMemcpyDeviceToHost, st));
+            VB_CUDA(cudaMemcpyAsync(&tail2[1], s_count.p + (T - 1), 4, cudaMemcpyDeviceToHost, st));
+            VB_CUDA(cudaStreamSynchronize(st));
+            const uint64_t R = (uint64_t)tail2[0] + tail2[1];
+            if (R > T && R <= 0x7fffffffull / 3) {
+                VB_CUDA(rlo.alloc(R)); VB_CUDA(rhi.alloc(R));
+                k_split_emit<<<(T + 127) / 128, 128, 0, st>>>(T, b, s_count.p, s_offs.p, rlo.p, rhi.p); launches++;
+                VB_CHECK_LAUNCH();
+                VB_CUDA(cudaStreamSynchronize(st));            // prio / s_count / s_offs are released at the end of this block
+                b.blo = rlo.p; b.bhi = rhi.p;
+                T = (uint32_t)R;
+            }
+        }
+    }
+    grid = (T + 255) / 256;
+    VB_CUDA(nlo.alloc(2 * (size_t)T)); VB_CUDA(nhi.alloc(2 * (size_t)T));
+    VB_CUDA(vals.alloc(T)); VB_CUDA(vals2.alloc(T));
+    VB_CUDA(left.alloc(T)); VB_CUDA(right.alloc(T)); VB_CUDA(first.alloc(T)); VB_CUDA(last.alloc(T));
+    VB_CUDA(parent.alloc(2 * (size_t)T)); VB_CUDA(flags.alloc(T));
+    VB_CUDA(keys.alloc(T)); VB_CUDA(keys2.alloc(T));
+    VB_CUDA(q0.alloc(T)); VB_CUDA(q1.alloc(T));
+    // worst case one wide node per 2 leaves is never reached; T+1 nodes is a safe bound
+    VB_CUDA(cudaMalloc(&d_nodes, ((size_t)T + 1) * sizeof(vb_wide_node)));
+    if (cudaMalloc(&d_tris, 3 * (size_t)T * sizeof(float4)) != cudaSuccess) { cudaFree(d_nodes); return ctx->fail(VB_ERR_CUDA, "vb_accel_build: out of device memory"); }
+    b.keys = keys.p; b.keys2 = keys2.p; b.vals = vals.p; b.vals2 = vals2.p; b.nlo = nlo.p; b.nhi = nhi.p;
+    b.left = left.p; b.right = right.p; b.first = first.p; b.last = last.p; b.parent = parent.p; b.flags = flags.p;
+    k_morton<<<grid, 256, 0, st>>>(T, T_tris, b, ctx->opt_size_classes); launches++;
     VB_CHECK_LAUNCH();
     {
         size_t tmp_bytes = 0;
@@ -219,7 +259,7 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     VB_CUDA(cudaMemcpyAsync(h_cls, cls_count.p, sizeof(h_cls), cudaMemcpyDeviceToHost, st));
     VB_CUDA(cudaStreamSynchronize(st));
     const bool want_ploc = ctx->opt_ploc < 0 ? (h_cls[2] + h_cls[3]) > 0 : ctx->opt_ploc != 0;
-    const bool ploc = want_ploc && T > 2;
+    const bool ploc = want_ploc && allow_ploc && T > 2;
     ctx->last_build_ploc = ploc;
     const uint32_t max_leaf = 1u;        // the traversal's slot-order triangle addressing needs one triangle per leaf slot
     if (ploc) {
@@ -252,7 +292,12 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
         uint32_t zero = 0;
         VB_CUDA(cudaMemcpyAsync(&cnt.p->next_items, &zero, 4, cudaMemcpyHostToDevice, st));
         std::swap(qin, qout);
-        if (++levels > 256) return ctx->fail(VB_ERR_STATE, "vb_accel_build: collapse did not terminate");
+        if (++levels > ctx->opt_max_levels && n_items) {          // a deeper tree would overflow the traversal stack: refuse it
+            cudaFree(d_nodes); cudaFree(d_tris);
+            ctx->ev_pool.push_back(e0); ctx->ev_pool.push_back(e1);
+            *too_deep = true;
+            return VB_OK;
+        }
     }
     VB_CUDA(cudaEventRecord(e1, st));
     VB_CUDA(cudaStreamSynchronize(st));
@@ -272,7 +317,8 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     ctx->accel.n_nodes = hc.n_nodes; ctx->accel.n_tris = T; ctx->accel.built = true;
 
     vb_build_stats &s = ctx->build_stats;
-    s.n_triangles = T; s.n_nodes = hc.n_nodes; s.node_bytes = (uint64_t)hc.n_nodes * sizeof(vb_wide_node); s.tri_bytes = (uint64_t)T * 48;
+    s.n_triangles = T_tris; s.n_nodes = hc.n_nodes; s.node_bytes = (uint64_t)hc.n_nodes * sizeof(vb_wide_node); s.tri_bytes = (uint64_t)T * 48;
+    s.n_references = T;
     s.build_ms = ms;
     for (int a = 0; a < 3; ++a) { s.scene_lo[a] = ord2f(hs[a]); s.scene_hi[a] = ord2f(hs[3 + a]); }
     // ray-sort box: mean +- 2.5 sigma of the triangle centroids, clipped to the scene box. Rays start on
@@ -281,7 +327,7 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     double hm[6];
     VB_CUDA(cudaMemcpy(hm, moments.p, sizeof(hm), cudaMemcpyDeviceToHost));
     for (int a = 0; a < 3; ++a) {
-        double mean = hm[a] / T, var = std::max(0.0, hm[3 + a] / T - mean * mean), sd = std::sqrt(var);
+        double mean = hm[a] / T_tris, var = std::max(0.0, hm[3 + a] / T_tris - mean * mean), sd = std::sqrt(var);
         double lo = std::max((double)s.scene_lo[a], mean - 2.5 * sd), hi = std::min((double)s.scene_hi[a], mean + 2.5 * sd);
         if (!(hi > lo)) { lo = s.scene_lo[a]; hi = s.scene_hi[a]; }
         ctx->sort_lo[a] = (float)lo; ctx->sort_hi[a] = (float)hi;
@@ -290,4 +336,20 @@ int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
     ctx->prof["all"].ms += ms; ctx->prof["all"].launches += launches;
     if (out) *out = s;
     return VB_OK;
+}
+
+// Agglomerative clustering can produce chain-like trees (nested shells: every merge adds one triangle to the cluster inside it) whose
+// wide form is deeper than the traversal stack; the radix tree's depth is bounded by its key length (63 Morton + 32 index bits, seven
+// binary levels per wide level on a chain), so such a scene is rebuilt with it. A tree that is still too deep is refused.
+int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
+    bool too_deep = false;
+    int rc = accel_build_once(ctx, out, true, &too_deep);
+    if (rc || !too_deep) return rc;
+    if (ctx->last_build_ploc) {
+        ctx->prof["bvh_build_radix_fallback"].launches += 1;          // visible through vb_profile_get
+        rc = accel_build_once(ctx, out, false, &too_deep);
+        if (rc || !too_deep) return rc;
+    }
+    return ctx->fail(VB_ERR_UNSUPPORTED, "vb_accel_build: the BVH is deeper than the traversal stack (" +
+                                             std::to_string(ctx->opt_max_levels) + " wide levels)");
 }

@@ -135,6 +135,8 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     else if (k == "trace.tri_thr") ctx->opt_tri_thr = (int)value;
     else if (k == "build.max_leaf") { if ((int)value != 1) return ctx->fail(VB_ERR_INVALID, "vb_ctx_set_option: build.max_leaf is fixed at 1 (one triangle per leaf slot)"); }
     else if (k == "build.ploc") ctx->opt_ploc = value < 0 ? -1 : (value != 0 ? 1 : 0);
+    else if (k == "build.max_levels") ctx->opt_max_levels = std::min(VB_TRAVERSAL_STACK_ENTRIES, std::max(1, (int)value));   // test hook: lower the depth the build accepts
+    else if (k == "build.split_pct") ctx->opt_split_pct = std::min(400, std::max(0, (int)value));
     else if (k == "build.size_classes") ctx->opt_size_classes = value != 0 ? 1 : 0;
     else if (k == "trace.sort_rays") ctx->opt_sort_rays = (int)value;
     else if (k == "trace.sort_oct_shift") ctx->opt_sort_oct_shift = std::min(21, std::max(0, (int)value));
@@ -233,6 +235,7 @@ int vb_mesh_upload(vb_ctx *ctx, const float *pos3, const float *nrm3, const floa
     *mesh_id = (uint32_t)ctx->meshes.size();
     ctx->meshes.push_back(m);
     ctx->accel.built = false;
+    ctx->geom_version++;
     return VB_OK;
 }
 
@@ -252,6 +255,7 @@ int vb_mesh_upload_soup(vb_ctx *ctx, const float *pos9, vb_mem mem, uint64_t nt,
     *mesh_id = (uint32_t)ctx->meshes.size();
     ctx->meshes.push_back(m);
     ctx->accel.built = false;
+    ctx->geom_version++;
     return VB_OK;
 }
 
@@ -268,6 +272,24 @@ int vb_instances_set(vb_ctx *ctx, const vb_instance *inst, uint32_t n) {
         VB_CUDA(cudaMemcpy(ctx->d_instances, inst, sizeof(vb_instance) * n, cudaMemcpyHostToDevice));
     }
     ctx->accel.built = false;
+    ctx->geom_version++;
+    return VB_OK;
+}
+
+int vb_meshes_clear(vb_ctx *ctx) {
+    if (!ctx) return VB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (auto &m : ctx->meshes) {
+        if (m.owns_pos) cudaFree(m.pos);
+        cudaFree(m.nrm); cudaFree(m.uv); cudaFree(m.tri);
+    }
+    ctx->meshes.clear();
+    ctx->instances.clear();
+    cudaFree(ctx->d_instances); ctx->d_instances = nullptr;
+    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
+    ctx->accel = vb_accel();
+    ctx->geom_version++;
     return VB_OK;
 }
 

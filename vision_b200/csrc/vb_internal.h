@@ -17,6 +17,9 @@
 
 #define VB_CHECK_LAUNCH() VB_CUDA(cudaGetLastError())
 
+// entries of the traversal stack (vb_trace.cuh: VB_SM_STACK in shared memory + VB_LOCAL_STACK in local memory); the build refuses deeper trees
+#define VB_TRAVERSAL_STACK_ENTRIES 64
+
 struct vb_device_mesh {
     float *pos = nullptr;      // 3*nv
     float *nrm = nullptr;      // 3*nv (may be null)
@@ -63,6 +66,7 @@ struct vb_ctx {
     std::string err;
     std::vector<vb_device_mesh> meshes;
     std::vector<vb_instance> instances;
+    uint64_t geom_version = 0;               // bumped by every mesh / instance change: the path tracer re-derives its tables only then
     vb_instance *d_instances = nullptr;
     vb_accel accel;
     vb_build_stats build_stats{};
@@ -79,6 +83,8 @@ struct vb_ctx {
     int opt_max_leaf = 1;
     int opt_ploc = -1;                       // build: 1 = PLOC clustering (vb_bvh_ploc.cuh), 0 = radix tree, -1 = automatic
     bool last_build_ploc = false;
+    int opt_max_levels = VB_TRAVERSAL_STACK_ENTRIES;    // build: deepest wide tree accepted (never more than the traversal stack holds)
+    int opt_split_pct = 0;                   // build: triangle pre-splitting budget, extra references in percent of the triangle count (vb_bvh_split.cuh)
     int opt_size_classes = 1;                // build: triangle size class as the top bits of the Morton sort key
     int opt_sort_rays = 1, opt_sort_min_rays = 1 << 16;
     int opt_sort_oct_shift = 0;              // ray sort key: direction octant above this many low Morton bits (vb_ray_sort_key)

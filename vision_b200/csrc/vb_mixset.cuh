@@ -3,7 +3,7 @@
 // sample_wi_impl, src/base/scattering/lobe.cpp:495-562,598-683). A LobeSet over the lobes of two child materials: each child is a
 // single Lobe or a principled set whose sub-lobes are pulled up (flatten) with sample_weight *= parent sample weight and
 // weight *= parent SAMPLE weight. Children are walked in order, so the flattened list never has to be materialised.
-// Included by vb_principled.cuh; compiled only into the PT_PRINCIPLED kernel instantiations (the "heavy" shading launch).
+// Included by vb_principled.cuh; compiled only into the PT_LOBESET kernel instantiations (the "heavy" shading launch of scenes that have mix / add).
 #pragma once
 
 namespace {

@@ -43,10 +43,12 @@ enum : int { PT_CONTINUE = 1, PT_SHADOW = 2, PT_VERTEX = 4, PT_LIGHT = 8 };
 // into a separate kernel instantiation so that scenes without it keep the lean kernel.
 // VARIANT = bit flags: PT_PRINCIPLED = the principled BSDF's code is compiled in, PT_HERO = hero spectrum: only those
 // variants carry the path's wavelengths; without the flag `swl` is a compile-time nullptr and every spec_* call folds away.
-enum : int { PT_LEAN = 0, PT_PRINCIPLED = 1, PT_HERO = 2 };
+// PT_LOBESET (only with PT_PRINCIPLED) = the mix / add materials' code (vb_mixset.cuh: two children, each possibly a principled set) is
+// compiled in as well; scenes with principled materials but no mix / add keep the smaller frame of the plain principled kernels.
+enum : int { PT_LEAN = 0, PT_PRINCIPLED = 1, PT_HERO = 2, PT_LOBESET = 4 };
 template <int VARIANT>
 __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay &ray, const VbHit &hit, VbRay &shadow, f3 &pending) {
-    constexpr bool PRINCIPLED = (VARIANT & PT_PRINCIPLED) != 0, HERO = (VARIANT & PT_HERO) != 0;
+    constexpr bool PRINCIPLED = (VARIANT & PT_PRINCIPLED) != 0, HERO = (VARIANT & PT_HERO) != 0, LOBESET = (VARIANT & PT_LOBESET) != 0;
     Swl wl;
     const Swl *swl = nullptr;
     if (HERO) { wl = swl_make(ps.swl); swl = &wl; }
@@ -150,7 +152,7 @@ __device__ __forceinline__ int pt_bounce(const PtScene &S, PathState &ps, VbRay 
         float f = phase_HG(dot(it.wo, wi), it.g);
         se.f = f3{f, f, f}; se.pdf = f; se.flags = 0;
         bs = phase_sample(it.g, it.wo, sampler);
-    } else if (PRINCIPLED && (S.materials[it.mat_id].type == VB_MAT_MIX || S.materials[it.mat_id].type == VB_MAT_ADD)) {
+    } else if (LOBESET && (S.materials[it.mat_id].type == VB_MAT_MIX || S.materials[it.mat_id].type == VB_MAT_ADD)) {
         mixset_shade(S, swl, it, wi, sampler, se, bs);
         hemisphere_discard(se, it.wo, wi, it.ng);
         hemisphere_discard(bs.eval, it.wo, bs.wi, it.ng);

@@ -225,7 +225,8 @@ struct vb_pt_state {
     uint32_t n_alias = 0;
     uint32_t lsel_offset = 0, lsel_size = 0; float lsel_integral = 0.f;     // vb_light_sampler_set
     uint32_t env_separate = 0; float env_prob = 0.f;                        // vb_light_sampler_env_set
-    bool has_principled = false;
+    bool has_principled = false;       // principled, mix or add in the scene: the heavy shading launch
+    bool has_lobeset = false;          // mix or add in the scene: the heavy launch's PT_LOBESET instantiation
     std::vector<DevMesh> h_meshes;
     DevMesh *d_meshes = nullptr;
     DevInst *d_inst = nullptr;
@@ -276,6 +277,8 @@ void vb_pt_destroy(vb_ctx *ctx) {
 // device tables for meshes/instances (the analogue of Geometry::upload, geometry.cpp:64-71)
 static int pt_sync_geometry(vb_ctx *ctx) {
     vb_pt_state *p = pt_state(ctx);
+    if (p->geom_version == ctx->geom_version) return VB_OK;         // meshes and instances unchanged since the tables were made
+    p->geom_version = ~0ull;
     cudaFree(p->d_meshes); cudaFree(p->d_inst); p->d_meshes = nullptr; p->d_inst = nullptr;
     std::vector<DevMesh> hm(ctx->meshes.size());
     for (size_t i = 0; i < hm.size(); ++i) hm[i] = DevMesh{ctx->meshes[i].pos, ctx->meshes[i].nrm, ctx->meshes[i].uv, ctx->meshes[i].tri};
@@ -306,6 +309,7 @@ static int pt_sync_geometry(vb_ctx *ctx) {
         VB_CUDA(cudaMalloc(&p->d_inst, sizeof(DevInst) * hi.size()));
         VB_CUDA(cudaMemcpy(p->d_inst, hi.data(), sizeof(DevInst) * hi.size(), cudaMemcpyHostToDevice));
     }
+    p->geom_version = ctx->geom_version;
     return VB_OK;
 }
 
@@ -355,6 +359,7 @@ int vb_materials_set(vb_ctx *ctx, const vb_material_rec *mat, uint32_t n) {
     uint32_t types = 0;
     for (uint32_t i = 0; i < n; ++i) types |= 1u << mat[i].type;
     p->n_mat_types = (uint32_t)__builtin_popcount(types);
+    p->has_lobeset = (types & ((1u << VB_MAT_MIX) | (1u << VB_MAT_ADD))) != 0;
     p->has_principled = (types & ((1u << VB_MAT_PRINCIPLED) | (1u << VB_MAT_MIX) | (1u << VB_MAT_ADD))) != 0;   // the lobe-SET materials: heavy shading launch
     p->h_mat.assign(mat, mat + n);
     p->spec_dirty = true;
@@ -562,6 +567,16 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
         if (mesh >= ctx->meshes.size() || (uint64_t)l.alias_size != ctx->meshes[mesh].nt)
             return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": area light alias_size differs from its instance's triangle count");
     }
+    // every texture slot of the material and light records must name an uploaded texture (eval_slot3 indexes S.textures with it)
+    {
+        const uint32_t n_tex = (uint32_t)p->tex_mem.size();
+        auto bad = [n_tex](const vb_slot &sl) { return sl.tex_id != VB_INVALID_ID && sl.tex_id >= n_tex; };
+        for (auto &m : p->h_mat)
+            if (bad(m.color) || bad(m.roughness) || bad(m.spec) || bad(m.ior) || bad(m.sigma))
+                return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": material slot tex_id out of range (vb_textures_set)");
+        for (auto &l : p->h_lights)
+            if (bad(l.color)) return ctx->fail(VB_ERR_INVALID, std::string(fn) + ": light colour tex_id out of range (vb_textures_set)");
+    }
     if (p->env_separate && p->env_light != VB_INVALID_ID && p->n_lights < 2)
         return ctx->fail(VB_ERR_UNSUPPORTED, std::string(fn) + ": env_separate needs a light besides the environment light");
     int rc = pt_sync_geometry(ctx);
@@ -651,9 +666,9 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     VB_CUDA(cudaMemsetAsync(p->d_counters, 0, sizeof(PtCounters), ctx->stream));
     ctx->prof_begin("path_trace", 1);
     if (dump) k_path_trace<true, PT_LEAN><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, 1, 1, mode, 0, p->rt, p->accum, p->d_counters, hi, hp, hu, hv, ht);
-    else if (S.params.spectrum == VB_SPECTRUM_HERO) k_path_trace<false, PT_HERO | PT_PRINCIPLED><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt,
+    else if (S.params.spectrum == VB_SPECTRUM_HERO) k_path_trace<false, PT_HERO | PT_PRINCIPLED | PT_LOBESET><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt,
                                                                                                                p->accum, p->d_counters, nullptr, nullptr, nullptr, nullptr, nullptr);
-    else if (p->has_principled) k_path_trace<false, PT_PRINCIPLED><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum,
+    else if (p->has_principled) k_path_trace<false, PT_PRINCIPLED | PT_LOBESET><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum,
                                                                                            p->d_counters, nullptr, nullptr, nullptr, nullptr, nullptr);
     else k_path_trace<false, PT_LEAN><<<grid, PT_BLOCK, 0, ctx->stream>>>(S, first, n_frames, stride, mode, p->frames_done, p->rt, p->accum, p->d_counters,
                                                                        nullptr, nullptr, nullptr, nullptr, nullptr);

@@ -84,8 +84,12 @@ static int wf_render_batch(vb_ctx *ctx, vb_pt_state *p, vb_wf_buffers &w, const 
     VB_CHECK_LAUNCH();
     uint32_t n = S.params.max_depth ? P : 0;
     int cur = 0;
-    const uint32_t max_iter = 4 * S.params.max_depth + 64;      // medium boundaries do not count as bounces
-    for (uint32_t iter = 0; n && iter < max_iter; ++iter) {
+    // The loop runs until every path has finished, like the megakernel's per-path loop: crossings of material-less medium boundaries
+    // do not count as bounces, so max_depth does not bound the iterations. The cap only turns a queue that never drains (a bug) into
+    // an error instead of a hang; paths are never dropped.
+    const uint32_t max_iter = 1u << 16;
+    for (uint32_t iter = 0; n; ++iter) {
+        if (iter >= max_iter) return ctx->fail(VB_ERR_STATE, "vb_render_frames: the wavefront queue did not drain after 65536 iterations");
         uint64_t *k0 = w.keys[2 * cur], *k1 = w.keys[2 * cur + 1];
         WfQueue Qin{w.rays[cur], k0, w.slot_q[cur]};
         WfQueue Qout{w.rays[cur ^ 1], w.keys[2 * (cur ^ 1)], w.slot_q[cur ^ 1]};
@@ -111,14 +115,17 @@ static int wf_render_batch(vb_ctx *ctx, vb_pt_state *p, vb_wf_buffers &w, const 
                     case PT_LEAN: VB_SHADE(PT_LEAN); break;
                     case PT_PRINCIPLED: VB_SHADE(PT_PRINCIPLED); break;
                     case PT_HERO: VB_SHADE(PT_HERO); break;
-                    default: VB_SHADE(PT_HERO | PT_PRINCIPLED); break;
+                    case PT_HERO | PT_PRINCIPLED: VB_SHADE(PT_HERO | PT_PRINCIPLED); break;
+                    case PT_PRINCIPLED | PT_LOBESET: VB_SHADE(PT_PRINCIPLED | PT_LOBESET); break;
+                    default: VB_SHADE(PT_HERO | PT_PRINCIPLED | PT_LOBESET); break;
                 }
 #undef VB_SHADE
             };
             const int base = hero ? PT_HERO : PT_LEAN;
+            const int heavy = base | PT_PRINCIPLED | (p->has_lobeset ? PT_LOBESET : 0);
             if (!p->has_principled) shade(base, 0);
-            else if (order && ctx->opt_pt_split_principled) { shade(base, 1); shade(base | PT_PRINCIPLED, 2); }   // material-ordered queue: two launches
-            else shade(base | PT_PRINCIPLED, 0);
+            else if (order && ctx->opt_pt_split_principled) { shade(base, 1); shade(heavy, 2); }   // material-ordered queue: two launches
+            else shade(heavy, 0);
         }
         ctx->prof_end();
         VB_CHECK_LAUNCH();

@@ -13,6 +13,9 @@
 
 #define VB_SM_STACK 12
 #define VB_LOCAL_STACK 52
+#ifdef VB_TRAVERSAL_STACK_ENTRIES
+static_assert(VB_SM_STACK + VB_LOCAL_STACK == VB_TRAVERSAL_STACK_ENTRIES, "vb_internal.h states the traversal stack size the build checks against");
+#endif
 
 struct VbRay { float ox, oy, oz, tmin, dx, dy, dz, tmax; };
 struct VbHit { uint32_t inst, prim; float u, v, t; };
