@@ -23,8 +23,81 @@ __device__ __forceinline__ uint32_t quant_exp(float extent) {
     return min(e, 254u);
 }
 
+
+// ---- cost-optimal collapse (dynamic programme over the binary tree, after Ylitie, Karras & Laine 2017) ----
+// A ray visits a wide node iff it hits the node's box in its parent, so the expected number of node visits per ray is
+// proportional to the SUM OF THE WIDE NODES' BOX AREAS; triangles sit in their own leaf slots with their own boxes whatever
+// the topology, so their cost is a constant. For every binary node n and every slot budget i = 1..7:
+//   c(n, 1) = A(n) + D(n, 8)                       n becomes a wide node; its subtree is dealt over that node's 8 slots
+//   c(n, i) = min(D(n, i), c(n, i - 1))            n is dissolved into its parent's wide node and may use up to i slots there
+//   D(n, j) = min over 0 < k < j of c(left, k) + c(right, j - k),     c(triangle, .) = 0
+// k_collapse_cost fills c bottom-up (second arrival at a node computes it, like k_refit); k_collapse re-derives the
+// arg-min choices top-down. The greedy rule (open the largest child until 8) fills the bottom of the tree badly - a 9-triangle
+// subtree becomes a 7-triangle node with a 2-triangle child - and that is where most nodes are.
+#define VB_DP_W 7
+__device__ __forceinline__ float dp_cost(const float *dp, uint32_t T, uint32_t x, int i) {          // c(x, i), i in 1..7
+    return x >= T - 1 ? 0.f : __ldcg(dp + (size_t)x * VB_DP_W + (i - 1));
+}
+__device__ __forceinline__ float dp_distribute(const float *dp, uint32_t T, uint32_t L, uint32_t R, int j, int &best_k) {
+    float best = FLT_MAX; best_k = 1;
+    for (int k = 1; k < j; ++k) {
+        float c = dp_cost(dp, T, L, min(k, VB_DP_W)) + dp_cost(dp, T, R, min(j - k, VB_DP_W));
+        if (c < best) { best = c; best_k = k; }
+    }
+    return best;
+}
+__global__ void __launch_bounds__(256) k_collapse_cost(uint32_t T, BuildBufs b, float *dp) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= T || T == 1) return;
+    uint32_t p = b.parent[T - 1 + g];
+    while (p != 0xffffffffu) {
+        __threadfence();
+        if (atomicAdd(&b.flags[p], 1u) == 0) return;
+        uint32_t L = b.left[p], R = b.right[p];
+        float cl[VB_DP_W], cr[VB_DP_W];
+#pragma unroll
+        for (int i = 0; i < VB_DP_W; ++i) { cl[i] = dp_cost(dp, T, L, i + 1); cr[i] = dp_cost(dp, T, R, i + 1); }
+        float c[VB_DP_W + 1];                        // c[j - 1] for j = 1..8, c[7] = D(p, 8)
+#pragma unroll
+        for (int j = 2; j <= 8; ++j) {
+            float best = FLT_MAX;
+#pragma unroll
+            for (int k = 1; k < j; ++k) if (k <= VB_DP_W && j - k <= VB_DP_W) best = fminf(best, cl[k - 1] + cr[j - k - 1]);
+            c[j - 1] = best;
+        }
+        c[0] = half_area(b.nlo[p], b.nhi[p]) + c[7];
+#pragma unroll
+        for (int i = 1; i < VB_DP_W; ++i) c[i] = fminf(c[i], c[i - 1]);
+#pragma unroll
+        for (int i = 0; i < VB_DP_W; ++i) dp[(size_t)p * VB_DP_W + i] = c[i];
+        p = b.parent[p];
+    }
+}
+// children of the wide node rooted at binary node `root` under the cost table: at most 8, in c[]
+__device__ __forceinline__ int dp_children(const float *dp, uint32_t T, const BuildBufs &b, uint32_t root, uint32_t *c) {
+    uint32_t st_node[8]; int st_j[8]; int sp = 0, n = 0, k;
+    {
+        uint32_t L = b.left[root], R = b.right[root];
+        dp_distribute(dp, T, L, R, 8, k);
+        st_node[sp] = R; st_j[sp++] = 8 - k; st_node[sp] = L; st_j[sp++] = k;
+    }
+    while (sp) {
+        uint32_t x = st_node[--sp]; int j = min(st_j[sp], VB_DP_W);
+        for (;;) {
+            if (x >= T - 1 || j == 1) { c[n++] = x; break; }
+            uint32_t L = b.left[x], R = b.right[x];
+            float d = dp_distribute(dp, T, L, R, j, k);
+            if (d < dp_cost(dp, T, x, j - 1)) {            // dissolve x: its children share the j slots
+                st_node[sp] = R; st_j[sp++] = j - k;
+                x = L; j = k;
+            } else j--;
+        }
+    }
+    return n;
+}
+
 __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n_in, WorkItem *out, Counters *cnt,
-                                                  uint32_t T, BuildBufs b, vb_wide_node *nodes, float4 *tris_out, uint32_t max_leaf) {
+                                                  uint32_t T, BuildBufs b, vb_wide_node *nodes, float4 *tris_out, uint32_t max_leaf, const float *dp) {
     uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= n_in) return;
     WorkItem it = in[w];
@@ -33,6 +106,7 @@ __global__ void __launch_bounds__(128) k_collapse(const WorkItem *in, uint32_t n
 
     uint32_t c[8]; int n;
     if (leaf_like(it.bvh2)) { c[0] = it.bvh2; n = 1; }
+    else if (dp) n = dp_children(dp, T, b, it.bvh2, c);
     else {
         c[0] = b.left[it.bvh2]; c[1] = b.right[it.bvh2]; n = 2;
         while (n < 8) {
@@ -275,6 +349,14 @@ static int accel_build_once(vb_ctx *ctx, vb_build_stats *out, bool allow_ploc, b
         VB_CHECK_LAUNCH();
     }
 
+    // cost table of the cost-optimal collapse ("build.collapse" = 1; 0 = greedy largest-area opening)
+    DevBuf<float> dp;
+    if (ctx->opt_collapse && T > 2) {
+        VB_CUDA(dp.alloc((size_t)(T - 1) * VB_DP_W));
+        VB_CUDA(cudaMemsetAsync(flags.p, 0, sizeof(uint32_t) * T, st));
+        k_collapse_cost<<<grid, 256, 0, st>>>(T, b, dp.p); launches++;
+        VB_CHECK_LAUNCH();
+    }
     // level-synchronous collapse; root work item: BVH2 root = node 0 (or the single leaf when T==1)
     Counters hc{0, 1, 0, 0};
     WorkItem root{T == 1 ? 0u : 0u, 0u};
@@ -284,7 +366,7 @@ static int accel_build_once(vb_ctx *ctx, vb_build_stats *out, bool allow_ploc, b
     uint32_t n_items = 1;
     int levels = 0;
     while (n_items) {
-        k_collapse<<<(n_items + 127) / 128, 128, 0, st>>>(qin, n_items, qout, cnt.p, T, b, d_nodes, d_tris, max_leaf); launches++;
+        k_collapse<<<(n_items + 127) / 128, 128, 0, st>>>(qin, n_items, qout, cnt.p, T, b, d_nodes, d_tris, max_leaf, dp.p); launches++;
         VB_CHECK_LAUNCH();
         VB_CUDA(cudaMemcpyAsync(&hc, cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
         VB_CUDA(cudaStreamSynchronize(st));

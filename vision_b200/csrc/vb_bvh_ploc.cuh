@@ -88,6 +88,8 @@ __global__ void __launch_bounds__(256) k_ploc_merge(uint32_t n, uint32_t T, uint
         b.nlo[id] = make_float4(fminf(alo.x, clo.x), fminf(alo.y, clo.y), fminf(alo.z, clo.z), 0.f);
         b.nhi[id] = make_float4(fmaxf(ahi.x, chi.x), fmaxf(ahi.y, chi.y), fmaxf(ahi.z, chi.z), 0.f);
         b.left[id] = L; b.right[id] = R;
+        b.parent[L] = id; b.parent[R] = id;
+        if (id == 0) b.parent[0] = 0xffffffffu;          // the last merge is the root
         b.first[id] = 0; b.last[id] = max_leaf;          // leaf ranges are not contiguous here: never "leaf-like" for the collapse
     }
     out[(uint32_t)s] = id;

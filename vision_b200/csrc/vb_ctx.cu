@@ -136,6 +136,7 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     else if (k == "build.max_leaf") { if ((int)value != 1) return ctx->fail(VB_ERR_INVALID, "vb_ctx_set_option: build.max_leaf is fixed at 1 (one triangle per leaf slot)"); }
     else if (k == "build.ploc") ctx->opt_ploc = value < 0 ? -1 : (value != 0 ? 1 : 0);
     else if (k == "build.max_levels") ctx->opt_max_levels = std::min(VB_TRAVERSAL_STACK_ENTRIES, std::max(1, (int)value));   // test hook: lower the depth the build accepts
+    else if (k == "build.collapse") ctx->opt_collapse = value != 0 ? 1 : 0;
     else if (k == "build.split_pct") ctx->opt_split_pct = std::min(400, std::max(0, (int)value));
     else if (k == "build.size_classes") ctx->opt_size_classes = value != 0 ? 1 : 0;
     else if (k == "trace.sort_rays") ctx->opt_sort_rays = (int)value;

@@ -84,6 +84,7 @@ struct vb_ctx {
     int opt_ploc = -1;                       // build: 1 = PLOC clustering (vb_bvh_ploc.cuh), 0 = radix tree, -1 = automatic
     bool last_build_ploc = false;
     int opt_max_levels = VB_TRAVERSAL_STACK_ENTRIES;    // build: deepest wide tree accepted (never more than the traversal stack holds)
+    int opt_collapse = 1;                    // build: 1 = cost-optimal collapse (dynamic programme over the binary tree), 0 = greedy largest-area opening
     int opt_split_pct = 0;                   // build: triangle pre-splitting budget, extra references in percent of the triangle count (vb_bvh_split.cuh)
     int opt_size_classes = 1;                // build: triangle size class as the top bits of the Morton sort key
     int opt_sort_rays = 1, opt_sort_min_rays = 1 << 16;
