@@ -221,10 +221,35 @@ VB_API int vb_film_reduce_peers(vb_ctx *const *ctxs, uint32_t n, uint32_t root, 
 /* ---- G-buffer of the camera stage (reference rt_geom, src/base/sensor/frame_buffer.cpp:156-219) ---------------------------- */
 /* denoiser / AOV planes of the primary hit for ONE frame index, w*h float4 each, all colours through Spectrum::linear_srgb:
  * NORMAL (shading normal, 1) - zero where the camera ray misses; ALBEDO (MaterialEvaluator::albedo(wo), 1); EMISSION
- * (LightSampler::evaluate_hit_wi L, 1); GEOM (Sensor::linear_depth, p_film.x, p_film.y, hit ? 1 : 0). Motion vectors are not produced. */
-enum { VB_AOV_NORMAL = 0, VB_AOV_ALBEDO = 1, VB_AOV_EMISSION = 2, VB_AOV_GEOM = 3, VB_AOV_COUNT = 4 };
+ * (LightSampler::evaluate_hit_wi L, 1); GEOM (Sensor::linear_depth, p_film.x, p_film.y, hit ? 1 : 0); MOTION (motion vector
+ * p_film - prev_raster_coord(hit position) in pixels, 0, 0; zero where the ray misses: FrameBuffer::compute_motion_vec,
+ * frame_buffer.cpp:483-491). GRADIENT is written by vb_gbuffer_gradient, not by vb_gbuffer_render. */
+enum { VB_AOV_NORMAL = 0, VB_AOV_ALBEDO = 1, VB_AOV_EMISSION = 2, VB_AOV_GEOM = 3, VB_AOV_MOTION = 4, VB_AOV_GRADIENT = 5, VB_AOV_COUNT = 6 };
+/* The camera of the PREVIOUS frame, as Sensor::store_prev_data keeps it after every render (src/base/sensor/sensor.cpp:89-93:
+ * prev_w2s_ = inverse(c2w), prev_s2r_ = inverse(raster_to_sensor)); the sensor-to-raster map is given by its parameters (this
+ * library's camera is analytic: vb_camera). Until it is called - and after a call with prev = NULL - the previous camera is the
+ * current one (a static camera). */
+typedef struct vb_camera_prev {
+    float w2c[16];             /* inverse of the previous camera_to_world(), column-major */
+    float tan_fov_y_over_2;
+    float screen_lo[2], screen_hi[2];
+    float pad[3];
+} vb_camera_prev;
+VB_API int vb_camera_prev_set(vb_ctx *ctx, const vb_camera_prev *prev);
 VB_API int vb_gbuffer_render(vb_ctx *ctx, uint32_t frame_index);
+/* rt_gradient (FrameBuffer::compute_gradient, frame_buffer.cpp:221-275) over the planes of the last vb_gbuffer_render: per pixel the
+ * mean forward / backward difference of the shading normal and of the linear depth over the 3x3 neighbourhood (clipped at the
+ * picture's edge), GRADIENT = (length(|dn/dx| + |dn/dy|), |dz/dx| + |dz/dy|, 0, 0) = PixelGeometry::normal_fwidth.w, depth_gradient */
+VB_API int vb_gbuffer_gradient(vb_ctx *ctx);
 VB_API int vb_gbuffer_download(vb_ctx *ctx, int which, float *rgba);
+
+/* ---- render-graph passes of the `customized` pipeline (reference src/render_core/pass/, src/pipelines/customized/pipeline.cpp:28-44) -- */
+/* integrate + accumulate are vb_render_frames(frame, 1, 1, VB_ACCUM_LERP): RT = (Li, 1), ACCUM = lerp(1 / (frame + 1), ACCUM, RT).
+ * tonemapping (pass/tonemapping.cpp:26-33): OUTPUT = (tone_mapper(ACCUM.rgb), 1) - no exposure curve, unlike vb_film_resolve.
+ * gamma (pass/gamma.cpp:21-27): VIEW = linear_to_srgb(OUTPUT) on all four channels; VB_FILM_VIEW is the graph's output buffer. */
+#define VB_FILM_VIEW 3
+VB_API int vb_pass_tonemapping(vb_ctx *ctx, int tonemap);
+VB_API int vb_pass_gamma(vb_ctx *ctx);
 
 /* ---- debug / parity surface ------------------------------------------------------------------- */
 /* primary hit of every pixel for one frame index (== reference rt_compute_pixel, frame_buffer.cpp:277-291) */

@@ -74,6 +74,7 @@ void vo_scene_set_spectrum(void *h, const vb_spectrum_rec *r) {
     s.spectrum.rgb2spec = nullptr;
 }
 void vo_scene_set_camera(void *h, const vb_camera *c) { ((Scene *)h)->camera = *c; }
+void vo_scene_set_camera_prev(void *h, const vb_camera_prev *c) { Scene *s = (Scene *)h; s->have_camera_prev = c != nullptr; if (c) s->camera_prev = *c; }
 void vo_scene_set_integrator(void *h, const vb_pt_params *p) { ((Scene *)h)->params = *p; }
 void vo_scene_build(void *h, int threads, int brute) {
     Scene &s = *(Scene *)h;
@@ -152,7 +153,7 @@ void vo_primary_hits(void *h, uint32_t w, uint32_t hgt, uint32_t frame, uint32_t
     ms->params.max_depth = saved;
 }
 
-// rt_geom's G-buffer planes for one frame index: out = 4 planes of w*h float4 (normal, albedo, emission, geom)
+// rt_geom's G-buffer planes for one frame index: out = 5 planes of w*h float4 (normal, albedo, emission, geom, motion)
 void vo_gbuffer(void *h, uint32_t w, uint32_t hgt, uint32_t frame, float *out, int threads) {
     const Scene &s = *(Scene *)h;
     std::atomic<uint32_t> next_row{0};
@@ -161,10 +162,10 @@ void vo_gbuffer(void *h, uint32_t w, uint32_t hgt, uint32_t frame, float *out, i
             uint32_t y = next_row.fetch_add(1);
             if (y >= hgt) break;
             for (uint32_t x = 0; x < w; ++x) {
-                float a[16];
+                float a[20];
                 s.render_sample(x, y, w, hgt, frame, nullptr, nullptr, a);
                 size_t i = (size_t)y * w + x, n = (size_t)w * hgt;
-                for (int p = 0; p < 4; ++p) for (int c = 0; c < 4; ++c) out[(p * n + i) * 4 + c] = a[4 * p + c];
+                for (int p = 0; p < 5; ++p) for (int c = 0; c < 4; ++c) out[(p * n + i) * 4 + c] = a[4 * p + c];
             }
         }
     };
@@ -172,6 +173,67 @@ void vo_gbuffer(void *h, uint32_t w, uint32_t hgt, uint32_t frame, float *out, i
     for (int k = 1; k < std::max(1, threads); ++k) th.emplace_back(work);
     work();
     for (auto &x : th) x.join();
+}
+
+// rt_gradient (FrameBuffer::compute_gradient, frame_buffer.cpp:221-275) over the NORMAL and GEOM planes: out = w*h float4
+// (normal_fwidth, depth_gradient, 0, 0). Loop order, clipping and the divisions by the sample counts as written there.
+void vo_gbuffer_gradient(const float *normal, const float *geom, uint32_t w, uint32_t hgt, float *out) {
+    const int W = (int)w, H = (int)hgt;
+    for (int cy = 0; cy < H; ++cy)
+        for (int cx = 0; cx < W; ++cx) {
+            const float *cnp = normal + 4 * ((size_t)cy * W + cx);
+            const float3 cn{cnp[0], cnp[1], cnp[2]};
+            const float cd = geom[4 * ((size_t)cy * W + cx)];
+            uint32_t xn = 0, yn = 0;
+            float3 ndx{0, 0, 0}, ndy{0, 0, 0};
+            float ddx = 0.f, ddy = 0.f;
+            for (int x = std::max(0, cx - 1); x <= std::min(cx + 1, W - 1); ++x)
+                for (int y = std::max(0, cy - 1); y <= std::min(cy + 1, H - 1); ++y) {
+                    const float *np = normal + 4 * ((size_t)y * W + x);
+                    const float3 nn{np[0], np[1], np[2]};
+                    const float nd = geom[4 * ((size_t)y * W + x)];
+                    if (cx > x) { xn++; ndx = ndx + (cn - nn); ddx += cd - nd; }
+                    else if (x > cx) { xn++; ndx = ndx + (nn - cn); ddx += nd - cd; }
+                    if (cy > y) { yn++; ndy = ndy + (cn - nn); ddy += cd - nd; }
+                    else if (y > cy) { yn++; ndy = ndy + (nn - cn); ddy += nd - cd; }
+                }
+            const float fx = (float)xn, fy = (float)yn;
+            ndx = float3{ndx.x / fx, ndx.y / fx, ndx.z / fx}; ndy = float3{ndy.x / fy, ndy.y / fy, ndy.z / fy};
+            const float3 nf{std::fabs(ndx.x) + std::fabs(ndy.x), std::fabs(ndx.y) + std::fabs(ndy.y), std::fabs(ndx.z) + std::fabs(ndy.z)};
+            ddx = ddx / fx; ddy = ddy / fy;
+            float *o = out + 4 * ((size_t)cy * W + cx);
+            o[0] = length(nf); o[1] = std::fabs(ddx) + std::fabs(ddy); o[2] = 0.f; o[3] = 0.f;
+        }
+}
+
+// render-graph passes of the `customized` pipeline over n float4 pixels: accumulate (pass/accumulate.cpp:19-24), tonemapping
+// (pass/tonemapping.cpp:26-33 with tonemapper/impl.cpp:21-46), gamma (pass/gamma.cpp:21-27; linear_to_srgb = the sRGB OETF on [0, 1],
+// its power through the shared vlog / vexp)
+void vo_pass_accumulate(const float *input, float *output, uint64_t n, uint32_t frame_index) {
+    const float t = 1.f / ((float)frame_index + 1.f);
+    for (uint64_t i = 0; i < n; ++i) {
+        for (int c = 0; c < 3; ++c) output[4 * i + c] = output[4 * i + c] + t * (input[4 * i + c] - output[4 * i + c]);   // ocarina lerp(t, a, b) = a + t * (b - a)
+        output[4 * i + 3] = 1.f;
+    }
+}
+void vo_pass_tonemapping(const float *input, float *output, uint64_t n, int tonemap) {
+    for (uint64_t i = 0; i < n; ++i) {
+        for (int c = 0; c < 3; ++c) {
+            float x = input[4 * i + c];
+            if (tonemap == VB_TONEMAP_ACES) {
+                float y = (x * (2.51f * x + 0.03f)) / (x * (2.43f * x + 0.59f) + 0.14f);
+                x = std::min(1.0f, std::max(0.0f, y));
+            } else if (tonemap == VB_TONEMAP_REINHARD) x = x / (x + 1.0f);
+            output[4 * i + c] = x;
+        }
+        output[4 * i + 3] = 1.f;
+    }
+}
+void vo_pass_gamma(const float *input, float *output, uint64_t n) {
+    for (uint64_t i = 0; i < 4 * n; ++i) {
+        float x = std::min(std::max(input[i], 0.f), 1.f);
+        output[i] = x <= 0.0031308f ? 12.92f * x : 1.055f * vexp(vlog(x) * (1.0f / 2.4f)) - 0.055f;
+    }
 }
 
 // known-answer helpers

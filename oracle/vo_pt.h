@@ -54,6 +54,7 @@ struct Scene {
     std::vector<float> rgb2spec;
     uint32_t rgb2spec_res = 0;
     vb_camera camera{};
+    vb_camera_prev camera_prev{}; bool have_camera_prev = false;   // Sensor::store_prev_data (sensor.cpp:89-93); unset = static camera
     vb_pt_params params{};
     Accel accel;
     bool brute = false;
@@ -64,8 +65,8 @@ struct Scene {
     bool trace_any(const Ray &r, PathStats *st) const;
 
     // one pixel-sample: returns L (linear sRGB), optionally the primary hit
-    // aov (nullable, 16 floats): rt_geom's G-buffer planes for this pixel-sample (frame_buffer.cpp:156-219) - normal.xyz 1 | albedo.rgb 1 |
-    // emission.rgb 1 | linear depth, p_film.x, p_film.y, hit flag; when given, the function returns after the camera stage
+    // aov (nullable, 20 floats): rt_geom's G-buffer planes for this pixel-sample (frame_buffer.cpp:156-219) - normal.xyz 1 | albedo.rgb 1 |
+    // emission.rgb 1 | linear depth, p_film.x, p_film.y, hit flag | motion vector.xy 0 0; when given, the function returns after the camera stage
     float3 render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st, float *aov = nullptr) const;
 };
 

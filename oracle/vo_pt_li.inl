@@ -57,6 +57,26 @@ Interaction compute_surface_interaction(const Scene &sc, uint32_t inst_id, uint3
     return it;
 }
 
+// previous-camera record of a static camera: inverse of the affine camera_to_world by Gauss-Jordan elimination with row pivoting in
+// double precision, rounded once to float (the reference keeps inverse(c2w) / inverse(raster_to_sensor), sensor.cpp:89-93)
+inline vb_camera_prev camera_prev_of(const vb_camera &cam) {
+    double a[4][8];
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { a[r][c] = cam.c2w[c * 4 + r]; a[r][4 + c] = r == c ? 1.0 : 0.0; }
+    for (int i = 0; i < 4; ++i) {
+        int piv = i;
+        for (int r = i + 1; r < 4; ++r) if (std::fabs(a[r][i]) > std::fabs(a[piv][i])) piv = r;
+        if (piv != i) for (int c = 0; c < 8; ++c) std::swap(a[i][c], a[piv][c]);
+        const double inv = 1.0 / a[i][i];
+        for (int c = 0; c < 8; ++c) a[i][c] *= inv;
+        for (int r = 0; r < 4; ++r) if (r != i) { const double f = a[r][i]; for (int c = 0; c < 8; ++c) a[r][c] -= f * a[i][c]; }
+    }
+    vb_camera_prev out{};
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) out.w2c[c * 4 + r] = (float)a[r][4 + c];
+    out.tan_fov_y_over_2 = cam.tan_fov_y_over_2;
+    out.screen_lo[0] = cam.screen_lo[0]; out.screen_lo[1] = cam.screen_lo[1]; out.screen_hi[0] = cam.screen_hi[0]; out.screen_hi[1] = cam.screen_hi[1];
+    return out;
+}
+
 inline float3 flip_to(float3 n, float3 dir) { return dot(n, dir) > 0.f ? n : -n; }
 
 // reference interaction.h:279-299 / interaction.cpp:115-135
@@ -417,7 +437,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
         uint32_t wp = 0;                                            // RenderEnv::initial precedes sampler.start(pixel, frame, 0) (:168-172)
         if (params.spectrum == 1) { Sampler ws; ws.start(px, py, frame, 0xffffffffu); (void)ws.next_1d(); wp = ws.state & 0x00ffffffu; }
         Swl gw = swl_make(*this, wp);
-        for (int i = 0; i < 16; ++i) aov[i] = 0.f;
+        for (int i = 0; i < 20; ++i) aov[i] = 0.f;
         aov[7] = 1.f; aov[11] = 1.f;                                // albedo / emission are written for every pixel as (0, 0, 0, 1)
         aov[13] = p_film.x; aov[14] = p_film.y;
         if (!ph.is_miss()) {
@@ -430,6 +450,16 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
             float3 fwd{c2w.m[2][0], c2w.m[2][1], c2w.m[2][2]}, cpos{c2w.m[3][0], c2w.m[3][1], c2w.m[3][2]};
             aov[12] = dot(fwd, it.pos - cpos);
             aov[15] = 1.f;
+            {   // FrameBuffer::compute_motion_vec (frame_buffer.cpp:483-491) = p_film - Sensor::prev_raster_coord(pos).xy (sensor.cpp:95-100):
+                // world -> previous sensor space, divide by z, sensor -> raster (the analytic camera's screen window map inverted)
+                vb_camera_prev pc = have_camera_prev ? camera_prev : camera_prev_of(camera);
+                float4x4 w2c; std::memcpy(&w2c, pc.w2c, 64);
+                float3 q = transform_point(w2c, it.pos);
+                float sx = (q.x / q.z) / pc.tan_fov_y_over_2, sy = (q.y / q.z) / pc.tan_fov_y_over_2;
+                float rx = (sx - pc.screen_lo[0]) / (pc.screen_hi[0] - pc.screen_lo[0]) * (float)w;
+                float ry = (pc.screen_hi[1] - sy) / (pc.screen_hi[1] - pc.screen_lo[1]) * (float)h;
+                aov[16] = p_film.x - rx; aov[17] = p_film.y - ry;
+            }
             if (it.mat_id != VB_INVALID_ID) {
                 float cos_theta = dot(it.shading.z, it.wo);          // MaterialEvaluator::albedo, material.cpp:91-98
                 const uint32_t mt = materials[it.mat_id].type;

@@ -228,12 +228,50 @@ class OracleScene:
         return out
 
 
-def oracle_gbuffer(osc, frame, threads=8):
-    """rt_geom's G-buffer planes from the oracle: {"normal", "albedo", "emission", "geom"} -> (h, w, 4) float32"""
+def oracle_gbuffer(osc, frame, threads=8, gradient=False):
+    """rt_geom's G-buffer planes from the oracle: {"normal", "albedo", "emission", "geom", "motion"[, "gradient"]} -> (h, w, 4) float32;
+    gradient=True adds rt_gradient's plane (normal_fwidth, depth_gradient, 0, 0)"""
     w, h = osc.sc.resolution
-    out = np.empty((4, h, w, 4), np.float32)
+    out = np.empty((5, h, w, 4), np.float32)
     lib = osc.o.lib
     lib.vo_gbuffer.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int]
     lib.vo_gbuffer.restype = None
     lib.vo_gbuffer(osc.h, w, h, frame, _p(out), threads)
-    return dict(zip(("normal", "albedo", "emission", "geom"), out))
+    d = dict(zip(("normal", "albedo", "emission", "geom", "motion"), out))
+    if gradient:
+        g = np.empty((h, w, 4), np.float32)
+        lib.vo_gbuffer_gradient.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
+        lib.vo_gbuffer_gradient.restype = None
+        lib.vo_gbuffer_gradient(_p(np.ascontiguousarray(d["normal"])), _p(np.ascontiguousarray(d["geom"])), w, h, _p(g))
+        d["gradient"] = g
+    return d
+
+
+def oracle_camera_prev_set(osc, pc):
+    """pc: capi.vb_camera_prev or None (None = back to the static camera)"""
+    lib = osc.o.lib
+    lib.vo_scene_set_camera_prev.argtypes = [C.c_void_p, C.c_void_p]
+    lib.vo_scene_set_camera_prev.restype = None
+    lib.vo_scene_set_camera_prev(osc.h, C.byref(pc) if pc is not None else None)
+
+
+def oracle_pass(o, name, src, dst=None, arg=0):
+    """render-graph passes of the customized pipeline on (h, w, 4) float32 pictures: accumulate (dst updated in place, arg = frame index),
+    tonemapping (arg = tone mapper), gamma"""
+    lib = o.lib
+    src = np.ascontiguousarray(src, np.float32)
+    n = src.size // 4
+    if name == "accumulate":
+        lib.vo_pass_accumulate.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32]; lib.vo_pass_accumulate.restype = None
+        lib.vo_pass_accumulate(_p(src), _p(dst), n, arg)
+        return dst
+    out = np.empty_like(src)
+    if name == "tonemapping":
+        lib.vo_pass_tonemapping.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int]; lib.vo_pass_tonemapping.restype = None
+        lib.vo_pass_tonemapping(_p(src), _p(out), n, arg)
+    elif name == "gamma":
+        lib.vo_pass_gamma.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]; lib.vo_pass_gamma.restype = None
+        lib.vo_pass_gamma(_p(src), _p(out), n)
+    else:
+        raise ValueError(name)
+    return out

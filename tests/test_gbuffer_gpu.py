@@ -64,3 +64,124 @@ def test_gbuffer_needs_render_first(vbctx):
     assert vbctx.lib.vb_gbuffer_download(vbctx.h, 0, a.ctypes.data) != 0      # film size changed: no G-buffer of this size yet
     assert vbctx.lib.vb_gbuffer_download(vbctx.h, 9, a.ctypes.data) != 0
     assert vbctx.gbuffer(0)["normal"].shape == (17, 33, 4)
+
+
+def _prev_camera(sc, shift):
+    """the record Sensor::store_prev_data would hold for the scene's camera moved by `shift` (world units): inverse c2w in double"""
+    c2w = np.array(list(sc.camera.c2w), np.float64).reshape(4, 4).T          # column-major -> matrix
+    c2w[:3, 3] += np.asarray(shift, np.float64)
+    w2c = np.linalg.inv(c2w)
+    return w2c, np.ascontiguousarray(w2c.T, np.float32).reshape(16)
+
+
+@pytest.mark.parametrize("name", ["cbox_matte", "cbox_materials"])
+def test_motion_vectors_and_gradient_match_oracle(vbctx, oracle, name):
+    """rt_geom's motion vectors (frame_buffer.cpp:483-491, sensor.cpp:95-100) and rt_gradient (frame_buffer.cpp:221-275),
+    GPU vs oracle bit for bit: static camera (no previous camera given) and a previous camera displaced by (0.3, -0.2, 0.1)."""
+    import oracle_lib
+    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / f"{name}.json", {"resolution": [96, 80], "spp": 1})
+    vbctx.upload_scene(sc)
+    osc = oracle_lib.OracleScene(oracle, sc, threads=oracle.hw_threads())
+    g = vbctx.gbuffer(3, gradient=True)
+    o = oracle_lib.oracle_gbuffer(osc, 3, threads=oracle.hw_threads(), gradient=True)
+    for k in ("normal", "geom", "motion", "gradient"):
+        assert np.array_equal(g[k], o[k], equal_nan=True), (name, k)
+    hit = g["geom"][..., 3] == 1
+    assert np.abs(g["motion"][hit][:, :2]).max() < 2e-3 and (g["motion"][~hit] == 0).all()      # static camera: zero up to rounding
+    assert (g["motion"][..., 2:] == 0).all()
+    _, w2c = _prev_camera(sc, (0.3, -0.2, 0.1))
+    pc = vbctx.camera_prev_set(w2c, sc.camera.tan_fov_y_over_2, list(sc.camera.screen_lo), list(sc.camera.screen_hi))
+    oracle_lib.oracle_camera_prev_set(osc, pc)
+    try:
+        g2 = vbctx.gbuffer(3)
+        o2 = oracle_lib.oracle_gbuffer(osc, 3, threads=oracle.hw_threads())
+        assert np.array_equal(g2["motion"], o2["motion"])
+        assert np.abs(g2["motion"][hit][:, :2]).max() > 1.0                                     # the camera moved: pixels moved
+    finally:
+        vbctx.lib.vb_camera_prev_set(vbctx.h, None)
+        oracle_lib.oracle_camera_prev_set(osc, None)
+    g3 = vbctx.gbuffer(3)
+    assert np.array_equal(g3["motion"], g["motion"])                                            # forgotten: static again
+
+
+def test_motion_vector_known_answer(vbctx):
+    """double-precision pinhole projection of the hit point through the displaced previous camera (numpy) vs the MOTION plane"""
+    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", {"resolution": [64, 64], "spp": 1})
+    vbctx.upload_scene(sc)
+    w2c64, w2c = _prev_camera(sc, (0.25, 0.1, -0.3))
+    vbctx.camera_prev_set(w2c, sc.camera.tan_fov_y_over_2, list(sc.camera.screen_lo), list(sc.camera.screen_hi))
+    try:
+        g = vbctx.gbuffer(0)
+        hits = vbctx.dump_primary_hits(0)
+    finally:
+        vbctx.lib.vb_camera_prev_set(vbctx.h, None)
+    # world position of the primary hit from depth along the camera ray is not available host-side; rebuild it from the current camera:
+    # p_world = c2w * (dir * t) with the ray of this pixel-sample unknown -> use linear depth + p_film instead (pinhole: lens radius 0)
+    assert sc.camera.lens_radius == 0
+    c2w = np.array(list(sc.camera.c2w), np.float64).reshape(4, 4).T
+    tan = float(sc.camera.tan_fov_y_over_2)
+    lo, hi = np.array(list(sc.camera.screen_lo), np.float64), np.array(list(sc.camera.screen_hi), np.float64)
+    pf = g["geom"][..., 1:3].astype(np.float64)
+    depth = g["geom"][..., 0].astype(np.float64)
+    sx = lo[0] + pf[..., 0] / 64 * (hi[0] - lo[0]); sy = hi[1] - pf[..., 1] / 64 * (hi[1] - lo[1])
+    pcam = np.stack([sx * tan * depth, sy * tan * depth, depth, np.ones_like(depth)], -1)       # camera-space point at that linear depth
+    pw = pcam @ c2w.T
+    q = pw @ w2c64.T
+    rx = ((q[..., 0] / q[..., 2]) / tan - lo[0]) / (hi[0] - lo[0]) * 64
+    ry = (hi[1] - (q[..., 1] / q[..., 2]) / tan) / (hi[1] - lo[1]) * 64
+    hit = g["geom"][..., 3] == 1
+    assert np.allclose(g["motion"][..., 0][hit], (pf[..., 0] - rx)[hit], atol=2e-2)
+    assert np.allclose(g["motion"][..., 1][hit], (pf[..., 1] - ry)[hit], atol=2e-2)
+    assert np.abs(g["motion"][hit][:, :2]).max() > 0.5
+
+
+def test_gradient_known_answers(vbctx):
+    """rt_gradient on cbox matte: zero normal width inside a flat wall, non-zero along the wall / floor edge; depth gradient of the back
+    wall (perpendicular to the view axis) is zero, of the floor positive; numpy restatement of the 3x3 stencil on an interior pixel"""
+    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", {"resolution": [96, 96], "spp": 1})
+    vbctx.upload_scene(sc)
+    g = vbctx.gbuffer(0, gradient=True)
+    n, d, gr = g["normal"][..., :3], g["geom"][..., 0], g["gradient"]
+    assert np.isfinite(gr).all() and (gr[..., 2:] == 0).all() and (gr[..., :2] >= 0).all()
+    same = np.ones((96, 96), bool)
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            same[1:-1, 1:-1] &= (n[1 + dy:95 + dy, 1 + dx:95 + dx] == n[1:-1, 1:-1]).all(-1)
+    same[0] = same[-1] = False; same[:, 0] = same[:, -1] = False
+    assert same.mean() > 0.5 and (gr[..., 0][same] == 0).all()
+    edge = ~same; edge[0] = edge[-1] = False; edge[:, 0] = edge[:, -1] = False
+    assert (gr[..., 0][edge] > 0).mean() > 0.9
+    back = (np.abs(n - np.float32([0, 0, 1])).max(-1) < 1e-5) & same
+    floor = (np.abs(n - np.float32([0, 1, 0])).max(-1) < 1e-5) & same
+    assert gr[..., 1][back].max() < 1e-3 and gr[..., 1][floor].min() > 1e-3
+    y, x = 40, 50                                                                     # interior pixel: 6 samples per axis
+    ddx = sum(float(d[y + j, x + 1]) - float(d[y, x]) for j in (-1, 0, 1)) + sum(float(d[y, x]) - float(d[y + j, x - 1]) for j in (-1, 0, 1))
+    ddy = sum(float(d[y + 1, x + i]) - float(d[y, x]) for i in (-1, 0, 1)) + sum(float(d[y, x]) - float(d[y - 1, x + i]) for i in (-1, 0, 1))
+    assert abs(gr[y, x, 1] - (abs(ddx / 6) + abs(ddy / 6))) < 1e-5
+
+
+def test_render_graph_passes_match_oracle(vbctx, oracle):
+    """the customized pipeline's passes (src/render_core/pass/*.cpp) frame by frame: integrate + accumulate (one fused launch),
+    tonemapping (no exposure curve), gamma; every buffer equals the oracle's restatement of the pass kernels bit for bit"""
+    import oracle_lib
+    sc = scene_py.build_scene(ROOT / "scenes" / "cbox" / "cbox_matte.json", {"resolution": [64, 48], "spp": 1})
+    vbctx.upload_scene(sc)
+    vbctx.film_clear()
+    acc = np.zeros((48, 64, 4), np.float32)
+    for frame in range(3):
+        vbctx.render_frames(frame, 1, 1, capi.VB_ACCUM_LERP)
+        rt = vbctx.film_download(capi.VB_FILM_RT)
+        oracle_lib.oracle_pass(oracle, "accumulate", rt, acc, frame)
+        assert np.array_equal(vbctx.film_download(capi.VB_FILM_ACCUM), acc), frame
+        for tm in (capi.VB_TONEMAP_LINEAR, capi.VB_TONEMAP_ACES, capi.VB_TONEMAP_REINHARD):
+            vbctx.pass_tonemapping(tm)
+            out = vbctx.film_download(capi.VB_FILM_OUTPUT)
+            assert np.array_equal(out, oracle_lib.oracle_pass(oracle, "tonemapping", acc, arg=tm)), (frame, tm)
+            vbctx.pass_gamma()
+            view = vbctx.film_download(capi.VB_FILM_VIEW)
+            assert np.array_equal(view, oracle_lib.oracle_pass(oracle, "gamma", out)), (frame, tm)
+    # linear_to_srgb runs on alpha too (gamma.cpp:24): 1.055f * 1 - 0.055f = 0.99999994 in fp32
+    assert np.abs(view[..., 3] - 1).max() < 1e-6 and view[..., :3].max() <= 1 and view[..., :3].min() >= 0
+    x = out[..., :3].astype(np.float64).clip(0, 1)                                    # sRGB OETF in double
+    ref = np.where(x <= 0.0031308, 12.92 * x, 1.055 * x ** (1 / 2.4) - 0.055)
+    assert np.abs(view[..., :3] - ref).max() < 1e-5

@@ -286,3 +286,62 @@ def test_model_import_follows_the_reference_importer():
     hp.prepare_records()
     rec = hp.records()
     assert sum(len(m["pos"]) for m in rec.meshes) == 91146 and sum(len(m["tri"]) for m in rec.meshes) == 103832
+
+
+def _graph_order(spec):
+    lib = host_api.load()
+    lib.vh_render_graph_order.argtypes = [C.c_char_p, C.c_char_p, C.c_uint64]
+    lib.vh_render_graph_order.restype = C.c_int
+    buf = C.create_string_buffer(512)
+    rc = lib.vh_render_graph_order(spec.encode(), buf, 512)
+    return rc, buf.value.decode()
+
+
+def test_render_graph_setup():
+    """the `customized` pipeline's render graph (src/render_graph/graph.cpp:37-104, customized/pipeline.cpp:28-44): pass
+    plugins exist, set-up orders the passes by a depth-first walk from the marked output, drops unreached passes, and refuses broken wiring"""
+    names = host_api.plugin_names()
+    for want in ("vision-pipeline-customized#constructor", "vision-pass-integrate#constructor", "vision-pass-accumulate#constructor",
+                 "vision-pass-tonemapping#constructor", "vision-pass-gamma#constructor"):
+        assert want in names, want
+    passes = "gamma=gamma,tonemapping=tonemapping,integrate=integrate,accumulate=accumulate"
+    edges = "integrate.radiance>accumulate.input,accumulate.output>tonemapping.input,tonemapping.output>gamma.input"
+    assert _graph_order(f"{passes};{edges};gamma.output") == (0, "integrate accumulate tonemapping gamma")
+    # output marked earlier in the chain: the passes behind it are eliminated
+    assert _graph_order(f"{passes};{edges};accumulate.output") == (0, "integrate accumulate")
+    # an extra, unconnected pass is never scheduled
+    assert _graph_order(f"{passes},spare=gamma;{edges};gamma.output") == (0, "integrate accumulate tonemapping gamma")
+    rc, msg = _graph_order(f"{passes};integrate.radiance>accumulate.input,tonemapping.output>gamma.input;gamma.output")
+    assert rc != 0 and "tonemapping.input" in msg and "not connected" in msg
+    rc, msg = _graph_order(f"{passes};integrate.radiance>gamma.input;gamma.output")            # gamma's kernel reads the tone-mapped plane
+    assert rc != 0 and "integrate.radiance -> gamma.input" in msg
+    rc, msg = _graph_order(f"{passes};{edges};gamma.picture")
+    assert rc != 0 and "no output 'picture'" in msg
+    rc, msg = _graph_order(f"a=tonemapping,b=tonemapping;a.output>b.input,b.output>a.input;b.output")
+    assert rc != 0 and "cycle" in msg
+    rc, msg = _graph_order(f"a=denoise;;a.output")
+    assert rc != 0 and "vision-pass-denoise" in msg
+
+
+@pytest.mark.gpu
+def test_customized_pipeline_renders_graph_output(oracle):
+    """scenes/cbox/cbox_customized.json ("pipeline": {"type": "customized"}) through the C++ host: after n frames the graph's output buffer
+    equals gamma(tonemapping_linear(ACCUM)) of the oracle's pass restatements over the SAME accumulation the fixed pipeline produces, and
+    the previous camera is stored after every frame (static camera: zero motion vectors)"""
+    import oracle_lib
+    hp = host_api.HostPipeline(ROOT / "scenes" / "cbox" / "cbox_customized.json")
+    hp.prepare(0)
+    hp.render(5)
+    pic = hp.final_picture()
+    acc = hp.accum()
+    assert pic.shape == (128, 128, 4) and np.abs(pic[..., 3] - 1).max() < 1e-6
+    want = oracle_lib.oracle_pass(oracle, "gamma", oracle_lib.oracle_pass(oracle, "tonemapping", acc, arg=capi.VB_TONEMAP_LINEAR))
+    assert np.array_equal(pic, want)
+    # the same five frames through the fixed pipeline's ONE batched launch accumulate to the same film, bit for bit
+    fx = host_api.HostPipeline(ROOT / "scenes" / "cbox" / "cbox_matte.json", {"resolution": [128, 128]})
+    fx.prepare(0)
+    fx.render(5)
+    assert np.array_equal(fx.accum(), acc)
+    g = hp.context().gbuffer(0)
+    hit = g["geom"][..., 3] == 1
+    assert np.abs(g["motion"][hit][:, :2]).max() < 2e-3

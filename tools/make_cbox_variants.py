@@ -168,3 +168,10 @@ esp["light_sampler"]["param"].update({"env_separate": True, "env_prob": 0.7})
 esd = copy.deepcopy(dr)
 esd["light_sampler"]["param"].update({"env_separate": True})          # env_prob default 0.5
 (root / "cbox_env_separate_directional.json").write_text(json.dumps(esd, indent=1))
+
+# cbox_customized.json: the matte box rendered by the `customized` pipeline (render graph integrate -> accumulate ->
+# tonemapping -> gamma, src/pipelines/customized/pipeline.cpp:28-44) at 128x128
+cu = copy.deepcopy(base)
+cu["pipeline"]["type"] = "customized"
+cu["pipeline"]["param"]["frame_buffer"]["param"]["resolution"] = [128, 128]
+(root / "cbox_customized.json").write_text(json.dumps(cu, indent=1))

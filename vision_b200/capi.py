@@ -387,6 +387,11 @@ class vb_camera(C.Structure):
                 ("filter_table_offset", C.c_uint32)]
 
 
+class vb_camera_prev(C.Structure):
+    _fields_ = [("w2c", C.c_float * 16), ("tan_fov_y_over_2", C.c_float), ("screen_lo", C.c_float * 2), ("screen_hi", C.c_float * 2),
+                ("pad", C.c_float * 3)]
+
+
 class vb_pt_params(C.Structure):
     _fields_ = [("max_depth", C.c_uint32), ("min_depth", C.c_uint32), ("rr_threshold", C.c_float),
                 ("mis_mode", C.c_uint32), ("spectrum", C.c_uint32), ("sampler", C.c_uint32),
@@ -427,7 +432,7 @@ VB_LIGHT_SAMPLER_UNIFORM, VB_LIGHT_SAMPLER_POWER = 0, 1
 VB_FILTER_BOX, VB_FILTER_TRIANGLE, VB_FILTER_FITTED = 0, 1, 2
 VB_FILTER_TABLE_SIZE = 20
 VB_ACCUM_LERP, VB_ACCUM_SUM = 0, 1
-VB_FILM_RT, VB_FILM_ACCUM, VB_FILM_OUTPUT = 0, 1, 2
+VB_FILM_RT, VB_FILM_ACCUM, VB_FILM_OUTPUT, VB_FILM_VIEW = 0, 1, 2, 3
 VB_TONEMAP_LINEAR, VB_TONEMAP_ACES, VB_TONEMAP_REINHARD = 0, 1, 2
 
 
@@ -463,6 +468,10 @@ def _bind_pt(lib):
         "vb_render_stats": [vp, C.POINTER(C.c_uint64)],
         "vb_gbuffer_render": [vp, C.c_uint32],
         "vb_gbuffer_download": [vp, C.c_int, vp],
+        "vb_gbuffer_gradient": [vp],
+        "vb_camera_prev_set": [vp, C.POINTER(vb_camera_prev)],
+        "vb_pass_tonemapping": [vp, C.c_int],
+        "vb_pass_gamma": [vp],
         "vb_render_work": [vp, C.POINTER(C.c_uint64)],
         "vb_nccl_unique_id": [vp],
         "vb_nccl_comm_create": [vp, vp, C.c_int, C.c_int, C.POINTER(vp)],
@@ -556,6 +565,7 @@ def _pt_methods():
         sep, prob = getattr(sc, "light_sampler_env", (0, 0.0))
         self._check(self.lib.vb_light_sampler_env_set(self.h, sep, prob), "vb_light_sampler_env_set")
         self._check(self.lib.vb_camera_set(self.h, C.byref(sc.camera)), "vb_camera_set")
+        self._check(self.lib.vb_camera_prev_set(self.h, None), "vb_camera_prev_set")          # a new scene starts with a static camera
         self._check(self.lib.vb_integrator_set(self.h, C.byref(sc.params)), "vb_integrator_set")
         self._check(self.lib.vb_film_create(self.h, sc.resolution[0], sc.resolution[1]), "vb_film_create")
         self._res = sc.resolution
@@ -581,16 +591,35 @@ def _pt_methods():
         self._check(self.lib.vb_film_device_ptr(self.h, which, C.byref(p)), "vb_film_device_ptr")
         return p.value
 
-    def gbuffer(self, frame) -> dict:
-        """rt_geom's G-buffer planes of one frame index: {"normal", "albedo", "emission", "geom"} -> (h, w, 4) float32"""
+    def gbuffer(self, frame, gradient=False) -> dict:
+        """rt_geom's G-buffer planes of one frame index: {"normal", "albedo", "emission", "geom", "motion"[, "gradient"]} -> (h, w, 4) float32;
+        gradient=True also runs rt_gradient (vb_gbuffer_gradient)"""
         self._check(self.lib.vb_gbuffer_render(self.h, frame), "vb_gbuffer_render")
+        if gradient:
+            self._check(self.lib.vb_gbuffer_gradient(self.h), "vb_gbuffer_gradient")
         w, h = self._res
         out = {}
-        for which, name in enumerate(("normal", "albedo", "emission", "geom")):
+        for which, name in enumerate(("normal", "albedo", "emission", "geom", "motion") + (("gradient",) if gradient else ())):
             a = np.empty((h, w, 4), np.float32)
             self._check(self.lib.vb_gbuffer_download(self.h, which, a.ctypes.data), "vb_gbuffer_download")
             out[name] = a
         return out
+
+    def camera_prev_set(self, w2c, tan_fov_y_over_2, screen_lo, screen_hi):
+        """Sensor::store_prev_data: the previous frame's camera (w2c = inverse of its camera_to_world, 16 floats column-major)"""
+        pc = vb_camera_prev()
+        pc.w2c[:] = [float(x) for x in np.asarray(w2c, np.float32).reshape(16)]
+        pc.tan_fov_y_over_2 = float(tan_fov_y_over_2)
+        pc.screen_lo[:] = [float(x) for x in screen_lo]
+        pc.screen_hi[:] = [float(x) for x in screen_hi]
+        self._check(self.lib.vb_camera_prev_set(self.h, C.byref(pc)), "vb_camera_prev_set")
+        return pc
+
+    def pass_tonemapping(self, tonemap):
+        self._check(self.lib.vb_pass_tonemapping(self.h, tonemap), "vb_pass_tonemapping")
+
+    def pass_gamma(self):
+        self._check(self.lib.vb_pass_gamma(self.h), "vb_pass_gamma")
 
     def dump_primary_hits(self, frame):
         w, h = self._res
@@ -627,7 +656,7 @@ def _pt_methods():
         return {"closest_nodes": w[0], "closest_tris": w[1], "any_nodes": w[2], "any_tris": w[3]}
 
     for f in (render_work, upload_scene, render_frames, film_clear, film_resolve, film_download, film_device_ptr,
-              dump_primary_hits, render_stats, gbuffer, nccl_comm_create, nccl_comm_destroy, film_allreduce):
+              dump_primary_hits, render_stats, gbuffer, camera_prev_set, pass_tonemapping, pass_gamma, nccl_comm_create, nccl_comm_destroy, film_allreduce):
         setattr(Context, f.__name__, f)
 
 

@@ -106,9 +106,10 @@ __global__ void __launch_bounds__(PT_BLOCK) k_path_trace(const __grid_constant__
 // rt_geom's G-buffer outputs for one frame index (reference frame_buffer.cpp:156-219): shading normal, material albedo, emission of
 // the primary hit (all through Spectrum::linear_srgb), linear depth + film position. Planes: out[plane * n_pix + pix] (float4);
 // normal: (ns, 1) on a hit, zero otherwise (the reference leaves a missed pixel's normal unwritten); albedo / emission: (rgb, 1) for every
-// pixel; geom: (Sensor::linear_depth, p_film.x, p_film.y, hit ? 1 : 0). Motion vectors need a previous camera and are not produced.
+// pixel; geom: (Sensor::linear_depth, p_film.x, p_film.y, hit ? 1 : 0); motion: (p_film - Sensor::prev_raster_coord(hit position), 0, 0),
+// zero on a miss (frame_buffer.cpp:483-491, sensor.cpp:95-100 with the sensor-to-raster map of the analytic camera inverted).
 template <int VARIANT>
-__global__ void __launch_bounds__(PT_BLOCK) k_gbuffer(const __grid_constant__ PtScene S, uint32_t frame, float4 *out) {
+__global__ void __launch_bounds__(PT_BLOCK) k_gbuffer(const __grid_constant__ PtScene S, const __grid_constant__ vb_camera_prev PC, uint32_t frame, float4 *out) {
     constexpr bool PRINCIPLED = (VARIANT & PT_PRINCIPLED) != 0, HERO = (VARIANT & PT_HERO) != 0;
     __shared__ uint2 s_stack_all[VB_SM_STACK * PT_BLOCK];
     uint2 *s_stack = s_stack_all + threadIdx.x;
@@ -128,7 +129,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_gbuffer(const __grid_constant__ Pt
     uint32_t d0 = 0, d1 = 0;
     vb_traverse<false, false>(S.accel, ray, hit, s_stack, PT_BLOCK, d0, d1, mg);
     float4 normal = make_float4(0.f, 0.f, 0.f, 0.f), albedo = make_float4(0.f, 0.f, 0.f, 1.f), emission = make_float4(0.f, 0.f, 0.f, 1.f);
-    float4 geom = make_float4(0.f, p_film.x, p_film.y, 0.f);
+    float4 geom = make_float4(0.f, p_film.x, p_film.y, 0.f), motion = make_float4(0.f, 0.f, 0.f, 0.f);
     if (hit.inst != VB_INVALID_ID) {
         Interaction it = compute_surface_interaction(S, hit.inst, hit.prim, hit.u, hit.v, true);
         f3 rd{ray.dx, ray.dy, ray.dz}, ro{ray.ox, ray.oy, ray.oz};
@@ -138,6 +139,13 @@ __global__ void __launch_bounds__(PT_BLOCK) k_gbuffer(const __grid_constant__ Pt
         const float *m = S.cam.c2w;                                  // Sensor::linear_depth: rigid c2w -> projection on its third column
         geom.x = dot(f3{m[8], m[9], m[10]}, it.pos - f3{m[12], m[13], m[14]});
         geom.w = 1.f;
+        {                                                            // Sensor::prev_raster_coord: world -> previous sensor space, / z, -> raster
+            f3 pc = transform_point(PC.w2c, it.pos);
+            float sx = (pc.x / pc.z) / PC.tan_fov_y_over_2, sy = (pc.y / pc.z) / PC.tan_fov_y_over_2;
+            float rx = (sx - PC.screen_lo[0]) / (PC.screen_hi[0] - PC.screen_lo[0]) * (float)S.width;
+            float ry = (PC.screen_hi[1] - sy) / (PC.screen_hi[1] - PC.screen_lo[1]) * (float)S.height;
+            motion.x = p_film.x - rx; motion.y = p_film.y - ry;
+        }
         if (it.mat_id != VB_INVALID_ID) {
             float cos_theta = dot(it.shading.z, it.wo);              // MaterialEvaluator::albedo, material.cpp:91-98
             f3 a;
@@ -161,6 +169,66 @@ __global__ void __launch_bounds__(PT_BLOCK) k_gbuffer(const __grid_constant__ Pt
         }
     }
     out[pix] = normal; out[(size_t)n_pix + pix] = albedo; out[2 * (size_t)n_pix + pix] = emission; out[3 * (size_t)n_pix + pix] = geom;
+    out[4 * (size_t)n_pix + pix] = motion;
+}
+
+// rt_gradient (frame_buffer.cpp:221-275): sums in the reference's loop order (x outer, y inner over the clipped 3x3 window, centre included
+// and contributing nothing), then the divisions by the sample counts - a 1-pixel-wide picture divides by zero there as well.
+__global__ void __launch_bounds__(256) k_gbuffer_gradient(const float4 *normal, const float4 *geom, float4 *out, int w, int h) {
+    int pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= w * h) return;
+    const int cx = pix % w, cy = pix / w;
+    const float4 cn = normal[pix];
+    const float cd = geom[pix].x;
+    uint32_t xn = 0, yn = 0;
+    f3 ndx{0, 0, 0}, ndy{0, 0, 0};
+    float ddx = 0.f, ddy = 0.f;
+    for (int x = max(0, cx - 1); x <= min(cx + 1, w - 1); ++x)
+        for (int y = max(0, cy - 1); y <= min(cy + 1, h - 1); ++y) {
+            const float4 nn = normal[y * w + x];
+            const float nd = geom[y * w + x].x;
+            const f3 c{cn.x, cn.y, cn.z}, n{nn.x, nn.y, nn.z};
+            if (cx > x) { xn++; ndx = ndx + (c - n); ddx += cd - nd; }
+            else if (x > cx) { xn++; ndx = ndx + (n - c); ddx += nd - cd; }
+            if (cy > y) { yn++; ndy = ndy + (c - n); ddy += cd - nd; }
+            else if (y > cy) { yn++; ndy = ndy + (n - c); ddy += nd - cd; }
+        }
+    const float fx = (float)xn, fy = (float)yn;
+    ndx = f3{ndx.x / fx, ndx.y / fx, ndx.z / fx}; ndy = f3{ndy.x / fy, ndy.y / fy, ndy.z / fy};
+    const f3 nf{fabsf(ndx.x) + fabsf(ndy.x), fabsf(ndx.y) + fabsf(ndy.y), fabsf(ndx.z) + fabsf(ndy.z)};
+    ddx = ddx / fx; ddy = ddy / fy;
+    out[pix] = make_float4(length(nf), fabsf(ddx) + fabsf(ddy), 0.f, 0.f);
+}
+
+// render-graph passes (pass/tonemapping.cpp:26-33, pass/gamma.cpp:21-27). linear_to_srgb: the sRGB OETF on [0, 1] with the
+// power written over the shared vlog / vexp, so that the host restatement gives the same bits.
+__device__ __forceinline__ float linear_to_srgb1(float x) {
+    x = fmin_(fmax_(x, 0.f), 1.f);
+    return x <= 0.0031308f ? 12.92f * x : 1.055f * vexp(vlog(x) * (1.0f / 2.4f)) - 0.055f;
+}
+__global__ void __launch_bounds__(256) k_pass_tonemapping(const float4 *in, float4 *out, uint32_t n, int tonemap) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 v = in[i];
+    float c[3] = {v.x, v.y, v.z};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float x = c[k];
+        if (tonemap == VB_TONEMAP_ACES) {
+            float y = (x * (2.51f * x + 0.03f)) / (x * (2.43f * x + 0.59f) + 0.14f);
+            x = fmin_(1.0f, fmax_(0.0f, y));
+        } else if (tonemap == VB_TONEMAP_REINHARD) {
+            x = x / (x + 1.0f);
+        }
+        c[k] = x;
+    }
+    out[i] = make_float4(c[0], c[1], c[2], 1.0f);
+}
+__global__ void __launch_bounds__(256) k_pass_gamma(const float4 *in, float4 *out, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 v = in[i];
+    out[i] = make_float4(linear_to_srgb1(v.x), linear_to_srgb1(v.y), linear_to_srgb1(v.z), linear_to_srgb1(v.w));
 }
 
 // reference frame_buffer.cpp:72-74,135-144 + tonemapper/impl.cpp:21-46
@@ -238,7 +306,10 @@ struct vb_pt_state {
     vb_medium_rec *d_mediums = nullptr; uint32_t n_mediums = 0;
     float *d_spd_values = nullptr; float4 *d_spd_meta = nullptr; uint32_t n_spds = 0; std::vector<uint32_t> h_spd_sizes;
     float *d_rgb2spec = nullptr; vb_spectrum_rec spectrum{}; bool have_spectrum = false;
-    float4 *d_gbuffer = nullptr; size_t gbuffer_n = 0;       // 4 planes of w*h float4 (vb_gbuffer_render)
+    float4 *d_gbuffer = nullptr; size_t gbuffer_n = 0;       // VB_AOV_COUNT planes of w*h float4 (vb_gbuffer_render, vb_gbuffer_gradient)
+    bool gbuffer_valid = false;                              // a vb_gbuffer_render has filled the planes
+    vb_camera_prev cam_prev{}; bool have_cam_prev = false;   // vb_camera_prev_set
+    float4 *view = nullptr;                                  // VB_FILM_VIEW (vb_pass_gamma), allocated on first use
     float4 *d_spec_cache = nullptr; size_t spec_cache_n = 0; bool spec_dirty = true;   // hero: decoded constant colour slots (k_spec_cache)
     std::vector<vb_material_rec> h_mat;            // kept for the SPD index checks at render time
     std::vector<vb_light_rec> h_lights;            // kept for the instance / table checks at render time
@@ -267,7 +338,7 @@ void vb_pt_destroy(vb_ctx *ctx) {
     for (auto t : p->tex_mem) cudaFree(t);
     for (auto &l : p->luts) cudaFree((void *)l.data);
     cudaFree(p->d_mediums);
-    cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta); cudaFree(p->d_rgb2spec); cudaFree(p->d_spec_cache); cudaFree(p->d_gbuffer);
+    cudaFree(p->d_spd_values); cudaFree(p->d_spd_meta); cudaFree(p->d_rgb2spec); cudaFree(p->d_spec_cache); cudaFree(p->d_gbuffer); cudaFree(p->view);
     cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output); cudaFree(p->d_counters);
     if (p->wf) { wf_free(*p->wf); delete p->wf; }
     delete p;
@@ -529,8 +600,8 @@ int vb_film_create(vb_ctx *ctx, uint32_t width, uint32_t height) {
     if (!width || !height) return ctx->fail(VB_ERR_INVALID, "vb_film_create: empty film");
     cudaSetDevice(ctx->device);
     vb_pt_state *p = pt_state(ctx);
-    cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output);
-    p->rt = p->accum = p->output = nullptr;
+    cudaFree(p->rt); cudaFree(p->accum); cudaFree(p->output); cudaFree(p->view);
+    p->rt = p->accum = p->output = p->view = nullptr;
     size_t bytes = sizeof(float4) * (size_t)width * height;
     VB_CUDA(cudaMalloc(&p->rt, bytes)); VB_CUDA(cudaMalloc(&p->accum, bytes)); VB_CUDA(cudaMalloc(&p->output, bytes));
     p->w = width; p->h = height;
@@ -546,6 +617,27 @@ int vb_film_clear(vb_ctx *ctx) {
     VB_CUDA(cudaMemsetAsync(p->accum, 0, bytes, ctx->stream));
     VB_CUDA(cudaMemsetAsync(p->output, 0, bytes, ctx->stream));
     p->frames_done = 0;
+    return VB_OK;
+}
+
+// The previous-camera record of a camera: inverse of its (affine) camera-to-world matrix by Gauss-Jordan elimination in double
+// precision, rounded once to float. Used when no vb_camera_prev_set call has been made (static camera).
+static int camera_prev_from(vb_ctx *ctx, const vb_camera &cam, vb_camera_prev *out) {
+    double a[4][8];
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { a[r][c] = cam.c2w[c * 4 + r]; a[r][4 + c] = r == c ? 1.0 : 0.0; }
+    for (int i = 0; i < 4; ++i) {
+        int piv = i;
+        for (int r = i + 1; r < 4; ++r) if (std::fabs(a[r][i]) > std::fabs(a[piv][i])) piv = r;
+        if (!(std::fabs(a[piv][i]) > 0.0)) return ctx->fail(VB_ERR_INVALID, "vb_gbuffer_render: the camera_to_world matrix is singular");
+        if (piv != i) for (int c = 0; c < 8; ++c) std::swap(a[i][c], a[piv][c]);
+        const double inv = 1.0 / a[i][i];
+        for (int c = 0; c < 8; ++c) a[i][c] *= inv;
+        for (int r = 0; r < 4; ++r) if (r != i) { const double f = a[r][i]; for (int c = 0; c < 8; ++c) a[r][c] -= f * a[i][c]; }
+    }
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) out->w2c[c * 4 + r] = (float)a[r][4 + c];
+    out->tan_fov_y_over_2 = cam.tan_fov_y_over_2;
+    out->screen_lo[0] = cam.screen_lo[0]; out->screen_lo[1] = cam.screen_lo[1]; out->screen_hi[0] = cam.screen_hi[0]; out->screen_hi[1] = cam.screen_hi[1];
+    out->pad[0] = out->pad[1] = out->pad[2] = 0.f;
     return VB_OK;
 }
 
@@ -632,10 +724,15 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
         unsigned g = (n_pix + PT_BLOCK - 1) / PT_BLOCK;
         ctx->prof_begin("gbuffer", 1);
         const bool hero = S.params.spectrum == VB_SPECTRUM_HERO;
-        if (hero && p->has_principled) k_gbuffer<PT_HERO | PT_PRINCIPLED><<<g, PT_BLOCK, 0, ctx->stream>>>(S, first, gbuf);
-        else if (hero) k_gbuffer<PT_HERO><<<g, PT_BLOCK, 0, ctx->stream>>>(S, first, gbuf);
-        else if (p->has_principled) k_gbuffer<PT_PRINCIPLED><<<g, PT_BLOCK, 0, ctx->stream>>>(S, first, gbuf);
-        else k_gbuffer<PT_LEAN><<<g, PT_BLOCK, 0, ctx->stream>>>(S, first, gbuf);
+        vb_camera_prev PC = p->cam_prev;
+        if (!p->have_cam_prev) {                                      // static camera: the previous camera is the current one
+            int rc = camera_prev_from(ctx, p->cam, &PC);
+            if (rc) return rc;
+        }
+        if (hero && p->has_principled) k_gbuffer<PT_HERO | PT_PRINCIPLED><<<g, PT_BLOCK, 0, ctx->stream>>>(S, PC, first, gbuf);
+        else if (hero) k_gbuffer<PT_HERO><<<g, PT_BLOCK, 0, ctx->stream>>>(S, PC, first, gbuf);
+        else if (p->has_principled) k_gbuffer<PT_PRINCIPLED><<<g, PT_BLOCK, 0, ctx->stream>>>(S, PC, first, gbuf);
+        else k_gbuffer<PT_LEAN><<<g, PT_BLOCK, 0, ctx->stream>>>(S, PC, first, gbuf);
         ctx->prof_end();
         VB_CHECK_LAUNCH();
         return VB_OK;
@@ -706,7 +803,8 @@ int vb_film_download(vb_ctx *ctx, float *rgba, int which) {
     vb_pt_state *p = pt_state(ctx);
     if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_film_download: no film");
     cudaSetDevice(ctx->device);
-    const float4 *src = which == VB_FILM_RT ? p->rt : (which == VB_FILM_OUTPUT ? p->output : p->accum);
+    if (which == VB_FILM_VIEW && !p->view) return ctx->fail(VB_ERR_STATE, "vb_film_download: no view buffer (vb_pass_gamma)");
+    const float4 *src = which == VB_FILM_RT ? p->rt : (which == VB_FILM_OUTPUT ? p->output : (which == VB_FILM_VIEW ? p->view : p->accum));
     VB_CUDA(cudaMemcpyAsync(rgba, src, sizeof(float4) * (size_t)p->w * p->h, cudaMemcpyDeviceToHost, ctx->stream));
     VB_CUDA(cudaStreamSynchronize(ctx->stream));
     return VB_OK;
@@ -716,7 +814,8 @@ int vb_film_device_ptr(vb_ctx *ctx, int which, void **ptr) {
     if (!ctx || !ptr) return VB_ERR_INVALID;
     vb_pt_state *p = pt_state(ctx);
     if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_film_device_ptr: no film");
-    *ptr = which == VB_FILM_RT ? (void *)p->rt : (which == VB_FILM_OUTPUT ? (void *)p->output : (void *)p->accum);
+    if (which == VB_FILM_VIEW && !p->view) return ctx->fail(VB_ERR_STATE, "vb_film_device_ptr: no view buffer (vb_pass_gamma)");
+    *ptr = which == VB_FILM_RT ? (void *)p->rt : (which == VB_FILM_OUTPUT ? (void *)p->output : (which == VB_FILM_VIEW ? (void *)p->view : (void *)p->accum));
     return VB_OK;
 }
 
@@ -729,9 +828,64 @@ int vb_gbuffer_render(vb_ctx *ctx, uint32_t frame_index) {
     if (p->gbuffer_n != n) {
         cudaFree(p->d_gbuffer); p->d_gbuffer = nullptr; p->gbuffer_n = 0;
         VB_CUDA(cudaMalloc(&p->d_gbuffer, sizeof(float4) * VB_AOV_COUNT * n));
-        p->gbuffer_n = n;
+        VB_CUDA(cudaMemsetAsync(p->d_gbuffer, 0, sizeof(float4) * VB_AOV_COUNT * n, ctx->stream));
+        p->gbuffer_n = n; p->gbuffer_valid = false;
     }
-    return pt_launch(ctx, "vb_gbuffer_render", frame_index, 1, 1, VB_ACCUM_SUM, false, nullptr, nullptr, nullptr, nullptr, nullptr, p->d_gbuffer);
+    int rc = pt_launch(ctx, "vb_gbuffer_render", frame_index, 1, 1, VB_ACCUM_SUM, false, nullptr, nullptr, nullptr, nullptr, nullptr, p->d_gbuffer);
+    if (rc == VB_OK) p->gbuffer_valid = true;
+    return rc;
+}
+
+int vb_camera_prev_set(vb_ctx *ctx, const vb_camera_prev *prev) {
+    if (!ctx) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!prev) { p->have_cam_prev = false; return VB_OK; }          // forget it: back to the static camera
+    if (!(prev->tan_fov_y_over_2 > 0.f) || !(prev->screen_hi[0] > prev->screen_lo[0]) || !(prev->screen_hi[1] > prev->screen_lo[1]))
+        return ctx->fail(VB_ERR_INVALID, "vb_camera_prev_set: empty field of view or screen window");
+    p->cam_prev = *prev; p->have_cam_prev = true;
+    return VB_OK;
+}
+
+int vb_gbuffer_gradient(vb_ctx *ctx) {
+    if (!ctx) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    const size_t n = (size_t)p->w * p->h;
+    if (!p->d_gbuffer || p->gbuffer_n != n || !p->gbuffer_valid) return ctx->fail(VB_ERR_STATE, "vb_gbuffer_gradient: no G-buffer (vb_gbuffer_render)");
+    cudaSetDevice(ctx->device);
+    ctx->prof_begin("gbuffer_gradient", 1);
+    k_gbuffer_gradient<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(p->d_gbuffer + VB_AOV_NORMAL * n, p->d_gbuffer + VB_AOV_GEOM * n,
+                                                                             p->d_gbuffer + VB_AOV_GRADIENT * n, (int)p->w, (int)p->h);
+    ctx->prof_end();
+    VB_CHECK_LAUNCH();
+    return VB_OK;
+}
+
+int vb_pass_tonemapping(vb_ctx *ctx, int tonemap) {
+    if (!ctx) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_pass_tonemapping: no film (vb_film_create)");
+    if (tonemap < VB_TONEMAP_LINEAR || tonemap > VB_TONEMAP_REINHARD) return ctx->fail(VB_ERR_INVALID, "vb_pass_tonemapping: unknown tone mapper");
+    cudaSetDevice(ctx->device);
+    const uint32_t n = p->w * p->h;
+    ctx->prof_begin("film", 1);
+    k_pass_tonemapping<<<(n + 255) / 256, 256, 0, ctx->stream>>>(p->accum, p->output, n, tonemap);
+    ctx->prof_end();
+    VB_CHECK_LAUNCH();
+    return VB_OK;
+}
+
+int vb_pass_gamma(vb_ctx *ctx) {
+    if (!ctx) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_pass_gamma: no film (vb_film_create)");
+    cudaSetDevice(ctx->device);
+    const uint32_t n = p->w * p->h;
+    if (!p->view) VB_CUDA(cudaMalloc(&p->view, sizeof(float4) * (size_t)n));
+    ctx->prof_begin("film", 1);
+    k_pass_gamma<<<(n + 255) / 256, 256, 0, ctx->stream>>>(p->output, p->view, n);
+    ctx->prof_end();
+    VB_CHECK_LAUNCH();
+    return VB_OK;
 }
 
 int vb_gbuffer_download(vb_ctx *ctx, int which, float *rgba) {

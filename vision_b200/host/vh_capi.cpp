@@ -1,5 +1,6 @@
 // extern "C" surface of the host layer (libvision_host.so) for the Python harness and the CLI.
 #include "vh_scene.h"
+#include "vh_graph.h"
 #include <cstring>
 
 using namespace vh;
@@ -115,6 +116,27 @@ VB_API uint64_t vh_plugin_names(char *dst, uint64_t cap) {
     for (auto &n : PluginRegistry::instance().names()) s += n + "\n";
     if (dst && cap > s.size()) std::memcpy(dst, s.c_str(), s.size() + 1);
     return s.size() + 1;
+}
+/* Render-graph set-up without a device (tests): `spec` = "name=type,name=type;src.chan>dst.chan,...;out.chan". Returns 0 and the ordered,
+ * simplified pass list ("integrate accumulate ...") in dst, or -1 and the error text. */
+VB_API int vh_render_graph_order(const char *spec, char *dst, uint64_t cap) {
+    std::string out; int rc = 0;
+    try {
+        std::string sp(spec);
+        std::vector<std::string> part;
+        size_t a = 0;
+        for (size_t i = 0; i <= sp.size(); ++i) if (i == sp.size() || sp[i] == ';') { part.push_back(sp.substr(a, i - a)); a = i + 1; }
+        if (part.size() != 3) throw std::runtime_error("render graph spec: passes;edges;output");
+        auto split = [](const std::string &x, char c) { std::vector<std::string> v; size_t b = 0; for (size_t i = 0; i <= x.size(); ++i) if (i == x.size() || x[i] == c) { if (i > b) v.push_back(x.substr(b, i - b)); b = i + 1; } return v; };
+        RenderGraph g;
+        for (auto &pt : split(part[0], ',')) { auto kv = split(pt, '='); if (kv.size() != 2) throw std::runtime_error("render graph spec: name=type"); g.add_pass(RenderPass::create(kv[1]), kv[0]); }
+        for (auto &e : split(part[1], ',')) { auto kv = split(e, '>'); if (kv.size() != 2) throw std::runtime_error("render graph spec: src>dst"); g.add_edge(kv[0], kv[1]); }
+        g.mark_output(part[2]);
+        g.setup();
+        for (auto *p : g.pass_list()) out += (out.empty() ? "" : " ") + p->pass_name;
+    } catch (const std::exception &e) { out = e.what(); rc = -1; }
+    if (dst && cap) { size_t n = std::min<size_t>(out.size(), cap - 1); std::memcpy(dst, out.data(), n); dst[n] = 0; }
+    return rc;
 }
 VB_API uint64_t vh_scene_log(vh_pipeline *h, char *dst, uint64_t cap) {
     std::string s;

@@ -18,6 +18,22 @@ Mat4 mat4_mul(const Mat4 &a, const Mat4 &b) {
 static float3 norm3(float3 v) { double l = std::sqrt((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z); return {(float)(v.x / l), (float)(v.y / l), (float)(v.z / l)}; }
 static float3 cross3(float3 a, float3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
 // left-handed camera frame [right, up, forward, position]; forward = target - pos
+Mat4 mat4_inverse(const Mat4 &m) {
+    double a[4][8];
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { a[r][c] = m[c * 4 + r]; a[r][4 + c] = r == c ? 1.0 : 0.0; }
+    for (int i = 0; i < 4; ++i) {
+        int piv = i;
+        for (int r = i + 1; r < 4; ++r) if (std::fabs(a[r][i]) > std::fabs(a[piv][i])) piv = r;
+        if (!(std::fabs(a[piv][i]) > 0.0)) throw std::runtime_error("mat4_inverse: singular matrix");
+        if (piv != i) for (int c = 0; c < 8; ++c) std::swap(a[i][c], a[piv][c]);
+        const double inv = 1.0 / a[i][i];
+        for (int c = 0; c < 8; ++c) a[i][c] *= inv;
+        for (int r = 0; r < 4; ++r) if (r != i) { const double f = a[r][i]; for (int c = 0; c < 8; ++c) a[r][c] -= f * a[i][c]; }
+    }
+    Mat4 out{};
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) out[c * 4 + r] = (float)a[r][4 + c];
+    return out;
+}
 Mat4 look_at(float3 pos, float3 target, float3 up) {
     float3 fwd = norm3({target.x - pos.x, target.y - pos.y, target.z - pos.z});
     float3 right = norm3(cross3(fwd, up));

@@ -13,6 +13,7 @@ struct float3 { float x, y, z; };
 using Mat4 = std::array<float, 16>;     // column-major: m[4*c + r], column 3 = translation
 Mat4 mat4_identity();
 Mat4 mat4_mul(const Mat4 &a, const Mat4 &b);
+Mat4 mat4_inverse(const Mat4 &m);                        // Gauss-Jordan with row pivoting in double precision, rounded once
 Mat4 look_at(float3 pos, float3 target, float3 up);       // columns: right, up, forward, position
 Mat4 rotation_x(float deg), rotation_y(float deg), rotation_z(float deg);
 Mat4 translation(float3 t);
@@ -75,6 +76,7 @@ struct LightSamplerDesc : NodeDesc { std::vector<LightDesc> light_descs; LightSa
 struct SpectrumDesc : NodeDesc { SpectrumDesc() : NodeDesc("Spectrum") {} void init(const ParameterSet &ps); };
 struct WarperDesc : NodeDesc { WarperDesc() : NodeDesc("Warper") { sub_type = "alias"; } };
 struct FrameBufferDesc : NodeDesc { ToneMapperDesc tone_mapper; FrameBufferDesc() : NodeDesc("FrameBuffer") {} void init(const ParameterSet &ps); };
+struct PassDesc : NodeDesc { explicit PassDesc(const std::string &type) : NodeDesc("Pass") { sub_type = type; } };   // RenderPass::create(name)
 struct PipelineDesc : NodeDesc { FrameBufferDesc frame_buffer_desc; PipelineDesc() : NodeDesc("Pipeline") {} void init(const ParameterSet &ps); };
 struct OutputDesc { uint32_t spp = 0; uint32_t save_exit = 0; std::string fn = "output.png"; bool denoise = false; void init(const ParameterSet &ps); };
 struct RenderSettingDesc { uint32_t polymorphic_mode = 1; float min_world_radius = 10.f; float ray_offset_factor = 1.f; void init(const ParameterSet &ps); };

@@ -144,10 +144,11 @@ void save_png(const std::string &path, const float *rgba01, uint32_t w, uint32_t
 
 // Pipeline::save_result / final_picture (pipeline.cpp:190-198,337-354): the tone-mapped picture gets the display gamma unless the
 // file is .exr / .hdr (here: .hdr / .pfm, the float formats this build writes)
-void save_image(const std::string &path, const float *rgba, uint32_t w, uint32_t h) {
+void save_image(const std::string &path, const float *rgba, uint32_t w, uint32_t h, bool display_referred) {
+    if (display_referred && !ends_with_ci(path, ".png")) throw std::runtime_error("save_image: a gamma-corrected picture (render graph output) is written as .png only");
     if (ends_with_ci(path, ".hdr")) save_hdr(path, rgba, w, h);
     else if (ends_with_ci(path, ".pfm")) save_pfm(path, rgba, w, h);
-    else if (ends_with_ci(path, ".png")) save_png(path, rgba, w, h, true);
+    else if (ends_with_ci(path, ".png")) save_png(path, rgba, w, h, !display_referred);
     else if (ends_with_ci(path, ".ppm")) save_ppm(path, rgba, w, h);
     else if (ends_with_ci(path, ".exr")) save_exr(path, rgba, w, h, false);      // linear, like .hdr (pipeline.cpp:337-354)
     else throw std::runtime_error("save_image: unsupported output format '" + path + "' (.png, .ppm, .exr, .hdr, .pfm)");

@@ -344,7 +344,17 @@ void Pipeline::prepare(int device) {
     check(vb_integrator_set(ctx, &records.params), "vb_integrator_set");
     check(vb_film_create(ctx, records.width, records.height), "vb_film_create");
 }
-void Pipeline::render(uint32_t n_frames) { scene.integrator->render(*this, n_frames); }
+void Pipeline::render(uint32_t n_frames) { scene.integrator->render(*this, n_frames); after_render(); }
+// Sensor::store_prev_data: the camera this frame was rendered with becomes the "previous camera" of the next G-buffer's motion vectors
+void Pipeline::after_render() {
+    vb_camera_prev prev{};
+    Mat4 c2w; std::memcpy(c2w.data(), records.camera.c2w, 64);
+    Mat4 w2c = mat4_inverse(c2w);
+    std::memcpy(prev.w2c, w2c.data(), 64);
+    prev.tan_fov_y_over_2 = records.camera.tan_fov_y_over_2;
+    for (int k = 0; k < 2; ++k) { prev.screen_lo[k] = records.camera.screen_lo[k]; prev.screen_hi[k] = records.camera.screen_hi[k]; }
+    check(vb_camera_prev_set(ctx, &prev), "vb_camera_prev_set");
+}
 void Pipeline::final_picture(std::vector<float> &rgba) {
     if (dist_world > 1) {
         if (!nccl_comm) throw std::runtime_error("Pipeline::final_picture: partitioned render without a communicator (nccl_init)");

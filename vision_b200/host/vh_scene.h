@@ -23,7 +23,7 @@ void save_ppm(const std::string &path, const float *rgba01, uint32_t w, uint32_t
 Image load_hdr(const std::string &path);
 void save_hdr(const std::string &path, const float *rgba, uint32_t w, uint32_t h);
 void save_png(const std::string &path, const float *rgba01, uint32_t w, uint32_t h, bool gamma);
-void save_image(const std::string &path, const float *rgba, uint32_t w, uint32_t h);
+void save_image(const std::string &path, const float *rgba, uint32_t w, uint32_t h, bool display_referred = false);   // true: already gamma-corrected
 void rgbe_encode(const float *rgb, unsigned char *out);
 void rgbe_decode(const unsigned char *in, float *rgb);
 
@@ -108,9 +108,11 @@ public:
     void set_partition(uint32_t rank, uint32_t world);
     void nccl_init(const void *id128);                // after prepare(): vb_nccl_comm_create on this pipeline's context
     int accumulate_mode() const { return dist_world > 1 ? VB_ACCUM_SUM : VB_ACCUM_LERP; }
-    void prepare(int device);                         // uploads through the C ABI, builds the BVH
-    void render(uint32_t n_frames);                   // integrator->render
-    void final_picture(std::vector<float> &rgba);     // [all-reduce +] resolve + download (pipeline.cpp:337-354)
+    virtual void prepare(int device);                 // uploads through the C ABI, builds the BVH
+    virtual void render(uint32_t n_frames);           // integrator->render, then after_render()
+    virtual void final_picture(std::vector<float> &rgba);     // [all-reduce +] resolve + download (pipeline.cpp:337-354)
+    virtual bool output_is_display_referred() const { return false; }   // true: final_picture() is already gamma-corrected (customized graph)
+    void after_render();                              // pipeline.cpp:307-311: Sensor::after_render -> store_prev_data (sensor.cpp:85-93)
     ~Pipeline() override;
     void check(int rc, const char *what) const;
 };

@@ -62,7 +62,7 @@ int main(int argc, char **argv) {
                 p->records.width, p->records.height, n, (unsigned long long)p->build_stats.n_triangles,
                 (unsigned long long)p->build_stats.n_nodes, p->build_stats.build_ms,
                 std::chrono::duration<double, std::milli>(t1 - t0).count(), std::chrono::duration<double, std::milli>(t2 - t1).count());
-        vh::save_image(out, img.data(), p->records.width, p->records.height);      // .png / .ppm (display gamma) or .hdr / .pfm (linear)
+        vh::save_image(out, img.data(), p->records.width, p->records.height, p->output_is_display_referred());      // .png / .ppm (display gamma) or .hdr / .pfm (linear)
         if (!pfm.empty()) {
             std::vector<float> acc((size_t)p->records.width * p->records.height * 4);
             p->check(vb_film_download(p->ctx, acc.data(), VB_FILM_ACCUM), "vb_film_download");
