@@ -254,6 +254,20 @@ VB_API int vb_pass_gamma(vb_ctx *ctx);
 /* ---- debug / parity surface ------------------------------------------------------------------- */
 /* primary hit of every pixel for one frame index (== reference rt_compute_pixel, frame_buffer.cpp:277-291) */
 VB_API int vb_dump_primary_hits(vb_ctx *ctx, uint32_t frame_index, const vb_hits_soa *out);
+/* Per-vertex dump of ONE path (the first place to look when a film differs from the oracle's): pixel (px, py) of frame
+ * `frame_index` is traced by the megakernel loop and one record is written per closest-hit ray of IlluminationIntegrator::Li
+ * (reference src/base/integral/integrator.cpp:160-311, its only_direct supplement included) with the path state BEFORE that vertex
+ * is shaded; a last record with inst = prim = VB_PATH_END carries the final throughput and radiance (= the pixel-sample the film gets).
+ * `out` is host memory for `max` records; *n_vertices = records the path produced (all of them written only if <= max). */
+#define VB_PATH_END 0xfffffffeu
+typedef struct vb_path_vertex {
+    float ray_o[3], ray_tmin, ray_d[3], ray_tmax;      /* the ray as traced */
+    uint32_t inst, prim; float u, v;                   /* its closest hit; VB_INVALID_ID = miss */
+    float t; uint32_t bounces, sampler_state, medium;  /* hit distance; Li's `bounces`; LCG state and current medium id before the vertex */
+    float throughput[3], scatter_pdf;
+    float radiance[3], eta_scale;                      /* `ret` so far (shadow rays of earlier vertices resolved) */
+} vb_path_vertex;
+VB_API int vb_dump_path_trace(vb_ctx *ctx, uint32_t px, uint32_t py, uint32_t frame_index, vb_path_vertex *out, uint32_t max, uint32_t *n_vertices);
 /* counters of the last vb_render_frames call: [0] closest-hit rays, [1] any-hit rays, [2] shaded vertices,
  * [3] shadow rays culled before tracing because their contribution is exactly zero (the reference traces them:
  * [1] + [3] is its any-hit count) */

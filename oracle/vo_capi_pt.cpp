@@ -175,6 +175,15 @@ void vo_gbuffer(void *h, uint32_t w, uint32_t hgt, uint32_t frame, float *out, i
     for (auto &x : th) x.join();
 }
 
+// per-vertex dump of one path (the record layout of vb_dump_path_trace): returns the number of records, writes at most `max`
+uint32_t vo_dump_path_trace(void *h, uint32_t w, uint32_t hgt, uint32_t px, uint32_t py, uint32_t frame, vb_path_vertex *out, uint32_t max) {
+    const Scene &s = *(Scene *)h;
+    std::vector<vb_path_vertex> v;
+    s.render_sample(px, py, w, hgt, frame, nullptr, nullptr, nullptr, &v);
+    for (uint32_t i = 0; i < v.size() && i < max; ++i) out[i] = v[i];
+    return (uint32_t)v.size();
+}
+
 // rt_gradient (FrameBuffer::compute_gradient, frame_buffer.cpp:221-275) over the NORMAL and GEOM planes: out = w*h float4
 // (normal_fwidth, depth_gradient, 0, 0). Loop order, clipping and the divisions by the sample counts as written there.
 void vo_gbuffer_gradient(const float *normal, const float *geom, uint32_t w, uint32_t hgt, float *out) {

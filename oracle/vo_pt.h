@@ -67,7 +67,9 @@ struct Scene {
     // one pixel-sample: returns L (linear sRGB), optionally the primary hit
     // aov (nullable, 20 floats): rt_geom's G-buffer planes for this pixel-sample (frame_buffer.cpp:156-219) - normal.xyz 1 | albedo.rgb 1 |
     // emission.rgb 1 | linear depth, p_film.x, p_film.y, hit flag | motion vector.xy 0 0; when given, the function returns after the camera stage
-    float3 render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st, float *aov = nullptr) const;
+    // dump (nullable): one vb_path_vertex per closest-hit ray of Li with the path state before the vertex, then the VB_PATH_END record
+    float3 render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st, float *aov = nullptr,
+                         std::vector<vb_path_vertex> *dump = nullptr) const;
 };
 
 // ---- shared small functions (unit-tested against known answers) ----

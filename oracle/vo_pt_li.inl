@@ -382,7 +382,8 @@ inline BSDFSample phase_sample(float g, float3 wo, Sampler &sampler) {
 
 }  // namespace
 
-float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st, float *aov) const {
+float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, uint32_t frame, Hit *primary, PathStats *st, float *aov,
+                            std::vector<vb_path_vertex> *dump) const {
     Sampler sampler;
     // ---- rt_geom: camera ray, reference frame_buffer.cpp:172-182, sampler.h:65-73 ----
     sampler.start(px, py, frame, 0u);
@@ -491,8 +492,20 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
     const float3 primary_dir = ray.d;
     float eta_scale = 1.f;
     const uint32_t max_depth = params.max_depth;
+    auto put = [&](const Ray &r, uint32_t inst, uint32_t prim, float u, float v, float t, uint32_t bounces) {
+        if (!dump) return;
+        vb_path_vertex o{};
+        o.ray_o[0] = r.o.x; o.ray_o[1] = r.o.y; o.ray_o[2] = r.o.z; o.ray_tmin = r.tmin;
+        o.ray_d[0] = r.d.x; o.ray_d[1] = r.d.y; o.ray_d[2] = r.d.z; o.ray_tmax = r.tmax;
+        o.inst = inst; o.prim = prim; o.u = u; o.v = v; o.t = t;
+        o.bounces = bounces; o.sampler_state = sampler.state; o.medium = ray_medium;
+        o.throughput[0] = throughput.x; o.throughput[1] = throughput.y; o.throughput[2] = throughput.z; o.scatter_pdf = scatter_pdf;
+        o.radiance[0] = ret.x; o.radiance[1] = ret.y; o.radiance[2] = ret.z; o.eta_scale = eta_scale;
+        dump->push_back(o);
+    };
     for (uint32_t bounces = 0; bounces < max_depth; ++bounces) {
         Hit hit = trace_closest(ray, st);
+        put(ray, hit.inst, hit.prim, hit.u, hit.v, hit.t, bounces);
         if (hit.is_miss()) {                                        // evaluate_miss, integrator.cpp:137-158 + lightsampler.cpp:289-300
             if (env_light != VB_INVALID_ID) {
                 const vb_light_rec &l = lights[env_light];
@@ -611,6 +624,7 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
         for (uint32_t bounce = 0; bounce < 1u; ++bounce) {
             Hit hit = trace_closest(ray, st);
             if (ray.d.x == primary_dir.x && ray.d.y == primary_dir.y && ray.d.z == primary_dir.z) break;      // primary_miss: nothing was scattered
+            put(ray, hit.inst, hit.prim, hit.u, hit.v, hit.t, max_depth);
             if (hit.is_miss()) {
                 if (env_light != VB_INVALID_ID) {
                     const vb_light_rec &l = lights[env_light];
@@ -658,6 +672,12 @@ float3 Scene::render_sample(uint32_t px, uint32_t py, uint32_t w, uint32_t h, ui
         }
     }
     (void)prev_surface_ng;
+    if (dump) {                                                     // the end record: final radiance + sampler state only
+        vb_path_vertex o{};
+        o.inst = VB_PATH_END; o.prim = VB_PATH_END; o.sampler_state = sampler.state;
+        o.radiance[0] = ret.x; o.radiance[1] = ret.y; o.radiance[2] = ret.z;
+        dump->push_back(o);
+    }
     return ret;
 }
 

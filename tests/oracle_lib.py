@@ -247,6 +247,19 @@ def oracle_gbuffer(osc, frame, threads=8, gradient=False):
     return d
 
 
+def oracle_dump_path_trace(osc, px, py, frame, max_vertices=256) -> bytes:
+    """raw vb_path_vertex records of one pixel-sample from the oracle (same layout as capi.Context.dump_path_trace)"""
+    from vision_b200 import capi
+    w, h = osc.sc.resolution
+    buf = (capi.vb_path_vertex * max_vertices)()
+    lib = osc.o.lib
+    lib.vo_dump_path_trace.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32]
+    lib.vo_dump_path_trace.restype = C.c_uint32
+    n = lib.vo_dump_path_trace(osc.h, w, h, px, py, frame, buf, max_vertices)
+    assert n <= max_vertices
+    return bytes(buf)[:n * C.sizeof(capi.vb_path_vertex)]
+
+
 def oracle_camera_prev_set(osc, pc):
     """pc: capi.vb_camera_prev or None (None = back to the static camera)"""
     lib = osc.o.lib

@@ -392,6 +392,16 @@ class vb_camera_prev(C.Structure):
                 ("pad", C.c_float * 3)]
 
 
+class vb_path_vertex(C.Structure):
+    _fields_ = [("ray_o", C.c_float * 3), ("ray_tmin", C.c_float), ("ray_d", C.c_float * 3), ("ray_tmax", C.c_float),
+                ("inst", C.c_uint32), ("prim", C.c_uint32), ("u", C.c_float), ("v", C.c_float),
+                ("t", C.c_float), ("bounces", C.c_uint32), ("sampler_state", C.c_uint32), ("medium", C.c_uint32),
+                ("throughput", C.c_float * 3), ("scatter_pdf", C.c_float), ("radiance", C.c_float * 3), ("eta_scale", C.c_float)]
+
+
+VB_PATH_END = 0xFFFFFFFE
+
+
 class vb_pt_params(C.Structure):
     _fields_ = [("max_depth", C.c_uint32), ("min_depth", C.c_uint32), ("rr_threshold", C.c_float),
                 ("mis_mode", C.c_uint32), ("spectrum", C.c_uint32), ("sampler", C.c_uint32),
@@ -466,6 +476,7 @@ def _bind_pt(lib):
         "vb_film_device_ptr": [vp, C.c_int, C.POINTER(vp)],
         "vb_dump_primary_hits": [vp, C.c_uint32, C.POINTER(vb_hits_soa)],
         "vb_render_stats": [vp, C.POINTER(C.c_uint64)],
+        "vb_dump_path_trace": [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, C.c_uint32, C.POINTER(C.c_uint32)],
         "vb_gbuffer_render": [vp, C.c_uint32],
         "vb_gbuffer_download": [vp, C.c_int, vp],
         "vb_gbuffer_gradient": [vp],
@@ -621,6 +632,15 @@ def _pt_methods():
     def pass_gamma(self):
         self._check(self.lib.vb_pass_gamma(self.h), "vb_pass_gamma")
 
+    def dump_path_trace(self, px, py, frame, max_vertices=256) -> bytes:
+        """the path of one pixel-sample as raw vb_path_vertex records (96 bytes each, the VB_PATH_END record last)"""
+        buf = (vb_path_vertex * max_vertices)()
+        n = C.c_uint32()
+        self._check(self.lib.vb_dump_path_trace(self.h, px, py, frame, buf, max_vertices, C.byref(n)), "vb_dump_path_trace")
+        if n.value > max_vertices:
+            raise VbError(f"vb_dump_path_trace: the path has {n.value} vertices, room for {max_vertices}")
+        return bytes(buf)[:n.value * C.sizeof(vb_path_vertex)]
+
     def dump_primary_hits(self, frame):
         w, h = self._res
         n = w * h
@@ -656,7 +676,7 @@ def _pt_methods():
         return {"closest_nodes": w[0], "closest_tris": w[1], "any_nodes": w[2], "any_tris": w[3]}
 
     for f in (render_work, upload_scene, render_frames, film_clear, film_resolve, film_download, film_device_ptr,
-              dump_primary_hits, render_stats, gbuffer, camera_prev_set, pass_tonemapping, pass_gamma, nccl_comm_create, nccl_comm_destroy, film_allreduce):
+              dump_primary_hits, dump_path_trace, render_stats, gbuffer, camera_prev_set, pass_tonemapping, pass_gamma, nccl_comm_create, nccl_comm_destroy, film_allreduce):
         setattr(Context, f.__name__, f)
 
 

@@ -200,6 +200,58 @@ __global__ void __launch_bounds__(256) k_gbuffer_gradient(const float4 *normal, 
     out[pix] = make_float4(length(nf), fabsf(ddx) + fabsf(ddy), 0.f, 0.f);
 }
 
+// vb_dump_path_trace: the megakernel loop for ONE pixel-sample, every lane of one warp walking the same path (no divergence, lane 0
+// writes): one record per closest-hit ray with the path state before pt_bounce, then the VB_PATH_END record.
+template <int VARIANT>
+__global__ void __launch_bounds__(32) k_dump_path(const __grid_constant__ PtScene S, uint32_t px, uint32_t py, uint32_t frame,
+                                                  vb_path_vertex *out, uint32_t max_out, uint32_t *n_out) {
+    __shared__ uint2 s_stack_all[VB_SM_STACK * 32];
+    uint2 *s_stack = s_stack_all + threadIdx.x;
+    const VbTrav mg = vb_trav_init();
+    uint32_t d0 = 0, d1 = 0, n = 0;
+    Sampler sampler;
+    sampler.start(px, py, frame, 0u);
+    VbRay ray = generate_camera_ray(S, sampler, px, py);
+    PathState ps;
+    path_begin(S, ps, px, py, frame);
+    auto put = [&](const VbRay &r, uint32_t inst, uint32_t prim, float u, float v, float t) {
+        if (threadIdx.x == 0 && n < max_out) {
+            vb_path_vertex &o = out[n];
+            o.ray_o[0] = r.ox; o.ray_o[1] = r.oy; o.ray_o[2] = r.oz; o.ray_tmin = r.tmin;
+            o.ray_d[0] = r.dx; o.ray_d[1] = r.dy; o.ray_d[2] = r.dz; o.ray_tmax = r.tmax;
+            o.inst = inst; o.prim = prim; o.u = u; o.v = v; o.t = t;
+            o.bounces = ps.bounces; o.sampler_state = ps.sampler.state; o.medium = ps.ray_medium;
+            o.throughput[0] = ps.throughput.x; o.throughput[1] = ps.throughput.y; o.throughput[2] = ps.throughput.z; o.scatter_pdf = ps.scatter_pdf;
+            o.radiance[0] = ps.ret.x; o.radiance[1] = ps.ret.y; o.radiance[2] = ps.ret.z; o.eta_scale = ps.eta_scale;
+        }
+        n++;
+    };
+    if (S.params.max_depth > 0) {
+        for (;;) {
+            VbHit hit;
+            vb_traverse<false, false>(S.accel, ray, hit, s_stack, 32, d0, d1, mg);
+            put(ray, hit.inst, hit.prim, hit.u, hit.v, hit.t);
+            VbRay shadow;
+            f3 pending{0, 0, 0};
+            int flags = pt_bounce<VARIANT>(S, ps, ray, hit, shadow, pending);
+            if (flags & PT_SHADOW) {
+                VbHit sh;
+                if (!vb_traverse<true, false>(S.accel, shadow, sh, s_stack, 32, d0, d1, mg)) ps.ret = ps.ret + pending;
+            }
+            if (!(flags & PT_CONTINUE)) break;
+        }
+    }
+    if (threadIdx.x == 0 && n < max_out) {                          // the end record: final radiance + sampler state only
+        vb_path_vertex o;
+        memset(&o, 0, sizeof(o));
+        o.inst = VB_PATH_END; o.prim = VB_PATH_END; o.sampler_state = ps.sampler.state;
+        o.radiance[0] = ps.ret.x; o.radiance[1] = ps.ret.y; o.radiance[2] = ps.ret.z;
+        out[n] = o;
+    }
+    n++;
+    if (threadIdx.x == 0) *n_out = n;
+}
+
 // render-graph passes (pass/tonemapping.cpp:26-33, pass/gamma.cpp:21-27). linear_to_srgb: the sRGB OETF on [0, 1] with the
 // power written over the shared vlog / vexp, so that the host restatement gives the same bits.
 __device__ __forceinline__ float linear_to_srgb1(float x) {
@@ -307,6 +359,7 @@ struct vb_pt_state {
     float *d_spd_values = nullptr; float4 *d_spd_meta = nullptr; uint32_t n_spds = 0; std::vector<uint32_t> h_spd_sizes;
     float *d_rgb2spec = nullptr; vb_spectrum_rec spectrum{}; bool have_spectrum = false;
     float4 *d_gbuffer = nullptr; size_t gbuffer_n = 0;       // VB_AOV_COUNT planes of w*h float4 (vb_gbuffer_render, vb_gbuffer_gradient)
+    vb_path_vertex *dump_out = nullptr; uint32_t dump_max = 0, dump_px = 0, dump_py = 0; uint32_t *dump_n = nullptr;   // vb_dump_path_trace request (pt_launch)
     bool gbuffer_valid = false;                              // a vb_gbuffer_render has filled the planes
     vb_camera_prev cam_prev{}; bool have_cam_prev = false;   // vb_camera_prev_set
     float4 *view = nullptr;                                  // VB_FILM_VIEW (vb_pass_gamma), allocated on first use
@@ -720,6 +773,16 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     S.cam = p->cam; S.params = p->params; S.width = p->w; S.height = p->h;
     if (S.params.ray_offset_factor == 0.f) S.params.ray_offset_factor = 1.f;
     uint32_t n_pix = p->w * p->h;
+    if (p->dump_out) {                                               // vb_dump_path_trace: one pixel-sample, one warp
+        ctx->prof_begin("dump_path", 1);
+        const bool hero = S.params.spectrum == VB_SPECTRUM_HERO;
+        if (hero) k_dump_path<PT_HERO | PT_PRINCIPLED | PT_LOBESET><<<1, 32, 0, ctx->stream>>>(S, p->dump_px, p->dump_py, first, p->dump_out, p->dump_max, p->dump_n);
+        else if (p->has_principled) k_dump_path<PT_PRINCIPLED | PT_LOBESET><<<1, 32, 0, ctx->stream>>>(S, p->dump_px, p->dump_py, first, p->dump_out, p->dump_max, p->dump_n);
+        else k_dump_path<PT_LEAN><<<1, 32, 0, ctx->stream>>>(S, p->dump_px, p->dump_py, first, p->dump_out, p->dump_max, p->dump_n);
+        ctx->prof_end();
+        VB_CHECK_LAUNCH();
+        return VB_OK;
+    }
     if (gbuf) {                                                      // rt_geom's G-buffer planes for frame index `first`
         unsigned g = (n_pix + PT_BLOCK - 1) / PT_BLOCK;
         ctx->prof_begin("gbuffer", 1);
@@ -921,6 +984,27 @@ int vb_dump_primary_hits(vb_ctx *ctx, uint32_t frame_index, const vb_hits_soa *o
         for (int k = 0; k < 5; ++k) VB_CUDA(cudaMemcpyAsync(dst[k], src[k], n * 4, cudaMemcpyDeviceToHost, ctx->stream));
         VB_CUDA(cudaStreamSynchronize(ctx->stream));
     }
+    return VB_OK;
+}
+
+int vb_dump_path_trace(vb_ctx *ctx, uint32_t px, uint32_t py, uint32_t frame_index, vb_path_vertex *out, uint32_t max, uint32_t *n_vertices) {
+    if (!ctx || !n_vertices || (!out && max)) return VB_ERR_INVALID;
+    vb_pt_state *p = pt_state(ctx);
+    if (!p->accum) return ctx->fail(VB_ERR_STATE, "vb_dump_path_trace: no film");
+    if (px >= p->w || py >= p->h) return ctx->fail(VB_ERR_INVALID, "vb_dump_path_trace: pixel outside the film");
+    cudaSetDevice(ctx->device);
+    int rc = ctx->ensure_stage(sizeof(vb_path_vertex) * (size_t)max + 16);
+    if (rc) return rc;
+    p->dump_out = (vb_path_vertex *)((char *)ctx->stage + 16); p->dump_n = (uint32_t *)ctx->stage;
+    p->dump_max = max; p->dump_px = px; p->dump_py = py;
+    rc = pt_launch(ctx, "vb_dump_path_trace", frame_index, 1, 1, VB_ACCUM_SUM, false, nullptr, nullptr, nullptr, nullptr, nullptr);
+    vb_path_vertex *d_out = p->dump_out; uint32_t *d_n = p->dump_n;
+    p->dump_out = nullptr; p->dump_n = nullptr;
+    if (rc) return rc;
+    VB_CUDA(cudaMemcpyAsync(n_vertices, d_n, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VB_CUDA(cudaStreamSynchronize(ctx->stream));
+    const uint32_t n = *n_vertices < max ? *n_vertices : max;
+    if (n) VB_CUDA(cudaMemcpy(out, d_out, sizeof(vb_path_vertex) * (size_t)n, cudaMemcpyDeviceToHost));
     return VB_OK;
 }
 
