@@ -99,7 +99,7 @@ int vb_ctx_destroy(vb_ctx *ctx) {
     cudaFree(ctx->d_instances);
     cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
     cudaFree(ctx->stage); cudaFree(ctx->sort_buf);
-    for (int k = 0; k < 2; ++k) { cudaFree(ctx->rec_stage[k]); if (ctx->rec_done[k]) cudaEventDestroy(ctx->rec_done[k]); }
+    for (int k = 0; k < 2; ++k) { cudaFree(ctx->rec_stage[k]); if (ctx->rec_done[k]) cudaEventDestroy(ctx->rec_done[k]); if (ctx->rec_traced[k]) cudaEventDestroy(ctx->rec_traced[k]); }
     vb_pt_destroy(ctx);
     if (ctx->copy_in) {
         cudaStreamDestroy(ctx->copy_in); cudaStreamDestroy(ctx->copy_out);
@@ -151,6 +151,7 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     else if (k == "trace.host_chunks") ctx->opt_host_chunks = std::min(VB_MAX_HOST_CHUNKS, std::max(1, (int)value));
     else if (k == "trace.host_chunk_min_rays") ctx->opt_host_chunk_min_rays = std::max(1024, (int)value);
     else if (k == "trace.async") ctx->opt_trace_async = value != 0 ? 1 : 0;
+    else if (k == "trace.async_chunks") ctx->opt_async_chunks = std::min(VB_MAX_HOST_CHUNKS, std::max(1, (int)value));
     else if (k == "trace.blocks_per_sm") ctx->opt_blocks_per_sm = std::max(1, (int)value);
     else return ctx->fail(VB_ERR_INVALID, "vb_ctx_set_option: unknown key " + k);
     return VB_OK;

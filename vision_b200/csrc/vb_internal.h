@@ -102,8 +102,9 @@ struct vb_ctx {
     cudaEvent_t ev_in[VB_MAX_HOST_CHUNKS] = {}, ev_out[VB_MAX_HOST_CHUNKS] = {};
     int ensure_copy_streams();
     // record-form host calls (vb_trace_*_records): two alternating staging sets, "done" event of the call that last used each
-    void *rec_stage[2] = {nullptr, nullptr}; size_t rec_bytes[2] = {0, 0}; cudaEvent_t rec_done[2] = {nullptr, nullptr};
+    void *rec_stage[2] = {nullptr, nullptr}; size_t rec_bytes[2] = {0, 0}; cudaEvent_t rec_done[2] = {nullptr, nullptr}, rec_traced[2] = {nullptr, nullptr};
     unsigned rec_call = 0; bool rec_pending = false;
+    int opt_async_chunks = 2;                // ray ranges per host-buffer record call when trace.async = 1
     int opt_trace_async = 0;                 // 1: host-buffer record calls return once queued; vb_ctx_synchronize completes them
     vb_pt_state *pt = nullptr;
 

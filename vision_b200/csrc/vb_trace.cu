@@ -360,6 +360,9 @@ int run_trace_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits,
     int C = 1;
     if (host && ctx->opt_host_chunks > 1 && n >= (uint64_t)ctx->opt_host_chunk_min_rays * 2)
         C = (int)std::min<uint64_t>((uint64_t)std::min(ctx->opt_host_chunks, VB_MAX_HOST_CHUNKS), n / (uint64_t)ctx->opt_host_chunk_min_rays);
+    // asynchronous calls overlap ACROSS calls (copy-in of call k + 1 under the traversal of call k), so fewer, larger ranges win:
+    // they sort and trace more efficiently (measured, tools/sweep_e2e.sh: 1 / 2 / 3 / 4 / 6 ranges = 1542 / 1629 / 1617 / 1550 / 1442 Mrays/s)
+    if (ctx->opt_trace_async) C = std::min(C, std::max(1, ctx->opt_async_chunks));
     const uint64_t per = C > 1 ? (((n + C - 1) / C + 1023) & ~1023ull) : n;
     if (host) { int rc = ctx->ensure_copy_streams(); if (rc) return rc; }
     cudaStream_t s_in = host ? ctx->copy_in : st, s_out = host ? ctx->copy_out : st;
@@ -377,14 +380,28 @@ int run_trace_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits,
             VB_CUDA(cudaMalloc(&ctx->rec_stage[set], need));
             ctx->rec_bytes[set] = need;
         }
-        if (!ctx->rec_done[set]) VB_CUDA(cudaEventCreateWithFlags(&ctx->rec_done[set], cudaEventDisableTiming));
-        else VB_CUDA(cudaStreamWaitEvent(s_in, ctx->rec_done[set], 0));      // the call that used this set two calls ago has drained
+        // The set was last used two calls ago. Its RAY half is free once that call's traversal has run (rec_traced, on the context's
+        // stream): this call's host-to-device copies wait for that only. Its RESULT half is free once that call's device-to-host copies
+        // have drained (rec_done, on the copy-out stream): this call's kernels wait for that. With one event for both, copy-in of call
+        // k + 2 could not start before copy-out of call k had finished and the three engines never ran at the same time.
+        if (!ctx->rec_done[set]) {
+            VB_CUDA(cudaEventCreateWithFlags(&ctx->rec_done[set], cudaEventDisableTiming));
+            VB_CUDA(cudaEventCreateWithFlags(&ctx->rec_traced[set], cudaEventDisableTiming));
+        } else {
+            VB_CUDA(cudaStreamWaitEvent(s_in, ctx->rec_traced[set], 0));
+            VB_CUDA(cudaStreamWaitEvent(st, ctx->rec_done[set], 0));
+        }
         char *base = (char *)ctx->rec_stage[set];
         d_rays = (const float4 *)base;
         if (any) d_occ = (uint8_t *)(base + 32 * n); else d_hits = (uint4 *)(base + 32 * n);
-        // the copy streams start after whatever the caller queued on the context's stream
-        VB_CUDA(cudaEventRecord(ctx->ev_in[0], st));
-        VB_CUDA(cudaStreamWaitEvent(s_in, ctx->ev_in[0], 0));
+        // synchronous calls: the copy-in stream starts after whatever the caller queued on the context's stream. Asynchronous calls
+        // ("trace.async"): no such edge - the context's stream still holds the PREVIOUS call's traversal, and the point of the mode is
+        // that this call's copy-in runs under it; host input buffers are read as of the call, like any host pointer handed to an
+        // asynchronous copy
+        if (!ctx->opt_trace_async) {
+            VB_CUDA(cudaEventRecord(ctx->ev_in[0], st));
+            VB_CUDA(cudaStreamWaitEvent(s_in, ctx->ev_in[0], 0));
+        }
     }
     int rc = ctx->ensure_stage(256 + 8 * (size_t)VB_MAX_HOST_CHUNKS * 2);
     if (rc) return rc;
@@ -451,6 +468,7 @@ int run_trace_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits,
     ctx->prof_end();
     VB_CHECK_LAUNCH();
     if (host) {
+        VB_CUDA(cudaEventRecord(ctx->rec_traced[set], st));
         VB_CUDA(cudaEventRecord(ctx->rec_done[set], s_out));
         ctx->rec_pending = true;
         if (!ctx->opt_trace_async) return vb_ctx_synchronize(ctx);       // host buffers are valid (and reusable) on return
