@@ -1,4 +1,4 @@
-"""Sweep the traversal tunables on the bench workload (run under gpurun)."""
+"""Sweep the traversal tunables on the bench workload (run under gpurun): trace.refill_thr x trace.tri_thr x trace.blocks_per_sm."""
 import itertools, json, sys
 from pathlib import Path
 import torch
@@ -14,19 +14,16 @@ mid = ctx.mesh_upload_soup(mesh); ctx.instances_set([{"mesh_id": mid}])
 d = {k: torch.from_numpy(v).cuda() for k, v in rays.items()}
 da = dict(d, tmax=d["tmax_any"])
 hits = None; occ = None
+st = ctx.accel_build()
 def run(tag):
     global hits, occ
     for _ in range(2):
         hits = ctx.trace_closest(d, hits); occ = ctx.trace_any(da, occ)
     ctx.profile_reset()
-    for _ in range(3):
+    for _ in range(4):
         hits = ctx.trace_closest(d, hits); occ = ctx.trace_any(da, occ)
     c, _ = ctx.profile_get("trace_closest"); a, _ = ctx.profile_get("trace_any")
-    _, nn, nt = ctx.trace_closest(d, hits, counted=True)
-    print(f"{tag}: closest {c/3:.2f} ms ({n/(c/3)/1e3:.0f} Mrays/s)  any {a/3:.2f} ms ({n/(a/3)/1e3:.0f} Mrays/s) nodes/ray {nn/n:.1f} tris/ray {nt/n:.1f}", flush=True)
-for ml in (1,):
-    ctx.set_option("build.max_leaf", ml)
-    st = ctx.accel_build()
-    for bps in (8, 10):
-        ctx.set_option("trace.blocks_per_sm", bps)
-        run(f"max_leaf={ml} bps={bps}")
+    print(f"{tag}: closest {c/4:.2f} ms any {a/4:.2f} ms total {2*n/((c+a)/4)/1e3:.0f} Mrays/s", flush=True)
+for refill, tri, bps in itertools.product((24, 28, 30), (8, 12, 16), (8, 12)):
+    ctx.set_option("trace.refill_thr", refill); ctx.set_option("trace.tri_thr", tri); ctx.set_option("trace.blocks_per_sm", bps)
+    run(f"refill={refill} tri={tri} bps={bps}")

@@ -12,7 +12,9 @@
 namespace vh {
 
 // ---- images ------------------------------------------------------------------------------------
-static float srgb_to_linear(float c) { return c <= 0.04045f ? c / 12.92f : std::pow((c + 0.055f) / 1.055f, 2.4f); }
+// sRGB EOTF of a texel, evaluated in double precision and rounded once (the Python twin does the same, so host and twin textures are
+// bit-identical; float powf differs between libm and numpy by an ulp on a few of the 256 levels)
+static float srgb_to_linear(float c) { const double x = (double)c; return (float)(x <= 0.04045 ? x / 12.92 : std::pow((x + 0.055) / 1.055, 2.4)); }
 static float linear_to_srgb(float c) { c = std::min(1.f, std::max(0.f, c)); return c <= 0.0031308f ? 12.92f * c : 1.055f * std::pow(c, 1.f / 2.4f) - 0.055f; }
 
 static bool read_pnm_token(std::istream &f, std::string &tok) {

@@ -417,7 +417,7 @@ def load_image(path, color_space):
     from PIL import Image
     im = np.asarray(Image.open(path).convert("RGBA"), np.float32) / f32(255.0)
     if color_space == "srgb" and Path(path).suffix.lower() not in (".exr", ".hdr"):
-        c = im[..., :3]
+        c = im[..., :3].astype(np.float64)            # double precision, rounded once: the C++ host layer does the same (bit-identical textures)
         lin = np.where(c <= 0.04045, c / 12.92, ((c + 0.055) / 1.055) ** 2.4).astype(f32)
         im = np.concatenate([lin, im[..., 3:]], axis=-1)
     return np.ascontiguousarray(im, f32)
