@@ -140,6 +140,7 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     else if (k == "build.split_pct") ctx->opt_split_pct = std::min(400, std::max(0, (int)value));
     else if (k == "build.size_classes") ctx->opt_size_classes = value != 0 ? 1 : 0;
     else if (k == "trace.sort_rays") ctx->opt_sort_rays = (int)value;
+    else if (k == "trace.sort_skip_bits") ctx->opt_sort_skip_bits = std::min(16, std::max(0, (int)value));
     else if (k == "trace.sort_oct_shift") ctx->opt_sort_oct_shift = std::min(21, std::max(0, (int)value));
     else if (k == "trace.sort_min_rays") ctx->opt_sort_min_rays = std::max(1, (int)value);
     else if (k == "pt.schedule") ctx->opt_pt_schedule = value != 0 ? 1 : 0;

@@ -88,7 +88,8 @@ struct vb_ctx {
     int opt_split_pct = 0;                   // build: triangle pre-splitting budget, extra references in percent of the triangle count (vb_bvh_split.cuh)
     int opt_size_classes = 1;                // build: triangle size class as the top bits of the Morton sort key
     int opt_sort_rays = 1, opt_sort_min_rays = 1 << 16;
-    int opt_sort_oct_shift = 0;              // ray sort key: direction octant above this many low Morton bits (vb_ray_sort_key)
+    int opt_sort_skip_bits = 8;              // ray sort: low key bits the radix sort ignores (8 = two 8-bit passes instead of three, coarser order)
+    int opt_sort_oct_shift = 8;              // ray sort key: direction octant above this many low Morton bits (vb_ray_sort_key)
     int opt_pt_schedule = 0;                 // 0 = wavefront (default), 1 = megakernel
     int opt_pt_sort_material = 1;            // wavefront: order shading entries by material
     int opt_pt_spec_cache = 1;               // hero spectrum: constant colour slots decoded once per scene (k_spec_cache)

@@ -272,7 +272,7 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
         if (do_sort) {
             size_t cub_bytes = 0;
             cub::DoubleBuffer<uint32_t> dk0(nullptr, nullptr), dv0(nullptr, nullptr);
-            VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk0, dv0, (int)m, 0, 24, st));
+            VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk0, dv0, (int)m, ctx->opt_sort_skip_bits, 24, st));
             size_t nb = ((m * 4 + 255) & ~255ull);
             size_t total = 4 * nb + 32 * m + cub_bytes + 256;
             if (total > ctx->sort_bytes) {
@@ -292,7 +292,7 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
             unsigned g2 = (unsigned)((m + 255) / 256);
             k_ray_keys<<<g2, 256, 0, st>>>(Rc, (uint32_t)m, lo, ie, k0, v0, d_aos, (uint32_t)ctx->opt_sort_oct_shift);
             cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
-            cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)m, 0, 24, st);
+            cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)m, ctx->opt_sort_skip_bits, 24, st);
             if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }
             perm = dv.Current();
             RS = d_aos;                 // k_trace gathers ray perm[i] itself: no separate reorder pass
@@ -429,7 +429,7 @@ int run_trace_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits,
         if (ctx->opt_sort_rays && m >= (uint64_t)ctx->opt_sort_min_rays) {
             size_t cub_bytes = 0;
             cub::DoubleBuffer<uint32_t> dk0(nullptr, nullptr), dv0(nullptr, nullptr);
-            VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk0, dv0, (int)m, 0, 24, st));
+            VB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk0, dv0, (int)m, ctx->opt_sort_skip_bits, 24, st));
             size_t nb = ((m * 4 + 255) & ~255ull);
             size_t total = 4 * nb + cub_bytes + 256;
             if (total > ctx->sort_bytes) {
@@ -447,7 +447,7 @@ int run_trace_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits,
                                     1.f / fmaxf(ctx->sort_hi[2] - ctx->sort_lo[2], 1e-30f));
             k_ray_keys_aos<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(RS, (uint32_t)m, lo, ie, k0, v0, (uint32_t)ctx->opt_sort_oct_shift);
             cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(v0, v1);
-            cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)m, 0, 24, st);
+            cudaError_t ce = cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, dk, dv, (int)m, ctx->opt_sort_skip_bits, 24, st);
             if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }
             perm = dv.Current();
             launches += 5;
@@ -498,14 +498,14 @@ int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *
     if (ctx->opt_sort_rays && !coherent && n >= (uint32_t)ctx->opt_sort_min_rays) {
         size_t cub_bytes = 0;
         cub::DoubleBuffer<uint64_t> dk(keyidx, keyidx_alt);
-        VB_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, cub_bytes, dk, (int)n, 32, 56, st));
+        VB_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, cub_bytes, dk, (int)n, 32 + ctx->opt_sort_skip_bits, 56, st));
         if (cub_bytes > ctx->sort_bytes) {
             if (ctx->sort_buf) cudaFree(ctx->sort_buf);
             ctx->sort_buf = nullptr; ctx->sort_bytes = 0;
             VB_CUDA(cudaMalloc(&ctx->sort_buf, cub_bytes + 256));
             ctx->sort_bytes = cub_bytes + 256;
         }
-        cudaError_t ce = cub::DeviceRadixSort::SortKeys(ctx->sort_buf, cub_bytes, dk, (int)n, 32, 56, st);
+        cudaError_t ce = cub::DeviceRadixSort::SortKeys(ctx->sort_buf, cub_bytes, dk, (int)n, 32 + ctx->opt_sort_skip_bits, 56, st);
         if (ce != cudaSuccess) { ctx->prof_end(); return ctx->fail(VB_ERR_CUDA, std::string("ray sort: ") + cudaGetErrorString(ce)); }
         perm = (const uint32_t *)dk.Current();
         launches += 4;
