@@ -79,7 +79,7 @@ struct vb_ctx {
     void *stage = nullptr; size_t stage_bytes = 0;
     int sm_count = 148;
     // tunables (vb_ctx_set_option)
-    int opt_refill_thr = 28, opt_tri_thr = 12, opt_blocks_per_sm = 8;
+    int opt_refill_thr = 24, opt_tri_thr = 12, opt_blocks_per_sm = 8;
     int opt_max_leaf = 1;
     int opt_ploc = -1;                       // build: 1 = PLOC clustering (vb_bvh_ploc.cuh), 0 = radix tree, -1 = automatic
     bool last_build_ploc = false;
