@@ -191,10 +191,10 @@ def pt_section(a, rank, world, local_rank, stream, which="cbox"):
             hp.film_allreduce()
         ctx.film_resolve(capi.VB_ACCUM_SUM if world > 1 else capi.VB_ACCUM_LERP, info["exposure"], info["tonemap"])
 
-    # warm-up: one FULL wavefront batch per rank (pt.max_paths = 32 Mi paths: the queues reach their final size here, so that no
+    # warm-up: one FULL wavefront batch per rank (pt.max_paths = 64 Mi paths: the queues reach their final size here, so that no
     # cudaMalloc of several GB lands in the timed region - measured: up to 0.6 s when earlier sections had just freed theirs), not the
     # whole config
-    hp.invalidate(); hp.render(min(spp_total, max(2, (1 << 25) // (w * h)) * world))
+    hp.invalidate(); hp.render(min(spp_total, max(2, (1 << 26) // (w * h)) * world))
     if world > 1:
         hp.film_allreduce()
     torch.cuda.synchronize()

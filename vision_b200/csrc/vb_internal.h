@@ -95,7 +95,7 @@ struct vb_ctx {
     int opt_pt_spec_cache = 1;               // hero spectrum: constant colour slots decoded once per scene (k_spec_cache)
     int opt_pt_split_principled = 1;         // wavefront: principled-BSDF entries shaded by their own launch, the rest by the lean kernel
     int opt_pt_count_work = 0;               // wavefront: instrumented traversal (nodes / triangles per ray), never timed
-    int64_t opt_pt_max_paths = 1 << 25;      // wavefront: paths in flight per batch
+    int64_t opt_pt_max_paths = 1 << 26;      // wavefront: paths in flight per batch
     void *sort_buf = nullptr; size_t sort_bytes = 0;
     // host-buffer calls of vb_trace_*: ray ranges pipelined over copy-in / compute / copy-out streams (vb_trace.cu run_trace)
     int opt_host_chunks = 4, opt_host_chunk_min_rays = 1 << 20;
