@@ -37,6 +37,8 @@ struct BuildBufs {
     uint32_t *flags;       // T-1
     uint32_t *cls_count;   // 4    triangles per size class (k_morton)
     double *moments;       // 6    sum and sum of squares of the triangle centroids (ray-sort box, size classes)
+    float extra_pad;       // added to the conservative leaf padding (bottom-level trees of the two-level structure: rounding of the ray's transform)
+    uint32_t absolute;     // 1: leaf records hold the three vertices (p0,prim) (p1) (p2) instead of (v0,prim) (e1,inst) (e2,0)
 };
 
 // normative world transform: FMA chain identical to oracle vo::transform_point
@@ -70,8 +72,13 @@ __global__ void __launch_bounds__(256) k_flatten(const InstGeom *inst, const uin
         float3 e1 = make_float3(__fsub_rn(p1.x, p0.x), __fsub_rn(p1.y, p0.y), __fsub_rn(p1.z, p0.z));
         float3 e2 = make_float3(__fsub_rn(p2.x, p0.x), __fsub_rn(p2.y, p0.y), __fsub_rn(p2.z, p0.z));
         b.tri_in[3 * (size_t)g + 0] = make_float4(p0.x, p0.y, p0.z, __uint_as_float(prim));
-        b.tri_in[3 * (size_t)g + 1] = make_float4(e1.x, e1.y, e1.z, __uint_as_float(a));
-        b.tri_in[3 * (size_t)g + 2] = make_float4(e2.x, e2.y, e2.z, 0.f);
+        if (b.absolute) {                      // bottom-level tree: the traversal transforms the vertices itself (vb_traverse_tl)
+            b.tri_in[3 * (size_t)g + 1] = make_float4(p1.x, p1.y, p1.z, 0.f);
+            b.tri_in[3 * (size_t)g + 2] = make_float4(p2.x, p2.y, p2.z, 0.f);
+        } else {
+            b.tri_in[3 * (size_t)g + 1] = make_float4(e1.x, e1.y, e1.z, __uint_as_float(a));
+            b.tri_in[3 * (size_t)g + 2] = make_float4(e2.x, e2.y, e2.z, 0.f);
+        }
         // bounds from v0, v0+e1, v0+e2 (what the intersector effectively sees)
         float3 q1 = make_float3(p0.x + e1.x, p0.y + e1.y, p0.z + e1.z);
         float3 q2 = make_float3(p0.x + e2.x, p0.y + e2.y, p0.z + e2.z);
@@ -193,7 +200,7 @@ __global__ void __launch_bounds__(256) k_refit(uint32_t T, BuildBufs b) {
     float dx = shi.x - slo.x, dy = shi.y - slo.y, dz = shi.z - slo.z;
     // conservative padding (DESIGN.md "Intersection contract"): slab tests never cull a hit
     // that the normative triangle test accepts
-    float pad = sqrtf(dx * dx + dy * dy + dz * dz) * 0x1p-20f + 1e-30f;
+    float pad = sqrtf(dx * dx + dy * dy + dz * dz) * 0x1p-20f + 1e-30f + b.extra_pad;
     uint32_t src = b.vals[g];
     float4 lo = b.blo[src], hi = b.bhi[src];
     lo.x -= pad; lo.y -= pad; lo.z -= pad; hi.x += pad; hi.y += pad; hi.z += pad;
@@ -211,6 +218,54 @@ __global__ void __launch_bounds__(256) k_refit(uint32_t T, BuildBufs b) {
         b.nhi[p] = make_float4(fmaxf(e.x, f.x), fmaxf(e.y, f.y), fmaxf(e.z, f.z), 0.f);
         p = b.parent[p];
     }
+}
+
+// ---- two-level structure: world box of every instance, and the top-level build's "primitives" ----
+// exact world bounds of an instance = union over its triangles of what k_flatten would compute for them (same transform chain)
+__global__ void __launch_bounds__(256) k_inst_bounds(const InstGeom *inst, const uint32_t *offsets, uint32_t n_inst, uint32_t T, uint32_t *boxes) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= T) return;
+    uint32_t a = 0, c = n_inst;
+    while (c - a > 1) { uint32_t m = (a + c) >> 1; if (offsets[m] <= g) a = m; else c = m; }
+    const InstGeom &I = inst[a];
+    uint32_t prim = g - offsets[a];
+    uint32_t i0, i1, i2;
+    if (I.soup) { i0 = 3 * prim; i1 = i0 + 1; i2 = i0 + 2; }
+    else { i0 = I.tri[3 * prim]; i1 = I.tri[3 * prim + 1]; i2 = I.tri[3 * prim + 2]; }
+    float3 p0 = xform_point(I.o2w, make_float3(I.pos[3 * i0], I.pos[3 * i0 + 1], I.pos[3 * i0 + 2]));
+    float3 p1 = xform_point(I.o2w, make_float3(I.pos[3 * i1], I.pos[3 * i1 + 1], I.pos[3 * i1 + 2]));
+    float3 p2 = xform_point(I.o2w, make_float3(I.pos[3 * i2], I.pos[3 * i2 + 1], I.pos[3 * i2 + 2]));
+    float3 e1 = make_float3(__fsub_rn(p1.x, p0.x), __fsub_rn(p1.y, p0.y), __fsub_rn(p1.z, p0.z));
+    float3 e2 = make_float3(__fsub_rn(p2.x, p0.x), __fsub_rn(p2.y, p0.y), __fsub_rn(p2.z, p0.z));
+    float3 q1 = make_float3(p0.x + e1.x, p0.y + e1.y, p0.z + e1.z), q2 = make_float3(p0.x + e2.x, p0.y + e2.y, p0.z + e2.z);
+    float lo[3] = {fminf(p0.x, fminf(fminf(p1.x, q1.x), fminf(p2.x, q2.x))), fminf(p0.y, fminf(fminf(p1.y, q1.y), fminf(p2.y, q2.y))),
+                   fminf(p0.z, fminf(fminf(p1.z, q1.z), fminf(p2.z, q2.z)))};
+    float hi[3] = {fmaxf(p0.x, fmaxf(fmaxf(p1.x, q1.x), fmaxf(p2.x, q2.x))), fmaxf(p0.y, fmaxf(fmaxf(p1.y, q1.y), fmaxf(p2.y, q2.y))),
+                   fmaxf(p0.z, fmaxf(fmaxf(p1.z, q1.z), fmaxf(p2.z, q2.z)))};
+    for (int k = 0; k < 3; ++k) { atomicMin(&boxes[6 * a + k], f2ord(lo[k])); atomicMax(&boxes[6 * a + 3 + k], f2ord(hi[k])); }
+}
+// top-level "triangles": one per instance - record (bits of the root node of its mesh's tree, instance id), box = the instance's world box
+__global__ void __launch_bounds__(256) k_tlas_prims(uint32_t n_inst, const uint32_t *boxes, const uint32_t *roots, BuildBufs b) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_inst) return;
+    float lo[3], hi[3];
+    for (int k = 0; k < 3; ++k) { lo[k] = ord2f(boxes[6 * g + k]); hi[k] = ord2f(boxes[6 * g + 3 + k]); }
+    b.tri_in[3 * (size_t)g + 0] = make_float4(__uint_as_float(roots[g]), __uint_as_float(g), 0.f, __uint_as_float(g));
+    b.tri_in[3 * (size_t)g + 1] = make_float4(0.f, 0.f, 0.f, __uint_as_float(g));
+    b.tri_in[3 * (size_t)g + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
+    b.blo[g] = make_float4(lo[0], lo[1], lo[2], __uint_as_float(g));
+    b.bhi[g] = make_float4(hi[0], hi[1], hi[2], 0.f);
+    for (int k = 0; k < 3; ++k) { atomicMin(&b.scene[k], f2ord(lo[k])); atomicMax(&b.scene[3 + k], f2ord(hi[k])); }
+    for (int k = 0; k < 3; ++k) {
+        double m = 0.5 * ((double)lo[k] + (double)hi[k]);
+        atomicAdd(b.moments + k, m); atomicAdd(b.moments + 3 + k, m * m);
+    }
+}
+// a bottom-level tree appended behind others: its nodes' child / triangle indices become absolute
+__global__ void __launch_bounds__(256) k_offset_nodes(vb_wide_node *nodes, uint32_t n, uint32_t node_off, uint32_t tri_off) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    nodes[g].child_base += node_off; nodes[g].tri_base += tri_off;
 }
 
 }  // namespace

@@ -216,27 +216,36 @@ template <class T> struct DevBuf {
 
 // One build. *too_deep = the wide tree has more levels than the traversal stack has entries (VB_TRAVERSAL_STACK_ENTRIES: one entry
 // per level is the worst case of vb_traverse); nothing is installed in that case.
-static int accel_build_once(vb_ctx *ctx, vb_build_stats *out, bool allow_ploc, bool *too_deep) {
+// What one build runs over: every instance flattened to world space (the default), ONE mesh in its object space (a bottom-level tree of the
+// two-level structure: vertices kept in the leaf records, extra leaf padding), or given boxes (the top-level tree: one "triangle" per instance).
+struct BuildInput {
+    enum Mode { FLATTEN = 0, MESH = 1, TOP = 2 } mode = FLATTEN;
+    uint32_t mesh_id = 0; float extra_pad = 0.f;                    // MESH
+    const uint32_t *inst_boxes = nullptr, *inst_roots = nullptr;    // TOP: device arrays (6 ordered uints per instance; root node per instance)
+};
+
+static int accel_build_once(vb_ctx *ctx, vb_build_stats *out, bool allow_ploc, bool *too_deep, const BuildInput &in = BuildInput()) {
     *too_deep = false;
     cudaStream_t st = ctx->stream;
-    uint32_t n_inst = (uint32_t)ctx->instances.size();
+    uint32_t n_inst = in.mode == BuildInput::MESH ? 1u : (uint32_t)ctx->instances.size();
     if (n_inst == 0) return ctx->fail(VB_ERR_STATE, "vb_accel_build: no instances set");
     std::vector<InstGeom> hg(n_inst);
     std::vector<uint32_t> off(n_inst + 1, 0);
     uint64_t total = 0;
     for (uint32_t i = 0; i < n_inst; ++i) {
-        const vb_device_mesh &m = ctx->meshes[ctx->instances[i].mesh_id];
+        const vb_device_mesh &m = ctx->meshes[in.mode == BuildInput::MESH ? in.mesh_id : ctx->instances[i].mesh_id];
         hg[i].pos = m.pos; hg[i].tri = m.tri; hg[i].soup = m.soup ? 1u : 0u; hg[i].pad = 0;
-        memcpy(hg[i].o2w, ctx->instances[i].o2w, 64);
+        if (in.mode == BuildInput::MESH) { for (int k = 0; k < 16; ++k) hg[i].o2w[k] = (k % 5 == 0) ? 1.f : 0.f; }
+        else memcpy(hg[i].o2w, ctx->instances[i].o2w, 64);
         off[i] = (uint32_t)total;
-        total += m.nt;
+        total += in.mode == BuildInput::TOP ? 1u : m.nt;
     }
     if (total == 0) return ctx->fail(VB_ERR_STATE, "vb_accel_build: scene has no triangles");
     if (total > 0x7fffffffull / 3) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_accel_build: more than 715M triangles");
     off[n_inst] = (uint32_t)total;
     uint32_t T = (uint32_t)total;
 
-    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
+    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris); cudaFree(ctx->accel.xf);
     ctx->accel = vb_accel();
 
     DevBuf<InstGeom> d_geom; DevBuf<uint32_t> d_off;
@@ -252,7 +261,8 @@ static int accel_build_once(vb_ctx *ctx, vb_build_stats *out, bool allow_ploc, b
 
     // the per-leaf buffers are sized after the pre-splitting pass (R references >= T triangles)
     BuildBufs b{tri_in.p, blo.p, bhi.p, scene.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
-                nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, cls_count.p, moments.p};
+                nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, cls_count.p, moments.p,
+                in.mode == BuildInput::MESH ? in.extra_pad : 0.f, in.mode == BuildInput::MESH ? 1u : 0u};
 
     cudaEvent_t e0 = ctx->get_event(), e1 = ctx->get_event();
     VB_CUDA(cudaMemcpyAsync(d_geom.p, hg.data(), sizeof(InstGeom) * n_inst, cudaMemcpyHostToDevice, st));
@@ -264,11 +274,13 @@ static int accel_build_once(vb_ctx *ctx, vb_build_stats *out, bool allow_ploc, b
     uint64_t launches = 0;
     uint32_t grid = (T + 255) / 256;
     VB_CUDA(cudaMemsetAsync(moments.p, 0, 8 * sizeof(double), st));
-    k_flatten<<<grid, 256, 0, st>>>(d_geom.p, d_off.p, n_inst, T, b); launches++;
+    if (in.mode == BuildInput::TOP) k_tlas_prims<<<grid, 256, 0, st>>>(T, in.inst_boxes, in.inst_roots, b);
+    else k_flatten<<<grid, 256, 0, st>>>(d_geom.p, d_off.p, n_inst, T, b);
+    launches++;
     VB_CHECK_LAUNCH();
     // ---- triangle pre-splitting (vb_bvh_split.cuh): T triangles -> R references ----
     const uint32_t T_tris = T;
-    if (ctx->opt_split_pct > 0 && T >= 8) {
+    if (ctx->opt_split_pct > 0 && T >= 8 && in.mode == BuildInput::FLATTEN) {
         DevBuf<float> prio; DevBuf<uint32_t> s_count, s_offs;
         VB_CUDA(prio.alloc(T)); VB_CUDA(s_count.alloc(T)); VB_CUDA(s_offs.alloc(T));
         k_split_priority<<<grid, 256, 0, st>>>(T, b, prio.p, moments.p + 6); launches++;
@@ -381,6 +393,7 @@ static int accel_build_once(vb_ctx *ctx, vb_build_stats *out, bool allow_ploc, b
             return VB_OK;
         }
     }
+    ctx->last_build_levels = levels;
     VB_CUDA(cudaEventRecord(e1, st));
     VB_CUDA(cudaStreamSynchronize(st));
     float ms = 0.f;
@@ -423,7 +436,174 @@ static int accel_build_once(vb_ctx *ctx, vb_build_stats *out, bool allow_ploc, b
 // Agglomerative clustering can produce chain-like trees (nested shells: every merge adds one triangle to the cluster inside it) whose
 // wide form is deeper than the traversal stack; the radix tree's depth is bounded by its key length (63 Morton + 32 index bits, seven
 // binary levels per wide level on a chain), so such a scene is rebuilt with it. A tree that is still too deep is refused.
+// one tree with the PLOC -> radix fallback of the single-level build
+static int accel_build_tree(vb_ctx *ctx, const BuildInput &in, const char *what) {
+    bool too_deep = false;
+    int rc = accel_build_once(ctx, nullptr, true, &too_deep, in);
+    if (rc || !too_deep) return rc;
+    if (ctx->last_build_ploc) {
+        ctx->prof["bvh_build_radix_fallback"].launches += 1;
+        rc = accel_build_once(ctx, nullptr, false, &too_deep, in);
+        if (rc || !too_deep) return rc;
+    }
+    return ctx->fail(VB_ERR_UNSUPPORTED, std::string("vb_accel_build: ") + what + " is deeper than the traversal stack");
+}
+
+// inverse of an affine object-to-world matrix (column-major 4x4) by Gauss-Jordan elimination with row pivoting in double precision
+static bool invert_affine(const float *m, double inv[4][4]) {
+    double a[4][8];
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { a[r][c] = m[c * 4 + r]; a[r][4 + c] = r == c ? 1.0 : 0.0; }
+    for (int i = 0; i < 4; ++i) {
+        int piv = i;
+        for (int r = i + 1; r < 4; ++r) if (std::fabs(a[r][i]) > std::fabs(a[piv][i])) piv = r;
+        if (!(std::fabs(a[piv][i]) > 0.0)) return false;
+        if (piv != i) for (int c = 0; c < 8; ++c) std::swap(a[i][c], a[piv][c]);
+        const double s = 1.0 / a[i][i];
+        for (int c = 0; c < 8; ++c) a[i][c] *= s;
+        for (int r = 0; r < 4; ++r) if (r != i) { const double f = a[r][i]; for (int c = 0; c < 8; ++c) a[r][c] -= f * a[i][c]; }
+    }
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) inv[r][c] = a[r][4 + c];
+    return true;
+}
+
+// Two-level structure ("build.two_level" = 1; the shape of the reference's own build, geometry.cpp:36-53: a GAS per mesh, an IAS over
+// the instances): ONE bottom-level tree per unique mesh in object space + a top-level tree over the instances' world boxes, laid out in
+// one node array (top level first, root = node 0) and one record array (instance records, then every mesh's triangles). Memory and
+// build time follow the UNIQUE triangles, not the instanced ones. Traversal: vb_traverse_tl (vb_trace.cuh); results are bit for bit
+// those of the flattened structure.
+static int accel_build_two_level(vb_ctx *ctx, vb_build_stats *out) {
+    cudaStream_t st = ctx->stream;
+    const uint32_t n_inst = (uint32_t)ctx->instances.size();
+    if (n_inst == 0) return ctx->fail(VB_ERR_STATE, "vb_accel_build: no instances set");
+    cudaEvent_t e0 = ctx->get_event(), e1 = ctx->get_event();
+    VB_CUDA(cudaEventRecord(e0, st));
+    // ---- world box of every instance (exact: over its transformed triangles), scene box ----
+    std::vector<InstGeom> hg(n_inst);
+    std::vector<uint32_t> off(n_inst + 1, 0);
+    uint64_t total = 0;
+    for (uint32_t i = 0; i < n_inst; ++i) {
+        const vb_device_mesh &m = ctx->meshes[ctx->instances[i].mesh_id];
+        hg[i].pos = m.pos; hg[i].tri = m.tri; hg[i].soup = m.soup ? 1u : 0u; hg[i].pad = 0;
+        memcpy(hg[i].o2w, ctx->instances[i].o2w, 64);
+        off[i] = (uint32_t)total; total += m.nt;
+    }
+    if (total == 0) return ctx->fail(VB_ERR_STATE, "vb_accel_build: scene has no triangles");
+    if (total > 0xffffffffull) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_accel_build: more than 4G instanced triangles");
+    off[n_inst] = (uint32_t)total;
+    DevBuf<InstGeom> d_geom; DevBuf<uint32_t> d_off, d_boxes, d_roots;
+    VB_CUDA(d_geom.alloc(n_inst)); VB_CUDA(d_off.alloc(n_inst + 1)); VB_CUDA(d_boxes.alloc(6 * (size_t)n_inst)); VB_CUDA(d_roots.alloc(n_inst));
+    std::vector<uint32_t> hb(6 * (size_t)n_inst);
+    for (uint32_t i = 0; i < n_inst; ++i) for (int k = 0; k < 6; ++k) hb[6 * (size_t)i + k] = k < 3 ? 0xffffffffu : 0u;
+    VB_CUDA(cudaMemcpyAsync(d_geom.p, hg.data(), sizeof(InstGeom) * n_inst, cudaMemcpyHostToDevice, st));
+    VB_CUDA(cudaMemcpyAsync(d_off.p, off.data(), sizeof(uint32_t) * (n_inst + 1), cudaMemcpyHostToDevice, st));
+    VB_CUDA(cudaMemcpyAsync(d_boxes.p, hb.data(), sizeof(uint32_t) * hb.size(), cudaMemcpyHostToDevice, st));
+    k_inst_bounds<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_geom.p, d_off.p, n_inst, (uint32_t)total, d_boxes.p);
+    VB_CHECK_LAUNCH();
+    VB_CUDA(cudaMemcpyAsync(hb.data(), d_boxes.p, sizeof(uint32_t) * hb.size(), cudaMemcpyDeviceToHost, st));
+    VB_CUDA(cudaStreamSynchronize(st));
+    double wlo[3] = {1e300, 1e300, 1e300}, whi[3] = {-1e300, -1e300, -1e300};
+    for (uint32_t i = 0; i < n_inst; ++i) {
+        if (ctx->meshes[ctx->instances[i].mesh_id].nt == 0) return ctx->fail(VB_ERR_UNSUPPORTED, "vb_accel_build (two-level): an instance of an empty mesh");
+        for (int k = 0; k < 3; ++k) { wlo[k] = std::min(wlo[k], (double)ord2f(hb[6 * (size_t)i + k])); whi[k] = std::max(whi[k], (double)ord2f(hb[6 * (size_t)i + 3 + k])); }
+    }
+    double wdiag = 0, wmag = 0;
+    for (int k = 0; k < 3; ++k) { wdiag += (whi[k] - wlo[k]) * (whi[k] - wlo[k]); wmag = std::max(wmag, std::max(std::fabs(wlo[k]), std::fabs(whi[k]))); }
+    wdiag = std::sqrt(wdiag);
+    // ---- transforms: rows of o2w and of w2o per instance; per mesh the padding that covers the rounding of a ray moved into its space:
+    // |error of w2o * o| <= ~2^-21 * rowsum(|w2o|) * (|o| + |translation|); 2^-19 * rowsum * (|world| + diag) leaves a factor of four
+    std::vector<float> hxf(24 * (size_t)n_inst);
+    std::map<uint32_t, float> mesh_pad;
+    for (uint32_t i = 0; i < n_inst; ++i) {
+        const float *m = ctx->instances[i].o2w;
+        double inv[4][4];
+        if (!invert_affine(m, inv)) return ctx->fail(VB_ERR_INVALID, "vb_accel_build (two-level): singular instance transform");
+        float *x = hxf.data() + 24 * (size_t)i;
+        for (int r = 0; r < 3; ++r) { x[4 * r + 0] = m[r]; x[4 * r + 1] = m[4 + r]; x[4 * r + 2] = m[8 + r]; x[4 * r + 3] = m[12 + r]; }
+        double rowsum = 0;
+        for (int r = 0; r < 3; ++r) {
+            for (int c = 0; c < 4; ++c) x[12 + 4 * r + c] = (float)inv[r][c];
+            rowsum = std::max(rowsum, std::fabs(inv[r][0]) + std::fabs(inv[r][1]) + std::fabs(inv[r][2]));
+        }
+        float pad = (float)(0x1p-19 * rowsum * (wmag + wdiag));
+        float &mp = mesh_pad[ctx->instances[i].mesh_id];
+        mp = std::max(mp, pad);
+    }
+    // ---- one bottom-level tree per unique mesh ----
+    struct Blas { uint4 *nodes; float4 *tris; uint64_t n_nodes, n_tris; int levels; };
+    std::map<uint32_t, Blas> blas;
+    auto release = [&]() { for (auto &kv : blas) { cudaFree(kv.second.nodes); cudaFree(kv.second.tris); } };
+    uint64_t sum_nodes = 0, sum_tris = 0; int max_levels = 0;
+    for (auto &kv : mesh_pad) {
+        BuildInput in; in.mode = BuildInput::MESH; in.mesh_id = kv.first; in.extra_pad = kv.second;
+        int rc = accel_build_tree(ctx, in, "a mesh's bottom-level tree");
+        if (rc) { release(); return rc; }
+        Blas b{ctx->accel.nodes, ctx->accel.tris, ctx->accel.n_nodes, ctx->accel.n_tris, ctx->last_build_levels};
+        ctx->accel = vb_accel();                                   // ownership moved
+        blas[kv.first] = b;
+        sum_nodes += b.n_nodes; sum_tris += b.n_tris; max_levels = std::max(max_levels, b.levels);
+    }
+    // ---- top-level tree over the instance boxes; an instance's record carries the ABSOLUTE root node of its mesh's tree ----
+    // (absolute positions are known once the top level's node count is: build it with relative roots, patch afterwards)
+    std::vector<uint32_t> rel_root(n_inst);
+    {
+        std::map<uint32_t, uint64_t> node_off; uint64_t o = 0;
+        for (auto &kv : blas) { node_off[kv.first] = o; o += kv.second.n_nodes; }
+        for (uint32_t i = 0; i < n_inst; ++i) rel_root[i] = (uint32_t)node_off[ctx->instances[i].mesh_id];
+    }
+    VB_CUDA(cudaMemcpyAsync(d_roots.p, rel_root.data(), sizeof(uint32_t) * n_inst, cudaMemcpyHostToDevice, st));
+    BuildInput tin; tin.mode = BuildInput::TOP; tin.inst_boxes = d_boxes.p; tin.inst_roots = d_roots.p;
+    int rc = accel_build_tree(ctx, tin, "the top-level tree");
+    if (rc) { release(); return rc; }
+    const uint64_t top_nodes = ctx->accel.n_nodes, top_recs = ctx->accel.n_tris;
+    const int top_levels = ctx->last_build_levels;
+    if (top_levels + max_levels + 3 > VB_TRAVERSAL_STACK_ENTRIES) { release(); return ctx->fail(VB_ERR_UNSUPPORTED, "vb_accel_build (two-level): top + bottom levels exceed the traversal stack"); }
+    if (top_nodes + sum_nodes > 0xffffffffull || top_recs + sum_tris > 0xffffffffull) { release(); return ctx->fail(VB_ERR_UNSUPPORTED, "vb_accel_build (two-level): more than 4G nodes or records"); }
+    // ---- merge: [top nodes][mesh trees ...], [instance records][mesh triangles ...]; indices made absolute ----
+    uint4 *nodes = nullptr; float4 *tris = nullptr; float4 *xf = nullptr;
+    VB_CUDA(cudaMalloc(&nodes, (top_nodes + sum_nodes) * sizeof(vb_wide_node)));
+    VB_CUDA(cudaMalloc(&tris, (top_recs + sum_tris) * 48));
+    VB_CUDA(cudaMalloc(&xf, hxf.size() * sizeof(float)));
+    VB_CUDA(cudaMemcpyAsync(nodes, ctx->accel.nodes, top_nodes * sizeof(vb_wide_node), cudaMemcpyDeviceToDevice, st));
+    VB_CUDA(cudaMemcpyAsync(tris, ctx->accel.tris, top_recs * 48, cudaMemcpyDeviceToDevice, st));
+    VB_CUDA(cudaMemcpyAsync(xf, hxf.data(), hxf.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+    {   // instance records: relative root -> absolute (the records are float4 triples; .x of the first holds the root's bits)
+        std::vector<float> rec(top_recs * 12);
+        VB_CUDA(cudaMemcpyAsync(rec.data(), ctx->accel.tris, top_recs * 48, cudaMemcpyDeviceToHost, st));
+        VB_CUDA(cudaStreamSynchronize(st));
+        for (uint64_t k = 0; k < top_recs; ++k) { uint32_t r; memcpy(&r, &rec[12 * k], 4); r += (uint32_t)top_nodes; memcpy(&rec[12 * k], &r, 4); }
+        VB_CUDA(cudaMemcpyAsync(tris, rec.data(), top_recs * 48, cudaMemcpyHostToDevice, st));
+        VB_CUDA(cudaStreamSynchronize(st));
+    }
+    uint64_t no = top_nodes, to = top_recs;
+    for (auto &kv : blas) {
+        Blas &b = kv.second;
+        VB_CUDA(cudaMemcpyAsync(nodes + no * VB_NODE_U4, b.nodes, b.n_nodes * sizeof(vb_wide_node), cudaMemcpyDeviceToDevice, st));
+        VB_CUDA(cudaMemcpyAsync(tris + to * 3, b.tris, b.n_tris * 48, cudaMemcpyDeviceToDevice, st));
+        k_offset_nodes<<<(unsigned)((b.n_nodes + 255) / 256), 256, 0, st>>>((vb_wide_node *)(nodes + no * VB_NODE_U4), (uint32_t)b.n_nodes, (uint32_t)no, (uint32_t)to);
+        no += b.n_nodes; to += b.n_tris;
+    }
+    VB_CHECK_LAUNCH();
+    VB_CUDA(cudaEventRecord(e1, st));
+    VB_CUDA(cudaStreamSynchronize(st));
+    release();
+    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
+    ctx->accel = vb_accel();
+    ctx->accel.nodes = nodes; ctx->accel.tris = tris; ctx->accel.xf = xf;
+    ctx->accel.n_nodes = top_nodes + sum_nodes; ctx->accel.n_tris = top_recs + sum_tris; ctx->accel.built = true;
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    ctx->ev_pool.push_back(e0); ctx->ev_pool.push_back(e1);
+    vb_build_stats &s = ctx->build_stats;
+    s.n_triangles = sum_tris; s.n_references = sum_tris; s.n_nodes = ctx->accel.n_nodes;
+    s.node_bytes = ctx->accel.n_nodes * sizeof(vb_wide_node); s.tri_bytes = ctx->accel.n_tris * 48 + hxf.size() * sizeof(float);
+    s.build_ms = ms;
+    for (int a = 0; a < 3; ++a) { s.scene_lo[a] = (float)wlo[a]; s.scene_hi[a] = (float)whi[a]; ctx->sort_lo[a] = (float)wlo[a]; ctx->sort_hi[a] = (float)whi[a]; }
+    if (out) *out = s;
+    return VB_OK;
+}
+
 int vb_accel_build_impl(vb_ctx *ctx, vb_build_stats *out) {
+    if (ctx->opt_two_level) return accel_build_two_level(ctx, out);
     bool too_deep = false;
     int rc = accel_build_once(ctx, out, true, &too_deep);
     if (rc || !too_deep) return rc;

@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(256) k_ploc_leaves(uint32_t T, BuildBufs b, ui
     float3 slo = make_float3(ord2f(b.scene[0]), ord2f(b.scene[1]), ord2f(b.scene[2]));
     float3 shi = make_float3(ord2f(b.scene[3]), ord2f(b.scene[4]), ord2f(b.scene[5]));
     float dx = shi.x - slo.x, dy = shi.y - slo.y, dz = shi.z - slo.z;
-    float pad = sqrtf(dx * dx + dy * dy + dz * dz) * 0x1p-20f + 1e-30f;
+    float pad = sqrtf(dx * dx + dy * dy + dz * dz) * 0x1p-20f + 1e-30f + b.extra_pad;
     uint32_t src = b.vals[g];
     float4 lo = b.blo[src], hi = b.bhi[src];
     lo.x -= pad; lo.y -= pad; lo.z -= pad; hi.x += pad; hi.y += pad; hi.z += pad;

@@ -97,7 +97,7 @@ int vb_ctx_destroy(vb_ctx *ctx) {
         cudaFree(m.nrm); cudaFree(m.uv); cudaFree(m.tri);
     }
     cudaFree(ctx->d_instances);
-    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
+    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris); cudaFree(ctx->accel.xf);
     cudaFree(ctx->stage); cudaFree(ctx->sort_buf);
     for (int k = 0; k < 2; ++k) { cudaFree(ctx->rec_stage[k]); if (ctx->rec_done[k]) cudaEventDestroy(ctx->rec_done[k]); if (ctx->rec_traced[k]) cudaEventDestroy(ctx->rec_traced[k]); }
     vb_pt_destroy(ctx);
@@ -136,6 +136,7 @@ int vb_ctx_set_option(vb_ctx *ctx, const char *key, double value) {
     else if (k == "build.max_leaf") { if ((int)value != 1) return ctx->fail(VB_ERR_INVALID, "vb_ctx_set_option: build.max_leaf is fixed at 1 (one triangle per leaf slot)"); }
     else if (k == "build.ploc") ctx->opt_ploc = value < 0 ? -1 : (value != 0 ? 1 : 0);
     else if (k == "build.max_levels") ctx->opt_max_levels = std::min(VB_TRAVERSAL_STACK_ENTRIES, std::max(1, (int)value));   // test hook: lower the depth the build accepts
+    else if (k == "build.two_level") ctx->opt_two_level = value != 0 ? 1 : 0;
     else if (k == "build.collapse") ctx->opt_collapse = value != 0 ? 1 : 0;
     else if (k == "build.split_pct") ctx->opt_split_pct = std::min(400, std::max(0, (int)value));
     else if (k == "build.size_classes") ctx->opt_size_classes = value != 0 ? 1 : 0;
@@ -290,7 +291,7 @@ int vb_meshes_clear(vb_ctx *ctx) {
     ctx->meshes.clear();
     ctx->instances.clear();
     cudaFree(ctx->d_instances); ctx->d_instances = nullptr;
-    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
+    cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris); cudaFree(ctx->accel.xf);
     ctx->accel = vb_accel();
     ctx->geom_version++;
     return VB_OK;

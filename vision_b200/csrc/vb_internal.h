@@ -54,6 +54,8 @@ struct vb_prof_slot { double ms = 0; uint64_t launches = 0; };
 struct vb_accel {
     uint4 *nodes = nullptr;    // n_nodes * VB_NODE_U4 uint4
     float4 *tris = nullptr;    // n_tris * 3 float4: (v0,prim) (e1,inst) (e2,0)
+    float4 *xf = nullptr;      // two-level structure only: 6 float4 per instance (rows of o2w, rows of w2o); then `nodes` = top level + all
+                               // bottom-level trees, `tris` = instance records + object-space triangles (p0,prim) (p1) (p2) (vb_trace.cuh)
     uint64_t n_nodes = 0, n_tris = 0;
     bool built = false;
 };
@@ -84,6 +86,8 @@ struct vb_ctx {
     int opt_ploc = -1;                       // build: 1 = PLOC clustering (vb_bvh_ploc.cuh), 0 = radix tree, -1 = automatic
     bool last_build_ploc = false;
     int opt_max_levels = VB_TRAVERSAL_STACK_ENTRIES;    // build: deepest wide tree accepted (never more than the traversal stack holds)
+    int last_build_levels = 0;               // wide levels of the last tree built
+    int opt_two_level = 0;                   // build: 1 = one bottom-level tree per unique mesh + a top-level tree over the instances
     int opt_collapse = 1;                    // build: 1 = cost-optimal collapse (dynamic programme over the binary tree), 0 = greedy largest-area opening
     int opt_split_pct = 0;                   // build: triangle pre-splitting budget, extra references in percent of the triangle count (vb_bvh_split.cuh)
     int opt_size_classes = 1;                // build: triangle size class as the top bits of the Morton sort key

@@ -727,7 +727,7 @@ static int pt_launch(vb_ctx *ctx, const char *fn, uint32_t first, uint32_t n_fra
     int rc = pt_sync_geometry(ctx);
     if (rc) return rc;
     PtScene S{};
-    S.accel = VbAccelView{ctx->accel.nodes, ctx->accel.tris};
+    S.accel = VbAccelView{ctx->accel.nodes, ctx->accel.tris, ctx->accel.xf};
     S.meshes = p->d_meshes; S.instances = p->d_inst; S.materials = p->d_mat; S.lights = p->d_lights; S.n_lights = p->n_lights; S.env_light = p->env_light;
     S.lsel_offset = p->lsel_offset; S.lsel_size = p->lsel_size; S.lsel_integral = p->lsel_integral;
     S.env_separate = (p->env_separate && p->env_light != VB_INVALID_ID) ? 1u : 0u; S.env_prob = p->env_prob;

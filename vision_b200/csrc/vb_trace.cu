@@ -175,6 +175,46 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
 }
 
 
+// Two-level structure ("build.two_level"): same arguments as k_trace, one ray per thread, grid-stride, vb_traverse_tl over this thread's
+// column of the shared stack. A kernel of its own so that the persistent flattened kernel above keeps its registers.
+template <bool ANY, bool COUNT>
+__global__ void __launch_bounds__(TRACE_BLOCK, 4) k_trace_tl(VbAccelView A, RaysDev R, uint64_t n, HitsDev H, uint8_t *occ,
+                                                          unsigned long long *counters, unsigned long long *next_ray,
+                                                          int REFILL_THR, int TRI_THR,
+                                                          const float4 *__restrict__ RS, const uint32_t *__restrict__ perm, int perm_stride,
+                                                          uint4 *H4) {
+    __shared__ uint2 s_stack_all[VB_SM_STACK * TRACE_BLOCK];
+    const VbTrav V = vb_trav_init();
+    const unsigned lane = threadIdx.x & 31u;
+    uint32_t nn = 0, nt = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += (uint64_t)gridDim.x * TRACE_BLOCK) {
+        uint64_t ri = i;
+        VbRay r;
+        if (RS) {
+            if (perm) ri = __ldg(perm + i * perm_stride);
+            float4 a = __ldg(RS + 2 * ri), b = __ldg(RS + 2 * ri + 1);
+            r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
+        } else {
+            r.ox = __ldg(R.ox + ri); r.oy = __ldg(R.oy + ri); r.oz = __ldg(R.oz + ri); r.tmin = __ldg(R.tmin + ri);
+            r.dx = __ldg(R.dx + ri); r.dy = __ldg(R.dy + ri); r.dz = __ldg(R.dz + ri); r.tmax = __ldg(R.tmax + ri);
+        }
+        VbHit h;
+        bool found = vb_traverse_tl<ANY, COUNT>(A, r, h, s_stack_all + threadIdx.x, TRACE_BLOCK, nn, nt, V);
+        if (ANY) occ[ri] = found ? 1 : 0;
+        else if (H4) H4[ri] = make_uint4(h.inst, h.prim, __float_as_uint(h.u), __float_as_uint(h.v));
+        else { H.inst[ri] = h.inst; H.prim[ri] = h.prim; H.u[ri] = h.u; H.v[ri] = h.v; H.t[ri] = h.t; }
+    }
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(~0u, nn, o); nt += __shfl_xor_sync(~0u, nt, o); }
+        if (lane == 0) { atomicAdd(&counters[0], nn); atomicAdd(&counters[1], nt); }
+    }
+}
+template <bool ANY, bool COUNT, class... Args>
+static void launch_trace(unsigned grid, cudaStream_t st, const VbAccelView &A, Args... args) {
+    if (A.xf) k_trace_tl<ANY, COUNT><<<grid, TRACE_BLOCK, 0, st>>>(A, args...);
+    else k_trace<ANY, COUNT><<<grid, TRACE_BLOCK, 0, st>>>(A, args...);
+}
+
 // ---- ray sorting: 24-bit Morton code of the origin (scene-normalised) + 3-bit direction octant ----
 // Incoherent rays become spatially coherent batches: consecutive rays walk the same subtrees, so
 // node/triangle fetches hit in L1/L2 instead of going to HBM as random 80/48-byte gathers.
@@ -246,7 +286,7 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
         VB_CUDA(cudaStreamWaitEvent(s_out, ctx->ev_in[0], 0));
     }
 
-    VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
+    VbAccelView A{ctx->accel.nodes, ctx->accel.tris, ctx->accel.xf};
     uint64_t launches = 0;
     ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
     for (int c = 0; c < C; ++c) {
@@ -299,11 +339,11 @@ int run_trace(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_so
             launches += 5;
         }
         if (any) {
-            if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
-            else k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+            if (count) launch_trace<true, true>(grid, st, A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+            else launch_trace<true, false>(grid, st, A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
         } else {
-            if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
-            else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+            if (count) launch_trace<false, true>(grid, st, A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+            else launch_trace<false, false>(grid, st, A, Rc, m, Hc, occ_c, d_cnt, d_next, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
         }
         if (out_host) {
             if (C > 1) { VB_CUDA(cudaEventRecord(ctx->ev_out[c], st)); VB_CUDA(cudaStreamWaitEvent(s_out, ctx->ev_out[c], 0)); }
@@ -410,7 +450,7 @@ int run_trace_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits,
     unsigned long long *d_next0 = d_cnt + 4 + (size_t)set * VB_MAX_HOST_CHUNKS;
     VB_CUDA(cudaMemsetAsync(d_next0, 0, 8 * (size_t)VB_MAX_HOST_CHUNKS, st));
 
-    VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
+    VbAccelView A{ctx->accel.nodes, ctx->accel.tris, ctx->accel.xf};
     uint64_t launches = 0;
     ctx->prof_begin(any ? "trace_any" : "trace_closest", 1);
     for (int c = 0; c < C; ++c) {
@@ -455,8 +495,8 @@ int run_trace_records(vb_ctx *ctx, const vb_ray *rays, uint64_t n, vb_hit *hits,
         RaysDev R0{};
         HitsDev H0{};
         // perm == nullptr with RS set: k_trace reads ray i of the AoS array directly
-        if (any) k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R0, m, H0, d_occ + r0, d_cnt, d_next0 + c, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
-        else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R0, m, H0, nullptr, d_cnt, d_next0 + c, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, d_hits + r0);
+        if (any) launch_trace<true, false>(grid, st, A, R0, m, H0, d_occ + r0, d_cnt, d_next0 + c, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+        else launch_trace<false, false>(grid, st, A, R0, m, H0, nullptr, d_cnt, d_next0 + c, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, d_hits + r0);
         if (host) {
             VB_CUDA(cudaEventRecord(ctx->ev_out[c], st));
             VB_CUDA(cudaStreamWaitEvent(s_out, ctx->ev_out[c], 0));
@@ -510,15 +550,15 @@ int vb_trace_queue(vb_ctx *ctx, const float4 *rays, uint64_t *keyidx, uint64_t *
         perm = (const uint32_t *)dk.Current();
         launches += 4;
     }
-    VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
+    VbAccelView A{ctx->accel.nodes, ctx->accel.tris, ctx->accel.xf};
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctx->opt_blocks_per_sm, ((uint64_t)n + TRACE_BLOCK - 1) / TRACE_BLOCK);
     RaysDev R{};
     HitsDev H{};
     // work != null: instrumented run, [nodes popped, triangles tested] are ADDED to work[0..1] (never timed)
-    if (work && any) k_trace<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, occ, work, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, nullptr);
-    else if (work) k_trace<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, nullptr, work, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, hits4);
-    else if (any) k_trace<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, occ, d_cnt, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, nullptr);
-    else k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, nullptr, d_cnt, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, hits4);
+    if (work && any) launch_trace<true, true>(grid, st, A, R, n, H, occ, work, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, nullptr);
+    else if (work) launch_trace<false, true>(grid, st, A, R, n, H, nullptr, work, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, hits4);
+    else if (any) launch_trace<true, false>(grid, st, A, R, n, H, occ, d_cnt, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, nullptr);
+    else launch_trace<false, false>(grid, st, A, R, n, H, nullptr, d_cnt, d_cnt + 2, ctx->opt_refill_thr, ctx->opt_tri_thr, rays, perm, 2, hits4);
     ctx->cur_launches = launches;
     ctx->prof_end();
     VB_CHECK_LAUNCH();
@@ -596,7 +636,7 @@ int vb_trace_closest_static(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, co
     VB_CUDA(cudaMemsetAsync(d_cnt, 0, STATIC_CNT_BYTES, st));          // the array keeps the last call's contents: the ray counter must start at 0
     RaysDev R{rays->ox, rays->oy, rays->oz, rays->tmin, rays->dx, rays->dy, rays->dz, rays->tmax};
     HitsDev H{out->inst, out->prim, out->u, out->v, out->t};
-    VbAccelView A{ctx->accel.nodes, ctx->accel.tris};
+    VbAccelView A{ctx->accel.nodes, ctx->accel.tris, ctx->accel.xf};
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * ctx->opt_blocks_per_sm, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
     const float4 *RS = nullptr; const uint32_t *perm = nullptr;
     if (ctx->opt_sort_rays && n >= (uint64_t)ctx->opt_sort_min_rays) {      // same in-call ray sort as run_trace, over the static scratch
@@ -618,7 +658,7 @@ int vb_trace_closest_static(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, co
         perm = dv.Current();
         RS = d_aos;
     }
-    k_trace<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, R, n, H, nullptr, d_cnt, d_cnt + 4, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
+    launch_trace<false, false>(grid, st, A, R, n, H, nullptr, d_cnt, d_cnt + 4, ctx->opt_refill_thr, ctx->opt_tri_thr, RS, perm, 1, nullptr);
     VB_CHECK_LAUNCH();
     return VB_OK;
 }

@@ -23,6 +23,9 @@ struct VbHit { uint32_t inst, prim; float u, v, t; };
 struct VbAccelView {
     const uint4 *__restrict__ nodes;
     const float4 *__restrict__ tris;
+    // two-level structure ("build.two_level"): per instance 6 float4 - rows 0..2 of object-to-world (x y z | translation), rows 0..2 of
+    // world-to-object; nullptr = the flattened single-level structure (default)
+    const float4 *__restrict__ xf;
 };
 
 // Normative triangle test (DESIGN.md "Intersection contract"); mirrors oracle
@@ -194,10 +197,15 @@ __device__ __forceinline__ void vb_commit_hit(VbHit &hit, float &tmax, float4 a,
     if (better) { hit.inst = inst; hit.prim = prim; hit.u = u; hit.v = v; hit.t = t; tmax = t; }
 }
 
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool vb_traverse_tl(const VbAccelView &A, const VbRay rw, VbHit &hit, uint2 *s_stack, int stride,
+                                            uint32_t &n_nodes, uint32_t &n_tris, const VbTrav V);
+
 // s_stack points at this thread's column of the shared stack: entry e lives at s_stack[e * stride]
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool vb_traverse(const VbAccelView &A, VbRay r, VbHit &hit, uint2 *s_stack, int stride,
                                             uint32_t &n_nodes, uint32_t &n_tris, const VbTrav V) {
+    if (A.xf) return vb_traverse_tl<ANY, COUNT>(A, r, hit, s_stack, stride, n_nodes, n_tris, V);      // two-level structure (uniform branch)
     uint2 l_stack[VB_LOCAL_STACK];
     int sp = 0;
     float idx = vb_safe_rcp(r.dx), idy = vb_safe_rcp(r.dy), idz = vb_safe_rcp(r.dz);
@@ -244,6 +252,114 @@ __device__ __forceinline__ bool vb_traverse(const VbAccelView &A, VbRay r, VbHit
         }
     }
     return hit.inst != 0xffffffffu;
+}
+
+// ---- two-level traversal (option "build.two_level"; reference geometry.cpp:36-53: one GAS per instance + IAS) ------------------------
+// The top level is a wide BVH over the instances' WORLD boxes; a leaf slot of it is one instance (record: (bits of the root node of its
+// mesh's bottom-level tree, instance id)). A bottom-level tree is built once per unique mesh in OBJECT space; its leaf records hold the
+// three object-space vertices (p0, prim) (p1) (p2). Inside an instance the boxes are tested against the ray moved into object space
+// (same parameter t: the transform is affine and the direction is not re-normalised), but every TRIANGLE is tested in WORLD space: its
+// vertices go through the normative object-to-world chain (the one k_flatten uses), so v0, e1, e2 - and with them t, u, v and the winner
+// of every tie - are bit for bit those of the flattened structure. The bottom-level boxes carry an extra padding that covers the
+// rounding of the ray's transform (vb_bvh_collapse.cuh). Stack entries: node groups as in vb_traverse; a LEAF group (pending instances of
+// a top-level node: top byte 0, bits 8..15 set); the SENTINEL (x = 0xffffffff) that marks the way back out of an instance.
+#define VB_TL_SENTINEL 0xffffffffu
+__device__ __forceinline__ float3 vb_xf_point(float4 r0, float4 r1, float4 r2, float x, float y, float z) {     // == xform_point of the build
+    return make_float3(__fmaf_rn(r0.z, z, __fmaf_rn(r0.y, y, __fmaf_rn(r0.x, x, r0.w))),
+                       __fmaf_rn(r1.z, z, __fmaf_rn(r1.y, y, __fmaf_rn(r1.x, x, r1.w))),
+                       __fmaf_rn(r2.z, z, __fmaf_rn(r2.y, y, __fmaf_rn(r2.x, x, r2.w))));
+}
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool vb_traverse_tl(const VbAccelView &A, const VbRay rw, VbHit &hit, uint2 *s_stack, int stride,
+                                            uint32_t &n_nodes, uint32_t &n_tris, const VbTrav V) {
+    uint2 l_stack[VB_LOCAL_STACK];
+    int sp = 0;
+    auto push = [&](uint2 e) {
+        if (sp < VB_SM_STACK) s_stack[sp * stride] = e;
+        else if (sp < VB_SM_STACK + VB_LOCAL_STACK) l_stack[sp - VB_SM_STACK] = e;
+        sp++;
+    };
+    auto pop = [&]() -> uint2 {
+        sp--;
+        if (sp < VB_SM_STACK) return s_stack[sp * stride];
+        if (sp < VB_SM_STACK + VB_LOCAL_STACK) return l_stack[sp - VB_SM_STACK];
+        return make_uint2(0u, 0u);
+    };
+    hit.inst = 0xffffffffu; hit.prim = 0xffffffffu; hit.u = 0.f; hit.v = 0.f; hit.t = 0.f;
+    if (!(rw.tmin < rw.tmax)) return false;
+    float tmax = rw.tmax;
+    VbRay r = rw;                                   // the ray of the current space (world, or the object space of cur_inst)
+    float idx, idy, idz; uint32_t oct_inv, lut_o;
+    auto set_space = [&]() {
+        idx = vb_safe_rcp(r.dx); idy = vb_safe_rcp(r.dy); idz = vb_safe_rcp(r.dz);
+        uint32_t oct = (r.dx < 0.f ? 4u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 1u : 0u);
+        oct_inv = 7u - oct; lut_o = V.lut + (oct_inv << 8);
+    };
+    set_space();
+    uint32_t cur_inst = 0xffffffffu;
+    uint2 G = make_uint2(0u, 0x80000000u);          // root group of the top level
+    uint2 Tg = make_uint2(0u, 0u);
+    for (;;) {
+        if (G.y & 0xff000000u) {                    // a node group with un-visited children: visit the nearest
+            uint32_t hits_imask = G.y;
+            uint32_t bit = 31u - __clz(hits_imask);
+            G.y &= ~(1u << bit);
+            if (G.y & 0xff000000u) push(G);
+            uint32_t slot = (bit - 24u) ^ oct_inv;
+            uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot) & 0xffu);
+            if (COUNT) n_nodes++;
+            vb_node_step(A.nodes, G.x + rel, r, idx, idy, idz, tmax, V.mg, lut_o, G, Tg);
+        }
+        while (Tg.y > 0xffu) {
+            const uint32_t rec = vb_next_triangle(Tg);
+            const float4 *tp = A.tris + (size_t)rec * 3;
+            if (cur_inst == 0xffffffffu) {          // top level: the leaf is an instance - enter it
+                const float4 a = __ldg(tp);
+                if (G.y & 0xff000000u) push(G);
+                if (Tg.y > 0xffu) push(Tg);
+                push(make_uint2(VB_TL_SENTINEL, 0u));
+                cur_inst = __float_as_uint(a.y);
+                const float4 *xf = A.xf + (size_t)cur_inst * 6;
+                const float4 w0 = __ldg(xf + 3), w1 = __ldg(xf + 4), w2 = __ldg(xf + 5);
+                float3 o = vb_xf_point(w0, w1, w2, rw.ox, rw.oy, rw.oz);
+                r.ox = o.x; r.oy = o.y; r.oz = o.z;
+                r.dx = __fmaf_rn(w0.z, rw.dz, __fmaf_rn(w0.y, rw.dy, __fmul_rn(w0.x, rw.dx)));
+                r.dy = __fmaf_rn(w1.z, rw.dz, __fmaf_rn(w1.y, rw.dy, __fmul_rn(w1.x, rw.dx)));
+                r.dz = __fmaf_rn(w2.z, rw.dz, __fmaf_rn(w2.y, rw.dy, __fmul_rn(w2.x, rw.dx)));
+                set_space();
+                G = make_uint2(__float_as_uint(a.x), 0x80000000u);      // root group of the instance's bottom-level tree
+                Tg = make_uint2(0u, 0u);
+                break;
+            }
+            // bottom level: the triangle, moved to world space by the build's own transform chain, against the WORLD ray
+            const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+            const float4 *xf = A.xf + (size_t)cur_inst * 6;
+            const float4 m0 = __ldg(xf), m1 = __ldg(xf + 1), m2 = __ldg(xf + 2);
+            const float3 p0 = vb_xf_point(m0, m1, m2, q0.x, q0.y, q0.z), p1 = vb_xf_point(m0, m1, m2, q1.x, q1.y, q1.z),
+                         p2 = vb_xf_point(m0, m1, m2, q2.x, q2.y, q2.z);
+            const float4 a = make_float4(p0.x, p0.y, p0.z, q0.w);
+            const float4 b = make_float4(__fsub_rn(p1.x, p0.x), __fsub_rn(p1.y, p0.y), __fsub_rn(p1.z, p0.z), __uint_as_float(cur_inst));
+            const float4 c = make_float4(__fsub_rn(p2.x, p0.x), __fsub_rn(p2.y, p0.y), __fsub_rn(p2.z, p0.z), 0.f);
+            if (COUNT) n_tris++;
+            float t, u, v;
+            if (vb_intersect_triangle(rw, a, b, c, rw.tmax, t, u, v)) {
+                if (ANY) return true;
+                vb_commit_hit(hit, tmax, a, b, t, u, v);
+            }
+        }
+        if (!(G.y & 0xff000000u) && !(Tg.y > 0xffu)) {          // nothing left here: next stack entry
+            for (;;) {
+                if (sp == 0) return hit.inst != 0xffffffffu;
+                uint2 e = pop();
+                if (e.x == VB_TL_SENTINEL && e.y == 0u) {       // back out of the instance
+                    cur_inst = 0xffffffffu; r = rw; set_space();
+                    continue;
+                }
+                if (e.y & 0xff000000u) { G = e; Tg = make_uint2(0u, 0u); break; }
+                if (e.y > 0xffu) { Tg = e; G = make_uint2(0u, 0u); break; }
+            }
+        }
+    }
 }
 
 // ---- ray sort key: 21-bit Morton code of the origin (128^3 cells of the scene box) + 3-bit direction
