@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(256) k_wf_material_keys(PtScene S, uint32_t n,
 // own entries; warps whose entries all belong to the other launch exit at once.
 template <int VARIANT>
 #ifndef VB_SHADE_MIN_BLOCKS
-#define VB_SHADE_MIN_BLOCKS 4
+#define VB_SHADE_MIN_BLOCKS 5      /* 96 registers, 20 warps per SM: the lean kernels are latency-bound (profiles/round2_classroom_shade_trace_ncu_full.txt); 4 -> 5: classroom +1 %, dispersion +5 %; 6: no further gain */
 #endif
 #ifndef VB_SHADE_MIN_BLOCKS_PRINCIPLED
 #define VB_SHADE_MIN_BLOCKS_PRINCIPLED 3      /* the principled instantiations trade resident warps (12 instead of 16 per SM) for 168 registers */
