@@ -138,3 +138,17 @@ def test_classroom_through_the_host_layer(two_level):
         hp.close()
     assert np.array_equal(films[1][0], films[0][0])
     assert films[1][1]["n_triangles"] == films[0][1]["n_triangles"] == 103832       # no mesh is instanced twice in this scene
+
+
+def test_vision_cli_two_level_flag(tmp_path):
+    """vision-cli --two-level writes the same linear film (.pfm) as the default build"""
+    import subprocess
+    cli = str(ROOT / "vision_b200" / "vision-cli")
+    scene = str(ROOT / "scenes" / "cbox" / "cbox_materials.json")
+    outs = []
+    for k, extra in enumerate(([], ["--two-level"])):
+        pfm = tmp_path / f"f{k}.pfm"
+        r = subprocess.run([cli, "-s", scene, "-o", str(tmp_path / f"o{k}.png"), "--pfm", str(pfm), "--spp", "2"] + extra, capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stderr[-500:]
+        outs.append(pfm.read_bytes())
+    assert outs[0] == outs[1] and len(outs[0]) > 256 * 256 * 12

@@ -310,6 +310,7 @@ void Pipeline::init_scene(const SceneDesc &d) { scene.init(d); }
 void Pipeline::prepare(int device) {
     scene.prepare(records);
     if (vb_ctx_create(device, &ctx) != VB_OK) throw std::runtime_error(std::string("vb_ctx_create failed: ") + vb_last_error(nullptr));
+    for (auto &kv : options) check(vb_ctx_set_option(ctx, kv.first.c_str(), kv.second), ("vb_ctx_set_option " + kv.first).c_str());
     std::vector<uint32_t> ids;
     for (auto &m : records.meshes) {
         uint32_t id;

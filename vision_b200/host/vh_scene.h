@@ -104,6 +104,7 @@ public:
     // of every render(n) call into a SUM film; final_picture() first makes the film whole (NCCL all-reduce over `nccl_comm`,
     // one process per GPU) - or render_on_gpus() below does it over peer memory (one process, several GPUs)
     uint32_t dist_rank = 0, dist_world = 1;
+    std::vector<std::pair<std::string, double>> options;      // vb_ctx_set_option pairs applied before the BVH is built (e.g. build.two_level)
     void *nccl_comm = nullptr;
     void set_partition(uint32_t rank, uint32_t world);
     void nccl_init(const void *id128);                // after prepare(): vb_nccl_comm_create on this pipeline's context

@@ -1,6 +1,8 @@
 // vision-cli: headless stand-in for the reference's GUI-only driver (src/apps/vision-gui/main.cpp:10-14,
 // application.cpp:37-49,174-199; CLI flags of src/base/cli_parser.cpp:18-43 that this path uses).
-//   vision-cli -s <scene.json> [-o out.ppm] [--spp N] [-d cuda] [--device-index I] [--pfm out.pfm] [--gpus N [--nccl]]
+//   vision-cli -s <scene.json> [-o out.ppm] [--spp N] [-d cuda] [--device-index I] [--pfm out.pfm] [--gpus N [--nccl]] [--two-level] [--opt key=value]
+// --two-level: one BVH per unique mesh + a top-level BVH over the instances (the reference's GAS / IAS shape) instead of the flattened default;
+// --opt: any vb_ctx_set_option pair, applied before the BVH is built.
 // --gpus N: the spp frame indices are split over N GPUs of this box (rank g renders g, g + N, ...), films reduced + resolved over
 // NVLink peer memory (vb_film_reduce_peers) or, with --nccl, by ncclAllReduce (vb_film_allreduce).
 #include "vh_scene.h"
@@ -11,6 +13,7 @@
 int main(int argc, char **argv) {
     std::string scene, out = "output.ppm", pfm, aov, device = "cuda";
     uint32_t spp = 0, gpus = 1; int dev_index = 0; bool nccl = false;
+    std::vector<std::pair<std::string, double>> options;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
         auto next = [&]() { if (i + 1 >= argc) { fprintf(stderr, "missing value for %s\n", a.c_str()); exit(2); } return std::string(argv[++i]); };
@@ -23,6 +26,8 @@ int main(int argc, char **argv) {
         else if (a == "--device-index") dev_index = std::stoi(next());
         else if (a == "--gpus") gpus = (uint32_t)std::stoul(next());
         else if (a == "--nccl") nccl = true;
+        else if (a == "--two-level") options.emplace_back("build.two_level", 1.0);
+        else if (a == "--opt") { std::string kv = next(); size_t eq = kv.find('='); if (eq == std::string::npos) { fprintf(stderr, "--opt wants key=value\n"); return 2; } options.emplace_back(kv.substr(0, eq), std::stod(kv.substr(eq + 1))); }
         else if (a == "-h" || a == "--help") { printf("vision-cli -s scene.json [-o out.png|.ppm|.hdr|.pfm] [--pfm out.pfm] [--aov prefix] [--spp N] [-d cuda] [--gpus N [--nccl]]\n"); return 0; }
         else fprintf(stderr, "ignored argument %s\n", a.c_str());
     }
@@ -50,6 +55,7 @@ int main(int argc, char **argv) {
         }
         auto t0 = std::chrono::steady_clock::now();
         auto p = vh::import_scene(scene);
+        p->options = options;
         p->prepare(dev_index);
         for (auto &l : p->scene.log) fprintf(stderr, "[vision] %s\n", l.c_str());
         uint32_t n = spp ? spp : p->records.spp;
