@@ -102,7 +102,7 @@ template <int VARIANT>
 #define VB_SHADE_MIN_BLOCKS 5      /* 96 registers, 20 warps per SM: the lean kernels are latency-bound (profiles/round2_classroom_shade_trace_ncu_full.txt); 4 -> 5: classroom +1 %, dispersion +5 %; 6: no further gain */
 #endif
 #ifndef VB_SHADE_MIN_BLOCKS_PRINCIPLED
-#define VB_SHADE_MIN_BLOCKS_PRINCIPLED 3      /* the principled instantiations trade resident warps (12 instead of 16 per SM) for 168 registers */
+#define VB_SHADE_MIN_BLOCKS_PRINCIPLED 4      /* 128 registers, 16 warps per SM (3 x 168 registers until round 2: dispersion +1.6 %, cbox_principled +2.6 %, tools/sweep_shade_occ.sh) */
 #endif
 __global__ void __launch_bounds__(128, (VARIANT & PT_PRINCIPLED) ? VB_SHADE_MIN_BLOCKS_PRINCIPLED : VB_SHADE_MIN_BLOCKS) k_wf_shade(const __grid_constant__ PtScene S, uint32_t n, WfQueue Qin, const uint64_t *__restrict__ order, const uint4 *__restrict__ hits4,
                                                   WfState st, WfQueue Qout, WfQueue Qsh, float4 *sh_pend, WfSortBox B, WfCounters *cnt, int filter) {
