@@ -530,8 +530,11 @@ static int accel_build_two_level(vb_ctx *ctx, vb_build_stats *out) {
     }
     // ---- one bottom-level tree per unique mesh ----
     struct Blas { uint4 *nodes; float4 *tris; uint64_t n_nodes, n_tris; int levels; };
-    std::map<uint32_t, Blas> blas;
-    auto release = [&]() { for (auto &kv : blas) { cudaFree(kv.second.nodes); cudaFree(kv.second.tris); } };
+    struct BlasSet : std::map<uint32_t, Blas> {          // frees whatever is still held on every way out (VB_CUDA returns included)
+        void release() { for (auto &kv : *this) { cudaFree(kv.second.nodes); cudaFree(kv.second.tris); kv.second.nodes = nullptr; kv.second.tris = nullptr; } }
+        ~BlasSet() { release(); }
+    } blas;
+    auto release = [&]() { blas.release(); };
     uint64_t sum_nodes = 0, sum_tris = 0; int max_levels = 0;
     for (auto &kv : mesh_pad) {
         BuildInput in; in.mode = BuildInput::MESH; in.mesh_id = kv.first; in.extra_pad = kv.second;
@@ -559,7 +562,9 @@ static int accel_build_two_level(vb_ctx *ctx, vb_build_stats *out) {
     if (top_levels + max_levels + 3 > VB_TRAVERSAL_STACK_ENTRIES) { release(); return ctx->fail(VB_ERR_UNSUPPORTED, "vb_accel_build (two-level): top + bottom levels exceed the traversal stack"); }
     if (top_nodes + sum_nodes > 0xffffffffull || top_recs + sum_tris > 0xffffffffull) { release(); return ctx->fail(VB_ERR_UNSUPPORTED, "vb_accel_build (two-level): more than 4G nodes or records"); }
     // ---- merge: [top nodes][mesh trees ...], [instance records][mesh triangles ...]; indices made absolute ----
-    uint4 *nodes = nullptr; float4 *tris = nullptr; float4 *xf = nullptr;
+    struct Merged { uint4 *nodes = nullptr; float4 *tris = nullptr; float4 *xf = nullptr; bool keep = false;
+                    ~Merged() { if (!keep) { cudaFree(nodes); cudaFree(tris); cudaFree(xf); } } } mg;
+    uint4 *&nodes = mg.nodes; float4 *&tris = mg.tris; float4 *&xf = mg.xf;
     VB_CUDA(cudaMalloc(&nodes, (top_nodes + sum_nodes) * sizeof(vb_wide_node)));
     VB_CUDA(cudaMalloc(&tris, (top_recs + sum_tris) * 48));
     VB_CUDA(cudaMalloc(&xf, hxf.size() * sizeof(float)));
@@ -588,7 +593,7 @@ static int accel_build_two_level(vb_ctx *ctx, vb_build_stats *out) {
     release();
     cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris);
     ctx->accel = vb_accel();
-    ctx->accel.nodes = nodes; ctx->accel.tris = tris; ctx->accel.xf = xf;
+    ctx->accel.nodes = nodes; ctx->accel.tris = tris; ctx->accel.xf = xf; mg.keep = true;
     ctx->accel.n_nodes = top_nodes + sum_nodes; ctx->accel.n_tris = top_recs + sum_tris; ctx->accel.built = true;
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e0, e1);

@@ -11,8 +11,12 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#ifndef VB_SM_STACK
 #define VB_SM_STACK 12
-#define VB_LOCAL_STACK 52
+#endif
+#ifndef VB_LOCAL_STACK
+#define VB_LOCAL_STACK (64 - VB_SM_STACK)
+#endif
 #ifdef VB_TRAVERSAL_STACK_ENTRIES
 static_assert(VB_SM_STACK + VB_LOCAL_STACK == VB_TRAVERSAL_STACK_ENTRIES, "vb_internal.h states the traversal stack size the build checks against");
 #endif
