@@ -95,7 +95,12 @@ typedef struct vb_build_stats {
     uint64_t n_references;     /* leaves of the BVH: n_triangles plus the extra references of triangle pre-splitting (option
                                 * "build.split_pct"); tri_bytes = 48 * n_references, and vb_accel_download's `tris` holds that many */
 } vb_build_stats;
-/* flattens instances to world space, builds the compressed 8-wide BVH on the GPU */
+/* Builds the compressed 8-wide BVH on the GPU (replaces mesh.build_bvh / accel_.add_instance / accel_.build_bvh,
+ * reference src/base/mgr/geometry.cpp:36-53). Default: every instance flattened to world space, ONE tree. Option "build.two_level" = 1
+ * (vb_ctx_set_option): one bottom-level tree per unique mesh in object space + a top-level tree over the instances - the reference's
+ * GAS / IAS shape; memory and build time follow the unique triangles, hit records are bit-identical to the flattened build's, traversal is
+ * 4-5x slower. Then n_triangles / n_references count the STORED (unique) triangles. Other build options: "build.ploc" (-1 automatic, 0 radix
+ * tree, 1 PLOC), "build.collapse" (1 cost-optimal 8-wide collapse, 0 greedy), "build.size_classes", "build.split_pct". */
 VB_API int vb_accel_build(vb_ctx *ctx, const vb_build_opts *opts, vb_build_stats *out);
 /* copies the built structure to host (test/diagnostic surface): nodes = n_nodes*96 bytes,
  * tris = n_triangles*48 bytes (float4 v0|prim, e1|inst, e2|0). Either pointer may be NULL. */
