@@ -94,7 +94,7 @@ int vb_ctx_destroy(vb_ctx *ctx) {
     for (auto e : ctx->ev_pool) cudaEventDestroy(e);
     for (auto &m : ctx->meshes) {
         if (m.owns_pos) cudaFree(m.pos);
-        cudaFree(m.nrm); cudaFree(m.uv); cudaFree(m.tri);
+        cudaFree(m.nrm); cudaFree(m.uv); cudaFree(m.tri); cudaFree(m.vtx); cudaFree(m.tri4);
     }
     cudaFree(ctx->d_instances);
     cudaFree(ctx->accel.nodes); cudaFree(ctx->accel.tris); cudaFree(ctx->accel.xf);
@@ -212,6 +212,17 @@ int vb_profile_get(vb_ctx *ctx, const char *name, double *ms, uint64_t *launches
     return VB_OK;
 }
 
+// shading-side copies of an indexed mesh: interleaved vertices and padded index triples (same values, fewer and wider loads)
+__global__ void __launch_bounds__(256) k_interleave_mesh(const float *pos, const float *nrm, const float *uv, uint32_t nv, float4 *vtx,
+                                                         const uint32_t *tri, uint32_t nt, uint4 *tri4) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < nv) {
+        vtx[2 * (size_t)g] = make_float4(pos[3 * (size_t)g], pos[3 * (size_t)g + 1], pos[3 * (size_t)g + 2], uv[2 * (size_t)g]);
+        vtx[2 * (size_t)g + 1] = make_float4(nrm[3 * (size_t)g], nrm[3 * (size_t)g + 1], nrm[3 * (size_t)g + 2], uv[2 * (size_t)g + 1]);
+    }
+    if (g < nt) tri4[g] = make_uint4(tri[3 * (size_t)g], tri[3 * (size_t)g + 1], tri[3 * (size_t)g + 2], 0u);
+}
+
 int vb_mesh_upload(vb_ctx *ctx, const float *pos3, const float *nrm3, const float *uv2, uint32_t nv,
                    const uint32_t *tri3, uint32_t nt, uint32_t *mesh_id) {
     if (!ctx) return VB_ERR_INVALID;
@@ -234,6 +245,13 @@ int vb_mesh_upload(vb_ctx *ctx, const float *pos3, const float *nrm3, const floa
     if (nt) {
         VB_CUDA(cudaMalloc(&m.tri, sizeof(uint32_t) * 3 * nt));
         VB_CUDA(cudaMemcpyAsync(m.tri, tri3, sizeof(uint32_t) * 3 * nt, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (nv && nt) {
+        VB_CUDA(cudaMalloc(&m.vtx, sizeof(float4) * 2 * (size_t)nv));
+        VB_CUDA(cudaMalloc(&m.tri4, sizeof(uint4) * (size_t)nt));
+        const uint32_t nmax = nv > nt ? nv : nt;
+        k_interleave_mesh<<<(nmax + 255) / 256, 256, 0, ctx->stream>>>(m.pos, m.nrm, m.uv, nv, m.vtx, m.tri, nt, m.tri4);
+        VB_CHECK_LAUNCH();
     }
     VB_CUDA(cudaStreamSynchronize(ctx->stream));
     *mesh_id = (uint32_t)ctx->meshes.size();
@@ -286,7 +304,7 @@ int vb_meshes_clear(vb_ctx *ctx) {
     VB_CUDA(cudaStreamSynchronize(ctx->stream));
     for (auto &m : ctx->meshes) {
         if (m.owns_pos) cudaFree(m.pos);
-        cudaFree(m.nrm); cudaFree(m.uv); cudaFree(m.tri);
+        cudaFree(m.nrm); cudaFree(m.uv); cudaFree(m.tri); cudaFree(m.vtx); cudaFree(m.tri4);
     }
     ctx->meshes.clear();
     ctx->instances.clear();

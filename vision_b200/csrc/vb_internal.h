@@ -25,6 +25,8 @@ struct vb_device_mesh {
     float *nrm = nullptr;      // 3*nv (may be null)
     float *uv = nullptr;       // 2*nv (may be null)
     uint32_t *tri = nullptr;   // 3*nt (null for soups)
+    float4 *vtx = nullptr;     // indexed meshes: 2 float4 per vertex (pos.xyz, u) (nrm.xyz, v) - one 32-byte sector per vertex for the shading gather
+    uint4 *tri4 = nullptr;     // indexed meshes: (i0, i1, i2, 0) per triangle - one 16-byte load instead of three 4-byte ones
     uint32_t nv = 0;
     uint64_t nt = 0;
     bool soup = false;

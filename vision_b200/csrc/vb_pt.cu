@@ -13,7 +13,7 @@ using namespace vbm;
 
 namespace {
 
-struct DevMesh { const float *pos, *nrm, *uv; const uint32_t *tri; };
+struct DevMesh { const float4 *vtx; const uint4 *tri4; };      // interleaved vertices (pos.xyz, u) (nrm.xyz, v); (i0, i1, i2, 0) per triangle
 struct DevInst {
     uint32_t mesh_id, mat_id, light_id, inside, outside, pad[3];
     float o2w[16];
@@ -88,15 +88,22 @@ __device__ __forceinline__ Interaction compute_surface_interaction(const PtScene
     it.prim_id = prim_id;
     const DevInst &I = S.instances[inst_id];
     const DevMesh M = S.meshes[I.mesh_id];
-    uint32_t i0 = __ldg(M.tri + 3 * prim_id), i1 = __ldg(M.tri + 3 * prim_id + 1), i2 = __ldg(M.tri + 3 * prim_id + 2);
+    const uint4 ti = __ldg(M.tri4 + prim_id);
+    const uint32_t i0 = ti.x, i1 = ti.y, i2 = ti.z;
+    // one 32-byte sector per vertex: (pos.xyz, u) (nrm.xyz, v)
+    uint4 va0, vb0, va1, vb1, va2, vb2;
+    vb_ld256(reinterpret_cast<const uint4 *>(M.vtx) + 2 * (size_t)i0, va0, vb0);
+    vb_ld256(reinterpret_cast<const uint4 *>(M.vtx) + 2 * (size_t)i1, va1, vb1);
+    vb_ld256(reinterpret_cast<const uint4 *>(M.vtx) + 2 * (size_t)i2, va2, vb2);
+    auto xyz = [](const uint4 &q) { return f3{__uint_as_float(q.x), __uint_as_float(q.y), __uint_as_float(q.z)}; };
     it.light_id = I.light_id; it.mat_id = I.mat_id;
     it.inside = I.inside; it.outside = I.outside; it.has_phase = false; it.g = 0.f;
-    f3 p0 = transform_point(I.o2w, ld3(M.pos, i0)), p1 = transform_point(I.o2w, ld3(M.pos, i1)), p2 = transform_point(I.o2w, ld3(M.pos, i2));
+    f3 p0 = transform_point(I.o2w, xyz(va0)), p1 = transform_point(I.o2w, xyz(va1)), p2 = transform_point(I.o2w, xyz(va2));
     it.pos = lerp3(bu, bv, p0, p1, p2);
     f3 dp02 = p0 - p2, dp12 = p1 - p2;
     f3 ng_un = cross(dp02, dp12);
     it.prim_area = 0.5f * length(ng_un);
-    f2 t0 = ld2(M.uv, i0), t1 = ld2(M.uv, i1), t2 = ld2(M.uv, i2);
+    f2 t0{__uint_as_float(va0.w), __uint_as_float(vb0.w)}, t1{__uint_as_float(va1.w), __uint_as_float(vb1.w)}, t2{__uint_as_float(va2.w), __uint_as_float(vb2.w)};
     f2 duv02{t0.x - t2.x, t0.y - t2.y}, duv12{t1.x - t2.x, t1.y - t2.y};
     float det = duv02.x * duv12.y - duv02.y * duv12.x;
     bool degenerate_uv = fabsf(det) < 1e-8f;
@@ -117,7 +124,7 @@ __device__ __forceinline__ Interaction compute_surface_interaction(const PtScene
     }
     it.shading = frame;
     if (is_complete) {
-        f3 normal = lerp3(bu, bv, ld3(M.nrm, i0), ld3(M.nrm, i1), ld3(M.nrm, i2));
+        f3 normal = lerp3(bu, bv, xyz(vb0), xyz(vb1), xyz(vb2));
         if (!is_zero(normal)) {
             f3 ns = normalize(apply_normal(I.nmat, normal));
             it.shading.update(ns);

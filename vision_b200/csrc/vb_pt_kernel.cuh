@@ -405,7 +405,7 @@ static int pt_sync_geometry(vb_ctx *ctx) {
     p->geom_version = ~0ull;
     cudaFree(p->d_meshes); cudaFree(p->d_inst); p->d_meshes = nullptr; p->d_inst = nullptr;
     std::vector<DevMesh> hm(ctx->meshes.size());
-    for (size_t i = 0; i < hm.size(); ++i) hm[i] = DevMesh{ctx->meshes[i].pos, ctx->meshes[i].nrm, ctx->meshes[i].uv, ctx->meshes[i].tri};
+    for (size_t i = 0; i < hm.size(); ++i) hm[i] = DevMesh{ctx->meshes[i].vtx, ctx->meshes[i].tri4};
     std::vector<DevInst> hi(ctx->instances.size());
     for (size_t i = 0; i < hi.size(); ++i) {
         const vb_instance &s = ctx->instances[i];
