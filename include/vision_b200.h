@@ -83,8 +83,9 @@ typedef struct vb_instance {
 } vb_instance;
 VB_API int vb_instances_set(vb_ctx *ctx, const vb_instance *inst, uint32_t n);
 
+#define VB_BUILD_TWO_LEVEL 1u      /* this build only: as if option "build.two_level" were 1 */
 typedef struct vb_build_opts {
-    uint32_t flags;            /* reserved, 0 */
+    uint32_t flags;            /* 0 or VB_BUILD_* bits */
 } vb_build_opts;
 typedef struct vb_build_stats {
     uint64_t n_triangles;      /* flattened world-space triangles */

@@ -99,6 +99,12 @@ def test_soup_as_one_instance_and_device_rays(two_level, oracle):
     f = ctx.trace_closest(d)
     for k in ("inst", "prim", "u", "v", "t"):
         assert torch.equal(g[k], f[k]), k
+    st = ctx.accel_build(two_level=True)                  # the per-build flag (VB_BUILD_TWO_LEVEL) instead of the context option
+    g2 = ctx.trace_closest(d)
+    assert all(torch.equal(g2[k], f[k]) for k in f)
+    bad = capi.vb_build_opts(8)
+    assert ctx.lib.vb_accel_build(ctx.h, __import__("ctypes").byref(bad), None) != 0      # unknown flag: refused
+    ctx.accel_build()
     assert torch.equal(gr[:, 1].cpu(), f["prim"].cpu().view(torch.int32))
 
 

@@ -209,9 +209,10 @@ class Context:
             arr[i].o2w[:] = [float(x) for x in np.asarray(o2w, np.float32).reshape(-1)]
         self._check(self.lib.vb_instances_set(self.h, arr, len(instances)), "vb_instances_set")
 
-    def accel_build(self) -> dict:
+    def accel_build(self, two_level: bool = False) -> dict:
+        """two_level=True: VB_BUILD_TWO_LEVEL for this build (otherwise the context option build.two_level decides)"""
         st = vb_build_stats()
-        opts = vb_build_opts(0)
+        opts = vb_build_opts(1 if two_level else 0)
         self._check(self.lib.vb_accel_build(self.h, C.byref(opts), C.byref(st)), "vb_accel_build")
         return {"n_triangles": st.n_triangles, "n_nodes": st.n_nodes, "node_bytes": st.node_bytes,
                 "tri_bytes": st.tri_bytes, "build_ms": st.build_ms, "n_references": st.n_references,

@@ -315,10 +315,15 @@ int vb_meshes_clear(vb_ctx *ctx) {
     return VB_OK;
 }
 
-int vb_accel_build(vb_ctx *ctx, const vb_build_opts *, vb_build_stats *out) {
+int vb_accel_build(vb_ctx *ctx, const vb_build_opts *opts, vb_build_stats *out) {
     if (!ctx) return VB_ERR_INVALID;
+    if (opts && (opts->flags & ~VB_BUILD_TWO_LEVEL)) return ctx->fail(VB_ERR_INVALID, "vb_accel_build: unknown flag in vb_build_opts");
     cudaSetDevice(ctx->device);
-    return vb_accel_build_impl(ctx, out);
+    const int saved = ctx->opt_two_level;
+    if (opts && (opts->flags & VB_BUILD_TWO_LEVEL)) ctx->opt_two_level = 1;
+    int rc = vb_accel_build_impl(ctx, out);
+    ctx->opt_two_level = saved;
+    return rc;
 }
 
 int vb_accel_download(vb_ctx *ctx, void *nodes, void *tris) {
