@@ -94,13 +94,16 @@ def test_soup_as_one_instance_and_device_rays(two_level, oracle):
     g = ctx.trace_closest(d)
     rec = torch.from_numpy(capi.rays_to_records(rays)).cuda()
     gr = ctx.trace_closest_records(rec)
+    ctx.synchronize()                                      # device-buffer calls are asynchronous on the context's stream
     ctx.set_option("build.two_level", 0)
     ctx.accel_build()
     f = ctx.trace_closest(d)
+    ctx.synchronize()
     for k in ("inst", "prim", "u", "v", "t"):
         assert torch.equal(g[k], f[k]), k
     st = ctx.accel_build(two_level=True)                  # the per-build flag (VB_BUILD_TWO_LEVEL) instead of the context option
     g2 = ctx.trace_closest(d)
+    ctx.synchronize()
     assert all(torch.equal(g2[k], f[k]) for k in f)
     bad = capi.vb_build_opts(8)
     assert ctx.lib.vb_accel_build(ctx.h, __import__("ctypes").byref(bad), None) != 0      # unknown flag: refused

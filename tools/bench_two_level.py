@@ -18,6 +18,7 @@ def measure(ctx, tag):
     for _ in range(3):
         hits = ctx.trace_closest(d, hits); occ = ctx.trace_any(da, occ)
     c, _ = ctx.profile_get("trace_closest"); a, _ = ctx.profile_get("trace_any")
+    ctx.synchronize()
     print(f"  {tag}: closest {n/(c/3)/1e3:.0f} any {n/(a/3)/1e3:.0f} Mrays/s", flush=True)
     return hits
 ctx = Context(0)

@@ -41,6 +41,7 @@ def soup(tris, n=1 << 24):
         c, _ = ctx.profile_get("trace_closest"); a, _ = ctx.profile_get("trace_any")
         _, nn, nt = ctx.trace_closest(d, hits, counted=True)
         _, an, at = ctx.trace_any(da, occ, counted=True)
+        ctx.synchronize()
         sig = (hits["prim"].cpu().numpy().tobytes(), hits["t"].cpu().numpy().tobytes(), occ.cpu().numpy().tobytes())
         if ref is None:
             ref = sig
