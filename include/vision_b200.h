@@ -120,6 +120,9 @@ typedef struct vb_hits_soa {
     float *u, *v, *t;
     vb_mem mem;
 } vb_hits_soa;
+/* Completion: with HOST buffers (input or output) the call returns when the results are in the caller's memory. With DEVICE buffers on
+ * both sides it is stream-ordered on the context's stream (vb_ctx_set_stream) and returns once queued: read the results on that stream,
+ * or after vb_ctx_synchronize - a consumer on another stream races with the traversal kernel. */
 VB_API int vb_trace_closest(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, const vb_hits_soa *out);
 VB_API int vb_trace_any(vb_ctx *ctx, const vb_rays_soa *rays, uint64_t n, uint8_t *occluded, vb_mem out_mem);
 /* vb_trace_closest with NO allocation. This entry point has no counterpart in the reference; it was added
