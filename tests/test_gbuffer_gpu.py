@@ -185,3 +185,15 @@ def test_render_graph_passes_match_oracle(vbctx, oracle):
     x = out[..., :3].astype(np.float64).clip(0, 1)                                    # sRGB OETF in double
     ref = np.where(x <= 0.0031308, 12.92 * x, 1.055 * x ** (1 / 2.4) - 0.055)
     assert np.abs(view[..., :3] - ref).max() < 1e-5
+
+
+def test_vision_cli_writes_every_aov_plane(tmp_path):
+    """vision-cli --aov prefix: one .pfm per G-buffer plane (normal, albedo, emission, geom, motion, gradient)"""
+    import subprocess
+    cli = str(ROOT / "vision_b200" / "vision-cli")
+    r = subprocess.run([cli, "-s", str(ROOT / "scenes" / "cbox" / "cbox_matte.json"), "-o", str(tmp_path / "o.png"), "--spp", "1",
+                        "--aov", str(tmp_path / "g")], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-500:]
+    for name in ("normal", "albedo", "emission", "geom", "motion", "gradient"):
+        f = tmp_path / f"g_{name}.pfm"
+        assert f.exists() and f.stat().st_size > 256 * 256 * 12, name

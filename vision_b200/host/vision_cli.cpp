@@ -74,10 +74,11 @@ int main(int argc, char **argv) {
             p->check(vb_film_download(p->ctx, acc.data(), VB_FILM_ACCUM), "vb_film_download");
             vh::save_pfm(pfm, acc.data(), p->records.width, p->records.height);
         }
-        if (!aov.empty()) {       // rt_geom's G-buffer planes of frame 0 (the denoiser inputs): <prefix>_normal.pfm, _albedo.pfm, _emission.pfm, _geom.pfm
+        if (!aov.empty()) {       // rt_geom's G-buffer planes of frame 0 (the denoiser inputs): <prefix>_normal.pfm, _albedo.pfm, _emission.pfm, _geom.pfm, _motion.pfm, _gradient.pfm
             std::vector<float> plane((size_t)p->records.width * p->records.height * 4);
-            const char *names[VB_AOV_COUNT] = {"normal", "albedo", "emission", "geom"};
+            const char *names[VB_AOV_COUNT] = {"normal", "albedo", "emission", "geom", "motion", "gradient"};
             p->check(vb_gbuffer_render(p->ctx, 0), "vb_gbuffer_render");
+            p->check(vb_gbuffer_gradient(p->ctx), "vb_gbuffer_gradient");
             for (int k = 0; k < VB_AOV_COUNT; ++k) {
                 p->check(vb_gbuffer_download(p->ctx, k, plane.data()), "vb_gbuffer_download");
                 vh::save_pfm(aov + "_" + names[k] + ".pfm", plane.data(), p->records.width, p->records.height);
