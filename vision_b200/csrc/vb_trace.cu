@@ -178,7 +178,10 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_MIN_BLOCKS) k_trace(VbAccel
 // Two-level structure ("build.two_level"): same arguments as k_trace, one ray per thread, grid-stride, vb_traverse_tl over this thread's
 // column of the shared stack. A kernel of its own so that the persistent flattened kernel above keeps its registers.
 template <bool ANY, bool COUNT>
-__global__ void __launch_bounds__(TRACE_BLOCK, 4) k_trace_tl(VbAccelView A, RaysDev R, uint64_t n, HitsDev H, uint8_t *occ,
+#ifndef VB_TL_MIN_BLOCKS
+#define VB_TL_MIN_BLOCKS 8      /* 64 registers: 4 -> 8 resident CTAs = +10..16 % (tools/bench_two_level.py) */
+#endif
+__global__ void __launch_bounds__(TRACE_BLOCK, VB_TL_MIN_BLOCKS) k_trace_tl(VbAccelView A, RaysDev R, uint64_t n, HitsDev H, uint8_t *occ,
                                                           unsigned long long *counters, unsigned long long *next_ray,
                                                           int REFILL_THR, int TRI_THR,
                                                           const float4 *__restrict__ RS, const uint32_t *__restrict__ perm, int perm_stride,
@@ -187,7 +190,11 @@ __global__ void __launch_bounds__(TRACE_BLOCK, 4) k_trace_tl(VbAccelView A, Rays
     const VbTrav V = vb_trav_init();
     const unsigned lane = threadIdx.x & 31u;
     uint32_t nn = 0, nt = 0;
-    for (uint64_t i = (uint64_t)blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += (uint64_t)gridDim.x * TRACE_BLOCK) {
+    // warp-uniform trip count, lanes re-converge after every ray (a lane that finished early would otherwise run the fetch / store code
+    // of its next ray divergently against the others' traversal)
+    for (uint64_t i0 = (uint64_t)blockIdx.x * TRACE_BLOCK + (threadIdx.x & ~31u); i0 < n; i0 += (uint64_t)gridDim.x * TRACE_BLOCK, __syncwarp()) {
+        const uint64_t i = i0 + lane;
+        if (i >= n) continue;
         uint64_t ri = i;
         VbRay r;
         if (RS) {
